@@ -1,0 +1,175 @@
+/*
+ * photon_ml_b200.h -- C ABI of the B200-native GLM objective-evaluation path.
+ *
+ * This is the drop-in boundary for Photon ML's DistributedGLMLossFunction /
+ * SingleNodeGLMLossFunction (value, gradient, Hessian-vector, Hessian-diagonal).  The reference
+ * has no FFI of its own (it is 100 % JVM); each entry point below names the Scala member whose
+ * body it replaces.  Paths: lib/ = photon-lib/src/main/scala/com/linkedin/photon/ml/,
+ * api/ = photon-api/src/main/scala/com/linkedin/photon/ml/.  The JNI stubs that bind these
+ * symbols from Scala are in INTEGRATION.md and jni/.
+ *
+ * Conventions
+ *  - every function returns 0 (PML_OK) or a PML_E* code; pml_last_error() gives the message of
+ *    the calling thread's last failure.  PML_EINVAL corresponds to the reference's `require`
+ *    failures (IllegalArgumentException); NaN/Inf in data are not errors and propagate.
+ *  - plain pointers and sizes only.  "host" pointers are ordinary CPU memory owned by the caller
+ *    and never retained; "dev" pointers are CUDA device memory on the context's device.
+ *  - one context = one GPU = one stream.  Calls on one context are serialised by the library
+ *    (internal mutex); different contexts may be used from different threads concurrently.
+ *  - host-pointer entry points are synchronous (results are in the caller's buffers on return).
+ *    *_dev entry points enqueue on the context's stream and return; use pml_ctx_synchronize().
+ *  - there is no CPU fallback: without a CUDA device pml_ctx_create fails with PML_ECUDA.
+ */
+#ifndef PHOTON_ML_B200_H
+#define PHOTON_ML_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PML_OK 0
+#define PML_EINVAL 1 /* a `require` of the reference failed: sizes, intercept factor/shift, ... */
+#define PML_ECUDA 2  /* CUDA runtime / launch failure, or no device */
+#define PML_ENOMEM 3 /* device or host allocation failed */
+#define PML_ESTATE 4 /* call sequence error (e.g. cached Hessian-vector without a prior pass) */
+
+/* PointwiseLossFunction family (lib/function/glm/PointwiseLossFunction.scala:36-54). */
+#define PML_LOSS_LOGISTIC 0       /* api/function/glm/LogisticLossFunction.scala:70-89 */
+#define PML_LOSS_POISSON 1        /* api/function/glm/PoissonLossFunction.scala:40-52 */
+#define PML_LOSS_SQUARED 2        /* api/function/glm/SquaredLossFunction.scala:42-54 */
+#define PML_LOSS_SMOOTHED_HINGE 3 /* api/function/svm/SmoothedHingeLossFunction.scala:40-84 */
+
+/* element type of the `values` array handed to pml_dataset_create_* */
+#define PML_F32 0
+#define PML_F64 1
+
+/* how feature values are stored in HBM */
+#define PML_STORE_F32 0  /* 4 B/value; PML_EINVAL if a value is not exactly representable */
+#define PML_STORE_F64 1  /* 8 B/value, bit-exact for any Double the reference could hold */
+#define PML_STORE_AUTO 2 /* F32 when every value survives the round trip, else F64 */
+
+typedef struct pml_ctx pml_ctx;
+typedef struct pml_dataset pml_dataset;
+
+typedef struct pml_dataset_info {
+    int64_t n;             /* rows */
+    int64_t nnz;           /* stored entries */
+    int32_t d;             /* feature dimension (incl. intercept column if any) */
+    int32_t value_bytes;   /* 4 or 8: what PML_STORE_* resolved to */
+    int32_t margin_variant; /* lanes per row of the CSR margin kernel; 0 = segment-per-warp */
+    int32_t n_chunks;      /* CSC chunks of the transpose kernel */
+    int64_t nonempty_cols; /* columns with at least one entry */
+    int64_t device_bytes;  /* HBM held by this data set */
+    int64_t vg_algorithmic_bytes; /* bytes one value+gradient evaluation must move */
+    int64_t hv_algorithmic_bytes; /* same for a cold Hessian-vector product */
+} pml_dataset_info;
+
+/* message of the calling thread's last failing call ("" if none) */
+const char *pml_last_error(void);
+
+/* ---- context: one GPU, one stream ------------------------------------------------------- */
+/* Replaces the SparkContext / treeAggregateDepth pair a DistributedObjectiveFunction is built
+ * with (api/function/DistributedObjectiveFunction.scala:34-39). */
+int pml_ctx_create(int device, pml_ctx **out);
+int pml_ctx_destroy(pml_ctx *ctx);
+int pml_ctx_synchronize(pml_ctx *ctx);
+/* the cudaStream_t the context launches on, for callers that order their own work after it */
+int pml_ctx_stream(pml_ctx *ctx, void **out_stream);
+/* pinned host buffers (what a JNI shim backs its direct ByteBuffers with) */
+int pml_host_alloc(void **out, int64_t bytes);
+int pml_host_free(void *p);
+
+/* ---- data set: LabeledPoint rows packed once into device CSR + CSC ------------------------ */
+/* Replaces RDD[LabeledPoint] / Iterable[LabeledPoint] as `Data`
+ * (api/function/DistributedObjectiveFunction.scala:36, SingleNodeObjectiveFunction.scala:27;
+ * row type lib/data/LabeledPoint.scala:32-36).  Rows need not be sorted by column and may
+ * repeat a column (Breeze SparseVector allows both); offsets NULL = 0, weights NULL = 1
+ * (lib/constants/MathConst.scala:24-25).  row_ptr has n+1 entries, row_ptr[0] == 0. */
+int pml_dataset_create_csr(pml_ctx *ctx, int64_t n, int32_t d, const int64_t *row_ptr,
+                           const int32_t *col_idx, const void *values, int values_dtype,
+                           int storage, const double *labels, const double *offsets,
+                           const double *weights, pml_dataset **out);
+/* same, all pointers in device memory (the arrays are copied; the caller keeps ownership) */
+int pml_dataset_create_csr_dev(pml_ctx *ctx, int64_t n, int32_t d, const int64_t *row_ptr_dev,
+                               const int32_t *col_idx_dev, const void *values_dev,
+                               int values_dtype, int storage, const double *labels_dev,
+                               const double *offsets_dev, const double *weights_dev,
+                               pml_dataset **out);
+int pml_dataset_destroy(pml_dataset *ds);
+int pml_dataset_get_info(const pml_dataset *ds, pml_dataset_info *out);
+
+/* Coordinate.updateModel re-offsets the data every coordinate-descent pass
+ * (lib/algorithm/Coordinate.scala:59-62, api/data/FixedEffectDataSet.scala:45-54): only the
+ * n offsets are uploaded, the packed matrix stays.  NULL restores 0 / 1. */
+int pml_dataset_set_offsets(pml_dataset *ds, const double *offsets);
+/* down-sampling re-weights rows (api/optimization/DistributedOptimizationProblem.scala:145-160) */
+int pml_dataset_set_weights(pml_dataset *ds, const double *weights);
+int pml_dataset_set_labels(pml_dataset *ds, const double *labels);
+/* NormalizationContext(factors, shifts, interceptId) (lib/normalization/
+ * NormalizationContext.scala:39-47); NULL = None, intercept_id -1 = None.  Fails with
+ * PML_EINVAL exactly where the reference's requires do: shifts without intercept (:44),
+ * factors[intercept] != 1 or shifts[intercept] != 0
+ * (lib/function/glm/ValueAndGradientAggregator.scala:96-99,109-112). */
+int pml_dataset_set_normalization(pml_dataset *ds, const double *factors, const double *shifts,
+                                  int32_t intercept_id);
+
+/* ---- evaluations, host buffers (the drop-in calls) ---------------------------------------- */
+/* DistributedGLMLossFunction.calculate (api/function/glm/DistributedGLMLossFunction.scala:93-102)
+ * and SingleNodeGLMLossFunction.calculate (SingleNodeGLMLossFunction.scala:83-91), i.e.
+ * ValueAndGradientAggregator.calculateValueAndGradient (lib/function/glm/
+ * ValueAndGradientAggregator.scala:235-274).  With PML_LOSS_SMOOTHED_HINGE it is
+ * DistributedSmoothedHingeLossFunction.calculate (api/function/svm/
+ * DistributedSmoothedHingeLossFunction.scala:84-103): normalization is ignored, as there.
+ * coef and out_grad have d entries; the sums are unregularised (L2 stays on the caller's side,
+ * lib/function/L2Regularization.scala:115-125).  out_grad may be NULL (value only:
+ * DistributedGLMLossFunction.value, :64-68). */
+int pml_value_and_gradient(pml_dataset *ds, int loss, const double *coef, double *out_value,
+                           double *out_grad);
+/* DistributedGLMLossFunction.hessianVector (:114-125) = HessianVectorAggregator.calcHessianVector
+ * (lib/function/glm/HessianVectorAggregator.scala:136-178).  coef_tag: 0 = stateless (as the
+ * reference: the margin pass is redone); non-zero = identity of the coefficient vector (the JNI
+ * shim passes the Broadcast id).  When the tag equals the previous call's, coef is not read
+ * again and the cached per-row wt*l''(z) is reused -- TRON's CG loop calls hessianVector up to
+ * 20 times at fixed coefficients (lib/optimization/TRON.scala:294-301). */
+int pml_hessian_vector(pml_dataset *ds, int loss, const double *coef, uint64_t coef_tag,
+                       const double *v, double *out_hv);
+/* DistributedGLMLossFunction.hessianDiagonal (:134-137) = HessianDiagonalAggregator
+ * (lib/function/glm/HessianDiagonalAggregator.scala:51-61,89-125); ignores normalization. */
+int pml_hessian_diagonal(pml_dataset *ds, int loss, const double *coef, double *out_diag);
+/* Coordinate scoring, score_i = x_i . coef (api/algorithm/FixedEffectCoordinate.scala:158-165,
+ * lib/model/Coefficients.scala:53-58): no offset, no normalization.  out_scores has n entries. */
+int pml_scores(pml_dataset *ds, const double *coef, double *out_scores);
+
+/* ---- evaluations, device buffers (resident pipelines and the multi-GPU split) -------------- */
+/* Raw partial sums of this data set's rows: out_raw_dev[0..d) = vectorSum, [d] = valueSum,
+ * [d+1] = vectorShiftPrefactorSum -- the fields ValueAndGradientAggregator.merge adds up
+ * (lib/function/glm/ValueAndGradientAggregator.scala:161-176).  With rows sharded over several
+ * GPUs the caller sums these d+2 doubles across ranks (one all-reduce; it replaces Spark's
+ * treeAggregate, :243-247) and then calls pml_finalize_dev once. */
+int pml_value_and_gradient_raw_dev(pml_dataset *ds, int loss, const double *coef_dev,
+                                   double *out_raw_dev);
+int pml_hessian_vector_raw_dev(pml_dataset *ds, int loss, const double *coef_dev,
+                               uint64_t coef_tag, const double *v_dev, double *out_raw_dev);
+/* ValueAndGradientAggregator.getVector (:199-221): out_j = (raw_j - shift_j * raw[d+1]) *
+ * factor_j; *out_value_dev = raw[d] (may be NULL).  `loss` only matters for the smoothed hinge
+ * (normalization ignored). */
+int pml_finalize_dev(pml_dataset *ds, int loss, const double *raw_dev, double *out_value_dev,
+                     double *out_vec_dev);
+/* single-GPU convenience: raw + finalize, everything on the device */
+int pml_value_and_gradient_dev(pml_dataset *ds, int loss, const double *coef_dev,
+                               double *out_value_dev, double *out_grad_dev);
+int pml_hessian_vector_dev(pml_dataset *ds, int loss, const double *coef_dev, uint64_t coef_tag,
+                           const double *v_dev, double *out_hv_dev);
+
+/* number of kernel launches this context has issued (bench.py's gpu_launches) */
+int pml_ctx_launch_count(pml_ctx *ctx, int64_t *out);
+/* force a CSR margin-kernel variant: lanes per row in {1? no: 2,4,8,16,32}, 0 = segment-per-warp,
+ * -1 = back to the nnz/row heuristic.  For benchmarking and tests. */
+int pml_dataset_set_margin_variant(pml_dataset *ds, int lanes_per_row);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PHOTON_ML_B200_H */

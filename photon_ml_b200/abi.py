@@ -1,0 +1,273 @@
+"""ctypes binding of include/photon_ml_b200.h -- the same symbols the JNI shim binds.
+
+There is no CPU fallback: loading fails loudly if the CUDA library has not been built, and
+Context() fails loudly if no CUDA device is visible.
+"""
+import ctypes
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "lib", "libphoton_ml_b200.so")
+
+OK, EINVAL, ECUDA, ENOMEM, ESTATE = 0, 1, 2, 3, 4
+LOGISTIC, POISSON, SQUARED, SMOOTHED_HINGE = 0, 1, 2, 3
+F32, F64 = 0, 1
+STORE_F32, STORE_F64, STORE_AUTO = 0, 1, 2
+
+# every symbol include/photon_ml_b200.h declares (tests check the library exports all of them)
+SYMBOLS = [
+    "pml_last_error", "pml_ctx_create", "pml_ctx_destroy", "pml_ctx_synchronize", "pml_ctx_stream",
+    "pml_host_alloc", "pml_host_free", "pml_dataset_create_csr", "pml_dataset_create_csr_dev",
+    "pml_dataset_destroy", "pml_dataset_get_info", "pml_dataset_set_offsets", "pml_dataset_set_weights",
+    "pml_dataset_set_labels", "pml_dataset_set_normalization", "pml_value_and_gradient", "pml_hessian_vector",
+    "pml_hessian_diagonal", "pml_scores", "pml_value_and_gradient_raw_dev", "pml_hessian_vector_raw_dev",
+    "pml_finalize_dev", "pml_value_and_gradient_dev", "pml_hessian_vector_dev", "pml_ctx_launch_count",
+    "pml_dataset_set_margin_variant",
+]
+
+
+class PhotonError(RuntimeError):
+    """PML_ECUDA / PML_ENOMEM / PML_ESTATE (a RuntimeException on the Scala side)."""
+
+    def __init__(self, code, message):
+        super().__init__("photon_ml_b200 error %d: %s" % (code, message))
+        self.code = code
+
+
+class IllegalArgumentError(ValueError):
+    """PML_EINVAL: a `require` of the reference failed (IllegalArgumentException in Scala)."""
+
+    code = EINVAL
+
+
+class DatasetInfo(ctypes.Structure):
+    _fields_ = [("n", ctypes.c_int64), ("nnz", ctypes.c_int64), ("d", ctypes.c_int32),
+                ("value_bytes", ctypes.c_int32), ("margin_variant", ctypes.c_int32), ("n_chunks", ctypes.c_int32),
+                ("nonempty_cols", ctypes.c_int64), ("device_bytes", ctypes.c_int64),
+                ("vg_algorithmic_bytes", ctypes.c_int64), ("hv_algorithmic_bytes", ctypes.c_int64)]
+
+
+_lib = None
+
+
+def load():
+    """dlopen the CUDA library (no compute happens here; safe without a GPU)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError("%s is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                          "(nvcc, sm_100a). There is no CPU fallback." % LIB_PATH)
+    lib = ctypes.CDLL(LIB_PATH)
+    vp, i32, i64, u64, dbl = ctypes.c_void_p, ctypes.c_int32, ctypes.c_int64, ctypes.c_uint64, ctypes.c_double
+    pp = ctypes.POINTER(vp)
+    lib.pml_last_error.restype = ctypes.c_char_p
+    lib.pml_last_error.argtypes = []
+    sigs = {
+        "pml_ctx_create": [ctypes.c_int, pp],
+        "pml_ctx_destroy": [vp],
+        "pml_ctx_synchronize": [vp],
+        "pml_ctx_stream": [vp, pp],
+        "pml_host_alloc": [pp, i64],
+        "pml_host_free": [vp],
+        "pml_dataset_create_csr": [vp, i64, i32, vp, vp, vp, ctypes.c_int, ctypes.c_int, vp, vp, vp, pp],
+        "pml_dataset_create_csr_dev": [vp, i64, i32, vp, vp, vp, ctypes.c_int, ctypes.c_int, vp, vp, vp, pp],
+        "pml_dataset_destroy": [vp],
+        "pml_dataset_get_info": [vp, ctypes.POINTER(DatasetInfo)],
+        "pml_dataset_set_offsets": [vp, vp],
+        "pml_dataset_set_weights": [vp, vp],
+        "pml_dataset_set_labels": [vp, vp],
+        "pml_dataset_set_normalization": [vp, vp, vp, i32],
+        "pml_value_and_gradient": [vp, ctypes.c_int, vp, ctypes.POINTER(dbl), vp],
+        "pml_hessian_vector": [vp, ctypes.c_int, vp, u64, vp, vp],
+        "pml_hessian_diagonal": [vp, ctypes.c_int, vp, vp],
+        "pml_scores": [vp, vp, vp],
+        "pml_value_and_gradient_raw_dev": [vp, ctypes.c_int, vp, vp],
+        "pml_hessian_vector_raw_dev": [vp, ctypes.c_int, vp, u64, vp, vp],
+        "pml_finalize_dev": [vp, ctypes.c_int, vp, vp, vp],
+        "pml_value_and_gradient_dev": [vp, ctypes.c_int, vp, vp, vp],
+        "pml_hessian_vector_dev": [vp, ctypes.c_int, vp, u64, vp, vp],
+        "pml_ctx_launch_count": [vp, ctypes.POINTER(i64)],
+        "pml_dataset_set_margin_variant": [vp, ctypes.c_int],
+    }
+    for name, argtypes in sigs.items():
+        fn = getattr(lib, name)
+        fn.restype = ctypes.c_int
+        fn.argtypes = argtypes
+    _lib = lib
+    return lib
+
+
+def check(rc):
+    if rc == OK:
+        return
+    msg = load().pml_last_error().decode("utf-8", "replace")
+    if rc == EINVAL:
+        raise IllegalArgumentError(msg)
+    raise PhotonError(rc, msg)
+
+
+def _np(a, dtype, size=None, name="array"):
+    if a is None:
+        return None
+    a = np.ascontiguousarray(a, dtype=dtype)
+    if size is not None and a.shape != (size,):
+        raise IllegalArgumentError("Size mismatch. %s size: %d != %d." % (name, a.size, size))
+    return a
+
+
+def _ptr(a):
+    return None if a is None else a.ctypes.data_as(ctypes.c_void_p)
+
+
+class Context:
+    """One GPU, one stream (pml_ctx)."""
+
+    def __init__(self, device=0):
+        self._h = ctypes.c_void_p()
+        check(load().pml_ctx_create(int(device), ctypes.byref(self._h)))
+        self.device = int(device)
+
+    def synchronize(self):
+        check(load().pml_ctx_synchronize(self._h))
+
+    @property
+    def stream(self):
+        s = ctypes.c_void_p()
+        check(load().pml_ctx_stream(self._h, ctypes.byref(s)))
+        return s.value or 0
+
+    @property
+    def launch_count(self):
+        v = ctypes.c_int64()
+        check(load().pml_ctx_launch_count(self._h, ctypes.byref(v)))
+        return v.value
+
+    def close(self):
+        if self._h:
+            load().pml_ctx_destroy(self._h)
+            self._h = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Dataset:
+    """LabeledPoint rows packed once into device CSR + CSC (pml_dataset)."""
+
+    def __init__(self, ctx, handle, keepalive=None):
+        self.ctx = ctx
+        self._h = handle
+        self._keep = keepalive
+        info = self.info()
+        self.n, self.d, self.nnz = info.n, info.d, info.nnz
+
+    @classmethod
+    def from_csr(cls, ctx, n, d, row_ptr, col, val, label, offset=None, weight=None, storage=STORE_AUTO):
+        row_ptr = _np(row_ptr, np.int64, n + 1, "row_ptr")
+        col = _np(col, np.int32)
+        val = np.ascontiguousarray(val)
+        if val.dtype == np.float32:
+            dtype = F32
+        else:
+            val = val.astype(np.float64, copy=False)
+            dtype = F64
+        label = _np(label, np.float64, n, "labels")
+        offset = _np(offset, np.float64, n, "offsets")
+        weight = _np(weight, np.float64, n, "weights")
+        h = ctypes.c_void_p()
+        check(load().pml_dataset_create_csr(ctx._h, n, d, _ptr(row_ptr), _ptr(col), _ptr(val), dtype, storage,
+                                            _ptr(label), _ptr(offset), _ptr(weight), ctypes.byref(h)))
+        return cls(ctx, h)
+
+    @classmethod
+    def from_device_pointers(cls, ctx, n, d, row_ptr_dev, col_dev, val_dev, values_dtype, label_dev, offset_dev=None,
+                             weight_dev=None, storage=STORE_AUTO):
+        """All arguments are integer device addresses (e.g. torch.Tensor.data_ptr())."""
+        h = ctypes.c_void_p()
+        check(load().pml_dataset_create_csr_dev(ctx._h, n, d, row_ptr_dev, col_dev, val_dev, values_dtype, storage,
+                                                label_dev, offset_dev, weight_dev, ctypes.byref(h)))
+        return cls(ctx, h)
+
+    def info(self):
+        out = DatasetInfo()
+        check(load().pml_dataset_get_info(self._h, ctypes.byref(out)))
+        return out
+
+    def set_offsets(self, offsets):
+        check(load().pml_dataset_set_offsets(self._h, _ptr(_np(offsets, np.float64, self.n, "offsets"))))
+
+    def set_weights(self, weights):
+        check(load().pml_dataset_set_weights(self._h, _ptr(_np(weights, np.float64, self.n, "weights"))))
+
+    def set_labels(self, labels):
+        check(load().pml_dataset_set_labels(self._h, _ptr(_np(labels, np.float64, self.n, "labels"))))
+
+    def set_normalization(self, factors=None, shifts=None, intercept=None):
+        f = _np(factors, np.float64, self.d, "Factors vector")
+        s = _np(shifts, np.float64, self.d, "Shifts vector")
+        check(load().pml_dataset_set_normalization(self._h, _ptr(f), _ptr(s), -1 if intercept is None else int(intercept)))
+
+    def set_margin_variant(self, lanes_per_row):
+        check(load().pml_dataset_set_margin_variant(self._h, int(lanes_per_row)))
+
+    # ---- host-buffer evaluations -------------------------------------------------------------
+    def value_and_gradient(self, loss, coef, want_gradient=True, out=None):
+        coef = _np(coef, np.float64, self.d, "Coefficient")
+        value = ctypes.c_double()
+        grad = None
+        if want_gradient:
+            grad = out if out is not None else np.empty(self.d, dtype=np.float64)
+        check(load().pml_value_and_gradient(self._h, loss, _ptr(coef), ctypes.byref(value), _ptr(grad)))
+        return value.value, grad
+
+    def hessian_vector(self, loss, coef, v, tag=0, out=None):
+        coef = _np(coef, np.float64, self.d, "Coefficient")
+        v = _np(v, np.float64, self.d, "Multiply vector")
+        hv = out if out is not None else np.empty(self.d, dtype=np.float64)
+        check(load().pml_hessian_vector(self._h, loss, _ptr(coef), int(tag), _ptr(v), _ptr(hv)))
+        return hv
+
+    def hessian_diagonal(self, loss, coef):
+        coef = _np(coef, np.float64, self.d, "Coefficient")
+        diag = np.empty(self.d, dtype=np.float64)
+        check(load().pml_hessian_diagonal(self._h, loss, _ptr(coef), _ptr(diag)))
+        return diag
+
+    def scores(self, coef):
+        coef = _np(coef, np.float64, self.d, "Coefficient")
+        out = np.empty(self.n, dtype=np.float64)
+        check(load().pml_scores(self._h, _ptr(coef), _ptr(out)))
+        return out
+
+    # ---- device-buffer evaluations (integer device addresses) --------------------------------
+    def value_and_gradient_raw_dev(self, loss, coef_dev, out_raw_dev):
+        check(load().pml_value_and_gradient_raw_dev(self._h, loss, coef_dev, out_raw_dev))
+
+    def hessian_vector_raw_dev(self, loss, coef_dev, v_dev, out_raw_dev, tag=0):
+        check(load().pml_hessian_vector_raw_dev(self._h, loss, coef_dev, int(tag), v_dev, out_raw_dev))
+
+    def finalize_dev(self, loss, raw_dev, out_value_dev, out_vec_dev):
+        check(load().pml_finalize_dev(self._h, loss, raw_dev, out_value_dev, out_vec_dev))
+
+    def value_and_gradient_dev(self, loss, coef_dev, out_value_dev, out_grad_dev):
+        check(load().pml_value_and_gradient_dev(self._h, loss, coef_dev, out_value_dev, out_grad_dev))
+
+    def hessian_vector_dev(self, loss, coef_dev, v_dev, out_hv_dev, tag=0):
+        check(load().pml_hessian_vector_dev(self._h, loss, coef_dev, int(tag), v_dev, out_hv_dev))
+
+    def close(self):
+        if self._h:
+            load().pml_dataset_destroy(self._h)
+            self._h = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -1,0 +1,714 @@
+// api.cu -- the C ABI of include/photon_ml_b200.h: contexts, packed data sets, and the
+// evaluation entry points that string the kernels of kernels.cu together.
+#include <cuda_runtime.h>
+
+#include <cstring>
+#include <new>
+#include <string>
+
+#include "internal.h"
+
+namespace pml {
+
+static thread_local std::string g_error;
+
+void set_error(const std::string &msg) { g_error = msg; }
+
+int fail(int code, const std::string &msg)
+{
+    g_error = msg;
+    return code;
+}
+
+namespace {
+
+struct TmpDev {
+    void *p = nullptr;
+    ~TmpDev() { if (p) cudaFree(p); }
+};
+
+template <typename T>
+int dev_alloc(T **out, size_t count, int64_t *bytes)
+{
+    void *p = nullptr;
+    const size_t b = (count ? count : 1) * sizeof(T);
+    cudaError_t e = cudaMalloc(&p, b);
+    if (e != cudaSuccess) return fail(PML_ENOMEM, std::string("cudaMalloc of ") + std::to_string(b) + " bytes: " + cudaGetErrorString(e));
+    *out = static_cast<T *>(p);
+    if (bytes) *bytes += (int64_t)b;
+    return PML_OK;
+}
+
+int upload_optional(cudaStream_t s, double **slot, const double *src, int64_t n, bool from_device, int64_t *bytes)
+{
+    if (src == nullptr) {
+        if (*slot) {
+            cudaFree(*slot);
+            *slot = nullptr;
+            if (bytes) *bytes -= n * 8;
+        }
+        return PML_OK;
+    }
+    if (*slot == nullptr) PML_TRY(dev_alloc(slot, (size_t)n, bytes));
+    if (n > 0) {
+        PML_CUDA(cudaMemcpyAsync(*slot, src, sizeof(double) * (size_t)n,
+                                 from_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, s));
+        PML_CUDA(cudaStreamSynchronize(s));
+    }
+    return PML_OK;
+}
+
+// nnz/row -> CSR margin-kernel variant (DESIGN.md "row pass variants")
+int pick_variant(int64_t n, int64_t nnz)
+{
+    const double mean = n > 0 ? (double)nnz / (double)n : 0.0;
+    if (mean <= 24.0) return 0;  // segment-per-warp
+    if (mean <= 48.0) return 4;
+    if (mean <= 96.0) return 8;
+    if (mean <= 256.0) return 16;
+    return 32;
+}
+
+bool valid_loss(int loss) { return loss >= PML_LOSS_LOGISTIC && loss <= PML_LOSS_SMOOTHED_HINGE; }
+
+struct Guard {
+    pml_ctx *ctx;
+    explicit Guard(pml_ctx *c) : ctx(c) { ctx->mu.lock(); }
+    ~Guard() { ctx->mu.unlock(); }
+};
+
+int count(pml_ctx *ctx, int launched)
+{
+    if (launched < 0) {
+        cudaError_t e = cudaGetLastError();
+        return fail(PML_ECUDA, std::string("kernel launch failed: ") + cudaGetErrorString(e));
+    }
+    ctx->launches += launched;
+    return PML_OK;
+}
+
+// -------------------------------------------------------------------------------------------
+// evaluation pipelines (device pointers; the caller holds the context lock)
+// -------------------------------------------------------------------------------------------
+int run_col_and_fixup(pml_dataset *ds, bool square, double *out, bool with_scalars, bool write_value)
+{
+    pml_ctx *ctx = ds->ctx;
+    cudaStream_t s = ctx->stream;
+    ColPassParams cp;
+    cp.nnz = ds->nnz;
+    cp.row = ds->t.csc_row;
+    cp.val = ds->t.csc_val;
+    cp.nzcol_ptr = ds->t.nzcol_ptr;
+    cp.nzcol_id = ds->t.nzcol_id;
+    cp.chunk_col_lo = ds->t.chunk_col_lo;
+    cp.r = ds->r;
+    cp.out = out;
+    cp.carry_head = ds->carry_head;
+    cp.n_chunks = ds->t.n_chunks;
+    PML_TRY(count(ctx, launch_col_pass(s, ds->value_bytes, square, cp)));
+    PML_TRY(count(ctx, launch_fixup(s, ds->t.fix, ds->t.n_fix, ds->carry_head, out, ds->d,
+                                    with_scalars ? ds->partials : nullptr, ds->row_grid, write_value, true)));
+    return PML_OK;
+}
+
+int vg_raw(pml_dataset *ds, int loss, const double *coef_dev, double *out_raw_dev)
+{
+    pml_ctx *ctx = ds->ctx;
+    cudaStream_t s = ctx->stream;
+    const bool hinge = loss == PML_LOSS_SMOOTHED_HINGE;  // ignores normalization (SmoothedHingeLossFunction.scala:73-84)
+    const bool norm = !hinge && (ds->factors || ds->shifts);
+    RowPassParams rp;
+    std::memset(&rp, 0, sizeof(rp));
+    rp.vec = coef_dev;
+    if (norm) {
+        int np = 0;
+        PML_TRY(count(ctx, launch_prepare_vectors(s, ds->d, coef_dev, nullptr, ds->factors, ds->shifts, ds->vec,
+                                                  ds->shift_partials, &np)));
+        rp.vec = ds->vec;
+        if (ds->shifts) {
+            rp.shift_partials = ds->shift_partials;
+            rp.n_shift_partials = np;
+        }
+    }
+    PML_CUDA(cudaMemsetAsync(out_raw_dev, 0, sizeof(double) * (size_t)(ds->d + 2), s));
+    rp.n = ds->n;
+    rp.row_ptr = ds->row_ptr;
+    rp.col = ds->col;
+    rp.val = ds->val;
+    rp.label = ds->label;
+    rp.offset = ds->offset;
+    rp.weight = ds->weight;
+    rp.r = ds->r;
+    rp.partials = ds->partials;
+    rp.mode = MODE_VG;
+    rp.loss = loss;
+    PML_TRY(count(ctx, launch_row_pass(s, ctx->sm_count, ds->value_bytes, ds->lanes_per_row, false, rp, &ds->row_grid)));
+    return run_col_and_fixup(ds, false, out_raw_dev, true, true);
+}
+
+int hv_raw(pml_dataset *ds, int loss, const double *coef_dev, uint64_t tag, const double *v_dev, double *out_raw_dev)
+{
+    pml_ctx *ctx = ds->ctx;
+    cudaStream_t s = ctx->stream;
+    if (loss == PML_LOSS_SMOOTHED_HINGE)
+        return fail(PML_EINVAL, "the smoothed hinge loss is not twice differentiable (it only implements DiffFunction)");
+    const bool norm = ds->factors || ds->shifts;
+    const bool cached = tag != 0 && ds->cache_valid && ds->cached_tag == tag && ds->cached_loss == loss;
+    RowPassParams rp;
+    std::memset(&rp, 0, sizeof(rp));
+    rp.n = ds->n;
+    rp.row_ptr = ds->row_ptr;
+    rp.col = ds->col;
+    rp.val = ds->val;
+    rp.label = ds->label;
+    rp.offset = ds->offset;
+    rp.weight = ds->weight;
+    rp.r = ds->r;
+    rp.partials = ds->partials;
+    rp.loss = loss;
+    int np = 0;
+    if (!cached) {
+        if (coef_dev == nullptr) return fail(PML_EINVAL, "coefficients are required when no cached pass matches the tag");
+        if (tag != 0 && ds->dcache == nullptr) PML_TRY(dev_alloc(&ds->dcache, (size_t)ds->n, &ds->bytes));
+        PML_TRY(count(ctx, launch_prepare_vectors(s, ds->d, coef_dev, v_dev, ds->factors, ds->shifts, ds->vec,
+                                                  ds->shift_partials, &np)));
+        rp.vec = ds->vec;
+        if (ds->shifts) {
+            rp.shift_partials = ds->shift_partials;
+            rp.n_shift_partials = np;
+        }
+        rp.dcache = tag != 0 ? ds->dcache : nullptr;
+        rp.mode = MODE_HV_COLD;
+        PML_TRY(count(ctx, launch_row_pass(s, ctx->sm_count, ds->value_bytes, ds->lanes_per_row, true, rp, &ds->row_grid)));
+        ds->cache_valid = tag != 0;
+        ds->cached_tag = tag;
+        ds->cached_loss = loss;
+    } else {
+        rp.vec = v_dev;
+        if (norm) {
+            PML_TRY(count(ctx, launch_prepare_vectors(s, ds->d, v_dev, nullptr, ds->factors, ds->shifts, ds->vec,
+                                                      ds->shift_partials, &np)));
+            rp.vec = ds->vec;
+            if (ds->shifts) {
+                rp.shift_partials = ds->shift_partials;
+                rp.n_shift_partials = np;
+            }
+        }
+        rp.dcache = ds->dcache;
+        rp.mode = MODE_HV_CACHED;
+        PML_TRY(count(ctx, launch_row_pass(s, ctx->sm_count, ds->value_bytes, ds->lanes_per_row, false, rp, &ds->row_grid)));
+    }
+    PML_CUDA(cudaMemsetAsync(out_raw_dev, 0, sizeof(double) * (size_t)(ds->d + 2), s));
+    return run_col_and_fixup(ds, false, out_raw_dev, true, false);
+}
+
+int finalize(pml_dataset *ds, int loss, const double *raw_dev, double *out_value_dev, double *out_vec_dev)
+{
+    pml_ctx *ctx = ds->ctx;
+    const bool hinge = loss == PML_LOSS_SMOOTHED_HINGE;
+    return count(ctx, launch_finalize(ctx->stream, ds->d, raw_dev, hinge ? nullptr : ds->factors,
+                                      hinge ? nullptr : ds->shifts, out_value_dev, out_vec_dev));
+}
+
+int diag_dev(pml_dataset *ds, int loss, const double *coef_dev, double *out_dev /* d+2 */)
+{
+    pml_ctx *ctx = ds->ctx;
+    cudaStream_t s = ctx->stream;
+    if (loss == PML_LOSS_SMOOTHED_HINGE)
+        return fail(PML_EINVAL, "the smoothed hinge loss is not twice differentiable (it only implements DiffFunction)");
+    RowPassParams rp;
+    std::memset(&rp, 0, sizeof(rp));
+    rp.n = ds->n;
+    rp.row_ptr = ds->row_ptr;
+    rp.col = ds->col;
+    rp.val = ds->val;
+    rp.label = ds->label;
+    rp.offset = ds->offset;
+    rp.weight = ds->weight;
+    rp.r = ds->r;
+    rp.vec = coef_dev;
+    rp.mode = MODE_DIAG;
+    rp.loss = loss;
+    PML_TRY(count(ctx, launch_row_pass(s, ctx->sm_count, ds->value_bytes, ds->lanes_per_row, false, rp, &ds->row_grid)));
+    PML_CUDA(cudaMemsetAsync(out_dev, 0, sizeof(double) * (size_t)(ds->d + 2), s));
+    return run_col_and_fixup(ds, true, out_dev, false, false);
+}
+
+int check_ds(const pml_dataset *ds)
+{
+    if (ds == nullptr || ds->ctx == nullptr) return fail(PML_EINVAL, "null data set handle");
+    return PML_OK;
+}
+
+}  // namespace
+}  // namespace pml
+
+using namespace pml;
+
+// ===========================================================================================
+extern "C" {
+
+const char *pml_last_error(void) { return g_error.c_str(); }
+
+int pml_ctx_create(int device, pml_ctx **out)
+{
+    if (out == nullptr) return fail(PML_EINVAL, "out is null");
+    *out = nullptr;
+    int n_dev = 0;
+    cudaError_t e = cudaGetDeviceCount(&n_dev);
+    if (e != cudaSuccess || n_dev == 0)
+        return fail(PML_ECUDA, std::string("no CUDA device available (there is no CPU fallback): ") + cudaGetErrorString(e));
+    if (device < 0 || device >= n_dev) return fail(PML_EINVAL, "device index out of range");
+    PML_CUDA(cudaSetDevice(device));
+    pml_ctx *ctx = new (std::nothrow) pml_ctx();
+    if (!ctx) return fail(PML_ENOMEM, "host allocation failed");
+    ctx->device = device;
+    cudaDeviceProp prop;
+    PML_CUDA(cudaGetDeviceProperties(&prop, device));
+    ctx->sm_count = prop.multiProcessorCount;
+    if (prop.major < 10) {
+        delete ctx;
+        return fail(PML_ECUDA, "this library is built for sm_100a (B200) only");
+    }
+    PML_CUDA(cudaStreamCreate(&ctx->stream));
+    PML_CUDA(cudaMallocHost(&ctx->h_scalar, 64));
+    *out = ctx;
+    return PML_OK;
+}
+
+int pml_ctx_destroy(pml_ctx *ctx)
+{
+    if (!ctx) return PML_OK;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    cudaStreamDestroy(ctx->stream);
+    cudaFreeHost(ctx->h_scalar);
+    delete ctx;
+    return PML_OK;
+}
+
+int pml_ctx_synchronize(pml_ctx *ctx)
+{
+    if (!ctx) return fail(PML_EINVAL, "null context");
+    PML_CUDA(cudaSetDevice(ctx->device));
+    PML_CUDA(cudaStreamSynchronize(ctx->stream));
+    return PML_OK;
+}
+
+int pml_ctx_stream(pml_ctx *ctx, void **out_stream)
+{
+    if (!ctx || !out_stream) return fail(PML_EINVAL, "null argument");
+    *out_stream = (void *)ctx->stream;
+    return PML_OK;
+}
+
+int pml_ctx_launch_count(pml_ctx *ctx, int64_t *out)
+{
+    if (!ctx || !out) return fail(PML_EINVAL, "null argument");
+    *out = ctx->launches;
+    return PML_OK;
+}
+
+int pml_host_alloc(void **out, int64_t bytes)
+{
+    if (!out || bytes < 0) return fail(PML_EINVAL, "bad argument");
+    PML_CUDA(cudaMallocHost(out, (size_t)(bytes ? bytes : 1)));
+    return PML_OK;
+}
+
+int pml_host_free(void *p)
+{
+    if (p) PML_CUDA(cudaFreeHost(p));
+    return PML_OK;
+}
+
+int pml_dataset_destroy(pml_dataset *ds)
+{
+    if (!ds) return PML_OK;
+    if (ds->ctx) {
+        cudaSetDevice(ds->ctx->device);
+        cudaStreamSynchronize(ds->ctx->stream);
+    }
+    void *ptrs[] = { ds->row_ptr, ds->col, ds->val, ds->label, ds->offset, ds->weight, ds->t.csc_row, ds->t.csc_val,
+                     ds->t.nzcol_ptr, ds->t.nzcol_id, ds->t.chunk_col_lo, ds->t.fix, ds->factors, ds->shifts, ds->r,
+                     ds->dcache, ds->partials, ds->carry_head, ds->raw, ds->vec, ds->shift_partials, ds->io_a, ds->io_b,
+                     ds->io_n };
+    for (void *p : ptrs)
+        if (p) cudaFree(p);
+    delete ds;
+    return PML_OK;
+}
+
+int pml_dataset_create_csr_dev(pml_ctx *ctx, int64_t n, int32_t d, const int64_t *row_ptr_dev,
+                               const int32_t *col_idx_dev, const void *values_dev, int values_dtype,
+                               int storage, const double *labels_dev, const double *offsets_dev,
+                               const double *weights_dev, pml_dataset **out)
+{
+    if (!ctx || !out) return fail(PML_EINVAL, "null argument");
+    *out = nullptr;
+    if (n < 0 || d < 0) return fail(PML_EINVAL, "negative size");
+    if (n > 0 && (!row_ptr_dev || !labels_dev)) return fail(PML_EINVAL, "row_ptr and labels are required");
+    if (values_dtype != PML_F32 && values_dtype != PML_F64) return fail(PML_EINVAL, "values_dtype must be PML_F32 or PML_F64");
+    if (storage < PML_STORE_F32 || storage > PML_STORE_AUTO) return fail(PML_EINVAL, "unknown storage mode");
+    Guard g(ctx);
+    PML_CUDA(cudaSetDevice(ctx->device));
+    cudaStream_t s = ctx->stream;
+
+    pml_dataset *ds = new (std::nothrow) pml_dataset();
+    if (!ds) return fail(PML_ENOMEM, "host allocation failed");
+    ds->ctx = ctx;
+    ds->n = n;
+    ds->d = d;
+    struct Cleanup {
+        pml_dataset *ds;
+        pml_ctx *ctx;
+        ~Cleanup() {
+            if (ds) {
+                // pml_dataset_destroy takes no lock, so it is safe under the Guard
+                pml_dataset_destroy(ds);
+            }
+        }
+    } cleanup{ ds, ctx };
+
+    PML_TRY(dev_alloc(&ds->row_ptr, (size_t)n + 1, &ds->bytes));
+    if (n > 0) {
+        int64_t bad = 0;
+        PML_TRY(convert_row_ptr(s, row_ptr_dev, ds->row_ptr, n + 1, &bad));
+        if (bad) return fail(PML_EINVAL, "row_ptr must start at 0, be non-decreasing and stay below 4e9 entries per device");
+        uint32_t last = 0;
+        PML_CUDA(cudaMemcpyAsync(&last, ds->row_ptr + n, sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+        PML_CUDA(cudaStreamSynchronize(s));
+        ds->nnz = last;
+    } else {
+        PML_CUDA(cudaMemsetAsync(ds->row_ptr, 0, sizeof(uint32_t), s));
+        ds->nnz = 0;
+    }
+    const int64_t nnz = ds->nnz;
+    if (nnz > 0 && (!col_idx_dev || !values_dev)) return fail(PML_EINVAL, "col_idx and values are required");
+    if (nnz > 0 && d == 0) return fail(PML_EINVAL, "entries present but d == 0");
+
+    int64_t bad_cols = 0;
+    PML_TRY(check_columns(s, col_idx_dev, nnz, d, &bad_cols));
+    if (bad_cols)  // features.size == dim (ValueAndGradientAggregator.scala:141-143)
+        return fail(PML_EINVAL, "column index outside [0, d): " + std::to_string(bad_cols) + " entries");
+
+    const int src_bytes = values_dtype == PML_F32 ? 4 : 8;
+    int dst_bytes = src_bytes;
+    if (storage == PML_STORE_F64) dst_bytes = 8;
+    else if (src_bytes == 8) {
+        bool exact = true;
+        PML_TRY(narrow_check(s, static_cast<const double *>(values_dev), nnz, &exact));
+        if (exact) dst_bytes = 4;
+        else if (storage == PML_STORE_F32)
+            return fail(PML_EINVAL, "PML_STORE_F32 requested but some values are not exactly representable in fp32; "
+                                    "use PML_STORE_F64 or PML_STORE_AUTO");
+    }
+    ds->value_bytes = dst_bytes;
+
+    PML_TRY(dev_alloc(&ds->col, (size_t)nnz + 4, &ds->bytes));
+    {
+        void *v = nullptr;
+        cudaError_t e = cudaMalloc(&v, (size_t)(nnz + 4) * dst_bytes);
+        if (e != cudaSuccess) return fail(PML_ENOMEM, std::string("cudaMalloc values: ") + cudaGetErrorString(e));
+        ds->val = v;
+        ds->bytes += (nnz + 4) * dst_bytes;
+    }
+    if (nnz > 0) {
+        PML_CUDA(cudaMemcpyAsync(ds->col, col_idx_dev, sizeof(int32_t) * (size_t)nnz, cudaMemcpyDeviceToDevice, s));
+        PML_TRY(convert_values(s, values_dev, src_bytes, ds->val, dst_bytes, nnz));
+    }
+    PML_TRY(upload_optional(s, &ds->label, n > 0 ? labels_dev : nullptr, n, true, &ds->bytes));
+    if (ds->label == nullptr) PML_TRY(dev_alloc(&ds->label, 1, &ds->bytes));
+    PML_TRY(upload_optional(s, &ds->offset, offsets_dev, n, true, &ds->bytes));
+    PML_TRY(upload_optional(s, &ds->weight, weights_dev, n, true, &ds->bytes));
+
+    PML_TRY(build_transpose(s, n, d, nnz, ds->row_ptr, ds->col, ds->val, dst_bytes, &ds->t));
+    ds->bytes += ds->t.bytes;
+
+    PML_TRY(dev_alloc(&ds->r, (size_t)n, &ds->bytes));
+    PML_TRY(dev_alloc(&ds->partials, 2 * (size_t)MAX_PARTIALS, &ds->bytes));
+    PML_TRY(dev_alloc(&ds->shift_partials, 2 * (size_t)MAX_PARTIALS, &ds->bytes));
+    PML_TRY(dev_alloc(&ds->carry_head, (size_t)ds->t.n_chunks + 1, &ds->bytes));
+    PML_TRY(dev_alloc(&ds->raw, (size_t)d + 2, &ds->bytes));
+    PML_TRY(dev_alloc(&ds->vec, 2 * (size_t)d + 2, &ds->bytes));
+    PML_TRY(dev_alloc(&ds->io_a, (size_t)d + 2, &ds->bytes));
+    PML_TRY(dev_alloc(&ds->io_b, (size_t)d + 2, &ds->bytes));
+    ds->lanes_per_row = pick_variant(n, nnz);
+    PML_CUDA(cudaStreamSynchronize(s));
+    cleanup.ds = nullptr;
+    *out = ds;
+    return PML_OK;
+}
+
+int pml_dataset_create_csr(pml_ctx *ctx, int64_t n, int32_t d, const int64_t *row_ptr, const int32_t *col_idx,
+                           const void *values, int values_dtype, int storage, const double *labels,
+                           const double *offsets, const double *weights, pml_dataset **out)
+{
+    if (!ctx || !out) return fail(PML_EINVAL, "null argument");
+    *out = nullptr;
+    if (n < 0 || d < 0) return fail(PML_EINVAL, "negative size");
+    if (n > 0 && (!row_ptr || !labels)) return fail(PML_EINVAL, "row_ptr and labels are required");
+    if (values_dtype != PML_F32 && values_dtype != PML_F64) return fail(PML_EINVAL, "values_dtype must be PML_F32 or PML_F64");
+    const int64_t nnz = n > 0 ? row_ptr[n] : 0;
+    if (n > 0 && (row_ptr[0] != 0 || nnz < 0)) return fail(PML_EINVAL, "row_ptr must start at 0 and be non-decreasing");
+    if (nnz > 0 && (!col_idx || !values)) return fail(PML_EINVAL, "col_idx and values are required");
+    const int vb = values_dtype == PML_F32 ? 4 : 8;
+    TmpDev t_rp, t_col, t_val, t_lab, t_off, t_wt;
+    {
+        Guard g(ctx);
+        PML_CUDA(cudaSetDevice(ctx->device));
+        PML_CUDA(cudaMalloc(&t_rp.p, sizeof(int64_t) * (size_t)(n + 1)));
+        PML_CUDA(cudaMalloc(&t_col.p, sizeof(int32_t) * (size_t)(nnz + 1)));
+        PML_CUDA(cudaMalloc(&t_val.p, (size_t)vb * (size_t)(nnz + 1)));
+        PML_CUDA(cudaMalloc(&t_lab.p, sizeof(double) * (size_t)(n + 1)));
+        if (n > 0) {
+            PML_CUDA(cudaMemcpy(t_rp.p, row_ptr, sizeof(int64_t) * (size_t)(n + 1), cudaMemcpyHostToDevice));
+            PML_CUDA(cudaMemcpy(t_lab.p, labels, sizeof(double) * (size_t)n, cudaMemcpyHostToDevice));
+        }
+        if (nnz > 0) {
+            PML_CUDA(cudaMemcpy(t_col.p, col_idx, sizeof(int32_t) * (size_t)nnz, cudaMemcpyHostToDevice));
+            PML_CUDA(cudaMemcpy(t_val.p, values, (size_t)vb * (size_t)nnz, cudaMemcpyHostToDevice));
+        }
+        if (offsets && n > 0) {
+            PML_CUDA(cudaMalloc(&t_off.p, sizeof(double) * (size_t)n));
+            PML_CUDA(cudaMemcpy(t_off.p, offsets, sizeof(double) * (size_t)n, cudaMemcpyHostToDevice));
+        }
+        if (weights && n > 0) {
+            PML_CUDA(cudaMalloc(&t_wt.p, sizeof(double) * (size_t)n));
+            PML_CUDA(cudaMemcpy(t_wt.p, weights, sizeof(double) * (size_t)n, cudaMemcpyHostToDevice));
+        }
+    }
+    return pml_dataset_create_csr_dev(ctx, n, d, (const int64_t *)t_rp.p, (const int32_t *)t_col.p, t_val.p, values_dtype,
+                                      storage, (const double *)t_lab.p, (const double *)t_off.p, (const double *)t_wt.p,
+                                      out);
+}
+
+int pml_dataset_get_info(const pml_dataset *ds, pml_dataset_info *out)
+{
+    PML_TRY(check_ds(ds));
+    if (!out) return fail(PML_EINVAL, "out is null");
+    out->n = ds->n;
+    out->nnz = ds->nnz;
+    out->d = ds->d;
+    out->value_bytes = ds->value_bytes;
+    out->margin_variant = ds->lanes_per_row;
+    out->n_chunks = ds->t.n_chunks;
+    out->nonempty_cols = ds->t.m;
+    out->device_bytes = ds->bytes;
+    const int64_t V = ds->value_bytes, n = ds->n, d = ds->d, nnz = ds->nnz;
+    // CSR stream + CSC stream + (y, o, wt) + r written and read + pointers + (read w, write g)
+    out->vg_algorithmic_bytes = 2 * nnz * (V + 4) + n * 24 + n * 16 + (n + 1) * 4 + ((int64_t)d + 1) * 4 + (int64_t)d * 16;
+    out->hv_algorithmic_bytes = 2 * nnz * (V + 4) + n * 16 + n * 16 + (n + 1) * 4 + ((int64_t)d + 1) * 4 + (int64_t)d * 24;
+    return PML_OK;
+}
+
+static int set_rows(pml_dataset *ds, double **slot, const double *src, bool required)
+{
+    PML_TRY(check_ds(ds));
+    if (required && !src && ds->n > 0) return fail(PML_EINVAL, "null array");
+    Guard g(ds->ctx);
+    PML_CUDA(cudaSetDevice(ds->ctx->device));
+    ds->cache_valid = false;
+    return upload_optional(ds->ctx->stream, slot, src, ds->n, false, &ds->bytes);
+}
+
+int pml_dataset_set_offsets(pml_dataset *ds, const double *offsets) { return ds ? set_rows(ds, &ds->offset, offsets, false) : check_ds(ds); }
+int pml_dataset_set_weights(pml_dataset *ds, const double *weights) { return ds ? set_rows(ds, &ds->weight, weights, false) : check_ds(ds); }
+int pml_dataset_set_labels(pml_dataset *ds, const double *labels) { return ds ? set_rows(ds, &ds->label, labels, true) : check_ds(ds); }
+
+int pml_dataset_set_normalization(pml_dataset *ds, const double *factors, const double *shifts, int32_t intercept_id)
+{
+    PML_TRY(check_ds(ds));
+    if (intercept_id < -1 || intercept_id >= ds->d) return fail(PML_EINVAL, "intercept id outside [0, d)");
+    if (shifts && intercept_id < 0) return fail(PML_EINVAL, "Shift without intercept is illegal.");
+    if (factors && intercept_id >= 0 && factors[intercept_id] != 1.0)
+        return fail(PML_EINVAL, "The intercept should not be transformed. Intercept scaling factor: " +
+                                    std::to_string(factors[intercept_id]));
+    if (shifts && intercept_id >= 0 && shifts[intercept_id] != 0.0)
+        return fail(PML_EINVAL, "The intercept should not be transformed. Intercept shift: " + std::to_string(shifts[intercept_id]));
+    Guard g(ds->ctx);
+    PML_CUDA(cudaSetDevice(ds->ctx->device));
+    ds->cache_valid = false;
+    ds->intercept = intercept_id;
+    cudaStream_t s = ds->ctx->stream;
+    auto put = [&](double **slot, const double *src) -> int {
+        if (!src) {
+            if (*slot) { cudaFree(*slot); *slot = nullptr; }
+            return PML_OK;
+        }
+        if (!*slot) PML_TRY(dev_alloc(slot, (size_t)ds->d, &ds->bytes));
+        PML_CUDA(cudaMemcpyAsync(*slot, src, sizeof(double) * (size_t)ds->d, cudaMemcpyHostToDevice, s));
+        PML_CUDA(cudaStreamSynchronize(s));
+        return PML_OK;
+    };
+    PML_TRY(put(&ds->factors, factors));
+    PML_TRY(put(&ds->shifts, shifts));
+    return PML_OK;
+}
+
+int pml_dataset_set_margin_variant(pml_dataset *ds, int lanes_per_row)
+{
+    PML_TRY(check_ds(ds));
+    Guard g(ds->ctx);
+    if (lanes_per_row == -1) {
+        ds->lanes_per_row = pick_variant(ds->n, ds->nnz);
+        return PML_OK;
+    }
+    switch (lanes_per_row) {
+    case 0: case 2: case 4: case 8: case 16: case 32:
+        ds->lanes_per_row = lanes_per_row;
+        return PML_OK;
+    default:
+        return fail(PML_EINVAL, "lanes_per_row must be one of -1, 0, 2, 4, 8, 16, 32");
+    }
+}
+
+// ---- device-buffer entry points -------------------------------------------------------------
+int pml_value_and_gradient_raw_dev(pml_dataset *ds, int loss, const double *coef_dev, double *out_raw_dev)
+{
+    PML_TRY(check_ds(ds));
+    if (!valid_loss(loss)) return fail(PML_EINVAL, "unknown loss");
+    if (!coef_dev || !out_raw_dev) return fail(PML_EINVAL, "null buffer");
+    Guard g(ds->ctx);
+    PML_CUDA(cudaSetDevice(ds->ctx->device));
+    return vg_raw(ds, loss, coef_dev, out_raw_dev);
+}
+
+int pml_hessian_vector_raw_dev(pml_dataset *ds, int loss, const double *coef_dev, uint64_t coef_tag,
+                               const double *v_dev, double *out_raw_dev)
+{
+    PML_TRY(check_ds(ds));
+    if (!valid_loss(loss)) return fail(PML_EINVAL, "unknown loss");
+    if (!v_dev || !out_raw_dev) return fail(PML_EINVAL, "null buffer");
+    Guard g(ds->ctx);
+    PML_CUDA(cudaSetDevice(ds->ctx->device));
+    return hv_raw(ds, loss, coef_dev, coef_tag, v_dev, out_raw_dev);
+}
+
+int pml_finalize_dev(pml_dataset *ds, int loss, const double *raw_dev, double *out_value_dev, double *out_vec_dev)
+{
+    PML_TRY(check_ds(ds));
+    if (!valid_loss(loss)) return fail(PML_EINVAL, "unknown loss");
+    if (!raw_dev) return fail(PML_EINVAL, "null buffer");
+    Guard g(ds->ctx);
+    PML_CUDA(cudaSetDevice(ds->ctx->device));
+    return finalize(ds, loss, raw_dev, out_value_dev, out_vec_dev);
+}
+
+int pml_value_and_gradient_dev(pml_dataset *ds, int loss, const double *coef_dev, double *out_value_dev,
+                               double *out_grad_dev)
+{
+    PML_TRY(check_ds(ds));
+    if (!valid_loss(loss)) return fail(PML_EINVAL, "unknown loss");
+    if (!coef_dev) return fail(PML_EINVAL, "null buffer");
+    Guard g(ds->ctx);
+    PML_CUDA(cudaSetDevice(ds->ctx->device));
+    PML_TRY(vg_raw(ds, loss, coef_dev, ds->raw));
+    return finalize(ds, loss, ds->raw, out_value_dev, out_grad_dev);
+}
+
+int pml_hessian_vector_dev(pml_dataset *ds, int loss, const double *coef_dev, uint64_t coef_tag, const double *v_dev,
+                           double *out_hv_dev)
+{
+    PML_TRY(check_ds(ds));
+    if (!valid_loss(loss)) return fail(PML_EINVAL, "unknown loss");
+    if (!v_dev || !out_hv_dev) return fail(PML_EINVAL, "null buffer");
+    Guard g(ds->ctx);
+    PML_CUDA(cudaSetDevice(ds->ctx->device));
+    PML_TRY(hv_raw(ds, loss, coef_dev, coef_tag, v_dev, ds->raw));
+    return finalize(ds, loss, ds->raw, nullptr, out_hv_dev);
+}
+
+// ---- host-buffer entry points (the drop-in calls) ------------------------------------------
+int pml_value_and_gradient(pml_dataset *ds, int loss, const double *coef, double *out_value, double *out_grad)
+{
+    PML_TRY(check_ds(ds));
+    if (!valid_loss(loss)) return fail(PML_EINVAL, "unknown loss");
+    if (!coef && ds->d > 0) return fail(PML_EINVAL, "null coefficients");
+    if (!out_value) return fail(PML_EINVAL, "null out_value");
+    Guard g(ds->ctx);
+    PML_CUDA(cudaSetDevice(ds->ctx->device));
+    cudaStream_t s = ds->ctx->stream;
+    const size_t db = sizeof(double) * (size_t)ds->d;
+    if (ds->d > 0) PML_CUDA(cudaMemcpyAsync(ds->io_a, coef, db, cudaMemcpyHostToDevice, s));
+    PML_TRY(vg_raw(ds, loss, ds->io_a, ds->raw));
+    const bool norm = loss != PML_LOSS_SMOOTHED_HINGE && (ds->factors || ds->shifts);
+    const double *src = ds->raw;
+    if (norm && out_grad) {
+        PML_TRY(finalize(ds, loss, ds->raw, nullptr, ds->io_b));
+        src = ds->io_b;
+    }
+    if (out_grad && ds->d > 0) PML_CUDA(cudaMemcpyAsync(out_grad, src, db, cudaMemcpyDeviceToHost, s));
+    PML_CUDA(cudaMemcpyAsync(ds->ctx->h_scalar, ds->raw + ds->d, sizeof(double), cudaMemcpyDeviceToHost, s));
+    PML_CUDA(cudaStreamSynchronize(s));
+    *out_value = ds->ctx->h_scalar[0];
+    return PML_OK;
+}
+
+int pml_hessian_vector(pml_dataset *ds, int loss, const double *coef, uint64_t coef_tag, const double *v, double *out_hv)
+{
+    PML_TRY(check_ds(ds));
+    if (!valid_loss(loss)) return fail(PML_EINVAL, "unknown loss");
+    if ((!v || !out_hv) && ds->d > 0) return fail(PML_EINVAL, "null buffer");
+    Guard g(ds->ctx);
+    PML_CUDA(cudaSetDevice(ds->ctx->device));
+    cudaStream_t s = ds->ctx->stream;
+    const size_t db = sizeof(double) * (size_t)ds->d;
+    const bool cached = coef_tag != 0 && ds->cache_valid && ds->cached_tag == coef_tag && ds->cached_loss == loss;
+    if (!cached) {
+        if (!coef && ds->d > 0) return fail(PML_EINVAL, "null coefficients");
+        if (ds->d > 0) PML_CUDA(cudaMemcpyAsync(ds->io_a, coef, db, cudaMemcpyHostToDevice, s));
+    }
+    if (ds->d > 0) PML_CUDA(cudaMemcpyAsync(ds->io_b, v, db, cudaMemcpyHostToDevice, s));
+    PML_TRY(hv_raw(ds, loss, ds->io_a, coef_tag, ds->io_b, ds->raw));
+    const double *src = ds->raw;
+    if (ds->factors || ds->shifts) {
+        PML_TRY(finalize(ds, loss, ds->raw, nullptr, ds->io_b));
+        src = ds->io_b;
+    }
+    if (ds->d > 0) PML_CUDA(cudaMemcpyAsync(out_hv, src, db, cudaMemcpyDeviceToHost, s));
+    PML_CUDA(cudaStreamSynchronize(s));
+    return PML_OK;
+}
+
+int pml_hessian_diagonal(pml_dataset *ds, int loss, const double *coef, double *out_diag)
+{
+    PML_TRY(check_ds(ds));
+    if (!valid_loss(loss)) return fail(PML_EINVAL, "unknown loss");
+    if ((!coef || !out_diag) && ds->d > 0) return fail(PML_EINVAL, "null buffer");
+    Guard g(ds->ctx);
+    PML_CUDA(cudaSetDevice(ds->ctx->device));
+    cudaStream_t s = ds->ctx->stream;
+    const size_t db = sizeof(double) * (size_t)ds->d;
+    if (ds->d > 0) PML_CUDA(cudaMemcpyAsync(ds->io_a, coef, db, cudaMemcpyHostToDevice, s));
+    PML_TRY(diag_dev(ds, loss, ds->io_a, ds->raw));
+    if (ds->d > 0) PML_CUDA(cudaMemcpyAsync(out_diag, ds->raw, db, cudaMemcpyDeviceToHost, s));
+    PML_CUDA(cudaStreamSynchronize(s));
+    return PML_OK;
+}
+
+int pml_scores(pml_dataset *ds, const double *coef, double *out_scores)
+{
+    PML_TRY(check_ds(ds));
+    if ((!coef && ds->d > 0) || (!out_scores && ds->n > 0)) return fail(PML_EINVAL, "null buffer");
+    Guard g(ds->ctx);
+    PML_CUDA(cudaSetDevice(ds->ctx->device));
+    cudaStream_t s = ds->ctx->stream;
+    if (ds->d > 0) PML_CUDA(cudaMemcpyAsync(ds->io_a, coef, sizeof(double) * (size_t)ds->d, cudaMemcpyHostToDevice, s));
+    RowPassParams rp;
+    std::memset(&rp, 0, sizeof(rp));
+    rp.n = ds->n;
+    rp.row_ptr = ds->row_ptr;
+    rp.col = ds->col;
+    rp.val = ds->val;
+    rp.label = ds->label;
+    rp.r = ds->r;
+    rp.vec = ds->io_a;
+    rp.mode = MODE_SCORE;
+    PML_TRY(count(ds->ctx, launch_row_pass(s, ds->ctx->sm_count, ds->value_bytes, ds->lanes_per_row, false, rp, &ds->row_grid)));
+    if (ds->n > 0) PML_CUDA(cudaMemcpyAsync(out_scores, ds->r, sizeof(double) * (size_t)ds->n, cudaMemcpyDeviceToHost, s));
+    PML_CUDA(cudaStreamSynchronize(s));
+    return PML_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,164 @@
+// internal.h -- structures shared by the translation units of libphoton_ml_b200.so.
+// Nothing here is part of the ABI (include/photon_ml_b200.h is).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <mutex>
+#include <string>
+
+#include "../../include/photon_ml_b200.h"
+
+namespace pml {
+
+void set_error(const std::string &msg);
+int fail(int code, const std::string &msg);
+
+#define PML_CUDA(expr)                                                                       \
+    do {                                                                                     \
+        cudaError_t _e = (expr);                                                             \
+        if (_e != cudaSuccess)                                                               \
+            return ::pml::fail(_e == cudaErrorMemoryAllocation ? PML_ENOMEM : PML_ECUDA,     \
+                               std::string(#expr) + ": " + cudaGetErrorString(_e));          \
+    } while (0)
+
+#define PML_TRY(expr)               \
+    do {                            \
+        int _rc = (expr);           \
+        if (_rc != PML_OK) return _rc; \
+    } while (0)
+
+// ---- geometry of the transpose (CSC) kernel: one CTA reduces one chunk of TCHUNK entries ----
+constexpr int T_THREADS = 256;
+constexpr int T_ITEMS = 16;
+constexpr int TCHUNK = T_THREADS * T_ITEMS;  // 4096 entries = 32 KB of stream per chunk (fp32 values)
+
+// ---- geometry of the row (CSR) kernel ----
+constexpr int R_THREADS = 256;
+constexpr int R_WARPS = R_THREADS / 32;
+constexpr int R_STREAM_CAP = 512;  // products staged per warp per piece in the segment-per-warp variant
+constexpr int MAX_PARTIALS = 4096; // upper bound on row-kernel CTAs (block partials of F and P)
+
+enum RowMode {
+    MODE_VG = 0,        // r_i = wt*l'(z_i);  F += wt*l, P += wt*l'
+    MODE_HV_COLD = 1,   // gathers (ec, ev) pairs; r_i = wt*l''(z_i)*(x_i.ev - fs); caches wt*l''
+    MODE_HV_CACHED = 2, // gathers ev; r_i = D_i*(x_i.ev - fs)
+    MODE_DIAG = 3,      // r_i = wt*l''(z_i), raw coefficients
+    MODE_SCORE = 4      // r_i = x_i.c
+};
+
+struct RowPassParams {
+    int64_t n;
+    const uint32_t *row_ptr;  // n+1
+    const int32_t *col;       // nnz
+    const void *val;          // nnz (float or double)
+    const double *label;      // n
+    const double *offset;     // n or null
+    const double *weight;     // n or null
+    const double *vec;        // d doubles (ONE) or d double2 pairs (TWO)
+    const double *shift_partials;  // per-CTA partial dots ec.s (and ev.s interleaved when TWO) or null
+    int n_shift_partials;
+    double *r;                // n: per-row multiplier consumed by the transpose kernel
+    double *dcache;           // n: wt*l''(z) written (HV_COLD) or read (HV_CACHED)
+    double *partials;         // 2 * gridDim.x: per-CTA (F, P)
+    int mode;
+    int loss;
+};
+
+struct ColPassParams {
+    int64_t nnz;
+    const int32_t *row;           // nnz   CSC row indices
+    const void *val;              // nnz
+    const uint32_t *nzcol_ptr;    // m+1   starts of the non-empty columns
+    const int32_t *nzcol_id;      // m     their column ids
+    const int32_t *chunk_col_lo;  // n_chunks+1
+    const double *r;              // n
+    double *out;                  // d (+2): zeroed before the launch
+    double *carry_head;           // n_chunks
+    int n_chunks;
+};
+
+struct FixEntry {
+    int32_t col;          // column id the heads belong to
+    int32_t chunk_begin;  // carry_head[chunk_begin .. chunk_end) are added to out[col]
+    int32_t chunk_end;
+};
+
+// launchers (kernels.cu); each returns the number of kernels it launched, <0 on launch error
+int launch_prepare_vectors(cudaStream_t s, int d, const double *coef, const double *v, const double *factors,
+                           const double *shifts, double *out_vec, double *shift_partials, int *n_partials);
+int launch_row_pass(cudaStream_t s, int sm_count, int value_bytes, int lanes_per_row, bool two,
+                    const RowPassParams &p, int *grid_out);
+int launch_col_pass(cudaStream_t s, int value_bytes, bool square, const ColPassParams &p);
+int launch_fixup(cudaStream_t s, const FixEntry *fix, int n_fix, const double *carry_head, double *out, int d,
+                 const double *partials, int n_partials, bool write_value, bool write_prefactor);
+int launch_finalize(cudaStream_t s, int d, const double *raw, const double *factors, const double *shifts,
+                    double *out_value, double *out_vec);
+
+// pack.cu: builds the CSC copy and its chunk metadata on the device
+struct Packed;
+int build_transpose(cudaStream_t s, int64_t n, int32_t d, int64_t nnz, const uint32_t *row_ptr,
+                    const int32_t *col, const void *val, int value_bytes, Packed *out);
+int narrow_check(cudaStream_t s, const double *val, int64_t nnz, bool *all_exact);
+int convert_values(cudaStream_t s, const void *src, int src_bytes, void *dst, int dst_bytes, int64_t nnz);
+int check_columns(cudaStream_t s, const int32_t *col, int64_t nnz, int32_t d, int64_t *bad);
+int convert_row_ptr(cudaStream_t s, const int64_t *src, uint32_t *dst, int64_t n_plus_1, int64_t *bad);
+
+struct Packed {
+    int32_t *csc_row = nullptr;
+    void *csc_val = nullptr;
+    uint32_t *nzcol_ptr = nullptr;
+    int32_t *nzcol_id = nullptr;
+    int32_t *chunk_col_lo = nullptr;
+    FixEntry *fix = nullptr;
+    int64_t m = 0;  // non-empty columns
+    int n_chunks = 0;
+    int n_fix = 0;
+    int64_t bytes = 0;
+};
+
+}  // namespace pml
+
+struct pml_ctx {
+    int device = 0;
+    int sm_count = 148;
+    cudaStream_t stream = nullptr;
+    std::mutex mu;
+    int64_t launches = 0;
+    // pinned staging for scalars
+    double *h_scalar = nullptr;
+};
+
+struct pml_dataset {
+    pml_ctx *ctx = nullptr;
+    int64_t n = 0, nnz = 0;
+    int32_t d = 0;
+    int value_bytes = 4;
+    // CSR
+    uint32_t *row_ptr = nullptr;
+    int32_t *col = nullptr;
+    void *val = nullptr;
+    double *label = nullptr, *offset = nullptr, *weight = nullptr;
+    // CSC + chunk metadata
+    pml::Packed t;
+    // normalization
+    double *factors = nullptr, *shifts = nullptr;
+    int32_t intercept = -1;
+    // per-evaluation scratch (allocated once at pack time)
+    double *r = nullptr;           // n
+    double *dcache = nullptr;      // n, lazily allocated on the first Hessian-vector call
+    double *partials = nullptr;    // 2*MAX_PARTIALS
+    double *carry_head = nullptr;  // n_chunks
+    double *raw = nullptr;         // d+2
+    double *vec = nullptr;         // 2*d: effective coefficient (pairs) buffer
+    double *shift_partials = nullptr;  // 2*MAX_PARTIALS
+    double *io_a = nullptr, *io_b = nullptr;  // d+2 each: staging of host coef / v / outputs
+    double *io_n = nullptr;        // n, lazily: scores output staging
+    uint64_t cached_tag = 0;
+    int cached_loss = -1;
+    bool cache_valid = false;
+    int lanes_per_row = 8;  // resolved margin variant
+    int row_grid = 1;       // CTAs of the last row-pass launch (= number of (F, P) partials)
+    int64_t bytes = 0;
+};

@@ -1,0 +1,628 @@
+// kernels.cu -- the per-evaluation kernels of the GLM objective path (sm_100a).
+//
+//   prepare_vectors_kernel  a1/a6  ValueAndGradientAggregator.init / HessianVectorAggregator.init
+//   row_pass_kernel         a2/a7/a9  the per-row half of `add`: sparse dot, pointwise loss, scalars
+//   col_pass_kernel         a2/a7/a9  the axpy half of `add`, done column-wise over the CSC copy
+//   fixup_kernel            a3  the part of `merge` that joins columns split across chunks
+//   finalize_kernel         a4  getVector
+//
+// (aN = row of SURVEY.md 8a; reference file:line in DESIGN.md and at each kernel.)
+// All accumulation is fp64.  No atomics anywhere: every output word has exactly one writer, and
+// every reduction has a fixed shape, so results are bit-reproducible for a given packing.
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "internal.h"
+
+namespace pml {
+
+// ------------------------------------------------------------------------------------------
+// Pointwise losses.  The branch structure is the reference's; __dmul_rn / __dsub_rn keep nvcc
+// from contracting a*b+c into an FMA where Scala rounds twice.
+// ------------------------------------------------------------------------------------------
+
+// lib/util/MathUtils.scala:34-40
+__device__ __forceinline__ double log1p_exp(double x)
+{
+    return x > 0 ? x + log1p(exp(-x)) : log1p(exp(x));
+}
+
+// api/function/glm/LogisticLossFunction.scala:54
+__device__ __forceinline__ double sigmoid(double z) { return 1.0 / (1.0 + exp(-z)); }
+
+// (l, l'):  LogisticLossFunction.scala:70-77, PoissonLossFunction.scala:40-43,
+// SquaredLossFunction.scala:42-45, svm/SmoothedHingeLossFunction.scala:40-63.
+__device__ __forceinline__ void loss_and_dz(int loss, double z, double y, double &l, double &dl)
+{
+    switch (loss) {
+    case PML_LOSS_LOGISTIC:
+        if (y > 0.5) {  // MathConst.POSITIVE_RESPONSE_THRESHOLD, lib/constants/MathConst.scala:23
+            l = log1p_exp(-z);
+            dl = -sigmoid(-z);
+        } else {
+            l = log1p_exp(z);
+            dl = sigmoid(z);
+        }
+        break;
+    case PML_LOSS_POISSON: {
+        double pred = exp(z);  // no overflow guard, as in the reference
+        l = __dsub_rn(pred, __dmul_rn(z, y));
+        dl = pred - y;
+        break;
+    }
+    case PML_LOSS_SQUARED: {
+        double delta = z - y;
+        l = __dmul_rn(delta, delta) / 2.0;
+        dl = delta;
+        break;
+    }
+    default: {  // smoothed hinge; note `label < 0.5`, not `label > 0.5`
+        double yy = (y < 0.5) ? -1.0 : 1.0;
+        double t = yy * z;
+        double lv, dv;
+        if (t <= 0) lv = 0.5 - t;
+        else if (t < 1) lv = __dmul_rn(__dmul_rn(0.5, 1.0 - t), 1.0 - t);
+        else lv = 0.0;
+        if (t < 0) dv = -1.0;
+        else if (t < 1) dv = t - 1.0;
+        else dv = 0.0;
+        l = lv;
+        dl = dv * yy;
+        break;
+    }
+    }
+}
+
+// l'':  LogisticLossFunction.scala:86-89, PoissonLossFunction.scala:52, SquaredLossFunction.scala:54
+__device__ __forceinline__ double dzz_loss(int loss, double z)
+{
+    switch (loss) {
+    case PML_LOSS_LOGISTIC: {
+        double s = sigmoid(z);
+        return __dmul_rn(s, 1.0 - s);
+    }
+    case PML_LOSS_POISSON:
+        return exp(z);
+    case PML_LOSS_SQUARED:
+        return 1.0;
+    default:
+        return __longlong_as_double(0x7ff8000000000000LL);  // not twice differentiable
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// small helpers
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ double warp_sum(double v)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// Sum (a, b) over the CTA in a fixed order; result valid in every thread.  `red` holds
+// 2*warps doubles.  Safe to call repeatedly (leading barrier).
+template <int WARPS>
+__device__ __forceinline__ void block_sum2(double &a, double &b, double *red)
+{
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    a = warp_sum(a);
+    b = warp_sum(b);
+    __syncthreads();
+    if (lane == 0) {
+        red[2 * w] = a;
+        red[2 * w + 1] = b;
+    }
+    __syncthreads();
+    double sa = 0.0, sb = 0.0;
+#pragma unroll
+    for (int i = 0; i < WARPS; ++i) {
+        sa += red[2 * i];
+        sb += red[2 * i + 1];
+    }
+    a = sa;
+    b = sb;
+}
+
+__device__ __forceinline__ double widen(float v) { return (double)v; }
+__device__ __forceinline__ double widen(double v) { return v; }
+
+// ------------------------------------------------------------------------------------------
+// prepare_vectors_kernel -- ValueAndGradientAggregator.init (lib/function/glm/
+// ValueAndGradientAggregator.scala:90-122) and HessianVectorAggregator.init
+// (HessianVectorAggregator.scala:60-85): ec = coef .* factors, ev = v .* factors, and the two
+// dots with `shifts` as per-CTA partials (the row kernel adds them up in its prologue, so the
+// scalar needs no launch of its own).  When v != null the outputs are interleaved (ec_j, ev_j)
+// so that the row kernel fetches both with one 16-byte gather.
+// ------------------------------------------------------------------------------------------
+constexpr int PREP_THREADS = 256;
+
+__global__ void __launch_bounds__(PREP_THREADS)
+prepare_vectors_kernel(int d, const double *__restrict__ coef, const double *__restrict__ v,
+                       const double *__restrict__ factors, const double *__restrict__ shifts,
+                       double *__restrict__ out_vec, double *__restrict__ shift_partials)
+{
+    __shared__ double red[2 * (PREP_THREADS / 32)];
+    double s0 = 0.0, s1 = 0.0;
+    for (int j = blockIdx.x * PREP_THREADS + threadIdx.x; j < d; j += gridDim.x * PREP_THREADS) {
+        double f = factors ? factors[j] : 1.0;
+        double ec = factors ? __dmul_rn(coef[j], f) : coef[j];
+        double sh = shifts ? shifts[j] : 0.0;
+        s0 += __dmul_rn(ec, sh);
+        if (v) {
+            double ev = factors ? __dmul_rn(v[j], f) : v[j];
+            s1 += __dmul_rn(ev, sh);
+            reinterpret_cast<double2 *>(out_vec)[j] = make_double2(ec, ev);
+        } else {
+            out_vec[j] = ec;
+        }
+    }
+    block_sum2<PREP_THREADS / 32>(s0, s1, red);
+    if (threadIdx.x == 0) {
+        shift_partials[2 * blockIdx.x] = s0;
+        shift_partials[2 * blockIdx.x + 1] = s1;
+    }
+}
+
+int launch_prepare_vectors(cudaStream_t s, int d, const double *coef, const double *v, const double *factors,
+                           const double *shifts, double *out_vec, double *shift_partials, int *n_partials)
+{
+    int grid = (d + PREP_THREADS * 4 - 1) / (PREP_THREADS * 4);
+    if (grid < 1) grid = 1;
+    if (grid > 1024) grid = 1024;
+    prepare_vectors_kernel<<<grid, PREP_THREADS, 0, s>>>(d, coef, v, factors, shifts, out_vec, shift_partials);
+    *n_partials = grid;
+    return cudaGetLastError() == cudaSuccess ? 1 : -1;
+}
+
+// ------------------------------------------------------------------------------------------
+// row_pass_kernel -- the per-row half of ValueAndGradientAggregator.add
+// (ValueAndGradientAggregator.scala:132-153), HessianVectorAggregator.add
+// (HessianVectorAggregator.scala:96-121) and HessianDiagonalAggregator.add
+// (HessianDiagonalAggregator.scala:51-61): margin z_i = x_i.ec + o_i + marginShift
+// (LabeledPoint.computeMargin, lib/data/LabeledPoint.scala:62), the pointwise loss, the scalar
+// sums, and the per-row multiplier r_i that the column pass turns into the axpy.
+//
+// A warp owns 32 consecutive rows at a time.
+//   LPR in {2,4,8,16,32}: "lanes per row" -- 32/LPR rows are reduced concurrently by sub-warps
+//     of LPR lanes, LPR passes cover the 32 rows (LPR = 32 is warp-per-row).
+//   LPR == 0: segment-per-warp -- the warp streams the contiguous entry range of its 32 rows
+//     with fully coalesced loads, parks the products in shared memory, and each lane then adds
+//     up its own row in storage order (the reference's order, so margins match bit for bit).
+// Either way lane L ends up holding row L's dot product, so labels/offsets/weights are read and
+// r is written coalesced and the fp64 exp/log1p work runs with all 32 lanes active.
+// ------------------------------------------------------------------------------------------
+template <typename VT, bool TWO>
+__device__ __forceinline__ void gather_fma(const VT *__restrict__ val, const int32_t *__restrict__ col,
+                                           const double *__restrict__ vec, uint32_t k, double &a, double &b)
+{
+    int32_t c = __ldcs(col + k);
+    double x = widen(__ldcs(val + k));
+    if (TWO) {
+        double2 g = __ldg(reinterpret_cast<const double2 *>(vec) + c);
+        a = fma(x, g.x, a);
+        b = fma(x, g.y, b);
+    } else {
+        a = fma(x, __ldg(vec + c), a);
+    }
+}
+
+template <typename VT, int LPR, bool TWO>
+__global__ void __launch_bounds__(R_THREADS) row_pass_kernel(const RowPassParams p)
+{
+    constexpr int CAPE = TWO ? R_STREAM_CAP / 2 : R_STREAM_CAP;
+    __shared__ double red[2 * R_WARPS];
+    __shared__ double stage[(LPR == 0) ? R_WARPS * R_STREAM_CAP : 1];
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const VT *__restrict__ val = static_cast<const VT *>(p.val);
+    const int32_t *__restrict__ col = p.col;
+    const double *__restrict__ vec = p.vec;
+
+    // marginShift = -(ec . shifts); featureVectorProductShift = ev . shifts
+    double shift0 = 0.0, shift1 = 0.0;
+    if (p.shift_partials != nullptr) {
+        for (int i = threadIdx.x; i < p.n_shift_partials; i += R_THREADS) {
+            shift0 += p.shift_partials[2 * i];
+            shift1 += p.shift_partials[2 * i + 1];
+        }
+        block_sum2<R_WARPS>(shift0, shift1, red);
+    }
+    const double margin_shift = (p.mode == MODE_HV_CACHED) ? 0.0 : -shift0;
+    const double fs = (p.mode == MODE_HV_CACHED) ? shift0 : shift1;
+
+    double accF = 0.0, accP = 0.0;
+    const int64_t n_blk = (p.n + 31) >> 5;
+    for (int64_t blk = (int64_t)blockIdx.x * R_WARPS + warp; blk < n_blk; blk += (int64_t)gridDim.x * R_WARPS) {
+        const int64_t row0 = blk << 5;
+        const int64_t my_row = row0 + lane;
+        const int64_t clamp_lo = my_row < p.n ? my_row : p.n;
+        const int64_t clamp_hi = my_row + 1 < p.n ? my_row + 1 : p.n;
+        const uint32_t rp_lo = __ldg(p.row_ptr + clamp_lo);
+        const uint32_t rp_hi = __ldg(p.row_ptr + clamp_hi);
+        double za = 0.0, zb = 0.0;
+
+        if (LPR == 0) {
+            double *buf = stage + warp * R_STREAM_CAP;
+            const uint32_t base = __shfl_sync(0xffffffffu, rp_lo, 0);
+            const uint32_t lim = __shfl_sync(0xffffffffu, rp_hi, 31);
+            for (uint32_t pb = base; pb < lim; pb += CAPE) {
+                const uint32_t pe = (lim - pb > (uint32_t)CAPE) ? pb + CAPE : lim;
+#pragma unroll 4
+                for (uint32_t k = pb + lane; k < pe; k += 32) {
+                    int32_t c = __ldcs(col + k);
+                    double x = widen(__ldcs(val + k));
+                    if (TWO) {
+                        double2 g = __ldg(reinterpret_cast<const double2 *>(vec) + c);
+                        buf[k - pb] = __dmul_rn(x, g.x);
+                        buf[CAPE + (k - pb)] = __dmul_rn(x, g.y);
+                    } else {
+                        buf[k - pb] = __dmul_rn(x, __ldg(vec + c));
+                    }
+                }
+                __syncwarp();
+                const uint32_t lo = rp_lo > pb ? rp_lo : pb;
+                const uint32_t hi = rp_hi < pe ? rp_hi : pe;
+                for (uint32_t k = lo; k < hi; ++k) {
+                    za += buf[k - pb];
+                    if (TWO) zb += buf[CAPE + (k - pb)];
+                }
+                __syncwarp();
+            }
+        } else {
+            constexpr int L = (LPR == 0) ? 1 : LPR;  // keeps the dead branch compilable
+            constexpr int RPP = 32 / L;              // rows per pass
+            const int sub = lane / L, sl = lane % L;
+#pragma unroll 1
+            for (int pass = 0; pass < L; ++pass) {
+                const int rloc = pass * RPP + sub;
+                const uint32_t start = __shfl_sync(0xffffffffu, rp_lo, rloc);
+                const uint32_t end = __shfl_sync(0xffffffffu, rp_hi, rloc);
+                double a = 0.0, b = 0.0;
+                uint32_t k = start + sl;
+                for (; k + 3 * L < end; k += 4 * L) {
+                    double a1 = 0.0, b1 = 0.0, a2 = 0.0, b2 = 0.0, a3 = 0.0, b3 = 0.0;
+                    gather_fma<VT, TWO>(val, col, vec, k, a, b);
+                    gather_fma<VT, TWO>(val, col, vec, k + L, a1, b1);
+                    gather_fma<VT, TWO>(val, col, vec, k + 2 * L, a2, b2);
+                    gather_fma<VT, TWO>(val, col, vec, k + 3 * L, a3, b3);
+                    a += (a1 + a2) + a3;
+                    if (TWO) b += (b1 + b2) + b3;
+                }
+                for (; k < end; k += L) gather_fma<VT, TWO>(val, col, vec, k, a, b);
+#pragma unroll
+                for (int o = L / 2; o > 0; o >>= 1) {
+                    a += __shfl_xor_sync(0xffffffffu, a, o);
+                    if (TWO) b += __shfl_xor_sync(0xffffffffu, b, o);
+                }
+                // lane `lane` wants row `lane`: produced in pass lane/RPP by sub-warp lane%RPP
+                const double ga = __shfl_sync(0xffffffffu, a, (lane % RPP) * L);
+                const double gb = TWO ? __shfl_sync(0xffffffffu, b, (lane % RPP) * L) : 0.0;
+                if (lane / RPP == pass) {
+                    za = ga;
+                    zb = gb;
+                }
+            }
+        }
+
+        if (my_row < p.n) {
+            const double o = p.offset ? __ldcs(p.offset + my_row) : 0.0;
+            const double wt = p.weight ? __ldcs(p.weight + my_row) : 1.0;
+            switch (p.mode) {
+            case MODE_VG: {
+                const double z = (za + o) + margin_shift;
+                double l, dl;
+                loss_and_dz(p.loss, z, __ldcs(p.label + my_row), l, dl);
+                const double wdl = __dmul_rn(wt, dl);
+                p.r[my_row] = wdl;
+                accF += __dmul_rn(wt, l);
+                accP += wdl;
+                break;
+            }
+            case MODE_HV_COLD: {
+                const double z = (za + o) + margin_shift;
+                const double dq = __dmul_rn(wt, dzz_loss(p.loss, z));
+                if (p.dcache) p.dcache[my_row] = dq;
+                const double e = __dmul_rn(dq, zb - fs);
+                p.r[my_row] = e;
+                accP += e;
+                break;
+            }
+            case MODE_HV_CACHED: {
+                const double e = __dmul_rn(__ldcs(p.dcache + my_row), za - fs);
+                p.r[my_row] = e;
+                accP += e;
+                break;
+            }
+            case MODE_DIAG: {
+                const double z = za + o;
+                p.r[my_row] = __dmul_rn(wt, dzz_loss(p.loss, z));
+                break;
+            }
+            default:
+                p.r[my_row] = za;
+                break;
+            }
+        }
+    }
+
+    if (p.partials != nullptr) {
+        block_sum2<R_WARPS>(accF, accP, red);
+        if (threadIdx.x == 0) {
+            p.partials[2 * blockIdx.x] = accF;
+            p.partials[2 * blockIdx.x + 1] = accP;
+        }
+    }
+}
+
+template <typename VT, bool TWO>
+static int launch_row_variant(cudaStream_t s, int grid, int lpr, const RowPassParams &p)
+{
+    switch (lpr) {
+    case 0: row_pass_kernel<VT, 0, TWO><<<grid, R_THREADS, 0, s>>>(p); break;
+    case 2: row_pass_kernel<VT, 2, TWO><<<grid, R_THREADS, 0, s>>>(p); break;
+    case 4: row_pass_kernel<VT, 4, TWO><<<grid, R_THREADS, 0, s>>>(p); break;
+    case 8: row_pass_kernel<VT, 8, TWO><<<grid, R_THREADS, 0, s>>>(p); break;
+    case 16: row_pass_kernel<VT, 16, TWO><<<grid, R_THREADS, 0, s>>>(p); break;
+    case 32: row_pass_kernel<VT, 32, TWO><<<grid, R_THREADS, 0, s>>>(p); break;
+    default: return -1;
+    }
+    return cudaGetLastError() == cudaSuccess ? 1 : -1;
+}
+
+int launch_row_pass(cudaStream_t s, int sm_count, int value_bytes, int lanes_per_row, bool two,
+                    const RowPassParams &p, int *grid_out)
+{
+    const int64_t n_blk = (p.n + 31) / 32;
+    int64_t want = (n_blk + R_WARPS - 1) / R_WARPS;
+    int64_t cap = (int64_t)sm_count * 8;  // 8 CTAs of 256 threads fill an SM
+    if (cap > MAX_PARTIALS) cap = MAX_PARTIALS;
+    int grid = (int)(want < cap ? want : cap);
+    if (grid < 1) grid = 1;
+    *grid_out = grid;
+    if (value_bytes == 4)
+        return two ? launch_row_variant<float, true>(s, grid, lanes_per_row, p)
+                   : launch_row_variant<float, false>(s, grid, lanes_per_row, p);
+    return two ? launch_row_variant<double, true>(s, grid, lanes_per_row, p)
+               : launch_row_variant<double, false>(s, grid, lanes_per_row, p);
+}
+
+// ------------------------------------------------------------------------------------------
+// col_pass_kernel -- the axpy half of `add`, transposed: out_j = sum_i val_ij * r_i over the CSC
+// copy (vectorSum += (wt*l') x_i summed column by column instead of scattered row by row;
+// ValueAndGradientAggregator.scala:150, HessianVectorAggregator.scala:118; with SQUARE,
+// HessianDiagonalAggregator.scala:59).
+//
+// Work is split by ENTRIES, not by columns (column lengths are power-law): CTA c owns entries
+// [c*TCHUNK, (c+1)*TCHUNK).  It streams row indices and values with 128-bit loads, gathers r,
+// parks the fp64 products in shared memory, marks column starts, and then runs a blocked
+// segmented reduction: each thread adds up 16 consecutive products, a CTA-wide segmented scan
+// carries partial sums across threads.  Columns that start in the chunk are written by this CTA
+// (single writer); the part of the chunk that precedes its first column start belongs to a
+// column begun in an earlier chunk and goes to carry_head[c] for fixup_kernel.
+// ------------------------------------------------------------------------------------------
+struct SegScan {
+    int cnt;     // column starts seen
+    int flag;    // any column start seen
+    double val;  // running sum since the last column start
+};
+
+__device__ __forceinline__ SegScan seg_combine(const SegScan &l, const SegScan &r)
+{
+    SegScan o;
+    o.cnt = l.cnt + r.cnt;
+    o.flag = l.flag | r.flag;
+    o.val = r.flag ? r.val : l.val + r.val;
+    return o;
+}
+
+__device__ __forceinline__ int pad16(int p) { return p + (p >> 4); }
+
+template <typename VT, bool SQUARE>
+__global__ void __launch_bounds__(T_THREADS) col_pass_kernel(const ColPassParams p)
+{
+    __shared__ double prod[TCHUNK + TCHUNK / 16];
+    __shared__ __align__(16) unsigned char flags[TCHUNK];
+    __shared__ SegScan wagg[T_THREADS / 32];
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int c = blockIdx.x;
+    const int64_t base = (int64_t)c * TCHUNK;
+    const int cnt = (p.nnz - base) < TCHUNK ? (int)(p.nnz - base) : TCHUNK;
+    const int col_lo = p.chunk_col_lo[c], col_hi = p.chunk_col_lo[c + 1];
+    const VT *__restrict__ val = static_cast<const VT *>(p.val) + base;
+    const int32_t *__restrict__ row = p.row + base;
+    const double *__restrict__ r = p.r;
+
+    reinterpret_cast<uint4 *>(flags)[tid] = make_uint4(0, 0, 0, 0);
+
+    // ---- phase 1: stream the chunk, gather r, park products ----
+    if (cnt == TCHUNK) {
+#pragma unroll
+        for (int i = 0; i < T_ITEMS / 4; ++i) {
+            const int v4 = i * T_THREADS + tid;
+            const int4 rr = __ldcs(reinterpret_cast<const int4 *>(row) + v4);
+            double x0, x1, x2, x3;
+            if (sizeof(VT) == 4) {
+                const float4 vv = __ldcs(reinterpret_cast<const float4 *>(val) + v4);
+                x0 = vv.x; x1 = vv.y; x2 = vv.z; x3 = vv.w;
+            } else {
+                const double2 va = __ldcs(reinterpret_cast<const double2 *>(val) + 2 * v4);
+                const double2 vb = __ldcs(reinterpret_cast<const double2 *>(val) + 2 * v4 + 1);
+                x0 = va.x; x1 = va.y; x2 = vb.x; x3 = vb.y;
+            }
+            if (SQUARE) { x0 *= x0; x1 *= x1; x2 *= x2; x3 *= x3; }
+            const double r0 = __ldg(r + rr.x), r1 = __ldg(r + rr.y), r2 = __ldg(r + rr.z), r3 = __ldg(r + rr.w);
+            const int q = pad16(4 * v4);  // 4*v4 .. 4*v4+3 share one 16-group: contiguous after padding
+            prod[q] = __dmul_rn(r0, x0);
+            prod[q + 1] = __dmul_rn(r1, x1);
+            prod[q + 2] = __dmul_rn(r2, x2);
+            prod[q + 3] = __dmul_rn(r3, x3);
+        }
+    } else {
+        for (int e = tid; e < TCHUNK; e += T_THREADS) {
+            double v = 0.0;
+            if (e < cnt) {
+                double x = widen(val[e]);
+                if (SQUARE) x *= x;
+                v = __dmul_rn(__ldg(r + row[e]), x);
+            }
+            prod[pad16(e)] = v;
+        }
+    }
+    __syncthreads();  // flags are zero
+    for (int j = col_lo + tid; j < col_hi; j += T_THREADS) flags[(int64_t)p.nzcol_ptr[j] - base] = 1;
+    __syncthreads();
+
+    // ---- phase 2: blocked segmented reduction ----
+    const uint4 f4 = reinterpret_cast<const uint4 *>(flags)[tid];
+    const unsigned fw[4] = { f4.x, f4.y, f4.z, f4.w };
+    SegScan mine;
+    mine.cnt = __popc(f4.x) + __popc(f4.y) + __popc(f4.z) + __popc(f4.w);
+    mine.flag = mine.cnt > 0;
+    {
+        // value = sum after the last flag (whole run if none); a cheap first walk
+        double s = 0.0;
+#pragma unroll
+        for (int i = 0; i < T_ITEMS; ++i) {
+            if ((fw[i >> 2] >> ((i & 3) * 8)) & 0xff) s = 0.0;
+            s += prod[pad16(tid * T_ITEMS) + i];
+        }
+        mine.val = s;
+    }
+    // inclusive warp scan
+    SegScan inc = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        SegScan up;
+        up.cnt = __shfl_up_sync(0xffffffffu, inc.cnt, o);
+        up.flag = __shfl_up_sync(0xffffffffu, inc.flag, o);
+        up.val = __shfl_up_sync(0xffffffffu, inc.val, o);
+        if (lane >= o) inc = seg_combine(up, inc);
+    }
+    if (lane == 31) wagg[warp] = inc;
+    SegScan exc;
+    exc.cnt = __shfl_up_sync(0xffffffffu, inc.cnt, 1);
+    exc.flag = __shfl_up_sync(0xffffffffu, inc.flag, 1);
+    exc.val = __shfl_up_sync(0xffffffffu, inc.val, 1);
+    if (lane == 0) { exc.cnt = 0; exc.flag = 0; exc.val = 0.0; }
+    __syncthreads();
+    SegScan pre;
+    pre.cnt = 0; pre.flag = 0; pre.val = 0.0;
+    for (int w = 0; w < warp; ++w) pre = seg_combine(pre, wagg[w]);
+    exc = seg_combine(pre, exc);
+
+    // walk again, closing columns
+    if (mine.flag) {
+        double s = 0.0;
+        int ord = col_lo + exc.cnt;  // ordinal of the next column start this thread meets
+        bool first = true;
+#pragma unroll
+        for (int i = 0; i < T_ITEMS; ++i) {
+            if ((fw[i >> 2] >> ((i & 3) * 8)) & 0xff) {
+                const double total = first ? exc.val + s : s;
+                if (first && exc.cnt == 0) p.carry_head[c] = total;  // column began in an earlier chunk
+                else p.out[p.nzcol_id[ord - 1]] = total;
+                first = false;
+                ++ord;
+                s = 0.0;
+            }
+            s += prod[pad16(tid * T_ITEMS) + i];
+        }
+    }
+    if (tid == T_THREADS - 1) {
+        const SegScan tot = seg_combine(exc, mine);
+        if (tot.flag) p.out[p.nzcol_id[col_hi - 1]] = tot.val;  // last column started here: owner
+        else p.carry_head[c] = tot.val;                         // the whole chunk is one column's middle
+    }
+}
+
+int launch_col_pass(cudaStream_t s, int value_bytes, bool square, const ColPassParams &p)
+{
+    if (p.n_chunks <= 0) return 0;
+    if (value_bytes == 4) {
+        if (square) col_pass_kernel<float, true><<<p.n_chunks, T_THREADS, 0, s>>>(p);
+        else col_pass_kernel<float, false><<<p.n_chunks, T_THREADS, 0, s>>>(p);
+    } else {
+        if (square) col_pass_kernel<double, true><<<p.n_chunks, T_THREADS, 0, s>>>(p);
+        else col_pass_kernel<double, false><<<p.n_chunks, T_THREADS, 0, s>>>(p);
+    }
+    return cudaGetLastError() == cudaSuccess ? 1 : -1;
+}
+
+// ------------------------------------------------------------------------------------------
+// fixup_kernel -- the `merge` of partial aggregates (ValueAndGradientAggregator.scala:161-176)
+// as far as one GPU is concerned: columns cut by chunk boundaries get their heads added (one
+// warp per column, fixed order), and the last CTA adds up the row kernel's per-CTA (F, P).
+// ------------------------------------------------------------------------------------------
+constexpr int F_THREADS = 256;
+
+__global__ void __launch_bounds__(F_THREADS)
+fixup_kernel(const FixEntry *__restrict__ fix, int n_fix, const double *__restrict__ carry_head,
+             double *__restrict__ out, int d, const double *__restrict__ partials, int n_partials,
+             int write_value, int write_prefactor)
+{
+    __shared__ double red[2 * (F_THREADS / 32)];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (blockIdx.x == gridDim.x - 1 && partials != nullptr) {
+        double f = 0.0, pp = 0.0;
+        for (int i = threadIdx.x; i < n_partials; i += F_THREADS) {
+            f += partials[2 * i];
+            pp += partials[2 * i + 1];
+        }
+        block_sum2<F_THREADS / 32>(f, pp, red);
+        if (threadIdx.x == 0) {
+            out[d] = write_value ? f : 0.0;
+            out[d + 1] = write_prefactor ? pp : 0.0;
+        }
+        return;
+    }
+    const int q = blockIdx.x * (F_THREADS / 32) + warp;
+    if (q >= n_fix) return;
+    const FixEntry e = fix[q];
+    double s = 0.0;
+    for (int cc = e.chunk_begin + lane; cc < e.chunk_end; cc += 32) s += carry_head[cc];
+    s = warp_sum(s);
+    if (lane == 0) out[e.col] += s;
+}
+
+int launch_fixup(cudaStream_t s, const FixEntry *fix, int n_fix, const double *carry_head, double *out, int d,
+                 const double *partials, int n_partials, bool write_value, bool write_prefactor)
+{
+    int grid = (n_fix + (F_THREADS / 32) - 1) / (F_THREADS / 32) + (partials ? 1 : 0);
+    if (grid == 0) return 0;
+    fixup_kernel<<<grid, F_THREADS, 0, s>>>(fix, n_fix, carry_head, out, d, partials, n_partials,
+                                            write_value ? 1 : 0, write_prefactor ? 1 : 0);
+    return cudaGetLastError() == cudaSuccess ? 1 : -1;
+}
+
+// ------------------------------------------------------------------------------------------
+// finalize_kernel -- ValueAndGradientAggregator.getVector (:199-221):
+//   result_j = (vectorSum_j - shifts_j * vectorShiftPrefactorSum) * factors_j   (4 cases)
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+finalize_kernel(int d, const double *__restrict__ raw, const double *__restrict__ factors,
+                const double *__restrict__ shifts, double *__restrict__ out_value, double *__restrict__ out_vec)
+{
+    const double P = raw[d + 1];
+    if (blockIdx.x == 0 && threadIdx.x == 0 && out_value != nullptr) *out_value = raw[d];
+    if (out_vec == nullptr) return;
+    for (int j = blockIdx.x * 256 + threadIdx.x; j < d; j += gridDim.x * 256) {
+        double v = raw[j];
+        if (shifts) v = __dsub_rn(v, __dmul_rn(shifts[j], P));
+        if (factors) v = __dmul_rn(v, factors[j]);
+        out_vec[j] = v;
+    }
+}
+
+int launch_finalize(cudaStream_t s, int d, const double *raw, const double *factors, const double *shifts,
+                    double *out_value, double *out_vec)
+{
+    int grid = (d + 1023) / 1024;
+    if (grid < 1) grid = 1;
+    if (grid > 2048) grid = 2048;
+    finalize_kernel<<<grid, 256, 0, s>>>(d, raw, factors, shifts, out_value, out_vec);
+    return cudaGetLastError() == cudaSuccess ? 1 : -1;
+}
+
+}  // namespace pml
