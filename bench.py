@@ -1,0 +1,404 @@
+#!/usr/bin/env python
+"""bench.py -- value+gradient evaluations/s of the GLM objective path on B200.
+
+Workload (BASELINE.json configs[1], the configuration the metric is quoted on): Poisson
+regression, synthetic 10 M rows x 1 M features, 66 Zipf(1.1) draws per row (duplicates merged,
+so ~50 stored entries per row), values in {1,2,3,4}/4 (fp32-exact), offsets 0, weights 1.  A
+"step" is one value+gradient evaluation over all rows.  With --gpus N the SAME rows are sharded
+over N ranks (strong scaling); every rank produces raw partial sums and one NCCL all-reduce of
+d+2 doubles replaces Spark's treeAggregate.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W]                 our arm
+  python bench.py --impl reference [--gpus N] [--steps K] [--warmup W]  CPU restatement of the
+      reference loop on the host cores (Spark local[N] shape; no JVM on this box)
+
+One JSON line on stdout (rank 0).
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+N_ROWS = 10_000_000
+N_FEATS = 1_000_000
+DRAWS_PER_ROW = 66          # Zipf(1.1) duplicates merge: 66 draws leave ~50 stored entries per row
+ZIPF_A = 1.1
+GEN_CHUNK = 250_000          # rows per generator chunk; 40 chunks split evenly over 1/2/4/8 ranks
+SEED = 2
+LOSS_POISSON = 1
+CPU_SAMPLE_ROWS = 500_000    # bounded sample for the CPU baseline (two generator chunks)
+
+
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def generate_chunk(torch, device, chunk_id, cdf, w_true):
+    """One generator chunk: (lens[int64 rows], cols[int32], vals[float32], labels[float64])."""
+    g = torch.Generator(device=device)
+    g.manual_seed(SEED * 1_000_003 + chunk_id)
+    rows = GEN_CHUNK
+    u = torch.rand((rows, DRAWS_PER_ROW), generator=g, device=device, dtype=torch.float64)
+    cols = torch.searchsorted(cdf, u).clamp_(max=N_FEATS - 1)
+    cols, _ = torch.sort(cols, dim=1)
+    keep = torch.ones_like(cols, dtype=torch.bool)
+    keep[:, 1:] = cols[:, 1:] != cols[:, :-1]
+    vals = torch.randint(1, 5, (rows, DRAWS_PER_ROW), generator=g, device=device).to(torch.float64) / 4.0
+    margin = (vals * w_true[cols] * keep).sum(dim=1).clamp_(-5.0, 5.0)
+    labels = torch.poisson(torch.exp(margin), generator=g)
+    lens = keep.sum(dim=1)
+    return lens, cols[keep].to(torch.int32), vals[keep].to(torch.float32), labels
+
+
+def generate_rows(torch, device, chunk_ids):
+    ranks = torch.arange(1, N_FEATS + 1, device=device, dtype=torch.float64)
+    p = ranks.pow(-ZIPF_A)
+    cdf = torch.cumsum(p / p.sum(), dim=0)
+    g = torch.Generator(device=device)
+    g.manual_seed(SEED)
+    w_true = torch.randn(N_FEATS, generator=g, device=device, dtype=torch.float64) * 0.1
+    w_true = w_true * (torch.rand(N_FEATS, generator=g, device=device) < 0.01)
+    lens, cols, vals, labels = [], [], [], []
+    for c in chunk_ids:
+        a, b, v, y = generate_chunk(torch, device, c, cdf, w_true)
+        lens.append(a); cols.append(b); vals.append(v); labels.append(y)
+    lens = torch.cat(lens)
+    row_ptr = torch.zeros(lens.numel() + 1, dtype=torch.int64, device=device)
+    torch.cumsum(lens, dim=0, out=row_ptr[1:])
+    return row_ptr, torch.cat(cols), torch.cat(vals), torch.cat(labels)
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    FIELDS = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+              "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.gpu_index = gpu_index
+        self.lines = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu_index), "--query-gpu=" + self.FIELDS,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self.lines:
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, flag in zip(names, f[5:9]):
+                if flag.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def kernel_bytes(info, has_offset, has_weight):
+    """ALGORITHMIC bytes per launch of the two evaluation kernels."""
+    V = info.value_bytes
+    n, d, nnz, m = info.n, info.d, info.nnz, info.nonempty_cols
+    row = nnz * (V + 4) + (n + 1) * 4 + n * 8 * (1 + has_offset + has_weight) + n * 8 + d * 8
+    col = nnz * (V + 4) + n * 8 + m * 8 + (info.n_chunks + 1) * 4 + d * 8
+    return row, col
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    import photon_ml_b200 as pml
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            raise SystemExit("launch with torch.distributed.run --nproc-per-node %d for --gpus %d" % (args.gpus, args.gpus))
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=device)
+
+    ctx = pml.Context(local_rank)
+    ext = torch.cuda.ExternalStream(ctx.stream, device=device)
+
+    n_chunks = N_ROWS // GEN_CHUNK
+    mine = list(range(rank * n_chunks // world, (rank + 1) * n_chunks // world))
+    t0 = time.time()
+    row_ptr, cols, vals, labels = generate_rows(torch, device, mine)
+    torch.cuda.synchronize()
+    t_gen = time.time() - t0
+    n_local = labels.numel()
+    t0 = time.time()
+    ds = pml.Dataset.from_device_pointers(ctx, n_local, N_FEATS, row_ptr.data_ptr(), cols.data_ptr(), vals.data_ptr(),
+                                          pml.abi.F32, labels.data_ptr(), storage=pml.STORE_F32)
+    ctx.synchronize()
+    t_pack = time.time() - t0
+    del row_ptr, cols, vals, labels
+    torch.cuda.empty_cache()
+    info = ds.info()
+    d = info.d
+
+    gen = torch.Generator(device=device)
+    gen.manual_seed(99)
+    coef = torch.randn(d, generator=gen, device=device, dtype=torch.float64) * 0.02
+    raw = torch.empty(d + 2, dtype=torch.float64, device=device)
+    out_value = torch.empty(1, dtype=torch.float64, device=device)
+    out_grad = torch.empty(d, dtype=torch.float64, device=device)
+    torch.cuda.synchronize()
+
+    def step():
+        ds.value_and_gradient_raw_dev(LOSS_POISSON, coef.data_ptr(), raw.data_ptr())
+        if world > 1:
+            dist.all_reduce(raw)  # replaces treeAggregate (ValueAndGradientAggregator.scala:243-247)
+        ds.finalize_dev(LOSS_POISSON, raw.data_ptr(), out_value.data_ptr(), out_grad.data_ptr())
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    with torch.cuda.stream(ext):
+        for _ in range(args.warmup):
+            step()
+        barrier()
+        ctx.read_profile()
+        ctx.set_profiling(True)
+        sampler = ClockSampler(local_rank)
+        if rank == 0:
+            sampler.start()
+        launches0 = ctx.launch_count
+        start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        start.record(ext)
+        for _ in range(args.steps):
+            step()
+        stop.record(ext)
+        barrier()
+        ms = start.elapsed_time(stop)
+        clocks = sampler.stop() if rank == 0 else None
+        launches = ctx.launch_count - launches0
+        profile = ctx.read_profile()
+        ctx.set_profiling(False)
+
+        # ---- end to end through the host-buffer C ABI: pinned host coefficients in, gradient out
+        h_coef = torch.empty(d, dtype=torch.float64).pin_memory()
+        h_coef.copy_(coef.cpu())
+        h_grad = torch.empty(d, dtype=torch.float64).pin_memory()
+        h_raw = torch.empty(d + 2, dtype=torch.float64).pin_memory()
+        h_coef_np, h_grad_np = h_coef.numpy(), h_grad.numpy()
+
+        def e2e_step():
+            if world == 1:
+                return ds.value_and_gradient(LOSS_POISSON, h_coef_np, out=h_grad_np)[0]
+            coef.copy_(h_coef, non_blocking=True)
+            step()
+            h_grad.copy_(out_grad, non_blocking=True)
+            h_raw[:1].copy_(out_value, non_blocking=True)
+            ext.synchronize()
+            return float(h_raw[0])
+
+        for _ in range(max(3, args.warmup)):
+            e2e_step()
+        barrier()
+        e2e_steps = args.steps
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            e2e_value = e2e_step()
+        barrier()
+        e2e_s = time.perf_counter() - t0
+
+        # Hessian-vector products (TRON's inner loop): cold and with the cached margin pass
+        v = torch.randn(d, generator=gen, device=device, dtype=torch.float64)
+        hv_ms = {}
+        for name, tag in (("cold", 0), ("cached", 12345)):
+            def hv_step():
+                ds.hessian_vector_raw_dev(LOSS_POISSON, coef.data_ptr(), v.data_ptr(), raw.data_ptr(), tag=tag)
+                if world > 1:
+                    dist.all_reduce(raw)
+                ds.finalize_dev(LOSS_POISSON, raw.data_ptr(), None, out_grad.data_ptr())
+            for _ in range(3):
+                hv_step()
+            barrier()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(ext)
+            for _ in range(max(3, args.steps // 2)):
+                hv_step()
+            b.record(ext)
+            barrier()
+            hv_ms[name] = a.elapsed_time(b) / max(3, args.steps // 2)
+
+    # max over ranks
+    times = torch.tensor([ms, e2e_s], dtype=torch.float64, device=device)
+    if world > 1:
+        dist.all_reduce(times, op=dist.ReduceOp.MAX)
+    ms, e2e_s = float(times[0]), float(times[1])
+
+    if rank == 0:
+        peak, peak_src = peaks()
+        row_bytes, col_bytes = kernel_bytes(info, 0, 0)
+        row_ms = profile["row_pass"][0] / max(1, profile["row_pass"][1])
+        col_ms = profile["col_pass"][0] / max(1, profile["col_pass"][1])
+        dominant = "col_pass_kernel" if col_ms >= row_ms else "row_pass_kernel"
+        dom_bytes, dom_ms = (col_bytes, col_ms) if col_ms >= row_ms else (row_bytes, row_ms)
+        achieved = dom_bytes / (dom_ms * 1e-3) / 1e9
+        ms_per_step = ms / args.steps
+        step_bytes = info.vg_algorithmic_bytes - 2 * info.n * 8  # no offsets / weights in this workload
+        out = {
+            "metric": "value+gradient evals/s",
+            "value": 1e3 / ms_per_step,
+            "unit": "evals/s",
+            "n_gpus": world,
+            "steps": args.steps,
+            "warmup": args.warmup,
+            "ms_per_step": ms_per_step,
+            "higher_is_better": True,
+            "scaling": "strong",
+            "vs_baseline": None,
+            "dtype": "f64",
+            "data": "synthetic",
+            "config": {
+                "workload": "configs[1]: Poisson regression, 10M rows x 1M feats, 66 Zipf(1.1) draws/row "
+                            "(%.1f stored nnz/row), fp32 values, fp64 accumulation" % (info.nnz / max(1, info.n)),
+                "rows_total": N_ROWS, "rows_per_gpu": int(info.n), "nnz_per_gpu": int(info.nnz), "d": int(d),
+                "parallelism": "row-sharded x%d, one all-reduce of d+2 fp64" % world if world > 1 else "single GPU",
+                "l2_flush": "inputs larger than L2 (%.1f GB streamed per step vs 126 MB L2)" % (step_bytes / 1e9),
+                "row_pass_variant": int(info.margin_variant),
+                "generate_s": round(t_gen, 2), "pack_s": round(t_pack, 2),
+            },
+            "e2e": {"value": e2e_steps / e2e_s, "unit": "evals/s", "h2d_bytes_per_step": d * 8,
+                    "d2h_bytes_per_step": d * 8 + 8, "ms_per_step": 1e3 * e2e_s / e2e_steps,
+                    "api": "pml_value_and_gradient (host buffers, pinned)" if world == 1 else
+                           "H2D coef + raw_dev + NCCL all-reduce + finalize_dev + D2H", "objective": e2e_value},
+            "gpu_launches": int(launches),
+            "clocks": clocks,
+            "roofline": {"bound": "hbm", "kernel": dominant, "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "frac_of_nominal_8000": achieved / 8000.0, "peak_source": peak_src,
+                         "traffic": None, "algorithmic_bytes_per_launch": int(dom_bytes),
+                         "avg_launch_ms": dom_ms},
+            "kernels": {k: {"ms_per_launch": v[0] / max(1, v[1]), "launches": int(v[1])} for k, v in profile.items()},
+            "row_pass": {"algorithmic_bytes": int(row_bytes), "ms": row_ms, "GBps": row_bytes / (row_ms * 1e-3) / 1e9},
+            "col_pass": {"algorithmic_bytes": int(col_bytes), "ms": col_ms, "GBps": col_bytes / (col_ms * 1e-3) / 1e9},
+            "step_algorithmic_GBps": step_bytes / (ms_per_step * 1e-3) / 1e9,
+            "hessian_vector": {"cold_evals_per_s": 1e3 / hv_ms["cold"], "cached_evals_per_s": 1e3 / hv_ms["cached"],
+                               "cold_ms": hv_ms["cold"], "cached_ms": hv_ms["cached"]},
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            out["cpu_baseline"] = cpu_baseline(steps=10, warmup=2)
+        print(json.dumps(out))
+    ds.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def cpu_sample():
+    """The first CPU_SAMPLE_ROWS rows of the same synthetic data, generated on the host."""
+    import torch
+    row_ptr, cols, vals, labels = generate_rows(torch, torch.device("cpu"), range(CPU_SAMPLE_ROWS // GEN_CHUNK))
+    return (row_ptr.numpy(), cols.numpy(), vals.numpy().astype(np.float64), labels.numpy())
+
+
+def cpu_baseline(steps, warmup):
+    """The oracle (CPU restatement of the reference's row loop, partitioned like Spark local[N])
+    timed on this box's host cores, on a bounded sample, scaled to full-data evaluations/s."""
+    import oracle
+    cores = oracle.max_threads()
+    row_ptr, cols, vals, labels = cpu_sample()
+    data = oracle.Data(CPU_SAMPLE_ROWS, N_FEATS, row_ptr, cols, vals, labels)
+    coef = np.random.default_rng(99).normal(scale=0.02, size=N_FEATS)
+    for _ in range(warmup):
+        oracle.value_and_gradient(data, oracle.POISSON, coef, parts=cores)
+    times = []
+    for _ in range(steps):
+        t0 = time.perf_counter()
+        oracle.value_and_gradient(data, oracle.POISSON, coef, parts=cores)
+        times.append(time.perf_counter() - t0)
+    per_eval = statistics.median(times)
+    scale = N_ROWS / CPU_SAMPLE_ROWS
+    return {"value": 1.0 / (per_eval * scale), "unit": "evals/s", "cores": cores, "kind": "port",
+            "sample": "first %d of %d rows (%d nnz), %d partitions/threads, median of %d evaluations = %.4f s; "
+                      "scaled x%g to the full row count. CPU restatement of the reference loop (not Spark: no JVM "
+                      "on this box)" % (CPU_SAMPLE_ROWS, N_ROWS, len(cols), cores, steps, per_eval, scale),
+            "sample_eval_s": per_eval}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    steps = max(1, args.steps)
+    base = cpu_baseline(steps=steps, warmup=max(1, min(args.warmup, 3)))
+    ms_per_step = 1e3 / base["value"]
+    out = {
+        "impl": "reference",
+        "metric": "value+gradient evals/s", "value": base["value"], "unit": "evals/s",
+        "n_gpus": args.gpus, "steps": steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "configs[1]: Poisson regression, 10M rows x 1M feats, 66 Zipf(1.1) draws/row; "
+                               "each step = one evaluation of the bounded sample, scaled to the full row count",
+                   "rows_total": N_ROWS, "d": N_FEATS},
+        "cpu_baseline": base,
+        "e2e": {"value": base["value"], "unit": "evals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(out))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.warmup < 3 and args.impl == "ours":
+        args.warmup = 3
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

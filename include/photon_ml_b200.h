@@ -165,7 +165,19 @@ int pml_hessian_vector_dev(pml_dataset *ds, int loss, const double *coef_dev, ui
 
 /* number of kernel launches this context has issued (bench.py's gpu_launches) */
 int pml_ctx_launch_count(pml_ctx *ctx, int64_t *out);
-/* force a CSR margin-kernel variant: lanes per row in {1? no: 2,4,8,16,32}, 0 = segment-per-warp,
+/* Per-kernel device timing for the roofline report: with profiling on, every kernel class is
+ * bracketed by CUDA events on the context's stream; pml_ctx_read_profile synchronises, sums the
+ * elapsed milliseconds and launch counts per class since the last read, and clears them. */
+#define PML_K_PREPARE 0  /* prepare_vectors_kernel */
+#define PML_K_ROW 1      /* row_pass_kernel (CSR) */
+#define PML_K_COL 2      /* col_pass_kernel (CSC) */
+#define PML_K_FIXUP 3    /* fixup_kernel */
+#define PML_K_FINALIZE 4 /* finalize_kernel */
+#define PML_K_COUNT 8
+int pml_ctx_set_profiling(pml_ctx *ctx, int on);
+int pml_ctx_read_profile(pml_ctx *ctx, double *out_ms /* [PML_K_COUNT] */,
+                         int64_t *out_launches /* [PML_K_COUNT] */);
+/* force a CSR margin-kernel variant: lanes per row in {2,4,8,16,32}, 0 = segment-per-warp,
  * -1 = back to the nnz/row heuristic.  For benchmarking and tests. */
 int pml_dataset_set_margin_variant(pml_dataset *ds, int lanes_per_row);
 

@@ -24,7 +24,7 @@ SYMBOLS = [
     "pml_dataset_set_labels", "pml_dataset_set_normalization", "pml_value_and_gradient", "pml_hessian_vector",
     "pml_hessian_diagonal", "pml_scores", "pml_value_and_gradient_raw_dev", "pml_hessian_vector_raw_dev",
     "pml_finalize_dev", "pml_value_and_gradient_dev", "pml_hessian_vector_dev", "pml_ctx_launch_count",
-    "pml_dataset_set_margin_variant",
+    "pml_dataset_set_margin_variant", "pml_ctx_set_profiling", "pml_ctx_read_profile",
 ]
 
 
@@ -91,6 +91,8 @@ def load():
         "pml_hessian_vector_dev": [vp, ctypes.c_int, vp, u64, vp, vp],
         "pml_ctx_launch_count": [vp, ctypes.POINTER(i64)],
         "pml_dataset_set_margin_variant": [vp, ctypes.c_int],
+        "pml_ctx_set_profiling": [vp, ctypes.c_int],
+        "pml_ctx_read_profile": [vp, ctypes.POINTER(dbl), ctypes.POINTER(i64)],
     }
     for name, argtypes in sigs.items():
         fn = getattr(lib, name)
@@ -144,6 +146,18 @@ class Context:
         v = ctypes.c_int64()
         check(load().pml_ctx_launch_count(self._h, ctypes.byref(v)))
         return v.value
+
+    KERNEL_KINDS = ["prepare_vectors", "row_pass", "col_pass", "fixup", "finalize"]
+
+    def set_profiling(self, on):
+        check(load().pml_ctx_set_profiling(self._h, 1 if on else 0))
+
+    def read_profile(self):
+        """{kernel class: (total ms, launches)} since the last read (synchronises)."""
+        ms = (ctypes.c_double * 8)()
+        cnt = (ctypes.c_int64 * 8)()
+        check(load().pml_ctx_read_profile(self._h, ms, cnt))
+        return {k: (ms[i], cnt[i]) for i, k in enumerate(self.KERNEL_KINDS)}
 
     def close(self):
         if self._h:

@@ -87,6 +87,23 @@ int count(pml_ctx *ctx, int launched)
     return PML_OK;
 }
 
+// Launch through this wrapper so that, with profiling on, each kernel class is bracketed by
+// CUDA events on the context's stream (bench.py's live per-kernel durations).
+template <typename F>
+int run(pml_ctx *ctx, int kind, F &&launch)
+{
+    if (!ctx->profiling) return count(ctx, launch());
+    cudaEvent_t a, b;
+    PML_CUDA(cudaEventCreate(&a));
+    PML_CUDA(cudaEventCreate(&b));
+    PML_CUDA(cudaEventRecord(a, ctx->stream));
+    const int launched = launch();
+    PML_CUDA(cudaEventRecord(b, ctx->stream));
+    if (launched > 0) ctx->spans.push_back({ kind, a, b });
+    else { cudaEventDestroy(a); cudaEventDestroy(b); }
+    return count(ctx, launched);
+}
+
 // -------------------------------------------------------------------------------------------
 // evaluation pipelines (device pointers; the caller holds the context lock)
 // -------------------------------------------------------------------------------------------
@@ -105,9 +122,9 @@ int run_col_and_fixup(pml_dataset *ds, bool square, double *out, bool with_scala
     cp.out = out;
     cp.carry_head = ds->carry_head;
     cp.n_chunks = ds->t.n_chunks;
-    PML_TRY(count(ctx, launch_col_pass(s, ds->value_bytes, square, cp)));
-    PML_TRY(count(ctx, launch_fixup(s, ds->t.fix, ds->t.n_fix, ds->carry_head, out, ds->d,
-                                    with_scalars ? ds->partials : nullptr, ds->row_grid, write_value, true)));
+    PML_TRY(run(ctx, PML_K_COL, [&] { return launch_col_pass(s, ds->value_bytes, square, cp); }));
+    PML_TRY(run(ctx, PML_K_FIXUP, [&] { return launch_fixup(s, ds->t.fix, ds->t.n_fix, ds->carry_head, out, ds->d,
+                                    with_scalars ? ds->partials : nullptr, ds->row_grid, write_value, true); }));
     return PML_OK;
 }
 
@@ -122,8 +139,8 @@ int vg_raw(pml_dataset *ds, int loss, const double *coef_dev, double *out_raw_de
     rp.vec = coef_dev;
     if (norm) {
         int np = 0;
-        PML_TRY(count(ctx, launch_prepare_vectors(s, ds->d, coef_dev, nullptr, ds->factors, ds->shifts, ds->vec,
-                                                  ds->shift_partials, &np)));
+        PML_TRY(run(ctx, PML_K_PREPARE, [&] { return launch_prepare_vectors(s, ds->d, coef_dev, nullptr, ds->factors, ds->shifts, ds->vec,
+                                                  ds->shift_partials, &np); }));
         rp.vec = ds->vec;
         if (ds->shifts) {
             rp.shift_partials = ds->shift_partials;
@@ -142,7 +159,7 @@ int vg_raw(pml_dataset *ds, int loss, const double *coef_dev, double *out_raw_de
     rp.partials = ds->partials;
     rp.mode = MODE_VG;
     rp.loss = loss;
-    PML_TRY(count(ctx, launch_row_pass(s, ctx->sm_count, ds->value_bytes, ds->lanes_per_row, false, rp, &ds->row_grid)));
+    PML_TRY(run(ctx, PML_K_ROW, [&] { return launch_row_pass(s, ctx->sm_count, ds->value_bytes, ds->lanes_per_row, false, rp, &ds->row_grid); }));
     return run_col_and_fixup(ds, false, out_raw_dev, true, true);
 }
 
@@ -170,8 +187,8 @@ int hv_raw(pml_dataset *ds, int loss, const double *coef_dev, uint64_t tag, cons
     if (!cached) {
         if (coef_dev == nullptr) return fail(PML_EINVAL, "coefficients are required when no cached pass matches the tag");
         if (tag != 0 && ds->dcache == nullptr) PML_TRY(dev_alloc(&ds->dcache, (size_t)ds->n, &ds->bytes));
-        PML_TRY(count(ctx, launch_prepare_vectors(s, ds->d, coef_dev, v_dev, ds->factors, ds->shifts, ds->vec,
-                                                  ds->shift_partials, &np)));
+        PML_TRY(run(ctx, PML_K_PREPARE, [&] { return launch_prepare_vectors(s, ds->d, coef_dev, v_dev, ds->factors, ds->shifts, ds->vec,
+                                                  ds->shift_partials, &np); }));
         rp.vec = ds->vec;
         if (ds->shifts) {
             rp.shift_partials = ds->shift_partials;
@@ -179,15 +196,15 @@ int hv_raw(pml_dataset *ds, int loss, const double *coef_dev, uint64_t tag, cons
         }
         rp.dcache = tag != 0 ? ds->dcache : nullptr;
         rp.mode = MODE_HV_COLD;
-        PML_TRY(count(ctx, launch_row_pass(s, ctx->sm_count, ds->value_bytes, ds->lanes_per_row, true, rp, &ds->row_grid)));
+        PML_TRY(run(ctx, PML_K_ROW, [&] { return launch_row_pass(s, ctx->sm_count, ds->value_bytes, ds->lanes_per_row, true, rp, &ds->row_grid); }));
         ds->cache_valid = tag != 0;
         ds->cached_tag = tag;
         ds->cached_loss = loss;
     } else {
         rp.vec = v_dev;
         if (norm) {
-            PML_TRY(count(ctx, launch_prepare_vectors(s, ds->d, v_dev, nullptr, ds->factors, ds->shifts, ds->vec,
-                                                      ds->shift_partials, &np)));
+            PML_TRY(run(ctx, PML_K_PREPARE, [&] { return launch_prepare_vectors(s, ds->d, v_dev, nullptr, ds->factors, ds->shifts, ds->vec,
+                                                      ds->shift_partials, &np); }));
             rp.vec = ds->vec;
             if (ds->shifts) {
                 rp.shift_partials = ds->shift_partials;
@@ -196,7 +213,7 @@ int hv_raw(pml_dataset *ds, int loss, const double *coef_dev, uint64_t tag, cons
         }
         rp.dcache = ds->dcache;
         rp.mode = MODE_HV_CACHED;
-        PML_TRY(count(ctx, launch_row_pass(s, ctx->sm_count, ds->value_bytes, ds->lanes_per_row, false, rp, &ds->row_grid)));
+        PML_TRY(run(ctx, PML_K_ROW, [&] { return launch_row_pass(s, ctx->sm_count, ds->value_bytes, ds->lanes_per_row, false, rp, &ds->row_grid); }));
     }
     PML_CUDA(cudaMemsetAsync(out_raw_dev, 0, sizeof(double) * (size_t)(ds->d + 2), s));
     return run_col_and_fixup(ds, false, out_raw_dev, true, false);
@@ -206,8 +223,8 @@ int finalize(pml_dataset *ds, int loss, const double *raw_dev, double *out_value
 {
     pml_ctx *ctx = ds->ctx;
     const bool hinge = loss == PML_LOSS_SMOOTHED_HINGE;
-    return count(ctx, launch_finalize(ctx->stream, ds->d, raw_dev, hinge ? nullptr : ds->factors,
-                                      hinge ? nullptr : ds->shifts, out_value_dev, out_vec_dev));
+    return run(ctx, PML_K_FINALIZE, [&] { return launch_finalize(ctx->stream, ds->d, raw_dev, hinge ? nullptr : ds->factors,
+                                      hinge ? nullptr : ds->shifts, out_value_dev, out_vec_dev); });
 }
 
 int diag_dev(pml_dataset *ds, int loss, const double *coef_dev, double *out_dev /* d+2 */)
@@ -229,7 +246,7 @@ int diag_dev(pml_dataset *ds, int loss, const double *coef_dev, double *out_dev 
     rp.vec = coef_dev;
     rp.mode = MODE_DIAG;
     rp.loss = loss;
-    PML_TRY(count(ctx, launch_row_pass(s, ctx->sm_count, ds->value_bytes, ds->lanes_per_row, false, rp, &ds->row_grid)));
+    PML_TRY(run(ctx, PML_K_ROW, [&] { return launch_row_pass(s, ctx->sm_count, ds->value_bytes, ds->lanes_per_row, false, rp, &ds->row_grid); }));
     PML_CUDA(cudaMemsetAsync(out_dev, 0, sizeof(double) * (size_t)(ds->d + 2), s));
     return run_col_and_fixup(ds, true, out_dev, false, false);
 }
@@ -306,6 +323,33 @@ int pml_ctx_launch_count(pml_ctx *ctx, int64_t *out)
 {
     if (!ctx || !out) return fail(PML_EINVAL, "null argument");
     *out = ctx->launches;
+    return PML_OK;
+}
+
+int pml_ctx_set_profiling(pml_ctx *ctx, int on)
+{
+    if (!ctx) return fail(PML_EINVAL, "null context");
+    Guard g(ctx);
+    ctx->profiling = on != 0;
+    return PML_OK;
+}
+
+int pml_ctx_read_profile(pml_ctx *ctx, double *out_ms, int64_t *out_launches)
+{
+    if (!ctx || !out_ms || !out_launches) return fail(PML_EINVAL, "null argument");
+    Guard g(ctx);
+    PML_CUDA(cudaSetDevice(ctx->device));
+    PML_CUDA(cudaStreamSynchronize(ctx->stream));
+    for (int k = 0; k < PML_K_COUNT; ++k) { out_ms[k] = 0.0; out_launches[k] = 0; }
+    for (auto &sp : ctx->spans) {
+        float ms = 0.f;
+        PML_CUDA(cudaEventElapsedTime(&ms, sp.a, sp.b));
+        out_ms[sp.kind] += ms;
+        out_launches[sp.kind] += 1;
+        cudaEventDestroy(sp.a);
+        cudaEventDestroy(sp.b);
+    }
+    ctx->spans.clear();
     return PML_OK;
 }
 
@@ -705,7 +749,7 @@ int pml_scores(pml_dataset *ds, const double *coef, double *out_scores)
     rp.r = ds->r;
     rp.vec = ds->io_a;
     rp.mode = MODE_SCORE;
-    PML_TRY(count(ds->ctx, launch_row_pass(s, ds->ctx->sm_count, ds->value_bytes, ds->lanes_per_row, false, rp, &ds->row_grid)));
+    PML_TRY(run(ds->ctx, PML_K_ROW, [&] { return launch_row_pass(s, ds->ctx->sm_count, ds->value_bytes, ds->lanes_per_row, false, rp, &ds->row_grid); }));
     if (ds->n > 0) PML_CUDA(cudaMemcpyAsync(out_scores, ds->r, sizeof(double) * (size_t)ds->n, cudaMemcpyDeviceToHost, s));
     PML_CUDA(cudaStreamSynchronize(s));
     return PML_OK;

@@ -7,6 +7,7 @@
 
 #include <mutex>
 #include <string>
+#include <vector>
 
 #include "../../include/photon_ml_b200.h"
 
@@ -120,7 +121,14 @@ struct Packed {
 
 }  // namespace pml
 
+struct pml_span {
+    int kind;
+    cudaEvent_t a, b;
+};
+
 struct pml_ctx {
+    bool profiling = false;
+    std::vector<pml_span> spans;
     int device = 0;
     int sm_count = 148;
     cudaStream_t stream = nullptr;

@@ -125,7 +125,7 @@ def test_heart_fp32_storage_is_refused_but_f32_input_is_fine(ctx):
 def test_ragged_skewed_with_weights_offsets(ctx, variant, loss):
     # hot columns span several 4096-entry chunks (fix-up path), 5 % empty rows, many empty columns
     rng = np.random.default_rng(10 + variant)
-    n, d = 6000, 700
+    n, d = 6000, 4000
     row_ptr, col, val = util.random_csr(rng, n, d, 9, skew=1.3, empty_rows=0.05)
     off = rng.normal(scale=0.2, size=n)
     wt = rng.uniform(0.2, 3.0, size=n)
