@@ -181,6 +181,38 @@ int pml_ctx_read_profile(pml_ctx *ctx, double *out_ms /* [PML_K_COUNT] */,
  * -1 = back to the nnz/row heuristic.  For benchmarking and tests. */
 int pml_dataset_set_margin_variant(pml_dataset *ds, int lanes_per_row);
 
+/* ---- evaluation without any allocation ------------------------------------------------------ */
+/* No counterpart in the reference (the JVM allocates freely); this exists for callers of THIS
+ * library that must not trigger cudaMalloc/cudaFree: the JNI shim while it pins Java arrays with
+ * GetPrimitiveArrayCritical (the JVM may be holding off garbage collection for all threads, and
+ * cudaMalloc synchronises the device and can block), and executor threads that evaluate many
+ * small per-entity problems side by side on one GPU (an allocation in one stalls the kernels of
+ * all).  Such callers keep their rows in device memory themselves and cannot create a
+ * pml_dataset, because packing allocates.
+ *
+ * Computes *out_value_dev = sum_i weights[i] * l(x_i . coef + offsets[i], labels[i]) -- what
+ * DistributedGLMLossFunction.value returns when no normalization is set -- directly from the
+ * caller's CSR arrays (row_ptr_dev: n+1 int64 starting at 0; col_idx_dev in [0, d), not
+ * checked; values_dev float or double per values_dtype; offsets_dev / weights_dev may be NULL =
+ * 0 / 1).  All pointers are device memory on `device`; the work is enqueued on `stream`
+ * (a cudaStream_t, NULL = default stream) and the call returns without synchronising.
+ *
+ * It calls no cudaMalloc, cudaFree or allocating library routine.  Its scratch (one partial sum
+ * per 256 rows plus a completion counter, 512 KB) is a fixed array inside the library image,
+ * resident on every GPU that loads the library for the life of the process.  Consequences:
+ *  - n is limited to 16,777,216 rows (65,536 CTAs x 256 rows); larger n fails with PML_EINVAL.
+ *  - all calls on one device share that array: two calls whose kernels overlap on the GPU
+ *    (different streams, or different threads) race and give wrong sums.  Issue them on one
+ *    stream, or otherwise order them.  The array keeps the previous call's contents; the call
+ *    clears the counter itself, nothing needs resetting by the caller.
+ *  - the first call on each device also looks up the array's device address
+ *    (cudaGetSymbolAddress); make that first call before starting any stream capture. */
+int pml_value_noalloc_dev(int device, void *stream, int64_t n, int32_t d,
+                          const int64_t *row_ptr_dev, const int32_t *col_idx_dev,
+                          const void *values_dev, int values_dtype, const double *labels_dev,
+                          const double *offsets_dev, const double *weights_dev, int loss,
+                          const double *coef_dev, double *out_value_dev);
+
 #ifdef __cplusplus
 }
 #endif

@@ -25,6 +25,7 @@ SYMBOLS = [
     "pml_hessian_diagonal", "pml_scores", "pml_value_and_gradient_raw_dev", "pml_hessian_vector_raw_dev",
     "pml_finalize_dev", "pml_value_and_gradient_dev", "pml_hessian_vector_dev", "pml_ctx_launch_count",
     "pml_dataset_set_margin_variant", "pml_ctx_set_profiling", "pml_ctx_read_profile",
+    "pml_value_noalloc_dev",
 ]
 
 
@@ -93,6 +94,7 @@ def load():
         "pml_dataset_set_margin_variant": [vp, ctypes.c_int],
         "pml_ctx_set_profiling": [vp, ctypes.c_int],
         "pml_ctx_read_profile": [vp, ctypes.POINTER(dbl), ctypes.POINTER(i64)],
+        "pml_value_noalloc_dev": [ctypes.c_int, vp, i64, i32, vp, vp, vp, ctypes.c_int, vp, vp, vp, ctypes.c_int, vp, vp],
     }
     for name, argtypes in sigs.items():
         fn = getattr(lib, name)
@@ -122,6 +124,15 @@ def _np(a, dtype, size=None, name="array"):
 
 def _ptr(a):
     return None if a is None else a.ctypes.data_as(ctypes.c_void_p)
+
+
+def value_noalloc_dev(device, stream, n, d, row_ptr_dev, col_dev, val_dev, values_dtype, label_dev, offset_dev,
+                      weight_dev, loss, coef_dev, out_value_dev):
+    """pml_value_noalloc_dev: objective value from caller-owned device CSR arrays, for callers that
+    must not allocate (all arguments after `stream` are sizes or integer device addresses).
+    Asynchronous on `stream`; at most 16,777,216 rows; calls on one device must not overlap."""
+    check(load().pml_value_noalloc_dev(int(device), stream, n, d, row_ptr_dev, col_dev, val_dev, values_dtype, label_dev,
+                                       offset_dev, weight_dev, loss, coef_dev, out_value_dev))
 
 
 class Context:
