@@ -2,6 +2,7 @@
 // evaluation entry points that string the kernels of kernels.cu together.
 #include <cuda_runtime.h>
 
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <string>
@@ -115,14 +116,13 @@ int run_col_and_fixup(pml_dataset *ds, bool square, double *out, bool with_scala
     cp.nnz = ds->nnz;
     cp.row = ds->t.csc_row;
     cp.val = ds->t.csc_val;
-    cp.nzcol_ptr = ds->t.nzcol_ptr;
     cp.nzcol_id = ds->t.nzcol_id;
     cp.chunk_col_lo = ds->t.chunk_col_lo;
     cp.r = ds->r;
     cp.out = out;
     cp.carry_head = ds->carry_head;
     cp.n_chunks = ds->t.n_chunks;
-    PML_TRY(run(ctx, PML_K_COL, [&] { return launch_col_pass(s, ds->value_bytes, square, cp); }));
+    PML_TRY(run(ctx, PML_K_COL, [&] { return launch_col_pass(s, ds->value_bytes, square, ds->t.chunk_entries, cp); }));
     PML_TRY(run(ctx, PML_K_FIXUP, [&] { return launch_fixup(s, ds->t.fix, ds->t.n_fix, ds->carry_head, out, ds->d,
                                     with_scalars ? ds->partials : nullptr, ds->row_grid, write_value, true); }));
     return PML_OK;
@@ -136,13 +136,15 @@ int vg_raw(pml_dataset *ds, int loss, const double *coef_dev, double *out_raw_de
     const bool norm = !hinge && (ds->factors || ds->shifts);
     RowPassParams rp;
     std::memset(&rp, 0, sizeof(rp));
-    rp.vec = coef_dev;
-    if (norm) {
+    {
+        // always runs: besides ec = c .* f it moves the coefficients to the columns' internal ids
         int np = 0;
-        PML_TRY(run(ctx, PML_K_PREPARE, [&] { return launch_prepare_vectors(s, ds->d, coef_dev, nullptr, ds->factors, ds->shifts, ds->vec,
-                                                  ds->shift_partials, &np); }));
+        PML_TRY(run(ctx, PML_K_PREPARE, [&] {
+            return launch_prepare_vectors(s, ds->d, coef_dev, nullptr, norm ? ds->factors : nullptr,
+                                          norm ? ds->shifts : nullptr, ds->t.rank, ds->vec, ds->shift_partials, &np);
+        }));
         rp.vec = ds->vec;
-        if (ds->shifts) {
+        if (norm && ds->shifts) {
             rp.shift_partials = ds->shift_partials;
             rp.n_shift_partials = np;
         }
@@ -159,7 +161,7 @@ int vg_raw(pml_dataset *ds, int loss, const double *coef_dev, double *out_raw_de
     rp.partials = ds->partials;
     rp.mode = MODE_VG;
     rp.loss = loss;
-    PML_TRY(run(ctx, PML_K_ROW, [&] { return launch_row_pass(s, ctx->sm_count, ds->value_bytes, ds->lanes_per_row, false, rp, &ds->row_grid); }));
+    PML_TRY(run(ctx, PML_K_ROW, [&] { return launch_row_pass(s, ctx->sm_count, ds->value_bytes, ds->lanes_per_row, false, rp, ds->t.m, &ds->row_grid); }));
     return run_col_and_fixup(ds, false, out_raw_dev, true, true);
 }
 
@@ -187,8 +189,10 @@ int hv_raw(pml_dataset *ds, int loss, const double *coef_dev, uint64_t tag, cons
     if (!cached) {
         if (coef_dev == nullptr) return fail(PML_EINVAL, "coefficients are required when no cached pass matches the tag");
         if (tag != 0 && ds->dcache == nullptr) PML_TRY(dev_alloc(&ds->dcache, (size_t)ds->n, &ds->bytes));
-        PML_TRY(run(ctx, PML_K_PREPARE, [&] { return launch_prepare_vectors(s, ds->d, coef_dev, v_dev, ds->factors, ds->shifts, ds->vec,
-                                                  ds->shift_partials, &np); }));
+        PML_TRY(run(ctx, PML_K_PREPARE, [&] {
+            return launch_prepare_vectors(s, ds->d, coef_dev, v_dev, ds->factors, ds->shifts, ds->t.rank, ds->vec,
+                                          ds->shift_partials, &np);
+        }));
         rp.vec = ds->vec;
         if (ds->shifts) {
             rp.shift_partials = ds->shift_partials;
@@ -196,24 +200,23 @@ int hv_raw(pml_dataset *ds, int loss, const double *coef_dev, uint64_t tag, cons
         }
         rp.dcache = tag != 0 ? ds->dcache : nullptr;
         rp.mode = MODE_HV_COLD;
-        PML_TRY(run(ctx, PML_K_ROW, [&] { return launch_row_pass(s, ctx->sm_count, ds->value_bytes, ds->lanes_per_row, true, rp, &ds->row_grid); }));
+        PML_TRY(run(ctx, PML_K_ROW, [&] { return launch_row_pass(s, ctx->sm_count, ds->value_bytes, ds->lanes_per_row, true, rp, ds->t.m, &ds->row_grid); }));
         ds->cache_valid = tag != 0;
         ds->cached_tag = tag;
         ds->cached_loss = loss;
     } else {
-        rp.vec = v_dev;
-        if (norm) {
-            PML_TRY(run(ctx, PML_K_PREPARE, [&] { return launch_prepare_vectors(s, ds->d, v_dev, nullptr, ds->factors, ds->shifts, ds->vec,
-                                                      ds->shift_partials, &np); }));
-            rp.vec = ds->vec;
-            if (ds->shifts) {
-                rp.shift_partials = ds->shift_partials;
-                rp.n_shift_partials = np;
-            }
+        PML_TRY(run(ctx, PML_K_PREPARE, [&] {
+            return launch_prepare_vectors(s, ds->d, v_dev, nullptr, ds->factors, ds->shifts, ds->t.rank, ds->vec,
+                                          ds->shift_partials, &np);
+        }));
+        rp.vec = ds->vec;
+        if (ds->shifts) {
+            rp.shift_partials = ds->shift_partials;
+            rp.n_shift_partials = np;
         }
         rp.dcache = ds->dcache;
         rp.mode = MODE_HV_CACHED;
-        PML_TRY(run(ctx, PML_K_ROW, [&] { return launch_row_pass(s, ctx->sm_count, ds->value_bytes, ds->lanes_per_row, false, rp, &ds->row_grid); }));
+        PML_TRY(run(ctx, PML_K_ROW, [&] { return launch_row_pass(s, ctx->sm_count, ds->value_bytes, ds->lanes_per_row, false, rp, ds->t.m, &ds->row_grid); }));
     }
     PML_CUDA(cudaMemsetAsync(out_raw_dev, 0, sizeof(double) * (size_t)(ds->d + 2), s));
     return run_col_and_fixup(ds, false, out_raw_dev, true, false);
@@ -243,10 +246,17 @@ int diag_dev(pml_dataset *ds, int loss, const double *coef_dev, double *out_dev 
     rp.offset = ds->offset;
     rp.weight = ds->weight;
     rp.r = ds->r;
-    rp.vec = coef_dev;
+    {
+        int np = 0;  // raw coefficients (HessianDiagonalAggregator ignores normalization), moved to internal ids
+        PML_TRY(run(ctx, PML_K_PREPARE, [&] {
+            return launch_prepare_vectors(s, ds->d, coef_dev, nullptr, nullptr, nullptr, ds->t.rank, ds->vec,
+                                          ds->shift_partials, &np);
+        }));
+    }
+    rp.vec = ds->vec;
     rp.mode = MODE_DIAG;
     rp.loss = loss;
-    PML_TRY(run(ctx, PML_K_ROW, [&] { return launch_row_pass(s, ctx->sm_count, ds->value_bytes, ds->lanes_per_row, false, rp, &ds->row_grid); }));
+    PML_TRY(run(ctx, PML_K_ROW, [&] { return launch_row_pass(s, ctx->sm_count, ds->value_bytes, ds->lanes_per_row, false, rp, ds->t.m, &ds->row_grid); }));
     PML_CUDA(cudaMemsetAsync(out_dev, 0, sizeof(double) * (size_t)(ds->d + 2), s));
     return run_col_and_fixup(ds, true, out_dev, false, false);
 }
@@ -374,7 +384,7 @@ int pml_dataset_destroy(pml_dataset *ds)
         cudaStreamSynchronize(ds->ctx->stream);
     }
     void *ptrs[] = { ds->row_ptr, ds->col, ds->val, ds->label, ds->offset, ds->weight, ds->t.csc_row, ds->t.csc_val,
-                     ds->t.nzcol_ptr, ds->t.nzcol_id, ds->t.chunk_col_lo, ds->t.fix, ds->factors, ds->shifts, ds->r,
+                     ds->t.nzcol_ptr, ds->t.nzcol_id, ds->t.rank, ds->t.chunk_col_lo, ds->t.fix, ds->factors, ds->shifts, ds->r,
                      ds->dcache, ds->partials, ds->carry_head, ds->raw, ds->vec, ds->shift_partials, ds->io_a, ds->io_b,
                      ds->io_n };
     for (void *p : ptrs)
@@ -466,7 +476,12 @@ int pml_dataset_create_csr_dev(pml_ctx *ctx, int64_t n, int32_t d, const int64_t
     PML_TRY(upload_optional(s, &ds->offset, offsets_dev, n, true, &ds->bytes));
     PML_TRY(upload_optional(s, &ds->weight, weights_dev, n, true, &ds->bytes));
 
-    PML_TRY(build_transpose(s, n, d, nnz, ds->row_ptr, ds->col, ds->val, dst_bytes, &ds->t));
+    int chunk_entries = TCHUNK;
+    if (const char *e = std::getenv("PML_COL_ITEMS")) {  // tuning knob: entries per thread of the column pass
+        const int items = std::atoi(e);
+        if (items == 8 || items == 16) chunk_entries = items * T_THREADS;
+    }
+    PML_TRY(build_transpose(s, n, d, nnz, ds->row_ptr, ds->col, ds->val, dst_bytes, chunk_entries, &ds->t));
     ds->bytes += ds->t.bytes;
 
     PML_TRY(dev_alloc(&ds->r, (size_t)n, &ds->bytes));
@@ -747,9 +762,16 @@ int pml_scores(pml_dataset *ds, const double *coef, double *out_scores)
     rp.val = ds->val;
     rp.label = ds->label;
     rp.r = ds->r;
-    rp.vec = ds->io_a;
+    {
+        int np = 0;
+        PML_TRY(run(ds->ctx, PML_K_PREPARE, [&] {
+            return launch_prepare_vectors(s, ds->d, ds->io_a, nullptr, nullptr, nullptr, ds->t.rank, ds->vec,
+                                          ds->shift_partials, &np);
+        }));
+    }
+    rp.vec = ds->vec;
     rp.mode = MODE_SCORE;
-    PML_TRY(run(ds->ctx, PML_K_ROW, [&] { return launch_row_pass(s, ds->ctx->sm_count, ds->value_bytes, ds->lanes_per_row, false, rp, &ds->row_grid); }));
+    PML_TRY(run(ds->ctx, PML_K_ROW, [&] { return launch_row_pass(s, ds->ctx->sm_count, ds->value_bytes, ds->lanes_per_row, false, rp, ds->t.m, &ds->row_grid); }));
     if (ds->n > 0) PML_CUDA(cudaMemcpyAsync(out_scores, ds->r, sizeof(double) * (size_t)ds->n, cudaMemcpyDeviceToHost, s));
     PML_CUDA(cudaStreamSynchronize(s));
     return PML_OK;

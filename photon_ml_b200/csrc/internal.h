@@ -36,9 +36,10 @@ constexpr int T_ITEMS = 16;
 constexpr int TCHUNK = T_THREADS * T_ITEMS;  // 4096 entries = 32 KB of stream per chunk (fp32 values)
 
 // ---- geometry of the row (CSR) kernel ----
-constexpr int R_THREADS = 256;
+constexpr int R_THREADS = 1024;    // one persistent CTA per SM: the hot-coefficient table takes most of shared memory
 constexpr int R_WARPS = R_THREADS / 32;
-constexpr int R_STREAM_CAP = 512;  // products staged per warp per piece in the segment-per-warp variant
+constexpr int R_STREAM_CAP = 128;  // products staged per warp per piece in the segment-per-warp variant
+constexpr int R_MAX_DYN_SMEM = 220 * 1024;  // dynamic shared memory per row-pass CTA (227 KB minus static + margin)
 constexpr int MAX_PARTIALS = 4096; // upper bound on row-kernel CTAs (block partials of F and P)
 
 enum RowMode {
@@ -63,16 +64,16 @@ struct RowPassParams {
     double *r;                // n: per-row multiplier consumed by the transpose kernel
     double *dcache;           // n: wt*l''(z) written (HV_COLD) or read (HV_CACHED)
     double *partials;         // 2 * gridDim.x: per-CTA (F, P)
+    int n_hot;                // leading entries of vec staged in shared memory (set by the launcher)
     int mode;
     int loss;
 };
 
 struct ColPassParams {
     int64_t nnz;
-    const int32_t *row;           // nnz   CSC row indices
+    const int32_t *row;           // nnz   CSC row indices, bit 31 = first entry of a column
     const void *val;              // nnz
-    const uint32_t *nzcol_ptr;    // m+1   starts of the non-empty columns
-    const int32_t *nzcol_id;      // m     their column ids
+    const int32_t *nzcol_id;      // internal column id -> original column id
     const int32_t *chunk_col_lo;  // n_chunks+1
     const double *r;              // n
     double *out;                  // d (+2): zeroed before the launch
@@ -88,10 +89,12 @@ struct FixEntry {
 
 // launchers (kernels.cu); each returns the number of kernels it launched, <0 on launch error
 int launch_prepare_vectors(cudaStream_t s, int d, const double *coef, const double *v, const double *factors,
-                           const double *shifts, double *out_vec, double *shift_partials, int *n_partials);
+                           const double *shifts, const int32_t *rank, double *out_vec, double *shift_partials,
+                           int *n_partials);
 int launch_row_pass(cudaStream_t s, int sm_count, int value_bytes, int lanes_per_row, bool two,
-                    const RowPassParams &p, int *grid_out);
-int launch_col_pass(cudaStream_t s, int value_bytes, bool square, const ColPassParams &p);
+                    RowPassParams p, int64_t n_nonempty_cols, int *grid_out);
+int row_pass_hot_capacity(int lanes_per_row, bool two);
+int launch_col_pass(cudaStream_t s, int value_bytes, bool square, int chunk_entries, const ColPassParams &p);
 int launch_fixup(cudaStream_t s, const FixEntry *fix, int n_fix, const double *carry_head, double *out, int d,
                  const double *partials, int n_partials, bool write_value, bool write_prefactor);
 int launch_finalize(cudaStream_t s, int d, const double *raw, const double *factors, const double *shifts,
@@ -100,17 +103,19 @@ int launch_finalize(cudaStream_t s, int d, const double *raw, const double *fact
 // pack.cu: builds the CSC copy and its chunk metadata on the device
 struct Packed;
 int build_transpose(cudaStream_t s, int64_t n, int32_t d, int64_t nnz, const uint32_t *row_ptr,
-                    const int32_t *col, const void *val, int value_bytes, Packed *out);
+                    int32_t *col, const void *val, int value_bytes, int chunk_entries, Packed *out);
 int narrow_check(cudaStream_t s, const double *val, int64_t nnz, bool *all_exact);
 int convert_values(cudaStream_t s, const void *src, int src_bytes, void *dst, int dst_bytes, int64_t nnz);
 int check_columns(cudaStream_t s, const int32_t *col, int64_t nnz, int32_t d, int64_t *bad);
 int convert_row_ptr(cudaStream_t s, const int64_t *src, uint32_t *dst, int64_t n_plus_1, int64_t *bad);
 
 struct Packed {
-    int32_t *csc_row = nullptr;
+    int32_t *csc_row = nullptr;    // nnz: row index, bit 31 set on the first entry of each column
     void *csc_val = nullptr;
-    uint32_t *nzcol_ptr = nullptr;
-    int32_t *nzcol_id = nullptr;
+    uint32_t *nzcol_ptr = nullptr; // d+1: entry offset of each internal column (columns >= m are empty)
+    int32_t *nzcol_id = nullptr;   // d: internal id -> original column id
+    int32_t *rank = nullptr;       // d: original column id -> internal id
+    int chunk_entries = TCHUNK;
     int32_t *chunk_col_lo = nullptr;
     FixEntry *fix = nullptr;
     int64_t m = 0;  // non-empty columns

@@ -9,6 +9,12 @@
 // (aN = row of SURVEY.md 8a; reference file:line in DESIGN.md and at each kernel.)
 // All accumulation is fp64.  No atomics anywhere: every output word has exactly one writer, and
 // every reduction has a fixed shape, so results are bit-reproducible for a given packing.
+//
+// Columns carry "internal ids" assigned at pack time by descending entry count (pack.cu), so the
+// coefficients of the hottest columns sit at the front of the effective-coefficient vector and
+// can be staged in shared memory: a scattered 8-byte gather costs one L1 tag lookup per lane
+// (one per cycle per SM -- the measured limiter of the first version of these kernels), while
+// shared memory serves 32 lanes in a few cycles.
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -22,29 +28,32 @@ namespace pml {
 // ValueAndGradientAggregator.scala:90-122) and HessianVectorAggregator.init
 // (HessianVectorAggregator.scala:60-85): ec = coef .* factors, ev = v .* factors, and the two
 // dots with `shifts` as per-CTA partials (the row kernel adds them up in its prologue, so the
-// scalar needs no launch of its own).  When v != null the outputs are interleaved (ec_j, ev_j)
-// so that the row kernel fetches both with one 16-byte gather.
+// scalar needs no launch of its own).  The results are written at the columns' internal ids
+// (`rank`), and when v != null interleaved as (ec_j, ev_j) so that the row kernel fetches both
+// with one 16-byte access.
 // ------------------------------------------------------------------------------------------
 constexpr int PREP_THREADS = 256;
 
 __global__ void __launch_bounds__(PREP_THREADS)
 prepare_vectors_kernel(int d, const double *__restrict__ coef, const double *__restrict__ v,
                        const double *__restrict__ factors, const double *__restrict__ shifts,
-                       double *__restrict__ out_vec, double *__restrict__ shift_partials)
+                       const int32_t *__restrict__ rank, double *__restrict__ out_vec,
+                       double *__restrict__ shift_partials)
 {
     __shared__ double red[2 * (PREP_THREADS / 32)];
     double s0 = 0.0, s1 = 0.0;
     for (int j = blockIdx.x * PREP_THREADS + threadIdx.x; j < d; j += gridDim.x * PREP_THREADS) {
-        double f = factors ? factors[j] : 1.0;
-        double ec = factors ? __dmul_rn(coef[j], f) : coef[j];
-        double sh = shifts ? shifts[j] : 0.0;
+        const double f = factors ? factors[j] : 1.0;
+        const double ec = factors ? __dmul_rn(coef[j], f) : coef[j];
+        const double sh = shifts ? shifts[j] : 0.0;
+        const int32_t r = rank[j];
         s0 += __dmul_rn(ec, sh);
         if (v) {
-            double ev = factors ? __dmul_rn(v[j], f) : v[j];
+            const double ev = factors ? __dmul_rn(v[j], f) : v[j];
             s1 += __dmul_rn(ev, sh);
-            reinterpret_cast<double2 *>(out_vec)[j] = make_double2(ec, ev);
+            reinterpret_cast<double2 *>(out_vec)[r] = make_double2(ec, ev);
         } else {
-            out_vec[j] = ec;
+            out_vec[r] = ec;
         }
     }
     block_sum2<PREP_THREADS / 32>(s0, s1, red);
@@ -55,12 +64,13 @@ prepare_vectors_kernel(int d, const double *__restrict__ coef, const double *__r
 }
 
 int launch_prepare_vectors(cudaStream_t s, int d, const double *coef, const double *v, const double *factors,
-                           const double *shifts, double *out_vec, double *shift_partials, int *n_partials)
+                           const double *shifts, const int32_t *rank, double *out_vec, double *shift_partials,
+                           int *n_partials)
 {
     int grid = (d + PREP_THREADS * 4 - 1) / (PREP_THREADS * 4);
     if (grid < 1) grid = 1;
     if (grid > 1024) grid = 1024;
-    prepare_vectors_kernel<<<grid, PREP_THREADS, 0, s>>>(d, coef, v, factors, shifts, out_vec, shift_partials);
+    prepare_vectors_kernel<<<grid, PREP_THREADS, 0, s>>>(d, coef, v, factors, shifts, rank, out_vec, shift_partials);
     *n_partials = grid;
     return cudaGetLastError() == cudaSuccess ? 1 : -1;
 }
@@ -73,6 +83,10 @@ int launch_prepare_vectors(cudaStream_t s, int d, const double *coef, const doub
 // (LabeledPoint.computeMargin, lib/data/LabeledPoint.scala:62), the pointwise loss, the scalar
 // sums, and the per-row multiplier r_i that the column pass turns into the axpy.
 //
+// Persistent CTAs (one per SM when the hot table is large).  The first `n_hot` entries of the
+// effective-coefficient vector are copied to shared memory once per CTA; a lane whose column id
+// is below n_hot reads shared memory, the rest gather through L1.
+//
 // A warp owns 32 consecutive rows at a time.
 //   LPR in {2,4,8,16,32}: "lanes per row" -- 32/LPR rows are reduced concurrently by sub-warps
 //     of LPR lanes, LPR passes cover the 32 rows (LPR = 32 is warp-per-row).
@@ -82,32 +96,42 @@ int launch_prepare_vectors(cudaStream_t s, int d, const double *coef, const doub
 // Either way lane L ends up holding row L's dot product, so labels/offsets/weights are read and
 // r is written coalesced and the fp64 exp/log1p work runs with all 32 lanes active.
 // ------------------------------------------------------------------------------------------
-template <typename VT, bool TWO>
-__device__ __forceinline__ void gather_fma(const VT *__restrict__ val, const int32_t *__restrict__ col,
-                                           const double *__restrict__ vec, uint32_t k, double &a, double &b)
+template <bool TWO>
+__device__ __forceinline__ void lookup(const double *__restrict__ hot, int n_hot, const double *__restrict__ vec,
+                                       int32_t c, double &w0, double &w1)
 {
-    int32_t c = __ldcs(col + k);
-    double x = widen(__ldcs(val + k));
     if (TWO) {
-        double2 g = __ldg(reinterpret_cast<const double2 *>(vec) + c);
-        a = fma(x, g.x, a);
-        b = fma(x, g.y, b);
+        double2 g;
+        if (c < n_hot) g = reinterpret_cast<const double2 *>(hot)[c];
+        else g = __ldg(reinterpret_cast<const double2 *>(vec) + c);
+        w0 = g.x;
+        w1 = g.y;
     } else {
-        a = fma(x, __ldg(vec + c), a);
+        w0 = (c < n_hot) ? hot[c] : __ldg(vec + c);
+        w1 = 0.0;
     }
 }
 
 template <typename VT, int LPR, bool TWO>
-__global__ void __launch_bounds__(R_THREADS) row_pass_kernel(const RowPassParams p)
+__global__ void __launch_bounds__(R_THREADS, 1) row_pass_kernel(const RowPassParams p)
 {
     constexpr int CAPE = TWO ? R_STREAM_CAP / 2 : R_STREAM_CAP;
+    extern __shared__ __align__(16) double dyn_smem[];
     __shared__ double red[2 * R_WARPS];
-    __shared__ double stage[(LPR == 0) ? R_WARPS * R_STREAM_CAP : 1];
+    // dynamic shared memory: [stage (LPR == 0 only)] [hot table]
+    double *stage = dyn_smem;
+    double *hot = dyn_smem + ((LPR == 0) ? R_WARPS * R_STREAM_CAP : 0);
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const VT *__restrict__ val = static_cast<const VT *>(p.val);
     const int32_t *__restrict__ col = p.col;
     const double *__restrict__ vec = p.vec;
+    const int n_hot = p.n_hot;
+
+    {
+        const int words = TWO ? 2 * n_hot : n_hot;
+        for (int i = threadIdx.x; i < words; i += R_THREADS) hot[i] = vec[i];
+    }
 
     // marginShift = -(ec . shifts); featureVectorProductShift = ev . shifts
     double shift0 = 0.0, shift1 = 0.0;
@@ -118,6 +142,7 @@ __global__ void __launch_bounds__(R_THREADS) row_pass_kernel(const RowPassParams
         }
         block_sum2<R_WARPS>(shift0, shift1, red);
     }
+    __syncthreads();  // hot table visible
     const double margin_shift = (p.mode == MODE_HV_CACHED) ? 0.0 : -shift0;
     const double fs = (p.mode == MODE_HV_CACHED) ? shift0 : shift1;
 
@@ -140,15 +165,12 @@ __global__ void __launch_bounds__(R_THREADS) row_pass_kernel(const RowPassParams
                 const uint32_t pe = (lim - pb > (uint32_t)CAPE) ? pb + CAPE : lim;
 #pragma unroll 4
                 for (uint32_t k = pb + lane; k < pe; k += 32) {
-                    int32_t c = __ldcs(col + k);
-                    double x = widen(__ldcs(val + k));
-                    if (TWO) {
-                        double2 g = __ldg(reinterpret_cast<const double2 *>(vec) + c);
-                        buf[k - pb] = __dmul_rn(x, g.x);
-                        buf[CAPE + (k - pb)] = __dmul_rn(x, g.y);
-                    } else {
-                        buf[k - pb] = __dmul_rn(x, __ldg(vec + c));
-                    }
+                    const int32_t c = __ldcs(col + k);
+                    const double x = widen(__ldcs(val + k));
+                    double w0, w1;
+                    lookup<TWO>(hot, n_hot, vec, c, w0, w1);
+                    buf[k - pb] = __dmul_rn(x, w0);
+                    if (TWO) buf[CAPE + (k - pb)] = __dmul_rn(x, w1);
                 }
                 __syncwarp();
                 const uint32_t lo = rp_lo > pb ? rp_lo : pb;
@@ -171,15 +193,26 @@ __global__ void __launch_bounds__(R_THREADS) row_pass_kernel(const RowPassParams
                 double a = 0.0, b = 0.0;
                 uint32_t k = start + sl;
                 for (; k + 3 * L < end; k += 4 * L) {
-                    double a1 = 0.0, b1 = 0.0, a2 = 0.0, b2 = 0.0, a3 = 0.0, b3 = 0.0;
-                    gather_fma<VT, TWO>(val, col, vec, k, a, b);
-                    gather_fma<VT, TWO>(val, col, vec, k + L, a1, b1);
-                    gather_fma<VT, TWO>(val, col, vec, k + 2 * L, a2, b2);
-                    gather_fma<VT, TWO>(val, col, vec, k + 3 * L, a3, b3);
-                    a += (a1 + a2) + a3;
-                    if (TWO) b += (b1 + b2) + b3;
+                    const int32_t c0 = __ldcs(col + k), c1 = __ldcs(col + k + L);
+                    const int32_t c2 = __ldcs(col + k + 2 * L), c3 = __ldcs(col + k + 3 * L);
+                    const double x0 = widen(__ldcs(val + k)), x1 = widen(__ldcs(val + k + L));
+                    const double x2 = widen(__ldcs(val + k + 2 * L)), x3 = widen(__ldcs(val + k + 3 * L));
+                    double w00, w01, w10, w11, w20, w21, w30, w31;
+                    lookup<TWO>(hot, n_hot, vec, c0, w00, w01);
+                    lookup<TWO>(hot, n_hot, vec, c1, w10, w11);
+                    lookup<TWO>(hot, n_hot, vec, c2, w20, w21);
+                    lookup<TWO>(hot, n_hot, vec, c3, w30, w31);
+                    a += (x0 * w00 + x1 * w10) + (x2 * w20 + x3 * w30);
+                    if (TWO) b += (x0 * w01 + x1 * w11) + (x2 * w21 + x3 * w31);
                 }
-                for (; k < end; k += L) gather_fma<VT, TWO>(val, col, vec, k, a, b);
+                for (; k < end; k += L) {
+                    const int32_t c = __ldcs(col + k);
+                    const double x = widen(__ldcs(val + k));
+                    double w0, w1;
+                    lookup<TWO>(hot, n_hot, vec, c, w0, w1);
+                    a = fma(x, w0, a);
+                    if (TWO) b = fma(x, w1, b);
+                }
 #pragma unroll
                 for (int o = L / 2; o > 0; o >>= 1) {
                     a += __shfl_xor_sync(0xffffffffu, a, o);
@@ -245,36 +278,56 @@ __global__ void __launch_bounds__(R_THREADS) row_pass_kernel(const RowPassParams
     }
 }
 
-template <typename VT, bool TWO>
-static int launch_row_variant(cudaStream_t s, int grid, int lpr, const RowPassParams &p)
+template <typename VT, int LPR, bool TWO>
+static int launch_row_one(cudaStream_t s, int grid, size_t smem, const RowPassParams &p)
 {
-    switch (lpr) {
-    case 0: row_pass_kernel<VT, 0, TWO><<<grid, R_THREADS, 0, s>>>(p); break;
-    case 2: row_pass_kernel<VT, 2, TWO><<<grid, R_THREADS, 0, s>>>(p); break;
-    case 4: row_pass_kernel<VT, 4, TWO><<<grid, R_THREADS, 0, s>>>(p); break;
-    case 8: row_pass_kernel<VT, 8, TWO><<<grid, R_THREADS, 0, s>>>(p); break;
-    case 16: row_pass_kernel<VT, 16, TWO><<<grid, R_THREADS, 0, s>>>(p); break;
-    case 32: row_pass_kernel<VT, 32, TWO><<<grid, R_THREADS, 0, s>>>(p); break;
-    default: return -1;
-    }
+    // per device and per instantiation; cheap enough to repeat on every launch
+    if (smem > 48 * 1024 &&
+        cudaFuncSetAttribute(row_pass_kernel<VT, LPR, TWO>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             R_MAX_DYN_SMEM) != cudaSuccess)
+        return -1;
+    row_pass_kernel<VT, LPR, TWO><<<grid, R_THREADS, smem, s>>>(p);
     return cudaGetLastError() == cudaSuccess ? 1 : -1;
 }
 
+template <typename VT, bool TWO>
+static int launch_row_variant(cudaStream_t s, int grid, int lpr, size_t smem, const RowPassParams &p)
+{
+    switch (lpr) {
+    case 0: return launch_row_one<VT, 0, TWO>(s, grid, smem, p);
+    case 2: return launch_row_one<VT, 2, TWO>(s, grid, smem, p);
+    case 4: return launch_row_one<VT, 4, TWO>(s, grid, smem, p);
+    case 8: return launch_row_one<VT, 8, TWO>(s, grid, smem, p);
+    case 16: return launch_row_one<VT, 16, TWO>(s, grid, smem, p);
+    case 32: return launch_row_one<VT, 32, TWO>(s, grid, smem, p);
+    default: return -1;
+    }
+}
+
+int row_pass_hot_capacity(int lanes_per_row, bool two)
+{
+    const size_t stage = lanes_per_row == 0 ? sizeof(double) * R_WARPS * R_STREAM_CAP : 0;
+    return (int)((R_MAX_DYN_SMEM - stage) / (two ? 16 : 8));
+}
+
 int launch_row_pass(cudaStream_t s, int sm_count, int value_bytes, int lanes_per_row, bool two,
-                    const RowPassParams &p, int *grid_out)
+                    RowPassParams p, int64_t n_nonempty_cols, int *grid_out)
 {
     const int64_t n_blk = (p.n + 31) / 32;
     int64_t want = (n_blk + R_WARPS - 1) / R_WARPS;
-    int64_t cap = (int64_t)sm_count * 8;  // 8 CTAs of 256 threads fill an SM
-    if (cap > MAX_PARTIALS) cap = MAX_PARTIALS;
-    int grid = (int)(want < cap ? want : cap);
+    int grid = (int)(want < sm_count ? want : sm_count);
     if (grid < 1) grid = 1;
+    if (grid > MAX_PARTIALS) grid = MAX_PARTIALS;
     *grid_out = grid;
+    const int cap = row_pass_hot_capacity(lanes_per_row, two);
+    p.n_hot = (int)(n_nonempty_cols < cap ? n_nonempty_cols : cap);
+    const size_t stage = lanes_per_row == 0 ? sizeof(double) * R_WARPS * R_STREAM_CAP : 0;
+    const size_t smem = stage + (size_t)p.n_hot * (two ? 16 : 8);
     if (value_bytes == 4)
-        return two ? launch_row_variant<float, true>(s, grid, lanes_per_row, p)
-                   : launch_row_variant<float, false>(s, grid, lanes_per_row, p);
-    return two ? launch_row_variant<double, true>(s, grid, lanes_per_row, p)
-               : launch_row_variant<double, false>(s, grid, lanes_per_row, p);
+        return two ? launch_row_variant<float, true>(s, grid, lanes_per_row, smem, p)
+                   : launch_row_variant<float, false>(s, grid, lanes_per_row, smem, p);
+    return two ? launch_row_variant<double, true>(s, grid, lanes_per_row, smem, p)
+               : launch_row_variant<double, false>(s, grid, lanes_per_row, smem, p);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -284,12 +337,12 @@ int launch_row_pass(cudaStream_t s, int sm_count, int value_bytes, int lanes_per
 // HessianDiagonalAggregator.scala:59).
 //
 // Work is split by ENTRIES, not by columns (column lengths are power-law): CTA c owns entries
-// [c*TCHUNK, (c+1)*TCHUNK).  It streams row indices and values with 128-bit loads, gathers r,
-// parks the fp64 products in shared memory, marks column starts, and then runs a blocked
-// segmented reduction: each thread adds up 16 consecutive products, a CTA-wide segmented scan
-// carries partial sums across threads.  Columns that start in the chunk are written by this CTA
-// (single writer); the part of the chunk that precedes its first column start belongs to a
-// column begun in an earlier chunk and goes to carry_head[c] for fixup_kernel.
+// [c*CHUNK, (c+1)*CHUNK), CHUNK = 256*ITEMS.  Each thread loads ITEMS consecutive entries
+// (row index with the column-start flag in bit 31, value) with 128-bit loads, gathers r for all
+// of them at once, adds up its own run, and a CTA-wide segmented scan carries partial sums
+// across threads.  Columns that start in the chunk are written by this CTA (single writer); the
+// part of the chunk that precedes its first column start belongs to a column begun in an earlier
+// chunk and goes to carry_head[c] for fixup_kernel.
 // ------------------------------------------------------------------------------------------
 struct SegScan {
     int cnt;     // column starts seen
@@ -306,81 +359,67 @@ __device__ __forceinline__ SegScan seg_combine(const SegScan &l, const SegScan &
     return o;
 }
 
-__device__ __forceinline__ int pad16(int p) { return p + (p >> 4); }
-
-template <typename VT, bool SQUARE>
+template <typename VT, bool SQUARE, int ITEMS>
 __global__ void __launch_bounds__(T_THREADS) col_pass_kernel(const ColPassParams p)
 {
-    __shared__ double prod[TCHUNK + TCHUNK / 16];
-    __shared__ __align__(16) unsigned char flags[TCHUNK];
+    constexpr int CHUNK = T_THREADS * ITEMS;
     __shared__ SegScan wagg[T_THREADS / 32];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int c = blockIdx.x;
-    const int64_t base = (int64_t)c * TCHUNK;
-    const int cnt = (p.nnz - base) < TCHUNK ? (int)(p.nnz - base) : TCHUNK;
+    const int64_t base = (int64_t)c * CHUNK;
+    const int cnt = (p.nnz - base) < CHUNK ? (int)(p.nnz - base) : CHUNK;
     const int col_lo = p.chunk_col_lo[c], col_hi = p.chunk_col_lo[c + 1];
-    const VT *__restrict__ val = static_cast<const VT *>(p.val) + base;
-    const int32_t *__restrict__ row = p.row + base;
+    const VT *__restrict__ val = static_cast<const VT *>(p.val) + base + tid * ITEMS;
+    const int32_t *__restrict__ row = p.row + base + tid * ITEMS;
     const double *__restrict__ r = p.r;
 
-    reinterpret_cast<uint4 *>(flags)[tid] = make_uint4(0, 0, 0, 0);
-
-    // ---- phase 1: stream the chunk, gather r, park products ----
-    if (cnt == TCHUNK) {
+    // ---- load ITEMS consecutive entries (the arrays are padded by 16 entries past nnz) ----
+    int32_t rw[ITEMS];
+    double pr[ITEMS];
+    const int mine_cnt = cnt - tid * ITEMS;  // entries of this thread that exist (may be <= 0 in the last chunk)
 #pragma unroll
-        for (int i = 0; i < T_ITEMS / 4; ++i) {
-            const int v4 = i * T_THREADS + tid;
-            const int4 rr = __ldcs(reinterpret_cast<const int4 *>(row) + v4);
-            double x0, x1, x2, x3;
-            if (sizeof(VT) == 4) {
-                const float4 vv = __ldcs(reinterpret_cast<const float4 *>(val) + v4);
-                x0 = vv.x; x1 = vv.y; x2 = vv.z; x3 = vv.w;
-            } else {
-                const double2 va = __ldcs(reinterpret_cast<const double2 *>(val) + 2 * v4);
-                const double2 vb = __ldcs(reinterpret_cast<const double2 *>(val) + 2 * v4 + 1);
-                x0 = va.x; x1 = va.y; x2 = vb.x; x3 = vb.y;
-            }
-            if (SQUARE) { x0 *= x0; x1 *= x1; x2 *= x2; x3 *= x3; }
-            const double r0 = __ldg(r + rr.x), r1 = __ldg(r + rr.y), r2 = __ldg(r + rr.z), r3 = __ldg(r + rr.w);
-            const int q = pad16(4 * v4);  // 4*v4 .. 4*v4+3 share one 16-group: contiguous after padding
-            prod[q] = __dmul_rn(r0, x0);
-            prod[q + 1] = __dmul_rn(r1, x1);
-            prod[q + 2] = __dmul_rn(r2, x2);
-            prod[q + 3] = __dmul_rn(r3, x3);
+    for (int i = 0; i < ITEMS / 4; ++i) {
+        if (mine_cnt <= 0) {
+            rw[4 * i] = rw[4 * i + 1] = rw[4 * i + 2] = rw[4 * i + 3] = 0;
+            pr[4 * i] = pr[4 * i + 1] = pr[4 * i + 2] = pr[4 * i + 3] = 0.0;
+            continue;
         }
-    } else {
-        for (int e = tid; e < TCHUNK; e += T_THREADS) {
-            double v = 0.0;
-            if (e < cnt) {
-                double x = widen(val[e]);
-                if (SQUARE) x *= x;
-                v = __dmul_rn(__ldg(r + row[e]), x);
-            }
-            prod[pad16(e)] = v;
+        const int4 rr = __ldg(reinterpret_cast<const int4 *>(row) + i);
+        rw[4 * i] = rr.x; rw[4 * i + 1] = rr.y; rw[4 * i + 2] = rr.z; rw[4 * i + 3] = rr.w;
+        if (sizeof(VT) == 4) {
+            const float4 vv = __ldg(reinterpret_cast<const float4 *>(val) + i);
+            pr[4 * i] = vv.x; pr[4 * i + 1] = vv.y; pr[4 * i + 2] = vv.z; pr[4 * i + 3] = vv.w;
+        } else {
+            const double2 va = __ldg(reinterpret_cast<const double2 *>(val) + 2 * i);
+            const double2 vb = __ldg(reinterpret_cast<const double2 *>(val) + 2 * i + 1);
+            pr[4 * i] = va.x; pr[4 * i + 1] = va.y; pr[4 * i + 2] = vb.x; pr[4 * i + 3] = vb.y;
         }
     }
-    __syncthreads();  // flags are zero
-    for (int j = col_lo + tid; j < col_hi; j += T_THREADS) flags[(int64_t)p.nzcol_ptr[j] - base] = 1;
-    __syncthreads();
+    unsigned mask = 0;
+#pragma unroll
+    for (int i = 0; i < ITEMS; ++i) {
+        const bool live = i < mine_cnt;
+        if (live && rw[i] < 0) mask |= 1u << i;
+        const int32_t ri = live ? (rw[i] & 0x7fffffff) : 0;
+        double x = live ? pr[i] : 0.0;
+        if (SQUARE) x *= x;
+        pr[i] = __dmul_rn(__ldg(r + ri), x);
+    }
 
-    // ---- phase 2: blocked segmented reduction ----
-    const uint4 f4 = reinterpret_cast<const uint4 *>(flags)[tid];
-    const unsigned fw[4] = { f4.x, f4.y, f4.z, f4.w };
+    // ---- blocked segmented reduction ----
     SegScan mine;
-    mine.cnt = __popc(f4.x) + __popc(f4.y) + __popc(f4.z) + __popc(f4.w);
-    mine.flag = mine.cnt > 0;
+    mine.cnt = __popc(mask);
+    mine.flag = mask != 0;
     {
-        // value = sum after the last flag (whole run if none); a cheap first walk
         double s = 0.0;
 #pragma unroll
-        for (int i = 0; i < T_ITEMS; ++i) {
-            if ((fw[i >> 2] >> ((i & 3) * 8)) & 0xff) s = 0.0;
-            s += prod[pad16(tid * T_ITEMS) + i];
+        for (int i = 0; i < ITEMS; ++i) {
+            if ((mask >> i) & 1u) s = 0.0;
+            s += pr[i];
         }
-        mine.val = s;
+        mine.val = s;  // sum after the last column start (the whole run if there is none)
     }
-    // inclusive warp scan
     SegScan inc = mine;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -405,11 +444,11 @@ __global__ void __launch_bounds__(T_THREADS) col_pass_kernel(const ColPassParams
     // walk again, closing columns
     if (mine.flag) {
         double s = 0.0;
-        int ord = col_lo + exc.cnt;  // ordinal of the next column start this thread meets
+        int ord = col_lo + exc.cnt;  // internal id of the next column start this thread meets
         bool first = true;
 #pragma unroll
-        for (int i = 0; i < T_ITEMS; ++i) {
-            if ((fw[i >> 2] >> ((i & 3) * 8)) & 0xff) {
+        for (int i = 0; i < ITEMS; ++i) {
+            if ((mask >> i) & 1u) {
                 const double total = first ? exc.val + s : s;
                 if (first && exc.cnt == 0) p.carry_head[c] = total;  // column began in an earlier chunk
                 else p.out[p.nzcol_id[ord - 1]] = total;
@@ -417,7 +456,7 @@ __global__ void __launch_bounds__(T_THREADS) col_pass_kernel(const ColPassParams
                 ++ord;
                 s = 0.0;
             }
-            s += prod[pad16(tid * T_ITEMS) + i];
+            s += pr[i];
         }
     }
     if (tid == T_THREADS - 1) {
@@ -427,17 +466,24 @@ __global__ void __launch_bounds__(T_THREADS) col_pass_kernel(const ColPassParams
     }
 }
 
-int launch_col_pass(cudaStream_t s, int value_bytes, bool square, const ColPassParams &p)
+template <typename VT, bool SQUARE>
+static int launch_col_items(cudaStream_t s, int items, const ColPassParams &p)
 {
-    if (p.n_chunks <= 0) return 0;
-    if (value_bytes == 4) {
-        if (square) col_pass_kernel<float, true><<<p.n_chunks, T_THREADS, 0, s>>>(p);
-        else col_pass_kernel<float, false><<<p.n_chunks, T_THREADS, 0, s>>>(p);
-    } else {
-        if (square) col_pass_kernel<double, true><<<p.n_chunks, T_THREADS, 0, s>>>(p);
-        else col_pass_kernel<double, false><<<p.n_chunks, T_THREADS, 0, s>>>(p);
+    switch (items) {
+    case 8: col_pass_kernel<VT, SQUARE, 8><<<p.n_chunks, T_THREADS, 0, s>>>(p); break;
+    case 16: col_pass_kernel<VT, SQUARE, 16><<<p.n_chunks, T_THREADS, 0, s>>>(p); break;
+    default: return -1;
     }
     return cudaGetLastError() == cudaSuccess ? 1 : -1;
+}
+
+int launch_col_pass(cudaStream_t s, int value_bytes, bool square, int chunk_entries, const ColPassParams &p)
+{
+    if (p.n_chunks <= 0) return 0;
+    const int items = chunk_entries / T_THREADS;
+    if (value_bytes == 4)
+        return square ? launch_col_items<float, true>(s, items, p) : launch_col_items<float, false>(s, items, p);
+    return square ? launch_col_items<double, true>(s, items, p) : launch_col_items<double, false>(s, items, p);
 }
 
 // ------------------------------------------------------------------------------------------

@@ -1,6 +1,7 @@
 // pack.cu -- one-off packing of LabeledPoint rows (lib/data/LabeledPoint.scala:32-36) into the
-// device-resident layout the evaluation kernels read: the CSR arrays as given, plus a CSC copy
-// ordered by (column, row) with chunk metadata for col_pass_kernel.
+// device-resident layout the evaluation kernels read: CSR with columns renumbered by descending
+// frequency, plus a CSC copy ordered by (internal column, row) with chunk metadata for
+// col_pass_kernel.
 //
 // This runs once per data set (and never per evaluation); it uses CUB's device radix sort and
 // scan for the transposition.  The reference has no counterpart -- it re-reads JVM objects every
@@ -52,42 +53,39 @@ __global__ void permute_kernel(int64_t nnz, const uint32_t *__restrict__ perm, c
     }
 }
 
-// col_ptr[j] = first position in the sorted column keys with key >= j   (j in [0, d])
-__global__ void col_ptr_kernel(int32_t d, int64_t nnz, const int32_t *__restrict__ sorted_col, uint32_t *__restrict__ col_ptr)
+__global__ void count_cols_kernel(int64_t nnz, const int32_t *__restrict__ col, uint32_t *__restrict__ counts)
 {
-    for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j <= d; j += (int64_t)gridDim.x * blockDim.x) {
-        int64_t lo = 0, hi = nnz;
-        while (lo < hi) {
-            const int64_t mid = (lo + hi) >> 1;
-            if (sorted_col[mid] < (int32_t)j) lo = mid + 1;
-            else hi = mid;
-        }
-        col_ptr[j] = (uint32_t)lo;
+    for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < nnz; k += (int64_t)gridDim.x * blockDim.x)
+        atomicAdd(counts + col[k], 1u);  // integer counts: order-independent, so packing stays deterministic
+}
+
+// rank[orig] = internal id; counts how many columns are non-empty
+__global__ void invert_perm_kernel(int32_t d, const int32_t *__restrict__ orig_of, const uint32_t *__restrict__ sorted_counts,
+                                   int32_t *__restrict__ rank, unsigned long long *__restrict__ nonempty)
+{
+    int mine = 0;
+    for (int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; c < d; c += (int64_t)gridDim.x * blockDim.x) {
+        rank[orig_of[c]] = (int32_t)c;
+        if (sorted_counts[c] > 0) ++mine;
     }
+    if (mine) atomicAdd(nonempty, (unsigned long long)mine);
 }
 
-__global__ void nonempty_flag_kernel(int32_t d, const uint32_t *__restrict__ col_ptr, int32_t *__restrict__ flag)
+__global__ void remap_cols_kernel(int64_t nnz, int32_t *__restrict__ col, const int32_t *__restrict__ rank)
 {
-    for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < d; j += (int64_t)gridDim.x * blockDim.x)
-        flag[j] = col_ptr[j + 1] > col_ptr[j] ? 1 : 0;
+    for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < nnz; k += (int64_t)gridDim.x * blockDim.x)
+        col[k] = rank[col[k]];
 }
 
-__global__ void compact_cols_kernel(int32_t d, const uint32_t *__restrict__ col_ptr, const int32_t *__restrict__ flag,
-                                    const int32_t *__restrict__ pos, int64_t nnz, int64_t m,
-                                    uint32_t *__restrict__ nzcol_ptr, int32_t *__restrict__ nzcol_id)
+__global__ void mark_starts_kernel(int64_t m, const uint32_t *__restrict__ col_ptr, int32_t *__restrict__ csc_row)
 {
-    for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < d; j += (int64_t)gridDim.x * blockDim.x) {
-        if (flag[j]) {
-            nzcol_ptr[pos[j]] = col_ptr[j];
-            nzcol_id[pos[j]] = (int32_t)j;
-        }
-    }
-    if (blockIdx.x == 0 && threadIdx.x == 0) nzcol_ptr[m] = (uint32_t)nnz;
+    for (int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; c < m; c += (int64_t)gridDim.x * blockDim.x)
+        csc_row[col_ptr[c]] |= (int32_t)0x80000000;
 }
 
-// chunk_col_lo[c] = number of non-empty columns that start before entry c*TCHUNK;
-// head_nonempty[c] = 1 when entry c*TCHUNK is not itself a column start
-__global__ void chunk_meta_kernel(int n_chunks, int64_t m, const uint32_t *__restrict__ nzcol_ptr,
+// chunk_col_lo[c] = number of non-empty columns that start before entry c*chunk_entries;
+// head_nonempty[c] = 1 when entry c*chunk_entries is not itself a column start
+__global__ void chunk_meta_kernel(int n_chunks, int chunk_entries, int64_t m, const uint32_t *__restrict__ nzcol_ptr,
                                   int32_t *__restrict__ chunk_col_lo, int32_t *__restrict__ head_nonempty)
 {
     for (int c = blockIdx.x * blockDim.x + threadIdx.x; c <= n_chunks; c += gridDim.x * blockDim.x) {
@@ -95,7 +93,7 @@ __global__ void chunk_meta_kernel(int n_chunks, int64_t m, const uint32_t *__res
             chunk_col_lo[c] = (int32_t)m;
             continue;
         }
-        const uint32_t base = (uint32_t)((int64_t)c * TCHUNK);
+        const uint32_t base = (uint32_t)((int64_t)c * chunk_entries);
         int64_t lo = 0, hi = m;
         while (lo < hi) {
             const int64_t mid = (lo + hi) >> 1;
@@ -212,72 +210,102 @@ int check_columns(cudaStream_t s, const int32_t *col, int64_t nnz, int32_t d, in
     return PML_OK;
 }
 
+// Packing proper.  Columns are renumbered by descending entry count ("internal ids": the m
+// non-empty columns are exactly ids [0, m), hottest first; ties keep the original order), the CSR
+// column array is rewritten in place to internal ids, and the CSC copy is built in internal-id
+// order with the first entry of every column marked in bit 31 of its row index.
 int build_transpose(cudaStream_t s, int64_t n, int32_t d, int64_t nnz, const uint32_t *row_ptr,
-                    const int32_t *col, const void *val, int value_bytes, Packed *out)
+                    int32_t *col, const void *val, int value_bytes, int chunk_entries, Packed *out)
 {
-    out->n_chunks = (int)((nnz + TCHUNK - 1) / TCHUNK);
+    out->chunk_entries = chunk_entries;
+    out->n_chunks = (int)((nnz + chunk_entries - 1) / chunk_entries);
     const int n_chunks = out->n_chunks;
     out->bytes = 0;
+    const size_t dd = (size_t)d + 1;
 
-    PML_CUDA(cudaMalloc(&out->csc_row, sizeof(int32_t) * (size_t)(nnz + 4)));
-    PML_CUDA(cudaMalloc(&out->csc_val, (size_t)value_bytes * (size_t)(nnz + 4)));
+    PML_CUDA(cudaMalloc(&out->csc_row, sizeof(int32_t) * (size_t)(nnz + 16)));
+    PML_CUDA(cudaMalloc(&out->csc_val, (size_t)value_bytes * (size_t)(nnz + 16)));
     PML_CUDA(cudaMalloc(&out->chunk_col_lo, sizeof(int32_t) * (size_t)(n_chunks + 1)));
-    out->bytes += (int64_t)(sizeof(int32_t) + value_bytes) * (nnz + 4) + (int64_t)sizeof(int32_t) * (n_chunks + 1);
+    PML_CUDA(cudaMalloc(&out->rank, sizeof(int32_t) * dd));
+    PML_CUDA(cudaMalloc(&out->nzcol_id, sizeof(int32_t) * dd));
+    PML_CUDA(cudaMalloc(&out->nzcol_ptr, sizeof(uint32_t) * (dd + 1)));
+    out->bytes += (int64_t)(sizeof(int32_t) + value_bytes) * (nnz + 16) + (int64_t)sizeof(int32_t) * (n_chunks + 1) +
+                  (int64_t)dd * 12 + 4;
 
-    DevBuf entry_row, perm_in, perm_out, keys_out, col_ptr, flag, pos, head, tmp;
-    PML_CUDA(entry_row.alloc(sizeof(int32_t) * (size_t)nnz));
-    PML_CUDA(perm_in.alloc(sizeof(uint32_t) * (size_t)nnz));
-    PML_CUDA(perm_out.alloc(sizeof(uint32_t) * (size_t)nnz));
-    PML_CUDA(keys_out.alloc(sizeof(int32_t) * (size_t)nnz));
-    PML_CUDA(col_ptr.alloc(sizeof(uint32_t) * (size_t)(d + 1)));
-    PML_CUDA(flag.alloc(sizeof(int32_t) * (size_t)(d + 1)));
-    PML_CUDA(pos.alloc(sizeof(int32_t) * (size_t)(d + 1)));
+    DevBuf counts, counts_sorted, ids, entry_row, perm_in, perm_out, keys_out, head, tmp, m_dev;
+    PML_CUDA(counts.alloc(sizeof(uint32_t) * dd));
+    PML_CUDA(counts_sorted.alloc(sizeof(uint32_t) * dd));
+    PML_CUDA(ids.alloc(sizeof(int32_t) * dd));
+    PML_CUDA(m_dev.alloc(sizeof(unsigned long long)));
     PML_CUDA(head.alloc(sizeof(int32_t) * (size_t)(n_chunks + 1)));
 
+    // 1. entries per column, columns ordered by descending count (stable)
+    PML_CUDA(cudaMemsetAsync(counts.p, 0, sizeof(uint32_t) * dd, s));
+    PML_CUDA(cudaMemsetAsync(m_dev.p, 0, sizeof(unsigned long long), s));
+    if (nnz > 0) count_cols_kernel<<<grid_for(nnz), 256, 0, s>>>(nnz, col, counts.as<uint32_t>());
+    iota_kernel<<<grid_for(d), 256, 0, s>>>(d, ids.as<uint32_t>());
+    PML_CUDA(cudaGetLastError());
+    if (d > 0) {
+        size_t tb = 0;
+        PML_CUDA(cub::DeviceRadixSort::SortPairsDescending(nullptr, tb, counts.as<uint32_t>(), counts_sorted.as<uint32_t>(),
+                                                           ids.as<int32_t>(), out->nzcol_id, d, 0, 32, s));
+        DevBuf t1;
+        PML_CUDA(t1.alloc(tb));
+        PML_CUDA(cub::DeviceRadixSort::SortPairsDescending(t1.p, tb, counts.as<uint32_t>(), counts_sorted.as<uint32_t>(),
+                                                           ids.as<int32_t>(), out->nzcol_id, d, 0, 32, s));
+        invert_perm_kernel<<<grid_for(d), 256, 0, s>>>(d, out->nzcol_id, counts_sorted.as<uint32_t>(), out->rank,
+                                                      m_dev.as<unsigned long long>());
+        PML_CUDA(cudaGetLastError());
+        // 2. column starts over internal ids = exclusive scan of the sorted counts (entry d = nnz)
+        PML_CUDA(cudaMemsetAsync(counts_sorted.as<uint32_t>() + d, 0, sizeof(uint32_t), s));
+        size_t tb2 = 0;
+        PML_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tb2, counts_sorted.as<uint32_t>(), out->nzcol_ptr, d + 1, s));
+        DevBuf t2;
+        PML_CUDA(t2.alloc(tb2));
+        PML_CUDA(cub::DeviceScan::ExclusiveSum(t2.p, tb2, counts_sorted.as<uint32_t>(), out->nzcol_ptr, d + 1, s));
+    } else {
+        PML_CUDA(cudaMemsetAsync(out->nzcol_ptr, 0, sizeof(uint32_t), s));
+    }
+    unsigned long long m64 = 0;
+    PML_CUDA(cudaMemcpyAsync(&m64, m_dev.p, sizeof(m64), cudaMemcpyDeviceToHost, s));
+    PML_CUDA(cudaStreamSynchronize(s));
+    out->m = (int64_t)m64;
+    const int64_t m = out->m;
+
     if (nnz > 0) {
+        PML_CUDA(entry_row.alloc(sizeof(int32_t) * (size_t)nnz));
+        PML_CUDA(perm_in.alloc(sizeof(uint32_t) * (size_t)nnz));
+        PML_CUDA(perm_out.alloc(sizeof(uint32_t) * (size_t)nnz));
+        PML_CUDA(keys_out.alloc(sizeof(int32_t) * (size_t)nnz));
+        // 3. CSR columns -> internal ids, in place
+        remap_cols_kernel<<<grid_for(nnz), 256, 0, s>>>(nnz, col, out->rank);
         expand_rows_kernel<<<grid_for(n * 32), 256, 0, s>>>(n, row_ptr, entry_row.as<int32_t>());
         iota_kernel<<<grid_for(nnz), 256, 0, s>>>(nnz, perm_in.as<uint32_t>());
         PML_CUDA(cudaGetLastError());
         int end_bit = 1;
-        while (end_bit < 31 && (1LL << end_bit) < (int64_t)d) ++end_bit;
+        while (end_bit < 31 && (1LL << end_bit) < m) ++end_bit;
         size_t tmp_bytes = 0;
-        // stable LSD radix sort by column keeps rows ascending inside each column
-        PML_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, col, keys_out.as<int32_t>(), perm_in.as<uint32_t>(),
-                                                 perm_out.as<uint32_t>(), nnz, 0, end_bit, s));
+        // 4. stable LSD radix sort by internal column keeps rows ascending inside each column
+        PML_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, (const int32_t *)col, keys_out.as<int32_t>(),
+                                                 perm_in.as<uint32_t>(), perm_out.as<uint32_t>(), nnz, 0, end_bit, s));
         PML_CUDA(tmp.alloc(tmp_bytes));
-        PML_CUDA(cub::DeviceRadixSort::SortPairs(tmp.p, tmp_bytes, col, keys_out.as<int32_t>(), perm_in.as<uint32_t>(),
-                                                 perm_out.as<uint32_t>(), nnz, 0, end_bit, s));
+        PML_CUDA(cub::DeviceRadixSort::SortPairs(tmp.p, tmp_bytes, (const int32_t *)col, keys_out.as<int32_t>(),
+                                                 perm_in.as<uint32_t>(), perm_out.as<uint32_t>(), nnz, 0, end_bit, s));
         if (value_bytes == 4)
             permute_kernel<float><<<grid_for(nnz), 256, 0, s>>>(nnz, perm_out.as<uint32_t>(), entry_row.as<int32_t>(),
                                                                (const float *)val, out->csc_row, (float *)out->csc_val);
         else
             permute_kernel<double><<<grid_for(nnz), 256, 0, s>>>(nnz, perm_out.as<uint32_t>(), entry_row.as<int32_t>(),
                                                                 (const double *)val, out->csc_row, (double *)out->csc_val);
+        // 5. mark the first entry of every column in bit 31 of its row index
+        mark_starts_kernel<<<grid_for(m), 256, 0, s>>>(m, out->nzcol_ptr, out->csc_row);
         PML_CUDA(cudaGetLastError());
     }
-    col_ptr_kernel<<<grid_for((int64_t)d + 1), 256, 0, s>>>(d, nnz, keys_out.as<int32_t>(), col_ptr.as<uint32_t>());
-    nonempty_flag_kernel<<<grid_for(d), 256, 0, s>>>(d, col_ptr.as<uint32_t>(), flag.as<int32_t>());
-    PML_CUDA(cudaGetLastError());
-    {
-        DevBuf tmp2;
-        size_t tmp_bytes = 0;
-        PML_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, flag.as<int32_t>(), pos.as<int32_t>(), d + 1, s));
-        PML_CUDA(tmp2.alloc(tmp_bytes));
-        PML_CUDA(cudaMemsetAsync(flag.as<int32_t>() + d, 0, sizeof(int32_t), s));
-        PML_CUDA(cub::DeviceScan::ExclusiveSum(tmp2.p, tmp_bytes, flag.as<int32_t>(), pos.as<int32_t>(), d + 1, s));
-        int32_t m32 = 0;
-        PML_CUDA(cudaMemcpyAsync(&m32, pos.as<int32_t>() + d, sizeof(int32_t), cudaMemcpyDeviceToHost, s));
-        PML_CUDA(cudaStreamSynchronize(s));
-        out->m = m32;
-    }
-    const int64_t m = out->m;
-    PML_CUDA(cudaMalloc(&out->nzcol_ptr, sizeof(uint32_t) * (size_t)(m + 1)));
-    PML_CUDA(cudaMalloc(&out->nzcol_id, sizeof(int32_t) * (size_t)(m + 1)));
-    out->bytes += (int64_t)(sizeof(uint32_t) + sizeof(int32_t)) * (m + 1);
-    compact_cols_kernel<<<grid_for(d), 256, 0, s>>>(d, col_ptr.as<uint32_t>(), flag.as<int32_t>(), pos.as<int32_t>(), nnz, m,
-                                                   out->nzcol_ptr, out->nzcol_id);
-    chunk_meta_kernel<<<grid_for((int64_t)n_chunks + 1), 256, 0, s>>>(n_chunks, m, out->nzcol_ptr, out->chunk_col_lo,
-                                                                     head.as<int32_t>());
+    // tail padding is read by the vector loads of the last (partial) chunk's neighbours: keep it benign
+    PML_CUDA(cudaMemsetAsync(out->csc_row + nnz, 0, sizeof(int32_t) * 16, s));
+    PML_CUDA(cudaMemsetAsync((char *)out->csc_val + (size_t)nnz * value_bytes, 0, (size_t)value_bytes * 16, s));
+    chunk_meta_kernel<<<grid_for((int64_t)n_chunks + 1), 256, 0, s>>>(n_chunks, chunk_entries, m, out->nzcol_ptr,
+                                                                     out->chunk_col_lo, head.as<int32_t>());
     PML_CUDA(cudaGetLastError());
 
     // fix-up list: runs of consecutive chunks whose heads continue one column (host-side, tiny)
@@ -287,7 +315,7 @@ int build_transpose(cudaStream_t s, int64_t n, int32_t d, int64_t nnz, const uin
     if (n_chunks > 0)
         PML_CUDA(cudaMemcpyAsync(h_head.data(), head.p, sizeof(int32_t) * (size_t)n_chunks, cudaMemcpyDeviceToHost, s));
     PML_CUDA(cudaStreamSynchronize(s));
-    std::vector<int32_t> fix_ord;  // column ordinal per fix entry
+    std::vector<int32_t> fix_ord;  // internal column id per fix entry
     std::vector<FixEntry> fix;
     for (int c = 1; c < n_chunks; ++c) {
         if (!h_head[c]) continue;
@@ -296,7 +324,7 @@ int build_transpose(cudaStream_t s, int64_t n, int32_t d, int64_t nnz, const uin
             fix.back().chunk_end = c + 1;
         } else {
             FixEntry e;
-            e.col = ord;  // replaced by the column id below
+            e.col = ord;  // replaced by the original column id below
             e.chunk_begin = c;
             e.chunk_end = c + 1;
             fix.push_back(e);
