@@ -58,7 +58,7 @@ typedef struct pml_dataset_info {
     int64_t nnz;           /* stored entries */
     int32_t d;             /* feature dimension (incl. intercept column if any) */
     int32_t value_bytes;   /* 4 or 8: what PML_STORE_* resolved to */
-    int32_t margin_variant; /* lanes per row of the CSR margin kernel; 0 = segment-per-warp */
+    int32_t margin_variant; /* CSR margin kernel: lanes per row; 0 = segment-per-warp; 1 = segment-per-CTA */
     int32_t n_chunks;      /* CSC chunks of the transpose kernel */
     int64_t nonempty_cols; /* columns with at least one entry */
     int64_t device_bytes;  /* HBM held by this data set */
@@ -169,16 +169,18 @@ int pml_ctx_launch_count(pml_ctx *ctx, int64_t *out);
  * bracketed by CUDA events on the context's stream; pml_ctx_read_profile synchronises, sums the
  * elapsed milliseconds and launch counts per class since the last read, and clears them. */
 #define PML_K_PREPARE 0  /* prepare_vectors_kernel */
-#define PML_K_ROW 1      /* row_pass_kernel (CSR) */
-#define PML_K_COL 2      /* col_pass_kernel (CSC) */
+#define PML_K_ROW 1      /* CSR product: row_pass_kernel, or seg_spmv_kernel for variant 1 */
+#define PML_K_COL 2      /* CSC product: seg_spmv_kernel */
 #define PML_K_FIXUP 3    /* fixup_kernel */
 #define PML_K_FINALIZE 4 /* finalize_kernel */
+#define PML_K_EPILOGUE 5 /* row_epilogue_kernel (row-pass variant 1 only) */
 #define PML_K_COUNT 8
 int pml_ctx_set_profiling(pml_ctx *ctx, int on);
 int pml_ctx_read_profile(pml_ctx *ctx, double *out_ms /* [PML_K_COUNT] */,
                          int64_t *out_launches /* [PML_K_COUNT] */);
-/* force a CSR margin-kernel variant: lanes per row in {2,4,8,16,32}, 0 = segment-per-warp,
- * -1 = back to the nnz/row heuristic.  For benchmarking and tests. */
+/* force a CSR margin-kernel variant: lanes per row in {2,4,8,16,32} (32 = warp-per-row),
+ * 0 = segment-per-warp, 1 = segment-per-CTA (entry-chunked, load-balanced), -1 = back to the
+ * default choice.  For benchmarking and tests. */
 int pml_dataset_set_margin_variant(pml_dataset *ds, int lanes_per_row);
 
 /* ---- evaluation without any allocation ------------------------------------------------------ */

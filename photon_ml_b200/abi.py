@@ -158,7 +158,7 @@ class Context:
         check(load().pml_ctx_launch_count(self._h, ctypes.byref(v)))
         return v.value
 
-    KERNEL_KINDS = ["prepare_vectors", "row_pass", "col_pass", "fixup", "finalize"]
+    KERNEL_KINDS = ["prepare_vectors", "row_pass", "col_pass", "fixup", "finalize", "row_epilogue"]
 
     def set_profiling(self, on):
         check(load().pml_ctx_set_profiling(self._h, 1 if on else 0))

@@ -63,6 +63,7 @@ int upload_optional(cudaStream_t s, double **slot, const double *src, int64_t n,
 int pick_variant(int64_t n, int64_t nnz)
 {
     const double mean = n > 0 ? (double)nnz / (double)n : 0.0;
+    if (std::getenv("PML_ROW_VARIANT_HEURISTIC") == nullptr) return 1;  // segment-per-CTA (entry-chunked)
     if (mean <= 24.0) return 0;  // segment-per-warp
     if (mean <= 48.0) return 4;
     if (mean <= 96.0) return 8;
@@ -112,20 +113,89 @@ int run_col_and_fixup(pml_dataset *ds, bool square, double *out, bool with_scala
 {
     pml_ctx *ctx = ds->ctx;
     cudaStream_t s = ctx->stream;
-    ColPassParams cp;
+    SegParams cp;
+    std::memset(&cp, 0, sizeof(cp));
     cp.nnz = ds->nnz;
-    cp.row = ds->t.csc_row;
+    cp.idx = ds->t.csc_row;
     cp.val = ds->t.csc_val;
-    cp.nzcol_id = ds->t.nzcol_id;
-    cp.chunk_col_lo = ds->t.chunk_col_lo;
-    cp.r = ds->r;
+    cp.run_id = ds->t.nzcol_id;
+    cp.chunk_lo = ds->t.chunk_col_lo;
+    cp.table = ds->r;
     cp.out = out;
-    cp.carry_head = ds->carry_head;
+    cp.carry = ds->carry_head;
     cp.n_chunks = ds->t.n_chunks;
-    PML_TRY(run(ctx, PML_K_COL, [&] { return launch_col_pass(s, ds->value_bytes, square, ds->t.chunk_entries, cp); }));
-    PML_TRY(run(ctx, PML_K_FIXUP, [&] { return launch_fixup(s, ds->t.fix, ds->t.n_fix, ds->carry_head, out, ds->d,
-                                    with_scalars ? ds->partials : nullptr, ds->row_grid, write_value, true); }));
+    // r is gathered ~nnz/n times per element while the CSC stream is read once: ask L2 to keep r
+    const bool pin = ctx->l2_persist_bytes > 0 && ds->n > 0;
+    if (pin) {
+        cudaStreamAttrValue attr;
+        std::memset(&attr, 0, sizeof(attr));
+        size_t bytes = sizeof(double) * (size_t)ds->n;
+        if (bytes > (size_t)ctx->l2_window_max) bytes = (size_t)ctx->l2_window_max;
+        attr.accessPolicyWindow.base_ptr = ds->r;
+        attr.accessPolicyWindow.num_bytes = bytes;
+        const double ratio = (double)ctx->l2_persist_bytes / (double)bytes;
+        attr.accessPolicyWindow.hitRatio = ratio < 1.0 ? (float)ratio : 1.0f;
+        attr.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+        attr.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+        PML_CUDA(cudaStreamSetAttribute(s, cudaStreamAttributeAccessPolicyWindow, &attr));
+    }
+    PML_TRY(run(ctx, PML_K_COL, [&] {
+        return launch_seg_spmv(s, ctx->sm_count, ds->value_bytes, false, square, ds->t.chunk_entries, cp, 0);
+    }));
+    if (pin) {
+        cudaStreamAttrValue attr;
+        std::memset(&attr, 0, sizeof(attr));
+        attr.accessPolicyWindow.num_bytes = 0;
+        PML_CUDA(cudaStreamSetAttribute(s, cudaStreamAttributeAccessPolicyWindow, &attr));
+    }
+    PML_TRY(run(ctx, PML_K_FIXUP, [&] {
+        return launch_fixup(s, ds->t.fix, ds->t.n_fix, ds->carry_head, out, nullptr, nullptr, ds->d,
+                            with_scalars ? ds->partials : nullptr, ds->row_grid, write_value, true);
+    }));
     return PML_OK;
+}
+
+// The per-row half of an evaluation: either one of the warp-oriented row_pass_kernel variants, or
+// (variant 1) the entry-chunked seg_spmv_kernel followed by its fix-up and the row epilogue.
+int run_rows(pml_dataset *ds, RowPassParams &rp, bool two)
+{
+    pml_ctx *ctx = ds->ctx;
+    cudaStream_t s = ctx->stream;
+    if (ds->lanes_per_row != 1) {
+        return run(ctx, PML_K_ROW, [&] {
+            return launch_row_pass(s, ctx->sm_count, ds->value_bytes, ds->lanes_per_row, two, rp, ds->t.m, ds->row_threads,
+                                   ds->row_hot_cap, &ds->row_grid);
+        });
+    }
+    if (two && ds->zb == nullptr) {
+        PML_TRY(dev_alloc(&ds->zb, (size_t)ds->n, &ds->bytes));
+        PML_TRY(dev_alloc(&ds->carry_row2, (size_t)ds->rs.n_chunks + 1, &ds->bytes));
+    }
+    if (ds->rs.n_runs < ds->n) {  // empty rows have no run: their dot product is 0
+        PML_CUDA(cudaMemsetAsync(ds->za, 0, sizeof(double) * (size_t)ds->n, s));
+        if (two) PML_CUDA(cudaMemsetAsync(ds->zb, 0, sizeof(double) * (size_t)ds->n, s));
+    }
+    SegParams sp;
+    std::memset(&sp, 0, sizeof(sp));
+    sp.nnz = ds->nnz;
+    sp.idx = ds->col;
+    sp.val = ds->val;
+    sp.run_id = ds->rs.nzrow_id;
+    sp.chunk_lo = ds->rs.chunk_lo;
+    sp.table = rp.vec;
+    sp.out = ds->za;
+    sp.out2 = two ? ds->zb : nullptr;
+    sp.carry = ds->carry_row;
+    sp.carry2 = two ? ds->carry_row2 : nullptr;
+    sp.n_chunks = ds->rs.n_chunks;
+    PML_TRY(run(ctx, PML_K_ROW, [&] {
+        return launch_seg_spmv(s, ctx->sm_count, ds->value_bytes, two, false, ds->t.chunk_entries, sp, ds->t.m);
+    }));
+    PML_TRY(run(ctx, PML_K_FIXUP, [&] {
+        return launch_fixup(s, ds->rs.fix, ds->rs.n_fix, ds->carry_row, ds->za, two ? ds->carry_row2 : nullptr,
+                            two ? ds->zb : nullptr, 0, nullptr, 0, false, false);
+    }));
+    return run(ctx, PML_K_EPILOGUE, [&] { return launch_row_epilogue(s, ctx->sm_count, rp, ds->za, ds->zb, &ds->row_grid); });
 }
 
 int vg_raw(pml_dataset *ds, int loss, const double *coef_dev, double *out_raw_dev)
@@ -161,7 +231,7 @@ int vg_raw(pml_dataset *ds, int loss, const double *coef_dev, double *out_raw_de
     rp.partials = ds->partials;
     rp.mode = MODE_VG;
     rp.loss = loss;
-    PML_TRY(run(ctx, PML_K_ROW, [&] { return launch_row_pass(s, ctx->sm_count, ds->value_bytes, ds->lanes_per_row, false, rp, ds->t.m, &ds->row_grid); }));
+    PML_TRY(run_rows(ds, rp, false));
     return run_col_and_fixup(ds, false, out_raw_dev, true, true);
 }
 
@@ -200,7 +270,7 @@ int hv_raw(pml_dataset *ds, int loss, const double *coef_dev, uint64_t tag, cons
         }
         rp.dcache = tag != 0 ? ds->dcache : nullptr;
         rp.mode = MODE_HV_COLD;
-        PML_TRY(run(ctx, PML_K_ROW, [&] { return launch_row_pass(s, ctx->sm_count, ds->value_bytes, ds->lanes_per_row, true, rp, ds->t.m, &ds->row_grid); }));
+        PML_TRY(run_rows(ds, rp, true));
         ds->cache_valid = tag != 0;
         ds->cached_tag = tag;
         ds->cached_loss = loss;
@@ -216,7 +286,7 @@ int hv_raw(pml_dataset *ds, int loss, const double *coef_dev, uint64_t tag, cons
         }
         rp.dcache = ds->dcache;
         rp.mode = MODE_HV_CACHED;
-        PML_TRY(run(ctx, PML_K_ROW, [&] { return launch_row_pass(s, ctx->sm_count, ds->value_bytes, ds->lanes_per_row, false, rp, ds->t.m, &ds->row_grid); }));
+        PML_TRY(run_rows(ds, rp, false));
     }
     PML_CUDA(cudaMemsetAsync(out_raw_dev, 0, sizeof(double) * (size_t)(ds->d + 2), s));
     return run_col_and_fixup(ds, false, out_raw_dev, true, false);
@@ -256,7 +326,7 @@ int diag_dev(pml_dataset *ds, int loss, const double *coef_dev, double *out_dev 
     rp.vec = ds->vec;
     rp.mode = MODE_DIAG;
     rp.loss = loss;
-    PML_TRY(run(ctx, PML_K_ROW, [&] { return launch_row_pass(s, ctx->sm_count, ds->value_bytes, ds->lanes_per_row, false, rp, ds->t.m, &ds->row_grid); }));
+    PML_TRY(run_rows(ds, rp, false));
     PML_CUDA(cudaMemsetAsync(out_dev, 0, sizeof(double) * (size_t)(ds->d + 2), s));
     return run_col_and_fixup(ds, true, out_dev, false, false);
 }
@@ -298,6 +368,13 @@ int pml_ctx_create(int device, pml_ctx **out)
         return fail(PML_ECUDA, "this library is built for sm_100a (B200) only");
     }
     PML_CUDA(cudaStreamCreate(&ctx->stream));
+    if (std::getenv("PML_L2_PERSIST") != nullptr && prop.persistingL2CacheMaxSize > 0) {
+        // opt-in: reserve the persisting share of L2 for the per-row multiplier r (see run_col_and_fixup)
+        if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, (size_t)prop.persistingL2CacheMaxSize) == cudaSuccess) {
+            ctx->l2_persist_bytes = prop.persistingL2CacheMaxSize;
+            ctx->l2_window_max = prop.accessPolicyMaxWindowSize;
+        }
+    }
     PML_CUDA(cudaMallocHost(&ctx->h_scalar, 64));
     *out = ctx;
     return PML_OK;
@@ -384,7 +461,8 @@ int pml_dataset_destroy(pml_dataset *ds)
         cudaStreamSynchronize(ds->ctx->stream);
     }
     void *ptrs[] = { ds->row_ptr, ds->col, ds->val, ds->label, ds->offset, ds->weight, ds->t.csc_row, ds->t.csc_val,
-                     ds->t.nzcol_ptr, ds->t.nzcol_id, ds->t.rank, ds->t.chunk_col_lo, ds->t.fix, ds->factors, ds->shifts, ds->r,
+                     ds->t.nzcol_ptr, ds->t.nzcol_id, ds->t.rank, ds->t.chunk_col_lo, ds->t.fix, ds->rs.nzrow_id, ds->rs.chunk_lo,
+                     ds->rs.fix, ds->za, ds->zb, ds->carry_row, ds->carry_row2, ds->factors, ds->shifts, ds->r,
                      ds->dcache, ds->partials, ds->carry_head, ds->raw, ds->vec, ds->shift_partials, ds->io_a, ds->io_b,
                      ds->io_n };
     for (void *p : ptrs)
@@ -476,13 +554,14 @@ int pml_dataset_create_csr_dev(pml_ctx *ctx, int64_t n, int32_t d, const int64_t
     PML_TRY(upload_optional(s, &ds->offset, offsets_dev, n, true, &ds->bytes));
     PML_TRY(upload_optional(s, &ds->weight, weights_dev, n, true, &ds->bytes));
 
-    int chunk_entries = TCHUNK;
-    if (const char *e = std::getenv("PML_COL_ITEMS")) {  // tuning knob: entries per thread of the column pass
-        const int items = std::atoi(e);
-        if (items == 8 || items == 16) chunk_entries = items * T_THREADS;
-    }
+    const int chunk_entries = TCHUNK;
     PML_TRY(build_transpose(s, n, d, nnz, ds->row_ptr, ds->col, ds->val, dst_bytes, chunk_entries, &ds->t));
     ds->bytes += ds->t.bytes;
+    // after the transpose: from here on the CSR column array carries the row-start flags in bit 31
+    PML_TRY(build_row_side(s, n, nnz, ds->row_ptr, ds->col, chunk_entries, &ds->rs));
+    ds->bytes += ds->rs.bytes;
+    PML_TRY(dev_alloc(&ds->za, (size_t)n, &ds->bytes));
+    PML_TRY(dev_alloc(&ds->carry_row, (size_t)ds->rs.n_chunks + 1, &ds->bytes));
 
     PML_TRY(dev_alloc(&ds->r, (size_t)n, &ds->bytes));
     PML_TRY(dev_alloc(&ds->partials, 2 * (size_t)MAX_PARTIALS, &ds->bytes));
@@ -493,6 +572,8 @@ int pml_dataset_create_csr_dev(pml_ctx *ctx, int64_t n, int32_t d, const int64_t
     PML_TRY(dev_alloc(&ds->io_a, (size_t)d + 2, &ds->bytes));
     PML_TRY(dev_alloc(&ds->io_b, (size_t)d + 2, &ds->bytes));
     ds->lanes_per_row = pick_variant(n, nnz);
+    if (const char *e = std::getenv("PML_ROW_THREADS")) ds->row_threads = std::atoi(e) >= 1024 ? 1024 : 256;
+    if (const char *e = std::getenv("PML_ROW_HOT")) ds->row_hot_cap = std::atoi(e);
     PML_CUDA(cudaStreamSynchronize(s));
     cleanup.ds = nullptr;
     *out = ds;
@@ -614,11 +695,11 @@ int pml_dataset_set_margin_variant(pml_dataset *ds, int lanes_per_row)
         return PML_OK;
     }
     switch (lanes_per_row) {
-    case 0: case 2: case 4: case 8: case 16: case 32:
+    case 0: case 1: case 2: case 4: case 8: case 16: case 32:
         ds->lanes_per_row = lanes_per_row;
         return PML_OK;
     default:
-        return fail(PML_EINVAL, "lanes_per_row must be one of -1, 0, 2, 4, 8, 16, 32");
+        return fail(PML_EINVAL, "variant must be one of -1, 0, 1, 2, 4, 8, 16, 32");
     }
 }
 
@@ -771,7 +852,7 @@ int pml_scores(pml_dataset *ds, const double *coef, double *out_scores)
     }
     rp.vec = ds->vec;
     rp.mode = MODE_SCORE;
-    PML_TRY(run(ds->ctx, PML_K_ROW, [&] { return launch_row_pass(s, ds->ctx->sm_count, ds->value_bytes, ds->lanes_per_row, false, rp, ds->t.m, &ds->row_grid); }));
+    PML_TRY(run_rows(ds, rp, false));
     if (ds->n > 0) PML_CUDA(cudaMemcpyAsync(out_scores, ds->r, sizeof(double) * (size_t)ds->n, cudaMemcpyDeviceToHost, s));
     PML_CUDA(cudaStreamSynchronize(s));
     return PML_OK;

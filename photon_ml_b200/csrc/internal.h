@@ -30,14 +30,13 @@ int fail(int code, const std::string &msg);
         if (_rc != PML_OK) return _rc; \
     } while (0)
 
-// ---- geometry of the transpose (CSC) kernel: one CTA reduces one chunk of TCHUNK entries ----
-constexpr int T_THREADS = 256;
-constexpr int T_ITEMS = 16;
-constexpr int TCHUNK = T_THREADS * T_ITEMS;  // 4096 entries = 32 KB of stream per chunk (fp32 values)
+// ---- geometry of seg_spmv_kernel: a chunk is TCHUNK consecutive entries of the CSC (or CSR) stream ----
+constexpr int S_THREADS = 512;
+constexpr int S_ITEMS = 8;
+constexpr int TCHUNK = S_THREADS * S_ITEMS;  // 4096 entries = 32 KB of stream per chunk (fp32 values)
+constexpr int S_MAX_DYN_SMEM = 104 * 1024;   // hot table per CTA; two CTAs share an SM
 
 // ---- geometry of the row (CSR) kernel ----
-constexpr int R_THREADS = 1024;    // one persistent CTA per SM: the hot-coefficient table takes most of shared memory
-constexpr int R_WARPS = R_THREADS / 32;
 constexpr int R_STREAM_CAP = 128;  // products staged per warp per piece in the segment-per-warp variant
 constexpr int R_MAX_DYN_SMEM = 220 * 1024;  // dynamic shared memory per row-pass CTA (227 KB minus static + margin)
 constexpr int MAX_PARTIALS = 4096; // upper bound on row-kernel CTAs (block partials of F and P)
@@ -69,16 +68,17 @@ struct RowPassParams {
     int loss;
 };
 
-struct ColPassParams {
+struct SegParams {
     int64_t nnz;
-    const int32_t *row;           // nnz   CSC row indices, bit 31 = first entry of a column
-    const void *val;              // nnz
-    const int32_t *nzcol_id;      // internal column id -> original column id
-    const int32_t *chunk_col_lo;  // n_chunks+1
-    const double *r;              // n
-    double *out;                  // d (+2): zeroed before the launch
-    double *carry_head;           // n_chunks
+    const int32_t *idx;       // nnz: table index (CSC: row, CSR: internal column id); bit 31 = first entry of a run
+    const void *val;          // nnz
+    const int32_t *run_id;    // run ordinal -> output slot (CSC: original column id, CSR: row id); null = identity
+    const int32_t *chunk_lo;  // n_chunks+1: ordinal of the first run starting at or after each chunk
+    const double *table;      // what idx looks up (CSC: r, CSR: effective coefficients or (ec, ev) pairs)
+    double *out, *out2;       // one slot per run (zeroed beforehand where runs can be absent); out2 with TWO
+    double *carry, *carry2;   // n_chunks: sum of the part of a chunk that precedes its first run start
     int n_chunks;
+    int n_hot;                // leading table entries staged in shared memory (set by the launcher)
 };
 
 struct FixEntry {
@@ -92,18 +92,25 @@ int launch_prepare_vectors(cudaStream_t s, int d, const double *coef, const doub
                            const double *shifts, const int32_t *rank, double *out_vec, double *shift_partials,
                            int *n_partials);
 int launch_row_pass(cudaStream_t s, int sm_count, int value_bytes, int lanes_per_row, bool two,
-                    RowPassParams p, int64_t n_nonempty_cols, int *grid_out);
-int row_pass_hot_capacity(int lanes_per_row, bool two);
-int launch_col_pass(cudaStream_t s, int value_bytes, bool square, int chunk_entries, const ColPassParams &p);
-int launch_fixup(cudaStream_t s, const FixEntry *fix, int n_fix, const double *carry_head, double *out, int d,
-                 const double *partials, int n_partials, bool write_value, bool write_prefactor);
+                    RowPassParams p, int64_t n_nonempty_cols, int threads, int hot_cap, int *grid_out);
+int launch_seg_spmv(cudaStream_t s, int sm_count, int value_bytes, bool two, bool square, int chunk_entries,
+                    SegParams p, int64_t table_len);
+int seg_hot_capacity(bool two);
+int launch_row_epilogue(cudaStream_t s, int sm_count, const RowPassParams &p, const double *za, const double *zb,
+                        int *grid_out);
+int launch_fixup(cudaStream_t s, const FixEntry *fix, int n_fix, const double *carry_head, double *out,
+                 const double *carry_head2, double *out2, int d, const double *partials, int n_partials,
+                 bool write_value, bool write_prefactor);
 int launch_finalize(cudaStream_t s, int d, const double *raw, const double *factors, const double *shifts,
                     double *out_value, double *out_vec);
 
 // pack.cu: builds the CSC copy and its chunk metadata on the device
 struct Packed;
+struct RowSide;
 int build_transpose(cudaStream_t s, int64_t n, int32_t d, int64_t nnz, const uint32_t *row_ptr,
                     int32_t *col, const void *val, int value_bytes, int chunk_entries, Packed *out);
+int build_row_side(cudaStream_t s, int64_t n, int64_t nnz, const uint32_t *row_ptr, int32_t *col, int chunk_entries,
+                   RowSide *out);
 int narrow_check(cudaStream_t s, const double *val, int64_t nnz, bool *all_exact);
 int convert_values(cudaStream_t s, const void *src, int src_bytes, void *dst, int dst_bytes, int64_t nnz);
 int check_columns(cudaStream_t s, const int32_t *col, int64_t nnz, int32_t d, int64_t *bad);
@@ -124,6 +131,17 @@ struct Packed {
     int64_t bytes = 0;
 };
 
+// chunk metadata of the CSR stream (the column array itself carries the row-start flags)
+struct RowSide {
+    int32_t *nzrow_id = nullptr;  // non-empty row ordinal -> row id; null when no row is empty
+    int32_t *chunk_lo = nullptr;
+    FixEntry *fix = nullptr;
+    int64_t n_runs = 0;
+    int n_chunks = 0;
+    int n_fix = 0;
+    int64_t bytes = 0;
+};
+
 }  // namespace pml
 
 struct pml_span {
@@ -139,6 +157,8 @@ struct pml_ctx {
     cudaStream_t stream = nullptr;
     std::mutex mu;
     int64_t launches = 0;
+    int64_t l2_persist_bytes = 0;  // > 0: persisting L2 carve-out reserved for r
+    int64_t l2_window_max = 0;
     // pinned staging for scalars
     double *h_scalar = nullptr;
 };
@@ -155,6 +175,9 @@ struct pml_dataset {
     double *label = nullptr, *offset = nullptr, *weight = nullptr;
     // CSC + chunk metadata
     pml::Packed t;
+    pml::RowSide rs;
+    double *za = nullptr, *zb = nullptr;   // n each: sparse dots of row-pass variant 1 (zb lazily, Hessian-vector)
+    double *carry_row = nullptr, *carry_row2 = nullptr;  // rs.n_chunks each
     // normalization
     double *factors = nullptr, *shifts = nullptr;
     int32_t intercept = -1;
@@ -172,6 +195,8 @@ struct pml_dataset {
     int cached_loss = -1;
     bool cache_valid = false;
     int lanes_per_row = 8;  // resolved margin variant
+    int row_threads = 256;  // CTA shape of the warp-oriented row pass (256 or 1024)
+    int row_hot_cap = 0;    // cap on its shared-memory hot table (-1 = as much as fits)
     int row_grid = 1;       // CTAs of the last row-pass launch (= number of (F, P) partials)
     int64_t bytes = 0;
 };

@@ -112,9 +112,10 @@ __device__ __forceinline__ void lookup(const double *__restrict__ hot, int n_hot
     }
 }
 
-template <typename VT, int LPR, bool TWO>
-__global__ void __launch_bounds__(R_THREADS, 1) row_pass_kernel(const RowPassParams p)
+template <typename VT, int LPR, bool TWO, int R_THREADS>
+__global__ void __launch_bounds__(R_THREADS, R_THREADS >= 1024 ? 1 : 1280 / R_THREADS) row_pass_kernel(const RowPassParams p)
 {
+    constexpr int R_WARPS = R_THREADS / 32;
     constexpr int CAPE = TWO ? R_STREAM_CAP / 2 : R_STREAM_CAP;
     extern __shared__ __align__(16) double dyn_smem[];
     __shared__ double red[2 * R_WARPS];
@@ -165,7 +166,7 @@ __global__ void __launch_bounds__(R_THREADS, 1) row_pass_kernel(const RowPassPar
                 const uint32_t pe = (lim - pb > (uint32_t)CAPE) ? pb + CAPE : lim;
 #pragma unroll 4
                 for (uint32_t k = pb + lane; k < pe; k += 32) {
-                    const int32_t c = __ldcs(col + k);
+                    const int32_t c = __ldcs(col + k) & 0x7fffffff;
                     const double x = widen(__ldcs(val + k));
                     double w0, w1;
                     lookup<TWO>(hot, n_hot, vec, c, w0, w1);
@@ -193,8 +194,8 @@ __global__ void __launch_bounds__(R_THREADS, 1) row_pass_kernel(const RowPassPar
                 double a = 0.0, b = 0.0;
                 uint32_t k = start + sl;
                 for (; k + 3 * L < end; k += 4 * L) {
-                    const int32_t c0 = __ldcs(col + k), c1 = __ldcs(col + k + L);
-                    const int32_t c2 = __ldcs(col + k + 2 * L), c3 = __ldcs(col + k + 3 * L);
+                    const int32_t c0 = __ldcs(col + k) & 0x7fffffff, c1 = __ldcs(col + k + L) & 0x7fffffff;
+                    const int32_t c2 = __ldcs(col + k + 2 * L) & 0x7fffffff, c3 = __ldcs(col + k + 3 * L) & 0x7fffffff;
                     const double x0 = widen(__ldcs(val + k)), x1 = widen(__ldcs(val + k + L));
                     const double x2 = widen(__ldcs(val + k + 2 * L)), x3 = widen(__ldcs(val + k + 3 * L));
                     double w00, w01, w10, w11, w20, w21, w30, w31;
@@ -206,7 +207,7 @@ __global__ void __launch_bounds__(R_THREADS, 1) row_pass_kernel(const RowPassPar
                     if (TWO) b += (x0 * w01 + x1 * w11) + (x2 * w21 + x3 * w31);
                 }
                 for (; k < end; k += L) {
-                    const int32_t c = __ldcs(col + k);
+                    const int32_t c = __ldcs(col + k) & 0x7fffffff;
                     const double x = widen(__ldcs(val + k));
                     double w0, w1;
                     lookup<TWO>(hot, n_hot, vec, c, w0, w1);
@@ -278,212 +279,444 @@ __global__ void __launch_bounds__(R_THREADS, 1) row_pass_kernel(const RowPassPar
     }
 }
 
-template <typename VT, int LPR, bool TWO>
+template <typename VT, int LPR, bool TWO, int THREADS>
 static int launch_row_one(cudaStream_t s, int grid, size_t smem, const RowPassParams &p)
 {
     // per device and per instantiation; cheap enough to repeat on every launch
     if (smem > 48 * 1024 &&
-        cudaFuncSetAttribute(row_pass_kernel<VT, LPR, TWO>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        cudaFuncSetAttribute(row_pass_kernel<VT, LPR, TWO, THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              R_MAX_DYN_SMEM) != cudaSuccess)
         return -1;
-    row_pass_kernel<VT, LPR, TWO><<<grid, R_THREADS, smem, s>>>(p);
+    row_pass_kernel<VT, LPR, TWO, THREADS><<<grid, THREADS, smem, s>>>(p);
     return cudaGetLastError() == cudaSuccess ? 1 : -1;
 }
 
-template <typename VT, bool TWO>
+template <typename VT, bool TWO, int THREADS>
 static int launch_row_variant(cudaStream_t s, int grid, int lpr, size_t smem, const RowPassParams &p)
 {
     switch (lpr) {
-    case 0: return launch_row_one<VT, 0, TWO>(s, grid, smem, p);
-    case 2: return launch_row_one<VT, 2, TWO>(s, grid, smem, p);
-    case 4: return launch_row_one<VT, 4, TWO>(s, grid, smem, p);
-    case 8: return launch_row_one<VT, 8, TWO>(s, grid, smem, p);
-    case 16: return launch_row_one<VT, 16, TWO>(s, grid, smem, p);
-    case 32: return launch_row_one<VT, 32, TWO>(s, grid, smem, p);
+    case 0: return launch_row_one<VT, 0, TWO, THREADS>(s, grid, smem, p);
+    case 2: return launch_row_one<VT, 2, TWO, THREADS>(s, grid, smem, p);
+    case 4: return launch_row_one<VT, 4, TWO, THREADS>(s, grid, smem, p);
+    case 8: return launch_row_one<VT, 8, TWO, THREADS>(s, grid, smem, p);
+    case 16: return launch_row_one<VT, 16, TWO, THREADS>(s, grid, smem, p);
+    case 32: return launch_row_one<VT, 32, TWO, THREADS>(s, grid, smem, p);
     default: return -1;
     }
 }
 
-int row_pass_hot_capacity(int lanes_per_row, bool two)
-{
-    const size_t stage = lanes_per_row == 0 ? sizeof(double) * R_WARPS * R_STREAM_CAP : 0;
-    return (int)((R_MAX_DYN_SMEM - stage) / (two ? 16 : 8));
-}
-
+// Two shapes of the warp-oriented row pass: 1024 threads (one CTA per SM, up to ~28 K hot
+// coefficients in shared memory) or 256 threads (five CTAs per SM, a small hot table, most of the
+// 228 KB left to L1).  `threads`/`hot_cap` come from the data set (tuning knobs).
 int launch_row_pass(cudaStream_t s, int sm_count, int value_bytes, int lanes_per_row, bool two,
-                    RowPassParams p, int64_t n_nonempty_cols, int *grid_out)
+                    RowPassParams p, int64_t n_nonempty_cols, int threads, int hot_cap, int *grid_out)
 {
+    const int warps = threads / 32;
+    const int ctas_per_sm = threads >= 1024 ? 1 : 1280 / threads;
     const int64_t n_blk = (p.n + 31) / 32;
-    int64_t want = (n_blk + R_WARPS - 1) / R_WARPS;
-    int grid = (int)(want < sm_count ? want : sm_count);
+    int64_t want = (n_blk + warps - 1) / warps;
+    int64_t cap_grid = (int64_t)sm_count * ctas_per_sm;
+    int grid = (int)(want < cap_grid ? want : cap_grid);
     if (grid < 1) grid = 1;
     if (grid > MAX_PARTIALS) grid = MAX_PARTIALS;
     *grid_out = grid;
-    const int cap = row_pass_hot_capacity(lanes_per_row, two);
+    const size_t stage = lanes_per_row == 0 ? sizeof(double) * warps * R_STREAM_CAP : 0;
+    const size_t per_cta = (size_t)(R_MAX_DYN_SMEM / ctas_per_sm) - (ctas_per_sm > 1 ? 2048 : 0);
+    int64_t cap = per_cta > stage ? (int64_t)((per_cta - stage) / (two ? 16 : 8)) : 0;
+    if (hot_cap >= 0 && cap > hot_cap) cap = hot_cap;
     p.n_hot = (int)(n_nonempty_cols < cap ? n_nonempty_cols : cap);
-    const size_t stage = lanes_per_row == 0 ? sizeof(double) * R_WARPS * R_STREAM_CAP : 0;
     const size_t smem = stage + (size_t)p.n_hot * (two ? 16 : 8);
+    if (threads >= 1024) {
+        if (value_bytes == 4)
+            return two ? launch_row_variant<float, true, 1024>(s, grid, lanes_per_row, smem, p)
+                       : launch_row_variant<float, false, 1024>(s, grid, lanes_per_row, smem, p);
+        return two ? launch_row_variant<double, true, 1024>(s, grid, lanes_per_row, smem, p)
+                   : launch_row_variant<double, false, 1024>(s, grid, lanes_per_row, smem, p);
+    }
     if (value_bytes == 4)
-        return two ? launch_row_variant<float, true>(s, grid, lanes_per_row, smem, p)
-                   : launch_row_variant<float, false>(s, grid, lanes_per_row, smem, p);
-    return two ? launch_row_variant<double, true>(s, grid, lanes_per_row, smem, p)
-               : launch_row_variant<double, false>(s, grid, lanes_per_row, smem, p);
+        return two ? launch_row_variant<float, true, 256>(s, grid, lanes_per_row, smem, p)
+                   : launch_row_variant<float, false, 256>(s, grid, lanes_per_row, smem, p);
+    return two ? launch_row_variant<double, true, 256>(s, grid, lanes_per_row, smem, p)
+               : launch_row_variant<double, false, 256>(s, grid, lanes_per_row, smem, p);
 }
 
 // ------------------------------------------------------------------------------------------
-// col_pass_kernel -- the axpy half of `add`, transposed: out_j = sum_i val_ij * r_i over the CSC
-// copy (vectorSum += (wt*l') x_i summed column by column instead of scattered row by row;
-// ValueAndGradientAggregator.scala:150, HessianVectorAggregator.scala:118; with SQUARE,
-// HessianDiagonalAggregator.scala:59).
+// seg_spmv_kernel -- one kernel for both sparse products of an evaluation, chunked by ENTRIES.
 //
-// Work is split by ENTRIES, not by columns (column lengths are power-law): CTA c owns entries
-// [c*CHUNK, (c+1)*CHUNK), CHUNK = 256*ITEMS.  Each thread loads ITEMS consecutive entries
-// (row index with the column-start flag in bit 31, value) with 128-bit loads, gathers r for all
-// of them at once, adds up its own run, and a CTA-wide segmented scan carries partial sums
-// across threads.  Columns that start in the chunk are written by this CTA (single writer); the
-// part of the chunk that precedes its first column start belongs to a column begun in an earlier
-// chunk and goes to carry_head[c] for fixup_kernel.
+//   CSC side ("col pass"): out_j = sum_i val_ij * r_i -- the axpy half of `add`, transposed
+//     (vectorSum += (wt*l') x_i summed column by column instead of scattered row by row;
+//     ValueAndGradientAggregator.scala:150, HessianVectorAggregator.scala:118; with SQUARE,
+//     HessianDiagonalAggregator.scala:59).  idx = row index, table = r.
+//   CSR side (row-pass variant 1, "segment-per-CTA"): z_i = sum_j val_ij * ec_j
+//     (LabeledPoint.computeMargin, lib/data/LabeledPoint.scala:62).  idx = internal column id,
+//     table = effective coefficients, the first n_hot of them staged in shared memory; with TWO
+//     the table holds (ec_j, ev_j) pairs and two sums are produced (Hessian-vector, cold).
+//
+// Work is split by entries, not by rows/columns (their lengths are power-law): a chunk is
+// S_THREADS*ITEMS consecutive entries, persistent CTAs take chunks round-robin.  Each thread
+// loads ITEMS consecutive entries (index with the run-start flag in bit 31, value) with 128-bit
+// loads -- the next chunk's loads are issued before the current chunk is reduced, so the stream
+// stays in flight -- looks all of them up at once, adds up its own run, and a CTA-wide segmented
+// scan carries partial sums across threads.  Runs that start in the chunk are written by this
+// CTA (single writer); the part of the chunk that precedes its first run start belongs to a run
+// begun in an earlier chunk and goes to carry[c] for fixup_kernel.
 // ------------------------------------------------------------------------------------------
+template <bool TWO>
 struct SegScan {
-    int cnt;     // column starts seen
-    int flag;    // any column start seen
-    double val;  // running sum since the last column start
+    int cnt;      // run starts seen (0 = none)
+    double val;   // running sum since the last run start
+    double val2;  // second sum (TWO only)
 };
 
-__device__ __forceinline__ SegScan seg_combine(const SegScan &l, const SegScan &r)
+template <bool TWO>
+__device__ __forceinline__ SegScan<TWO> seg_identity()
 {
-    SegScan o;
-    o.cnt = l.cnt + r.cnt;
-    o.flag = l.flag | r.flag;
-    o.val = r.flag ? r.val : l.val + r.val;
+    SegScan<TWO> o;
+    o.cnt = 0;
+    o.val = 0.0;
+    o.val2 = 0.0;
     return o;
 }
 
-template <typename VT, bool SQUARE, int ITEMS>
-__global__ void __launch_bounds__(T_THREADS) col_pass_kernel(const ColPassParams p)
+template <bool TWO>
+__device__ __forceinline__ SegScan<TWO> seg_combine(const SegScan<TWO> &l, const SegScan<TWO> &r)
 {
-    constexpr int CHUNK = T_THREADS * ITEMS;
-    __shared__ SegScan wagg[T_THREADS / 32];
+    SegScan<TWO> o;
+    o.cnt = l.cnt + r.cnt;
+    o.val = r.cnt ? r.val : l.val + r.val;
+    o.val2 = TWO ? (r.cnt ? r.val2 : l.val2 + r.val2) : 0.0;
+    return o;
+}
 
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int c = blockIdx.x;
-    const int64_t base = (int64_t)c * CHUNK;
-    const int cnt = (p.nnz - base) < CHUNK ? (int)(p.nnz - base) : CHUNK;
-    const int col_lo = p.chunk_col_lo[c], col_hi = p.chunk_col_lo[c + 1];
-    const VT *__restrict__ val = static_cast<const VT *>(p.val) + base + tid * ITEMS;
-    const int32_t *__restrict__ row = p.row + base + tid * ITEMS;
-    const double *__restrict__ r = p.r;
+template <bool TWO>
+__device__ __forceinline__ SegScan<TWO> seg_shfl_up(const SegScan<TWO> &v, int o)
+{
+    SegScan<TWO> up;
+    up.cnt = __shfl_up_sync(0xffffffffu, v.cnt, o);
+    up.val = __shfl_up_sync(0xffffffffu, v.val, o);
+    up.val2 = TWO ? __shfl_up_sync(0xffffffffu, v.val2, o) : 0.0;
+    return up;
+}
 
-    // ---- load ITEMS consecutive entries (the arrays are padded by 16 entries past nnz) ----
-    int32_t rw[ITEMS];
-    double pr[ITEMS];
-    const int mine_cnt = cnt - tid * ITEMS;  // entries of this thread that exist (may be <= 0 in the last chunk)
+template <bool TWO>
+__device__ __forceinline__ SegScan<TWO> seg_shfl(const SegScan<TWO> &v, int src)
+{
+    SegScan<TWO> o;
+    o.cnt = __shfl_sync(0xffffffffu, v.cnt, src);
+    o.val = __shfl_sync(0xffffffffu, v.val, src);
+    o.val2 = TWO ? __shfl_sync(0xffffffffu, v.val2, src) : 0.0;
+    return o;
+}
+
+// One table look-up: shared memory for the hot prefix, the read-only global path otherwise.
+// Written as two predicated loads so that a warp mixing hot and cold indices does not diverge.
+template <bool HOT>
+__device__ __forceinline__ double seg_lookup(const double *hot, int n_hot, const double *__restrict__ table, int k)
+{
+    if (!HOT) return __ldg(table + k);
+    return (k < n_hot) ? hot[k] : __ldg(table + k);
+}
+
+template <bool HOT>
+__device__ __forceinline__ double2 seg_lookup2(const double *hot, int n_hot, const double *__restrict__ table, int k)
+{
+    if (!HOT || k >= n_hot) return __ldg(reinterpret_cast<const double2 *>(table) + k);
+    return reinterpret_cast<const double2 *>(hot)[k];
+}
+
+template <typename VT, int ITEMS>
+struct SegRegs {
+    int32_t idx[ITEMS];
+    VT val[ITEMS];
+};
+
+template <typename VT, int ITEMS>
+__device__ __forceinline__ void seg_load(SegRegs<VT, ITEMS> &g, const int32_t *__restrict__ idx, const VT *__restrict__ val,
+                                         int64_t first, int mine_cnt)
+{
+    if (mine_cnt <= 0) {
+#pragma unroll
+        for (int i = 0; i < ITEMS; ++i) { g.idx[i] = 0; g.val[i] = (VT)0; }
+        return;
+    }
+    // the arrays are padded by 16 entries past nnz, so a partially filled thread may read ahead
 #pragma unroll
     for (int i = 0; i < ITEMS / 4; ++i) {
-        if (mine_cnt <= 0) {
-            rw[4 * i] = rw[4 * i + 1] = rw[4 * i + 2] = rw[4 * i + 3] = 0;
-            pr[4 * i] = pr[4 * i + 1] = pr[4 * i + 2] = pr[4 * i + 3] = 0.0;
-            continue;
-        }
-        const int4 rr = __ldg(reinterpret_cast<const int4 *>(row) + i);
-        rw[4 * i] = rr.x; rw[4 * i + 1] = rr.y; rw[4 * i + 2] = rr.z; rw[4 * i + 3] = rr.w;
+        const int4 rr = __ldcs(reinterpret_cast<const int4 *>(idx + first) + i);
+        g.idx[4 * i] = rr.x; g.idx[4 * i + 1] = rr.y; g.idx[4 * i + 2] = rr.z; g.idx[4 * i + 3] = rr.w;
         if (sizeof(VT) == 4) {
-            const float4 vv = __ldg(reinterpret_cast<const float4 *>(val) + i);
-            pr[4 * i] = vv.x; pr[4 * i + 1] = vv.y; pr[4 * i + 2] = vv.z; pr[4 * i + 3] = vv.w;
+            const float4 vv = __ldcs(reinterpret_cast<const float4 *>(val + first) + i);
+            g.val[4 * i] = vv.x; g.val[4 * i + 1] = vv.y; g.val[4 * i + 2] = vv.z; g.val[4 * i + 3] = vv.w;
         } else {
-            const double2 va = __ldg(reinterpret_cast<const double2 *>(val) + 2 * i);
-            const double2 vb = __ldg(reinterpret_cast<const double2 *>(val) + 2 * i + 1);
-            pr[4 * i] = va.x; pr[4 * i + 1] = va.y; pr[4 * i + 2] = vb.x; pr[4 * i + 3] = vb.y;
+            const double2 va = __ldcs(reinterpret_cast<const double2 *>(val + first) + 2 * i);
+            const double2 vb = __ldcs(reinterpret_cast<const double2 *>(val + first) + 2 * i + 1);
+            g.val[4 * i] = va.x; g.val[4 * i + 1] = va.y; g.val[4 * i + 2] = vb.x; g.val[4 * i + 3] = vb.y;
         }
     }
+}
+
+// Reduces one chunk held in `cur`.  FULL = every thread owns ITEMS live entries (all chunks but
+// possibly the last), which removes the per-entry bounds tests from the common path.
+template <typename VT, int ITEMS, bool TWO, bool SQUARE, bool HOT, bool FULL>
+__device__ __forceinline__ void seg_chunk(const SegParams &p, const SegRegs<VT, ITEMS> &cur, int c, int mine_cnt,
+                                          const double *hot, SegScan<TWO> *wagg_c)
+{
+    constexpr int WARPS = S_THREADS / 32;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const double *__restrict__ table = p.table;
+    const int n_hot = p.n_hot;
+
+    // ---- look up and multiply ----
+    double pr[ITEMS], pr2[TWO ? ITEMS : 1];
     unsigned mask = 0;
 #pragma unroll
     for (int i = 0; i < ITEMS; ++i) {
-        const bool live = i < mine_cnt;
-        if (live && rw[i] < 0) mask |= 1u << i;
-        const int32_t ri = live ? (rw[i] & 0x7fffffff) : 0;
-        double x = live ? pr[i] : 0.0;
+        const bool live = FULL || i < mine_cnt;
+        if (live && cur.idx[i] < 0) mask |= 1u << i;
+        const int32_t k = live ? (cur.idx[i] & 0x7fffffff) : 0;
+        double x = live ? widen(cur.val[i]) : 0.0;
         if (SQUARE) x *= x;
-        pr[i] = __dmul_rn(__ldg(r + ri), x);
+        if (TWO) {
+            const double2 g = seg_lookup2<HOT>(hot, n_hot, table, k);
+            pr[i] = __dmul_rn(g.x, x);
+            pr2[i] = __dmul_rn(g.y, x);
+        } else {
+            pr[i] = __dmul_rn(seg_lookup<HOT>(hot, n_hot, table, k), x);
+        }
     }
 
     // ---- blocked segmented reduction ----
-    SegScan mine;
+    SegScan<TWO> mine;
     mine.cnt = __popc(mask);
-    mine.flag = mask != 0;
     {
-        double s = 0.0;
+        double s = 0.0, s2 = 0.0;
 #pragma unroll
         for (int i = 0; i < ITEMS; ++i) {
-            if ((mask >> i) & 1u) s = 0.0;
+            if ((mask >> i) & 1u) { s = 0.0; s2 = 0.0; }
             s += pr[i];
+            if (TWO) s2 += pr2[i];
         }
-        mine.val = s;  // sum after the last column start (the whole run if there is none)
+        mine.val = s;  // sum after the last run start (the whole thread if there is none)
+        mine.val2 = s2;
     }
-    SegScan inc = mine;
+    SegScan<TWO> inc = mine;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
-        SegScan up;
-        up.cnt = __shfl_up_sync(0xffffffffu, inc.cnt, o);
-        up.flag = __shfl_up_sync(0xffffffffu, inc.flag, o);
-        up.val = __shfl_up_sync(0xffffffffu, inc.val, o);
-        if (lane >= o) inc = seg_combine(up, inc);
+        const SegScan<TWO> up = seg_shfl_up<TWO>(inc, o);
+        if (lane >= o) inc = seg_combine<TWO>(up, inc);
     }
-    if (lane == 31) wagg[warp] = inc;
-    SegScan exc;
-    exc.cnt = __shfl_up_sync(0xffffffffu, inc.cnt, 1);
-    exc.flag = __shfl_up_sync(0xffffffffu, inc.flag, 1);
-    exc.val = __shfl_up_sync(0xffffffffu, inc.val, 1);
-    if (lane == 0) { exc.cnt = 0; exc.flag = 0; exc.val = 0.0; }
-    __syncthreads();
-    SegScan pre;
-    pre.cnt = 0; pre.flag = 0; pre.val = 0.0;
-    for (int w = 0; w < warp; ++w) pre = seg_combine(pre, wagg[w]);
-    exc = seg_combine(pre, exc);
+    if (lane == 31) wagg_c[warp] = inc;
+    SegScan<TWO> exc = seg_shfl_up<TWO>(inc, 1);
+    if (lane == 0) exc = seg_identity<TWO>();
+    __syncthreads();  // wagg is double-buffered by chunk parity, so one barrier per chunk suffices
+    SegScan<TWO> pre = seg_identity<TWO>();
+    for (int w = 0; w < warp; ++w) pre = seg_combine<TWO>(pre, wagg_c[w]);
+    exc = seg_combine<TWO>(pre, exc);
 
-    // walk again, closing columns
-    if (mine.flag) {
-        double s = 0.0;
-        int ord = col_lo + exc.cnt;  // internal id of the next column start this thread meets
+    const int run_lo = p.chunk_lo[c];
+    // walk again, closing runs
+    if (mask != 0) {
+        double s = 0.0, s2 = 0.0;
+        int ord = run_lo + exc.cnt;  // ordinal of the next run start this thread meets
         bool first = true;
 #pragma unroll
         for (int i = 0; i < ITEMS; ++i) {
             if ((mask >> i) & 1u) {
                 const double total = first ? exc.val + s : s;
-                if (first && exc.cnt == 0) p.carry_head[c] = total;  // column began in an earlier chunk
-                else p.out[p.nzcol_id[ord - 1]] = total;
+                const double total2 = TWO ? (first ? exc.val2 + s2 : s2) : 0.0;
+                if (first && exc.cnt == 0) {  // the run began in an earlier chunk
+                    p.carry[c] = total;
+                    if (TWO) p.carry2[c] = total2;
+                } else {
+                    const int slot = p.run_id ? p.run_id[ord - 1] : ord - 1;
+                    p.out[slot] = total;
+                    if (TWO) p.out2[slot] = total2;
+                }
                 first = false;
                 ++ord;
                 s = 0.0;
+                s2 = 0.0;
             }
             s += pr[i];
+            if (TWO) s2 += pr2[i];
         }
     }
-    if (tid == T_THREADS - 1) {
-        const SegScan tot = seg_combine(exc, mine);
-        if (tot.flag) p.out[p.nzcol_id[col_hi - 1]] = tot.val;  // last column started here: owner
-        else p.carry_head[c] = tot.val;                         // the whole chunk is one column's middle
+    if (tid == S_THREADS - 1) {
+        const SegScan<TWO> tot = seg_combine<TWO>(exc, mine);
+        if (tot.cnt) {  // the last run started here: this CTA owns its slot
+            const int last = run_lo + tot.cnt - 1;
+            const int slot = p.run_id ? p.run_id[last] : last;
+            p.out[slot] = tot.val;
+            if (TWO) p.out2[slot] = tot.val2;
+        } else {        // the whole chunk is the middle of one run
+            p.carry[c] = tot.val;
+            if (TWO) p.carry2[c] = tot.val2;
+        }
     }
 }
 
-template <typename VT, bool SQUARE>
-static int launch_col_items(cudaStream_t s, int items, const ColPassParams &p)
+template <typename VT, int ITEMS, bool TWO, bool SQUARE, bool HOT>
+__global__ void __launch_bounds__(S_THREADS, 2) seg_spmv_kernel(const SegParams p)
 {
-    switch (items) {
-    case 8: col_pass_kernel<VT, SQUARE, 8><<<p.n_chunks, T_THREADS, 0, s>>>(p); break;
-    case 16: col_pass_kernel<VT, SQUARE, 16><<<p.n_chunks, T_THREADS, 0, s>>>(p); break;
-    default: return -1;
+    constexpr int CHUNK = S_THREADS * ITEMS;
+    constexpr int WARPS = S_THREADS / 32;
+    extern __shared__ __align__(16) double hot[];
+    __shared__ SegScan<TWO> wagg[2][WARPS];
+
+    const int tid = threadIdx.x;
+    const VT *__restrict__ val = static_cast<const VT *>(p.val);
+    const int32_t *__restrict__ idx = p.idx;
+
+    if (HOT) {
+        const int words = TWO ? 2 * p.n_hot : p.n_hot;
+        for (int i = tid; i < words; i += S_THREADS) hot[i] = p.table[i];
+        __syncthreads();
+    }
+
+    SegRegs<VT, ITEMS> cur;
+    int c = blockIdx.x;
+    if (c < p.n_chunks) {
+        const int64_t base = (int64_t)c * CHUNK;
+        const int cnt = (p.nnz - base) < CHUNK ? (int)(p.nnz - base) : CHUNK;
+        seg_load<VT, ITEMS>(cur, idx, val, base + tid * ITEMS, cnt - tid * ITEMS);
+    }
+    int parity = 0;
+    for (; c < p.n_chunks; c += gridDim.x, parity ^= 1) {
+        const int64_t base = (int64_t)c * CHUNK;
+        const int cnt = (p.nnz - base) < CHUNK ? (int)(p.nnz - base) : CHUNK;
+
+        // issue the next chunk's loads before touching this one
+        SegRegs<VT, ITEMS> nxt;
+        const int cn = c + gridDim.x;
+        if (cn < p.n_chunks) {
+            const int64_t nb = (int64_t)cn * CHUNK;
+            const int ncnt = (p.nnz - nb) < CHUNK ? (int)(p.nnz - nb) : CHUNK;
+            seg_load<VT, ITEMS>(nxt, idx, val, nb + tid * ITEMS, ncnt - tid * ITEMS);
+        }
+        seg_chunk<VT, ITEMS, TWO, SQUARE, HOT, false>(p, cur, c, cnt - tid * ITEMS, hot, wagg[parity]);
+        cur = nxt;
+    }
+}
+
+template <typename VT, int ITEMS, bool TWO, bool SQUARE>
+static int launch_seg_one(cudaStream_t s, int grid, size_t smem, const SegParams &p)
+{
+    if (p.n_hot > 0) {
+        if (smem > 48 * 1024 &&
+            cudaFuncSetAttribute(seg_spmv_kernel<VT, ITEMS, TWO, SQUARE, true>,
+                                 cudaFuncAttributeMaxDynamicSharedMemorySize, S_MAX_DYN_SMEM) != cudaSuccess)
+            return -1;
+        seg_spmv_kernel<VT, ITEMS, TWO, SQUARE, true><<<grid, S_THREADS, smem, s>>>(p);
+    } else {
+        seg_spmv_kernel<VT, ITEMS, TWO, SQUARE, false><<<grid, S_THREADS, 0, s>>>(p);
     }
     return cudaGetLastError() == cudaSuccess ? 1 : -1;
 }
 
-int launch_col_pass(cudaStream_t s, int value_bytes, bool square, int chunk_entries, const ColPassParams &p)
+int seg_hot_capacity(bool two) { return (int)(S_MAX_DYN_SMEM / (two ? 16 : 8)); }
+
+// table_len = number of leading table entries worth staging (0 = no shared-memory table)
+int launch_seg_spmv(cudaStream_t s, int sm_count, int value_bytes, bool two, bool square, int chunk_entries,
+                    SegParams p, int64_t table_len)
 {
     if (p.n_chunks <= 0) return 0;
-    const int items = chunk_entries / T_THREADS;
-    if (value_bytes == 4)
-        return square ? launch_col_items<float, true>(s, items, p) : launch_col_items<float, false>(s, items, p);
-    return square ? launch_col_items<double, true>(s, items, p) : launch_col_items<double, false>(s, items, p);
+    const int cap = seg_hot_capacity(two);
+    p.n_hot = (int)(table_len < cap ? table_len : cap);
+    const size_t smem = (size_t)p.n_hot * (two ? 16 : 8);
+    int grid = sm_count * 2;
+    if (grid > p.n_chunks) grid = p.n_chunks;
+    const int items = chunk_entries / S_THREADS;
+    if (items != 8) return -1;
+    if (value_bytes == 4) {
+        if (two) return launch_seg_one<float, 8, true, false>(s, grid, smem, p);
+        return square ? launch_seg_one<float, 8, false, true>(s, grid, smem, p)
+                      : launch_seg_one<float, 8, false, false>(s, grid, smem, p);
+    }
+    if (two) return launch_seg_one<double, 8, true, false>(s, grid, smem, p);
+    return square ? launch_seg_one<double, 8, false, true>(s, grid, smem, p)
+                  : launch_seg_one<double, 8, false, false>(s, grid, smem, p);
+}
+
+// ------------------------------------------------------------------------------------------
+// row_epilogue_kernel -- the scalar half of `add` for row-pass variant 1, where the sparse dots
+// were produced by seg_spmv_kernel: z_i = dot_i + o_i + marginShift, pointwise loss, r_i and the
+// per-CTA (F, P) partials.  Same arithmetic, in the same order, as row_pass_kernel's epilogue.
+// ------------------------------------------------------------------------------------------
+constexpr int E_THREADS = 256;
+
+__global__ void __launch_bounds__(E_THREADS) row_epilogue_kernel(const RowPassParams p, const double *__restrict__ za,
+                                                                 const double *__restrict__ zb)
+{
+    __shared__ double red[2 * (E_THREADS / 32)];
+    double shift0 = 0.0, shift1 = 0.0;
+    if (p.shift_partials != nullptr) {
+        for (int i = threadIdx.x; i < p.n_shift_partials; i += E_THREADS) {
+            shift0 += p.shift_partials[2 * i];
+            shift1 += p.shift_partials[2 * i + 1];
+        }
+        block_sum2<E_THREADS / 32>(shift0, shift1, red);
+    }
+    const double margin_shift = (p.mode == MODE_HV_CACHED) ? 0.0 : -shift0;
+    const double fs = (p.mode == MODE_HV_CACHED) ? shift0 : shift1;
+    double accF = 0.0, accP = 0.0;
+    for (int64_t i = (int64_t)blockIdx.x * E_THREADS + threadIdx.x; i < p.n; i += (int64_t)gridDim.x * E_THREADS) {
+        const double o = p.offset ? __ldcs(p.offset + i) : 0.0;
+        const double wt = p.weight ? __ldcs(p.weight + i) : 1.0;
+        const double dot = __ldcs(za + i);
+        switch (p.mode) {
+        case MODE_VG: {
+            const double z = (dot + o) + margin_shift;
+            double l, dl;
+            loss_and_dz(p.loss, z, __ldcs(p.label + i), l, dl);
+            const double wdl = __dmul_rn(wt, dl);
+            p.r[i] = wdl;
+            accF += __dmul_rn(wt, l);
+            accP += wdl;
+            break;
+        }
+        case MODE_HV_COLD: {
+            const double z = (dot + o) + margin_shift;
+            const double dq = __dmul_rn(wt, dzz_loss(p.loss, z));
+            if (p.dcache) p.dcache[i] = dq;
+            const double e = __dmul_rn(dq, __ldcs(zb + i) - fs);
+            p.r[i] = e;
+            accP += e;
+            break;
+        }
+        case MODE_HV_CACHED: {
+            const double e = __dmul_rn(__ldcs(p.dcache + i), dot - fs);
+            p.r[i] = e;
+            accP += e;
+            break;
+        }
+        case MODE_DIAG:
+            p.r[i] = __dmul_rn(wt, dzz_loss(p.loss, dot + o));
+            break;
+        default:
+            p.r[i] = dot;
+            break;
+        }
+    }
+    if (p.partials != nullptr) {
+        block_sum2<E_THREADS / 32>(accF, accP, red);
+        if (threadIdx.x == 0) {
+            p.partials[2 * blockIdx.x] = accF;
+            p.partials[2 * blockIdx.x + 1] = accP;
+        }
+    }
+}
+
+int launch_row_epilogue(cudaStream_t s, int sm_count, const RowPassParams &p, const double *za, const double *zb,
+                        int *grid_out)
+{
+    int64_t want = (p.n + E_THREADS - 1) / E_THREADS;
+    int64_t cap = (int64_t)sm_count * 8;
+    if (cap > MAX_PARTIALS) cap = MAX_PARTIALS;
+    int grid = (int)(want < cap ? want : cap);
+    if (grid < 1) grid = 1;
+    *grid_out = grid;
+    row_epilogue_kernel<<<grid, E_THREADS, 0, s>>>(p, za, zb);
+    return cudaGetLastError() == cudaSuccess ? 1 : -1;
 }
 
 // ------------------------------------------------------------------------------------------
@@ -495,8 +728,8 @@ constexpr int F_THREADS = 256;
 
 __global__ void __launch_bounds__(F_THREADS)
 fixup_kernel(const FixEntry *__restrict__ fix, int n_fix, const double *__restrict__ carry_head,
-             double *__restrict__ out, int d, const double *__restrict__ partials, int n_partials,
-             int write_value, int write_prefactor)
+             double *__restrict__ out, const double *__restrict__ carry_head2, double *__restrict__ out2, int d,
+             const double *__restrict__ partials, int n_partials, int write_value, int write_prefactor)
 {
     __shared__ double red[2 * (F_THREADS / 32)];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -516,18 +749,26 @@ fixup_kernel(const FixEntry *__restrict__ fix, int n_fix, const double *__restri
     const int q = blockIdx.x * (F_THREADS / 32) + warp;
     if (q >= n_fix) return;
     const FixEntry e = fix[q];
-    double s = 0.0;
-    for (int cc = e.chunk_begin + lane; cc < e.chunk_end; cc += 32) s += carry_head[cc];
+    double s = 0.0, s2 = 0.0;
+    for (int cc = e.chunk_begin + lane; cc < e.chunk_end; cc += 32) {
+        s += carry_head[cc];
+        if (carry_head2) s2 += carry_head2[cc];
+    }
     s = warp_sum(s);
-    if (lane == 0) out[e.col] += s;
+    s2 = warp_sum(s2);
+    if (lane == 0) {
+        out[e.col] += s;
+        if (carry_head2) out2[e.col] += s2;
+    }
 }
 
-int launch_fixup(cudaStream_t s, const FixEntry *fix, int n_fix, const double *carry_head, double *out, int d,
-                 const double *partials, int n_partials, bool write_value, bool write_prefactor)
+int launch_fixup(cudaStream_t s, const FixEntry *fix, int n_fix, const double *carry_head, double *out,
+                 const double *carry_head2, double *out2, int d, const double *partials, int n_partials,
+                 bool write_value, bool write_prefactor)
 {
     int grid = (n_fix + (F_THREADS / 32) - 1) / (F_THREADS / 32) + (partials ? 1 : 0);
     if (grid == 0) return 0;
-    fixup_kernel<<<grid, F_THREADS, 0, s>>>(fix, n_fix, carry_head, out, d, partials, n_partials,
+    fixup_kernel<<<grid, F_THREADS, 0, s>>>(fix, n_fix, carry_head, out, carry_head2, out2, d, partials, n_partials,
                                             write_value ? 1 : 0, write_prefactor ? 1 : 0);
     return cudaGetLastError() == cudaSuccess ? 1 : -1;
 }

@@ -77,6 +77,25 @@ __global__ void remap_cols_kernel(int64_t nnz, int32_t *__restrict__ col, const 
         col[k] = rank[col[k]];
 }
 
+__global__ void nonempty_rows_kernel(int64_t n, const uint32_t *__restrict__ row_ptr, int32_t *__restrict__ flag)
+{
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        flag[i] = row_ptr[i + 1] > row_ptr[i] ? 1 : 0;
+}
+
+__global__ void compact_rows_kernel(int64_t n, const uint32_t *__restrict__ row_ptr, const int32_t *__restrict__ flag,
+                                    const int32_t *__restrict__ pos, int64_t nnz, int64_t runs,
+                                    uint32_t *__restrict__ run_ptr, int32_t *__restrict__ run_id)
+{
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        if (flag[i]) {
+            run_ptr[pos[i]] = row_ptr[i];
+            run_id[pos[i]] = (int32_t)i;
+        }
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) run_ptr[runs] = (uint32_t)nnz;
+}
+
 __global__ void mark_starts_kernel(int64_t m, const uint32_t *__restrict__ col_ptr, int32_t *__restrict__ csc_row)
 {
     for (int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; c < m; c += (int64_t)gridDim.x * blockDim.x)
@@ -210,6 +229,50 @@ int check_columns(cudaStream_t s, const int32_t *col, int64_t nnz, int32_t d, in
     return PML_OK;
 }
 
+// Fix-up list: runs of consecutive chunks whose heads continue one run (host-side, tiny).
+// run_id maps a run ordinal to its output slot (null = identity).
+static int build_fix_list(cudaStream_t s, int n_chunks, const int32_t *chunk_lo_dev, const int32_t *head_dev,
+                          const int32_t *run_id_dev, int64_t n_runs, FixEntry **fix_out, int *n_fix_out, int64_t *bytes)
+{
+    std::vector<int32_t> h_lo((size_t)n_chunks + 1), h_head((size_t)n_chunks + 1, 0);
+    PML_CUDA(cudaMemcpyAsync(h_lo.data(), chunk_lo_dev, sizeof(int32_t) * (size_t)(n_chunks + 1), cudaMemcpyDeviceToHost, s));
+    if (n_chunks > 0)
+        PML_CUDA(cudaMemcpyAsync(h_head.data(), head_dev, sizeof(int32_t) * (size_t)n_chunks, cudaMemcpyDeviceToHost, s));
+    PML_CUDA(cudaStreamSynchronize(s));
+    std::vector<int32_t> fix_ord;  // run ordinal per fix entry
+    std::vector<FixEntry> fix;
+    for (int c = 1; c < n_chunks; ++c) {
+        if (!h_head[c]) continue;
+        const int32_t ord = h_lo[c] - 1;  // the run that was open when chunk c began
+        if (!fix.empty() && fix_ord.back() == ord && fix.back().chunk_end == c) {
+            fix.back().chunk_end = c + 1;
+        } else {
+            FixEntry e;
+            e.col = ord;  // replaced by the output slot below when there is a run_id map
+            e.chunk_begin = c;
+            e.chunk_end = c + 1;
+            fix.push_back(e);
+            fix_ord.push_back(ord);
+        }
+    }
+    *n_fix_out = (int)fix.size();
+    *fix_out = nullptr;
+    if (!fix.empty()) {
+        if (run_id_dev != nullptr) {
+            std::vector<int32_t> h_ids((size_t)n_runs);
+            // only a handful of ids are needed, but n_runs*4 bytes once at pack time is simpler than a gather
+            PML_CUDA(cudaMemcpyAsync(h_ids.data(), run_id_dev, sizeof(int32_t) * (size_t)n_runs, cudaMemcpyDeviceToHost, s));
+            PML_CUDA(cudaStreamSynchronize(s));
+            for (size_t q = 0; q < fix.size(); ++q) fix[q].col = h_ids[(size_t)fix_ord[q]];
+        }
+        PML_CUDA(cudaMalloc(fix_out, sizeof(FixEntry) * fix.size()));
+        PML_CUDA(cudaMemcpyAsync(*fix_out, fix.data(), sizeof(FixEntry) * fix.size(), cudaMemcpyHostToDevice, s));
+        PML_CUDA(cudaStreamSynchronize(s));
+        *bytes += (int64_t)sizeof(FixEntry) * (int64_t)fix.size();
+    }
+    return PML_OK;
+}
+
 // Packing proper.  Columns are renumbered by descending entry count ("internal ids": the m
 // non-empty columns are exactly ids [0, m), hottest first; ties keep the original order), the CSR
 // column array is rewritten in place to internal ids, and the CSC copy is built in internal-id
@@ -308,41 +371,58 @@ int build_transpose(cudaStream_t s, int64_t n, int32_t d, int64_t nnz, const uin
                                                                      out->chunk_col_lo, head.as<int32_t>());
     PML_CUDA(cudaGetLastError());
 
-    // fix-up list: runs of consecutive chunks whose heads continue one column (host-side, tiny)
-    std::vector<int32_t> h_lo((size_t)n_chunks + 1), h_head((size_t)n_chunks + 1, 0);
-    PML_CUDA(cudaMemcpyAsync(h_lo.data(), out->chunk_col_lo, sizeof(int32_t) * (size_t)(n_chunks + 1),
-                             cudaMemcpyDeviceToHost, s));
-    if (n_chunks > 0)
-        PML_CUDA(cudaMemcpyAsync(h_head.data(), head.p, sizeof(int32_t) * (size_t)n_chunks, cudaMemcpyDeviceToHost, s));
+    PML_TRY(build_fix_list(s, n_chunks, out->chunk_col_lo, head.as<int32_t>(), out->nzcol_id, m, &out->fix, &out->n_fix,
+                           &out->bytes));
+    return PML_OK;
+}
+
+// Chunk metadata of the CSR stream for row-pass variant 1: marks the first entry of every
+// non-empty row in bit 31 of its (internal) column id, lists the non-empty rows when some rows
+// are empty, and builds chunk_lo / fix exactly as for the CSC side.
+int build_row_side(cudaStream_t s, int64_t n, int64_t nnz, const uint32_t *row_ptr, int32_t *col, int chunk_entries,
+                   RowSide *out)
+{
+    out->n_chunks = (int)((nnz + chunk_entries - 1) / chunk_entries);
+    const int n_chunks = out->n_chunks;
+    out->bytes = 0;
+    PML_CUDA(cudaMalloc(&out->chunk_lo, sizeof(int32_t) * (size_t)(n_chunks + 1)));
+    out->bytes += (int64_t)sizeof(int32_t) * (n_chunks + 1);
+    DevBuf flag, pos, run_ptr, head;
+    PML_CUDA(flag.alloc(sizeof(int32_t) * (size_t)(n + 1)));
+    PML_CUDA(pos.alloc(sizeof(int32_t) * (size_t)(n + 1)));
+    PML_CUDA(head.alloc(sizeof(int32_t) * (size_t)(n_chunks + 1)));
+    // flag[i] = row i non-empty (same kernel as for columns: it only compares neighbouring pointers)
+    nonempty_rows_kernel<<<grid_for(n), 256, 0, s>>>(n, row_ptr, flag.as<int32_t>());
+    PML_CUDA(cudaMemsetAsync(flag.as<int32_t>() + n, 0, sizeof(int32_t), s));
+    PML_CUDA(cudaGetLastError());
+    {
+        DevBuf t;
+        size_t tb = 0;
+        PML_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tb, flag.as<int32_t>(), pos.as<int32_t>(), n + 1, s));
+        PML_CUDA(t.alloc(tb));
+        PML_CUDA(cub::DeviceScan::ExclusiveSum(t.p, tb, flag.as<int32_t>(), pos.as<int32_t>(), n + 1, s));
+    }
+    int32_t runs32 = 0;
+    PML_CUDA(cudaMemcpyAsync(&runs32, pos.as<int32_t>() + n, sizeof(int32_t), cudaMemcpyDeviceToHost, s));
     PML_CUDA(cudaStreamSynchronize(s));
-    std::vector<int32_t> fix_ord;  // internal column id per fix entry
-    std::vector<FixEntry> fix;
-    for (int c = 1; c < n_chunks; ++c) {
-        if (!h_head[c]) continue;
-        const int32_t ord = h_lo[c] - 1;  // the column that was open when chunk c began
-        if (!fix.empty() && fix_ord.back() == ord && fix.back().chunk_end == c) {
-            fix.back().chunk_end = c + 1;
-        } else {
-            FixEntry e;
-            e.col = ord;  // replaced by the original column id below
-            e.chunk_begin = c;
-            e.chunk_end = c + 1;
-            fix.push_back(e);
-            fix_ord.push_back(ord);
-        }
+    out->n_runs = runs32;
+    const int64_t runs = out->n_runs;
+    const uint32_t *run_ptr_dev = row_ptr;
+    if (runs < n) {
+        PML_CUDA(cudaMalloc(&out->nzrow_id, sizeof(int32_t) * (size_t)(runs + 1)));
+        out->bytes += (int64_t)sizeof(int32_t) * (runs + 1);
+        PML_CUDA(run_ptr.alloc(sizeof(uint32_t) * (size_t)(runs + 1)));
+        compact_rows_kernel<<<grid_for(n), 256, 0, s>>>(n, row_ptr, flag.as<int32_t>(), pos.as<int32_t>(), nnz, runs,
+                                                       run_ptr.as<uint32_t>(), out->nzrow_id);
+        PML_CUDA(cudaGetLastError());
+        run_ptr_dev = run_ptr.as<uint32_t>();
     }
-    out->n_fix = (int)fix.size();
-    if (!fix.empty()) {
-        std::vector<int32_t> h_ids((size_t)m);
-        // only a handful of ids are needed, but m*4 bytes once at pack time is simpler than a gather
-        PML_CUDA(cudaMemcpyAsync(h_ids.data(), out->nzcol_id, sizeof(int32_t) * (size_t)m, cudaMemcpyDeviceToHost, s));
-        PML_CUDA(cudaStreamSynchronize(s));
-        for (size_t q = 0; q < fix.size(); ++q) fix[q].col = h_ids[(size_t)fix_ord[q]];
-        PML_CUDA(cudaMalloc(&out->fix, sizeof(FixEntry) * fix.size()));
-        PML_CUDA(cudaMemcpyAsync(out->fix, fix.data(), sizeof(FixEntry) * fix.size(), cudaMemcpyHostToDevice, s));
-        PML_CUDA(cudaStreamSynchronize(s));
-        out->bytes += (int64_t)sizeof(FixEntry) * (int64_t)fix.size();
-    }
+    if (nnz > 0) mark_starts_kernel<<<grid_for(runs), 256, 0, s>>>(runs, run_ptr_dev, col);
+    chunk_meta_kernel<<<grid_for((int64_t)n_chunks + 1), 256, 0, s>>>(n_chunks, chunk_entries, runs, run_ptr_dev,
+                                                                     out->chunk_lo, head.as<int32_t>());
+    PML_CUDA(cudaGetLastError());
+    PML_TRY(build_fix_list(s, n_chunks, out->chunk_lo, head.as<int32_t>(), out->nzrow_id, runs, &out->fix, &out->n_fix,
+                           &out->bytes));
     return PML_OK;
 }
 

@@ -17,7 +17,7 @@ pytestmark = pytest.mark.gpu
 
 TOL = 1e-11
 LOSSES = [oracle.LOGISTIC, oracle.POISSON, oracle.SQUARED]
-VARIANTS = [0, 2, 4, 8, 16, 32]
+VARIANTS = [0, 1, 2, 4, 8, 16, 32]
 
 
 @pytest.fixture(scope="module")

@@ -31,7 +31,7 @@ def main():
     raw = torch.empty(d + 2, dtype=torch.float64, device=device)
     torch.cuda.synchronize()
     rb, cb = bench.kernel_bytes(info, 0, 0)
-    variants = [int(x) for x in os.environ.get("SWEEP_VARIANTS", "0,4,8,16").split(",")]
+    variants = [int(x) for x in os.environ.get("SWEEP_VARIANTS", "1,8").split(",")]
     for var in variants:
         ds.set_margin_variant(var)
         for _ in range(3):
