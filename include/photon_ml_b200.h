@@ -183,6 +183,32 @@ int pml_ctx_read_profile(pml_ctx *ctx, double *out_ms /* [PML_K_COUNT] */,
  * default choice.  For benchmarking and tests. */
 int pml_dataset_set_margin_variant(pml_dataset *ds, int lanes_per_row);
 
+/* ---- batched per-entity problems (random effects) ------------------------------------------ */
+/* Replaces the body of the per-entity mapValues in RandomEffectCoordinate.updateModel
+ * (api/algorithm/RandomEffectCoordinate.scala:108-119), where each entity's
+ * SingleNodeGLMLossFunction.calculate (api/function/glm/SingleNodeGLMLossFunction.scala:83-91)
+ * runs over its own LocalDataSet (api/data/LocalDataSet.scala:36): all E local problems are
+ * evaluated together.  Rows are concatenated entity by entity (entity e owns rows
+ * [ent_row_ptr[e], ent_row_ptr[e+1])); col_local holds each row's indices in the entity's own
+ * (projected) space [0, ent_dim[e]).  Coefficients, gradients and multiply vectors of all
+ * entities are concatenated in entity order (entity e at [coef_ptr[e], coef_ptr[e+1]),
+ * coef_ptr = prefix sum of ent_dim).  Entities are independent, so with several GPUs each rank
+ * packs its own subset and no collective is needed. */
+typedef struct pml_batch pml_batch;
+int pml_batch_create_csr(pml_ctx *ctx, int64_t n_entities, const int64_t *ent_row_ptr,
+                         const int32_t *ent_dim, const int64_t *row_ptr, const int32_t *col_local,
+                         const void *values, int values_dtype, int storage, const double *labels,
+                         const double *offsets, const double *weights, pml_batch **out);
+int pml_batch_destroy(pml_batch *b);
+/* The block-diagonal data set behind the batch: pml_dataset_set_offsets / set_weights (rows in
+ * concatenated order), pml_hessian_vector, pml_hessian_diagonal and pml_scores apply to all
+ * entities at once through it.  Owned by the batch; do not destroy it. */
+int pml_batch_dataset(pml_batch *b, pml_dataset **out);
+int pml_batch_coef_ptr(pml_batch *b, int64_t *out /* E+1 */);
+/* out_values[e] = entity e's objective value; out_grads (may be NULL) = concatenated gradients */
+int pml_batch_value_and_gradient(pml_batch *b, int loss, const double *coefs, double *out_values,
+                                 double *out_grads);
+
 /* ---- evaluation without any allocation ------------------------------------------------------ */
 /* No counterpart in the reference (the JVM allocates freely); this exists for callers of THIS
  * library that must not trigger cudaMalloc/cudaFree: the JNI shim while it pins Java arrays with

@@ -25,7 +25,8 @@ SYMBOLS = [
     "pml_hessian_diagonal", "pml_scores", "pml_value_and_gradient_raw_dev", "pml_hessian_vector_raw_dev",
     "pml_finalize_dev", "pml_value_and_gradient_dev", "pml_hessian_vector_dev", "pml_ctx_launch_count",
     "pml_dataset_set_margin_variant", "pml_ctx_set_profiling", "pml_ctx_read_profile",
-    "pml_value_noalloc_dev",
+    "pml_value_noalloc_dev", "pml_batch_create_csr", "pml_batch_destroy", "pml_batch_dataset", "pml_batch_coef_ptr",
+    "pml_batch_value_and_gradient",
 ]
 
 
@@ -96,6 +97,13 @@ def load():
         "pml_ctx_read_profile": [vp, ctypes.POINTER(dbl), ctypes.POINTER(i64)],
         "pml_value_noalloc_dev": [ctypes.c_int, vp, i64, i32, vp, vp, vp, ctypes.c_int, vp, vp, vp, ctypes.c_int, vp, vp],
     }
+    sigs.update({
+        "pml_batch_create_csr": [vp, i64, vp, vp, vp, vp, vp, ctypes.c_int, ctypes.c_int, vp, vp, vp, pp],
+        "pml_batch_destroy": [vp],
+        "pml_batch_dataset": [vp, pp],
+        "pml_batch_coef_ptr": [vp, vp],
+        "pml_batch_value_and_gradient": [vp, ctypes.c_int, vp, vp, vp],
+    })
     for name, argtypes in sigs.items():
         fn = getattr(lib, name)
         fn.restype = ctypes.c_int
@@ -287,8 +295,64 @@ class Dataset:
         check(load().pml_hessian_vector_dev(self._h, loss, coef_dev, int(tag), v_dev, out_hv_dev))
 
     def close(self):
-        if self._h:
+        if self._h and not getattr(self, "_borrowed", False):
             load().pml_dataset_destroy(self._h)
+        self._h = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Batch:
+    """Many per-entity local problems evaluated together (pml_batch): the random-effect path."""
+
+    def __init__(self, ctx, ent_row_ptr, ent_dim, row_ptr, col_local, val, label, offset=None, weight=None,
+                 storage=STORE_AUTO):
+        self.ctx = ctx
+        ent_row_ptr = _np(ent_row_ptr, np.int64)
+        self.n_entities = len(ent_row_ptr) - 1
+        ent_dim = _np(ent_dim, np.int32, self.n_entities, "ent_dim")
+        n = int(ent_row_ptr[-1]) if self.n_entities > 0 else 0
+        row_ptr = _np(row_ptr, np.int64, n + 1, "row_ptr")
+        col_local = _np(col_local, np.int32)
+        val = np.ascontiguousarray(val)
+        if val.dtype == np.float32:
+            dtype = F32
+        else:
+            val = val.astype(np.float64, copy=False)
+            dtype = F64
+        label = _np(label, np.float64, n, "labels")
+        offset = _np(offset, np.float64, n, "offsets")
+        weight = _np(weight, np.float64, n, "weights")
+        self._h = ctypes.c_void_p()
+        check(load().pml_batch_create_csr(ctx._h, self.n_entities, _ptr(ent_row_ptr), _ptr(ent_dim), _ptr(row_ptr),
+                                          _ptr(col_local), _ptr(val), dtype, storage, _ptr(label), _ptr(offset),
+                                          _ptr(weight), ctypes.byref(self._h)))
+        self.coef_ptr = np.empty(self.n_entities + 1, dtype=np.int64)
+        check(load().pml_batch_coef_ptr(self._h, _ptr(self.coef_ptr)))
+        dsh = ctypes.c_void_p()
+        check(load().pml_batch_dataset(self._h, ctypes.byref(dsh)))
+        self.dataset = Dataset(ctx, dsh)   # block-diagonal view: set_offsets, hessian_vector, ... for all entities
+        self.dataset._borrowed = True
+        self.d_total = self.dataset.d
+
+    def value_and_gradient(self, loss, coefs, want_gradient=True):
+        coefs = _np(coefs, np.float64, self.d_total, "Coefficient")
+        values = np.empty(self.n_entities, dtype=np.float64)
+        grads = np.empty(self.d_total, dtype=np.float64) if want_gradient else None
+        check(load().pml_batch_value_and_gradient(self._h, loss, _ptr(coefs), _ptr(values), _ptr(grads)))
+        return values, grads
+
+    def hessian_vector(self, loss, coefs, vs, tag=0):
+        return self.dataset.hessian_vector(loss, coefs, vs, tag=tag)
+
+    def close(self):
+        if self._h:
+            self.dataset.close()
+            load().pml_batch_destroy(self._h)
             self._h = ctypes.c_void_p()
 
     def __del__(self):

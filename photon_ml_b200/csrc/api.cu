@@ -6,6 +6,7 @@
 #include <cstring>
 #include <new>
 #include <string>
+#include <vector>
 
 #include "internal.h"
 
@@ -59,16 +60,18 @@ int upload_optional(cudaStream_t s, double **slot, const double *src, int64_t n,
     return PML_OK;
 }
 
-// nnz/row -> CSR margin-kernel variant (DESIGN.md "row pass variants")
+// nnz/row -> CSR margin-kernel variant (DESIGN.md "row pass variants").  Measured on B200
+// (profiles/): with ~50 entries per row 8 lanes per row is fastest (1.28 ms vs 1.6 / 1.3 for 4 /
+// 16 lanes and 2.1-2.4 ms for the segment-per-warp and segment-per-CTA variants), i.e. about six
+// entries per lane; very short rows go to the entry-chunked variant, which does not care about
+// row boundaries.
 int pick_variant(int64_t n, int64_t nnz)
 {
     const double mean = n > 0 ? (double)nnz / (double)n : 0.0;
-    if (std::getenv("PML_ROW_VARIANT_HEURISTIC") == nullptr) return 1;  // segment-per-CTA (entry-chunked)
-    if (mean <= 24.0) return 0;  // segment-per-warp
-    if (mean <= 48.0) return 4;
-    if (mean <= 96.0) return 8;
-    if (mean <= 256.0) return 16;
-    return 32;
+    if (mean < 3.0) return 1;  // segment-per-CTA
+    int lanes = 2;
+    while (lanes < 32 && lanes * 2 * 6.0 <= mean) lanes *= 2;
+    return lanes;
 }
 
 bool valid_loss(int loss) { return loss >= PML_LOSS_LOGISTIC && loss <= PML_LOSS_SMOOTHED_HINGE; }
@@ -124,30 +127,9 @@ int run_col_and_fixup(pml_dataset *ds, bool square, double *out, bool with_scala
     cp.out = out;
     cp.carry = ds->carry_head;
     cp.n_chunks = ds->t.n_chunks;
-    // r is gathered ~nnz/n times per element while the CSC stream is read once: ask L2 to keep r
-    const bool pin = ctx->l2_persist_bytes > 0 && ds->n > 0;
-    if (pin) {
-        cudaStreamAttrValue attr;
-        std::memset(&attr, 0, sizeof(attr));
-        size_t bytes = sizeof(double) * (size_t)ds->n;
-        if (bytes > (size_t)ctx->l2_window_max) bytes = (size_t)ctx->l2_window_max;
-        attr.accessPolicyWindow.base_ptr = ds->r;
-        attr.accessPolicyWindow.num_bytes = bytes;
-        const double ratio = (double)ctx->l2_persist_bytes / (double)bytes;
-        attr.accessPolicyWindow.hitRatio = ratio < 1.0 ? (float)ratio : 1.0f;
-        attr.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
-        attr.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
-        PML_CUDA(cudaStreamSetAttribute(s, cudaStreamAttributeAccessPolicyWindow, &attr));
-    }
     PML_TRY(run(ctx, PML_K_COL, [&] {
         return launch_seg_spmv(s, ctx->sm_count, ds->value_bytes, false, square, ds->t.chunk_entries, cp, 0);
     }));
-    if (pin) {
-        cudaStreamAttrValue attr;
-        std::memset(&attr, 0, sizeof(attr));
-        attr.accessPolicyWindow.num_bytes = 0;
-        PML_CUDA(cudaStreamSetAttribute(s, cudaStreamAttributeAccessPolicyWindow, &attr));
-    }
     PML_TRY(run(ctx, PML_K_FIXUP, [&] {
         return launch_fixup(s, ds->t.fix, ds->t.n_fix, ds->carry_head, out, nullptr, nullptr, ds->d,
                             with_scalars ? ds->partials : nullptr, ds->row_grid, write_value, true);
@@ -229,6 +211,7 @@ int vg_raw(pml_dataset *ds, int loss, const double *coef_dev, double *out_raw_de
     rp.weight = ds->weight;
     rp.r = ds->r;
     rp.partials = ds->partials;
+    rp.row_loss = ds->want_row_loss ? ds->row_loss : nullptr;
     rp.mode = MODE_VG;
     rp.loss = loss;
     PML_TRY(run_rows(ds, rp, false));
@@ -368,13 +351,6 @@ int pml_ctx_create(int device, pml_ctx **out)
         return fail(PML_ECUDA, "this library is built for sm_100a (B200) only");
     }
     PML_CUDA(cudaStreamCreate(&ctx->stream));
-    if (std::getenv("PML_L2_PERSIST") != nullptr && prop.persistingL2CacheMaxSize > 0) {
-        // opt-in: reserve the persisting share of L2 for the per-row multiplier r (see run_col_and_fixup)
-        if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, (size_t)prop.persistingL2CacheMaxSize) == cudaSuccess) {
-            ctx->l2_persist_bytes = prop.persistingL2CacheMaxSize;
-            ctx->l2_window_max = prop.accessPolicyMaxWindowSize;
-        }
-    }
     PML_CUDA(cudaMallocHost(&ctx->h_scalar, 64));
     *out = ctx;
     return PML_OK;
@@ -462,7 +438,7 @@ int pml_dataset_destroy(pml_dataset *ds)
     }
     void *ptrs[] = { ds->row_ptr, ds->col, ds->val, ds->label, ds->offset, ds->weight, ds->t.csc_row, ds->t.csc_val,
                      ds->t.nzcol_ptr, ds->t.nzcol_id, ds->t.rank, ds->t.chunk_col_lo, ds->t.fix, ds->rs.nzrow_id, ds->rs.chunk_lo,
-                     ds->rs.fix, ds->za, ds->zb, ds->carry_row, ds->carry_row2, ds->factors, ds->shifts, ds->r,
+                     ds->rs.fix, ds->za, ds->zb, ds->carry_row, ds->carry_row2, ds->row_loss, ds->factors, ds->shifts, ds->r,
                      ds->dcache, ds->partials, ds->carry_head, ds->raw, ds->vec, ds->shift_partials, ds->io_a, ds->io_b,
                      ds->io_n };
     for (void *p : ptrs)
@@ -854,6 +830,158 @@ int pml_scores(pml_dataset *ds, const double *coef, double *out_scores)
     rp.mode = MODE_SCORE;
     PML_TRY(run_rows(ds, rp, false));
     if (ds->n > 0) PML_CUDA(cudaMemcpyAsync(out_scores, ds->r, sizeof(double) * (size_t)ds->n, cudaMemcpyDeviceToHost, s));
+    PML_CUDA(cudaStreamSynchronize(s));
+    return PML_OK;
+}
+
+// ---- batched per-entity problems (random effects) -------------------------------------------
+int pml_batch_create_csr(pml_ctx *ctx, int64_t n_entities, const int64_t *ent_row_ptr, const int32_t *ent_dim,
+                         const int64_t *row_ptr, const int32_t *col_local, const void *values, int values_dtype,
+                         int storage, const double *labels, const double *offsets, const double *weights,
+                         pml_batch **out)
+{
+    if (!ctx || !out) return fail(PML_EINVAL, "null argument");
+    *out = nullptr;
+    if (n_entities < 0) return fail(PML_EINVAL, "negative size");
+    if (n_entities > 0 && (!ent_row_ptr || !ent_dim)) return fail(PML_EINVAL, "ent_row_ptr and ent_dim are required");
+    if (n_entities > 0 && ent_row_ptr[0] != 0) return fail(PML_EINVAL, "ent_row_ptr must start at 0");
+    const int64_t n = n_entities > 0 ? ent_row_ptr[n_entities] : 0;
+    if (n > 0 && (!row_ptr || !labels)) return fail(PML_EINVAL, "row_ptr and labels are required");
+    const int64_t nnz = n > 0 ? row_ptr[n] : 0;
+    if (values_dtype != PML_F32 && values_dtype != PML_F64) return fail(PML_EINVAL, "values_dtype must be PML_F32 or PML_F64");
+    std::vector<int64_t> coef_ptr((size_t)n_entities + 1, 0);
+    for (int64_t e = 0; e < n_entities; ++e) {
+        if (ent_dim[e] < 0) return fail(PML_EINVAL, "negative entity dimension");
+        if (ent_row_ptr[e + 1] < ent_row_ptr[e]) return fail(PML_EINVAL, "ent_row_ptr must be non-decreasing");
+        coef_ptr[(size_t)e + 1] = coef_ptr[(size_t)e] + ent_dim[e];
+    }
+    const int64_t d_total = coef_ptr[(size_t)n_entities];
+    if (d_total > 2000000000LL) return fail(PML_EINVAL, "sum of entity dimensions exceeds 2e9; shard entities over more devices");
+
+    const int vb = values_dtype == PML_F32 ? 4 : 8;
+    TmpDev t_rp, t_col, t_val, t_lab, t_off, t_wt, t_erp, t_cp, t_dim, t_bad;
+    pml_batch *b = new (std::nothrow) pml_batch();
+    if (!b) return fail(PML_ENOMEM, "host allocation failed");
+    struct Cleanup {
+        pml_batch *b;
+        ~Cleanup() { if (b) pml_batch_destroy(b); }
+    } cleanup{ b };
+    b->n_entities = n_entities;
+    b->coef_ptr = coef_ptr;
+    {
+        Guard g(ctx);
+        PML_CUDA(cudaSetDevice(ctx->device));
+        cudaStream_t s = ctx->stream;
+        PML_CUDA(cudaMalloc(&t_rp.p, sizeof(int64_t) * (size_t)(n + 1)));
+        PML_CUDA(cudaMalloc(&t_col.p, sizeof(int32_t) * (size_t)(nnz + 1)));
+        PML_CUDA(cudaMalloc(&t_val.p, (size_t)vb * (size_t)(nnz + 1)));
+        PML_CUDA(cudaMalloc(&t_lab.p, sizeof(double) * (size_t)(n + 1)));
+        PML_CUDA(cudaMalloc(&t_cp.p, sizeof(int64_t) * (size_t)(n_entities + 1)));
+        PML_CUDA(cudaMalloc(&t_dim.p, sizeof(int32_t) * (size_t)(n_entities + 1)));
+        PML_CUDA(cudaMalloc(&t_bad.p, sizeof(unsigned long long)));
+        PML_CUDA(cudaMalloc((void **)&b->ent_row_ptr, sizeof(int64_t) * (size_t)(n_entities + 1)));
+        PML_CUDA(cudaMalloc((void **)&b->ent_values, sizeof(double) * (size_t)(n_entities + 1)));
+        PML_CUDA(cudaMemsetAsync(t_bad.p, 0, sizeof(unsigned long long), s));
+        if (n_entities > 0) {
+            PML_CUDA(cudaMemcpyAsync(b->ent_row_ptr, ent_row_ptr, sizeof(int64_t) * (size_t)(n_entities + 1), cudaMemcpyHostToDevice, s));
+            PML_CUDA(cudaMemcpyAsync(t_cp.p, coef_ptr.data(), sizeof(int64_t) * (size_t)(n_entities + 1), cudaMemcpyHostToDevice, s));
+            PML_CUDA(cudaMemcpyAsync(t_dim.p, ent_dim, sizeof(int32_t) * (size_t)n_entities, cudaMemcpyHostToDevice, s));
+        } else {
+            PML_CUDA(cudaMemsetAsync(b->ent_row_ptr, 0, sizeof(int64_t), s));
+        }
+        if (n > 0) {
+            // row_ptr must be valid before it is dereferenced on the device
+            for (int64_t i = 0; i < n; ++i)
+                if (row_ptr[i + 1] < row_ptr[i] || row_ptr[i] < 0) return fail(PML_EINVAL, "row_ptr must start at 0 and be non-decreasing");
+            if (row_ptr[0] != 0) return fail(PML_EINVAL, "row_ptr must start at 0 and be non-decreasing");
+            PML_CUDA(cudaMemcpyAsync(t_rp.p, row_ptr, sizeof(int64_t) * (size_t)(n + 1), cudaMemcpyHostToDevice, s));
+            PML_CUDA(cudaMemcpyAsync(t_lab.p, labels, sizeof(double) * (size_t)n, cudaMemcpyHostToDevice, s));
+        }
+        if (nnz > 0) {
+            if (!col_local || !values) return fail(PML_EINVAL, "col_idx and values are required");
+            PML_CUDA(cudaMemcpyAsync(t_col.p, col_local, sizeof(int32_t) * (size_t)nnz, cudaMemcpyHostToDevice, s));
+            PML_CUDA(cudaMemcpyAsync(t_val.p, values, (size_t)vb * (size_t)nnz, cudaMemcpyHostToDevice, s));
+        }
+        if (offsets && n > 0) {
+            PML_CUDA(cudaMalloc(&t_off.p, sizeof(double) * (size_t)n));
+            PML_CUDA(cudaMemcpyAsync(t_off.p, offsets, sizeof(double) * (size_t)n, cudaMemcpyHostToDevice, s));
+        }
+        if (weights && n > 0) {
+            PML_CUDA(cudaMalloc(&t_wt.p, sizeof(double) * (size_t)n));
+            PML_CUDA(cudaMemcpyAsync(t_wt.p, weights, sizeof(double) * (size_t)n, cudaMemcpyHostToDevice, s));
+        }
+        // local column j of entity e -> global column coef_ptr[e] + j (checks j < ent_dim[e])
+        if (nnz > 0) {
+            PML_TRY(count(ctx, launch_globalize_cols(s, n_entities, b->ent_row_ptr, (const int64_t *)t_cp.p,
+                                                     (const int32_t *)t_dim.p, (const int64_t *)t_rp.p, (int32_t *)t_col.p,
+                                                     (unsigned long long *)t_bad.p)));
+        }
+        unsigned long long bad = 0;
+        PML_CUDA(cudaMemcpyAsync(&bad, t_bad.p, sizeof(bad), cudaMemcpyDeviceToHost, s));
+        PML_CUDA(cudaStreamSynchronize(s));
+        if (bad) return fail(PML_EINVAL, "local column index outside [0, ent_dim[e]): " + std::to_string(bad) + " entries");
+    }
+    PML_TRY(pml_dataset_create_csr_dev(ctx, n, (int32_t)d_total, (const int64_t *)t_rp.p, (const int32_t *)t_col.p, t_val.p,
+                                       values_dtype, storage, (const double *)t_lab.p, (const double *)t_off.p,
+                                       (const double *)t_wt.p, &b->ds));
+    {
+        Guard g(ctx);
+        PML_TRY(dev_alloc(&b->ds->row_loss, (size_t)n, &b->ds->bytes));
+    }
+    cleanup.b = nullptr;
+    *out = b;
+    return PML_OK;
+}
+
+int pml_batch_destroy(pml_batch *b)
+{
+    if (!b) return PML_OK;
+    if (b->ds) {
+        cudaSetDevice(b->ds->ctx->device);
+        cudaStreamSynchronize(b->ds->ctx->stream);
+    }
+    if (b->ent_row_ptr) cudaFree(b->ent_row_ptr);
+    if (b->ent_values) cudaFree(b->ent_values);
+    if (b->ds) pml_dataset_destroy(b->ds);
+    delete b;
+    return PML_OK;
+}
+
+int pml_batch_dataset(pml_batch *b, pml_dataset **out)
+{
+    if (!b || !out) return fail(PML_EINVAL, "null argument");
+    *out = b->ds;
+    return PML_OK;
+}
+
+int pml_batch_coef_ptr(pml_batch *b, int64_t *out)
+{
+    if (!b || !out) return fail(PML_EINVAL, "null argument");
+    std::memcpy(out, b->coef_ptr.data(), sizeof(int64_t) * b->coef_ptr.size());
+    return PML_OK;
+}
+
+int pml_batch_value_and_gradient(pml_batch *b, int loss, const double *coefs, double *out_values, double *out_grads)
+{
+    if (!b || !b->ds) return fail(PML_EINVAL, "null batch handle");
+    pml_dataset *ds = b->ds;
+    if (!valid_loss(loss)) return fail(PML_EINVAL, "unknown loss");
+    if ((!coefs && ds->d > 0) || (!out_values && b->n_entities > 0)) return fail(PML_EINVAL, "null buffer");
+    Guard g(ds->ctx);
+    PML_CUDA(cudaSetDevice(ds->ctx->device));
+    cudaStream_t s = ds->ctx->stream;
+    const size_t db = sizeof(double) * (size_t)ds->d;
+    if (ds->d > 0) PML_CUDA(cudaMemcpyAsync(ds->io_a, coefs, db, cudaMemcpyHostToDevice, s));
+    ds->want_row_loss = true;
+    const int rc = vg_raw(ds, loss, ds->io_a, ds->raw);
+    ds->want_row_loss = false;
+    PML_TRY(rc);
+    PML_TRY(run(ds->ctx, PML_K_EPILOGUE, [&] {
+        return launch_entity_values(s, b->n_entities, b->ent_row_ptr, ds->row_loss, b->ent_values);
+    }));
+    if (out_grads && ds->d > 0) PML_CUDA(cudaMemcpyAsync(out_grads, ds->raw, db, cudaMemcpyDeviceToHost, s));
+    if (b->n_entities > 0)
+        PML_CUDA(cudaMemcpyAsync(out_values, b->ent_values, sizeof(double) * (size_t)b->n_entities, cudaMemcpyDeviceToHost, s));
     PML_CUDA(cudaStreamSynchronize(s));
     return PML_OK;
 }

@@ -63,6 +63,7 @@ struct RowPassParams {
     double *r;                // n: per-row multiplier consumed by the transpose kernel
     double *dcache;           // n: wt*l''(z) written (HV_COLD) or read (HV_CACHED)
     double *partials;         // 2 * gridDim.x: per-CTA (F, P)
+    double *row_loss;         // n or null: wt_i * l_i per row (batched per-entity values)
     int n_hot;                // leading entries of vec staged in shared memory (set by the launcher)
     int mode;
     int loss;
@@ -104,6 +105,11 @@ int launch_fixup(cudaStream_t s, const FixEntry *fix, int n_fix, const double *c
 int launch_finalize(cudaStream_t s, int d, const double *raw, const double *factors, const double *shifts,
                     double *out_value, double *out_vec);
 
+int launch_globalize_cols(cudaStream_t s, int64_t n_entities, const int64_t *ent_row_ptr, const int64_t *coef_ptr,
+                          const int32_t *ent_dim, const int64_t *row_ptr, int32_t *col, unsigned long long *bad);
+int launch_entity_values(cudaStream_t s, int64_t n_entities, const int64_t *ent_row_ptr, const double *row_loss,
+                         double *out);
+
 // pack.cu: builds the CSC copy and its chunk metadata on the device
 struct Packed;
 struct RowSide;
@@ -144,6 +150,14 @@ struct RowSide {
 
 }  // namespace pml
 
+struct pml_batch {
+    pml_dataset *ds = nullptr;      // the block-diagonal data set (owned)
+    int64_t n_entities = 0;
+    int64_t *ent_row_ptr = nullptr; // device, E+1
+    double *ent_values = nullptr;   // device, E
+    std::vector<int64_t> coef_ptr;  // host, E+1
+};
+
 struct pml_span {
     int kind;
     cudaEvent_t a, b;
@@ -157,8 +171,6 @@ struct pml_ctx {
     cudaStream_t stream = nullptr;
     std::mutex mu;
     int64_t launches = 0;
-    int64_t l2_persist_bytes = 0;  // > 0: persisting L2 carve-out reserved for r
-    int64_t l2_window_max = 0;
     // pinned staging for scalars
     double *h_scalar = nullptr;
 };
@@ -191,6 +203,8 @@ struct pml_dataset {
     double *shift_partials = nullptr;  // 2*MAX_PARTIALS
     double *io_a = nullptr, *io_b = nullptr;  // d+2 each: staging of host coef / v / outputs
     double *io_n = nullptr;        // n, lazily: scores output staging
+    double *row_loss = nullptr;    // n, lazily: per-row wt*l for per-entity objective values (pml_batch)
+    bool want_row_loss = false;
     uint64_t cached_tag = 0;
     int cached_loss = -1;
     bool cache_valid = false;

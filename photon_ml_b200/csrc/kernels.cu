@@ -239,7 +239,9 @@ __global__ void __launch_bounds__(R_THREADS, R_THREADS >= 1024 ? 1 : 1280 / R_TH
                 loss_and_dz(p.loss, z, __ldcs(p.label + my_row), l, dl);
                 const double wdl = __dmul_rn(wt, dl);
                 p.r[my_row] = wdl;
-                accF += __dmul_rn(wt, l);
+                const double wl = __dmul_rn(wt, l);
+                if (p.row_loss) p.row_loss[my_row] = wl;
+                accF += wl;
                 accP += wdl;
                 break;
             }
@@ -670,7 +672,9 @@ __global__ void __launch_bounds__(E_THREADS) row_epilogue_kernel(const RowPassPa
             loss_and_dz(p.loss, z, __ldcs(p.label + i), l, dl);
             const double wdl = __dmul_rn(wt, dl);
             p.r[i] = wdl;
-            accF += __dmul_rn(wt, l);
+            const double wl = __dmul_rn(wt, l);
+            if (p.row_loss) p.row_loss[i] = wl;
+            accF += wl;
             accP += wdl;
             break;
         }
@@ -799,6 +803,71 @@ int launch_finalize(cudaStream_t s, int d, const double *raw, const double *fact
     if (grid < 1) grid = 1;
     if (grid > 2048) grid = 2048;
     finalize_kernel<<<grid, 256, 0, s>>>(d, raw, factors, shifts, out_value, out_vec);
+    return cudaGetLastError() == cudaSuccess ? 1 : -1;
+}
+
+// ------------------------------------------------------------------------------------------
+// Batched per-entity problems (SingleNodeGLMLossFunction over RandomEffectDataSet.activeData,
+// api/algorithm/RandomEffectCoordinate.scala:108-119).  The E local problems are evaluated as ONE
+// block-diagonal problem: entity e's local column j becomes global column coef_ptr[e] + j, so
+// the row/column passes above produce every entity's gradient in one go; what is left is the
+// per-entity objective value, a segmented sum of the per-row wt*l over each entity's rows.
+// ------------------------------------------------------------------------------------------
+__global__ void globalize_cols_kernel(int64_t n_entities, const int64_t *__restrict__ ent_row_ptr,
+                                      const int64_t *__restrict__ coef_ptr, const int32_t *__restrict__ ent_dim,
+                                      const int64_t *__restrict__ row_ptr, int32_t *__restrict__ col,
+                                      unsigned long long *__restrict__ bad)
+{
+    // one warp per entity; lanes stride over the entity's entries
+    const int lane = threadIdx.x & 31;
+    int64_t e = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (; e < n_entities; e += nw) {
+        const int64_t a = row_ptr[ent_row_ptr[e]], b = row_ptr[ent_row_ptr[e + 1]];
+        const int64_t shift = coef_ptr[e];
+        const int32_t dim = ent_dim[e];
+        int wrong = 0;
+        for (int64_t k = a + lane; k < b; k += 32) {
+            const int32_t c = col[k];
+            if (c < 0 || c >= dim) ++wrong;
+            col[k] = (int32_t)(shift + c);
+        }
+        if (wrong) atomicAdd(bad, (unsigned long long)wrong);
+    }
+}
+
+int launch_globalize_cols(cudaStream_t s, int64_t n_entities, const int64_t *ent_row_ptr, const int64_t *coef_ptr,
+                          const int32_t *ent_dim, const int64_t *row_ptr, int32_t *col, unsigned long long *bad)
+{
+    if (n_entities <= 0) return 0;
+    int64_t grid = (n_entities * 32 + 255) / 256;
+    if (grid > 148 * 16) grid = 148 * 16;
+    globalize_cols_kernel<<<(int)grid, 256, 0, s>>>(n_entities, ent_row_ptr, coef_ptr, ent_dim, row_ptr, col, bad);
+    return cudaGetLastError() == cudaSuccess ? 1 : -1;
+}
+
+// value_e = sum over the entity's rows, lanes striding rows then a fixed shuffle tree
+__global__ void entity_values_kernel(int64_t n_entities, const int64_t *__restrict__ ent_row_ptr,
+                                     const double *__restrict__ row_loss, double *__restrict__ out)
+{
+    const int lane = threadIdx.x & 31;
+    int64_t e = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (; e < n_entities; e += nw) {
+        double s = 0.0;
+        for (int64_t i = ent_row_ptr[e] + lane; i < ent_row_ptr[e + 1]; i += 32) s += row_loss[i];
+        s = warp_sum(s);
+        if (lane == 0) out[e] = s;
+    }
+}
+
+int launch_entity_values(cudaStream_t s, int64_t n_entities, const int64_t *ent_row_ptr, const double *row_loss,
+                         double *out)
+{
+    if (n_entities <= 0) return 0;
+    int64_t grid = (n_entities * 32 + 255) / 256;
+    if (grid > 148 * 16) grid = 148 * 16;
+    entity_values_kernel<<<(int)grid, 256, 0, s>>>(n_entities, ent_row_ptr, row_loss, out);
     return cudaGetLastError() == cudaSuccess ? 1 : -1;
 }
 

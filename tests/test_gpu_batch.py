@@ -1,0 +1,90 @@
+"""Batched per-entity (random-effect) evaluation against the oracle run entity by entity --
+what RandomEffectCoordinate.updateModel does with one SingleNodeGLMLossFunction per entity
+(api/algorithm/RandomEffectCoordinate.scala:108-119).  `-m gpu`."""
+import numpy as np
+import pytest
+
+import oracle
+from tests import util
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-11
+
+
+def _entities(rng, n_entities, max_dim, mean_rows, skew_rows=True):
+    """Concatenated per-entity CSR in local column spaces; power-law row counts, some empty entities."""
+    if skew_rows:
+        rows = np.minimum((rng.pareto(1.2, size=n_entities) * mean_rows / 3 + 1).astype(np.int64), 40 * mean_rows)
+    else:
+        rows = rng.integers(1, 2 * mean_rows, size=n_entities)
+    rows[rng.random(n_entities) < 0.03] = 0          # entities with no active rows
+    dims = rng.integers(1, max_dim + 1, size=n_entities).astype(np.int32)
+    ent_row_ptr = np.concatenate([[0], np.cumsum(rows)]).astype(np.int64)
+    row_ptr, col, val = [0], [], []
+    for e in range(n_entities):
+        d_e = int(dims[e])
+        for _ in range(int(rows[e])):
+            k = int(rng.integers(0, min(d_e, 8) + 1))   # rows may be empty too
+            c = np.sort(rng.choice(d_e, size=k, replace=False)) if k else np.zeros(0, dtype=np.int64)
+            col.extend(c.tolist())
+            val.extend((rng.integers(1, 9, size=k) / 4.0).tolist())
+            row_ptr.append(len(col))
+    n = int(ent_row_ptr[-1])
+    return (ent_row_ptr, dims, np.asarray(row_ptr, np.int64), np.asarray(col, np.int32), np.asarray(val, np.float64), n)
+
+
+@pytest.mark.parametrize("loss", [oracle.LOGISTIC, oracle.POISSON, oracle.SQUARED])
+def test_batch_matches_per_entity_oracle(loss):
+    import photon_ml_b200 as pml
+    rng = np.random.default_rng(5 + loss)
+    ent_row_ptr, dims, row_ptr, col, val, n = _entities(rng, 600, 24, 12)
+    label = util.labels_for(rng, loss, n)
+    offset = rng.normal(scale=0.2, size=n)
+    weight = rng.uniform(0.5, 2.0, size=n)
+    ctx = pml.Context(0)
+    batch = pml.Batch(ctx, ent_row_ptr, dims, row_ptr, col, val, label, offset, weight)
+    assert batch.d_total == int(dims.sum())
+    coefs = rng.normal(scale=0.3, size=batch.d_total)
+    vs = rng.normal(size=batch.d_total)
+    values, grads = batch.value_and_gradient(loss, coefs)
+    hvs = batch.hessian_vector(loss, coefs, vs)
+    for e in range(len(dims)):
+        lo, hi = int(ent_row_ptr[e]), int(ent_row_ptr[e + 1])
+        a, b = int(batch.coef_ptr[e]), int(batch.coef_ptr[e + 1])
+        sl = slice(int(row_ptr[lo]), int(row_ptr[hi]))
+        local = oracle.Data(hi - lo, int(dims[e]), row_ptr[lo:hi + 1] - row_ptr[lo], col[sl], val[sl], label[lo:hi],
+                            offset[lo:hi], weight[lo:hi])
+        f_ref, g_ref = oracle.value_and_gradient(local, loss, coefs[a:b])
+        assert abs(values[e] - f_ref) <= TOL * max(abs(f_ref), 1e-300), (e, values[e], f_ref)
+        assert util.rel_err(grads[a:b], g_ref) <= TOL, e
+        assert util.rel_err(hvs[a:b], oracle.hessian_vector(local, loss, coefs[a:b], vs[a:b])) <= TOL, e
+    # residual offsets are refreshed through the underlying data set (Coordinate.scala:59-62)
+    off2 = rng.normal(size=n)
+    batch.dataset.set_offsets(off2)
+    values2, _ = batch.value_and_gradient(loss, coefs, want_gradient=False)
+    e = int(np.argmax(np.diff(ent_row_ptr)))
+    lo, hi = int(ent_row_ptr[e]), int(ent_row_ptr[e + 1])
+    sl = slice(int(row_ptr[lo]), int(row_ptr[hi]))
+    local = oracle.Data(hi - lo, int(dims[e]), row_ptr[lo:hi + 1] - row_ptr[lo], col[sl], val[sl], label[lo:hi],
+                        off2[lo:hi], weight[lo:hi])
+    a, b = int(batch.coef_ptr[e]), int(batch.coef_ptr[e + 1])
+    f_ref, _ = oracle.value_and_gradient(local, loss, coefs[a:b])
+    assert abs(values2[e] - f_ref) <= TOL * abs(f_ref)
+    batch.close()
+    ctx.close()
+
+
+def test_batch_rejects_bad_local_columns():
+    import photon_ml_b200 as pml
+    ctx = pml.Context(0)
+    ent_row_ptr = np.array([0, 2, 3], np.int64)
+    dims = np.array([2, 3], np.int32)
+    row_ptr = np.array([0, 1, 2, 3], np.int64)
+    with pytest.raises(pml.IllegalArgumentError):   # column 2 does not exist in entity 0 (d_e = 2)
+        pml.Batch(ctx, ent_row_ptr, dims, row_ptr, np.array([0, 2, 1], np.int32), np.ones(3), np.zeros(3))
+    b = pml.Batch(ctx, ent_row_ptr, dims, row_ptr, np.array([0, 1, 2], np.int32), np.ones(3), np.zeros(3))
+    values, grads = b.value_and_gradient(oracle.LOGISTIC, np.zeros(5))
+    assert np.allclose(values, [2 * np.log(2.0), np.log(2.0)], rtol=1e-14)
+    assert np.allclose(grads, [0.5, 0.5, 0.0, 0.0, 0.5], rtol=1e-14)
+    b.close()
+    ctx.close()
