@@ -1,0 +1,163 @@
+"""Host-side mirror of the reference's objective-function interface, backed by the CUDA library.
+
+Same names, argument meaning and error behaviour as
+  lib/function/ObjectiveFunction.scala:25-73, DiffFunction.scala:25-52, TwiceDiffFunction.scala:25-52,
+  api/function/glm/DistributedGLMLossFunction.scala:49-171, SingleNodeGLMLossFunction.scala:42-153,
+  api/function/svm/DistributedSmoothedHingeLossFunction.scala:84-103,
+  lib/function/L2Regularization.scala:25-184, lib/normalization/NormalizationContext.scala:39-111
+(paths under photon-lib / photon-api src/main/scala/com/linkedin/photon/ml).  `Data` is a packed
+photon_ml_b200.Dataset instead of an RDD / Iterable of LabeledPoint; `Coefficients` is a numpy
+vector.  In a JVM deployment these classes are the Scala shim of INTEGRATION.md; here they let the
+tests and the optimizer drivers read like the reference's.
+"""
+import numpy as np
+
+from . import abi
+
+
+class NormalizationContext:
+    """(factors, shifts, interceptId); NormalizationContext.scala:39-47."""
+
+    def __init__(self, factors=None, shifts=None, interceptId=None):
+        if shifts is not None and interceptId is None:
+            raise abi.IllegalArgumentError("Shift without intercept is illegal.")
+        if factors is not None and shifts is not None and len(factors) != len(shifts):
+            raise abi.IllegalArgumentError("Factors and shifts vectors should have the same size")
+        self.factors = None if factors is None else np.asarray(factors, dtype=np.float64)
+        self.shifts = None if shifts is None else np.asarray(shifts, dtype=np.float64)
+        self.interceptId = interceptId
+
+    def modelToOriginalSpace(self, coef):   # :64-80
+        out = np.array(coef, dtype=np.float64)
+        if self.factors is not None:
+            out = out * self.factors
+        if self.shifts is not None:
+            out[self.interceptId] -= out.dot(self.shifts)
+        return out
+
+    def modelToTransformedSpace(self, coef):  # :97-111
+        out = np.array(coef, dtype=np.float64)
+        if self.shifts is not None:
+            out[self.interceptId] += out.dot(self.shifts)
+        if self.factors is not None:
+            out = out / self.factors
+        return out
+
+
+def NoNormalization():
+    return NormalizationContext(None, None, None)
+
+
+class _NativeObjective:
+    """value / gradient / calculate (+ hessianVector / hessianDiagonal) on a packed Dataset."""
+
+    twice_differentiable = True
+
+    def __init__(self, loss):
+        self.loss = loss
+        self._norm_applied = {}   # dataset id -> NormalizationContext currently set on it
+        self._next_tag = 1
+        self._tags = {}
+
+    # the reference passes the context on every call; the packed data set keeps it between calls
+    def _apply(self, data, ctx):
+        if self._norm_applied.get(id(data)) is not ctx:
+            data.set_normalization(ctx.factors, ctx.shifts, ctx.interceptId)
+            self._norm_applied[id(data)] = ctx
+
+    def domainDimension(self, data):
+        return data.d
+
+    def value(self, data, coefficients, normalizationContext):
+        return self.calculate(data, coefficients, normalizationContext, want_gradient=False)[0]
+
+    def gradient(self, data, coefficients, normalizationContext):
+        return self.calculate(data, coefficients, normalizationContext)[1]
+
+    def calculate(self, data, coefficients, normalizationContext, want_gradient=True):
+        self._apply(data, normalizationContext)
+        return data.value_and_gradient(self.loss, coefficients, want_gradient=want_gradient)
+
+    def hessianVector(self, data, coefficients, multiplyVector, normalizationContext):
+        if not self.twice_differentiable:
+            raise abi.IllegalArgumentError("not a TwiceDiffFunction")
+        self._apply(data, normalizationContext)
+        # the coefficient vector's identity is the cache tag (TRON's CG loop keeps passing the same one)
+        key = id(coefficients)
+        if self._tags.get("key") != key or not np.array_equal(self._tags.get("copy"), coefficients):
+            self._tags = {"key": key, "copy": np.array(coefficients, copy=True), "tag": self._next_tag}
+            self._next_tag += 1
+        return data.hessian_vector(self.loss, coefficients, multiplyVector, tag=self._tags["tag"])
+
+    def hessianDiagonal(self, data, coefficients):
+        if not self.twice_differentiable:
+            raise abi.IllegalArgumentError("not a TwiceDiffFunction")
+        return data.hessian_diagonal(self.loss, coefficients)
+
+
+class L2RegularizationMixin:
+    """L2Regularization / L2RegularizationDiff / L2RegularizationTwiceDiff, stacked on the host side
+    exactly as in the reference (the kernels return the unregularised sums)."""
+
+    l2RegWeight = 0.0
+
+    def calculate(self, data, coefficients, normalizationContext, want_gradient=True):
+        value, grad = super().calculate(data, coefficients, normalizationContext, want_gradient)
+        c = np.asarray(coefficients, dtype=np.float64)
+        value = value + self.l2RegWeight * c.dot(c) / 2          # :69-70
+        if grad is not None:
+            grad = grad + c * self.l2RegWeight                    # :133
+        return value, grad
+
+    def hessianVector(self, data, coefficients, multiplyVector, normalizationContext):
+        hv = super().hessianVector(data, coefficients, multiplyVector, normalizationContext)
+        return hv + np.asarray(multiplyVector, dtype=np.float64) * self.l2RegWeight   # :151-157,176
+
+    def hessianDiagonal(self, data, coefficients):
+        return super().hessianDiagonal(data, coefficients) + self.l2RegWeight          # :167-168,183
+
+
+class DistributedGLMLossFunction(_NativeObjective):
+    """api/function/glm/DistributedGLMLossFunction.scala; `loss` is one of abi.LOGISTIC / POISSON / SQUARED."""
+
+    def __init__(self, loss, treeAggregateDepth=1):
+        if treeAggregateDepth <= 0:   # DistributedObjectiveFunction.scala:39
+            raise abi.IllegalArgumentError("Tree aggregate depth must be greater than 0: %d" % treeAggregateDepth)
+        super().__init__(loss)
+
+    @staticmethod
+    def create(loss, l2RegWeight=None, treeAggregateDepth=1):
+        """The factory of :151-170: L2 is mixed in only when the regularization type is L2."""
+        if l2RegWeight is None:
+            return DistributedGLMLossFunction(loss, treeAggregateDepth)
+        obj = _DistributedGLMLossFunctionWithL2(loss, treeAggregateDepth)
+        obj.l2RegWeight = float(l2RegWeight)
+        return obj
+
+
+class _DistributedGLMLossFunctionWithL2(L2RegularizationMixin, DistributedGLMLossFunction):
+    pass
+
+
+SingleNodeGLMLossFunction = DistributedGLMLossFunction   # same contract over a local data set
+
+
+class DistributedSmoothedHingeLossFunction(_NativeObjective):
+    """api/function/svm/DistributedSmoothedHingeLossFunction.scala: DiffFunction only; ignores normalization."""
+
+    twice_differentiable = False
+
+    def __init__(self, treeAggregateDepth=1):
+        super().__init__(abi.SMOOTHED_HINGE)
+
+    @staticmethod
+    def create(l2RegWeight=None, treeAggregateDepth=1):
+        if l2RegWeight is None:
+            return DistributedSmoothedHingeLossFunction(treeAggregateDepth)
+        obj = _HingeWithL2(treeAggregateDepth)
+        obj.l2RegWeight = float(l2RegWeight)
+        return obj
+
+
+class _HingeWithL2(L2RegularizationMixin, DistributedSmoothedHingeLossFunction):
+    pass
