@@ -278,7 +278,8 @@ def run_ours(args):
         row_bytes, col_bytes = kernel_bytes(info, 0, 0)
         row_ms = profile["row_pass"][0] / max(1, profile["row_pass"][1])
         col_ms = profile["col_pass"][0] / max(1, profile["col_pass"][1])
-        dominant = "col_pass_kernel" if col_ms >= row_ms else "row_pass_kernel"
+        dominant = ("seg_spmv_kernel (CSC pass, X^T r)" if col_ms >= row_ms
+                    else "row_pass_kernel<%d lanes/row> (CSR pass, X w + pointwise)" % info.margin_variant)
         dom_bytes, dom_ms = (col_bytes, col_ms) if col_ms >= row_ms else (row_bytes, row_ms)
         achieved = dom_bytes / (dom_ms * 1e-3) / 1e9
         ms_per_step = ms / args.steps
@@ -324,11 +325,53 @@ def run_ours(args):
         }
         if world == 1 and not args.no_cpu_baseline:
             out["cpu_baseline"] = cpu_baseline(steps=10, warmup=2)
+        if world == 1 and not args.no_convergence:
+            out["convergence"] = convergence(ctx, ds, d)
         print(json.dumps(out))
     ds.close()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def convergence(ctx, ds, d):
+    """Metric (3): optimizer wall time to convergence, driven through the host-buffer C ABI.
+    TRON on this run's configs[1] data (Hessian-vector path) and LBFGS on configs[0] (a1a-shaped: the
+    first 1605 rows of the reference's a9a fixture), the latter also on the CPU oracle under the same
+    driver so that iteration counts can be compared."""
+    import oracle
+    import photon_ml_b200 as pml
+    from photon_ml_b200.function import DistributedGLMLossFunction, NoNormalization
+    from photon_ml_b200.optimization import LBFGS, TRON
+    from tests import util
+    from tests.objectives import OracleGLMObjective
+    out = {}
+    t0 = time.perf_counter()
+    tron = TRON(NoNormalization())
+    _, f = tron.optimize(DistributedGLMLossFunction.create(LOSS_POISSON, l2RegWeight=1.0), np.zeros(d), ds)
+    out["tron_configs1_poisson_l2_1"] = {
+        "wall_s": time.perf_counter() - t0, "iterations": tron.currentState.iter, "reason": tron.convergenceReason,
+        "value_gradient_evals": tron.evaluations, "hessian_vector_evals": tron.hessian_vector_evaluations, "objective": f}
+    n1, d1, row_ptr, col, val, label = util.read_libsvm(os.path.join(util.GOLDEN, "a9a_1605.libsvm"), d=123,
+                                                        add_intercept=True)
+    small = pml.Dataset.from_csr(ctx, n1, d1, row_ptr, col, val, label)
+    ref = oracle.Data(n1, d1, row_ptr, col, val, label)
+    runs = []
+    for lam in (100.0, 10.0, 1.0, 0.1):   # README.md:252 regularization weights
+        g, c = LBFGS(NoNormalization(), maxNumIterations=50), LBFGS(NoNormalization(), maxNumIterations=50)
+        t0 = time.perf_counter()
+        wg, fg = g.optimize(DistributedGLMLossFunction.create(pml.LOGISTIC, l2RegWeight=lam), np.zeros(d1), small)
+        tg = time.perf_counter() - t0
+        t0 = time.perf_counter()
+        wc, fc = c.optimize(OracleGLMObjective(oracle.LOGISTIC, l2RegWeight=lam), np.zeros(d1), ref)
+        tc = time.perf_counter() - t0
+        runs.append({"lambda": lam, "gpu_wall_s": tg, "cpu_oracle_wall_s": tc, "gpu_iterations": g.currentState.iter,
+                     "cpu_iterations": c.currentState.iter, "gpu_evals": g.evaluations, "cpu_evals": c.evaluations,
+                     "us_per_eval_gpu": 1e6 * tg / g.evaluations,
+                     "max_coef_diff": float(np.max(np.abs(wg - wc))), "objective": fg})
+    out["lbfgs_configs0_a1a_logistic_l2"] = runs
+    small.close()
+    return out
 
 
 def cpu_sample():
@@ -391,6 +434,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-convergence", action="store_true")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = 3
