@@ -458,24 +458,24 @@ __device__ __forceinline__ void seg_load(SegRegs<VT, ITEMS> &g, const int32_t *_
 }
 
 // Reduces one chunk held in `cur`.  FULL = every thread owns ITEMS live entries (all chunks but
-// possibly the last), which removes the per-entry bounds tests from the common path.
+// possibly the last), which keeps the bounds tests out of the persistent loop.
 template <typename VT, int ITEMS, bool TWO, bool SQUARE, bool HOT, bool FULL>
 __device__ __forceinline__ void seg_chunk(const SegParams &p, const SegRegs<VT, ITEMS> &cur, int c, int mine_cnt,
                                           const double *hot, SegScan<TWO> *wagg_c)
 {
-    constexpr int WARPS = S_THREADS / 32;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const double *__restrict__ table = p.table;
     const int n_hot = p.n_hot;
 
-    // ---- look up and multiply ----
+    // ---- look up and multiply; collect the run-start flags ----
     double pr[ITEMS], pr2[TWO ? ITEMS : 1];
     unsigned mask = 0;
 #pragma unroll
     for (int i = 0; i < ITEMS; ++i) {
         const bool live = FULL || i < mine_cnt;
-        if (live && cur.idx[i] < 0) mask |= 1u << i;
-        const int32_t k = live ? (cur.idx[i] & 0x7fffffff) : 0;
+        const int32_t raw = live ? cur.idx[i] : 0;
+        mask |= ((unsigned)raw >> 31) << i;
+        const int32_t k = raw & 0x7fffffff;
         double x = live ? widen(cur.val[i]) : 0.0;
         if (SQUARE) x *= x;
         if (TWO) {
@@ -487,20 +487,27 @@ __device__ __forceinline__ void seg_chunk(const SegParams &p, const SegRegs<VT, 
         }
     }
 
-    // ---- blocked segmented reduction ----
-    SegScan<TWO> mine;
-    mine.cnt = __popc(mask);
+    // ---- thread-local pass: head = sum before the first run start, tail = sum after the last ----
+    double head = 0.0, head2 = 0.0, s = 0.0, s2 = 0.0;
     {
-        double s = 0.0, s2 = 0.0;
+        bool seen = false;
 #pragma unroll
         for (int i = 0; i < ITEMS; ++i) {
-            if ((mask >> i) & 1u) { s = 0.0; s2 = 0.0; }
+            if ((mask >> i) & 1u) {
+                if (!seen) { head = s; head2 = s2; seen = true; }
+                s = 0.0;
+                s2 = 0.0;
+            }
             s += pr[i];
             if (TWO) s2 += pr2[i];
         }
-        mine.val = s;  // sum after the last run start (the whole thread if there is none)
-        mine.val2 = s2;
     }
+    SegScan<TWO> mine;
+    mine.cnt = __popc(mask);
+    mine.val = s;  // the whole thread when it holds no run start
+    mine.val2 = s2;
+
+    // ---- CTA-wide segmented scan of (cnt, tail) ----
     SegScan<TWO> inc = mine;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -516,43 +523,72 @@ __device__ __forceinline__ void seg_chunk(const SegParams &p, const SegRegs<VT, 
     exc = seg_combine<TWO>(pre, exc);
 
     const int run_lo = p.chunk_lo[c];
-    // walk again, closing runs
+    const int32_t *__restrict__ run_id = p.run_id;
+    double *__restrict__ out = p.out;
     if (mask != 0) {
-        double s = 0.0, s2 = 0.0;
-        int ord = run_lo + exc.cnt;  // ordinal of the next run start this thread meets
-        bool first = true;
+        // the first run start in this thread closes the run that was open when the thread began
+        const double total = exc.val + head;
+        const double total2 = TWO ? exc.val2 + head2 : 0.0;
+        const int ord = run_lo + exc.cnt;  // ordinal of the run that STARTS at this thread's first flag
+        if (exc.cnt == 0) {                // ... so the run it closes began in an earlier chunk
+            p.carry[c] = total;
+            if (TWO) p.carry2[c] = total2;
+        } else {
+            const int slot = run_id ? run_id[ord - 1] : ord - 1;
+            out[slot] = total;
+            if (TWO) p.out2[slot] = total2;
+        }
+        if (mask & (mask - 1)) {           // two or more starts: runs lying entirely inside this thread
+            double t = 0.0, t2 = 0.0;
+            int o2 = ord;
+            bool first = true;
 #pragma unroll
-        for (int i = 0; i < ITEMS; ++i) {
-            if ((mask >> i) & 1u) {
-                const double total = first ? exc.val + s : s;
-                const double total2 = TWO ? (first ? exc.val2 + s2 : s2) : 0.0;
-                if (first && exc.cnt == 0) {  // the run began in an earlier chunk
-                    p.carry[c] = total;
-                    if (TWO) p.carry2[c] = total2;
-                } else {
-                    const int slot = p.run_id ? p.run_id[ord - 1] : ord - 1;
-                    p.out[slot] = total;
-                    if (TWO) p.out2[slot] = total2;
+            for (int i = 0; i < ITEMS; ++i) {
+                if ((mask >> i) & 1u) {
+                    if (!first) {
+                        const int slot = run_id ? run_id[o2 - 1] : o2 - 1;
+                        out[slot] = t;
+                        if (TWO) p.out2[slot] = t2;
+                    }
+                    first = false;
+                    ++o2;
+                    t = 0.0;
+                    t2 = 0.0;
                 }
-                first = false;
-                ++ord;
-                s = 0.0;
-                s2 = 0.0;
+                t += pr[i];
+                if (TWO) t2 += pr2[i];
             }
-            s += pr[i];
-            if (TWO) s2 += pr2[i];
         }
     }
     if (tid == S_THREADS - 1) {
         const SegScan<TWO> tot = seg_combine<TWO>(exc, mine);
         if (tot.cnt) {  // the last run started here: this CTA owns its slot
             const int last = run_lo + tot.cnt - 1;
-            const int slot = p.run_id ? p.run_id[last] : last;
-            p.out[slot] = tot.val;
+            const int slot = run_id ? run_id[last] : last;
+            out[slot] = tot.val;
             if (TWO) p.out2[slot] = tot.val2;
         } else {        // the whole chunk is the middle of one run
             p.carry[c] = tot.val;
             if (TWO) p.carry2[c] = tot.val2;
+        }
+    }
+}
+
+template <typename VT, int ITEMS>
+__device__ __forceinline__ void seg_load_full(SegRegs<VT, ITEMS> &g, const int32_t *__restrict__ idx,
+                                              const VT *__restrict__ val, int64_t first)
+{
+#pragma unroll
+    for (int i = 0; i < ITEMS / 4; ++i) {
+        const int4 rr = __ldcs(reinterpret_cast<const int4 *>(idx + first) + i);
+        g.idx[4 * i] = rr.x; g.idx[4 * i + 1] = rr.y; g.idx[4 * i + 2] = rr.z; g.idx[4 * i + 3] = rr.w;
+        if (sizeof(VT) == 4) {
+            const float4 vv = __ldcs(reinterpret_cast<const float4 *>(val + first) + i);
+            g.val[4 * i] = vv.x; g.val[4 * i + 1] = vv.y; g.val[4 * i + 2] = vv.z; g.val[4 * i + 3] = vv.w;
+        } else {
+            const double2 va = __ldcs(reinterpret_cast<const double2 *>(val + first) + 2 * i);
+            const double2 vb = __ldcs(reinterpret_cast<const double2 *>(val + first) + 2 * i + 1);
+            g.val[4 * i] = va.x; g.val[4 * i + 1] = va.y; g.val[4 * i + 2] = vb.x; g.val[4 * i + 3] = vb.y;
         }
     }
 }
@@ -575,28 +611,26 @@ __global__ void __launch_bounds__(S_THREADS, 2) seg_spmv_kernel(const SegParams 
         __syncthreads();
     }
 
+    // full chunks: persistent loop, the next chunk's loads in flight while this one is reduced
+    const int n_full = (int)(p.nnz / CHUNK);
+    const int grid = gridDim.x;
     SegRegs<VT, ITEMS> cur;
     int c = blockIdx.x;
-    if (c < p.n_chunks) {
-        const int64_t base = (int64_t)c * CHUNK;
-        const int cnt = (p.nnz - base) < CHUNK ? (int)(p.nnz - base) : CHUNK;
-        seg_load<VT, ITEMS>(cur, idx, val, base + tid * ITEMS, cnt - tid * ITEMS);
-    }
+    if (c < n_full) seg_load_full<VT, ITEMS>(cur, idx, val, (int64_t)c * CHUNK + tid * ITEMS);
     int parity = 0;
-    for (; c < p.n_chunks; c += gridDim.x, parity ^= 1) {
-        const int64_t base = (int64_t)c * CHUNK;
-        const int cnt = (p.nnz - base) < CHUNK ? (int)(p.nnz - base) : CHUNK;
-
-        // issue the next chunk's loads before touching this one
+    for (; c < n_full; c += grid, parity ^= 1) {
         SegRegs<VT, ITEMS> nxt;
-        const int cn = c + gridDim.x;
-        if (cn < p.n_chunks) {
-            const int64_t nb = (int64_t)cn * CHUNK;
-            const int ncnt = (p.nnz - nb) < CHUNK ? (int)(p.nnz - nb) : CHUNK;
-            seg_load<VT, ITEMS>(nxt, idx, val, nb + tid * ITEMS, ncnt - tid * ITEMS);
-        }
-        seg_chunk<VT, ITEMS, TWO, SQUARE, HOT, false>(p, cur, c, cnt - tid * ITEMS, hot, wagg[parity]);
+        const int cn = c + grid;
+        if (cn < n_full) seg_load_full<VT, ITEMS>(nxt, idx, val, (int64_t)cn * CHUNK + tid * ITEMS);
+        seg_chunk<VT, ITEMS, TWO, SQUARE, HOT, true>(p, cur, c, ITEMS, hot, wagg[parity]);
         cur = nxt;
+    }
+    // the last, partially filled chunk (if any) goes to the CTA that would have taken it next
+    if (n_full < p.n_chunks && (int)blockIdx.x == n_full % grid) {
+        const int64_t base = (int64_t)n_full * CHUNK;
+        const int cnt = (int)(p.nnz - base);
+        seg_load<VT, ITEMS>(cur, idx, val, base + tid * ITEMS, cnt - tid * ITEMS);
+        seg_chunk<VT, ITEMS, TWO, SQUARE, HOT, false>(p, cur, n_full, cnt - tid * ITEMS, hot, wagg[parity]);
     }
 }
 
