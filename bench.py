@@ -370,6 +370,21 @@ def convergence(ctx, ds, d):
                      "us_per_eval_gpu": 1e6 * tg / g.evaluations,
                      "max_coef_diff": float(np.max(np.abs(wg - wc))), "objective": fg})
     out["lbfgs_configs0_a1a_logistic_l2"] = runs
+    # the evaluation call alone (the Python optimizer loop above costs ~100 us per iteration by itself)
+    w = np.random.default_rng(1).normal(scale=0.1, size=d1)
+    g = np.empty(d1)
+    lat = {}
+    for _ in range(20):
+        small.value_and_gradient(pml.LOGISTIC, w, out=g)
+    t0 = time.perf_counter()
+    for _ in range(300):
+        small.value_and_gradient(pml.LOGISTIC, w, out=g)
+    lat["gpu_host_buffer_call_us"] = 1e6 * (time.perf_counter() - t0) / 300
+    t0 = time.perf_counter()
+    for _ in range(300):
+        oracle.value_and_gradient(ref, oracle.LOGISTIC, w)
+    lat["cpu_oracle_1_thread_us"] = 1e6 * (time.perf_counter() - t0) / 300
+    out["configs0_a1a_us_per_evaluation"] = lat
     small.close()
     return out
 
