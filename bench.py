@@ -230,12 +230,18 @@ def run_ours(args):
         def e2e_step():
             if world == 1:
                 return ds.value_and_gradient(LOSS_POISSON, h_coef_np, out=h_grad_np)[0]
-            coef.copy_(h_coef, non_blocking=True)
+            # the driver (rank 0) owns the host buffers: one upload, an NVLink broadcast of the coefficients
+            # (what sc.broadcast does in the reference, DistributedObjectiveFunction.scala:57-58), the
+            # evaluation with its all-reduce, and one download of gradient + value on rank 0
+            if rank == 0:
+                coef.copy_(h_coef, non_blocking=True)
+            dist.broadcast(coef, 0)
             step()
-            h_grad.copy_(out_grad, non_blocking=True)
-            h_raw[:1].copy_(out_value, non_blocking=True)
+            if rank == 0:
+                h_grad.copy_(out_grad, non_blocking=True)
+                h_raw[:1].copy_(out_value, non_blocking=True)
             ext.synchronize()
-            return float(h_raw[0])
+            return float(h_raw[0]) if rank == 0 else 0.0
 
         for _ in range(max(3, args.warmup)):
             e2e_step()
@@ -309,7 +315,8 @@ def run_ours(args):
             "e2e": {"value": e2e_steps / e2e_s, "unit": "evals/s", "h2d_bytes_per_step": d * 8,
                     "d2h_bytes_per_step": d * 8 + 8, "ms_per_step": 1e3 * e2e_s / e2e_steps,
                     "api": "pml_value_and_gradient (host buffers, pinned)" if world == 1 else
-                           "H2D coef + raw_dev + NCCL all-reduce + finalize_dev + D2H", "objective": e2e_value},
+                           "rank 0: H2D coef; NCCL broadcast; raw_dev; NCCL all-reduce; finalize_dev; rank 0: D2H",
+                    "objective": e2e_value},
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {"bound": "hbm", "kernel": dominant, "achieved": achieved, "peak": peak, "unit": "GB/s",
@@ -327,7 +334,7 @@ def run_ours(args):
             out["cpu_baseline"] = cpu_baseline(steps=10, warmup=2)
         if world == 1 and not args.no_convergence:
             out["convergence"] = convergence(ctx, ds, d)
-        print(json.dumps(out))
+        emit(out)
     ds.close()
     if world > 1:
         dist.barrier()
@@ -439,10 +446,24 @@ def run_reference(args):
         "e2e": {"value": base["value"], "unit": "evals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(out))
+    emit(out)
+
+
+_REAL_STDOUT = None
+
+
+def emit(obj):
+    """The one JSON line, on the process's real stdout."""
+    line = (json.dumps(obj) + "\n").encode()
+    os.write(_REAL_STDOUT if _REAL_STDOUT is not None else 1, line)
 
 
 def main():
+    # Native libraries (NCCL's version banner, ...) write to fd 1: park everything but the JSON line on stderr.
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
