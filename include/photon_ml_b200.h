@@ -163,6 +163,19 @@ int pml_value_and_gradient_dev(pml_dataset *ds, int loss, const double *coef_dev
 int pml_hessian_vector_dev(pml_dataset *ds, int loss, const double *coef_dev, uint64_t coef_tag,
                            const double *v_dev, double *out_hv_dev);
 
+/* ---- coordinate-descent glue kept on the device ---------------------------------------------- */
+/* score_i = x_i . coef for every row, left in device memory
+ * (api/algorithm/FixedEffectCoordinate.scala:158-165, lib/model/Coefficients.scala:53-58). */
+int pml_scores_dev(pml_dataset *ds, const double *coef_dev, double *out_scores_dev);
+/* pml_dataset_set_offsets from a device array (NULL = no offsets). */
+int pml_dataset_set_offsets_dev(pml_dataset *ds, const double *offsets_dev);
+/* out_i = base_i + scores[row_map[i]]: DataSet.addScoresToOffsets (api/data/FixedEffectDataSet.scala:
+ * 45-54, api/data/LocalDataSet.scala:82-89) without the RDD join.  row_map_dev translates this
+ * coordinate's row order into the other's (NULL = same order); base_offsets_dev NULL = 0. */
+int pml_offsets_from_scores_dev(pml_ctx *ctx, int64_t n, const double *base_offsets_dev,
+                                const double *scores_dev, const int64_t *row_map_dev,
+                                double *out_offsets_dev);
+
 /* number of kernel launches this context has issued (bench.py's gpu_launches) */
 int pml_ctx_launch_count(pml_ctx *ctx, int64_t *out);
 /* Per-kernel device timing for the roofline report: with profiling on, every kernel class is

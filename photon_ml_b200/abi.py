@@ -26,7 +26,7 @@ SYMBOLS = [
     "pml_finalize_dev", "pml_value_and_gradient_dev", "pml_hessian_vector_dev", "pml_ctx_launch_count",
     "pml_dataset_set_margin_variant", "pml_ctx_set_profiling", "pml_ctx_read_profile",
     "pml_value_noalloc_dev", "pml_batch_create_csr", "pml_batch_destroy", "pml_batch_dataset", "pml_batch_coef_ptr",
-    "pml_batch_value_and_gradient",
+    "pml_batch_value_and_gradient", "pml_scores_dev", "pml_dataset_set_offsets_dev", "pml_offsets_from_scores_dev",
 ]
 
 
@@ -103,6 +103,9 @@ def load():
         "pml_batch_dataset": [vp, pp],
         "pml_batch_coef_ptr": [vp, vp],
         "pml_batch_value_and_gradient": [vp, ctypes.c_int, vp, vp, vp],
+        "pml_scores_dev": [vp, vp, vp],
+        "pml_dataset_set_offsets_dev": [vp, vp],
+        "pml_offsets_from_scores_dev": [vp, i64, vp, vp, vp, vp],
     })
     for name, argtypes in sigs.items():
         fn = getattr(lib, name)
@@ -141,6 +144,11 @@ def value_noalloc_dev(device, stream, n, d, row_ptr_dev, col_dev, val_dev, value
     Asynchronous on `stream`; at most 16,777,216 rows; calls on one device must not overlap."""
     check(load().pml_value_noalloc_dev(int(device), stream, n, d, row_ptr_dev, col_dev, val_dev, values_dtype, label_dev,
                                        offset_dev, weight_dev, loss, coef_dev, out_value_dev))
+
+
+def offsets_from_scores_dev(ctx, n, base_offsets_dev, scores_dev, row_map_dev, out_offsets_dev):
+    """out[i] = base[i] + scores[row_map[i]] on the device (integer device addresses; None = absent)."""
+    check(load().pml_offsets_from_scores_dev(ctx._h, n, base_offsets_dev, scores_dev, row_map_dev, out_offsets_dev))
 
 
 class Context:
@@ -279,6 +287,12 @@ class Dataset:
         return out
 
     # ---- device-buffer evaluations (integer device addresses) --------------------------------
+    def scores_dev(self, coef_dev, out_scores_dev):
+        check(load().pml_scores_dev(self._h, coef_dev, out_scores_dev))
+
+    def set_offsets_dev(self, offsets_dev):
+        check(load().pml_dataset_set_offsets_dev(self._h, offsets_dev))
+
     def value_and_gradient_raw_dev(self, loss, coef_dev, out_raw_dev):
         check(load().pml_value_and_gradient_raw_dev(self._h, loss, coef_dev, out_raw_dev))
 

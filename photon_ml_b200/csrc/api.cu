@@ -180,7 +180,9 @@ int run_rows(pml_dataset *ds, RowPassParams &rp, bool two)
     return run(ctx, PML_K_EPILOGUE, [&] { return launch_row_epilogue(s, ctx->sm_count, rp, ds->za, ds->zb, &ds->row_grid); });
 }
 
-int vg_raw(pml_dataset *ds, int loss, const double *coef_dev, double *out_raw_dev)
+// want_vector = false: DistributedGLMLossFunction.value -- only valueSum (and prefactorSum) are wanted, so the
+// column pass is skipped and out_raw_dev[0..d) is left zero.
+int vg_raw(pml_dataset *ds, int loss, const double *coef_dev, double *out_raw_dev, bool want_vector = true)
 {
     pml_ctx *ctx = ds->ctx;
     cudaStream_t s = ctx->stream;
@@ -215,6 +217,12 @@ int vg_raw(pml_dataset *ds, int loss, const double *coef_dev, double *out_raw_de
     rp.mode = MODE_VG;
     rp.loss = loss;
     PML_TRY(run_rows(ds, rp, false));
+    if (!want_vector) {
+        return run(ctx, PML_K_FIXUP, [&] {
+            return launch_fixup(s, nullptr, 0, nullptr, out_raw_dev, nullptr, nullptr, ds->d, ds->partials, ds->row_grid,
+                                true, true);
+        });
+    }
     return run_col_and_fixup(ds, false, out_raw_dev, true, true);
 }
 
@@ -719,7 +727,7 @@ int pml_value_and_gradient_dev(pml_dataset *ds, int loss, const double *coef_dev
     if (!coef_dev) return fail(PML_EINVAL, "null buffer");
     Guard g(ds->ctx);
     PML_CUDA(cudaSetDevice(ds->ctx->device));
-    PML_TRY(vg_raw(ds, loss, coef_dev, ds->raw));
+    PML_TRY(vg_raw(ds, loss, coef_dev, ds->raw, out_grad_dev != nullptr));
     return finalize(ds, loss, ds->raw, out_value_dev, out_grad_dev);
 }
 
@@ -747,7 +755,7 @@ int pml_value_and_gradient(pml_dataset *ds, int loss, const double *coef, double
     cudaStream_t s = ds->ctx->stream;
     const size_t db = sizeof(double) * (size_t)ds->d;
     if (ds->d > 0) PML_CUDA(cudaMemcpyAsync(ds->io_a, coef, db, cudaMemcpyHostToDevice, s));
-    PML_TRY(vg_raw(ds, loss, ds->io_a, ds->raw));
+    PML_TRY(vg_raw(ds, loss, ds->io_a, ds->raw, out_grad != nullptr));
     const bool norm = loss != PML_LOSS_SMOOTHED_HINGE && (ds->factors || ds->shifts);
     const double *src = ds->raw;
     if (norm && out_grad) {
@@ -832,6 +840,61 @@ int pml_scores(pml_dataset *ds, const double *coef, double *out_scores)
     if (ds->n > 0) PML_CUDA(cudaMemcpyAsync(out_scores, ds->r, sizeof(double) * (size_t)ds->n, cudaMemcpyDeviceToHost, s));
     PML_CUDA(cudaStreamSynchronize(s));
     return PML_OK;
+}
+
+// ---- coordinate-descent glue on the device ---------------------------------
+int pml_scores_dev(pml_dataset *ds, const double *coef_dev, double *out_scores_dev)
+{
+    PML_TRY(check_ds(ds));
+    if ((!coef_dev && ds->d > 0) || (!out_scores_dev && ds->n > 0)) return fail(PML_EINVAL, "null buffer");
+    Guard g(ds->ctx);
+    PML_CUDA(cudaSetDevice(ds->ctx->device));
+    cudaStream_t s = ds->ctx->stream;
+    RowPassParams rp;
+    std::memset(&rp, 0, sizeof(rp));
+    rp.n = ds->n;
+    rp.row_ptr = ds->row_ptr;
+    rp.col = ds->col;
+    rp.val = ds->val;
+    rp.label = ds->label;
+    rp.r = ds->n > 0 ? out_scores_dev : ds->r;
+    {
+        int np = 0;
+        PML_TRY(run(ds->ctx, PML_K_PREPARE, [&] {
+            return launch_prepare_vectors(s, ds->d, coef_dev, nullptr, nullptr, nullptr, ds->t.rank, ds->vec,
+                                          ds->shift_partials, &np);
+        }));
+    }
+    rp.vec = ds->vec;
+    rp.mode = MODE_SCORE;
+    return run_rows(ds, rp, false);
+}
+
+int pml_dataset_set_offsets_dev(pml_dataset *ds, const double *offsets_dev)
+{
+    PML_TRY(check_ds(ds));
+    Guard g(ds->ctx);
+    PML_CUDA(cudaSetDevice(ds->ctx->device));
+    ds->cache_valid = false;
+    if (offsets_dev == nullptr) {
+        if (ds->offset) { cudaStreamSynchronize(ds->ctx->stream); cudaFree(ds->offset); ds->offset = nullptr; }
+        return PML_OK;
+    }
+    if (ds->offset == nullptr) PML_TRY(dev_alloc(&ds->offset, (size_t)ds->n, &ds->bytes));
+    if (ds->n > 0)
+        PML_CUDA(cudaMemcpyAsync(ds->offset, offsets_dev, sizeof(double) * (size_t)ds->n, cudaMemcpyDeviceToDevice,
+                                 ds->ctx->stream));
+    return PML_OK;
+}
+
+int pml_offsets_from_scores_dev(pml_ctx *ctx, int64_t n, const double *base_offsets_dev, const double *scores_dev,
+                                const int64_t *row_map_dev, double *out_offsets_dev)
+{
+    if (!ctx) return fail(PML_EINVAL, "null context");
+    if (n < 0 || (n > 0 && (!scores_dev || !out_offsets_dev))) return fail(PML_EINVAL, "bad argument");
+    Guard g(ctx);
+    PML_CUDA(cudaSetDevice(ctx->device));
+    return count(ctx, launch_offsets_from_scores(ctx->stream, n, base_offsets_dev, scores_dev, row_map_dev, out_offsets_dev));
 }
 
 // ---- batched per-entity problems (random effects) -------------------------------------------

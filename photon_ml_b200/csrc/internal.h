@@ -105,6 +105,8 @@ int launch_fixup(cudaStream_t s, const FixEntry *fix, int n_fix, const double *c
 int launch_finalize(cudaStream_t s, int d, const double *raw, const double *factors, const double *shifts,
                     double *out_value, double *out_vec);
 
+int launch_offsets_from_scores(cudaStream_t s, int64_t n, const double *base, const double *scores, const int64_t *row_map,
+                               double *out);
 int launch_globalize_cols(cudaStream_t s, int64_t n_entities, const int64_t *ent_row_ptr, const int64_t *coef_ptr,
                           const int32_t *ent_dim, const int64_t *row_ptr, int32_t *col, unsigned long long *bad);
 int launch_entity_values(cudaStream_t s, int64_t n_entities, const int64_t *ent_row_ptr, const double *row_loss,

@@ -905,4 +905,26 @@ int launch_entity_values(cudaStream_t s, int64_t n_entities, const int64_t *ent_
     return cudaGetLastError() == cudaSuccess ? 1 : -1;
 }
 
+// offsets'_i = base_i + score_{map(i)}: DataSet.addScoresToOffsets (api/data/FixedEffectDataSet.scala:45-54,
+// api/data/LocalDataSet.scala:82-89) without the RDD join -- `row_map` carries the row correspondence
+// between two coordinates' row orders (e.g. entity-grouped rows -> fixed-effect rows); null = identity.
+__global__ void offsets_from_scores_kernel(int64_t n, const double *__restrict__ base, const double *__restrict__ scores,
+                                           const int64_t *__restrict__ row_map, double *__restrict__ out)
+{
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const double b = base ? base[i] : 0.0;
+        out[i] = b + scores[row_map ? row_map[i] : i];
+    }
+}
+
+int launch_offsets_from_scores(cudaStream_t s, int64_t n, const double *base, const double *scores, const int64_t *row_map,
+                               double *out)
+{
+    if (n <= 0) return 0;
+    int64_t grid = (n + 255) / 256;
+    if (grid > 148 * 16) grid = 148 * 16;
+    offsets_from_scores_kernel<<<(int)grid, 256, 0, s>>>(n, base, scores, row_map, out);
+    return cudaGetLastError() == cudaSuccess ? 1 : -1;
+}
+
 }  // namespace pml

@@ -152,3 +152,52 @@ def test_config1_full_size_properties(ctx):
     assert abs(0.5 * np.sum((scores - y) ** 2) - sq[0]) <= 1e-11 * sq[0]
     for ds in (full, a, b):
         ds.close()
+
+
+def test_coordinate_descent_glue_stays_on_the_device(ctx):
+    # One GAME pass in miniature without host round trips of per-row data: fixed-effect scores
+    # (FixedEffectCoordinate.score) become the random-effect coordinate's offsets
+    # (DataSet.addScoresToOffsets) through a row map, because the random-effect rows are grouped by entity.
+    import torch
+    import photon_ml_b200 as pml
+    rng = np.random.default_rng(6)
+    n, d_fe, d_re, n_ent = 5000, 300, 12, 200
+    fe_ptr, fe_col, fe_val = util.random_csr(rng, n, d_fe, 15)
+    label = (rng.random(n) < 0.3).astype(np.float64)
+    base_offset = rng.normal(scale=0.1, size=n)
+    entity_of_row = rng.integers(0, n_ent, size=n)
+    row_map = np.argsort(entity_of_row, kind="stable").astype(np.int64)     # RE row i is FE row row_map[i]
+    rows = np.bincount(entity_of_row, minlength=n_ent)
+    ent_row_ptr = np.concatenate([[0], np.cumsum(rows)]).astype(np.int64)
+    re_ptr, re_col, re_val = util.random_csr(rng, n, d_re, 5)                # already in RE (entity-grouped) order
+    fe = pml.Dataset.from_csr(ctx, n, d_fe, fe_ptr, fe_col, fe_val, label, base_offset)
+    batch = pml.Batch(ctx, ent_row_ptr, np.full(n_ent, d_re, np.int32), re_ptr, re_col, re_val, label[row_map])
+    dev = torch.device("cuda", 0)
+    w_fe = torch.tensor(rng.normal(scale=0.2, size=d_fe), device=dev)
+    t_scores = torch.empty(n, dtype=torch.float64, device=dev)
+    t_base = torch.tensor(base_offset[row_map], device=dev)
+    t_map = torch.tensor(row_map, device=dev)
+    t_off = torch.empty(n, dtype=torch.float64, device=dev)
+    torch.cuda.synchronize()
+    fe.scores_dev(w_fe.data_ptr(), t_scores.data_ptr())
+    pml.abi.offsets_from_scores_dev(ctx, n, t_base.data_ptr(), t_scores.data_ptr(), t_map.data_ptr(), t_off.data_ptr())
+    batch.dataset.set_offsets_dev(t_off.data_ptr())
+    coefs = rng.normal(scale=0.3, size=batch.d_total)
+    values, grads = batch.value_and_gradient(pml.LOGISTIC, coefs)
+    X_fe = util.csr_to_dense(n, d_fe, fe_ptr, fe_col, fe_val)
+    off_ref = base_offset[row_map] + (X_fe @ w_fe.cpu().numpy())[row_map]
+    assert util.rel_err(t_off.cpu().numpy(), off_ref) <= TOL
+    gcol = (re_col + np.repeat(batch.coef_ptr[:-1], rows)[np.repeat(np.arange(n), np.diff(re_ptr))]).astype(np.int32)
+    ref = oracle.Data(n, batch.d_total, re_ptr, gcol, re_val, label[row_map], off_ref)
+    f_ref, g_ref = oracle.value_and_gradient(ref, oracle.LOGISTIC, coefs)
+    assert abs(values.sum() - f_ref) <= 1e-10 * abs(f_ref) and util.rel_err(grads, g_ref) <= TOL
+    # training-loss evaluator = value only: same number, no column pass
+    launches0 = ctx.launch_count
+    f_only, _ = batch.dataset.value_and_gradient(pml.LOGISTIC, coefs, want_gradient=False)
+    value_only_launches = ctx.launch_count - launches0
+    launches0 = ctx.launch_count
+    f_full, _ = batch.dataset.value_and_gradient(pml.LOGISTIC, coefs)
+    assert f_only == f_full and value_only_launches < ctx.launch_count - launches0
+    batch.dataset.set_offsets_dev(None)
+    batch.close()
+    fe.close()

@@ -86,7 +86,7 @@ def test_owlqn_l1_logistic_with_normalization(ctx):
     ds = pml.Dataset.from_csr(ctx, n, d, row_ptr, col, val, label)
     ref = oracle.Data(n, d, row_ptr, col, val, label)
     ctx_n = NormalizationContext(f, s, icpt)
-    gpu_opt, cpu_opt = OWLQN(2.0, ctx_n), OWLQN(2.0, ctx_n)
+    gpu_opt, cpu_opt = OWLQN(10.0, ctx_n), OWLQN(10.0, ctx_n)
     w_gpu, f_gpu = gpu_opt.optimize(DistributedGLMLossFunction.create(pml.LOGISTIC), np.zeros(d), ds)
     w_cpu, f_cpu = cpu_opt.optimize(OracleGLMObjective(oracle.LOGISTIC), np.zeros(d), ref)
     assert gpu_opt.currentState.iter == cpu_opt.currentState.iter
