@@ -521,13 +521,16 @@ int pml_dataset_create_csr_dev(pml_ctx *ctx, int64_t n, int32_t d, const int64_t
     }
     ds->value_bytes = dst_bytes;
 
-    PML_TRY(dev_alloc(&ds->col, (size_t)nnz + 4, &ds->bytes));
+    // 16 entries of zeroed padding: seg_spmv_kernel's 128-bit loads may read up to 7 entries past nnz
+    PML_TRY(dev_alloc(&ds->col, (size_t)nnz + 16, &ds->bytes));
+    PML_CUDA(cudaMemsetAsync(ds->col + nnz, 0, sizeof(int32_t) * 16, s));
     {
         void *v = nullptr;
-        cudaError_t e = cudaMalloc(&v, (size_t)(nnz + 4) * dst_bytes);
+        cudaError_t e = cudaMalloc(&v, (size_t)(nnz + 16) * dst_bytes);
         if (e != cudaSuccess) return fail(PML_ENOMEM, std::string("cudaMalloc values: ") + cudaGetErrorString(e));
         ds->val = v;
-        ds->bytes += (nnz + 4) * dst_bytes;
+        ds->bytes += (nnz + 16) * dst_bytes;
+        PML_CUDA(cudaMemsetAsync((char *)v + (size_t)nnz * dst_bytes, 0, (size_t)16 * dst_bytes, s));
     }
     if (nnz > 0) {
         PML_CUDA(cudaMemcpyAsync(ds->col, col_idx_dev, sizeof(int32_t) * (size_t)nnz, cudaMemcpyDeviceToDevice, s));
