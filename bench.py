@@ -284,8 +284,9 @@ def run_ours(args):
         row_bytes, col_bytes = kernel_bytes(info, 0, 0)
         row_ms = profile["row_pass"][0] / max(1, profile["row_pass"][1])
         col_ms = profile["col_pass"][0] / max(1, profile["col_pass"][1])
-        dominant = ("seg_spmv_kernel (CSC pass, X^T r)" if col_ms >= row_ms
-                    else "row_pass_kernel<%d lanes/row> (CSR pass, X w + pointwise)" % info.margin_variant)
+        dominant = ("seg_spmv_warp_kernel (CSC pass, X^T r)" if col_ms >= row_ms
+                    else ("seg_spmv_warp_kernel (CSR pass, X w)" if info.margin_variant == 1 else
+                          "row_pass_kernel<%d lanes/row> (CSR pass, X w + pointwise)" % info.margin_variant))
         dom_bytes, dom_ms = (col_bytes, col_ms) if col_ms >= row_ms else (row_bytes, row_ms)
         achieved = dom_bytes / (dom_ms * 1e-3) / 1e9
         ms_per_step = ms / args.steps

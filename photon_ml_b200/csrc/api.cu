@@ -68,7 +68,6 @@ int upload_optional(cudaStream_t s, double **slot, const double *src, int64_t n,
 int pick_variant(int64_t n, int64_t nnz)
 {
     const double mean = n > 0 ? (double)nnz / (double)n : 0.0;
-    if (mean < 3.0) return 1;  // segment-per-CTA
     int lanes = 2;
     while (lanes < 32 && lanes * 2 * 6.0 <= mean) lanes *= 2;
     return lanes;
@@ -131,7 +130,7 @@ int run_col_and_fixup(pml_dataset *ds, bool square, double *out, bool with_scala
         return launch_seg_spmv(s, ctx->sm_count, ds->value_bytes, false, square, ds->t.chunk_entries, cp, 0);
     }));
     PML_TRY(run(ctx, PML_K_FIXUP, [&] {
-        return launch_fixup(s, ds->t.fix, ds->t.n_fix, ds->carry_head, out, nullptr, nullptr, ds->d,
+        return launch_fixup(s, ds->t.fix, ds->t.n_fix, ds->t.n_fix_long, ds->carry_head, out, nullptr, nullptr, ds->d,
                             with_scalars ? ds->partials : nullptr, ds->row_grid, write_value, true);
     }));
     return PML_OK;
@@ -143,9 +142,13 @@ int run_rows(pml_dataset *ds, RowPassParams &rp, bool two)
 {
     pml_ctx *ctx = ds->ctx;
     cudaStream_t s = ctx->stream;
-    if (ds->lanes_per_row != 1) {
+    // Default split (measured, profiles/): single-vector passes (value+gradient, cached Hessian-vector, diagonal,
+    // scores) are fastest on the entry-chunked kernel (1.06 ms vs 1.29 ms at 50 entries/row); the paired
+    // (ec, ev) pass of a cold Hessian-vector product is fastest with lanes-per-row (1.59 vs 2.35 ms).
+    const int variant = ds->variant_forced ? ds->lanes_per_row : (two ? ds->lanes_per_row : 1);
+    if (variant != 1) {
         return run(ctx, PML_K_ROW, [&] {
-            return launch_row_pass(s, ctx->sm_count, ds->value_bytes, ds->lanes_per_row, two, rp, ds->t.m, ds->row_threads,
+            return launch_row_pass(s, ctx->sm_count, ds->value_bytes, variant, two, rp, ds->t.m, ds->row_threads,
                                    ds->row_hot_cap, &ds->row_grid);
         });
     }
@@ -174,7 +177,7 @@ int run_rows(pml_dataset *ds, RowPassParams &rp, bool two)
         return launch_seg_spmv(s, ctx->sm_count, ds->value_bytes, two, false, ds->t.chunk_entries, sp, ds->t.m);
     }));
     PML_TRY(run(ctx, PML_K_FIXUP, [&] {
-        return launch_fixup(s, ds->rs.fix, ds->rs.n_fix, ds->carry_row, ds->za, two ? ds->carry_row2 : nullptr,
+        return launch_fixup(s, ds->rs.fix, ds->rs.n_fix, ds->rs.n_fix_long, ds->carry_row, ds->za, two ? ds->carry_row2 : nullptr,
                             two ? ds->zb : nullptr, 0, nullptr, 0, false, false);
     }));
     return run(ctx, PML_K_EPILOGUE, [&] { return launch_row_epilogue(s, ctx->sm_count, rp, ds->za, ds->zb, &ds->row_grid); });
@@ -219,7 +222,7 @@ int vg_raw(pml_dataset *ds, int loss, const double *coef_dev, double *out_raw_de
     PML_TRY(run_rows(ds, rp, false));
     if (!want_vector) {
         return run(ctx, PML_K_FIXUP, [&] {
-            return launch_fixup(s, nullptr, 0, nullptr, out_raw_dev, nullptr, nullptr, ds->d, ds->partials, ds->row_grid,
+            return launch_fixup(s, nullptr, 0, 0, nullptr, out_raw_dev, nullptr, nullptr, ds->d, ds->partials, ds->row_grid,
                                 true, true);
         });
     }
@@ -541,7 +544,8 @@ int pml_dataset_create_csr_dev(pml_ctx *ctx, int64_t n, int32_t d, const int64_t
     PML_TRY(upload_optional(s, &ds->offset, offsets_dev, n, true, &ds->bytes));
     PML_TRY(upload_optional(s, &ds->weight, weights_dev, n, true, &ds->bytes));
 
-    const int chunk_entries = TCHUNK;
+    int chunk_entries = 256;  // one chunk per warp (seg_spmv_warp_kernel); PML_SEG_CTA=1 selects CTA-sized chunks
+    if (std::getenv("PML_SEG_CTA") != nullptr) chunk_entries = TCHUNK;
     PML_TRY(build_transpose(s, n, d, nnz, ds->row_ptr, ds->col, ds->val, dst_bytes, chunk_entries, &ds->t));
     ds->bytes += ds->t.bytes;
     // after the transpose: from here on the CSR column array carries the row-start flags in bit 31
@@ -618,7 +622,7 @@ int pml_dataset_get_info(const pml_dataset *ds, pml_dataset_info *out)
     out->nnz = ds->nnz;
     out->d = ds->d;
     out->value_bytes = ds->value_bytes;
-    out->margin_variant = ds->lanes_per_row;
+    out->margin_variant = ds->variant_forced ? ds->lanes_per_row : 1;  // variant of single-vector passes
     out->n_chunks = ds->t.n_chunks;
     out->nonempty_cols = ds->t.m;
     out->device_bytes = ds->bytes;
@@ -679,8 +683,10 @@ int pml_dataset_set_margin_variant(pml_dataset *ds, int lanes_per_row)
     Guard g(ds->ctx);
     if (lanes_per_row == -1) {
         ds->lanes_per_row = pick_variant(ds->n, ds->nnz);
+        ds->variant_forced = false;
         return PML_OK;
     }
+    ds->variant_forced = true;
     switch (lanes_per_row) {
     case 0: case 1: case 2: case 4: case 8: case 16: case 32:
         ds->lanes_per_row = lanes_per_row;

@@ -34,7 +34,8 @@ int fail(int code, const std::string &msg);
 constexpr int S_THREADS = 512;
 constexpr int S_ITEMS = 8;
 constexpr int TCHUNK = S_THREADS * S_ITEMS;  // 4096 entries = 32 KB of stream per chunk (fp32 values)
-constexpr int S_MAX_DYN_SMEM = 104 * 1024;   // hot table per CTA; two CTAs share an SM
+constexpr int S_MAX_DYN_SMEM = 104 * 1024;
+constexpr int SW_THREADS = 256;               // CTA size of the warp-chunk variant (4 CTAs per SM)   // hot table per CTA; two CTAs share an SM
 
 // ---- geometry of the row (CSR) kernel ----
 constexpr int R_STREAM_CAP = 128;  // products staged per warp per piece in the segment-per-warp variant
@@ -99,7 +100,7 @@ int launch_seg_spmv(cudaStream_t s, int sm_count, int value_bytes, bool two, boo
 int seg_hot_capacity(bool two);
 int launch_row_epilogue(cudaStream_t s, int sm_count, const RowPassParams &p, const double *za, const double *zb,
                         int *grid_out);
-int launch_fixup(cudaStream_t s, const FixEntry *fix, int n_fix, const double *carry_head, double *out,
+int launch_fixup(cudaStream_t s, const FixEntry *fix, int n_fix, int n_long, const double *carry_head, double *out,
                  const double *carry_head2, double *out2, int d, const double *partials, int n_partials,
                  bool write_value, bool write_prefactor);
 int launch_finalize(cudaStream_t s, int d, const double *raw, const double *factors, const double *shifts,
@@ -136,6 +137,7 @@ struct Packed {
     int64_t m = 0;  // non-empty columns
     int n_chunks = 0;
     int n_fix = 0;
+    int n_fix_long = 0;  // leading fix entries that span >= 32 chunks (one warp each)
     int64_t bytes = 0;
 };
 
@@ -147,6 +149,7 @@ struct RowSide {
     int64_t n_runs = 0;
     int n_chunks = 0;
     int n_fix = 0;
+    int n_fix_long = 0;  // leading fix entries that span >= 32 chunks (one warp each)
     int64_t bytes = 0;
 };
 
@@ -210,7 +213,8 @@ struct pml_dataset {
     uint64_t cached_tag = 0;
     int cached_loss = -1;
     bool cache_valid = false;
-    int lanes_per_row = 8;  // resolved margin variant
+    int lanes_per_row = 8;  // lanes-per-row variant used for paired (Hessian-vector, cold) passes, or the forced variant
+    bool variant_forced = false;  // pml_dataset_set_margin_variant pinned one variant for every pass
     int row_threads = 256;  // CTA shape of the warp-oriented row pass (256 or 1024)
     int row_hot_cap = 0;    // cap on its shared-memory hot table (-1 = as much as fits)
     int row_grid = 1;       // CTAs of the last row-pass launch (= number of (F, P) partials)

@@ -18,6 +18,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <cstdlib>
+
 #include "internal.h"
 #include "pointwise.cuh"
 
@@ -459,7 +461,8 @@ __device__ __forceinline__ void seg_load(SegRegs<VT, ITEMS> &g, const int32_t *_
 
 // Reduces one chunk held in `cur`.  FULL = every thread owns ITEMS live entries (all chunks but
 // possibly the last), which keeps the bounds tests out of the persistent loop.
-template <typename VT, int ITEMS, bool TWO, bool SQUARE, bool HOT, bool FULL>
+// WARP = the chunk belongs to one warp (32*ITEMS entries): the scan stops at the warp, no barrier.
+template <typename VT, int ITEMS, bool TWO, bool SQUARE, bool HOT, bool FULL, bool WARP = false>
 __device__ __forceinline__ void seg_chunk(const SegParams &p, const SegRegs<VT, ITEMS> &cur, int c, int mine_cnt,
                                           const double *hot, SegScan<TWO> *wagg_c)
 {
@@ -514,13 +517,15 @@ __device__ __forceinline__ void seg_chunk(const SegParams &p, const SegRegs<VT, 
         const SegScan<TWO> up = seg_shfl_up<TWO>(inc, o);
         if (lane >= o) inc = seg_combine<TWO>(up, inc);
     }
-    if (lane == 31) wagg_c[warp] = inc;
+    if (!WARP && lane == 31) wagg_c[warp] = inc;
     SegScan<TWO> exc = seg_shfl_up<TWO>(inc, 1);
     if (lane == 0) exc = seg_identity<TWO>();
-    __syncthreads();  // wagg is double-buffered by chunk parity, so one barrier per chunk suffices
-    SegScan<TWO> pre = seg_identity<TWO>();
-    for (int w = 0; w < warp; ++w) pre = seg_combine<TWO>(pre, wagg_c[w]);
-    exc = seg_combine<TWO>(pre, exc);
+    if (!WARP) {
+        __syncthreads();  // wagg is double-buffered by chunk parity, so one barrier per chunk suffices
+        SegScan<TWO> pre = seg_identity<TWO>();
+        for (int w = 0; w < warp; ++w) pre = seg_combine<TWO>(pre, wagg_c[w]);
+        exc = seg_combine<TWO>(pre, exc);
+    }
 
     const int run_lo = p.chunk_lo[c];
     const int32_t *__restrict__ run_id = p.run_id;
@@ -560,7 +565,7 @@ __device__ __forceinline__ void seg_chunk(const SegParams &p, const SegRegs<VT, 
             }
         }
     }
-    if (tid == S_THREADS - 1) {
+    if (WARP ? lane == 31 : tid == S_THREADS - 1) {
         const SegScan<TWO> tot = seg_combine<TWO>(exc, mine);
         if (tot.cnt) {  // the last run started here: this CTA owns its slot
             const int last = run_lo + tot.cnt - 1;
@@ -634,6 +639,61 @@ __global__ void __launch_bounds__(S_THREADS, 2) seg_spmv_kernel(const SegParams 
     }
 }
 
+// The same reduction with one chunk per WARP (32*ITEMS entries): no shared-memory exchange and no
+// barrier, at the price of 16x more chunk metadata and fix-up entries.
+template <typename VT, int ITEMS, bool TWO, bool SQUARE, bool HOT, int SW_THREADS>
+__global__ void __launch_bounds__(SW_THREADS, 1024 / SW_THREADS) seg_spmv_warp_kernel(const SegParams p)
+{
+    constexpr int CHUNK = 32 * ITEMS;
+    constexpr int WARPS = SW_THREADS / 32;
+    extern __shared__ __align__(16) double hot[];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const VT *__restrict__ val = static_cast<const VT *>(p.val);
+    const int32_t *__restrict__ idx = p.idx;
+    if (HOT) {
+        const int words = TWO ? 2 * p.n_hot : p.n_hot;
+        for (int i = tid; i < words; i += SW_THREADS) hot[i] = p.table[i];
+        __syncthreads();
+    }
+    const int n_full = (int)(p.nnz / CHUNK);
+    const int stride = gridDim.x * WARPS;
+    SegRegs<VT, ITEMS> cur;
+    int c = blockIdx.x * WARPS + warp;
+    if (c < n_full) seg_load_full<VT, ITEMS>(cur, idx, val, (int64_t)c * CHUNK + lane * ITEMS);
+    for (; c < n_full; c += stride) {
+        SegRegs<VT, ITEMS> nxt;
+        const int cn = c + stride;
+        if (cn < n_full) seg_load_full<VT, ITEMS>(nxt, idx, val, (int64_t)cn * CHUNK + lane * ITEMS);
+        seg_chunk<VT, ITEMS, TWO, SQUARE, HOT, true, true>(p, cur, c, ITEMS, hot, nullptr);
+        cur = nxt;
+    }
+    if (n_full < p.n_chunks && (int)(blockIdx.x * WARPS + warp) == n_full % stride) {
+        const int64_t base = (int64_t)n_full * CHUNK;
+        const int cnt = (int)(p.nnz - base);
+        seg_load<VT, ITEMS>(cur, idx, val, base + lane * ITEMS, cnt - lane * ITEMS);
+        seg_chunk<VT, ITEMS, TWO, SQUARE, HOT, false, true>(p, cur, n_full, cnt - lane * ITEMS, hot, nullptr);
+    }
+}
+
+template <typename VT, bool TWO, bool SQUARE, int SW_THREADS>
+static int launch_seg_warp(cudaStream_t s, int sm_count, size_t smem, const SegParams &p)
+{
+    const int warps = SW_THREADS / 32;
+    int grid = sm_count * (1024 / SW_THREADS);
+    const int want = (p.n_chunks + warps - 1) / warps;
+    if (grid > want) grid = want;
+    if (p.n_hot > 0) {
+        if (smem > 48 * 1024 &&
+            cudaFuncSetAttribute(seg_spmv_warp_kernel<VT, 8, TWO, SQUARE, true, SW_THREADS>,
+                                 cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * S_MAX_DYN_SMEM) != cudaSuccess)
+            return -1;
+        seg_spmv_warp_kernel<VT, 8, TWO, SQUARE, true, SW_THREADS><<<grid, SW_THREADS, smem, s>>>(p);
+    } else {
+        seg_spmv_warp_kernel<VT, 8, TWO, SQUARE, false, SW_THREADS><<<grid, SW_THREADS, 0, s>>>(p);
+    }
+    return cudaGetLastError() == cudaSuccess ? 1 : -1;
+}
+
 template <typename VT, int ITEMS, bool TWO, bool SQUARE>
 static int launch_seg_one(cudaStream_t s, int grid, size_t smem, const SegParams &p)
 {
@@ -661,6 +721,33 @@ int launch_seg_spmv(cudaStream_t s, int sm_count, int value_bytes, bool two, boo
     const size_t smem = (size_t)p.n_hot * (two ? 16 : 8);
     int grid = sm_count * 2;
     if (grid > p.n_chunks) grid = p.n_chunks;
+    if (chunk_entries == 256) {  // warp-sized chunks
+        // CTA shape and table size of the warp-chunk kernel (tuning knobs; defaults from the sweep in profiles/)
+        static const int threads_env = std::getenv("PML_SEG_WARP_THREADS") ? std::atoi(std::getenv("PML_SEG_WARP_THREADS")) : 0;
+        static const int cap_env = std::getenv("PML_SEG_WARP_HOT") ? std::atoi(std::getenv("PML_SEG_WARP_HOT")) : -1;
+        int threads = table_len > 0 ? 1024 : 256;   // with a table: one big CTA per SM shares it among 32 warps
+        if (threads_env == 256 || threads_env == 512 || threads_env == 1024) threads = threads_env;
+        size_t cap_w = (size_t)100 * 1024;
+        if (threads == 512) cap_w = (size_t)50 * 1024;
+        if (threads == 256) cap_w = (size_t)32 * 1024;
+        if (cap_env >= 0) cap_w = (size_t)cap_env * 1024;
+        const int64_t cap_entries = (int64_t)(cap_w / (two ? 16 : 8));
+        p.n_hot = (int)(table_len < cap_entries ? table_len : cap_entries);
+        const size_t smem_w = (size_t)p.n_hot * (two ? 16 : 8);
+#define PML_SEG_WARP_DISPATCH(T)                                                                              \
+        if (value_bytes == 4) {                                                                               \
+            if (two) return launch_seg_warp<float, true, false, T>(s, sm_count, smem_w, p);                   \
+            return square ? launch_seg_warp<float, false, true, T>(s, sm_count, smem_w, p)                    \
+                          : launch_seg_warp<float, false, false, T>(s, sm_count, smem_w, p);                  \
+        }                                                                                                     \
+        if (two) return launch_seg_warp<double, true, false, T>(s, sm_count, smem_w, p);                      \
+        return square ? launch_seg_warp<double, false, true, T>(s, sm_count, smem_w, p)                       \
+                      : launch_seg_warp<double, false, false, T>(s, sm_count, smem_w, p);
+        if (threads == 1024) { PML_SEG_WARP_DISPATCH(1024) }
+        if (threads == 512) { PML_SEG_WARP_DISPATCH(512) }
+        PML_SEG_WARP_DISPATCH(256)
+#undef PML_SEG_WARP_DISPATCH
+    }
     const int items = chunk_entries / S_THREADS;
     if (items != 8) return -1;
     if (value_bytes == 4) {
@@ -765,7 +852,7 @@ int launch_row_epilogue(cudaStream_t s, int sm_count, const RowPassParams &p, co
 constexpr int F_THREADS = 256;
 
 __global__ void __launch_bounds__(F_THREADS)
-fixup_kernel(const FixEntry *__restrict__ fix, int n_fix, const double *__restrict__ carry_head,
+fixup_kernel(const FixEntry *__restrict__ fix, int n_fix, int n_long, const double *__restrict__ carry_head,
              double *__restrict__ out, const double *__restrict__ carry_head2, double *__restrict__ out2, int d,
              const double *__restrict__ partials, int n_partials, int write_value, int write_prefactor)
 {
@@ -784,29 +871,47 @@ fixup_kernel(const FixEntry *__restrict__ fix, int n_fix, const double *__restri
         }
         return;
     }
-    const int q = blockIdx.x * (F_THREADS / 32) + warp;
+    // The list is ordered long runs first (pack time).  A run spanning >= 32 chunks gets a warp (lanes
+    // stride over its heads, fixed shuffle tree); short ones -- the bulk, usually one head -- get a thread.
+    const int long_blocks = (n_long + (F_THREADS / 32) - 1) / (F_THREADS / 32);
+    if ((int)blockIdx.x < long_blocks) {
+        const int q = blockIdx.x * (F_THREADS / 32) + warp;
+        if (q >= n_long) return;
+        const FixEntry e = fix[q];
+        double s = 0.0, s2 = 0.0;
+        for (int cc = e.chunk_begin + lane; cc < e.chunk_end; cc += 32) {
+            s += carry_head[cc];
+            if (carry_head2) s2 += carry_head2[cc];
+        }
+        s = warp_sum(s);
+        s2 = warp_sum(s2);
+        if (lane == 0) {
+            out[e.col] += s;
+            if (carry_head2) out2[e.col] += s2;
+        }
+        return;
+    }
+    const int q = n_long + ((int)blockIdx.x - long_blocks) * F_THREADS + threadIdx.x;
     if (q >= n_fix) return;
     const FixEntry e = fix[q];
     double s = 0.0, s2 = 0.0;
-    for (int cc = e.chunk_begin + lane; cc < e.chunk_end; cc += 32) {
+    for (int cc = e.chunk_begin; cc < e.chunk_end; ++cc) {
         s += carry_head[cc];
         if (carry_head2) s2 += carry_head2[cc];
     }
-    s = warp_sum(s);
-    s2 = warp_sum(s2);
-    if (lane == 0) {
-        out[e.col] += s;
-        if (carry_head2) out2[e.col] += s2;
-    }
+    out[e.col] += s;
+    if (carry_head2) out2[e.col] += s2;
 }
 
-int launch_fixup(cudaStream_t s, const FixEntry *fix, int n_fix, const double *carry_head, double *out,
+int launch_fixup(cudaStream_t s, const FixEntry *fix, int n_fix, int n_long, const double *carry_head, double *out,
                  const double *carry_head2, double *out2, int d, const double *partials, int n_partials,
                  bool write_value, bool write_prefactor)
 {
-    int grid = (n_fix + (F_THREADS / 32) - 1) / (F_THREADS / 32) + (partials ? 1 : 0);
+    const int long_blocks = (n_long + (F_THREADS / 32) - 1) / (F_THREADS / 32);
+    const int short_blocks = (n_fix - n_long + F_THREADS - 1) / F_THREADS;
+    const int grid = long_blocks + short_blocks + (partials ? 1 : 0);
     if (grid == 0) return 0;
-    fixup_kernel<<<grid, F_THREADS, 0, s>>>(fix, n_fix, carry_head, out, carry_head2, out2, d, partials, n_partials,
+    fixup_kernel<<<grid, F_THREADS, 0, s>>>(fix, n_fix, n_long, carry_head, out, carry_head2, out2, d, partials, n_partials,
                                             write_value ? 1 : 0, write_prefactor ? 1 : 0);
     return cudaGetLastError() == cudaSuccess ? 1 : -1;
 }

@@ -232,7 +232,8 @@ int check_columns(cudaStream_t s, const int32_t *col, int64_t nnz, int32_t d, in
 // Fix-up list: runs of consecutive chunks whose heads continue one run (host-side, tiny).
 // run_id maps a run ordinal to its output slot (null = identity).
 static int build_fix_list(cudaStream_t s, int n_chunks, const int32_t *chunk_lo_dev, const int32_t *head_dev,
-                          const int32_t *run_id_dev, int64_t n_runs, FixEntry **fix_out, int *n_fix_out, int64_t *bytes)
+                          const int32_t *run_id_dev, int64_t n_runs, FixEntry **fix_out, int *n_fix_out, int *n_long_out,
+                          int64_t *bytes)
 {
     std::vector<int32_t> h_lo((size_t)n_chunks + 1), h_head((size_t)n_chunks + 1, 0);
     PML_CUDA(cudaMemcpyAsync(h_lo.data(), chunk_lo_dev, sizeof(int32_t) * (size_t)(n_chunks + 1), cudaMemcpyDeviceToHost, s));
@@ -257,6 +258,7 @@ static int build_fix_list(cudaStream_t s, int n_chunks, const int32_t *chunk_lo_
     }
     *n_fix_out = (int)fix.size();
     *fix_out = nullptr;
+    *n_long_out = 0;
     if (!fix.empty()) {
         if (run_id_dev != nullptr) {
             std::vector<int32_t> h_ids((size_t)n_runs);
@@ -265,6 +267,15 @@ static int build_fix_list(cudaStream_t s, int n_chunks, const int32_t *chunk_lo_
             PML_CUDA(cudaStreamSynchronize(s));
             for (size_t q = 0; q < fix.size(); ++q) fix[q].col = h_ids[(size_t)fix_ord[q]];
         }
+        // long runs first (stable), so the kernel can give them a warp each
+        std::vector<FixEntry> ordered;
+        ordered.reserve(fix.size());
+        for (const FixEntry &e : fix)
+            if (e.chunk_end - e.chunk_begin >= 32) ordered.push_back(e);
+        *n_long_out = (int)ordered.size();
+        for (const FixEntry &e : fix)
+            if (e.chunk_end - e.chunk_begin < 32) ordered.push_back(e);
+        fix.swap(ordered);
         PML_CUDA(cudaMalloc(fix_out, sizeof(FixEntry) * fix.size()));
         PML_CUDA(cudaMemcpyAsync(*fix_out, fix.data(), sizeof(FixEntry) * fix.size(), cudaMemcpyHostToDevice, s));
         PML_CUDA(cudaStreamSynchronize(s));
@@ -372,7 +383,7 @@ int build_transpose(cudaStream_t s, int64_t n, int32_t d, int64_t nnz, const uin
     PML_CUDA(cudaGetLastError());
 
     PML_TRY(build_fix_list(s, n_chunks, out->chunk_col_lo, head.as<int32_t>(), out->nzcol_id, m, &out->fix, &out->n_fix,
-                           &out->bytes));
+                           &out->n_fix_long, &out->bytes));
     return PML_OK;
 }
 
@@ -422,7 +433,7 @@ int build_row_side(cudaStream_t s, int64_t n, int64_t nnz, const uint32_t *row_p
                                                                      out->chunk_lo, head.as<int32_t>());
     PML_CUDA(cudaGetLastError());
     PML_TRY(build_fix_list(s, n_chunks, out->chunk_lo, head.as<int32_t>(), out->nzrow_id, runs, &out->fix, &out->n_fix,
-                           &out->bytes));
+                           &out->n_fix_long, &out->bytes));
     return PML_OK;
 }
 
