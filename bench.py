@@ -284,6 +284,8 @@ def run_ours(args):
         row_bytes, col_bytes = kernel_bytes(info, 0, 0)
         row_ms = profile["row_pass"][0] / max(1, profile["row_pass"][1])
         col_ms = profile["col_pass"][0] / max(1, profile["col_pass"][1])
+        tiled_ms = profile["col_pass_tiled"][0] / max(1, profile["col_pass_tiled"][1])
+        col_ms += tiled_ms   # the CSC pass = tiled hot columns + plain cold columns
         dominant = ("seg_spmv_warp_kernel (CSC pass, X^T r)" if col_ms >= row_ms
                     else ("seg_spmv_warp_kernel (CSR pass, X w)" if info.margin_variant == 1 else
                           "row_pass_kernel<%d lanes/row> (CSR pass, X w + pointwise)" % info.margin_variant))
@@ -311,6 +313,8 @@ def run_ours(args):
                 "parallelism": "row-sharded x%d, one all-reduce of d+2 fp64" % world if world > 1 else "single GPU",
                 "l2_flush": "inputs larger than L2 (%.1f GB streamed per step vs 126 MB L2)" % (step_bytes / 1e9),
                 "row_pass_variant": int(info.margin_variant),
+                "csc_tiling": {"hot_cols": int(info.tiled_hot_cols), "tiles": int(info.tiled_tiles),
+                               "tile_rows": int(info.tiled_tile_rows)},
                 "generate_s": round(t_gen, 2), "pack_s": round(t_pack, 2),
             },
             "e2e": {"value": e2e_steps / e2e_s, "unit": "evals/s", "h2d_bytes_per_step": d * 8,

@@ -64,6 +64,10 @@ typedef struct pml_dataset_info {
     int64_t device_bytes;  /* HBM held by this data set */
     int64_t vg_algorithmic_bytes; /* bytes one value+gradient evaluation must move */
     int64_t hv_algorithmic_bytes; /* same for a cold Hessian-vector product */
+    int32_t tiled_hot_cols; /* columns of the CSC copy tiled by row blocks (0 = plain layout) */
+    int32_t tiled_tiles;    /* row tiles of that layout */
+    int32_t tiled_tile_rows;
+    int32_t reserved;
 } pml_dataset_info;
 
 /* message of the calling thread's last failing call ("" if none) */
@@ -187,6 +191,7 @@ int pml_ctx_launch_count(pml_ctx *ctx, int64_t *out);
 #define PML_K_FIXUP 3    /* fixup_kernel */
 #define PML_K_FINALIZE 4 /* finalize_kernel */
 #define PML_K_EPILOGUE 5 /* row_epilogue_kernel (row-pass variant 1 only) */
+#define PML_K_COL_TILED 6 /* seg_spmv_tiled_kernel: CSC pass over the hot columns, r staged in shared memory */
 #define PML_K_COUNT 8
 int pml_ctx_set_profiling(pml_ctx *ctx, int on);
 int pml_ctx_read_profile(pml_ctx *ctx, double *out_ms /* [PML_K_COUNT] */,

@@ -48,7 +48,9 @@ class DatasetInfo(ctypes.Structure):
     _fields_ = [("n", ctypes.c_int64), ("nnz", ctypes.c_int64), ("d", ctypes.c_int32),
                 ("value_bytes", ctypes.c_int32), ("margin_variant", ctypes.c_int32), ("n_chunks", ctypes.c_int32),
                 ("nonempty_cols", ctypes.c_int64), ("device_bytes", ctypes.c_int64),
-                ("vg_algorithmic_bytes", ctypes.c_int64), ("hv_algorithmic_bytes", ctypes.c_int64)]
+                ("vg_algorithmic_bytes", ctypes.c_int64), ("hv_algorithmic_bytes", ctypes.c_int64),
+                ("tiled_hot_cols", ctypes.c_int32), ("tiled_tiles", ctypes.c_int32), ("tiled_tile_rows", ctypes.c_int32),
+                ("reserved", ctypes.c_int32)]
 
 
 _lib = None
@@ -174,7 +176,7 @@ class Context:
         check(load().pml_ctx_launch_count(self._h, ctypes.byref(v)))
         return v.value
 
-    KERNEL_KINDS = ["prepare_vectors", "row_pass", "col_pass", "fixup", "finalize", "row_epilogue"]
+    KERNEL_KINDS = ["prepare_vectors", "row_pass", "col_pass", "fixup", "finalize", "row_epilogue", "col_pass_tiled"]
 
     def set_profiling(self, on):
         check(load().pml_ctx_set_profiling(self._h, 1 if on else 0))

@@ -115,12 +115,25 @@ int run_col_and_fixup(pml_dataset *ds, bool square, double *out, bool with_scala
 {
     pml_ctx *ctx = ds->ctx;
     cudaStream_t s = ctx->stream;
+    const TiledSide &hot = ds->t.hot;
+    if (hot.n_chunks > 0) {
+        // hot columns: r slices staged in shared memory, per-(tile, column) sums into `partial`
+        PML_CUDA(cudaMemsetAsync(hot.partial, 0, sizeof(double) * (size_t)hot.n_tiles * (size_t)hot.n_hot_cols, s));
+        PML_TRY(run(ctx, PML_K_COL_TILED, [&] {
+            return launch_seg_tiled(s, ctx->sm_count, ds->value_bytes, square, hot, ds->r, ds->n);
+        }));
+        PML_TRY(run(ctx, PML_K_FIXUP, [&] {
+            return launch_fixup(s, hot.fix, hot.n_fix, hot.n_fix_long, hot.carry, hot.partial, nullptr, nullptr, 0, nullptr,
+                                0, false, false);
+        }));
+        PML_TRY(run(ctx, PML_K_FINALIZE, [&] { return launch_reduce_partial(s, hot, ds->t.nzcol_id, out); }));
+    }
     SegParams cp;
     std::memset(&cp, 0, sizeof(cp));
-    cp.nnz = ds->nnz;
+    cp.nnz = ds->t.cold_nnz;
     cp.idx = ds->t.csc_row;
     cp.val = ds->t.csc_val;
-    cp.run_id = ds->t.nzcol_id;
+    cp.run_id = ds->t.cold_run_id;
     cp.chunk_lo = ds->t.chunk_col_lo;
     cp.table = ds->r;
     cp.out = out;
@@ -447,7 +460,8 @@ int pml_dataset_destroy(pml_dataset *ds)
         cudaSetDevice(ds->ctx->device);
         cudaStreamSynchronize(ds->ctx->stream);
     }
-    void *ptrs[] = { ds->row_ptr, ds->col, ds->val, ds->label, ds->offset, ds->weight, ds->t.csc_row, ds->t.csc_val,
+    void *ptrs[] = { ds->row_ptr, ds->col, ds->val, ds->label, ds->offset, ds->weight, ds->t.idx_alloc, ds->t.val_alloc, ds->t.hot.run_id, ds->t.hot.chunk_lo, ds->t.hot.tile_first_chunk, ds->t.hot.fix,
+                     ds->t.hot.partial, ds->t.hot.carry,
                      ds->t.nzcol_ptr, ds->t.nzcol_id, ds->t.rank, ds->t.chunk_col_lo, ds->t.fix, ds->rs.nzrow_id, ds->rs.chunk_lo,
                      ds->rs.fix, ds->za, ds->zb, ds->carry_row, ds->carry_row2, ds->row_loss, ds->factors, ds->shifts, ds->r,
                      ds->dcache, ds->partials, ds->carry_head, ds->raw, ds->vec, ds->shift_partials, ds->io_a, ds->io_b,
@@ -546,7 +560,7 @@ int pml_dataset_create_csr_dev(pml_ctx *ctx, int64_t n, int32_t d, const int64_t
 
     int chunk_entries = 256;  // one chunk per warp (seg_spmv_warp_kernel); PML_SEG_CTA=1 selects CTA-sized chunks
     if (std::getenv("PML_SEG_CTA") != nullptr) chunk_entries = TCHUNK;
-    PML_TRY(build_transpose(s, n, d, nnz, ds->row_ptr, ds->col, ds->val, dst_bytes, chunk_entries, &ds->t));
+    PML_TRY(build_transpose(s, ctx->sm_count, n, d, nnz, ds->row_ptr, ds->col, ds->val, dst_bytes, chunk_entries, &ds->t));
     ds->bytes += ds->t.bytes;
     // after the transpose: from here on the CSR column array carries the row-start flags in bit 31
     PML_TRY(build_row_side(s, n, nnz, ds->row_ptr, ds->col, chunk_entries, &ds->rs));
@@ -626,6 +640,10 @@ int pml_dataset_get_info(const pml_dataset *ds, pml_dataset_info *out)
     out->n_chunks = ds->t.n_chunks;
     out->nonempty_cols = ds->t.m;
     out->device_bytes = ds->bytes;
+    out->tiled_hot_cols = ds->t.hot.n_hot_cols;
+    out->tiled_tiles = ds->t.hot.n_tiles;
+    out->tiled_tile_rows = ds->t.hot.tile_rows;
+    out->reserved = 0;
     const int64_t V = ds->value_bytes, n = ds->n, d = ds->d, nnz = ds->nnz;
     // CSR stream + CSC stream + (y, o, wt) + r written and read + pointers + (read w, write g)
     out->vg_algorithmic_bytes = 2 * nnz * (V + 4) + n * 24 + n * 16 + (n + 1) * 4 + ((int64_t)d + 1) * 4 + (int64_t)d * 16;

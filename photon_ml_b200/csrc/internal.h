@@ -89,6 +89,8 @@ struct FixEntry {
     int32_t chunk_end;
 };
 
+struct TiledSide;
+
 // launchers (kernels.cu); each returns the number of kernels it launched, <0 on launch error
 int launch_prepare_vectors(cudaStream_t s, int d, const double *coef, const double *v, const double *factors,
                            const double *shifts, const int32_t *rank, double *out_vec, double *shift_partials,
@@ -106,6 +108,9 @@ int launch_fixup(cudaStream_t s, const FixEntry *fix, int n_fix, int n_long, con
 int launch_finalize(cudaStream_t s, int d, const double *raw, const double *factors, const double *shifts,
                     double *out_value, double *out_vec);
 
+int launch_seg_tiled(cudaStream_t s, int sm_count, int value_bytes, bool square, const TiledSide &t, const double *r,
+                     int64_t n);
+int launch_reduce_partial(cudaStream_t s, const TiledSide &t, const int32_t *nzcol_id, double *out);
 int launch_offsets_from_scores(cudaStream_t s, int64_t n, const double *base, const double *scores, const int64_t *row_map,
                                double *out);
 int launch_globalize_cols(cudaStream_t s, int64_t n_entities, const int64_t *ent_row_ptr, const int64_t *coef_ptr,
@@ -116,8 +121,11 @@ int launch_entity_values(cudaStream_t s, int64_t n_entities, const int64_t *ent_
 // pack.cu: builds the CSC copy and its chunk metadata on the device
 struct Packed;
 struct RowSide;
-int build_transpose(cudaStream_t s, int64_t n, int32_t d, int64_t nnz, const uint32_t *row_ptr,
+int build_transpose(cudaStream_t s, int sm_count, int64_t n, int32_t d, int64_t nnz, const uint32_t *row_ptr,
                     int32_t *col, const void *val, int value_bytes, int chunk_entries, Packed *out);
+constexpr int TILE_MAX_ROWS = 16000;            // r slice + zero slot <= 128 KB of shared memory
+constexpr int64_t TILE_MIN_ROWS_DEFAULT = 262144;  // below this r lives happily in L2: no tiling
+constexpr int64_t TILE_PARTIAL_BYTES = 64ll << 20; // cap on the (tile, column) partial matrix
 int build_row_side(cudaStream_t s, int64_t n, int64_t nnz, const uint32_t *row_ptr, int32_t *col, int chunk_entries,
                    RowSide *out);
 int narrow_check(cudaStream_t s, const double *val, int64_t nnz, bool *all_exact);
@@ -125,8 +133,31 @@ int convert_values(cudaStream_t s, const void *src, int src_bytes, void *dst, in
 int check_columns(cudaStream_t s, const int32_t *col, int64_t nnz, int32_t d, int64_t *bad);
 int convert_row_ptr(cudaStream_t s, const int64_t *src, uint32_t *dst, int64_t n_plus_1, int64_t *bad);
 
+// Hot columns of the CSC copy, tiled by row blocks so that a CTA gathers r from a slice staged in shared memory.
+struct TiledSide {
+    int32_t *idx = nullptr;        // view into Packed::idx_alloc: row index LOCAL to the tile (tile_rows = the zero slot
+    void *val = nullptr;           //   used by padding), bit 31 on the first entry of each (tile, column) run
+    int64_t len = 0;               // entries incl. padding; every tile starts at a multiple of 256
+    int32_t *run_id = nullptr;     // run ordinal -> slot tile * n_hot_cols + column in `partial`
+    int32_t *chunk_lo = nullptr;   // n_chunks + 1
+    int32_t *tile_first_chunk = nullptr;  // n_tiles + 1
+    FixEntry *fix = nullptr;
+    int n_fix = 0, n_fix_long = 0;
+    int n_chunks = 0;
+    int64_t n_runs = 0;
+    int tile_rows = 0, n_tiles = 0, n_hot_cols = 0;
+    double *partial = nullptr;     // n_tiles * n_hot_cols per-(tile, column) sums, reduced by reduce_partial_kernel
+    double *carry = nullptr;       // n_chunks
+};
+
 struct Packed {
-    int32_t *csc_row = nullptr;    // nnz: row index, bit 31 set on the first entry of each column
+    int32_t *idx_alloc = nullptr;  // one allocation holds [hot tiled region | cold region]
+    void *val_alloc = nullptr;
+    TiledSide hot;
+    // cold region (all columns when nothing is tiled): plain CSC ordered by (internal column, row)
+    int64_t cold_nnz = 0;
+    const int32_t *cold_run_id = nullptr;  // run ordinal -> original column id (= nzcol_id + hot.n_hot_cols)
+    int32_t *csc_row = nullptr;    // view: row index, bit 31 set on the first entry of each column
     void *csc_val = nullptr;
     uint32_t *nzcol_ptr = nullptr; // d+1: entry offset of each internal column (columns >= m are empty)
     int32_t *nzcol_id = nullptr;   // d: internal id -> original column id

@@ -694,6 +694,112 @@ static int launch_seg_warp(cudaStream_t s, int sm_count, size_t smem, const SegP
     return cudaGetLastError() == cudaSuccess ? 1 : -1;
 }
 
+// ------------------------------------------------------------------------------------------
+// seg_spmv_tiled_kernel -- the CSC pass over the hot columns, "staged through shared memory": the rows
+// are cut into tiles of <= 16000, a CTA (1024 threads, one per SM) copies the tile's slice of r into
+// shared memory once and its 32 warps then reduce the tile's warp-chunks with every gather served from
+// shared memory (a scattered 8-byte gather from global memory costs an L1 tag lookup per lane and a
+// 32-byte L2 sector; r is 8*n bytes and does not stay in L2 next to the stream).  One run = one
+// (tile, column) pair; its sum goes to partial[tile][column], reduced over tiles by reduce_partial_kernel.
+// Padding entries at the end of a tile point at the zero slot hot[tile_rows] with value 0.
+// ------------------------------------------------------------------------------------------
+constexpr int ST_THREADS = 1024;
+
+template <typename VT, bool SQUARE>
+__global__ void __launch_bounds__(ST_THREADS, 1)
+seg_spmv_tiled_kernel(const SegParams p, const int32_t *__restrict__ tile_first_chunk, int n_tiles, int tile_rows,
+                      const double *__restrict__ r, int64_t n)
+{
+    constexpr int ITEMS = 8;
+    constexpr int CHUNK = 32 * ITEMS;
+    constexpr int WARPS = ST_THREADS / 32;
+    extern __shared__ __align__(16) double hot[];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const VT *__restrict__ val = static_cast<const VT *>(p.val);
+    const int32_t *__restrict__ idx = p.idx;
+    for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+        __syncthreads();  // every warp is done with the previous tile's slice
+        const int64_t row0 = (int64_t)t * tile_rows;
+        for (int i = tid; i <= tile_rows; i += ST_THREADS) hot[i] = (i < tile_rows && row0 + i < n) ? r[row0 + i] : 0.0;
+        __syncthreads();
+        const int c_end = tile_first_chunk[t + 1];
+        int c = tile_first_chunk[t] + warp;
+        SegRegs<VT, ITEMS> cur;
+        if (c < c_end) seg_load_full<VT, ITEMS>(cur, idx, val, (int64_t)c * CHUNK + lane * ITEMS);
+        for (; c < c_end; c += WARPS) {
+            SegRegs<VT, ITEMS> nxt;
+            const int cn = c + WARPS;
+            if (cn < c_end) seg_load_full<VT, ITEMS>(nxt, idx, val, (int64_t)cn * CHUNK + lane * ITEMS);
+            seg_chunk<VT, ITEMS, false, SQUARE, true, true, true>(p, cur, c, ITEMS, hot, nullptr);
+            cur = nxt;
+        }
+    }
+}
+
+int launch_seg_tiled(cudaStream_t s, int sm_count, int value_bytes, bool square, const TiledSide &t, const double *r,
+                     int64_t n)
+{
+    if (t.n_chunks <= 0) return 0;
+    SegParams p;
+    p.nnz = t.len;
+    p.idx = t.idx;
+    p.val = t.val;
+    p.run_id = t.run_id;
+    p.chunk_lo = t.chunk_lo;
+    p.table = nullptr;
+    p.out = t.partial;
+    p.out2 = nullptr;
+    p.carry = t.carry;
+    p.carry2 = nullptr;
+    p.n_chunks = t.n_chunks;
+    p.n_hot = 0x7fffffff;  // every index is a shared-memory index
+    const size_t smem = sizeof(double) * (size_t)(t.tile_rows + 1);
+    const int grid = t.n_tiles < sm_count ? t.n_tiles : sm_count;
+#define PML_TILED(VT, SQ)                                                                                           \
+    do {                                                                                                            \
+        if (smem > 48 * 1024 && cudaFuncSetAttribute(seg_spmv_tiled_kernel<VT, SQ>,                                 \
+                                                     cudaFuncAttributeMaxDynamicSharedMemorySize,                   \
+                                                     (int)(sizeof(double) * (TILE_MAX_ROWS + 2))) != cudaSuccess)   \
+            return -1;                                                                                              \
+        seg_spmv_tiled_kernel<VT, SQ><<<grid, ST_THREADS, smem, s>>>(p, t.tile_first_chunk, t.n_tiles, t.tile_rows, r, n); \
+    } while (0)
+    if (value_bytes == 4) {
+        if (square) PML_TILED(float, true); else PML_TILED(float, false);
+    } else {
+        if (square) PML_TILED(double, true); else PML_TILED(double, false);
+    }
+#undef PML_TILED
+    return cudaGetLastError() == cudaSuccess ? 1 : -1;
+}
+
+// out[original id of hot column c] = sum over tiles of partial[tile][c], tiles in a fixed order:
+// 8 threads per column stride over the tiles, then a fixed tree over the 8.
+__global__ void __launch_bounds__(256)
+reduce_partial_kernel(int n_tiles, int K, const double *__restrict__ partial, const int32_t *__restrict__ nzcol_id,
+                      double *__restrict__ out)
+{
+    __shared__ double acc[8][33];
+    const int cx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int c = blockIdx.x * 32 + cx;
+    double s = 0.0;
+    if (c < K)
+        for (int t = ty; t < n_tiles; t += 8) s += partial[(size_t)t * K + c];
+    acc[ty][cx] = s;
+    __syncthreads();
+    if (ty == 0 && c < K) {
+        const double total = ((acc[0][cx] + acc[1][cx]) + (acc[2][cx] + acc[3][cx])) +
+                             ((acc[4][cx] + acc[5][cx]) + (acc[6][cx] + acc[7][cx]));
+        out[nzcol_id[c]] = total;
+    }
+}
+
+int launch_reduce_partial(cudaStream_t s, const TiledSide &t, const int32_t *nzcol_id, double *out)
+{
+    if (t.n_hot_cols <= 0) return 0;
+    reduce_partial_kernel<<<(t.n_hot_cols + 31) / 32, 256, 0, s>>>(t.n_tiles, t.n_hot_cols, t.partial, nzcol_id, out);
+    return cudaGetLastError() == cudaSuccess ? 1 : -1;
+}
+
 template <typename VT, int ITEMS, bool TWO, bool SQUARE>
 static int launch_seg_one(cudaStream_t s, int grid, size_t smem, const SegParams &p)
 {

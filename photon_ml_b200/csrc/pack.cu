@@ -9,6 +9,7 @@
 #include <cub/cub.cuh>
 #include <cuda_runtime.h>
 
+#include <cstdlib>
 #include <vector>
 
 #include "internal.h"
@@ -105,7 +106,8 @@ __global__ void mark_starts_kernel(int64_t m, const uint32_t *__restrict__ col_p
 // chunk_col_lo[c] = number of non-empty columns that start before entry c*chunk_entries;
 // head_nonempty[c] = 1 when entry c*chunk_entries is not itself a column start
 __global__ void chunk_meta_kernel(int n_chunks, int chunk_entries, int64_t m, const uint32_t *__restrict__ nzcol_ptr,
-                                  int32_t *__restrict__ chunk_col_lo, int32_t *__restrict__ head_nonempty)
+                                  int32_t *__restrict__ chunk_col_lo, int32_t *__restrict__ head_nonempty,
+                                  uint32_t ptr_offset = 0)
 {
     for (int c = blockIdx.x * blockDim.x + threadIdx.x; c <= n_chunks; c += gridDim.x * blockDim.x) {
         if (c == n_chunks) {
@@ -116,11 +118,11 @@ __global__ void chunk_meta_kernel(int n_chunks, int chunk_entries, int64_t m, co
         int64_t lo = 0, hi = m;
         while (lo < hi) {
             const int64_t mid = (lo + hi) >> 1;
-            if (nzcol_ptr[mid] < base) lo = mid + 1;
+            if (nzcol_ptr[mid] - ptr_offset < base) lo = mid + 1;
             else hi = mid;
         }
         chunk_col_lo[c] = (int32_t)lo;
-        head_nonempty[c] = (lo < m && nzcol_ptr[lo] == base) ? 0 : 1;
+        head_nonempty[c] = (lo < m && nzcol_ptr[lo] - ptr_offset == base) ? 0 : 1;
     }
 }
 
@@ -161,6 +163,70 @@ __global__ void check_cols_kernel(const int32_t *__restrict__ col, int64_t nnz, 
         if (c < 0 || c >= d) ++wrong;
     }
     if (wrong) atomicAdd(bad, (unsigned long long)wrong);
+}
+
+// key of an entry for the tiled layout: hot columns (< K) sort by (row tile, column), cold ones after, by column
+__global__ void tile_keys_kernel(int64_t nnz, const int32_t *__restrict__ col, const int32_t *__restrict__ entry_row,
+                                 int K, int tile_rows, int n_tiles, uint32_t *__restrict__ keys)
+{
+    for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < nnz; k += (int64_t)gridDim.x * blockDim.x) {
+        const int32_t c = col[k];
+        keys[k] = c < K ? (uint32_t)(entry_row[k] / tile_rows) * (uint32_t)K + (uint32_t)c
+                        : (uint32_t)n_tiles * (uint32_t)K + (uint32_t)(c - K);
+    }
+}
+
+// first sorted position whose key is >= t*K, for t in [0, n_tiles]
+__global__ void tile_starts_kernel(int n_tiles, int K, int64_t nnz, const uint32_t *__restrict__ sorted_keys,
+                                   uint32_t *__restrict__ hs)
+{
+    for (int t = blockIdx.x * blockDim.x + threadIdx.x; t <= n_tiles; t += gridDim.x * blockDim.x) {
+        const uint32_t want = (uint32_t)t * (uint32_t)K;
+        int64_t lo = 0, hi = nnz;
+        while (lo < hi) {
+            const int64_t mid = (lo + hi) >> 1;
+            if (sorted_keys[mid] < want) lo = mid + 1;
+            else hi = mid;
+        }
+        hs[t] = (uint32_t)lo;
+    }
+}
+
+__global__ void fill_pad_kernel(int64_t len, int32_t pad_idx, int32_t *__restrict__ idx)
+{
+    for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < len; k += (int64_t)gridDim.x * blockDim.x)
+        idx[k] = pad_idx;
+}
+
+// Moves sorted entry i to its place in [hot tiled | cold]; marks run starts; records, per sorted position,
+// whether a hot run starts there and where it landed (for the run list).
+template <typename VT>
+__global__ void tile_scatter_kernel(int64_t nnz, const uint32_t *__restrict__ sorted_keys, const uint32_t *__restrict__ perm,
+                                    const int32_t *__restrict__ entry_row, const VT *__restrict__ val, int K, int tile_rows,
+                                    int n_tiles, const uint32_t *__restrict__ hs, const uint32_t *__restrict__ po,
+                                    uint32_t cold_off, int32_t *__restrict__ idx, VT *__restrict__ out_val,
+                                    unsigned char *__restrict__ hot_run_flag, uint32_t *__restrict__ hot_dest)
+{
+    const uint32_t hot_keys = (uint32_t)n_tiles * (uint32_t)K;
+    const uint32_t n_hot = hs[n_tiles];
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nnz; i += (int64_t)gridDim.x * blockDim.x) {
+        const uint32_t key = sorted_keys[i];
+        const uint32_t src = perm[i];
+        const bool start = i == 0 || sorted_keys[i - 1] != key;
+        int32_t row = entry_row[src];
+        uint32_t dest;
+        if (key < hot_keys) {
+            const uint32_t t = key / (uint32_t)K;
+            dest = po[t] + ((uint32_t)i - hs[t]);
+            row -= (int32_t)t * tile_rows;
+            hot_run_flag[i] = start ? 1 : 0;
+            hot_dest[i] = dest;
+        } else {
+            dest = cold_off + ((uint32_t)i - n_hot);
+        }
+        idx[dest] = start ? (row | (int32_t)0x80000000) : row;
+        out_val[dest] = val[src];
+    }
 }
 
 inline int grid_for(int64_t n, int block = 256)
@@ -288,30 +354,29 @@ static int build_fix_list(cudaStream_t s, int n_chunks, const int32_t *chunk_lo_
 // non-empty columns are exactly ids [0, m), hottest first; ties keep the original order), the CSR
 // column array is rewritten in place to internal ids, and the CSC copy is built in internal-id
 // order with the first entry of every column marked in bit 31 of its row index.
-int build_transpose(cudaStream_t s, int64_t n, int32_t d, int64_t nnz, const uint32_t *row_ptr,
+static int build_tiled(cudaStream_t s, int sm_count, int64_t n, int64_t nnz, const uint32_t *row_ptr, const int32_t *col,
+                       const void *val, int value_bytes, int chunk_entries, const uint32_t *counts_sorted_dev, Packed *out,
+                       bool *tiled);
+
+int build_transpose(cudaStream_t s, int sm_count, int64_t n, int32_t d, int64_t nnz, const uint32_t *row_ptr,
                     int32_t *col, const void *val, int value_bytes, int chunk_entries, Packed *out)
 {
     out->chunk_entries = chunk_entries;
     out->n_chunks = (int)((nnz + chunk_entries - 1) / chunk_entries);
-    const int n_chunks = out->n_chunks;
+    int n_chunks = out->n_chunks;
     out->bytes = 0;
     const size_t dd = (size_t)d + 1;
 
-    PML_CUDA(cudaMalloc(&out->csc_row, sizeof(int32_t) * (size_t)(nnz + 16)));
-    PML_CUDA(cudaMalloc(&out->csc_val, (size_t)value_bytes * (size_t)(nnz + 16)));
-    PML_CUDA(cudaMalloc(&out->chunk_col_lo, sizeof(int32_t) * (size_t)(n_chunks + 1)));
     PML_CUDA(cudaMalloc(&out->rank, sizeof(int32_t) * dd));
     PML_CUDA(cudaMalloc(&out->nzcol_id, sizeof(int32_t) * dd));
     PML_CUDA(cudaMalloc(&out->nzcol_ptr, sizeof(uint32_t) * (dd + 1)));
-    out->bytes += (int64_t)(sizeof(int32_t) + value_bytes) * (nnz + 16) + (int64_t)sizeof(int32_t) * (n_chunks + 1) +
-                  (int64_t)dd * 12 + 4;
+    out->bytes += (int64_t)dd * 12 + 4;
 
     DevBuf counts, counts_sorted, ids, entry_row, perm_in, perm_out, keys_out, head, tmp, m_dev;
     PML_CUDA(counts.alloc(sizeof(uint32_t) * dd));
     PML_CUDA(counts_sorted.alloc(sizeof(uint32_t) * dd));
     PML_CUDA(ids.alloc(sizeof(int32_t) * dd));
     PML_CUDA(m_dev.alloc(sizeof(unsigned long long)));
-    PML_CUDA(head.alloc(sizeof(int32_t) * (size_t)(n_chunks + 1)));
 
     // 1. entries per column, columns ordered by descending count (stable)
     PML_CUDA(cudaMemsetAsync(counts.p, 0, sizeof(uint32_t) * dd, s));
@@ -345,14 +410,32 @@ int build_transpose(cudaStream_t s, int64_t n, int32_t d, int64_t nnz, const uin
     PML_CUDA(cudaStreamSynchronize(s));
     out->m = (int64_t)m64;
     const int64_t m = out->m;
+    out->cold_nnz = nnz;
+    out->cold_run_id = out->nzcol_id;
+
+    if (nnz > 0) {
+        // CSR columns -> internal ids, in place (both layouts below read them)
+        remap_cols_kernel<<<grid_for(nnz), 256, 0, s>>>(nnz, col, out->rank);
+        PML_CUDA(cudaGetLastError());
+        bool tiled = false;
+        PML_TRY(build_tiled(s, sm_count, n, nnz, row_ptr, col, val, value_bytes, chunk_entries, counts_sorted.as<uint32_t>(),
+                            out, &tiled));
+        if (tiled) return PML_OK;
+    }
+
+    PML_CUDA(cudaMalloc(&out->csc_row, sizeof(int32_t) * (size_t)(nnz + 16)));
+    PML_CUDA(cudaMalloc(&out->csc_val, (size_t)value_bytes * (size_t)(nnz + 16)));
+    out->idx_alloc = out->csc_row;
+    out->val_alloc = out->csc_val;
+    PML_CUDA(cudaMalloc(&out->chunk_col_lo, sizeof(int32_t) * (size_t)(n_chunks + 1)));
+    PML_CUDA(head.alloc(sizeof(int32_t) * (size_t)(n_chunks + 1)));
+    out->bytes += (int64_t)(sizeof(int32_t) + value_bytes) * (nnz + 16) + (int64_t)sizeof(int32_t) * (n_chunks + 1);
 
     if (nnz > 0) {
         PML_CUDA(entry_row.alloc(sizeof(int32_t) * (size_t)nnz));
         PML_CUDA(perm_in.alloc(sizeof(uint32_t) * (size_t)nnz));
         PML_CUDA(perm_out.alloc(sizeof(uint32_t) * (size_t)nnz));
         PML_CUDA(keys_out.alloc(sizeof(int32_t) * (size_t)nnz));
-        // 3. CSR columns -> internal ids, in place
-        remap_cols_kernel<<<grid_for(nnz), 256, 0, s>>>(nnz, col, out->rank);
         expand_rows_kernel<<<grid_for(n * 32), 256, 0, s>>>(n, row_ptr, entry_row.as<int32_t>());
         iota_kernel<<<grid_for(nnz), 256, 0, s>>>(nnz, perm_in.as<uint32_t>());
         PML_CUDA(cudaGetLastError());
@@ -384,6 +467,176 @@ int build_transpose(cudaStream_t s, int64_t n, int32_t d, int64_t nnz, const uin
 
     PML_TRY(build_fix_list(s, n_chunks, out->chunk_col_lo, head.as<int32_t>(), out->nzcol_id, m, &out->fix, &out->n_fix,
                            &out->n_fix_long, &out->bytes));
+    return PML_OK;
+}
+
+
+// The tiled layout: [hot region | cold region] in one allocation.
+//   hot  = entries of the K most frequent columns, ordered by (row tile, column, row); every tile is padded to a
+//          multiple of 256 entries with entries that reference the tile's zero slot (index tile_rows, value 0);
+//          the row index stored is local to the tile.  One run = one (tile, column) pair -> one slot of `partial`.
+//   cold = the remaining columns, ordered by (column, row) as in the plain layout.
+// K: columns with at least 2 entries per tile on average, capped by TILE_PARTIAL_BYTES for the partial matrix.
+static int build_tiled(cudaStream_t s, int sm_count, int64_t n, int64_t nnz, const uint32_t *row_ptr, const int32_t *col,
+                       const void *val, int value_bytes, int chunk_entries, const uint32_t *counts_sorted_dev, Packed *out,
+                       bool *tiled)
+{
+    *tiled = false;
+    if (chunk_entries != 256) return PML_OK;  // the tiled kernel works on warp-sized chunks
+    int64_t min_rows = TILE_MIN_ROWS_DEFAULT;
+    int forced_rows = 0;
+    if (const char *e = std::getenv("PML_TILE_MIN_ROWS")) min_rows = std::atoll(e);
+    if (const char *e = std::getenv("PML_TILE_ROWS")) forced_rows = std::atoi(e);  // tests: small tiles on small data
+    if (std::getenv("PML_NO_TILING") != nullptr || n < min_rows) return PML_OK;
+    const int64_t m = out->m;
+    // tile geometry: a multiple of the SM count when the data is large enough, tiles of <= TILE_MAX_ROWS rows
+    int64_t n_tiles = (n + TILE_MAX_ROWS - 1) / TILE_MAX_ROWS;
+    if (n_tiles > sm_count) n_tiles = (n_tiles + sm_count - 1) / sm_count * sm_count;
+    int tile_rows = (int)((n + n_tiles - 1) / n_tiles);
+    if (forced_rows > 0) tile_rows = forced_rows < TILE_MAX_ROWS ? forced_rows : TILE_MAX_ROWS;
+    n_tiles = (n + tile_rows - 1) / tile_rows;
+    // K from the sorted counts
+    int64_t k_cap = TILE_PARTIAL_BYTES / (8 * n_tiles);
+    if (k_cap > m) k_cap = m;
+    if (k_cap <= 0) return PML_OK;
+    std::vector<uint32_t> h_counts((size_t)k_cap);
+    PML_CUDA(cudaMemcpyAsync(h_counts.data(), counts_sorted_dev, sizeof(uint32_t) * (size_t)k_cap, cudaMemcpyDeviceToHost, s));
+    PML_CUDA(cudaStreamSynchronize(s));
+    int64_t K = 0;
+    while (K < k_cap && (int64_t)h_counts[(size_t)K] >= 2 * n_tiles) ++K;
+    if (K < 16 || n_tiles * K >= (1ll << 31)) return PML_OK;
+
+    DevBuf entry_row, keys, keys_sorted, perm_in, perm_out, tmp, hs_dev, po_dev, run_flag, hot_dest;
+    PML_CUDA(entry_row.alloc(sizeof(int32_t) * (size_t)nnz));
+    PML_CUDA(keys.alloc(sizeof(uint32_t) * (size_t)nnz));
+    PML_CUDA(keys_sorted.alloc(sizeof(uint32_t) * (size_t)nnz));
+    PML_CUDA(perm_in.alloc(sizeof(uint32_t) * (size_t)nnz));
+    PML_CUDA(perm_out.alloc(sizeof(uint32_t) * (size_t)nnz));
+    PML_CUDA(hs_dev.alloc(sizeof(uint32_t) * (size_t)(n_tiles + 1)));
+    PML_CUDA(po_dev.alloc(sizeof(uint32_t) * (size_t)(n_tiles + 1)));
+    expand_rows_kernel<<<grid_for(n * 32), 256, 0, s>>>(n, row_ptr, entry_row.as<int32_t>());
+    iota_kernel<<<grid_for(nnz), 256, 0, s>>>(nnz, perm_in.as<uint32_t>());
+    tile_keys_kernel<<<grid_for(nnz), 256, 0, s>>>(nnz, col, entry_row.as<int32_t>(), (int)K, tile_rows, (int)n_tiles,
+                                                   keys.as<uint32_t>());
+    PML_CUDA(cudaGetLastError());
+    const int64_t max_key = n_tiles * K + (m - K);
+    int end_bit = 1;
+    while (end_bit < 32 && (1LL << end_bit) <= max_key) ++end_bit;
+    size_t tmp_bytes = 0;
+    PML_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys.as<uint32_t>(), keys_sorted.as<uint32_t>(),
+                                             perm_in.as<uint32_t>(), perm_out.as<uint32_t>(), nnz, 0, end_bit, s));
+    PML_CUDA(tmp.alloc(tmp_bytes));
+    PML_CUDA(cub::DeviceRadixSort::SortPairs(tmp.p, tmp_bytes, keys.as<uint32_t>(), keys_sorted.as<uint32_t>(),
+                                             perm_in.as<uint32_t>(), perm_out.as<uint32_t>(), nnz, 0, end_bit, s));
+    tile_starts_kernel<<<grid_for(n_tiles + 1), 256, 0, s>>>((int)n_tiles, (int)K, nnz, keys_sorted.as<uint32_t>(),
+                                                             hs_dev.as<uint32_t>());
+    PML_CUDA(cudaGetLastError());
+    std::vector<uint32_t> hs((size_t)n_tiles + 1), po((size_t)n_tiles + 1, 0);
+    PML_CUDA(cudaMemcpyAsync(hs.data(), hs_dev.p, sizeof(uint32_t) * (size_t)(n_tiles + 1), cudaMemcpyDeviceToHost, s));
+    PML_CUDA(cudaStreamSynchronize(s));
+    std::vector<int32_t> first_chunk((size_t)n_tiles + 1, 0);
+    for (int64_t t = 0; t < n_tiles; ++t) {
+        const uint64_t cnt = hs[(size_t)t + 1] - hs[(size_t)t];
+        const uint64_t padded = (cnt + 255) / 256 * 256;
+        if ((uint64_t)po[(size_t)t] + padded > 4000000000ull) return PML_OK;  // would not fit 32-bit offsets: stay untiled
+        po[(size_t)t + 1] = po[(size_t)t] + (uint32_t)padded;
+        first_chunk[(size_t)t + 1] = (int32_t)(po[(size_t)t + 1] / 256);
+    }
+    const int64_t n_hot = hs[(size_t)n_tiles];
+    const int64_t hot_len = po[(size_t)n_tiles];
+    const int64_t cold_nnz = nnz - n_hot;
+    const int64_t total = hot_len + cold_nnz;
+    PML_CUDA(cudaMemcpyAsync(po_dev.p, po.data(), sizeof(uint32_t) * (size_t)(n_tiles + 1), cudaMemcpyHostToDevice, s));
+
+    TiledSide &h = out->hot;
+    PML_CUDA(cudaMalloc(&out->idx_alloc, sizeof(int32_t) * (size_t)(total + 16)));
+    PML_CUDA(cudaMalloc(&out->val_alloc, (size_t)value_bytes * (size_t)(total + 16)));
+    out->bytes += (int64_t)(sizeof(int32_t) + value_bytes) * (total + 16);
+    PML_CUDA(cudaMemsetAsync(out->val_alloc, 0, (size_t)value_bytes * (size_t)(total + 16), s));
+    PML_CUDA(cudaMemsetAsync(out->idx_alloc + hot_len, 0, sizeof(int32_t) * (size_t)(cold_nnz + 16), s));
+    fill_pad_kernel<<<grid_for(hot_len), 256, 0, s>>>(hot_len, tile_rows, out->idx_alloc);
+    PML_CUDA(run_flag.alloc((size_t)(n_hot + 1)));
+    PML_CUDA(hot_dest.alloc(sizeof(uint32_t) * (size_t)(n_hot + 1)));
+    if (value_bytes == 4)
+        tile_scatter_kernel<float><<<grid_for(nnz), 256, 0, s>>>(
+            nnz, keys_sorted.as<uint32_t>(), perm_out.as<uint32_t>(), entry_row.as<int32_t>(), (const float *)val, (int)K,
+            tile_rows, (int)n_tiles, hs_dev.as<uint32_t>(), po_dev.as<uint32_t>(), (uint32_t)hot_len, out->idx_alloc,
+            (float *)out->val_alloc, run_flag.as<unsigned char>(), hot_dest.as<uint32_t>());
+    else
+        tile_scatter_kernel<double><<<grid_for(nnz), 256, 0, s>>>(
+            nnz, keys_sorted.as<uint32_t>(), perm_out.as<uint32_t>(), entry_row.as<int32_t>(), (const double *)val, (int)K,
+            tile_rows, (int)n_tiles, hs_dev.as<uint32_t>(), po_dev.as<uint32_t>(), (uint32_t)hot_len, out->idx_alloc,
+            (double *)out->val_alloc, run_flag.as<unsigned char>(), hot_dest.as<uint32_t>());
+    PML_CUDA(cudaGetLastError());
+
+    // hot run list: positions (padded coordinates) and partial slots (= keys) of the run starts
+    DevBuf n_sel, run_ptr_hot;
+    PML_CUDA(n_sel.alloc(sizeof(int)));
+    PML_CUDA(run_ptr_hot.alloc(sizeof(uint32_t) * (size_t)(n_hot + 2)));
+    PML_CUDA(cudaMalloc(&h.run_id, sizeof(int32_t) * (size_t)(n_hot + 2)));  // trimmed below would need a copy: keep
+    {
+        DevBuf t1;
+        size_t tb = 0;
+        PML_CUDA(cub::DeviceSelect::Flagged(nullptr, tb, hot_dest.as<uint32_t>(), run_flag.as<unsigned char>(),
+                                            run_ptr_hot.as<uint32_t>(), n_sel.as<int>(), (int)n_hot, s));
+        PML_CUDA(t1.alloc(tb));
+        PML_CUDA(cub::DeviceSelect::Flagged(t1.p, tb, hot_dest.as<uint32_t>(), run_flag.as<unsigned char>(),
+                                            run_ptr_hot.as<uint32_t>(), n_sel.as<int>(), (int)n_hot, s));
+        PML_CUDA(cub::DeviceSelect::Flagged(t1.p, tb, reinterpret_cast<const int32_t *>(keys_sorted.as<uint32_t>()),
+                                            run_flag.as<unsigned char>(), h.run_id, n_sel.as<int>(), (int)n_hot, s));
+    }
+    int runs_hot = 0;
+    PML_CUDA(cudaMemcpyAsync(&runs_hot, n_sel.p, sizeof(int), cudaMemcpyDeviceToHost, s));
+    PML_CUDA(cudaStreamSynchronize(s));
+    const uint32_t hot_len32 = (uint32_t)hot_len;
+    PML_CUDA(cudaMemcpyAsync(run_ptr_hot.as<uint32_t>() + runs_hot, &hot_len32, sizeof(uint32_t), cudaMemcpyHostToDevice, s));
+    out->bytes += (int64_t)sizeof(int32_t) * (n_hot + 2);
+
+    h.idx = out->idx_alloc;
+    h.val = out->val_alloc;
+    h.len = hot_len;
+    h.n_runs = runs_hot;
+    h.n_chunks = (int)(hot_len / 256);
+    h.tile_rows = tile_rows;
+    h.n_tiles = (int)n_tiles;
+    h.n_hot_cols = (int)K;
+    PML_CUDA(cudaMalloc(&h.chunk_lo, sizeof(int32_t) * (size_t)(h.n_chunks + 1)));
+    PML_CUDA(cudaMalloc(&h.tile_first_chunk, sizeof(int32_t) * (size_t)(n_tiles + 1)));
+    PML_CUDA(cudaMalloc(&h.partial, sizeof(double) * (size_t)(n_tiles * K)));
+    PML_CUDA(cudaMalloc(&h.carry, sizeof(double) * (size_t)(h.n_chunks + 1)));
+    out->bytes += (int64_t)sizeof(int32_t) * (h.n_chunks + 1 + n_tiles + 1) + (int64_t)sizeof(double) * (n_tiles * K + h.n_chunks + 1);
+    PML_CUDA(cudaMemcpyAsync(h.tile_first_chunk, first_chunk.data(), sizeof(int32_t) * (size_t)(n_tiles + 1),
+                             cudaMemcpyHostToDevice, s));
+    {
+        DevBuf head;
+        PML_CUDA(head.alloc(sizeof(int32_t) * (size_t)(h.n_chunks + 1)));
+        chunk_meta_kernel<<<grid_for((int64_t)h.n_chunks + 1), 256, 0, s>>>(h.n_chunks, 256, runs_hot, run_ptr_hot.as<uint32_t>(),
+                                                                           h.chunk_lo, head.as<int32_t>());
+        PML_CUDA(cudaGetLastError());
+        PML_TRY(build_fix_list(s, h.n_chunks, h.chunk_lo, head.as<int32_t>(), h.run_id, runs_hot, &h.fix, &h.n_fix,
+                               &h.n_fix_long, &out->bytes));
+    }
+
+    // cold region: plain CSC over internal columns [K, m)
+    out->csc_row = out->idx_alloc + hot_len;
+    out->csc_val = (char *)out->val_alloc + (size_t)hot_len * value_bytes;
+    out->cold_nnz = cold_nnz;
+    out->cold_run_id = out->nzcol_id + K;
+    out->n_chunks = (int)((cold_nnz + 255) / 256);
+    PML_CUDA(cudaMalloc(&out->chunk_col_lo, sizeof(int32_t) * (size_t)(out->n_chunks + 1)));
+    out->bytes += (int64_t)sizeof(int32_t) * (out->n_chunks + 1);
+    {
+        DevBuf head;
+        PML_CUDA(head.alloc(sizeof(int32_t) * (size_t)(out->n_chunks + 1)));
+        chunk_meta_kernel<<<grid_for((int64_t)out->n_chunks + 1), 256, 0, s>>>(out->n_chunks, 256, m - K, out->nzcol_ptr + K,
+                                                                              out->chunk_col_lo, head.as<int32_t>(),
+                                                                              (uint32_t)n_hot);
+        PML_CUDA(cudaGetLastError());
+        PML_TRY(build_fix_list(s, out->n_chunks, out->chunk_col_lo, head.as<int32_t>(), out->cold_run_id, m - K, &out->fix,
+                               &out->n_fix, &out->n_fix_long, &out->bytes));
+    }
+    PML_CUDA(cudaStreamSynchronize(s));
+    *tiled = true;
     return PML_OK;
 }
 

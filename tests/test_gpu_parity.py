@@ -20,6 +20,18 @@ LOSSES = [oracle.LOGISTIC, oracle.POISSON, oracle.SQUARED]
 VARIANTS = [0, 1, 2, 4, 8, 16, 32]
 
 
+@pytest.fixture(autouse=True, params=["plain-csc", "tiled-csc"])
+def csc_layout(request, monkeypatch):
+    """Every test runs with the plain CSC layout and with the row-tiled one (hot columns gathered from
+    shared-memory slices of r), forced onto these small inputs with tiny tiles."""
+    if request.param == "tiled-csc":
+        monkeypatch.setenv("PML_TILE_MIN_ROWS", "0")
+        monkeypatch.setenv("PML_TILE_ROWS", "37")
+    else:
+        monkeypatch.setenv("PML_NO_TILING", "1")
+    yield
+
+
 @pytest.fixture(scope="module")
 def ctx():
     import photon_ml_b200 as pml
@@ -72,7 +84,12 @@ def test_a1a_shaped_logistic_all_row_variants(ctx, variant):
     # config 1 of BASELINE.json: the first 1605 rows of the reference's a9a fixture + intercept
     n, d, row_ptr, col, val, label = _a9a()
     ds, ref = _pair(ctx, n, d, row_ptr, col, val, label)
-    assert ds.info().value_bytes == 4  # all values are exactly 1.0
+    info = ds.info()
+    assert info.value_bytes == 4  # all values are exactly 1.0
+    if os.environ.get("PML_TILE_ROWS"):   # the tiled layout really is in use in the tiled-csc runs
+        assert info.tiled_hot_cols >= 16 and info.tiled_tiles == (n + 36) // 37 and info.tiled_tile_rows == 37
+    else:
+        assert info.tiled_hot_cols == 0
     ds.set_margin_variant(variant)
     _check_all(ds, ref, oracle.LOGISTIC, np.random.default_rng(1))
     ds.close()
