@@ -123,9 +123,9 @@ struct Packed;
 struct RowSide;
 int build_transpose(cudaStream_t s, int sm_count, int64_t n, int32_t d, int64_t nnz, const uint32_t *row_ptr,
                     int32_t *col, const void *val, int value_bytes, int chunk_entries, Packed *out);
-constexpr int TILE_MAX_ROWS = 16000;            // r slice + zero slot <= 128 KB of shared memory
+constexpr int TILE_MAX_ROWS = 25000;            // r slice + zero slot <= 200 KB of shared memory (one CTA per SM)
 constexpr int64_t TILE_MIN_ROWS_DEFAULT = 262144;  // below this r lives happily in L2: no tiling
-constexpr int64_t TILE_PARTIAL_BYTES = 64ll << 20; // cap on the (tile, column) partial matrix
+constexpr int64_t TILE_PARTIAL_BYTES = 128ll << 20; // cap on the (tile, column) partial matrix
 int build_row_side(cudaStream_t s, int64_t n, int64_t nnz, const uint32_t *row_ptr, int32_t *col, int chunk_entries,
                    RowSide *out);
 int narrow_check(cudaStream_t s, const double *val, int64_t nnz, bool *all_exact);

@@ -759,7 +759,7 @@ int launch_seg_tiled(cudaStream_t s, int sm_count, int value_bytes, bool square,
     do {                                                                                                            \
         if (smem > 48 * 1024 && cudaFuncSetAttribute(seg_spmv_tiled_kernel<VT, SQ>,                                 \
                                                      cudaFuncAttributeMaxDynamicSharedMemorySize,                   \
-                                                     (int)(sizeof(double) * (TILE_MAX_ROWS + 2))) != cudaSuccess)   \
+                                                     (int)(sizeof(double) * 28002)) != cudaSuccess)   \
             return -1;                                                                                              \
         seg_spmv_tiled_kernel<VT, SQ><<<grid, ST_THREADS, smem, s>>>(p, t.tile_first_chunk, t.n_tiles, t.tile_rows, r, n); \
     } while (0)

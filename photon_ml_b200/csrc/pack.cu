@@ -489,14 +489,18 @@ static int build_tiled(cudaStream_t s, int sm_count, int64_t n, int64_t nnz, con
     if (const char *e = std::getenv("PML_TILE_ROWS")) forced_rows = std::atoi(e);  // tests: small tiles on small data
     if (std::getenv("PML_NO_TILING") != nullptr || n < min_rows) return PML_OK;
     const int64_t m = out->m;
-    // tile geometry: a multiple of the SM count when the data is large enough, tiles of <= TILE_MAX_ROWS rows
-    int64_t n_tiles = (n + TILE_MAX_ROWS - 1) / TILE_MAX_ROWS;
+    int64_t max_rows = TILE_MAX_ROWS, partial_bytes = TILE_PARTIAL_BYTES;
+    if (const char *e = std::getenv("PML_TILE_MAX_ROWS")) max_rows = std::atoll(e);        // tuning knobs
+    if (const char *e = std::getenv("PML_TILE_PARTIAL_MB")) partial_bytes = std::atoll(e) << 20;
+    if (max_rows > 28000) max_rows = 28000;  // 227 KB of shared memory
+    // tile geometry: a multiple of the SM count when the data is large enough, tiles of <= max_rows rows
+    int64_t n_tiles = (n + max_rows - 1) / max_rows;
     if (n_tiles > sm_count) n_tiles = (n_tiles + sm_count - 1) / sm_count * sm_count;
     int tile_rows = (int)((n + n_tiles - 1) / n_tiles);
-    if (forced_rows > 0) tile_rows = forced_rows < TILE_MAX_ROWS ? forced_rows : TILE_MAX_ROWS;
+    if (forced_rows > 0) tile_rows = forced_rows < max_rows ? forced_rows : (int)max_rows;
     n_tiles = (n + tile_rows - 1) / tile_rows;
     // K from the sorted counts
-    int64_t k_cap = TILE_PARTIAL_BYTES / (8 * n_tiles);
+    int64_t k_cap = partial_bytes / (8 * n_tiles);
     if (k_cap > m) k_cap = m;
     if (k_cap <= 0) return PML_OK;
     std::vector<uint32_t> h_counts((size_t)k_cap);
