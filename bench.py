@@ -339,6 +339,7 @@ def run_ours(args):
             out["cpu_baseline"] = cpu_baseline(steps=10, warmup=2)
         if world == 1 and not args.no_convergence:
             out["convergence"] = convergence(ctx, ds, d)
+            out["random_effect_batch"] = random_effect_batch(ctx)
         emit(out)
     ds.close()
     if world > 1:
@@ -398,6 +399,57 @@ def convergence(ctx, ds, d):
     lat["cpu_oracle_1_thread_us"] = 1e6 * (time.perf_counter() - t0) / 300
     out["configs0_a1a_us_per_evaluation"] = lat
     small.close()
+    return out
+
+
+def random_effect_batch(ctx):
+    """configs[4]-shaped per-entity batch at 1/10 scale: 1 M entities, power-law rows per entity (mean ~4),
+    10 entries per row in a 32-dimensional per-entity space; every entity's value+gradient in one call."""
+    import photon_ml_b200 as pml
+    rng = np.random.default_rng(5)
+    n_ent, k, d_e = 1_000_000, 10, 32
+    rows = np.minimum(rng.zipf(1.8, size=n_ent), 2000).astype(np.int64)
+    ent_row_ptr = np.concatenate([[0], np.cumsum(rows)]).astype(np.int64)
+    n = int(ent_row_ptr[-1])
+    col = np.sort(rng.integers(0, d_e, size=(n, k), dtype=np.int32), axis=1).ravel()
+    row_ptr = np.arange(n + 1, dtype=np.int64) * k
+    val = np.ones(n * k, dtype=np.float32)
+    label = (rng.random(n) < 0.1).astype(np.float64)
+    t0 = time.perf_counter()
+    batch = pml.Batch(ctx, ent_row_ptr, np.full(n_ent, d_e, np.int32), row_ptr, col, val, label)
+    t_pack = time.perf_counter() - t0
+    coefs = rng.normal(scale=0.2, size=batch.d_total)
+    for _ in range(3):
+        batch.value_and_gradient(pml.LOGISTIC, coefs)
+    reps = 10
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        batch.value_and_gradient(pml.LOGISTIC, coefs)
+    per = (time.perf_counter() - t0) / reps
+    ctx.read_profile()
+    ctx.set_profiling(True)
+    batch.value_and_gradient(pml.LOGISTIC, coefs)
+    prof = ctx.read_profile()
+    ctx.set_profiling(False)
+    import torch
+    dev = torch.device("cuda", ctx.device)
+    t_coef = torch.tensor(coefs, device=dev)
+    t_val = torch.empty(n_ent, dtype=torch.float64, device=dev)
+    t_grad = torch.empty(batch.d_total, dtype=torch.float64, device=dev)
+    torch.cuda.synchronize()
+    for _ in range(3):
+        batch.value_and_gradient_dev(pml.LOGISTIC, t_coef.data_ptr(), t_val.data_ptr(), t_grad.data_ptr())
+    ctx.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        batch.value_and_gradient_dev(pml.LOGISTIC, t_coef.data_ptr(), t_val.data_ptr(), t_grad.data_ptr())
+    ctx.synchronize()
+    per_dev = (time.perf_counter() - t0) / reps
+    out = {"entities": n_ent, "rows": n, "entries": n * k, "coefficients": int(batch.d_total), "pack_s": round(t_pack, 2),
+           "ms_per_batch_evaluation_host_buffers": 1e3 * per, "entity_evaluations_per_s_host_buffers": n_ent / per,
+           "ms_per_batch_evaluation_device_buffers": 1e3 * per_dev, "entity_evaluations_per_s_device_buffers": n_ent / per_dev,
+           "device_ms": {kk: vv[0] for kk, vv in prof.items() if vv[1]}}
+    batch.close()
     return out
 
 

@@ -49,6 +49,9 @@ extern "C" {
 #define PML_STORE_F32 0  /* 4 B/value; PML_EINVAL if a value is not exactly representable */
 #define PML_STORE_F64 1  /* 8 B/value, bit-exact for any Double the reference could hold */
 #define PML_STORE_AUTO 2 /* F32 when every value survives the round trip, else F64 */
+/* OR-ed into `storage`: do not renumber columns by frequency -- for data whose column order already
+ * carries locality (the block-diagonal batches of per-entity problems use it internally) */
+#define PML_KEEP_COLUMN_ORDER_FLAG 0x100
 
 typedef struct pml_ctx pml_ctx;
 typedef struct pml_dataset pml_dataset;
@@ -191,6 +194,7 @@ int pml_ctx_launch_count(pml_ctx *ctx, int64_t *out);
 #define PML_K_FIXUP 3    /* fixup_kernel */
 #define PML_K_FINALIZE 4 /* finalize_kernel */
 #define PML_K_EPILOGUE 5 /* row_epilogue_kernel (row-pass variant 1 only) */
+#define PML_K_ENTITY 7   /* entity_values_kernel (per-entity objective values of a batch) */
 #define PML_K_COL_TILED 6 /* seg_spmv_tiled_kernel: CSC pass over the hot columns, r staged in shared memory */
 #define PML_K_COUNT 8
 int pml_ctx_set_profiling(pml_ctx *ctx, int on);
@@ -226,6 +230,10 @@ int pml_batch_coef_ptr(pml_batch *b, int64_t *out /* E+1 */);
 /* out_values[e] = entity e's objective value; out_grads (may be NULL) = concatenated gradients */
 int pml_batch_value_and_gradient(pml_batch *b, int loss, const double *coefs, double *out_values,
                                  double *out_grads);
+/* same with device buffers (asynchronous on the context's stream): what a device-resident batched
+ * optimizer calls every iteration -- no per-call transfer of the concatenated coefficient vector */
+int pml_batch_value_and_gradient_dev(pml_batch *b, int loss, const double *coefs_dev,
+                                     double *out_values_dev, double *out_grads_dev);
 
 /* ---- evaluation without any allocation ------------------------------------------------------ */
 /* No counterpart in the reference (the JVM allocates freely); this exists for callers of THIS

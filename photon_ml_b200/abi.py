@@ -26,7 +26,7 @@ SYMBOLS = [
     "pml_finalize_dev", "pml_value_and_gradient_dev", "pml_hessian_vector_dev", "pml_ctx_launch_count",
     "pml_dataset_set_margin_variant", "pml_ctx_set_profiling", "pml_ctx_read_profile",
     "pml_value_noalloc_dev", "pml_batch_create_csr", "pml_batch_destroy", "pml_batch_dataset", "pml_batch_coef_ptr",
-    "pml_batch_value_and_gradient", "pml_scores_dev", "pml_dataset_set_offsets_dev", "pml_offsets_from_scores_dev",
+    "pml_batch_value_and_gradient", "pml_batch_value_and_gradient_dev", "pml_scores_dev", "pml_dataset_set_offsets_dev", "pml_offsets_from_scores_dev",
 ]
 
 
@@ -105,6 +105,7 @@ def load():
         "pml_batch_dataset": [vp, pp],
         "pml_batch_coef_ptr": [vp, vp],
         "pml_batch_value_and_gradient": [vp, ctypes.c_int, vp, vp, vp],
+        "pml_batch_value_and_gradient_dev": [vp, ctypes.c_int, vp, vp, vp],
         "pml_scores_dev": [vp, vp, vp],
         "pml_dataset_set_offsets_dev": [vp, vp],
         "pml_offsets_from_scores_dev": [vp, i64, vp, vp, vp, vp],
@@ -176,7 +177,8 @@ class Context:
         check(load().pml_ctx_launch_count(self._h, ctypes.byref(v)))
         return v.value
 
-    KERNEL_KINDS = ["prepare_vectors", "row_pass", "col_pass", "fixup", "finalize", "row_epilogue", "col_pass_tiled"]
+    KERNEL_KINDS = ["prepare_vectors", "row_pass", "col_pass", "fixup", "finalize", "row_epilogue", "col_pass_tiled",
+                    "entity_values"]
 
     def set_profiling(self, on):
         check(load().pml_ctx_set_profiling(self._h, 1 if on else 0))
@@ -361,6 +363,10 @@ class Batch:
         grads = np.empty(self.d_total, dtype=np.float64) if want_gradient else None
         check(load().pml_batch_value_and_gradient(self._h, loss, _ptr(coefs), _ptr(values), _ptr(grads)))
         return values, grads
+
+    def value_and_gradient_dev(self, loss, coefs_dev, out_values_dev, out_grads_dev):
+        """Device buffers (integer addresses); asynchronous on the context's stream."""
+        check(load().pml_batch_value_and_gradient_dev(self._h, loss, coefs_dev, out_values_dev, out_grads_dev))
 
     def hessian_vector(self, loss, coefs, vs, tag=0):
         return self.dataset.hessian_vector(loss, coefs, vs, tag=tag)

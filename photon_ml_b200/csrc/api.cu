@@ -482,6 +482,8 @@ int pml_dataset_create_csr_dev(pml_ctx *ctx, int64_t n, int32_t d, const int64_t
     if (n < 0 || d < 0) return fail(PML_EINVAL, "negative size");
     if (n > 0 && (!row_ptr_dev || !labels_dev)) return fail(PML_EINVAL, "row_ptr and labels are required");
     if (values_dtype != PML_F32 && values_dtype != PML_F64) return fail(PML_EINVAL, "values_dtype must be PML_F32 or PML_F64");
+    const int storage_arg = storage;
+    storage &= ~PML_KEEP_COLUMN_ORDER_FLAG;
     if (storage < PML_STORE_F32 || storage > PML_STORE_AUTO) return fail(PML_EINVAL, "unknown storage mode");
     Guard g(ctx);
     PML_CUDA(cudaSetDevice(ctx->device));
@@ -560,7 +562,8 @@ int pml_dataset_create_csr_dev(pml_ctx *ctx, int64_t n, int32_t d, const int64_t
 
     int chunk_entries = 256;  // one chunk per warp (seg_spmv_warp_kernel); PML_SEG_CTA=1 selects CTA-sized chunks
     if (std::getenv("PML_SEG_CTA") != nullptr) chunk_entries = TCHUNK;
-    PML_TRY(build_transpose(s, ctx->sm_count, n, d, nnz, ds->row_ptr, ds->col, ds->val, dst_bytes, chunk_entries, &ds->t));
+    PML_TRY(build_transpose(s, ctx->sm_count, n, d, nnz, ds->row_ptr, ds->col, ds->val, dst_bytes, chunk_entries,
+                            (storage_arg & PML_KEEP_COLUMN_ORDER_FLAG) == 0, &ds->t));
     ds->bytes += ds->t.bytes;
     // after the transpose: from here on the CSR column array carries the row-start flags in bit 31
     PML_TRY(build_row_side(s, n, nnz, ds->row_ptr, ds->col, chunk_entries, &ds->rs));
@@ -1011,8 +1014,9 @@ int pml_batch_create_csr(pml_ctx *ctx, int64_t n_entities, const int64_t *ent_ro
         PML_CUDA(cudaStreamSynchronize(s));
         if (bad) return fail(PML_EINVAL, "local column index outside [0, ent_dim[e]): " + std::to_string(bad) + " entries");
     }
+    // block-diagonal: keep the column order (entity by entity), so an entity's coefficients stay contiguous
     PML_TRY(pml_dataset_create_csr_dev(ctx, n, (int32_t)d_total, (const int64_t *)t_rp.p, (const int32_t *)t_col.p, t_val.p,
-                                       values_dtype, storage, (const double *)t_lab.p, (const double *)t_off.p,
+                                       values_dtype, storage | PML_KEEP_COLUMN_ORDER_FLAG, (const double *)t_lab.p, (const double *)t_off.p,
                                        (const double *)t_wt.p, &b->ds));
     {
         Guard g(ctx);
@@ -1051,6 +1055,29 @@ int pml_batch_coef_ptr(pml_batch *b, int64_t *out)
     return PML_OK;
 }
 
+int pml_batch_value_and_gradient_dev(pml_batch *b, int loss, const double *coefs_dev, double *out_values_dev,
+                                     double *out_grads_dev)
+{
+    if (!b || !b->ds) return fail(PML_EINVAL, "null batch handle");
+    pml_dataset *ds = b->ds;
+    if (!valid_loss(loss)) return fail(PML_EINVAL, "unknown loss");
+    if ((!coefs_dev && ds->d > 0) || (!out_values_dev && b->n_entities > 0)) return fail(PML_EINVAL, "null buffer");
+    Guard g(ds->ctx);
+    PML_CUDA(cudaSetDevice(ds->ctx->device));
+    cudaStream_t s = ds->ctx->stream;
+    double *raw = ds->raw;
+    ds->want_row_loss = true;
+    const int rc = vg_raw(ds, loss, coefs_dev, raw, out_grads_dev != nullptr);
+    ds->want_row_loss = false;
+    PML_TRY(rc);
+    PML_TRY(run(ds->ctx, PML_K_ENTITY, [&] {
+        return launch_entity_values(s, b->n_entities, b->ent_row_ptr, ds->row_loss, out_values_dev);
+    }));
+    if (out_grads_dev && ds->d > 0)
+        PML_CUDA(cudaMemcpyAsync(out_grads_dev, ds->raw, sizeof(double) * (size_t)ds->d, cudaMemcpyDeviceToDevice, s));
+    return PML_OK;
+}
+
 int pml_batch_value_and_gradient(pml_batch *b, int loss, const double *coefs, double *out_values, double *out_grads)
 {
     if (!b || !b->ds) return fail(PML_EINVAL, "null batch handle");
@@ -1066,7 +1093,7 @@ int pml_batch_value_and_gradient(pml_batch *b, int loss, const double *coefs, do
     const int rc = vg_raw(ds, loss, ds->io_a, ds->raw);
     ds->want_row_loss = false;
     PML_TRY(rc);
-    PML_TRY(run(ds->ctx, PML_K_EPILOGUE, [&] {
+    PML_TRY(run(ds->ctx, PML_K_ENTITY, [&] {
         return launch_entity_values(s, b->n_entities, b->ent_row_ptr, ds->row_loss, b->ent_values);
     }));
     if (out_grads && ds->d > 0) PML_CUDA(cudaMemcpyAsync(out_grads, ds->raw, db, cudaMemcpyDeviceToHost, s));

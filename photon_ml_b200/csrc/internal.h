@@ -122,7 +122,7 @@ int launch_entity_values(cudaStream_t s, int64_t n_entities, const int64_t *ent_
 struct Packed;
 struct RowSide;
 int build_transpose(cudaStream_t s, int sm_count, int64_t n, int32_t d, int64_t nnz, const uint32_t *row_ptr,
-                    int32_t *col, const void *val, int value_bytes, int chunk_entries, Packed *out);
+                    int32_t *col, const void *val, int value_bytes, int chunk_entries, bool renumber, Packed *out);
 constexpr int TILE_MAX_ROWS = 25000;            // r slice + zero slot <= 200 KB of shared memory (one CTA per SM)
 constexpr int64_t TILE_MIN_ROWS_DEFAULT = 262144;  // below this r lives happily in L2: no tiling
 constexpr int64_t TILE_PARTIAL_BYTES = 128ll << 20; // cap on the (tile, column) partial matrix
@@ -245,6 +245,7 @@ struct pml_dataset {
     int cached_loss = -1;
     bool cache_valid = false;
     int lanes_per_row = 8;  // lanes-per-row variant used for paired (Hessian-vector, cold) passes, or the forced variant
+    bool keep_column_order = false;  // batches: columns are compacted, not renumbered by frequency
     bool variant_forced = false;  // pml_dataset_set_margin_variant pinned one variant for every pass
     int row_threads = 256;  // CTA shape of the warp-oriented row pass (256 or 1024)
     int row_hot_cap = 0;    // cap on its shared-memory hot table (-1 = as much as fits)

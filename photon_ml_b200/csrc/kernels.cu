@@ -1091,18 +1091,38 @@ int launch_globalize_cols(cudaStream_t s, int64_t n_entities, const int64_t *ent
     return cudaGetLastError() == cudaSuccess ? 1 : -1;
 }
 
-// value_e = sum over the entity's rows, lanes striding rows then a fixed shuffle tree
+// value_e = sum of the per-row wt*l over the entity's rows.  A warp takes 32 entities: a lane adds up its
+// own entity when it is small (the common case: a handful of rows), and entities with >= 64 rows are then
+// summed by the whole warp, lanes striding rows, with a fixed shuffle tree.  Fixed order either way.
 __global__ void entity_values_kernel(int64_t n_entities, const int64_t *__restrict__ ent_row_ptr,
                                      const double *__restrict__ row_loss, double *__restrict__ out)
 {
     const int lane = threadIdx.x & 31;
-    int64_t e = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const int64_t nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
-    for (; e < n_entities; e += nw) {
-        double s = 0.0;
-        for (int64_t i = ent_row_ptr[e] + lane; i < ent_row_ptr[e + 1]; i += 32) s += row_loss[i];
-        s = warp_sum(s);
-        if (lane == 0) out[e] = s;
+    int64_t e0 = (((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5) << 5;
+    const int64_t stride = (((int64_t)gridDim.x * blockDim.x) >> 5) << 5;
+    for (; e0 < n_entities; e0 += stride) {
+        const int64_t e = e0 + lane;
+        int64_t lo = 0, hi = 0;
+        if (e < n_entities) {
+            lo = ent_row_ptr[e];
+            hi = ent_row_ptr[e + 1];
+        }
+        const bool big = hi - lo >= 64;
+        if (e < n_entities && !big) {
+            double s = 0.0;
+            for (int64_t i = lo; i < hi; ++i) s += row_loss[i];
+            out[e] = s;
+        }
+        unsigned todo = __ballot_sync(0xffffffffu, big);
+        while (todo) {
+            const int src = __ffs(todo) - 1;
+            todo &= todo - 1;
+            const int64_t blo = __shfl_sync(0xffffffffu, lo, src), bhi = __shfl_sync(0xffffffffu, hi, src);
+            double s = 0.0;
+            for (int64_t i = blo + lane; i < bhi; i += 32) s += row_loss[i];
+            s = warp_sum(s);
+            if (lane == 0) out[e0 + src] = s;
+        }
     }
 }
 
@@ -1110,7 +1130,7 @@ int launch_entity_values(cudaStream_t s, int64_t n_entities, const int64_t *ent_
                          double *out)
 {
     if (n_entities <= 0) return 0;
-    int64_t grid = (n_entities * 32 + 255) / 256;
+    int64_t grid = (n_entities + 255) / 256;
     if (grid > 148 * 16) grid = 148 * 16;
     entity_values_kernel<<<(int)grid, 256, 0, s>>>(n_entities, ent_row_ptr, row_loss, out);
     return cudaGetLastError() == cudaSuccess ? 1 : -1;

@@ -72,6 +72,19 @@ __global__ void invert_perm_kernel(int32_t d, const int32_t *__restrict__ orig_o
     if (mine) atomicAdd(nonempty, (unsigned long long)mine);
 }
 
+__global__ void clamp_counts_kernel(int32_t d, const uint32_t *__restrict__ counts, uint32_t *__restrict__ keys)
+{
+    for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < d; j += (int64_t)gridDim.x * blockDim.x)
+        keys[j] = counts[j] > 0 ? 1u : 0u;
+}
+
+__global__ void gather_counts_kernel(int32_t d, const uint32_t *__restrict__ counts, const int32_t *__restrict__ orig_of,
+                                     uint32_t *__restrict__ counts_sorted)
+{
+    for (int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; c < d; c += (int64_t)gridDim.x * blockDim.x)
+        counts_sorted[c] = counts[orig_of[c]];
+}
+
 __global__ void remap_cols_kernel(int64_t nnz, int32_t *__restrict__ col, const int32_t *__restrict__ rank)
 {
     for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < nnz; k += (int64_t)gridDim.x * blockDim.x)
@@ -359,7 +372,7 @@ static int build_tiled(cudaStream_t s, int sm_count, int64_t n, int64_t nnz, con
                        bool *tiled);
 
 int build_transpose(cudaStream_t s, int sm_count, int64_t n, int32_t d, int64_t nnz, const uint32_t *row_ptr,
-                    int32_t *col, const void *val, int value_bytes, int chunk_entries, Packed *out)
+                    int32_t *col, const void *val, int value_bytes, int chunk_entries, bool renumber, Packed *out)
 {
     out->chunk_entries = chunk_entries;
     out->n_chunks = (int)((nnz + chunk_entries - 1) / chunk_entries);
@@ -385,13 +398,25 @@ int build_transpose(cudaStream_t s, int sm_count, int64_t n, int32_t d, int64_t 
     iota_kernel<<<grid_for(d), 256, 0, s>>>(d, ids.as<uint32_t>());
     PML_CUDA(cudaGetLastError());
     if (d > 0) {
+        // Sort key: the entry count (hot columns first), or -- when the caller's column order carries locality of
+        // its own, as the block-diagonal batches of per-entity problems do -- just "non-empty first", which the
+        // stable sort turns into a plain compaction that keeps the original order.
+        DevBuf sort_keys;
+        const uint32_t *keys_in = counts.as<uint32_t>();
+        if (!renumber) {
+            PML_CUDA(sort_keys.alloc(sizeof(uint32_t) * dd));
+            clamp_counts_kernel<<<grid_for(d), 256, 0, s>>>(d, counts.as<uint32_t>(), sort_keys.as<uint32_t>());
+            keys_in = sort_keys.as<uint32_t>();
+        }
         size_t tb = 0;
-        PML_CUDA(cub::DeviceRadixSort::SortPairsDescending(nullptr, tb, counts.as<uint32_t>(), counts_sorted.as<uint32_t>(),
+        PML_CUDA(cub::DeviceRadixSort::SortPairsDescending(nullptr, tb, keys_in, counts_sorted.as<uint32_t>(),
                                                            ids.as<int32_t>(), out->nzcol_id, d, 0, 32, s));
         DevBuf t1;
         PML_CUDA(t1.alloc(tb));
-        PML_CUDA(cub::DeviceRadixSort::SortPairsDescending(t1.p, tb, counts.as<uint32_t>(), counts_sorted.as<uint32_t>(),
+        PML_CUDA(cub::DeviceRadixSort::SortPairsDescending(t1.p, tb, keys_in, counts_sorted.as<uint32_t>(),
                                                            ids.as<int32_t>(), out->nzcol_id, d, 0, 32, s));
+        if (!renumber)  // the sorted keys are only 0/1: fetch the real counts in the new order
+            gather_counts_kernel<<<grid_for(d), 256, 0, s>>>(d, counts.as<uint32_t>(), out->nzcol_id, counts_sorted.as<uint32_t>());
         invert_perm_kernel<<<grid_for(d), 256, 0, s>>>(d, out->nzcol_id, counts_sorted.as<uint32_t>(), out->rank,
                                                       m_dev.as<unsigned long long>());
         PML_CUDA(cudaGetLastError());
@@ -418,6 +443,7 @@ int build_transpose(cudaStream_t s, int sm_count, int64_t n, int32_t d, int64_t 
         remap_cols_kernel<<<grid_for(nnz), 256, 0, s>>>(nnz, col, out->rank);
         PML_CUDA(cudaGetLastError());
         bool tiled = false;
+        if (renumber)
         PML_TRY(build_tiled(s, sm_count, n, nnz, row_ptr, col, val, value_bytes, chunk_entries, counts_sorted.as<uint32_t>(),
                             out, &tiled));
         if (tiled) return PML_OK;

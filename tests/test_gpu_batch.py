@@ -88,3 +88,26 @@ def test_batch_rejects_bad_local_columns():
     assert np.allclose(grads, [0.5, 0.5, 0.0, 0.0, 0.5], rtol=1e-14)
     b.close()
     ctx.close()
+
+
+def test_batch_device_buffers_match_host_buffers():
+    import torch
+    import photon_ml_b200 as pml
+    rng = np.random.default_rng(77)
+    ent_row_ptr, dims, row_ptr, col, val, n = _entities(rng, 900, 16, 20)
+    label = util.labels_for(rng, 0, n)
+    ctx = pml.Context(0)
+    batch = pml.Batch(ctx, ent_row_ptr, dims, row_ptr, col, val, label)
+    coefs = rng.normal(scale=0.3, size=batch.d_total)
+    values, grads = batch.value_and_gradient(pml.LOGISTIC, coefs)
+    dev = torch.device("cuda", 0)
+    t_coef = torch.tensor(coefs, device=dev)
+    t_val = torch.full((len(dims),), float("nan"), dtype=torch.float64, device=dev)
+    t_grad = torch.full((batch.d_total,), float("nan"), dtype=torch.float64, device=dev)
+    torch.cuda.synchronize()
+    batch.value_and_gradient_dev(pml.LOGISTIC, t_coef.data_ptr(), t_val.data_ptr(), t_grad.data_ptr())
+    ctx.synchronize()
+    assert np.array_equal(t_val.cpu().numpy(), values)       # same kernels, same order: bit-identical
+    assert np.array_equal(t_grad.cpu().numpy(), grads)
+    batch.close()
+    ctx.close()
