@@ -521,7 +521,8 @@ static int build_tiled(cudaStream_t s, int sm_count, int64_t n, int64_t nnz, con
     if (max_rows > 28000) max_rows = 28000;  // 227 KB of shared memory
     // tile geometry: a multiple of the SM count when the data is large enough, tiles of <= max_rows rows
     int64_t n_tiles = (n + max_rows - 1) / max_rows;
-    if (n_tiles > sm_count) n_tiles = (n_tiles + sm_count - 1) / sm_count * sm_count;
+    if (n_tiles < sm_count) n_tiles = sm_count;  // one persistent CTA per SM: never fewer tiles than SMs
+    n_tiles = (n_tiles + sm_count - 1) / sm_count * sm_count;
     int tile_rows = (int)((n + n_tiles - 1) / n_tiles);
     if (forced_rows > 0) tile_rows = forced_rows < max_rows ? forced_rows : (int)max_rows;
     n_tiles = (n + tile_rows - 1) / tile_rows;
