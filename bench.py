@@ -358,7 +358,22 @@ def convergence(ctx, ds, d):
     from photon_ml_b200.optimization import LBFGS, TRON
     from tests import util
     from tests.objectives import OracleGLMObjective
+    import torch
+    from photon_ml_b200.function import DeviceGLMLossFunction
     out = {}
+    # (a) optimizer state in device memory (torch tensors), only scalars come back
+    dev_obj = DeviceGLMLossFunction(ctx, LOSS_POISSON, l2RegWeight=1.0)
+    tron = TRON(NoNormalization())
+    with dev_obj.stream():
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        _, f = tron.optimize(dev_obj, torch.zeros(d, dtype=torch.float64, device=torch.device("cuda", ctx.device)), ds)
+        torch.cuda.synchronize()
+        wall = time.perf_counter() - t0
+    out["tron_configs1_poisson_l2_1_device_state"] = {
+        "wall_s": wall, "iterations": tron.currentState.iter, "reason": tron.convergenceReason,
+        "value_gradient_evals": tron.evaluations, "hessian_vector_evals": tron.hessian_vector_evaluations, "objective": f}
+    # (b) the drop-in shape: host vectors through the host-buffer ABI every evaluation (numpy optimizer state)
     t0 = time.perf_counter()
     tron = TRON(NoNormalization())
     _, f = tron.optimize(DistributedGLMLossFunction.create(LOSS_POISSON, l2RegWeight=1.0), np.zeros(d), ds)

@@ -28,6 +28,8 @@ class NormalizationContext:
         self.interceptId = interceptId
 
     def modelToOriginalSpace(self, coef):   # :64-80
+        if self.factors is None and self.shifts is None and not isinstance(coef, np.ndarray):
+            return coef.clone()              # device tensors pass through an empty context untouched
         out = np.array(coef, dtype=np.float64)
         if self.factors is not None:
             out = out * self.factors
@@ -36,6 +38,8 @@ class NormalizationContext:
         return out
 
     def modelToTransformedSpace(self, coef):  # :97-111
+        if self.factors is None and self.shifts is None and not isinstance(coef, np.ndarray):
+            return coef.clone()
         out = np.array(coef, dtype=np.float64)
         if self.shifts is not None:
             out[self.interceptId] += out.dot(self.shifts)
@@ -161,3 +165,53 @@ class DistributedSmoothedHingeLossFunction(_NativeObjective):
 
 class _HingeWithL2(L2RegularizationMixin, DistributedSmoothedHingeLossFunction):
     pass
+
+
+class DeviceGLMLossFunction:
+    """The same objective with coefficients, gradients and Hessian-vector products as torch tensors on the
+    GPU (the *_dev entry points of the C ABI): an optimizer driven through it keeps its whole state in device
+    memory and only reads scalars back.  L2 is applied on the device when l2RegWeight is given.  Run the
+    optimizer inside `with objective.stream():` so that torch's own kernels are ordered on the context's stream."""
+
+    twice_differentiable = True
+
+    def __init__(self, ctx, loss, l2RegWeight=None):
+        import torch
+        self._torch = torch
+        self.ctx, self.loss = ctx, loss
+        self.l2RegWeight = None if l2RegWeight is None else float(l2RegWeight)
+        self._ext = torch.cuda.ExternalStream(ctx.stream, device=torch.device("cuda", ctx.device))
+        self._tag, self._tag_src = 0, None
+
+    def stream(self):
+        return self._torch.cuda.stream(self._ext)
+
+    def _apply(self, data, ctx):
+        if ctx.factors is not None or ctx.shifts is not None:
+            data.set_normalization(ctx.factors, ctx.shifts, ctx.interceptId)
+
+    def calculate(self, data, coefficients, normalizationContext, want_gradient=True):
+        torch = self._torch
+        self._apply(data, normalizationContext)
+        value = torch.empty(1, dtype=torch.float64, device=coefficients.device)
+        grad = torch.empty_like(coefficients) if want_gradient else None
+        data.value_and_gradient_dev(self.loss, coefficients.data_ptr(), value.data_ptr(),
+                                    grad.data_ptr() if want_gradient else None)
+        f = float(value)
+        if self.l2RegWeight is not None:
+            f += self.l2RegWeight * float(coefficients.dot(coefficients)) / 2
+            if want_gradient:
+                grad += coefficients * self.l2RegWeight
+        return f, grad
+
+    def hessianVector(self, data, coefficients, multiplyVector, normalizationContext):
+        torch = self._torch
+        self._apply(data, normalizationContext)
+        if self._tag_src is not coefficients:     # TRON passes the same tensor object for a whole CG loop
+            self._tag_src = coefficients
+            self._tag += 1
+        hv = torch.empty_like(coefficients)
+        data.hessian_vector_dev(self.loss, coefficients.data_ptr(), multiplyVector.data_ptr(), hv.data_ptr(), tag=self._tag)
+        if self.l2RegWeight is not None:
+            hv += multiplyVector * self.l2RegWeight
+        return hv

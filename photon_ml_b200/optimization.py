@@ -22,6 +22,22 @@ import time
 import numpy as np
 
 
+def _norm(x):
+    """2-norm of a numpy vector or a torch tensor (the drivers work on either: with torch tensors on the GPU the
+    whole optimizer state stays in device memory and only scalars come back)."""
+    if isinstance(x, np.ndarray):
+        return float(np.linalg.norm(x))
+    return float(x.norm())
+
+
+def _zeros_like(x):
+    return np.zeros_like(x) if isinstance(x, np.ndarray) else x.new_zeros(x.shape)
+
+
+def _copy(x):
+    return np.array(x, dtype=np.float64) if isinstance(x, np.ndarray) else x.clone()
+
+
 class OptimizerState:
     def __init__(self, coefficients, loss, gradient, iter):
         self.coefficients, self.loss, self.gradient, self.iter = coefficients, loss, gradient, iter
@@ -65,7 +81,7 @@ class Optimizer:
 
     def _setAbsTolerances(self, state):          # :68-71
         self.lossAbsTolerance = state.loss * self.relTolerance
-        self.gradientAbsTolerance = float(np.linalg.norm(state.gradient)) * self.relTolerance
+        self.gradientAbsTolerance = _norm(state.gradient) * self.relTolerance
 
     def _updateCurrentState(self, state):        # :73-90
         if self.trackedStates is not None and state is not self.currentState:
@@ -83,7 +99,7 @@ class Optimizer:
             return OBJECTIVE_NOT_IMPROVING
         if abs(cur.loss - prev.loss) <= self.lossAbsTolerance:
             return FUNCTION_VALUES_CONVERGED
-        if float(np.linalg.norm(cur.gradient)) <= self.gradientAbsTolerance:
+        if _norm(cur.gradient) <= self.gradientAbsTolerance:
             return GRADIENT_CONVERGED
         return None
 
@@ -98,7 +114,7 @@ class Optimizer:
     def optimize(self, objectiveFunction, initialCoefficients, data):   # :172-196
         normalized = self.normalizationContext.modelToTransformedSpace(initialCoefficients)
         self.clearOptimizerInnerState()
-        self._setAbsTolerances(self.calculateState(objectiveFunction, np.zeros_like(normalized), data))
+        self._setAbsTolerances(self.calculateState(objectiveFunction, _zeros_like(normalized), data))
         initialState = self.calculateState(objectiveFunction, normalized, data)
         self.init(objectiveFunction, initialState, data)
         self._updateCurrentState(initialState)
@@ -129,7 +145,7 @@ class TRON(Optimizer):
         self.cg_iterations = []
 
     def init(self, objectiveFunction, initState, data):          # :112-113
-        self.delta = float(np.linalg.norm(initState.gradient))
+        self.delta = _norm(initState.gradient)
 
     def clearOptimizerInnerState(self):
         super().clearOptimizerInnerState()
@@ -151,7 +167,7 @@ class TRON(Optimizer):
             value, gradient = objectiveFunction.calculate(data, updated, self.normalizationContext)
             self.evaluations += 1
             actualReduction = prevValue - value
-            stepNorm = float(np.linalg.norm(step))
+            stepNorm = _norm(step)
             if isFirstIteration:
                 self.delta = min(self.delta, stepNorm)
             if value - prevValue - gs <= 0:
@@ -176,14 +192,14 @@ class TRON(Optimizer):
         return finalState
 
     def _truncatedCG(self, objectiveFunction, gradient, truncationBoundary, data, coefficients):   # :279-339
-        step = np.zeros_like(gradient)
+        step = _zeros_like(gradient)
         residual = gradient * -1.0
-        direction = residual.copy()
-        tol = 0.1 * float(np.linalg.norm(gradient))
+        direction = _copy(residual)
+        tol = 0.1 * _norm(gradient)
         iteration, done = 0, False
         rTr = float(residual.dot(residual))
         while iteration < self.MAX_CG_ITERATIONS and not done:
-            if float(np.linalg.norm(residual)) <= tol:
+            if _norm(residual) <= tol:
                 done = True
             else:
                 iteration += 1
@@ -191,7 +207,7 @@ class TRON(Optimizer):
                 self.hessian_vector_evaluations += 1
                 alpha = rTr / float(direction.dot(Hd))
                 step += direction * alpha
-                if float(np.linalg.norm(step)) > truncationBoundary:
+                if _norm(step) > truncationBoundary:
                     alpha = -alpha
                     step += direction * alpha
                     std = float(step.dot(direction))
@@ -279,7 +295,7 @@ class LBFGS(Optimizer):
         # breezeOptimizer.iterations(f, x0) followed by next(): Breeze evaluates f(x0) itself (LBFGS.scala:64-65)
         value, gradient = objectiveFunction.calculate(data, initState.coefficients, self.normalizationContext)
         self.evaluations += 1
-        self._x = np.array(initState.coefficients, dtype=np.float64)
+        self._x = _copy(initState.coefficients)
         self._f, self._g = value, gradient
         self._S, self._Y = [], []
         self._inner_iter = 0
@@ -290,7 +306,7 @@ class LBFGS(Optimizer):
         return f, g
 
     def _direction(self, adj_g):
-        q = -adj_g.copy()
+        q = -_copy(adj_g)
         alphas = []
         for s, y in zip(reversed(self._S), reversed(self._Y)):
             rho = 1.0 / float(y.dot(s))
@@ -314,7 +330,7 @@ class LBFGS(Optimizer):
             self.evaluations += 1
             return ft, float(gt.dot(direction)), (xt, ft, gt)
 
-        init = 1.0 / float(np.linalg.norm(direction)) if self._inner_iter == 0 else 1.0
+        init = 1.0 / _norm(direction) if self._inner_iter == 0 else 1.0
         _, _, payload = _strong_wolfe(phi, f, gd, init)
         return payload
 
@@ -324,7 +340,7 @@ class LBFGS(Optimizer):
             return currState                   # "LBFGS is converged": the same state object comes back
         x, f, g = self._x, self._f, self._g
         adj_f, adj_g = self._adjusted(x, f, g)
-        if float(np.linalg.norm(adj_g)) <= max(self.tolerance * abs(adj_f), 1e-8):
+        if _norm(adj_g) <= max(self.tolerance * abs(adj_f), 1e-8):
             self._inner_converged = True       # already stationary (Breeze tests convergence on the initial state too)
             return currState
         direction = self._direction(adj_g)
@@ -337,7 +353,7 @@ class LBFGS(Optimizer):
             return currState
         xn, fn, gn = payload
         s, y = xn - x, gn - g
-        if float(s.dot(y)) > 1e-10 * float(np.linalg.norm(s)) * float(np.linalg.norm(y)):
+        if float(s.dot(y)) > 1e-10 * _norm(s) * _norm(y):
             self._S.append(s)
             self._Y.append(y)
             if len(self._S) > self.m:
@@ -347,7 +363,7 @@ class LBFGS(Optimizer):
         self._inner_iter += 1
         adj_fn, adj_gn = self._adjusted(xn, fn, gn)
         # Breeze's own stopping rule: |adjusted gradient| <= max(tolerance * |adjusted value|, 1e-8)
-        if float(np.linalg.norm(adj_gn)) <= max(self.tolerance * abs(adj_fn), 1e-8) or self._inner_iter >= self.maxNumIterations:
+        if _norm(adj_gn) <= max(self.tolerance * abs(adj_fn), 1e-8) or self._inner_iter >= self.maxNumIterations:
             self._inner_converged = True
         return OptimizerState(project_coefficients(xn, self.constraintMap), adj_fn, adj_gn, currState.iter + 1)
 
@@ -374,7 +390,7 @@ class OWLQN(LBFGS):
     def _line_search(self, objectiveFunction, data, x, f, g, adj_f, adj_g, direction):
         orthant = np.where(x != 0, np.sign(x), -np.sign(adj_g))
         gd = float(adj_g.dot(direction))
-        t = 1.0 / float(np.linalg.norm(direction)) if self._inner_iter == 0 else 1.0
+        t = 1.0 / _norm(direction) if self._inner_iter == 0 else 1.0
         for _ in range(30):
             xt = x + t * direction
             xt = np.where(np.sign(xt) == orthant, xt, 0.0)

@@ -93,3 +93,24 @@ def test_owlqn_l1_logistic_with_normalization(ctx):
     assert np.count_nonzero(w_gpu) == np.count_nonzero(w_cpu) < d        # L1 zeroed some coefficients
     assert np.max(np.abs(w_gpu - w_cpu)) <= 1e-6 * max(1.0, np.max(np.abs(w_cpu)))
     ds.close()
+
+
+def test_tron_with_device_resident_state_matches_host_state(ctx):
+    # the same TRON driver with torch tensors on the GPU (the *_dev entry points) and with numpy vectors
+    import torch
+    import photon_ml_b200 as pml
+    from photon_ml_b200.function import DeviceGLMLossFunction, DistributedGLMLossFunction, NoNormalization
+    from photon_ml_b200.optimization import TRON
+    n, d, row_ptr, col, val, label = util.read_libsvm(os.path.join(util.GOLDEN, "a9a_1605.libsvm"), d=123, add_intercept=True)
+    ds = pml.Dataset.from_csr(ctx, n, d, row_ptr, col, val, label)
+    host_opt, dev_opt = TRON(NoNormalization()), TRON(NoNormalization())
+    w_host, f_host = host_opt.optimize(DistributedGLMLossFunction.create(pml.LOGISTIC, l2RegWeight=10.0), np.zeros(d), ds)
+    obj = DeviceGLMLossFunction(ctx, pml.LOGISTIC, l2RegWeight=10.0)
+    with obj.stream():
+        w_dev, f_dev = dev_opt.optimize(obj, torch.zeros(d, dtype=torch.float64, device="cuda:0"), ds)
+        torch.cuda.synchronize()
+    assert dev_opt.currentState.iter == host_opt.currentState.iter
+    assert dev_opt.cg_iterations == host_opt.cg_iterations
+    assert abs(f_dev - f_host) <= 1e-9 * abs(f_host)
+    assert np.max(np.abs(w_dev.cpu().numpy() - w_host)) <= 1e-6 * max(1.0, np.max(np.abs(w_host)))
+    ds.close()
