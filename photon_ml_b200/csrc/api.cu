@@ -140,7 +140,7 @@ int run_col_and_fixup(pml_dataset *ds, bool square, double *out, bool with_scala
     cp.carry = ds->carry_head;
     cp.n_chunks = ds->t.n_chunks;
     PML_TRY(run(ctx, PML_K_COL, [&] {
-        return launch_seg_spmv(s, ctx->sm_count, ds->value_bytes, false, square, ds->t.chunk_entries, cp, 0);
+        return launch_seg_spmv(s, ctx->sm_count, ds->value_bytes, false, square, cp, 0);
     }));
     PML_TRY(run(ctx, PML_K_FIXUP, [&] {
         return launch_fixup(s, ds->t.fix, ds->t.n_fix, ds->t.n_fix_long, ds->carry_head, out, nullptr, nullptr, ds->d,
@@ -161,8 +161,7 @@ int run_rows(pml_dataset *ds, RowPassParams &rp, bool two)
     const int variant = ds->variant_forced ? ds->lanes_per_row : (two ? ds->lanes_per_row : 1);
     if (variant != 1) {
         return run(ctx, PML_K_ROW, [&] {
-            return launch_row_pass(s, ctx->sm_count, ds->value_bytes, variant, two, rp, ds->t.m, ds->row_threads,
-                                   ds->row_hot_cap, &ds->row_grid);
+            return launch_row_pass(s, ctx->sm_count, ds->value_bytes, variant, two, rp, &ds->row_grid);
         });
     }
     if (two && ds->zb == nullptr) {
@@ -187,7 +186,7 @@ int run_rows(pml_dataset *ds, RowPassParams &rp, bool two)
     sp.carry2 = two ? ds->carry_row2 : nullptr;
     sp.n_chunks = ds->rs.n_chunks;
     PML_TRY(run(ctx, PML_K_ROW, [&] {
-        return launch_seg_spmv(s, ctx->sm_count, ds->value_bytes, two, false, ds->t.chunk_entries, sp, ds->t.m);
+        return launch_seg_spmv(s, ctx->sm_count, ds->value_bytes, two, false, sp, ds->t.m);
     }));
     PML_TRY(run(ctx, PML_K_FIXUP, [&] {
         return launch_fixup(s, ds->rs.fix, ds->rs.n_fix, ds->rs.n_fix_long, ds->carry_row, ds->za, two ? ds->carry_row2 : nullptr,
@@ -560,12 +559,12 @@ int pml_dataset_create_csr_dev(pml_ctx *ctx, int64_t n, int32_t d, const int64_t
     PML_TRY(upload_optional(s, &ds->offset, offsets_dev, n, true, &ds->bytes));
     PML_TRY(upload_optional(s, &ds->weight, weights_dev, n, true, &ds->bytes));
 
-    int chunk_entries = 256;  // one chunk per warp (seg_spmv_warp_kernel); PML_SEG_CTA=1 selects CTA-sized chunks
-    if (std::getenv("PML_SEG_CTA") != nullptr) chunk_entries = TCHUNK;
+    const int chunk_entries = SEG_CHUNK;
     PML_TRY(build_transpose(s, ctx->sm_count, n, d, nnz, ds->row_ptr, ds->col, ds->val, dst_bytes, chunk_entries,
                             (storage_arg & PML_KEEP_COLUMN_ORDER_FLAG) == 0, &ds->t));
     ds->bytes += ds->t.bytes;
-    // after the transpose: from here on the CSR column array carries the row-start flags in bit 31
+    // after the transpose (which sorts by the column ids): from here on the CSR column array carries the row-start
+    // flags in bit 31
     PML_TRY(build_row_side(s, n, nnz, ds->row_ptr, ds->col, chunk_entries, &ds->rs));
     ds->bytes += ds->rs.bytes;
     PML_TRY(dev_alloc(&ds->za, (size_t)n, &ds->bytes));
@@ -580,8 +579,6 @@ int pml_dataset_create_csr_dev(pml_ctx *ctx, int64_t n, int32_t d, const int64_t
     PML_TRY(dev_alloc(&ds->io_a, (size_t)d + 2, &ds->bytes));
     PML_TRY(dev_alloc(&ds->io_b, (size_t)d + 2, &ds->bytes));
     ds->lanes_per_row = pick_variant(n, nnz);
-    if (const char *e = std::getenv("PML_ROW_THREADS")) ds->row_threads = std::atoi(e) >= 1024 ? 1024 : 256;
-    if (const char *e = std::getenv("PML_ROW_HOT")) ds->row_hot_cap = std::atoi(e);
     PML_CUDA(cudaStreamSynchronize(s));
     cleanup.ds = nullptr;
     *out = ds;

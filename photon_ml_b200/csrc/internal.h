@@ -30,16 +30,14 @@ int fail(int code, const std::string &msg);
         if (_rc != PML_OK) return _rc; \
     } while (0)
 
-// ---- geometry of seg_spmv_kernel: a chunk is TCHUNK consecutive entries of the CSC (or CSR) stream ----
-constexpr int S_THREADS = 512;
-constexpr int S_ITEMS = 8;
-constexpr int TCHUNK = S_THREADS * S_ITEMS;  // 4096 entries = 32 KB of stream per chunk (fp32 values)
-constexpr int S_MAX_DYN_SMEM = 104 * 1024;
-constexpr int SW_THREADS = 256;               // CTA size of the warp-chunk variant (4 CTAs per SM)   // hot table per CTA; two CTAs share an SM
+// ---- geometry of the entry-chunked kernels: a chunk is SEG_CHUNK consecutive entries, owned by one warp ----
+constexpr int SEG_CHUNK = 256;               // 32 lanes x 8 entries
+constexpr int SEG_TABLE_BYTES = 96 * 1024;   // hot prefix of the coefficient vector staged per CTA (CSR stream)
 
-// ---- geometry of the row (CSR) kernel ----
-constexpr int R_STREAM_CAP = 128;  // products staged per warp per piece in the segment-per-warp variant
-constexpr int R_MAX_DYN_SMEM = 220 * 1024;  // dynamic shared memory per row-pass CTA (227 KB minus static + margin)
+// ---- geometry of the lanes-per-row / segment-per-warp row kernel ----
+constexpr int R_THREADS = 256;
+constexpr int R_WARPS = R_THREADS / 32;
+constexpr int R_STREAM_CAP = 512;  // products staged per warp per piece in the segment-per-warp variant
 constexpr int MAX_PARTIALS = 4096; // upper bound on row-kernel CTAs (block partials of F and P)
 
 enum RowMode {
@@ -65,7 +63,6 @@ struct RowPassParams {
     double *dcache;           // n: wt*l''(z) written (HV_COLD) or read (HV_CACHED)
     double *partials;         // 2 * gridDim.x: per-CTA (F, P)
     double *row_loss;         // n or null: wt_i * l_i per row (batched per-entity values)
-    int n_hot;                // leading entries of vec staged in shared memory (set by the launcher)
     int mode;
     int loss;
 };
@@ -95,11 +92,9 @@ struct TiledSide;
 int launch_prepare_vectors(cudaStream_t s, int d, const double *coef, const double *v, const double *factors,
                            const double *shifts, const int32_t *rank, double *out_vec, double *shift_partials,
                            int *n_partials);
-int launch_row_pass(cudaStream_t s, int sm_count, int value_bytes, int lanes_per_row, bool two,
-                    RowPassParams p, int64_t n_nonempty_cols, int threads, int hot_cap, int *grid_out);
-int launch_seg_spmv(cudaStream_t s, int sm_count, int value_bytes, bool two, bool square, int chunk_entries,
-                    SegParams p, int64_t table_len);
-int seg_hot_capacity(bool two);
+int launch_row_pass(cudaStream_t s, int sm_count, int value_bytes, int lanes_per_row, bool two, const RowPassParams &p,
+                    int *grid_out);
+int launch_seg_spmv(cudaStream_t s, int sm_count, int value_bytes, bool two, bool square, SegParams p, int64_t table_len);
 int launch_row_epilogue(cudaStream_t s, int sm_count, const RowPassParams &p, const double *za, const double *zb,
                         int *grid_out);
 int launch_fixup(cudaStream_t s, const FixEntry *fix, int n_fix, int n_long, const double *carry_head, double *out,
@@ -162,7 +157,7 @@ struct Packed {
     uint32_t *nzcol_ptr = nullptr; // d+1: entry offset of each internal column (columns >= m are empty)
     int32_t *nzcol_id = nullptr;   // d: internal id -> original column id
     int32_t *rank = nullptr;       // d: original column id -> internal id
-    int chunk_entries = TCHUNK;
+    int chunk_entries = SEG_CHUNK;
     int32_t *chunk_col_lo = nullptr;
     FixEntry *fix = nullptr;
     int64_t m = 0;  // non-empty columns
@@ -247,8 +242,6 @@ struct pml_dataset {
     int lanes_per_row = 8;  // lanes-per-row variant used for paired (Hessian-vector, cold) passes, or the forced variant
     bool keep_column_order = false;  // batches: columns are compacted, not renumbered by frequency
     bool variant_forced = false;  // pml_dataset_set_margin_variant pinned one variant for every pass
-    int row_threads = 256;  // CTA shape of the warp-oriented row pass (256 or 1024)
-    int row_hot_cap = 0;    // cap on its shared-memory hot table (-1 = as much as fits)
     int row_grid = 1;       // CTAs of the last row-pass launch (= number of (F, P) partials)
     int64_t bytes = 0;
 };

@@ -1,9 +1,13 @@
 // kernels.cu -- the per-evaluation kernels of the GLM objective path (sm_100a).
 //
 //   prepare_vectors_kernel  a1/a6  ValueAndGradientAggregator.init / HessianVectorAggregator.init
-//   row_pass_kernel         a2/a7/a9  the per-row half of `add`: sparse dot, pointwise loss, scalars
-//   col_pass_kernel         a2/a7/a9  the axpy half of `add`, done column-wise over the CSC copy
-//   fixup_kernel            a3  the part of `merge` that joins columns split across chunks
+//   row_pass_kernel         a2/a7/a9  the per-row half of `add` (lanes-per-row and segment-per-warp variants)
+//   seg_spmv_warp_kernel    a2/a7/a9  entry-chunked segmented product: the CSR stream (default for single-vector
+//                                     passes) and the cold columns of the CSC copy
+//   seg_spmv_tiled_kernel   a2/a7/a9  the axpy half of `add` over the hot columns of the CSC copy, r staged in
+//                                     shared memory tile by tile
+//   row_epilogue_kernel     a2/a7/a9  pointwise loss and scalar sums after seg_spmv_warp_kernel on the CSR stream
+//   fixup_kernel, reduce_partial_kernel  a3  the part of `merge` that joins runs split across chunks / tiles
 //   finalize_kernel         a4  getVector
 //
 // (aN = row of SURVEY.md 8a; reference file:line in DESIGN.md and at each kernel.)
@@ -12,13 +16,11 @@
 //
 // Columns carry "internal ids" assigned at pack time by descending entry count (pack.cu), so the
 // coefficients of the hottest columns sit at the front of the effective-coefficient vector and
-// can be staged in shared memory: a scattered 8-byte gather costs one L1 tag lookup per lane
-// (one per cycle per SM -- the measured limiter of the first version of these kernels), while
-// shared memory serves 32 lanes in a few cycles.
+// can be staged in shared memory: a scattered 8-byte gather from global memory costs an L1 tag
+// lookup per lane and a 32-byte L2 sector (the measured limiter of the first version of these
+// kernels), while shared memory serves 32 lanes in a few cycles.
 #include <cuda_runtime.h>
 #include <stdint.h>
-
-#include <cstdlib>
 
 #include "internal.h"
 #include "pointwise.cuh"
@@ -85,9 +87,8 @@ int launch_prepare_vectors(cudaStream_t s, int d, const double *coef, const doub
 // (LabeledPoint.computeMargin, lib/data/LabeledPoint.scala:62), the pointwise loss, the scalar
 // sums, and the per-row multiplier r_i that the column pass turns into the axpy.
 //
-// Persistent CTAs (one per SM when the hot table is large).  The first `n_hot` entries of the
-// effective-coefficient vector are copied to shared memory once per CTA; a lane whose column id
-// is below n_hot reads shared memory, the rest gather through L1.
+// This is the warp-oriented form of the pass (persistent 256-thread CTAs, gathers through L1); by default it
+// serves the paired (ec, ev) pass of a cold Hessian-vector product, and any pass when a variant is forced.
 //
 // A warp owns 32 consecutive rows at a time.
 //   LPR in {2,4,8,16,32}: "lanes per row" -- 32/LPR rows are reduced concurrently by sub-warps
@@ -99,42 +100,29 @@ int launch_prepare_vectors(cudaStream_t s, int d, const double *coef, const doub
 // r is written coalesced and the fp64 exp/log1p work runs with all 32 lanes active.
 // ------------------------------------------------------------------------------------------
 template <bool TWO>
-__device__ __forceinline__ void lookup(const double *__restrict__ hot, int n_hot, const double *__restrict__ vec,
-                                       int32_t c, double &w0, double &w1)
+__device__ __forceinline__ void gather(const double *__restrict__ vec, int32_t c, double &w0, double &w1)
 {
     if (TWO) {
-        double2 g;
-        if (c < n_hot) g = reinterpret_cast<const double2 *>(hot)[c];
-        else g = __ldg(reinterpret_cast<const double2 *>(vec) + c);
+        const double2 g = __ldg(reinterpret_cast<const double2 *>(vec) + c);
         w0 = g.x;
         w1 = g.y;
     } else {
-        w0 = (c < n_hot) ? hot[c] : __ldg(vec + c);
+        w0 = __ldg(vec + c);
         w1 = 0.0;
     }
 }
 
-template <typename VT, int LPR, bool TWO, int R_THREADS>
-__global__ void __launch_bounds__(R_THREADS, R_THREADS >= 1024 ? 1 : 1280 / R_THREADS) row_pass_kernel(const RowPassParams p)
+template <typename VT, int LPR, bool TWO>
+__global__ void __launch_bounds__(R_THREADS, 5) row_pass_kernel(const RowPassParams p)
 {
-    constexpr int R_WARPS = R_THREADS / 32;
     constexpr int CAPE = TWO ? R_STREAM_CAP / 2 : R_STREAM_CAP;
-    extern __shared__ __align__(16) double dyn_smem[];
     __shared__ double red[2 * R_WARPS];
-    // dynamic shared memory: [stage (LPR == 0 only)] [hot table]
-    double *stage = dyn_smem;
-    double *hot = dyn_smem + ((LPR == 0) ? R_WARPS * R_STREAM_CAP : 0);
+    __shared__ double stage[(LPR == 0) ? R_WARPS * R_STREAM_CAP : 1];
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const VT *__restrict__ val = static_cast<const VT *>(p.val);
     const int32_t *__restrict__ col = p.col;
     const double *__restrict__ vec = p.vec;
-    const int n_hot = p.n_hot;
-
-    {
-        const int words = TWO ? 2 * n_hot : n_hot;
-        for (int i = threadIdx.x; i < words; i += R_THREADS) hot[i] = vec[i];
-    }
 
     // marginShift = -(ec . shifts); featureVectorProductShift = ev . shifts
     double shift0 = 0.0, shift1 = 0.0;
@@ -145,7 +133,6 @@ __global__ void __launch_bounds__(R_THREADS, R_THREADS >= 1024 ? 1 : 1280 / R_TH
         }
         block_sum2<R_WARPS>(shift0, shift1, red);
     }
-    __syncthreads();  // hot table visible
     const double margin_shift = (p.mode == MODE_HV_CACHED) ? 0.0 : -shift0;
     const double fs = (p.mode == MODE_HV_CACHED) ? shift0 : shift1;
 
@@ -171,7 +158,7 @@ __global__ void __launch_bounds__(R_THREADS, R_THREADS >= 1024 ? 1 : 1280 / R_TH
                     const int32_t c = __ldcs(col + k) & 0x7fffffff;
                     const double x = widen(__ldcs(val + k));
                     double w0, w1;
-                    lookup<TWO>(hot, n_hot, vec, c, w0, w1);
+                    gather<TWO>(vec, c, w0, w1);
                     buf[k - pb] = __dmul_rn(x, w0);
                     if (TWO) buf[CAPE + (k - pb)] = __dmul_rn(x, w1);
                 }
@@ -201,10 +188,10 @@ __global__ void __launch_bounds__(R_THREADS, R_THREADS >= 1024 ? 1 : 1280 / R_TH
                     const double x0 = widen(__ldcs(val + k)), x1 = widen(__ldcs(val + k + L));
                     const double x2 = widen(__ldcs(val + k + 2 * L)), x3 = widen(__ldcs(val + k + 3 * L));
                     double w00, w01, w10, w11, w20, w21, w30, w31;
-                    lookup<TWO>(hot, n_hot, vec, c0, w00, w01);
-                    lookup<TWO>(hot, n_hot, vec, c1, w10, w11);
-                    lookup<TWO>(hot, n_hot, vec, c2, w20, w21);
-                    lookup<TWO>(hot, n_hot, vec, c3, w30, w31);
+                    gather<TWO>(vec, c0, w00, w01);
+                    gather<TWO>(vec, c1, w10, w11);
+                    gather<TWO>(vec, c2, w20, w21);
+                    gather<TWO>(vec, c3, w30, w31);
                     a += (x0 * w00 + x1 * w10) + (x2 * w20 + x3 * w30);
                     if (TWO) b += (x0 * w01 + x1 * w11) + (x2 * w21 + x3 * w31);
                 }
@@ -212,7 +199,7 @@ __global__ void __launch_bounds__(R_THREADS, R_THREADS >= 1024 ? 1 : 1280 / R_TH
                     const int32_t c = __ldcs(col + k) & 0x7fffffff;
                     const double x = widen(__ldcs(val + k));
                     double w0, w1;
-                    lookup<TWO>(hot, n_hot, vec, c, w0, w1);
+                    gather<TWO>(vec, c, w0, w1);
                     a = fma(x, w0, a);
                     if (TWO) b = fma(x, w1, b);
                 }
@@ -283,69 +270,42 @@ __global__ void __launch_bounds__(R_THREADS, R_THREADS >= 1024 ? 1 : 1280 / R_TH
     }
 }
 
-template <typename VT, int LPR, bool TWO, int THREADS>
-static int launch_row_one(cudaStream_t s, int grid, size_t smem, const RowPassParams &p)
+template <typename VT, bool TWO>
+static int launch_row_variant(cudaStream_t s, int grid, int lpr, const RowPassParams &p)
 {
-    // per device and per instantiation; cheap enough to repeat on every launch
-    if (smem > 48 * 1024 &&
-        cudaFuncSetAttribute(row_pass_kernel<VT, LPR, TWO, THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             R_MAX_DYN_SMEM) != cudaSuccess)
-        return -1;
-    row_pass_kernel<VT, LPR, TWO, THREADS><<<grid, THREADS, smem, s>>>(p);
+    switch (lpr) {
+    case 0: row_pass_kernel<VT, 0, TWO><<<grid, R_THREADS, 0, s>>>(p); break;
+    case 2: row_pass_kernel<VT, 2, TWO><<<grid, R_THREADS, 0, s>>>(p); break;
+    case 4: row_pass_kernel<VT, 4, TWO><<<grid, R_THREADS, 0, s>>>(p); break;
+    case 8: row_pass_kernel<VT, 8, TWO><<<grid, R_THREADS, 0, s>>>(p); break;
+    case 16: row_pass_kernel<VT, 16, TWO><<<grid, R_THREADS, 0, s>>>(p); break;
+    case 32: row_pass_kernel<VT, 32, TWO><<<grid, R_THREADS, 0, s>>>(p); break;
+    default: return -1;
+    }
     return cudaGetLastError() == cudaSuccess ? 1 : -1;
 }
 
-template <typename VT, bool TWO, int THREADS>
-static int launch_row_variant(cudaStream_t s, int grid, int lpr, size_t smem, const RowPassParams &p)
+// 256-thread CTAs, five per SM: the gathers live on L1 (a shared-memory table of hot coefficients was
+// measured for this kernel and lost more L1 than it saved).
+int launch_row_pass(cudaStream_t s, int sm_count, int value_bytes, int lanes_per_row, bool two, const RowPassParams &p,
+                    int *grid_out)
 {
-    switch (lpr) {
-    case 0: return launch_row_one<VT, 0, TWO, THREADS>(s, grid, smem, p);
-    case 2: return launch_row_one<VT, 2, TWO, THREADS>(s, grid, smem, p);
-    case 4: return launch_row_one<VT, 4, TWO, THREADS>(s, grid, smem, p);
-    case 8: return launch_row_one<VT, 8, TWO, THREADS>(s, grid, smem, p);
-    case 16: return launch_row_one<VT, 16, TWO, THREADS>(s, grid, smem, p);
-    case 32: return launch_row_one<VT, 32, TWO, THREADS>(s, grid, smem, p);
-    default: return -1;
-    }
-}
-
-// Two shapes of the warp-oriented row pass: 1024 threads (one CTA per SM, up to ~28 K hot
-// coefficients in shared memory) or 256 threads (five CTAs per SM, a small hot table, most of the
-// 228 KB left to L1).  `threads`/`hot_cap` come from the data set (tuning knobs).
-int launch_row_pass(cudaStream_t s, int sm_count, int value_bytes, int lanes_per_row, bool two,
-                    RowPassParams p, int64_t n_nonempty_cols, int threads, int hot_cap, int *grid_out)
-{
-    const int warps = threads / 32;
-    const int ctas_per_sm = threads >= 1024 ? 1 : 1280 / threads;
     const int64_t n_blk = (p.n + 31) / 32;
-    int64_t want = (n_blk + warps - 1) / warps;
-    int64_t cap_grid = (int64_t)sm_count * ctas_per_sm;
-    int grid = (int)(want < cap_grid ? want : cap_grid);
+    int64_t want = (n_blk + R_WARPS - 1) / R_WARPS;
+    int64_t cap = (int64_t)sm_count * 5;
+    if (cap > MAX_PARTIALS) cap = MAX_PARTIALS;
+    int grid = (int)(want < cap ? want : cap);
     if (grid < 1) grid = 1;
-    if (grid > MAX_PARTIALS) grid = MAX_PARTIALS;
     *grid_out = grid;
-    const size_t stage = lanes_per_row == 0 ? sizeof(double) * warps * R_STREAM_CAP : 0;
-    const size_t per_cta = (size_t)(R_MAX_DYN_SMEM / ctas_per_sm) - (ctas_per_sm > 1 ? 2048 : 0);
-    int64_t cap = per_cta > stage ? (int64_t)((per_cta - stage) / (two ? 16 : 8)) : 0;
-    if (hot_cap >= 0 && cap > hot_cap) cap = hot_cap;
-    p.n_hot = (int)(n_nonempty_cols < cap ? n_nonempty_cols : cap);
-    const size_t smem = stage + (size_t)p.n_hot * (two ? 16 : 8);
-    if (threads >= 1024) {
-        if (value_bytes == 4)
-            return two ? launch_row_variant<float, true, 1024>(s, grid, lanes_per_row, smem, p)
-                       : launch_row_variant<float, false, 1024>(s, grid, lanes_per_row, smem, p);
-        return two ? launch_row_variant<double, true, 1024>(s, grid, lanes_per_row, smem, p)
-                   : launch_row_variant<double, false, 1024>(s, grid, lanes_per_row, smem, p);
-    }
     if (value_bytes == 4)
-        return two ? launch_row_variant<float, true, 256>(s, grid, lanes_per_row, smem, p)
-                   : launch_row_variant<float, false, 256>(s, grid, lanes_per_row, smem, p);
-    return two ? launch_row_variant<double, true, 256>(s, grid, lanes_per_row, smem, p)
-               : launch_row_variant<double, false, 256>(s, grid, lanes_per_row, smem, p);
+        return two ? launch_row_variant<float, true>(s, grid, lanes_per_row, p)
+                   : launch_row_variant<float, false>(s, grid, lanes_per_row, p);
+    return two ? launch_row_variant<double, true>(s, grid, lanes_per_row, p)
+               : launch_row_variant<double, false>(s, grid, lanes_per_row, p);
 }
 
 // ------------------------------------------------------------------------------------------
-// seg_spmv_kernel -- one kernel for both sparse products of an evaluation, chunked by ENTRIES.
+// seg_spmv_warp_kernel -- one kernel for both sparse products of an evaluation, chunked by ENTRIES.
 //
 //   CSC side ("col pass"): out_j = sum_i val_ij * r_i -- the axpy half of `add`, transposed
 //     (vectorSum += (wt*l') x_i summed column by column instead of scattered row by row;
@@ -356,14 +316,14 @@ int launch_row_pass(cudaStream_t s, int sm_count, int value_bytes, int lanes_per
 //     table = effective coefficients, the first n_hot of them staged in shared memory; with TWO
 //     the table holds (ec_j, ev_j) pairs and two sums are produced (Hessian-vector, cold).
 //
-// Work is split by entries, not by rows/columns (their lengths are power-law): a chunk is
-// S_THREADS*ITEMS consecutive entries, persistent CTAs take chunks round-robin.  Each thread
-// loads ITEMS consecutive entries (index with the run-start flag in bit 31, value) with 128-bit
+// Work is split by entries, not by rows/columns (their lengths are power-law): a chunk is 256
+// consecutive entries owned by one warp, persistent CTAs hand chunks to their warps round-robin.
+// Each lane loads 8 consecutive entries (index with the run-start flag in bit 31, value) with 128-bit
 // loads -- the next chunk's loads are issued before the current chunk is reduced, so the stream
-// stays in flight -- looks all of them up at once, adds up its own run, and a CTA-wide segmented
-// scan carries partial sums across threads.  Runs that start in the chunk are written by this
-// CTA (single writer); the part of the chunk that precedes its first run start belongs to a run
-// begun in an earlier chunk and goes to carry[c] for fixup_kernel.
+// stays in flight -- looks all of them up at once, adds up its own run, and a warp-wide segmented
+// scan (shuffles only) carries partial sums across lanes.  Runs that start in the chunk are written
+// by this warp (single writer); the part of the chunk that precedes its first run start belongs to a
+// run begun in an earlier chunk and goes to carry[c] for fixup_kernel.
 // ------------------------------------------------------------------------------------------
 template <bool TWO>
 struct SegScan {
@@ -461,12 +421,12 @@ __device__ __forceinline__ void seg_load(SegRegs<VT, ITEMS> &g, const int32_t *_
 
 // Reduces one chunk held in `cur`.  FULL = every thread owns ITEMS live entries (all chunks but
 // possibly the last), which keeps the bounds tests out of the persistent loop.
-// WARP = the chunk belongs to one warp (32*ITEMS entries): the scan stops at the warp, no barrier.
-template <typename VT, int ITEMS, bool TWO, bool SQUARE, bool HOT, bool FULL, bool WARP = false>
+// A chunk belongs to one warp (32*ITEMS entries): the scan is warp-wide, no barrier, no shared memory.
+template <typename VT, int ITEMS, bool TWO, bool SQUARE, bool HOT, bool FULL>
 __device__ __forceinline__ void seg_chunk(const SegParams &p, const SegRegs<VT, ITEMS> &cur, int c, int mine_cnt,
-                                          const double *hot, SegScan<TWO> *wagg_c)
+                                          const double *hot)
 {
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int lane = threadIdx.x & 31;
     const double *__restrict__ table = p.table;
     const int n_hot = p.n_hot;
 
@@ -510,22 +470,15 @@ __device__ __forceinline__ void seg_chunk(const SegParams &p, const SegRegs<VT, 
     mine.val = s;  // the whole thread when it holds no run start
     mine.val2 = s2;
 
-    // ---- CTA-wide segmented scan of (cnt, tail) ----
+    // ---- warp-wide segmented scan of (cnt, tail) ----
     SegScan<TWO> inc = mine;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
         const SegScan<TWO> up = seg_shfl_up<TWO>(inc, o);
         if (lane >= o) inc = seg_combine<TWO>(up, inc);
     }
-    if (!WARP && lane == 31) wagg_c[warp] = inc;
     SegScan<TWO> exc = seg_shfl_up<TWO>(inc, 1);
     if (lane == 0) exc = seg_identity<TWO>();
-    if (!WARP) {
-        __syncthreads();  // wagg is double-buffered by chunk parity, so one barrier per chunk suffices
-        SegScan<TWO> pre = seg_identity<TWO>();
-        for (int w = 0; w < warp; ++w) pre = seg_combine<TWO>(pre, wagg_c[w]);
-        exc = seg_combine<TWO>(pre, exc);
-    }
 
     const int run_lo = p.chunk_lo[c];
     const int32_t *__restrict__ run_id = p.run_id;
@@ -565,9 +518,9 @@ __device__ __forceinline__ void seg_chunk(const SegParams &p, const SegRegs<VT, 
             }
         }
     }
-    if (WARP ? lane == 31 : tid == S_THREADS - 1) {
+    if (lane == 31) {
         const SegScan<TWO> tot = seg_combine<TWO>(exc, mine);
-        if (tot.cnt) {  // the last run started here: this CTA owns its slot
+        if (tot.cnt) {  // the last run started here: this warp owns its slot
             const int last = run_lo + tot.cnt - 1;
             const int slot = run_id ? run_id[last] : last;
             out[slot] = tot.val;
@@ -598,49 +551,8 @@ __device__ __forceinline__ void seg_load_full(SegRegs<VT, ITEMS> &g, const int32
     }
 }
 
-template <typename VT, int ITEMS, bool TWO, bool SQUARE, bool HOT>
-__global__ void __launch_bounds__(S_THREADS, 2) seg_spmv_kernel(const SegParams p)
-{
-    constexpr int CHUNK = S_THREADS * ITEMS;
-    constexpr int WARPS = S_THREADS / 32;
-    extern __shared__ __align__(16) double hot[];
-    __shared__ SegScan<TWO> wagg[2][WARPS];
-
-    const int tid = threadIdx.x;
-    const VT *__restrict__ val = static_cast<const VT *>(p.val);
-    const int32_t *__restrict__ idx = p.idx;
-
-    if (HOT) {
-        const int words = TWO ? 2 * p.n_hot : p.n_hot;
-        for (int i = tid; i < words; i += S_THREADS) hot[i] = p.table[i];
-        __syncthreads();
-    }
-
-    // full chunks: persistent loop, the next chunk's loads in flight while this one is reduced
-    const int n_full = (int)(p.nnz / CHUNK);
-    const int grid = gridDim.x;
-    SegRegs<VT, ITEMS> cur;
-    int c = blockIdx.x;
-    if (c < n_full) seg_load_full<VT, ITEMS>(cur, idx, val, (int64_t)c * CHUNK + tid * ITEMS);
-    int parity = 0;
-    for (; c < n_full; c += grid, parity ^= 1) {
-        SegRegs<VT, ITEMS> nxt;
-        const int cn = c + grid;
-        if (cn < n_full) seg_load_full<VT, ITEMS>(nxt, idx, val, (int64_t)cn * CHUNK + tid * ITEMS);
-        seg_chunk<VT, ITEMS, TWO, SQUARE, HOT, true>(p, cur, c, ITEMS, hot, wagg[parity]);
-        cur = nxt;
-    }
-    // the last, partially filled chunk (if any) goes to the CTA that would have taken it next
-    if (n_full < p.n_chunks && (int)blockIdx.x == n_full % grid) {
-        const int64_t base = (int64_t)n_full * CHUNK;
-        const int cnt = (int)(p.nnz - base);
-        seg_load<VT, ITEMS>(cur, idx, val, base + tid * ITEMS, cnt - tid * ITEMS);
-        seg_chunk<VT, ITEMS, TWO, SQUARE, HOT, false>(p, cur, n_full, cnt - tid * ITEMS, hot, wagg[parity]);
-    }
-}
-
-// The same reduction with one chunk per WARP (32*ITEMS entries): no shared-memory exchange and no
-// barrier, at the price of 16x more chunk metadata and fix-up entries.
+// Persistent CTAs; warp w of CTA b takes chunks (b*WARPS + w) + k*(grid*WARPS).  With a table (the CSR stream) one
+// 1024-thread CTA per SM shares the hot prefix among 32 warps; without (cold CSC columns) 256-thread CTAs.
 template <typename VT, int ITEMS, bool TWO, bool SQUARE, bool HOT, int SW_THREADS>
 __global__ void __launch_bounds__(SW_THREADS, 1024 / SW_THREADS) seg_spmv_warp_kernel(const SegParams p)
 {
@@ -664,14 +576,14 @@ __global__ void __launch_bounds__(SW_THREADS, 1024 / SW_THREADS) seg_spmv_warp_k
         SegRegs<VT, ITEMS> nxt;
         const int cn = c + stride;
         if (cn < n_full) seg_load_full<VT, ITEMS>(nxt, idx, val, (int64_t)cn * CHUNK + lane * ITEMS);
-        seg_chunk<VT, ITEMS, TWO, SQUARE, HOT, true, true>(p, cur, c, ITEMS, hot, nullptr);
+        seg_chunk<VT, ITEMS, TWO, SQUARE, HOT, true>(p, cur, c, ITEMS, hot);
         cur = nxt;
     }
     if (n_full < p.n_chunks && (int)(blockIdx.x * WARPS + warp) == n_full % stride) {
         const int64_t base = (int64_t)n_full * CHUNK;
         const int cnt = (int)(p.nnz - base);
         seg_load<VT, ITEMS>(cur, idx, val, base + lane * ITEMS, cnt - lane * ITEMS);
-        seg_chunk<VT, ITEMS, TWO, SQUARE, HOT, false, true>(p, cur, n_full, cnt - lane * ITEMS, hot, nullptr);
+        seg_chunk<VT, ITEMS, TWO, SQUARE, HOT, false>(p, cur, n_full, cnt - lane * ITEMS, hot);
     }
 }
 
@@ -685,7 +597,7 @@ static int launch_seg_warp(cudaStream_t s, int sm_count, size_t smem, const SegP
     if (p.n_hot > 0) {
         if (smem > 48 * 1024 &&
             cudaFuncSetAttribute(seg_spmv_warp_kernel<VT, 8, TWO, SQUARE, true, SW_THREADS>,
-                                 cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * S_MAX_DYN_SMEM) != cudaSuccess)
+                                 cudaFuncAttributeMaxDynamicSharedMemorySize, SEG_TABLE_BYTES) != cudaSuccess)
             return -1;
         seg_spmv_warp_kernel<VT, 8, TWO, SQUARE, true, SW_THREADS><<<grid, SW_THREADS, smem, s>>>(p);
     } else {
@@ -730,7 +642,7 @@ seg_spmv_tiled_kernel(const SegParams p, const int32_t *__restrict__ tile_first_
             SegRegs<VT, ITEMS> nxt;
             const int cn = c + WARPS;
             if (cn < c_end) seg_load_full<VT, ITEMS>(nxt, idx, val, (int64_t)cn * CHUNK + lane * ITEMS);
-            seg_chunk<VT, ITEMS, false, SQUARE, true, true, true>(p, cur, c, ITEMS, hot, nullptr);
+            seg_chunk<VT, ITEMS, false, SQUARE, true, true>(p, cur, c, ITEMS, hot);
             cur = nxt;
         }
     }
@@ -800,70 +712,27 @@ int launch_reduce_partial(cudaStream_t s, const TiledSide &t, const int32_t *nzc
     return cudaGetLastError() == cudaSuccess ? 1 : -1;
 }
 
-template <typename VT, int ITEMS, bool TWO, bool SQUARE>
-static int launch_seg_one(cudaStream_t s, int grid, size_t smem, const SegParams &p)
-{
-    if (p.n_hot > 0) {
-        if (smem > 48 * 1024 &&
-            cudaFuncSetAttribute(seg_spmv_kernel<VT, ITEMS, TWO, SQUARE, true>,
-                                 cudaFuncAttributeMaxDynamicSharedMemorySize, S_MAX_DYN_SMEM) != cudaSuccess)
-            return -1;
-        seg_spmv_kernel<VT, ITEMS, TWO, SQUARE, true><<<grid, S_THREADS, smem, s>>>(p);
-    } else {
-        seg_spmv_kernel<VT, ITEMS, TWO, SQUARE, false><<<grid, S_THREADS, 0, s>>>(p);
-    }
-    return cudaGetLastError() == cudaSuccess ? 1 : -1;
-}
-
-int seg_hot_capacity(bool two) { return (int)(S_MAX_DYN_SMEM / (two ? 16 : 8)); }
-
-// table_len = number of leading table entries worth staging (0 = no shared-memory table)
-int launch_seg_spmv(cudaStream_t s, int sm_count, int value_bytes, bool two, bool square, int chunk_entries,
-                    SegParams p, int64_t table_len)
+// table_len = number of leading table entries worth staging in shared memory (0 = none)
+int launch_seg_spmv(cudaStream_t s, int sm_count, int value_bytes, bool two, bool square, SegParams p, int64_t table_len)
 {
     if (p.n_chunks <= 0) return 0;
-    const int cap = seg_hot_capacity(two);
-    p.n_hot = (int)(table_len < cap ? table_len : cap);
+    const int64_t cap_entries = SEG_TABLE_BYTES / (two ? 16 : 8);
+    p.n_hot = (int)(table_len < cap_entries ? table_len : cap_entries);
     const size_t smem = (size_t)p.n_hot * (two ? 16 : 8);
-    int grid = sm_count * 2;
-    if (grid > p.n_chunks) grid = p.n_chunks;
-    if (chunk_entries == 256) {  // warp-sized chunks
-        // CTA shape and table size of the warp-chunk kernel (tuning knobs; defaults from the sweep in profiles/)
-        static const int threads_env = std::getenv("PML_SEG_WARP_THREADS") ? std::atoi(std::getenv("PML_SEG_WARP_THREADS")) : 0;
-        static const int cap_env = std::getenv("PML_SEG_WARP_HOT") ? std::atoi(std::getenv("PML_SEG_WARP_HOT")) : -1;
-        int threads = table_len > 0 ? 1024 : 256;   // with a table: one big CTA per SM shares it among 32 warps
-        if (threads_env == 256 || threads_env == 512 || threads_env == 1024) threads = threads_env;
-        size_t cap_w = (size_t)100 * 1024;
-        if (threads == 512) cap_w = (size_t)50 * 1024;
-        if (threads == 256) cap_w = (size_t)32 * 1024;
-        if (cap_env >= 0) cap_w = (size_t)cap_env * 1024;
-        const int64_t cap_entries = (int64_t)(cap_w / (two ? 16 : 8));
-        p.n_hot = (int)(table_len < cap_entries ? table_len : cap_entries);
-        const size_t smem_w = (size_t)p.n_hot * (two ? 16 : 8);
-#define PML_SEG_WARP_DISPATCH(T)                                                                              \
-        if (value_bytes == 4) {                                                                               \
-            if (two) return launch_seg_warp<float, true, false, T>(s, sm_count, smem_w, p);                   \
-            return square ? launch_seg_warp<float, false, true, T>(s, sm_count, smem_w, p)                    \
-                          : launch_seg_warp<float, false, false, T>(s, sm_count, smem_w, p);                  \
-        }                                                                                                     \
-        if (two) return launch_seg_warp<double, true, false, T>(s, sm_count, smem_w, p);                      \
-        return square ? launch_seg_warp<double, false, true, T>(s, sm_count, smem_w, p)                       \
-                      : launch_seg_warp<double, false, false, T>(s, sm_count, smem_w, p);
-        if (threads == 1024) { PML_SEG_WARP_DISPATCH(1024) }
-        if (threads == 512) { PML_SEG_WARP_DISPATCH(512) }
-        PML_SEG_WARP_DISPATCH(256)
+#define PML_SEG_WARP_DISPATCH(T)                                                                       \
+    do {                                                                                               \
+        if (value_bytes == 4) {                                                                        \
+            if (two) return launch_seg_warp<float, true, false, T>(s, sm_count, smem, p);              \
+            return square ? launch_seg_warp<float, false, true, T>(s, sm_count, smem, p)               \
+                          : launch_seg_warp<float, false, false, T>(s, sm_count, smem, p);             \
+        }                                                                                              \
+        if (two) return launch_seg_warp<double, true, false, T>(s, sm_count, smem, p);                 \
+        return square ? launch_seg_warp<double, false, true, T>(s, sm_count, smem, p)                  \
+                      : launch_seg_warp<double, false, false, T>(s, sm_count, smem, p);                \
+    } while (0)
+    if (p.n_hot > 0) PML_SEG_WARP_DISPATCH(1024);
+    PML_SEG_WARP_DISPATCH(256);
 #undef PML_SEG_WARP_DISPATCH
-    }
-    const int items = chunk_entries / S_THREADS;
-    if (items != 8) return -1;
-    if (value_bytes == 4) {
-        if (two) return launch_seg_one<float, 8, true, false>(s, grid, smem, p);
-        return square ? launch_seg_one<float, 8, false, true>(s, grid, smem, p)
-                      : launch_seg_one<float, 8, false, false>(s, grid, smem, p);
-    }
-    if (two) return launch_seg_one<double, 8, true, false>(s, grid, smem, p);
-    return square ? launch_seg_one<double, 8, false, true>(s, grid, smem, p)
-                  : launch_seg_one<double, 8, false, false>(s, grid, smem, p);
 }
 
 // ------------------------------------------------------------------------------------------

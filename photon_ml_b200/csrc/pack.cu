@@ -1,7 +1,7 @@
 // pack.cu -- one-off packing of LabeledPoint rows (lib/data/LabeledPoint.scala:32-36) into the
 // device-resident layout the evaluation kernels read: CSR with columns renumbered by descending
 // frequency, plus a CSC copy ordered by (internal column, row) with chunk metadata for
-// col_pass_kernel.
+// the column-pass kernels.
 //
 // This runs once per data set (and never per evaluation); it uses CUB's device radix sort and
 // scan for the transposition.  The reference has no counterpart -- it re-reads JVM objects every
