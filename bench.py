@@ -133,6 +133,26 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
+def ncu_traffic(kernel_substrings):
+    """DRAM bytes (read + write) per launch of the named kernels, summed, from the committed `ncu --set full`
+    capture of this same workload (profiles/); None when the capture is not there."""
+    import csv
+    path = os.path.join(ROOT, "profiles", "r01_tiled_ncu_full.csv")
+    if not os.path.exists(path):
+        return None
+    rows = list(csv.reader(open(path)))
+    hdr, units = rows[0], rows[1]
+    ki, ri, wi = hdr.index("Kernel Name"), hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
+    scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    total, found = 0.0, set()
+    for r in rows[2:]:
+        for sub in kernel_substrings:
+            if sub in r[ki] and sub not in found:
+                total += float(r[ri]) * scale[units[ri]] + float(r[wi]) * scale[units[wi]]
+                found.add(sub)
+    return total if len(found) == len(kernel_substrings) else None
+
+
 def kernel_bytes(info, has_offset, has_weight):
     """ALGORITHMIC bytes per launch of the two evaluation kernels."""
     V = info.value_bytes
@@ -286,10 +306,16 @@ def run_ours(args):
         col_ms = profile["col_pass"][0] / max(1, profile["col_pass"][1])
         tiled_ms = profile["col_pass_tiled"][0] / max(1, profile["col_pass_tiled"][1])
         col_ms += tiled_ms   # the CSC pass = tiled hot columns + plain cold columns
-        dominant = ("seg_spmv_warp_kernel (CSC pass, X^T r)" if col_ms >= row_ms
+        dominant = ("CSC pass X^T r: seg_spmv_tiled_kernel (hot columns) + seg_spmv_warp_kernel (cold columns)" if col_ms >= row_ms
                     else ("seg_spmv_warp_kernel (CSR pass, X w)" if info.margin_variant == 1 else
                           "row_pass_kernel<%d lanes/row> (CSR pass, X w + pointwise)" % info.margin_variant))
         dom_bytes, dom_ms = (col_bytes, col_ms) if col_ms >= row_ms else (row_bytes, row_ms)
+        if world > 1:
+            traffic = None   # the capture is of the single-GPU shard sizes
+        elif col_ms >= row_ms:
+            traffic = ncu_traffic(["seg_spmv_tiled_kernel", "0, 0, 0, 256>"])   # tiled hot columns + cold columns
+        else:
+            traffic = ncu_traffic(["0, 0, 1, 1024>"])
         achieved = dom_bytes / (dom_ms * 1e-3) / 1e9
         ms_per_step = ms / args.steps
         step_bytes = info.vg_algorithmic_bytes - 2 * info.n * 8  # no offsets / weights in this workload
@@ -326,7 +352,8 @@ def run_ours(args):
             "clocks": clocks,
             "roofline": {"bound": "hbm", "kernel": dominant, "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "frac_of_nominal_8000": achieved / 8000.0, "peak_source": peak_src,
-                         "traffic": None, "algorithmic_bytes_per_launch": int(dom_bytes),
+                         "traffic": traffic, "traffic_source": "profiles/r01_tiled_ncu_full.csv (ncu --set full, dram read+write)",
+                         "algorithmic_bytes_per_launch": int(dom_bytes),
                          "avg_launch_ms": dom_ms},
             "kernels": {k: {"ms_per_launch": v[0] / max(1, v[1]), "launches": int(v[1])} for k, v in profile.items()},
             "row_pass": {"algorithmic_bytes": int(row_bytes), "ms": row_ms, "GBps": row_bytes / (row_ms * 1e-3) / 1e9},

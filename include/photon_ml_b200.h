@@ -61,7 +61,7 @@ typedef struct pml_dataset_info {
     int64_t nnz;           /* stored entries */
     int32_t d;             /* feature dimension (incl. intercept column if any) */
     int32_t value_bytes;   /* 4 or 8: what PML_STORE_* resolved to */
-    int32_t margin_variant; /* CSR margin kernel: lanes per row; 0 = segment-per-warp; 1 = segment-per-CTA */
+    int32_t margin_variant; /* CSR margin kernel of single-vector passes: lanes per row; 0 = segment-per-warp; 1 = entry-chunked */
     int32_t n_chunks;      /* CSC chunks of the transpose kernel */
     int64_t nonempty_cols; /* columns with at least one entry */
     int64_t device_bytes;  /* HBM held by this data set */
@@ -200,9 +200,11 @@ int pml_ctx_launch_count(pml_ctx *ctx, int64_t *out);
 int pml_ctx_set_profiling(pml_ctx *ctx, int on);
 int pml_ctx_read_profile(pml_ctx *ctx, double *out_ms /* [PML_K_COUNT] */,
                          int64_t *out_launches /* [PML_K_COUNT] */);
-/* force a CSR margin-kernel variant: lanes per row in {2,4,8,16,32} (32 = warp-per-row),
- * 0 = segment-per-warp, 1 = segment-per-CTA (entry-chunked, load-balanced), -1 = back to the
- * default choice.  For benchmarking and tests. */
+/* force a CSR margin-kernel variant for every pass: lanes per row in {2,4,8,16,32} (32 =
+ * warp-per-row), 0 = segment-per-warp (32-row blocks), 1 = entry-chunked (256-entry warp chunks,
+ * load-balanced), -1 = back to the default choice (1 for single-vector passes, lanes per row
+ * chosen from nnz/row for the paired pass of a cold Hessian-vector product).  For benchmarking
+ * and tests. */
 int pml_dataset_set_margin_variant(pml_dataset *ds, int lanes_per_row);
 
 /* ---- batched per-entity problems (random effects) ------------------------------------------ */
