@@ -575,6 +575,7 @@ static int build_tiled(cudaStream_t s, int sm_count, int64_t n, int64_t nnz, con
     }
     const int64_t n_hot = hs[(size_t)n_tiles];
     const int64_t hot_len = po[(size_t)n_tiles];
+    if (n_hot > 2000000000ll) return PML_OK;  // the run compaction below counts with 32-bit ints: stay untiled
     const int64_t cold_nnz = nnz - n_hot;
     const int64_t total = hot_len + cold_nnz;
     PML_CUDA(cudaMemcpyAsync(po_dev.p, po.data(), sizeof(uint32_t) * (size_t)(n_tiles + 1), cudaMemcpyHostToDevice, s));
