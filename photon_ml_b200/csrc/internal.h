@@ -38,6 +38,7 @@ constexpr int SEG_TABLE_BYTES = 96 * 1024;   // hot prefix of the coefficient ve
 constexpr int R_THREADS = 256;
 constexpr int R_WARPS = R_THREADS / 32;
 constexpr int R_STREAM_CAP = 512;  // products staged per warp per piece in the segment-per-warp variant
+constexpr int SMALL_IO_DIM = 4096;   // host vectors up to this length are staged through pinned memory
 constexpr int MAX_PARTIALS = 4096; // upper bound on row-kernel CTAs (block partials of F and P)
 
 enum RowMode {
@@ -202,8 +203,20 @@ struct pml_ctx {
     cudaStream_t stream = nullptr;
     std::mutex mu;
     int64_t launches = 0;
-    // pinned staging for scalars
+    // pinned staging for scalars, and for small coefficient / gradient vectors of host-buffer calls
     double *h_scalar = nullptr;
+    double *h_stage = nullptr;  // 2 * (SMALL_IO_DIM + 2) doubles
+};
+
+// a captured value+gradient sequence and what it was captured for
+struct pml_graph {
+    cudaGraphExec_t exec = nullptr;
+    uint64_t version = 0;
+    int loss = -1;
+    const double *coef = nullptr;
+    double *out = nullptr;
+    bool want_vector = true, want_row_loss = false;
+    int kernels = 0;
 };
 
 struct pml_dataset {
@@ -240,6 +253,9 @@ struct pml_dataset {
     int cached_loss = -1;
     bool cache_valid = false;
     int lanes_per_row = 8;  // lanes-per-row variant used for paired (Hessian-vector, cold) passes, or the forced variant
+    uint64_t version = 1;       // bumped by every change to rows / normalization / variant (invalidates vg_graph)
+    pml_graph vg_graph;
+    bool graph_failed = false;
     bool keep_column_order = false;  // batches: columns are compacted, not renumbered by frequency
     bool variant_forced = false;  // pml_dataset_set_margin_variant pinned one variant for every pass
     int row_grid = 1;       // CTAs of the last row-pass launch (= number of (F, P) partials)
