@@ -534,7 +534,9 @@ static int build_tiled(cudaStream_t s, int sm_count, int64_t n, int64_t nnz, con
     PML_CUDA(cudaMemcpyAsync(h_counts.data(), counts_sorted_dev, sizeof(uint32_t) * (size_t)k_cap, cudaMemcpyDeviceToHost, s));
     PML_CUDA(cudaStreamSynchronize(s));
     int64_t K = 0;
-    while (K < k_cap && (int64_t)h_counts[(size_t)K] >= 2 * n_tiles) ++K;
+    int64_t min_run = 2;  // average entries per (tile, column) run a column must reach to be tiled
+    if (const char *e = std::getenv("PML_TILE_MIN_RUN")) min_run = std::atoll(e);
+    while (K < k_cap && (int64_t)h_counts[(size_t)K] >= min_run * n_tiles) ++K;
     if (K < 16 || n_tiles * K >= (1ll << 31)) return PML_OK;
 
     DevBuf entry_row, keys, keys_sorted, perm_in, perm_out, tmp, hs_dev, po_dev, run_flag, hot_dest;

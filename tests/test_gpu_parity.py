@@ -379,3 +379,40 @@ def test_medium_problem_properties_and_oracle(ctx):
     gm = ds.value_and_gradient(oracle.POISSON, w - eps * v1)[1]
     assert util.rel_err((gp - gm) / (2 * eps), h1) <= 1e-5
     ds.close()
+
+
+def test_two_contexts_from_two_threads():
+    # Handles on different contexts may be used concurrently from different threads (TestNG parallel=methods,
+    # executor task threads); each context has its own stream and lock.
+    import threading
+    import photon_ml_b200 as pml
+    rng = np.random.default_rng(200)
+    n, d = 4000, 150
+    problems = []
+    for _ in range(2):
+        row_ptr, col, val = util.random_csr(rng, n, d, 10, skew=1.1)
+        label = util.labels_for(rng, 0, n)
+        w = rng.normal(scale=0.3, size=d)
+        ref = oracle.Data(n, d, row_ptr, col, val, label)
+        problems.append((row_ptr, col, val, label, w, oracle.value_and_gradient(ref, oracle.LOGISTIC, w)))
+    errors = []
+
+    def work(k):
+        try:
+            row_ptr, col, val, label, w, (f_ref, g_ref) = problems[k]
+            c = pml.Context(0)
+            ds = pml.Dataset.from_csr(c, n, d, row_ptr, col, val, label)
+            for _ in range(50):
+                f, g = ds.value_and_gradient(oracle.LOGISTIC, w)
+                assert abs(f - f_ref) <= TOL * abs(f_ref) and util.rel_err(g, g_ref) <= TOL
+            ds.close()
+            c.close()
+        except Exception as e:  # noqa: BLE001
+            errors.append(repr(e))
+
+    threads = [threading.Thread(target=work, args=(k,)) for k in range(2)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert not errors, errors
