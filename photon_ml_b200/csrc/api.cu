@@ -117,8 +117,8 @@ int run_col_and_fixup(pml_dataset *ds, bool square, double *out, bool with_scala
     cudaStream_t s = ctx->stream;
     const TiledSide &hot = ds->t.hot;
     if (hot.n_chunks > 0) {
-        // hot columns: r slices staged in shared memory, per-(tile, column) sums into `partial`
-        PML_CUDA(cudaMemsetAsync(hot.partial, 0, sizeof(double) * (size_t)hot.n_tiles * (size_t)hot.n_hot_cols, s));
+        // hot columns: r slices staged in shared memory, per-(tile, column) sums into `partial` (zeroed when packed:
+        // every run is assigned afresh by each pass, slots without a run are never written)
         PML_TRY(run(ctx, PML_K_COL_TILED, [&] {
             return launch_seg_tiled(s, ctx->sm_count, ds->value_bytes, square, hot, ds->r, ds->n);
         }));
@@ -126,7 +126,9 @@ int run_col_and_fixup(pml_dataset *ds, bool square, double *out, bool with_scala
             return launch_fixup(s, hot.fix, hot.n_fix, hot.n_fix_long, hot.carry, hot.partial, nullptr, nullptr, 0, nullptr,
                                 0, false, false);
         }));
-        PML_TRY(run(ctx, PML_K_FINALIZE, [&] { return launch_reduce_partial(s, hot, ds->t.nzcol_id, out); }));
+        PML_TRY(run(ctx, PML_K_FINALIZE, [&] { 
+            return launch_reduce_partial(s, hot.n_tiles, hot.n_hot_cols, hot.partial, ds->t.nzcol_id, out);
+        }));
     }
     SegParams cp;
     std::memset(&cp, 0, sizeof(cp));
@@ -136,15 +138,30 @@ int run_col_and_fixup(pml_dataset *ds, bool square, double *out, bool with_scala
     cp.run_id = ds->t.cold_run_id;
     cp.chunk_lo = ds->t.chunk_col_lo;
     cp.table = ds->r;
-    cp.out = out;
     cp.carry = ds->carry_head;
     cp.n_chunks = ds->t.n_chunks;
+    // cold columns cut into super blocks of rows: per-(super block, column) sums (slots without a run stay zero from
+    // pack time), then one reduction over the blocks
+    const bool super = ds->t.n_super > 1;
+    double *col_out = super ? ds->t.cold_partial : out;
+    cp.out = col_out;
     PML_TRY(run(ctx, PML_K_COL, [&] {
         return launch_seg_spmv(s, ctx->sm_count, ds->value_bytes, false, square, cp, 0);
     }));
+    if (super) {
+        PML_TRY(run(ctx, PML_K_FIXUP, [&] {
+            return launch_fixup(s, ds->t.fix, ds->t.n_fix, ds->t.n_fix_long, ds->carry_head, col_out, nullptr, nullptr, 0,
+                                nullptr, 0, false, false);
+        }));
+        PML_TRY(run(ctx, PML_K_FINALIZE, [&] {
+            return launch_reduce_partial(s, ds->t.n_super, ds->t.cold_cols, ds->t.cold_partial,
+                                         ds->t.nzcol_id + hot.n_hot_cols, out);
+        }));
+    }
     PML_TRY(run(ctx, PML_K_FIXUP, [&] {
-        return launch_fixup(s, ds->t.fix, ds->t.n_fix, ds->t.n_fix_long, ds->carry_head, out, nullptr, nullptr, ds->d,
-                            with_scalars ? ds->partials : nullptr, ds->row_grid, write_value, true);
+        return launch_fixup(s, super ? nullptr : ds->t.fix, super ? 0 : ds->t.n_fix, super ? 0 : ds->t.n_fix_long,
+                            ds->carry_head, out, nullptr, nullptr, ds->d, with_scalars ? ds->partials : nullptr,
+                            ds->row_grid, write_value, true);
     }));
     return PML_OK;
 }
@@ -243,27 +260,34 @@ int vg_raw_launches(pml_dataset *ds, int loss, const double *coef_dev, double *o
 
 // The value+gradient sequence is 8-11 launches and 2-3 memsets with nothing data-dependent on the host side, so
 // it is captured once per (data-set state, loss, buffers) into a CUDA graph and replayed: on small problems and on
-// small per-GPU shards the gaps between launches are a visible share of the evaluation (config 1: 58 -> us; 8 GPUs:
-// 0.52 ms steps).  Any change to the data set (offsets, weights, labels, normalization, variant) bumps `version`
-// and the next call re-captures.  Profiling (per-kernel events) and PML_NO_GRAPH=1 bypass the graph.
-int vg_raw(pml_dataset *ds, int loss, const double *coef_dev, double *out_raw_dev, bool want_vector = true)
+// small per-GPU shards the gaps between launches are a visible share of the evaluation (profiles/: config 1 and the
+// 8-GPU steps).  Any change to the data set (offsets, weights, labels, normalization, variant) bumps `version`
+// and the next call re-captures.  Profiling (per-kernel events) and PML_NO_GRAPH=1 bypass the graph; so does a
+// caller that hands over different buffers on every call (re-capturing costs more than the launches it saves).
+template <typename F>
+int replay(pml_dataset *ds, pml_graph &g, const pml_graph_key &key, F &&launches)
 {
     pml_ctx *ctx = ds->ctx;
     static const bool disabled = std::getenv("PML_NO_GRAPH") != nullptr;
-    if (disabled || ctx->profiling || ds->graph_failed) return vg_raw_launches(ds, loss, coef_dev, out_raw_dev, want_vector);
-    pml_graph &g = ds->vg_graph;
-    const bool hit = g.exec != nullptr && g.version == ds->version && g.loss == loss && g.coef == coef_dev &&
-                     g.out == out_raw_dev && g.want_vector == want_vector && g.want_row_loss == ds->want_row_loss;
-    if (!hit) {
+    if (disabled || ctx->profiling || ds->graph_failed) return launches();
+    if (g.exec == nullptr || !(g.key == key)) {
+        if (g.misses >= 4 && !(g.last == key)) {  // buffers keep changing: plain launches until a key repeats
+            g.last = key;
+            return launches();
+        }
+        const bool same_but_buffers = g.exec != nullptr && g.key.version == key.version && g.key.loss == key.loss &&
+                                      g.key.flags == key.flags;
+        g.misses = (same_but_buffers && !(g.last == key)) ? g.misses + 1 : 0;
+        g.last = key;
         if (g.exec) { cudaGraphExecDestroy(g.exec); g.exec = nullptr; }
         cudaGraph_t graph = nullptr;
         const int64_t before = ctx->launches;
         if (cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeRelaxed) != cudaSuccess) {
             cudaGetLastError();
             ds->graph_failed = true;
-            return vg_raw_launches(ds, loss, coef_dev, out_raw_dev, want_vector);
+            return launches();
         }
-        const int rc = vg_raw_launches(ds, loss, coef_dev, out_raw_dev, want_vector);
+        const int rc = launches();
         const cudaError_t e = cudaStreamEndCapture(ctx->stream, &graph);
         g.kernels = (int)(ctx->launches - before);
         ctx->launches = before;
@@ -274,29 +298,35 @@ int vg_raw(pml_dataset *ds, int loss, const double *coef_dev, double *out_raw_de
             g.exec = nullptr;
             ds->graph_failed = true;  // e.g. a launch that cannot be captured: stay on plain launches
             if (rc != PML_OK) return rc;
-            return vg_raw_launches(ds, loss, coef_dev, out_raw_dev, want_vector);
+            return launches();
         }
         cudaGraphDestroy(graph);
-        g.version = ds->version;
-        g.loss = loss;
-        g.coef = coef_dev;
-        g.out = out_raw_dev;
-        g.want_vector = want_vector;
-        g.want_row_loss = ds->want_row_loss;
+        g.key = key;
     }
+    else g.misses = 0;
     PML_CUDA(cudaGraphLaunch(g.exec, ctx->stream));
     ctx->launches += g.kernels;
     return PML_OK;
 }
 
-int hv_raw(pml_dataset *ds, int loss, const double *coef_dev, uint64_t tag, const double *v_dev, double *out_raw_dev)
+int vg_raw(pml_dataset *ds, int loss, const double *coef_dev, double *out_raw_dev, bool want_vector = true)
+{
+    pml_graph_key key;
+    key.version = ds->version;
+    key.loss = loss;
+    key.coef = coef_dev;
+    key.out = out_raw_dev;
+    key.flags = (want_vector ? 1 : 0) | (ds->want_row_loss ? 2 : 0);
+    return replay(ds, ds->vg_graph, key, [&] { return vg_raw_launches(ds, loss, coef_dev, out_raw_dev, want_vector); });
+}
+
+// The launches of one Hessian-vector product.  cached = the curvature wt*l''(z) of every row is taken from dcache
+// (written by an earlier product at the same coefficients), so only ev is gathered; keep = write dcache.
+int hv_raw_launches(pml_dataset *ds, int loss, const double *coef_dev, const double *v_dev, double *out_raw_dev, bool cached,
+                    bool keep)
 {
     pml_ctx *ctx = ds->ctx;
     cudaStream_t s = ctx->stream;
-    if (loss == PML_LOSS_SMOOTHED_HINGE)
-        return fail(PML_EINVAL, "the smoothed hinge loss is not twice differentiable (it only implements DiffFunction)");
-    const bool norm = ds->factors || ds->shifts;
-    const bool cached = tag != 0 && ds->cache_valid && ds->cached_tag == tag && ds->cached_loss == loss;
     RowPassParams rp;
     std::memset(&rp, 0, sizeof(rp));
     rp.n = ds->n;
@@ -310,40 +340,74 @@ int hv_raw(pml_dataset *ds, int loss, const double *coef_dev, uint64_t tag, cons
     rp.partials = ds->partials;
     rp.loss = loss;
     int np = 0;
-    if (!cached) {
-        if (coef_dev == nullptr) return fail(PML_EINVAL, "coefficients are required when no cached pass matches the tag");
-        if (tag != 0 && ds->dcache == nullptr) PML_TRY(dev_alloc(&ds->dcache, (size_t)ds->n, &ds->bytes));
-        PML_TRY(run(ctx, PML_K_PREPARE, [&] {
-            return launch_prepare_vectors(s, ds->d, coef_dev, v_dev, ds->factors, ds->shifts, ds->t.rank, ds->vec,
-                                          ds->shift_partials, &np);
-        }));
-        rp.vec = ds->vec;
-        if (ds->shifts) {
-            rp.shift_partials = ds->shift_partials;
-            rp.n_shift_partials = np;
-        }
-        rp.dcache = tag != 0 ? ds->dcache : nullptr;
-        rp.mode = MODE_HV_COLD;
-        PML_TRY(run_rows(ds, rp, true));
-        ds->cache_valid = tag != 0;
-        ds->cached_tag = tag;
-        ds->cached_loss = loss;
-    } else {
-        PML_TRY(run(ctx, PML_K_PREPARE, [&] {
-            return launch_prepare_vectors(s, ds->d, v_dev, nullptr, ds->factors, ds->shifts, ds->t.rank, ds->vec,
-                                          ds->shift_partials, &np);
-        }));
-        rp.vec = ds->vec;
-        if (ds->shifts) {
-            rp.shift_partials = ds->shift_partials;
-            rp.n_shift_partials = np;
-        }
-        rp.dcache = ds->dcache;
-        rp.mode = MODE_HV_CACHED;
-        PML_TRY(run_rows(ds, rp, false));
+    PML_TRY(run(ctx, PML_K_PREPARE, [&] {
+        return cached ? launch_prepare_vectors(s, ds->d, v_dev, nullptr, ds->factors, ds->shifts, ds->t.rank, ds->vec,
+                                               ds->shift_partials, &np)
+                      : launch_prepare_vectors(s, ds->d, coef_dev, v_dev, ds->factors, ds->shifts, ds->t.rank, ds->vec,
+                                               ds->shift_partials, &np);
+    }));
+    rp.vec = ds->vec;
+    if (ds->shifts) {
+        rp.shift_partials = ds->shift_partials;
+        rp.n_shift_partials = np;
     }
+    rp.dcache = (cached || keep) ? ds->dcache : nullptr;
+    rp.mode = cached ? MODE_HV_CACHED : MODE_HV_COLD;
+    PML_TRY(run_rows(ds, rp, !cached));
     PML_CUDA(cudaMemsetAsync(out_raw_dev, 0, sizeof(double) * (size_t)(ds->d + 2), s));
     return run_col_and_fixup(ds, false, out_raw_dev, true, false);
+}
+
+// TRON asks for tens of Hessian-vector products per outer iteration, on small problems each a handful of
+// launch-bound kernels: both sequences (with and without the margin pass) are replayed as CUDA graphs like vg_raw.
+int hv_raw(pml_dataset *ds, int loss, const double *coef_dev, uint64_t tag, const double *v_dev, double *out_raw_dev)
+{
+    if (loss == PML_LOSS_SMOOTHED_HINGE)
+        return fail(PML_EINVAL, "the smoothed hinge loss is not twice differentiable (it only implements DiffFunction)");
+    const bool cached = tag != 0 && ds->cache_valid && ds->cached_tag == tag && ds->cached_loss == loss;
+    const bool keep = tag != 0;
+    if (!cached) {
+        if (coef_dev == nullptr) return fail(PML_EINVAL, "coefficients are required when no cached pass matches the tag");
+        // allocate outside the captured sequence
+        if (keep && ds->dcache == nullptr) PML_TRY(dev_alloc(&ds->dcache, (size_t)ds->n, &ds->bytes));
+        if (ds->lanes_per_row == 1 && ds->zb == nullptr) {  // the paired pass on the entry-chunked kernel (run_rows)
+            PML_TRY(dev_alloc(&ds->zb, (size_t)ds->n, &ds->bytes));
+            PML_TRY(dev_alloc(&ds->carry_row2, (size_t)ds->rs.n_chunks + 1, &ds->bytes));
+        }
+    }
+    pml_graph_key key;
+    key.version = ds->version;
+    key.loss = loss;
+    key.coef = cached ? nullptr : coef_dev;
+    key.v = v_dev;
+    key.out = out_raw_dev;
+    key.flags = keep ? 1 : 0;
+    PML_TRY(replay(ds, cached ? ds->hv_cached_graph : ds->hv_cold_graph, key,
+                   [&] { return hv_raw_launches(ds, loss, coef_dev, v_dev, out_raw_dev, cached, keep); }));
+    if (!cached) {
+        ds->cache_valid = keep;
+        ds->cached_tag = tag;
+        ds->cached_loss = loss;
+    }
+    return PML_OK;
+}
+
+// Device-pointer callers (torch tensors) tend to hand over a different buffer on every call, which would force a
+// re-capture each time.  Up to STAGE_DEV_DIM coefficients the vector is copied (device to device, a few us) into the
+// data set's own buffer once the pointer differs from the one the graph holds, so the replay keeps hitting.
+constexpr int STAGE_DEV_DIM = 1 << 20;
+
+const double *stable_input(pml_dataset *ds, const pml_graph &g, const double *held, const double *p, double *stage)
+{
+    static const bool disabled = std::getenv("PML_NO_GRAPH") != nullptr;
+    if (p == nullptr || p == held || p == stage || g.exec == nullptr || ds->d > STAGE_DEV_DIM || disabled ||
+        ds->ctx->profiling || ds->graph_failed)
+        return p;
+    if (cudaMemcpyAsync(stage, p, sizeof(double) * (size_t)ds->d, cudaMemcpyDeviceToDevice, ds->ctx->stream) != cudaSuccess) {
+        cudaGetLastError();
+        return p;
+    }
+    return stage;
 }
 
 int finalize(pml_dataset *ds, int loss, const double *raw_dev, double *out_value_dev, double *out_vec_dev)
@@ -423,7 +487,7 @@ int pml_ctx_create(int device, pml_ctx **out)
     }
     PML_CUDA(cudaStreamCreate(&ctx->stream));
     PML_CUDA(cudaMallocHost(&ctx->h_scalar, 64));
-    PML_CUDA(cudaMallocHost(&ctx->h_stage, sizeof(double) * 2 * (SMALL_IO_DIM + 2)));
+    PML_CUDA(cudaMallocHost(&ctx->h_stage, sizeof(double) * 3 * (SMALL_IO_DIM + 2)));
     *out = ctx;
     return PML_OK;
 }
@@ -509,9 +573,10 @@ int pml_dataset_destroy(pml_dataset *ds)
         cudaSetDevice(ds->ctx->device);
         cudaStreamSynchronize(ds->ctx->stream);
     }
-    if (ds->vg_graph.exec) cudaGraphExecDestroy(ds->vg_graph.exec);
+    for (pml_graph *g : { &ds->vg_graph, &ds->hv_cold_graph, &ds->hv_cached_graph })
+        if (g->exec) cudaGraphExecDestroy(g->exec);
     void *ptrs[] = { ds->row_ptr, ds->col, ds->val, ds->label, ds->offset, ds->weight, ds->t.idx_alloc, ds->t.val_alloc, ds->t.hot.run_id, ds->t.hot.chunk_lo, ds->t.hot.tile_first_chunk, ds->t.hot.fix,
-                     ds->t.hot.partial, ds->t.hot.carry,
+                     ds->t.hot.partial, ds->t.hot.carry, ds->t.cold_slot, ds->t.cold_partial,
                      ds->t.nzcol_ptr, ds->t.nzcol_id, ds->t.rank, ds->t.chunk_col_lo, ds->t.fix, ds->rs.nzrow_id, ds->rs.chunk_lo,
                      ds->rs.fix, ds->za, ds->zb, ds->carry_row, ds->carry_row2, ds->row_loss, ds->factors, ds->shifts, ds->r,
                      ds->dcache, ds->partials, ds->carry_head, ds->raw, ds->vec, ds->shift_partials, ds->io_a, ds->io_b,
@@ -809,6 +874,7 @@ int pml_value_and_gradient_dev(pml_dataset *ds, int loss, const double *coef_dev
     if (!coef_dev) return fail(PML_EINVAL, "null buffer");
     Guard g(ds->ctx);
     PML_CUDA(cudaSetDevice(ds->ctx->device));
+    coef_dev = stable_input(ds, ds->vg_graph, ds->vg_graph.key.coef, coef_dev, ds->io_a);
     PML_TRY(vg_raw(ds, loss, coef_dev, ds->raw, out_grad_dev != nullptr));
     return finalize(ds, loss, ds->raw, out_value_dev, out_grad_dev);
 }
@@ -821,6 +887,10 @@ int pml_hessian_vector_dev(pml_dataset *ds, int loss, const double *coef_dev, ui
     if (!v_dev || !out_hv_dev) return fail(PML_EINVAL, "null buffer");
     Guard g(ds->ctx);
     PML_CUDA(cudaSetDevice(ds->ctx->device));
+    const bool cached = coef_tag != 0 && ds->cache_valid && ds->cached_tag == coef_tag && ds->cached_loss == loss;
+    const pml_graph &hg = cached ? ds->hv_cached_graph : ds->hv_cold_graph;
+    if (!cached) coef_dev = stable_input(ds, hg, hg.key.coef, coef_dev, ds->io_a);
+    v_dev = stable_input(ds, hg, hg.key.v, v_dev, ds->io_b);
     PML_TRY(hv_raw(ds, loss, coef_dev, coef_tag, v_dev, ds->raw));
     return finalize(ds, loss, ds->raw, nullptr, out_hv_dev);
 }
@@ -870,19 +940,29 @@ int pml_hessian_vector(pml_dataset *ds, int loss, const double *coef, uint64_t c
     cudaStream_t s = ds->ctx->stream;
     const size_t db = sizeof(double) * (size_t)ds->d;
     const bool cached = coef_tag != 0 && ds->cache_valid && ds->cached_tag == coef_tag && ds->cached_loss == loss;
+    // small vectors through pinned staging, as in pml_value_and_gradient
+    const bool staged = ds->d <= SMALL_IO_DIM;
+    double *h_coef = ds->ctx->h_stage, *h_out = h_coef + SMALL_IO_DIM + 2, *h_v = h_out + SMALL_IO_DIM + 2;
     if (!cached) {
         if (!coef && ds->d > 0) return fail(PML_EINVAL, "null coefficients");
-        if (ds->d > 0) PML_CUDA(cudaMemcpyAsync(ds->io_a, coef, db, cudaMemcpyHostToDevice, s));
+        if (ds->d > 0) {
+            if (staged) std::memcpy(h_coef, coef, db);
+            PML_CUDA(cudaMemcpyAsync(ds->io_a, staged ? h_coef : coef, db, cudaMemcpyHostToDevice, s));
+        }
     }
-    if (ds->d > 0) PML_CUDA(cudaMemcpyAsync(ds->io_b, v, db, cudaMemcpyHostToDevice, s));
+    if (ds->d > 0) {
+        if (staged) std::memcpy(h_v, v, db);
+        PML_CUDA(cudaMemcpyAsync(ds->io_b, staged ? h_v : v, db, cudaMemcpyHostToDevice, s));
+    }
     PML_TRY(hv_raw(ds, loss, ds->io_a, coef_tag, ds->io_b, ds->raw));
     const double *src = ds->raw;
     if (ds->factors || ds->shifts) {
         PML_TRY(finalize(ds, loss, ds->raw, nullptr, ds->io_b));
         src = ds->io_b;
     }
-    if (ds->d > 0) PML_CUDA(cudaMemcpyAsync(out_hv, src, db, cudaMemcpyDeviceToHost, s));
+    if (ds->d > 0) PML_CUDA(cudaMemcpyAsync(staged ? h_out : out_hv, src, db, cudaMemcpyDeviceToHost, s));
     PML_CUDA(cudaStreamSynchronize(s));
+    if (staged && ds->d > 0) std::memcpy(out_hv, h_out, db);
     return PML_OK;
 }
 

@@ -106,7 +106,8 @@ int launch_finalize(cudaStream_t s, int d, const double *raw, const double *fact
 
 int launch_seg_tiled(cudaStream_t s, int sm_count, int value_bytes, bool square, const TiledSide &t, const double *r,
                      int64_t n);
-int launch_reduce_partial(cudaStream_t s, const TiledSide &t, const int32_t *nzcol_id, double *out);
+int launch_reduce_partial(cudaStream_t s, int n_tiles, int n_cols, const double *partial, const int32_t *nzcol_id,
+                          double *out);
 int launch_offsets_from_scores(cudaStream_t s, int64_t n, const double *base, const double *scores, const int64_t *row_map,
                                double *out);
 int launch_globalize_cols(cudaStream_t s, int64_t n_entities, const int64_t *ent_row_ptr, const int64_t *coef_ptr,
@@ -122,6 +123,8 @@ int build_transpose(cudaStream_t s, int sm_count, int64_t n, int32_t d, int64_t 
 constexpr int TILE_MAX_ROWS = 25000;            // r slice + zero slot <= 200 KB of shared memory (one CTA per SM)
 constexpr int64_t TILE_MIN_ROWS_DEFAULT = 262144;  // below this r lives happily in L2: no tiling
 constexpr int64_t TILE_PARTIAL_BYTES = 128ll << 20; // cap on the (tile, column) partial matrix
+constexpr int64_t SUPER_ROWS_DEFAULT = 6ll << 20;   // rows per super block of the cold columns: 48 MB of r in the L2
+constexpr int64_t SUPER_MIN_ROWS_DEFAULT = 12ll << 20; // up to this many rows r (96 MB) is left in one piece
 int build_row_side(cudaStream_t s, int64_t n, int64_t nnz, const uint32_t *row_ptr, int32_t *col, int chunk_entries,
                    RowSide *out);
 int narrow_check(cudaStream_t s, const double *val, int64_t nnz, bool *all_exact);
@@ -152,7 +155,12 @@ struct Packed {
     TiledSide hot;
     // cold region (all columns when nothing is tiled): plain CSC ordered by (internal column, row)
     int64_t cold_nnz = 0;
-    const int32_t *cold_run_id = nullptr;  // run ordinal -> original column id (= nzcol_id + hot.n_hot_cols)
+    const int32_t *cold_run_id = nullptr;  // run ordinal -> original column id (= nzcol_id + hot.n_hot_cols), or,
+                                           //   with super blocks, -> slot of cold_partial (= cold_slot)
+    int n_super = 1;                       // super blocks of rows the cold region is cut into (1 = plain CSC)
+    int cold_cols = 0;                     // m - hot.n_hot_cols when n_super > 1
+    int32_t *cold_slot = nullptr;          // owned; run ordinal -> super block * cold_cols + (column - K)
+    double *cold_partial = nullptr;        // n_super * cold_cols per-(super block, column) sums
     int32_t *csc_row = nullptr;    // view: row index, bit 31 set on the first entry of each column
     void *csc_val = nullptr;
     uint32_t *nzcol_ptr = nullptr; // d+1: entry offset of each internal column (columns >= m are empty)
@@ -209,14 +217,25 @@ struct pml_ctx {
 };
 
 // a captured value+gradient sequence and what it was captured for
+// What a captured launch sequence depends on besides the kernels' own inputs: replayed only while all of it matches.
+struct pml_graph_key {
+    uint64_t version = 0;       // state of the data set (rows, normalization, variant)
+    int loss = -1;
+    const double *coef = nullptr, *v = nullptr;
+    double *out = nullptr;
+    int flags = 0;              // sequence-specific switches (want_vector, want_row_loss, cache the curvature ...)
+    bool operator==(const pml_graph_key &o) const
+    {
+        return version == o.version && loss == o.loss && coef == o.coef && v == o.v && out == o.out && flags == o.flags;
+    }
+};
+
 struct pml_graph {
     cudaGraphExec_t exec = nullptr;
-    uint64_t version = 0;
-    int loss = -1;
-    const double *coef = nullptr;
-    double *out = nullptr;
-    bool want_vector = true, want_row_loss = false;
+    pml_graph_key key;   // what `exec` was captured for
+    pml_graph_key last;  // the most recent request
     int kernels = 0;
+    int misses = 0;  // consecutive re-captures caused by nothing but different buffers
 };
 
 struct pml_dataset {
@@ -255,6 +274,7 @@ struct pml_dataset {
     int lanes_per_row = 8;  // lanes-per-row variant used for paired (Hessian-vector, cold) passes, or the forced variant
     uint64_t version = 1;       // bumped by every change to rows / normalization / variant (invalidates vg_graph)
     pml_graph vg_graph;
+    pml_graph hv_cold_graph, hv_cached_graph;  // Hessian-vector: margin pass included / curvature taken from dcache
     bool graph_failed = false;
     bool keep_column_order = false;  // batches: columns are compacted, not renumbered by frequency
     bool variant_forced = false;  // pml_dataset_set_margin_variant pinned one variant for every pass

@@ -705,10 +705,27 @@ reduce_partial_kernel(int n_tiles, int K, const double *__restrict__ partial, co
     }
 }
 
-int launch_reduce_partial(cudaStream_t s, const TiledSide &t, const int32_t *nzcol_id, double *out)
+// The same for a handful of row blocks (the super blocks of the cold columns): one thread per column.
+__global__ void __launch_bounds__(256)
+reduce_few_kernel(int n_blocks, int n_cols, const double *__restrict__ partial, const int32_t *__restrict__ nzcol_id,
+                  double *__restrict__ out)
 {
-    if (t.n_hot_cols <= 0) return 0;
-    reduce_partial_kernel<<<(t.n_hot_cols + 31) / 32, 256, 0, s>>>(t.n_tiles, t.n_hot_cols, t.partial, nzcol_id, out);
+    const int c = blockIdx.x * 256 + threadIdx.x;
+    if (c >= n_cols) return;
+    double s = 0.0;
+    for (int t = 0; t < n_blocks; ++t) s += __ldcs(partial + (size_t)t * n_cols + c);
+    out[nzcol_id[c]] = s;
+}
+
+int launch_reduce_partial(cudaStream_t s, int n_tiles, int n_cols, const double *partial, const int32_t *nzcol_id,
+                          double *out)
+{
+    if (n_cols <= 0) return 0;
+    if (n_tiles <= 16) {
+        reduce_few_kernel<<<(n_cols + 255) / 256, 256, 0, s>>>(n_tiles, n_cols, partial, nzcol_id, out);
+        return cudaGetLastError() == cudaSuccess ? 1 : -1;
+    }
+    reduce_partial_kernel<<<(n_cols + 31) / 32, 256, 0, s>>>(n_tiles, n_cols, partial, nzcol_id, out);
     return cudaGetLastError() == cudaSuccess ? 1 : -1;
 }
 

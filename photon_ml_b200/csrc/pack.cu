@@ -178,15 +178,26 @@ __global__ void check_cols_kernel(const int32_t *__restrict__ col, int64_t nnz, 
     if (wrong) atomicAdd(bad, (unsigned long long)wrong);
 }
 
-// key of an entry for the tiled layout: hot columns (< K) sort by (row tile, column), cold ones after, by column
+// key of an entry for the tiled layout: hot columns (< K) sort by (row tile, column); cold ones after, by
+// (super block of rows, column) -- super blocks keep the slice of r the cold gathers touch inside the L2
 __global__ void tile_keys_kernel(int64_t nnz, const int32_t *__restrict__ col, const int32_t *__restrict__ entry_row,
-                                 int K, int tile_rows, int n_tiles, uint32_t *__restrict__ keys)
+                                 int K, int tile_rows, int n_tiles, int super_rows, uint32_t cold_cols,
+                                 uint32_t *__restrict__ keys)
 {
     for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < nnz; k += (int64_t)gridDim.x * blockDim.x) {
         const int32_t c = col[k];
-        keys[k] = c < K ? (uint32_t)(entry_row[k] / tile_rows) * (uint32_t)K + (uint32_t)c
-                        : (uint32_t)n_tiles * (uint32_t)K + (uint32_t)(c - K);
+        const int32_t row = entry_row[k];
+        keys[k] = c < K ? (uint32_t)(row / tile_rows) * (uint32_t)K + (uint32_t)c
+                        : (uint32_t)n_tiles * (uint32_t)K + (uint32_t)(row / super_rows) * cold_cols + (uint32_t)(c - K);
     }
+}
+
+// slot of a cold run in cold_partial = its key less the hot key range (keys are unsigned: sort them as such)
+__global__ void cold_slots_kernel(int64_t runs, const int32_t *__restrict__ run_keys, uint32_t hot_keys,
+                                  int32_t *__restrict__ slot)
+{
+    for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < runs; q += (int64_t)gridDim.x * blockDim.x)
+        slot[q] = (int32_t)((uint32_t)run_keys[q] - hot_keys);
 }
 
 // first sorted position whose key is >= t*K, for t in [0, n_tiles]
@@ -212,13 +223,13 @@ __global__ void fill_pad_kernel(int64_t len, int32_t pad_idx, int32_t *__restric
 }
 
 // Moves sorted entry i to its place in [hot tiled | cold]; marks run starts; records, per sorted position,
-// whether a hot run starts there and where it landed (for the run list).
+// whether a run starts there and where it landed (for the run lists).
 template <typename VT>
 __global__ void tile_scatter_kernel(int64_t nnz, const uint32_t *__restrict__ sorted_keys, const uint32_t *__restrict__ perm,
                                     const int32_t *__restrict__ entry_row, const VT *__restrict__ val, int K, int tile_rows,
                                     int n_tiles, const uint32_t *__restrict__ hs, const uint32_t *__restrict__ po,
                                     uint32_t cold_off, int32_t *__restrict__ idx, VT *__restrict__ out_val,
-                                    unsigned char *__restrict__ hot_run_flag, uint32_t *__restrict__ hot_dest)
+                                    unsigned char *__restrict__ run_flag, uint32_t *__restrict__ run_dest)
 {
     const uint32_t hot_keys = (uint32_t)n_tiles * (uint32_t)K;
     const uint32_t n_hot = hs[n_tiles];
@@ -232,11 +243,11 @@ __global__ void tile_scatter_kernel(int64_t nnz, const uint32_t *__restrict__ so
             const uint32_t t = key / (uint32_t)K;
             dest = po[t] + ((uint32_t)i - hs[t]);
             row -= (int32_t)t * tile_rows;
-            hot_run_flag[i] = start ? 1 : 0;
-            hot_dest[i] = dest;
         } else {
             dest = cold_off + ((uint32_t)i - n_hot);
         }
+        run_flag[i] = start ? 1 : 0;
+        run_dest[i] = dest;
         idx[dest] = start ? (row | (int32_t)0x80000000) : row;
         out_val[dest] = val[src];
     }
@@ -538,6 +549,16 @@ static int build_tiled(cudaStream_t s, int sm_count, int64_t n, int64_t nnz, con
     if (const char *e = std::getenv("PML_TILE_MIN_RUN")) min_run = std::atoll(e);
     while (K < k_cap && (int64_t)h_counts[(size_t)K] >= min_run * n_tiles) ++K;
     if (K < 16 || n_tiles * K >= (1ll << 31)) return PML_OK;
+    // cold columns: super blocks of rows whose slice of r (8 bytes a row) stays in the L2 next to the stream
+    const int64_t cold_cols = m - K;
+    // (r of up to SUPER_MIN_ROWS rows stays there as a whole: measured, no gain from cutting it)
+    int64_t super_max = n > SUPER_MIN_ROWS_DEFAULT ? SUPER_ROWS_DEFAULT : n;
+    if (const char *e = std::getenv("PML_SUPER_ROWS")) super_max = std::atoll(e);
+    if (super_max < 1) super_max = 1;
+    int64_t n_super = cold_cols > 0 ? (n + super_max - 1) / super_max : 1;
+    if (n_tiles * K + n_super * cold_cols >= (1ll << 32) || n_super * cold_cols >= (1ll << 31)) n_super = 1;
+    const int super_rows = (int)((n + n_super - 1) / n_super);
+    n_super = (n + super_rows - 1) / super_rows;
 
     DevBuf entry_row, keys, keys_sorted, perm_in, perm_out, tmp, hs_dev, po_dev, run_flag, hot_dest;
     PML_CUDA(entry_row.alloc(sizeof(int32_t) * (size_t)nnz));
@@ -550,9 +571,10 @@ static int build_tiled(cudaStream_t s, int sm_count, int64_t n, int64_t nnz, con
     expand_rows_kernel<<<grid_for(n * 32), 256, 0, s>>>(n, row_ptr, entry_row.as<int32_t>());
     iota_kernel<<<grid_for(nnz), 256, 0, s>>>(nnz, perm_in.as<uint32_t>());
     tile_keys_kernel<<<grid_for(nnz), 256, 0, s>>>(nnz, col, entry_row.as<int32_t>(), (int)K, tile_rows, (int)n_tiles,
+                                                   super_rows, (uint32_t)(cold_cols > 0 ? cold_cols : 1),
                                                    keys.as<uint32_t>());
     PML_CUDA(cudaGetLastError());
-    const int64_t max_key = n_tiles * K + (m - K);
+    const int64_t max_key = n_tiles * K + n_super * cold_cols;
     int end_bit = 1;
     while (end_bit < 32 && (1LL << end_bit) <= max_key) ++end_bit;
     size_t tmp_bytes = 0;
@@ -577,8 +599,9 @@ static int build_tiled(cudaStream_t s, int sm_count, int64_t n, int64_t nnz, con
     }
     const int64_t n_hot = hs[(size_t)n_tiles];
     const int64_t hot_len = po[(size_t)n_tiles];
-    if (n_hot > 2000000000ll) return PML_OK;  // the run compaction below counts with 32-bit ints: stay untiled
     const int64_t cold_nnz = nnz - n_hot;
+    // the run compaction below counts with 32-bit ints: stay untiled
+    if (n_hot > 2000000000ll || (n_super > 1 && cold_nnz > 2000000000ll)) return PML_OK;
     const int64_t total = hot_len + cold_nnz;
     PML_CUDA(cudaMemcpyAsync(po_dev.p, po.data(), sizeof(uint32_t) * (size_t)(n_tiles + 1), cudaMemcpyHostToDevice, s));
 
@@ -589,8 +612,8 @@ static int build_tiled(cudaStream_t s, int sm_count, int64_t n, int64_t nnz, con
     PML_CUDA(cudaMemsetAsync(out->val_alloc, 0, (size_t)value_bytes * (size_t)(total + 16), s));
     PML_CUDA(cudaMemsetAsync(out->idx_alloc + hot_len, 0, sizeof(int32_t) * (size_t)(cold_nnz + 16), s));
     fill_pad_kernel<<<grid_for(hot_len), 256, 0, s>>>(hot_len, tile_rows, out->idx_alloc);
-    PML_CUDA(run_flag.alloc((size_t)(n_hot + 1)));
-    PML_CUDA(hot_dest.alloc(sizeof(uint32_t) * (size_t)(n_hot + 1)));
+    PML_CUDA(run_flag.alloc((size_t)(nnz + 1)));
+    PML_CUDA(hot_dest.alloc(sizeof(uint32_t) * (size_t)(nnz + 1)));
     if (value_bytes == 4)
         tile_scatter_kernel<float><<<grid_for(nnz), 256, 0, s>>>(
             nnz, keys_sorted.as<uint32_t>(), perm_out.as<uint32_t>(), entry_row.as<int32_t>(), (const float *)val, (int)K,
@@ -637,6 +660,7 @@ static int build_tiled(cudaStream_t s, int sm_count, int64_t n, int64_t nnz, con
     PML_CUDA(cudaMalloc(&h.chunk_lo, sizeof(int32_t) * (size_t)(h.n_chunks + 1)));
     PML_CUDA(cudaMalloc(&h.tile_first_chunk, sizeof(int32_t) * (size_t)(n_tiles + 1)));
     PML_CUDA(cudaMalloc(&h.partial, sizeof(double) * (size_t)(n_tiles * K)));
+    PML_CUDA(cudaMemsetAsync(h.partial, 0, sizeof(double) * (size_t)(n_tiles * K), s));  // slots without a run stay 0
     PML_CUDA(cudaMalloc(&h.carry, sizeof(double) * (size_t)(h.n_chunks + 1)));
     out->bytes += (int64_t)sizeof(int32_t) * (h.n_chunks + 1 + n_tiles + 1) + (int64_t)sizeof(double) * (n_tiles * K + h.n_chunks + 1);
     PML_CUDA(cudaMemcpyAsync(h.tile_first_chunk, first_chunk.data(), sizeof(int32_t) * (size_t)(n_tiles + 1),
@@ -651,15 +675,51 @@ static int build_tiled(cudaStream_t s, int sm_count, int64_t n, int64_t nnz, con
                                &h.n_fix_long, &out->bytes));
     }
 
-    // cold region: plain CSC over internal columns [K, m)
+    // cold region: CSC over internal columns [K, m), one copy per super block of rows
     out->csc_row = out->idx_alloc + hot_len;
     out->csc_val = (char *)out->val_alloc + (size_t)hot_len * value_bytes;
     out->cold_nnz = cold_nnz;
-    out->cold_run_id = out->nzcol_id + K;
     out->n_chunks = (int)((cold_nnz + 255) / 256);
     PML_CUDA(cudaMalloc(&out->chunk_col_lo, sizeof(int32_t) * (size_t)(out->n_chunks + 1)));
     out->bytes += (int64_t)sizeof(int32_t) * (out->n_chunks + 1);
-    {
+    if (n_super > 1 && cold_nnz > 0) {
+        // one run = one (super block, column) pair -> slot [super block][column - K] of cold_partial, which
+        // reduce_partial_kernel adds up over the super blocks; the run list comes from the run-start flags
+        DevBuf run_ptr_cold, run_key_cold, t1, head;
+        PML_CUDA(run_ptr_cold.alloc(sizeof(uint32_t) * (size_t)(cold_nnz + 2)));
+        PML_CUDA(run_key_cold.alloc(sizeof(int32_t) * (size_t)(cold_nnz + 2)));
+        size_t tb = 0;
+        PML_CUDA(cub::DeviceSelect::Flagged(nullptr, tb, hot_dest.as<uint32_t>() + n_hot, run_flag.as<unsigned char>() + n_hot,
+                                            run_ptr_cold.as<uint32_t>(), n_sel.as<int>(), (int)cold_nnz, s));
+        PML_CUDA(t1.alloc(tb));
+        PML_CUDA(cub::DeviceSelect::Flagged(t1.p, tb, hot_dest.as<uint32_t>() + n_hot, run_flag.as<unsigned char>() + n_hot,
+                                            run_ptr_cold.as<uint32_t>(), n_sel.as<int>(), (int)cold_nnz, s));
+        PML_CUDA(cub::DeviceSelect::Flagged(t1.p, tb, reinterpret_cast<const int32_t *>(keys_sorted.as<uint32_t>()) + n_hot,
+                                            run_flag.as<unsigned char>() + n_hot, run_key_cold.as<int32_t>(),
+                                            n_sel.as<int>(), (int)cold_nnz, s));
+        int runs_cold = 0;
+        PML_CUDA(cudaMemcpyAsync(&runs_cold, n_sel.p, sizeof(int), cudaMemcpyDeviceToHost, s));
+        PML_CUDA(cudaStreamSynchronize(s));
+        const uint32_t end32 = (uint32_t)(hot_len + cold_nnz);
+        PML_CUDA(cudaMemcpyAsync(run_ptr_cold.as<uint32_t>() + runs_cold, &end32, sizeof(uint32_t), cudaMemcpyHostToDevice, s));
+        PML_CUDA(cudaMalloc(&out->cold_slot, sizeof(int32_t) * (size_t)(runs_cold + 1)));
+        cold_slots_kernel<<<grid_for(runs_cold), 256, 0, s>>>(runs_cold, run_key_cold.as<int32_t>(),
+                                                             (uint32_t)(n_tiles * K), out->cold_slot);
+        out->cold_run_id = out->cold_slot;
+        out->n_super = (int)n_super;
+        out->cold_cols = (int)cold_cols;
+        PML_CUDA(cudaMalloc(&out->cold_partial, sizeof(double) * (size_t)(n_super * cold_cols)));
+        PML_CUDA(cudaMemsetAsync(out->cold_partial, 0, sizeof(double) * (size_t)(n_super * cold_cols), s));
+        out->bytes += (int64_t)sizeof(int32_t) * (runs_cold + 1) + (int64_t)sizeof(double) * n_super * cold_cols;
+        PML_CUDA(head.alloc(sizeof(int32_t) * (size_t)(out->n_chunks + 1)));
+        chunk_meta_kernel<<<grid_for((int64_t)out->n_chunks + 1), 256, 0, s>>>(out->n_chunks, 256, runs_cold,
+                                                                              run_ptr_cold.as<uint32_t>(), out->chunk_col_lo,
+                                                                              head.as<int32_t>(), (uint32_t)hot_len);
+        PML_CUDA(cudaGetLastError());
+        PML_TRY(build_fix_list(s, out->n_chunks, out->chunk_col_lo, head.as<int32_t>(), out->cold_run_id, runs_cold, &out->fix,
+                               &out->n_fix, &out->n_fix_long, &out->bytes));
+    } else {
+        out->cold_run_id = out->nzcol_id + K;
         DevBuf head;
         PML_CUDA(head.alloc(sizeof(int32_t) * (size_t)(out->n_chunks + 1)));
         chunk_meta_kernel<<<grid_for((int64_t)out->n_chunks + 1), 256, 0, s>>>(out->n_chunks, 256, m - K, out->nzcol_ptr + K,

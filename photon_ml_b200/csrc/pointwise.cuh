@@ -14,12 +14,6 @@ namespace pml {
 // from contracting a*b+c into an FMA where Scala rounds twice.
 // ------------------------------------------------------------------------------------------
 
-// lib/util/MathUtils.scala:34-40
-__device__ __forceinline__ double log1p_exp(double x)
-{
-    return x > 0 ? x + log1p(exp(-x)) : log1p(exp(x));
-}
-
 // api/function/glm/LogisticLossFunction.scala:54
 __device__ __forceinline__ double sigmoid(double z) { return 1.0 / (1.0 + exp(-z)); }
 
@@ -28,15 +22,23 @@ __device__ __forceinline__ double sigmoid(double z) { return 1.0 / (1.0 + exp(-z
 __device__ __forceinline__ void loss_and_dz(int loss, double z, double y, double &l, double &dl)
 {
     switch (loss) {
-    case PML_LOSS_LOGISTIC:
-        if (y > 0.5) {  // MathConst.POSITIVE_RESPONSE_THRESHOLD, lib/constants/MathConst.scala:23
-            l = log1p_exp(-z);
-            dl = -sigmoid(-z);
-        } else {
-            l = log1p_exp(z);
-            dl = sigmoid(z);
-        }
+    case PML_LOSS_LOGISTIC: {
+        // The reference takes (log1pExp(-z), -sigmoid(-z)) for positive labels and (log1pExp(z), sigmoid(z))
+        // otherwise: both are (log1pExp(m), +-sigmoid(m)) with m = -+z.  Written without the branches -- a warp
+        // mixing labels or signs would otherwise run every exp/log1p twice, and fp64 transcendentals are what
+        // bounds the per-row epilogue -- and with one exp: e = exp(-|m|) serves log1pExp (lib/util/MathUtils.scala:34-40:
+        // x > 0 ? x + log1p(exp(-x)) : log1p(exp(x))) exactly as in the reference
+        // and gives sigmoid(m) = 1/(1+e) for m > 0 (the reference's expression) or e/(1+e) (equal to the
+        // reference's 1/(1+exp(-m)) to an ulp).
+        const bool positive = y > 0.5;  // MathConst.POSITIVE_RESPONSE_THRESHOLD, lib/constants/MathConst.scala:23
+        const double m = positive ? -z : z;
+        const double e = exp(-fabs(m));
+        const double lp = log1p(e);
+        l = m > 0 ? m + lp : lp;
+        const double sg = (m > 0 ? 1.0 : e) / (1.0 + e);
+        dl = positive ? -sg : sg;
         break;
+    }
     case PML_LOSS_POISSON: {
         double pred = exp(z);  // no overflow guard, as in the reference
         l = __dsub_rn(pred, __dmul_rn(z, y));

@@ -20,13 +20,15 @@ LOSSES = [oracle.LOGISTIC, oracle.POISSON, oracle.SQUARED]
 VARIANTS = [0, 1, 2, 4, 8, 16, 32]
 
 
-@pytest.fixture(autouse=True, params=["plain-csc", "tiled-csc"])
+@pytest.fixture(autouse=True, params=["plain-csc", "tiled-csc", "tiled-csc-super"])
 def csc_layout(request, monkeypatch):
-    """Every test runs with the plain CSC layout and with the row-tiled one (hot columns gathered from
-    shared-memory slices of r), forced onto these small inputs with tiny tiles."""
-    if request.param == "tiled-csc":
+    """Every test runs with the plain CSC layout, with the row-tiled one (hot columns gathered from
+    shared-memory slices of r), forced onto these small inputs with tiny tiles, and with the cold columns
+    additionally cut into super blocks of rows (per-(super block, column) sums reduced afterwards)."""
+    if request.param.startswith("tiled-csc"):
         monkeypatch.setenv("PML_TILE_MIN_ROWS", "0")
         monkeypatch.setenv("PML_TILE_ROWS", "37")
+        monkeypatch.setenv("PML_SUPER_ROWS", "101" if request.param.endswith("super") else "1000000000")
     else:
         monkeypatch.setenv("PML_NO_TILING", "1")
     yield
