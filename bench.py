@@ -5,8 +5,9 @@ Workload (BASELINE.json configs[1], the configuration the metric is quoted on): 
 regression, synthetic 10 M rows x 1 M features, 66 Zipf(1.1) draws per row (duplicates merged,
 so ~50 stored entries per row), values in {1,2,3,4}/4 (fp32-exact), offsets 0, weights 1.  A
 "step" is one value+gradient evaluation over all rows.  With --gpus N the SAME rows are sharded
-over N ranks (strong scaling); every rank produces raw partial sums and one NCCL all-reduce of
-d+2 doubles replaces Spark's treeAggregate.
+over N ranks (strong scaling); every rank produces raw partial sums and one merge of d+2 doubles
+(the library's peer-memory kernel; PML_BENCH_COLLECTIVE=nccl for torch's NCCL all-reduce) replaces
+Spark's treeAggregate.
 
   python bench.py [--gpus N] [--steps K] [--warmup W]                 our arm
   python bench.py --impl reference [--gpus N] [--steps K] [--warmup W]  CPU restatement of the
@@ -206,10 +207,35 @@ def run_ours(args):
     out_grad = torch.empty(d, dtype=torch.float64, device=device)
     torch.cuda.synchronize()
 
+    # The exchange step that replaces treeAggregate (ValueAndGradientAggregator.scala:243-247): by default the
+    # library's own merge kernel over NVLink peer memory, fused with getVector (peer.cu); PML_BENCH_COLLECTIVE=nccl
+    # (or a box without peer access) takes torch's NCCL all-reduce of the d+2 raw sums followed by finalize_dev.
+    peer, collective = None, "none"
+    if world > 1:
+        collective = "nccl all-reduce of d+2 doubles, then finalize_dev"
+        if os.environ.get("PML_BENCH_COLLECTIVE", "peer") == "peer":
+            try:
+                peer = pml.Peer(ctx, d)
+            except Exception as e:  # noqa: BLE001
+                sys.stderr.write("rank %d: peer memory unavailable (%s)\n" % (rank, e))
+            ok = torch.tensor([1 if peer is not None else 0], device=device)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+            if int(ok) == 0:
+                if peer is not None:
+                    peer.close()
+                peer = None
+            else:
+                collective = "peer_merge_kernel: sums over NVLink peer memory in rank order, fused with getVector"
+                result = torch.as_tensor(peer.result_array(), device=device)
+                out_grad, out_value = result[:d], result[d:d + 1]   # the library's result buffer, no copy
+
     def step():
+        if peer is not None:
+            peer.value_and_gradient(ds, LOSS_POISSON, coef.data_ptr())
+            return
         ds.value_and_gradient_raw_dev(LOSS_POISSON, coef.data_ptr(), raw.data_ptr())
         if world > 1:
-            dist.all_reduce(raw)  # replaces treeAggregate (ValueAndGradientAggregator.scala:243-247)
+            dist.all_reduce(raw)
         ds.finalize_dev(LOSS_POISSON, raw.data_ptr(), out_value.data_ptr(), out_grad.data_ptr())
 
     def barrier():
@@ -286,6 +312,9 @@ def run_ours(args):
         hv_ms = {}
         for name, tag in (("cold", 0), ("cached", 12345)):
             def hv_step():
+                if peer is not None:
+                    peer.hessian_vector(ds, LOSS_POISSON, coef.data_ptr(), v.data_ptr(), tag=tag)
+                    return
                 ds.hessian_vector_raw_dev(LOSS_POISSON, coef.data_ptr(), v.data_ptr(), raw.data_ptr(), tag=tag)
                 if world > 1:
                     dist.all_reduce(raw)
@@ -344,7 +373,8 @@ def run_ours(args):
                 "workload": "configs[1]: Poisson regression, 10M rows x 1M feats, 66 Zipf(1.1) draws/row "
                             "(%.1f stored nnz/row), fp32 values, fp64 accumulation" % (info.nnz / max(1, info.n)),
                 "rows_total": N_ROWS, "rows_per_gpu": int(info.n), "nnz_per_gpu": int(info.nnz), "d": int(d),
-                "parallelism": "row-sharded x%d, one all-reduce of d+2 fp64" % world if world > 1 else "single GPU",
+                "parallelism": "row-sharded x%d, one merge of d+2 fp64 per evaluation" % world if world > 1 else "single GPU",
+                "collective": collective,
                 "l2_flush": "inputs larger than L2 (%.1f GB streamed per step vs 126 MB L2)" % (step_bytes / 1e9),
                 "row_pass_variant": int(info.margin_variant),
                 "launch_mode": "plain launches with per-kernel events in the timed region" if world == 1 else
@@ -356,7 +386,7 @@ def run_ours(args):
             "e2e": {"value": e2e_steps / e2e_s, "unit": "evals/s", "h2d_bytes_per_step": d * 8,
                     "d2h_bytes_per_step": d * 8 + 8, "ms_per_step": 1e3 * e2e_s / e2e_steps,
                     "api": "pml_value_and_gradient (host buffers, pinned)" if world == 1 else
-                           "rank 0: H2D coef; NCCL broadcast; raw_dev; NCCL all-reduce; finalize_dev; rank 0: D2H",
+                           "rank 0: H2D coef; NCCL broadcast of coef; evaluation + merge (%s); rank 0: D2H" % collective,
                     "objective": e2e_value},
             "gpu_launches": int(launches),
             "clocks": clocks,

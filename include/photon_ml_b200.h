@@ -196,7 +196,8 @@ int pml_ctx_launch_count(pml_ctx *ctx, int64_t *out);
 #define PML_K_EPILOGUE 5 /* row_epilogue_kernel (row-pass variant 1 only) */
 #define PML_K_ENTITY 7   /* entity_values_kernel (per-entity objective values of a batch) */
 #define PML_K_COL_TILED 6 /* seg_spmv_tiled_kernel: CSC pass over the hot columns, r staged in shared memory */
-#define PML_K_COUNT 8
+#define PML_K_PEER 8     /* peer_merge_kernel: merge over NVLink peer memory + getVector */
+#define PML_K_COUNT 9
 int pml_ctx_set_profiling(pml_ctx *ctx, int on);
 int pml_ctx_read_profile(pml_ctx *ctx, double *out_ms /* [PML_K_COUNT] */,
                          int64_t *out_launches /* [PML_K_COUNT] */);
@@ -236,6 +237,44 @@ int pml_batch_value_and_gradient(pml_batch *b, int loss, const double *coefs, do
  * optimizer calls every iteration -- no per-call transfer of the concatenated coefficient vector */
 int pml_batch_value_and_gradient_dev(pml_batch *b, int loss, const double *coefs_dev,
                                      double *out_values_dev, double *out_grads_dev);
+
+/* same for the Hessian-vector product (SingleNodeGLMLossFunction.hessianVector :103-113, what a batched per-entity
+ * TRON calls in its conjugate-gradient loop); coef_tag as in pml_hessian_vector. */
+int pml_batch_hessian_vector(pml_batch *b, int loss, const double *coefs, uint64_t coef_tag, const double *vs,
+                             double *out_hvs);
+int pml_batch_hessian_vector_dev(pml_batch *b, int loss, const double *coefs_dev, uint64_t coef_tag,
+                                 const double *vs_dev, double *out_hvs_dev);
+/* residual offsets of all rows in concatenated order (LocalDataSet.addScoresToOffsets, api/data/LocalDataSet.scala:82-89) */
+int pml_batch_set_offsets(pml_batch *b, const double *offsets);
+/* active[e] == 0 takes entity e out of the following evaluations: its value, gradient and Hessian-vector entries
+ * come back as 0 (a lock-step batched optimizer uses this for entities that have converged).  NULL = all active. */
+int pml_batch_set_active(pml_batch *b, const uint8_t *active /* E, host */);
+
+/* ---- the merge step across GPUs over peer memory ------------------------------------------------ */
+/* One process per GPU.  Replaces treeAggregate's merge (ValueAndGradientAggregator.scala:161-176, :243-247;
+ * HessianVectorAggregator.scala:136-152) AND getVector (:199-221) by one kernel per rank that adds up the ranks'
+ * raw sums over NVLink peer memory, in rank order, and leaves the finished value / vector on every rank
+ * (bit-identical everywhere).  Set-up: every rank creates a pml_peer, publishes pml_peer_handle() to all ranks
+ * by any host-side means (the Python binding uses torch.distributed.all_gather_object; a Spark driver would collect
+ * and broadcast them), and passes the rank-ordered concatenation to pml_peer_connect().  Every rank must then
+ * make the same sequence of *_allreduce_dev calls; normalization factors / shifts must be identical on all ranks.
+ * A rank that never arrives makes the others give up after a few seconds with PML_ECUDA on their next call. */
+#define PML_MAX_PEERS 8
+#define PML_PEER_HANDLE_BYTES 64
+typedef struct pml_peer pml_peer;
+int pml_peer_create(pml_ctx *ctx, int rank, int world, int32_t d, pml_peer **out);
+int pml_peer_handle(pml_peer *peer, void *out_handle /* PML_PEER_HANDLE_BYTES */);
+int pml_peer_connect(pml_peer *peer, const void *all_handles /* world * PML_PEER_HANDLE_BYTES, rank order */);
+int pml_peer_destroy(pml_peer *peer);
+/* The rank's exchange buffers (device memory owned by the peer handle): raw = d+2 doubles the evaluation fills,
+ * result = d+1 doubles, [vector(d), value], valid after an *_allreduce_dev call in stream order. */
+int pml_peer_buffers(pml_peer *peer, double **raw_dev, double **result_dev);
+/* DistributedGLMLossFunction.calculate over all ranks' rows: this rank's raw sums, the merge, getVector.
+ * Asynchronous on the context's stream.  out_* may be NULL (read the result buffer instead: no copy). */
+int pml_value_and_gradient_allreduce_dev(pml_dataset *ds, pml_peer *peer, int loss, const double *coef_dev,
+                                         double *out_value_dev, double *out_grad_dev);
+int pml_hessian_vector_allreduce_dev(pml_dataset *ds, pml_peer *peer, int loss, const double *coef_dev,
+                                     uint64_t coef_tag, const double *v_dev, double *out_hv_dev);
 
 /* ---- evaluation without any allocation ------------------------------------------------------ */
 /* No counterpart in the reference (the JVM allocates freely); this exists for callers of THIS

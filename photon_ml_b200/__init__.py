@@ -6,5 +6,5 @@ include/photon_ml_b200.h).  This package is the thin host side used by tests and
 ctypes binding (abi) and a mirror of the reference's objective-function classes (function).
 """
 from . import abi  # noqa: F401
-from .abi import (Batch, Context, Dataset, IllegalArgumentError, PhotonError, LOGISTIC, POISSON, SQUARED,  # noqa: F401
+from .abi import (Batch, Context, Dataset, IllegalArgumentError, Peer, PhotonError, LOGISTIC, POISSON, SQUARED,  # noqa: F401
                   SMOOTHED_HINGE, STORE_AUTO, STORE_F32, STORE_F64)

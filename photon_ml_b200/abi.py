@@ -5,6 +5,7 @@ Context() fails loudly if no CUDA device is visible.
 """
 import ctypes
 import os
+import weakref
 
 import numpy as np
 
@@ -27,6 +28,9 @@ SYMBOLS = [
     "pml_dataset_set_margin_variant", "pml_ctx_set_profiling", "pml_ctx_read_profile",
     "pml_value_noalloc_dev", "pml_batch_create_csr", "pml_batch_destroy", "pml_batch_dataset", "pml_batch_coef_ptr",
     "pml_batch_value_and_gradient", "pml_batch_value_and_gradient_dev", "pml_scores_dev", "pml_dataset_set_offsets_dev", "pml_offsets_from_scores_dev",
+    "pml_batch_hessian_vector", "pml_batch_hessian_vector_dev", "pml_batch_set_offsets", "pml_batch_set_active",
+    "pml_peer_create", "pml_peer_handle", "pml_peer_connect", "pml_peer_destroy", "pml_peer_buffers",
+    "pml_value_and_gradient_allreduce_dev", "pml_hessian_vector_allreduce_dev",
 ]
 
 
@@ -109,6 +113,17 @@ def load():
         "pml_scores_dev": [vp, vp, vp],
         "pml_dataset_set_offsets_dev": [vp, vp],
         "pml_offsets_from_scores_dev": [vp, i64, vp, vp, vp, vp],
+        "pml_batch_hessian_vector": [vp, ctypes.c_int, vp, u64, vp, vp],
+        "pml_batch_hessian_vector_dev": [vp, ctypes.c_int, vp, u64, vp, vp],
+        "pml_batch_set_offsets": [vp, vp],
+        "pml_batch_set_active": [vp, vp],
+        "pml_peer_create": [vp, ctypes.c_int, ctypes.c_int, i32, pp],
+        "pml_peer_handle": [vp, vp],
+        "pml_peer_connect": [vp, vp],
+        "pml_peer_destroy": [vp],
+        "pml_peer_buffers": [vp, pp, pp],
+        "pml_value_and_gradient_allreduce_dev": [vp, vp, ctypes.c_int, vp, vp, vp],
+        "pml_hessian_vector_allreduce_dev": [vp, vp, ctypes.c_int, vp, u64, vp, vp],
     })
     for name, argtypes in sigs.items():
         fn = getattr(lib, name)
@@ -178,20 +193,31 @@ class Context:
         return v.value
 
     KERNEL_KINDS = ["prepare_vectors", "row_pass", "col_pass", "fixup", "finalize", "row_epilogue", "col_pass_tiled",
-                    "entity_values"]
+                    "entity_values", "peer_merge"]
 
     def set_profiling(self, on):
         check(load().pml_ctx_set_profiling(self._h, 1 if on else 0))
 
     def read_profile(self):
         """{kernel class: (total ms, launches)} since the last read (synchronises)."""
-        ms = (ctypes.c_double * 8)()
-        cnt = (ctypes.c_int64 * 8)()
+        ms = (ctypes.c_double * len(self.KERNEL_KINDS))()
+        cnt = (ctypes.c_int64 * len(self.KERNEL_KINDS))()
         check(load().pml_ctx_read_profile(self._h, ms, cnt))
         return {k: (ms[i], cnt[i]) for i, k in enumerate(self.KERNEL_KINDS)}
 
+    def _adopt(self, child):
+        """Handles created on this context are closed before it (whatever order the interpreter drops them in)."""
+        if not hasattr(self, "_children"):
+            self._children = weakref.WeakSet()
+        self._children.add(child)
+
     def close(self):
         if self._h:
+            for child in list(getattr(self, "_children", ())):
+                try:
+                    child.close()
+                except Exception:
+                    pass
             load().pml_ctx_destroy(self._h)
             self._h = ctypes.c_void_p()
 
@@ -209,6 +235,7 @@ class Dataset:
         self.ctx = ctx
         self._h = handle
         self._keep = keepalive
+        ctx._adopt(self)
         info = self.info()
         self.n, self.d, self.nnz = info.n, info.d, info.nnz
 
@@ -356,6 +383,7 @@ class Batch:
         self.dataset = Dataset(ctx, dsh)   # block-diagonal view: set_offsets, hessian_vector, ... for all entities
         self.dataset._borrowed = True
         self.d_total = self.dataset.d
+        ctx._adopt(self)
 
     def value_and_gradient(self, loss, coefs, want_gradient=True):
         coefs = _np(coefs, np.float64, self.d_total, "Coefficient")
@@ -369,12 +397,97 @@ class Batch:
         check(load().pml_batch_value_and_gradient_dev(self._h, loss, coefs_dev, out_values_dev, out_grads_dev))
 
     def hessian_vector(self, loss, coefs, vs, tag=0):
-        return self.dataset.hessian_vector(loss, coefs, vs, tag=tag)
+        """Concatenated per-entity Hessian-vector products (SingleNodeGLMLossFunction.hessianVector for every entity)."""
+        coefs = _np(coefs, np.float64, self.d_total, "Coefficient")
+        vs = _np(vs, np.float64, self.d_total, "Multiply vector")
+        out = np.empty(self.d_total, dtype=np.float64)
+        check(load().pml_batch_hessian_vector(self._h, loss, _ptr(coefs), tag, _ptr(vs), _ptr(out)))
+        return out
+
+    def hessian_vector_dev(self, loss, coefs_dev, vs_dev, out_hvs_dev, tag=0):
+        check(load().pml_batch_hessian_vector_dev(self._h, loss, coefs_dev, tag, vs_dev, out_hvs_dev))
+
+    def set_offsets(self, offsets):
+        """Residual offsets of all rows, concatenated entity order (LocalDataSet.addScoresToOffsets)."""
+        n = self.dataset.n
+        check(load().pml_batch_set_offsets(self._h, _ptr(_np(offsets, np.float64, n, "offsets"))))
+
+    def set_active(self, active):
+        """active[e] falsy: entity e's value / gradient / Hessian-vector entries come back as 0.  None = all."""
+        a = None if active is None else np.ascontiguousarray(np.asarray(active) != 0, dtype=np.uint8)
+        if a is not None and a.shape != (self.n_entities,):
+            raise IllegalArgumentError("Size mismatch. active size: %d != %d." % (a.size, self.n_entities))
+        check(load().pml_batch_set_active(self._h, _ptr(a)))
 
     def close(self):
         if self._h:
             self.dataset.close()
             load().pml_batch_destroy(self._h)
+            self._h = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+PEER_HANDLE_BYTES = 64
+MAX_PEERS = 8
+
+
+class _DeviceArray:
+    """A view of library-owned device memory that torch.as_tensor(..., device='cuda') can wrap without a copy."""
+
+    def __init__(self, ptr, count, owner):
+        self._owner = owner
+        self.__cuda_array_interface__ = {"shape": (count,), "typestr": "<f8", "data": (ptr, False), "version": 2}
+
+
+class Peer:
+    """This rank's end of the merge over NVLink peer memory (pml_peer): one process per GPU.
+
+    `exchange(handle_bytes) -> [handle_bytes of every rank, in rank order]` is the only host-side communication;
+    the default uses torch.distributed.all_gather_object on the default process group."""
+
+    def __init__(self, ctx, d, rank=None, world=None, exchange=None):
+        if rank is None or world is None:
+            import torch.distributed as dist
+            rank, world = dist.get_rank(), dist.get_world_size()
+        self.ctx, self.d, self.rank, self.world = ctx, int(d), int(rank), int(world)
+        self._h = ctypes.c_void_p()
+        check(load().pml_peer_create(ctx._h, self.rank, self.world, self.d, ctypes.byref(self._h)))
+        mine = ctypes.create_string_buffer(PEER_HANDLE_BYTES)
+        check(load().pml_peer_handle(self._h, mine))
+        if exchange is None:
+            def exchange(h):
+                import torch.distributed as dist
+                got = [None] * self.world
+                dist.all_gather_object(got, h)
+                return got
+        handles = exchange(mine.raw) if self.world > 1 else [mine.raw]
+        blob = b"".join(handles)
+        if len(blob) != PEER_HANDLE_BYTES * self.world:
+            raise IllegalArgumentError("expected %d handles of %d bytes" % (self.world, PEER_HANDLE_BYTES))
+        check(load().pml_peer_connect(self._h, blob))
+        raw, res = ctypes.c_void_p(), ctypes.c_void_p()
+        check(load().pml_peer_buffers(self._h, ctypes.byref(raw), ctypes.byref(res)))
+        self.raw_ptr, self.result_ptr = raw.value, res.value
+        ctx._adopt(self)
+
+    def result_array(self):
+        """[vector(d), value] of the last *_allreduce_dev call, as a __cuda_array_interface__ object (no copy)."""
+        return _DeviceArray(self.result_ptr, self.d + 1, self)
+
+    def value_and_gradient(self, ds, loss, coef_dev, out_value_dev=None, out_grad_dev=None):
+        check(load().pml_value_and_gradient_allreduce_dev(ds._h, self._h, loss, coef_dev, out_value_dev, out_grad_dev))
+
+    def hessian_vector(self, ds, loss, coef_dev, v_dev, out_hv_dev=None, tag=0):
+        check(load().pml_hessian_vector_allreduce_dev(ds._h, self._h, loss, coef_dev, tag, v_dev, out_hv_dev))
+
+    def close(self):
+        if self._h:
+            load().pml_peer_destroy(self._h)
             self._h = ctypes.c_void_p()
 
     def __del__(self):

@@ -1178,6 +1178,8 @@ int pml_batch_destroy(pml_batch *b)
     }
     if (b->ent_row_ptr) cudaFree(b->ent_row_ptr);
     if (b->ent_values) cudaFree(b->ent_values);
+    if (b->coef_ptr_dev) cudaFree(b->coef_ptr_dev);
+    if (b->active_dev) cudaFree(b->active_dev);
     if (b->ds) pml_dataset_destroy(b->ds);
     delete b;
     return PML_OK;
@@ -1217,6 +1219,10 @@ int pml_batch_value_and_gradient_dev(pml_batch *b, int loss, const double *coefs
     }));
     if (out_grads_dev && ds->d > 0)
         PML_CUDA(cudaMemcpyAsync(out_grads_dev, ds->raw, sizeof(double) * (size_t)ds->d, cudaMemcpyDeviceToDevice, s));
+    if (b->active_dev)
+        PML_TRY(run(ds->ctx, PML_K_ENTITY, [&] {
+            return launch_mask_entities(s, b->n_entities, b->coef_ptr_dev, b->active_dev, out_values_dev, out_grads_dev);
+        }));
     return PML_OK;
 }
 
@@ -1238,10 +1244,136 @@ int pml_batch_value_and_gradient(pml_batch *b, int loss, const double *coefs, do
     PML_TRY(run(ds->ctx, PML_K_ENTITY, [&] {
         return launch_entity_values(s, b->n_entities, b->ent_row_ptr, ds->row_loss, b->ent_values);
     }));
+    if (b->active_dev)
+        PML_TRY(run(ds->ctx, PML_K_ENTITY, [&] {
+            return launch_mask_entities(s, b->n_entities, b->coef_ptr_dev, b->active_dev, b->ent_values,
+                                        out_grads ? ds->raw : nullptr);
+        }));
     if (out_grads && ds->d > 0) PML_CUDA(cudaMemcpyAsync(out_grads, ds->raw, db, cudaMemcpyDeviceToHost, s));
     if (b->n_entities > 0)
         PML_CUDA(cudaMemcpyAsync(out_values, b->ent_values, sizeof(double) * (size_t)b->n_entities, cudaMemcpyDeviceToHost, s));
     PML_CUDA(cudaStreamSynchronize(s));
+    return PML_OK;
+}
+
+int pml_batch_hessian_vector_dev(pml_batch *b, int loss, const double *coefs_dev, uint64_t coef_tag, const double *vs_dev,
+                                 double *out_hvs_dev)
+{
+    if (!b || !b->ds) return fail(PML_EINVAL, "null batch handle");
+    pml_dataset *ds = b->ds;
+    // entities are the diagonal blocks of one data set: the product of the block-diagonal Hessian with the
+    // concatenated vector is the concatenation of the per-entity products
+    PML_TRY(pml_hessian_vector_dev(ds, loss, coefs_dev, coef_tag, vs_dev, out_hvs_dev));
+    if (b->active_dev) {
+        Guard g(ds->ctx);
+        PML_TRY(run(ds->ctx, PML_K_ENTITY, [&] {
+            return launch_mask_entities(ds->ctx->stream, b->n_entities, b->coef_ptr_dev, b->active_dev, nullptr, out_hvs_dev);
+        }));
+    }
+    return PML_OK;
+}
+
+int pml_batch_hessian_vector(pml_batch *b, int loss, const double *coefs, uint64_t coef_tag, const double *vs, double *out_hvs)
+{
+    if (!b || !b->ds) return fail(PML_EINVAL, "null batch handle");
+    pml_dataset *ds = b->ds;
+    PML_TRY(pml_hessian_vector(ds, loss, coefs, coef_tag, vs, out_hvs));
+    if (b->active_dev && ds->d > 0) {  // rare on the host path: mask on the host copy
+        std::vector<uint8_t> act((size_t)b->n_entities);
+        PML_CUDA(cudaMemcpy(act.data(), b->active_dev, act.size(), cudaMemcpyDeviceToHost));
+        for (int64_t e = 0; e < b->n_entities; ++e)
+            if (!act[(size_t)e])
+                for (int64_t j = b->coef_ptr[(size_t)e]; j < b->coef_ptr[(size_t)e + 1]; ++j) out_hvs[j] = 0.0;
+    }
+    return PML_OK;
+}
+
+int pml_batch_set_offsets(pml_batch *b, const double *offsets)
+{
+    if (!b || !b->ds) return fail(PML_EINVAL, "null batch handle");
+    return pml_dataset_set_offsets(b->ds, offsets);
+}
+
+int pml_batch_set_active(pml_batch *b, const uint8_t *active)
+{
+    if (!b || !b->ds) return fail(PML_EINVAL, "null batch handle");
+    pml_dataset *ds = b->ds;
+    Guard g(ds->ctx);
+    PML_CUDA(cudaSetDevice(ds->ctx->device));
+    cudaStream_t s = ds->ctx->stream;
+    if (active == nullptr) {
+        if (b->active_dev) {
+            PML_CUDA(cudaStreamSynchronize(s));
+            cudaFree(b->active_dev);
+            b->active_dev = nullptr;
+        }
+        return PML_OK;
+    }
+    if (b->n_entities == 0) return PML_OK;
+    if (b->coef_ptr_dev == nullptr) {
+        PML_CUDA(cudaMalloc(&b->coef_ptr_dev, sizeof(int64_t) * (size_t)(b->n_entities + 1)));
+        PML_CUDA(cudaMemcpyAsync(b->coef_ptr_dev, b->coef_ptr.data(), sizeof(int64_t) * (size_t)(b->n_entities + 1),
+                                 cudaMemcpyHostToDevice, s));
+    }
+    if (b->active_dev == nullptr) PML_CUDA(cudaMalloc(&b->active_dev, (size_t)b->n_entities));
+    PML_CUDA(cudaMemcpyAsync(b->active_dev, active, (size_t)b->n_entities, cudaMemcpyHostToDevice, s));
+    PML_CUDA(cudaStreamSynchronize(s));
+    return PML_OK;
+}
+
+// ---- the merge step across GPUs over peer memory (peer.cu) ------------------------------------
+static int check_peer(const pml_dataset *ds, const pml_peer *peer)
+{
+    if (peer == nullptr) return fail(PML_EINVAL, "null peer handle");
+    if (peer->ctx != ds->ctx) return fail(PML_EINVAL, "the peer handle belongs to another context");
+    if (peer->d != ds->d) return fail(PML_EINVAL, "the peer handle was created for another dimension");
+    if (!peer->connected) return fail(PML_ESTATE, "pml_peer_connect has not been called");
+    if (*peer->h_status != 0)
+        return fail(PML_ECUDA, "an earlier merge over peer memory timed out waiting for another rank");
+    return PML_OK;
+}
+
+int pml_value_and_gradient_allreduce_dev(pml_dataset *ds, pml_peer *peer, int loss, const double *coef_dev,
+                                         double *out_value_dev, double *out_grad_dev)
+{
+    PML_TRY(check_ds(ds));
+    PML_TRY(check_peer(ds, peer));
+    if (!valid_loss(loss)) return fail(PML_EINVAL, "unknown loss");
+    if (!coef_dev) return fail(PML_EINVAL, "null buffer");
+    Guard g(ds->ctx);
+    PML_CUDA(cudaSetDevice(ds->ctx->device));
+    cudaStream_t s = ds->ctx->stream;
+    const bool hinge = loss == PML_LOSS_SMOOTHED_HINGE;
+    coef_dev = stable_input(ds, ds->vg_graph, ds->vg_graph.key.coef, coef_dev, ds->io_a);
+    PML_TRY(vg_raw(ds, loss, coef_dev, peer_raw(peer), true));
+    PML_TRY(run(ds->ctx, PML_K_PEER, [&] {
+        return launch_peer_merge(s, ds->ctx->sm_count, peer, hinge ? nullptr : ds->factors, hinge ? nullptr : ds->shifts);
+    }));
+    const double *res = peer_result(peer);
+    if (out_grad_dev && ds->d > 0)
+        PML_CUDA(cudaMemcpyAsync(out_grad_dev, res, sizeof(double) * (size_t)ds->d, cudaMemcpyDeviceToDevice, s));
+    if (out_value_dev) PML_CUDA(cudaMemcpyAsync(out_value_dev, res + ds->d, sizeof(double), cudaMemcpyDeviceToDevice, s));
+    return PML_OK;
+}
+
+int pml_hessian_vector_allreduce_dev(pml_dataset *ds, pml_peer *peer, int loss, const double *coef_dev, uint64_t coef_tag,
+                                     const double *v_dev, double *out_hv_dev)
+{
+    PML_TRY(check_ds(ds));
+    PML_TRY(check_peer(ds, peer));
+    if (!valid_loss(loss)) return fail(PML_EINVAL, "unknown loss");
+    if (!v_dev) return fail(PML_EINVAL, "null buffer");
+    Guard g(ds->ctx);
+    PML_CUDA(cudaSetDevice(ds->ctx->device));
+    cudaStream_t s = ds->ctx->stream;
+    const bool cached = coef_tag != 0 && ds->cache_valid && ds->cached_tag == coef_tag && ds->cached_loss == loss;
+    const pml_graph &hg = cached ? ds->hv_cached_graph : ds->hv_cold_graph;
+    if (!cached) coef_dev = stable_input(ds, hg, hg.key.coef, coef_dev, ds->io_a);
+    v_dev = stable_input(ds, hg, hg.key.v, v_dev, ds->io_b);
+    PML_TRY(hv_raw(ds, loss, coef_dev, coef_tag, v_dev, peer_raw(peer)));
+    PML_TRY(run(ds->ctx, PML_K_PEER, [&] { return launch_peer_merge(s, ds->ctx->sm_count, peer, ds->factors, ds->shifts); }));
+    if (out_hv_dev && ds->d > 0)
+        PML_CUDA(cudaMemcpyAsync(out_hv_dev, peer_result(peer), sizeof(double) * (size_t)ds->d, cudaMemcpyDeviceToDevice, s));
     return PML_OK;
 }
 

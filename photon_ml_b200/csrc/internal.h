@@ -114,6 +114,8 @@ int launch_globalize_cols(cudaStream_t s, int64_t n_entities, const int64_t *ent
                           const int32_t *ent_dim, const int64_t *row_ptr, int32_t *col, unsigned long long *bad);
 int launch_entity_values(cudaStream_t s, int64_t n_entities, const int64_t *ent_row_ptr, const double *row_loss,
                          double *out);
+int launch_mask_entities(cudaStream_t s, int64_t n_entities, const int64_t *coef_ptr, const uint8_t *active, double *values,
+                         double *vec);
 
 // pack.cu: builds the CSC copy and its chunk metadata on the device
 struct Packed;
@@ -190,12 +192,32 @@ struct RowSide {
 
 }  // namespace pml
 
+// One rank's end of the peer-memory merge (peer.cu)
+struct pml_peer {
+    pml_ctx *ctx = nullptr;
+    int rank = 0, world = 1;
+    int64_t d = 0;
+    void *slab = nullptr;                      // [header | raw (d+2) | result (d+1)], cudaMalloc'ed, exported by IPC
+    void *peer_slab[PML_MAX_PEERS] = {};       // every rank's slab as mapped here ([rank] = slab)
+    bool opened[PML_MAX_PEERS] = {};
+    bool connected = false;
+    int *h_status = nullptr, *d_status = nullptr;  // mapped host word: 1 = a barrier timed out
+};
+
+namespace pml {
+int launch_peer_merge(cudaStream_t s, int sm_count, const pml_peer *peer, const double *factors, const double *shifts);
+double *peer_raw(const pml_peer *peer);
+double *peer_result(const pml_peer *peer);
+}  // namespace pml
+
 struct pml_batch {
     pml_dataset *ds = nullptr;      // the block-diagonal data set (owned)
     int64_t n_entities = 0;
     int64_t *ent_row_ptr = nullptr; // device, E+1
     double *ent_values = nullptr;   // device, E
     std::vector<int64_t> coef_ptr;  // host, E+1
+    int64_t *coef_ptr_dev = nullptr; // device, E+1 (allocated by set_active)
+    uint8_t *active_dev = nullptr;  // device, E; null = every entity active
 };
 
 struct pml_span {

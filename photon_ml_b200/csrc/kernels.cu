@@ -937,6 +937,33 @@ int launch_finalize(cudaStream_t s, int d, const double *raw, const double *fact
     return cudaGetLastError() == cudaSuccess ? 1 : -1;
 }
 
+// Entities taken out of a batched evaluation (pml_batch_set_active): their value and their slice of the
+// concatenated vector come back as 0.  One warp per entity.
+__global__ void __launch_bounds__(256)
+mask_entities_kernel(int64_t n_entities, const int64_t *__restrict__ coef_ptr, const uint8_t *__restrict__ active,
+                     double *__restrict__ values, double *__restrict__ vec)
+{
+    const int lane = threadIdx.x & 31;
+    int64_t e = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (; e < n_entities; e += nw) {
+        if (active[e]) continue;
+        if (values && lane == 0) values[e] = 0.0;
+        if (vec)
+            for (int64_t j = coef_ptr[e] + lane; j < coef_ptr[e + 1]; j += 32) vec[j] = 0.0;
+    }
+}
+
+int launch_mask_entities(cudaStream_t s, int64_t n_entities, const int64_t *coef_ptr, const uint8_t *active, double *values,
+                         double *vec)
+{
+    if (n_entities <= 0 || active == nullptr || (values == nullptr && vec == nullptr)) return 0;
+    int64_t grid = (n_entities * 32 + 255) / 256;
+    if (grid > 148 * 8) grid = 148 * 8;
+    mask_entities_kernel<<<(int)grid, 256, 0, s>>>(n_entities, coef_ptr, active, values, vec);
+    return cudaGetLastError() == cudaSuccess ? 1 : -1;
+}
+
 // ------------------------------------------------------------------------------------------
 // Batched per-entity problems (SingleNodeGLMLossFunction over RandomEffectDataSet.activeData,
 // api/algorithm/RandomEffectCoordinate.scala:108-119).  The E local problems are evaluated as ONE

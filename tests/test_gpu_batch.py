@@ -111,3 +111,63 @@ def test_batch_device_buffers_match_host_buffers():
     assert np.array_equal(t_grad.cpu().numpy(), grads)
     batch.close()
     ctx.close()
+
+
+def test_batch_active_mask_and_batch_offsets():
+    """pml_batch_set_active takes entities out of value / gradient / Hessian-vector results (host and device
+    buffers); pml_batch_set_offsets is pml_dataset_set_offsets on the concatenated rows."""
+    import torch
+    import photon_ml_b200 as pml
+    loss = oracle.LOGISTIC
+    rng = np.random.default_rng(77)
+    ent_row_ptr, dims, row_ptr, col, val, n = _entities(rng, 300, 16, 10)
+    label = util.labels_for(rng, loss, n)
+    ctx = pml.Context(0)
+    batch = pml.Batch(ctx, ent_row_ptr, dims, row_ptr, col, val, label)
+    coefs = rng.normal(scale=0.3, size=batch.d_total)
+    vs = rng.normal(size=batch.d_total)
+    values, grads = batch.value_and_gradient(loss, coefs)
+    batch.hessian_vector(loss, coefs, vs, tag=3)
+    hvs = batch.hessian_vector(loss, coefs, vs, tag=3)   # the cached-curvature path, as the masked calls below
+    active = rng.random(len(dims)) < 0.6
+    batch.set_active(active)
+    m_values, m_grads = batch.value_and_gradient(loss, coefs)
+    m_hvs = batch.hessian_vector(loss, coefs, vs, tag=3)
+    elem_active = np.repeat(active, dims)
+    assert np.array_equal(m_values, np.where(active, values, 0.0))
+    assert np.array_equal(m_grads, np.where(elem_active, grads, 0.0))
+    assert np.array_equal(m_hvs, np.where(elem_active, hvs, 0.0))
+    # device buffers
+    dev = torch.device("cuda", 0)
+    with torch.cuda.stream(torch.cuda.ExternalStream(ctx.stream, device=dev)):
+        c = torch.from_numpy(coefs).to(dev)
+        v = torch.from_numpy(vs).to(dev)
+        ov = torch.full((len(dims),), 7.0, dtype=torch.float64, device=dev)
+        og = torch.full((batch.d_total,), 7.0, dtype=torch.float64, device=dev)
+        oh = torch.full((batch.d_total,), 7.0, dtype=torch.float64, device=dev)
+        batch.value_and_gradient_dev(loss, c.data_ptr(), ov.data_ptr(), og.data_ptr())
+        batch.hessian_vector_dev(loss, c.data_ptr(), v.data_ptr(), oh.data_ptr(), tag=3)
+        ctx.synchronize()
+        assert np.array_equal(ov.cpu().numpy(), m_values)
+        assert np.array_equal(og.cpu().numpy(), m_grads)
+        assert np.array_equal(oh.cpu().numpy(), m_hvs)
+    batch.set_active(None)
+    again, _ = batch.value_and_gradient(loss, coefs, want_gradient=False)
+    assert np.array_equal(again, values)
+    with pytest.raises(pml.IllegalArgumentError):
+        batch.set_active(np.ones(len(dims) + 1))
+    # offsets through the batch handle
+    off = rng.normal(scale=0.5, size=n)
+    batch.set_offsets(off)
+    shifted, _ = batch.value_and_gradient(loss, coefs, want_gradient=False)
+    e = int(np.argmax(np.diff(ent_row_ptr)))
+    lo, hi = int(ent_row_ptr[e]), int(ent_row_ptr[e + 1])
+    sl = slice(int(row_ptr[lo]), int(row_ptr[hi]))
+    local = oracle.Data(hi - lo, int(dims[e]), row_ptr[lo:hi + 1] - row_ptr[lo], col[sl], val[sl], label[lo:hi], off[lo:hi])
+    a, b = int(batch.coef_ptr[e]), int(batch.coef_ptr[e + 1])
+    f_ref, _ = oracle.value_and_gradient(local, loss, coefs[a:b])
+    assert abs(shifted[e] - f_ref) <= TOL * abs(f_ref)
+    with pytest.raises(pml.IllegalArgumentError):
+        batch.set_offsets(off[:-1])
+    batch.close()
+    ctx.close()
