@@ -1,7 +1,7 @@
 // peer.cu -- the `merge` step across GPUs (ValueAndGradientAggregator.merge :161-176 as driven by treeAggregate,
 // :243-247) fused with getVector (:199-221), over NVLink peer memory, one process per GPU.
 //
-// Every rank owns a slab [header | raw (d+2) | result (d+1)] allocated with cudaMalloc and opened by all the other
+// Every rank owns a slab [header | raw (d+2, padded) | result (d+1, padded)] allocated with cudaMalloc and opened by all the other
 // ranks through CUDA IPC.  After a rank's evaluation kernels have left its raw sums [vectorSum(d), valueSum,
 // prefactorSum] in its slab, ONE kernel per rank does the whole exchange:
 //   1. barrier: tell every peer "my raw sums are complete", wait until every peer said so;
@@ -67,6 +67,13 @@ __device__ __forceinline__ double ld_peer(const double *p)
     return v;
 }
 
+__device__ __forceinline__ double2 ld_peer2(const double *p)
+{
+    double2 v;
+    asm volatile("ld.relaxed.sys.global.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "l"(p) : "memory");
+    return v;
+}
+
 __device__ __forceinline__ void wait_for(const unsigned int *flag, unsigned int epoch, int *status)
 {
     const long long t0 = clock64();
@@ -79,10 +86,12 @@ __device__ __forceinline__ void wait_for(const unsigned int *flag, unsigned int 
     }
 }
 
+// raw and result are both padded to an even number of doubles: everything moves as 16-byte pairs
+__host__ __device__ __forceinline__ int64_t slab_stride(int64_t d) { return (d + 3) & ~(int64_t)1; }
 __device__ __forceinline__ double *slab_raw(char *slab) { return reinterpret_cast<double *>(slab + PEER_HEADER_BYTES); }
 __device__ __forceinline__ double *slab_result(char *slab, int64_t d)
 {
-    return reinterpret_cast<double *>(slab + PEER_HEADER_BYTES) + (d + 2);
+    return reinterpret_cast<double *>(slab + PEER_HEADER_BYTES) + slab_stride(d);
 }
 
 template <int WORLD>
@@ -103,22 +112,32 @@ __global__ void __launch_bounds__(PEER_THREADS) peer_merge_kernel(const PeerPara
     double P = 0.0;
 #pragma unroll
     for (int q = 0; q < WORLD; ++q) P += ld_peer(slab_raw(p.slab[q]) + d + 1);
-    const int64_t per = (d + 1 + WORLD - 1) / WORLD;  // indices [0, d] -- slot d is the value
+    // elements [0, d] (slot d is the value) as pairs; a trailing pair may take the prefactor slot d+1 along (unused)
+    const int64_t n_pairs = (d + 2) / 2;
+    const int64_t per = (n_pairs + WORLD - 1) / WORLD;
     const int64_t lo = per * p.rank;
-    const int64_t hi = lo + per < d + 1 ? lo + per : d + 1;
-    for (int64_t i = lo + (int64_t)blockIdx.x * PEER_THREADS + threadIdx.x; i < hi; i += (int64_t)gridDim.x * PEER_THREADS) {
-        double part[WORLD];
+    const int64_t hi = lo + per < n_pairs ? lo + per : n_pairs;
+    for (int64_t k = lo + (int64_t)blockIdx.x * PEER_THREADS + threadIdx.x; k < hi; k += (int64_t)gridDim.x * PEER_THREADS) {
+        const int64_t i = 2 * k;
+        double2 part[WORLD];
 #pragma unroll
-        for (int q = 0; q < WORLD; ++q) part[q] = ld_peer(slab_raw(p.slab[q]) + i);
-        double v = 0.0;
+        for (int q = 0; q < WORLD; ++q) part[q] = ld_peer2(slab_raw(p.slab[q]) + i);
+        double2 v = make_double2(0.0, 0.0);
 #pragma unroll
-        for (int q = 0; q < WORLD; ++q) v += part[q];
+        for (int q = 0; q < WORLD; ++q) {
+            v.x += part[q].x;
+            v.y += part[q].y;
+        }
         if (i < d) {
-            if (p.shifts) v = __dsub_rn(v, __dmul_rn(p.shifts[i], P));
-            if (p.factors) v = __dmul_rn(v, p.factors[i]);
+            if (p.shifts) v.x = __dsub_rn(v.x, __dmul_rn(p.shifts[i], P));
+            if (p.factors) v.x = __dmul_rn(v.x, p.factors[i]);
+        }
+        if (i + 1 < d) {
+            if (p.shifts) v.y = __dsub_rn(v.y, __dmul_rn(p.shifts[i + 1], P));
+            if (p.factors) v.y = __dmul_rn(v.y, p.factors[i + 1]);
         }
 #pragma unroll
-        for (int q = 0; q < WORLD; ++q) slab_result(p.slab[q], d)[i] = v;
+        for (int q = 0; q < WORLD; ++q) *reinterpret_cast<double2 *>(slab_result(p.slab[q], d) + i) = v;
     }
 
     // ---- 3. everyone's stores are out ----
@@ -151,7 +170,7 @@ int launch_peer_merge(cudaStream_t s, int sm_count, const pml_peer *peer, const 
     p.factors = factors;
     p.shifts = shifts;
     p.status = peer->d_status;
-    const int64_t per = (peer->d + 1 + peer->world - 1) / peer->world;
+    const int64_t per = ((peer->d + 2) / 2 + peer->world - 1) / peer->world;
     int64_t grid = (per + PEER_THREADS - 1) / PEER_THREADS;
     if (grid > sm_count) grid = sm_count;
     if (grid < 1) grid = 1;
@@ -169,9 +188,9 @@ int launch_peer_merge(cudaStream_t s, int sm_count, const pml_peer *peer, const 
     return cudaGetLastError() == cudaSuccess ? 1 : -1;
 }
 
-size_t peer_slab_bytes(int64_t d) { return PEER_HEADER_BYTES + sizeof(double) * (size_t)(2 * d + 3); }
+size_t peer_slab_bytes(int64_t d) { return PEER_HEADER_BYTES + sizeof(double) * (size_t)(2 * slab_stride(d)); }
 double *peer_raw(const pml_peer *peer) { return reinterpret_cast<double *>(static_cast<char *>(peer->slab) + PEER_HEADER_BYTES); }
-double *peer_result(const pml_peer *peer) { return peer_raw(peer) + (peer->d + 2); }
+double *peer_result(const pml_peer *peer) { return peer_raw(peer) + slab_stride(peer->d); }
 
 }  // namespace pml
 
