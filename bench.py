@@ -225,7 +225,12 @@ def run_ours(args):
                     peer.close()
                 peer = None
             else:
-                collective = "peer_merge_kernel: sums over NVLink peer memory in rank order, fused with getVector"
+                if peer.transport == "multicast":
+                    collective = ("peer_merge_mc_kernel: in-switch sums (multimem.ld_reduce over an NVSwitch multicast "
+                                  "object) fused with getVector, results fanned out by multimem.st")
+                else:
+                    collective = ("peer_merge_kernel: sums over NVLink peer memory in rank order, fused with getVector"
+                                  " (multicast unavailable: %s)" % getattr(peer, "multicast_error", "disabled"))
                 result = torch.as_tensor(peer.result_array(), device=device)
                 out_grad, out_value = result[:d], result[d:d + 1]   # the library's result buffer, no copy
 

@@ -266,6 +266,22 @@ int pml_peer_create(pml_ctx *ctx, int rank, int world, int32_t d, pml_peer **out
 int pml_peer_handle(pml_peer *peer, void *out_handle /* PML_PEER_HANDLE_BYTES */);
 int pml_peer_connect(pml_peer *peer, const void *all_handles /* world * PML_PEER_HANDLE_BYTES, rank order */);
 int pml_peer_destroy(pml_peer *peer);
+/* Optional second transport: an NVSwitch multicast object (NVLS) over the ranks' slabs -- the switch adds
+ * (multimem.ld_reduce) and fans out (multimem.st), so a rank moves 1/N of the vector instead of (N-1)/N each way.
+ * Rank 0 calls _export and hands the returned POSIX file descriptor to the other ranks (SCM_RIGHTS over a Unix
+ * socket; the caller closes its descriptors afterwards); every rank calls _join (rank 0 with fd = -1), the ranks
+ * agree on the host that all joins succeeded, then every rank calls _bind (which blocks until all have joined).
+ * From then on *_allreduce_dev uses the multicast kernel and pml_peer_buffers returns the multicast-bound
+ * buffers.  Any failure (no NVSwitch fabric, no permission) leaves the peer-to-peer transport in place. */
+/* which physical GPU a context is on ("0000:1b:00.0"): ranks that share a GPU cannot form a multicast team */
+int pml_ctx_pci_bus_id(pml_ctx *ctx, char *out, int len /* >= 16 */);
+#define PML_PEER_P2P 0
+#define PML_PEER_MULTICAST 1
+int pml_peer_multicast_export(pml_peer *peer, int *out_fd);
+int pml_peer_multicast_join(pml_peer *peer, int fd);
+int pml_peer_multicast_bind(pml_peer *peer);
+int pml_peer_multicast_release(pml_peer *peer); /* back to the peer-to-peer transport (e.g. another rank failed to bind) */
+int pml_peer_transport(pml_peer *peer, int *out /* PML_PEER_P2P or PML_PEER_MULTICAST */);
 /* The rank's exchange buffers (device memory owned by the peer handle): raw = d+2 doubles the evaluation fills,
  * result = d+1 doubles, [vector(d), value], valid after an *_allreduce_dev call in stream order. */
 int pml_peer_buffers(pml_peer *peer, double **raw_dev, double **result_dev);
@@ -275,6 +291,9 @@ int pml_value_and_gradient_allreduce_dev(pml_dataset *ds, pml_peer *peer, int lo
                                          double *out_value_dev, double *out_grad_dev);
 int pml_hessian_vector_allreduce_dev(pml_dataset *ds, pml_peer *peer, int loss, const double *coef_dev,
                                      uint64_t coef_tag, const double *v_dev, double *out_hv_dev);
+/* The merge + getVector alone, for callers that filled the raw buffer themselves (pml_*_raw_dev with
+ * out_raw_dev = the peer's raw buffer): same as pml_finalize_dev after an all-reduce of the raw sums. */
+int pml_peer_merge_dev(pml_dataset *ds, pml_peer *peer, int loss);
 
 /* ---- evaluation without any allocation ------------------------------------------------------ */
 /* No counterpart in the reference (the JVM allocates freely); this exists for callers of THIS

@@ -31,6 +31,8 @@ SYMBOLS = [
     "pml_batch_hessian_vector", "pml_batch_hessian_vector_dev", "pml_batch_set_offsets", "pml_batch_set_active",
     "pml_peer_create", "pml_peer_handle", "pml_peer_connect", "pml_peer_destroy", "pml_peer_buffers",
     "pml_value_and_gradient_allreduce_dev", "pml_hessian_vector_allreduce_dev",
+    "pml_peer_multicast_export", "pml_peer_multicast_join", "pml_peer_multicast_bind", "pml_peer_multicast_release",
+    "pml_peer_transport", "pml_ctx_pci_bus_id", "pml_peer_merge_dev",
 ]
 
 
@@ -122,6 +124,13 @@ def load():
         "pml_peer_connect": [vp, vp],
         "pml_peer_destroy": [vp],
         "pml_peer_buffers": [vp, pp, pp],
+        "pml_peer_multicast_export": [vp, ctypes.POINTER(ctypes.c_int)],
+        "pml_peer_multicast_join": [vp, ctypes.c_int],
+        "pml_peer_multicast_bind": [vp],
+        "pml_peer_multicast_release": [vp],
+        "pml_peer_transport": [vp, ctypes.POINTER(ctypes.c_int)],
+        "pml_ctx_pci_bus_id": [vp, ctypes.c_char_p, ctypes.c_int],
+        "pml_peer_merge_dev": [vp, vp, ctypes.c_int],
         "pml_value_and_gradient_allreduce_dev": [vp, vp, ctypes.c_int, vp, vp, vp],
         "pml_hessian_vector_allreduce_dev": [vp, vp, ctypes.c_int, vp, u64, vp, vp],
     })
@@ -450,7 +459,7 @@ class Peer:
     `exchange(handle_bytes) -> [handle_bytes of every rank, in rank order]` is the only host-side communication;
     the default uses torch.distributed.all_gather_object on the default process group."""
 
-    def __init__(self, ctx, d, rank=None, world=None, exchange=None):
+    def __init__(self, ctx, d, rank=None, world=None, exchange=None, multicast=None):
         if rank is None or world is None:
             import torch.distributed as dist
             rank, world = dist.get_rank(), dist.get_world_size()
@@ -470,10 +479,83 @@ class Peer:
         if len(blob) != PEER_HANDLE_BYTES * self.world:
             raise IllegalArgumentError("expected %d handles of %d bytes" % (self.world, PEER_HANDLE_BYTES))
         check(load().pml_peer_connect(self._h, blob))
+        self.transport = "p2p"
+        # The multicast transport is opt-in: fp64 multimem requests are 8 bytes each (no vector form), and measured
+        # on B200 the switch reduces them slower than peer loads move 16-byte pairs once d exceeds ~10^5.
+        if multicast is None:
+            multicast = os.environ.get("PML_MULTICAST") == "1"
+        if multicast and self.world > 1:
+            self.multicast_error = self._try_multicast(exchange)
+            if self.multicast_error is None:
+                self.transport = "multicast"
         raw, res = ctypes.c_void_p(), ctypes.c_void_p()
         check(load().pml_peer_buffers(self._h, ctypes.byref(raw), ctypes.byref(res)))
         self.raw_ptr, self.result_ptr = raw.value, res.value
         ctx._adopt(self)
+
+    def _try_multicast(self, exchange):
+        """Binds the ranks' slabs to one NVSwitch multicast object; returns None on success, else why not (every
+        rank returns the same verdict, and the peer-to-peer transport stays in place)."""
+        import socket
+        import tempfile
+        lib = load()
+        bus = ctypes.create_string_buffer(64)
+        check(lib.pml_ctx_pci_bus_id(self.ctx._h, bus, 64))
+        buses = exchange(bus.value)
+        if len(set(buses)) != self.world:
+            return "ranks share a GPU (%s)" % ", ".join(b.decode() for b in buses)
+        fd = ctypes.c_int(-1)
+        ok, why, path, srv = True, None, None, None
+        if self.rank == 0:
+            rc = lib.pml_peer_multicast_export(self._h, ctypes.byref(fd))
+            ok = rc == OK
+            if not ok:
+                why = lib.pml_last_error().decode("utf-8", "replace")
+            else:
+                path = os.path.join(tempfile.gettempdir(), "pml_mc_%d_%x.sock" % (os.getpid(), id(self)))
+                srv = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+                srv.bind(path)
+                srv.listen(self.world)
+                srv.settimeout(60)
+        ok, why, path = exchange((ok, why, path))[0]
+        if not ok:
+            return why
+        mine, err = -1, None
+        try:
+            if self.rank == 0:
+                for _ in range(self.world - 1):
+                    conn, _ = srv.accept()
+                    socket.send_fds(conn, [b"m"], [fd.value])
+                    conn.close()
+            else:
+                c = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+                c.settimeout(60)
+                c.connect(path)
+                _, fds, _, _ = socket.recv_fds(c, 16, 1)
+                c.close()
+                mine = fds[0]
+        except OSError as e:
+            err = "passing the multicast file descriptor failed: %s" % e
+        finally:
+            if srv is not None:
+                srv.close()
+                try:
+                    os.unlink(path)
+                except OSError:
+                    pass
+        if err is None and lib.pml_peer_multicast_join(self._h, mine) != OK:
+            err = lib.pml_last_error().decode("utf-8", "replace")
+        for f in (mine, fd.value):
+            if f >= 0:
+                os.close(f)
+        errs = [e for e in exchange(err) if e is not None]
+        if not errs and lib.pml_peer_multicast_bind(self._h) != OK:
+            err = lib.pml_last_error().decode("utf-8", "replace")
+        errs = errs or [e for e in exchange(err) if e is not None]
+        if errs:
+            lib.pml_peer_multicast_release(self._h)
+            return errs[0]
+        return None
 
     def result_array(self):
         """[vector(d), value] of the last *_allreduce_dev call, as a __cuda_array_interface__ object (no copy)."""
@@ -484,6 +566,10 @@ class Peer:
 
     def hessian_vector(self, ds, loss, coef_dev, v_dev, out_hv_dev=None, tag=0):
         check(load().pml_hessian_vector_allreduce_dev(ds._h, self._h, loss, coef_dev, tag, v_dev, out_hv_dev))
+
+    def merge(self, ds, loss):
+        """Merge + getVector of whatever the ranks left in their raw buffers (raw_ptr)."""
+        check(load().pml_peer_merge_dev(ds._h, self._h, loss))
 
     def close(self):
         if self._h:

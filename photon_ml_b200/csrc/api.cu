@@ -1356,6 +1356,20 @@ int pml_value_and_gradient_allreduce_dev(pml_dataset *ds, pml_peer *peer, int lo
     return PML_OK;
 }
 
+int pml_peer_merge_dev(pml_dataset *ds, pml_peer *peer, int loss)
+{
+    PML_TRY(check_ds(ds));
+    PML_TRY(check_peer(ds, peer));
+    if (!valid_loss(loss)) return fail(PML_EINVAL, "unknown loss");
+    Guard g(ds->ctx);
+    PML_CUDA(cudaSetDevice(ds->ctx->device));
+    const bool hinge = loss == PML_LOSS_SMOOTHED_HINGE;
+    return run(ds->ctx, PML_K_PEER, [&] {
+        return launch_peer_merge(ds->ctx->stream, ds->ctx->sm_count, peer, hinge ? nullptr : ds->factors,
+                                 hinge ? nullptr : ds->shifts);
+    });
+}
+
 int pml_hessian_vector_allreduce_dev(pml_dataset *ds, pml_peer *peer, int loss, const double *coef_dev, uint64_t coef_tag,
                                      const double *v_dev, double *out_hv_dev)
 {

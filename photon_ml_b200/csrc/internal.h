@@ -202,12 +202,18 @@ struct pml_peer {
     bool opened[PML_MAX_PEERS] = {};
     bool connected = false;
     int *h_status = nullptr, *d_status = nullptr;  // mapped host word: 1 = a barrier timed out
+    // NVSwitch multicast transport (optional): the slab again, in memory bound to a multicast object
+    unsigned long long mc_handle = 0, mc_mem = 0;  // CUmemGenericAllocationHandle
+    size_t mc_bytes = 0;
+    bool mc_bound = false;
+    void *uc_va = nullptr, *mc_va = nullptr;       // this rank's copy / all ranks' copies
 };
 
 namespace pml {
 int launch_peer_merge(cudaStream_t s, int sm_count, const pml_peer *peer, const double *factors, const double *shifts);
 double *peer_raw(const pml_peer *peer);
 double *peer_result(const pml_peer *peer);
+size_t peer_slab_bytes(int64_t d, int world);
 }  // namespace pml
 
 struct pml_batch {

@@ -1,22 +1,25 @@
 // peer.cu -- the `merge` step across GPUs (ValueAndGradientAggregator.merge :161-176 as driven by treeAggregate,
 // :243-247) fused with getVector (:199-221), over NVLink peer memory, one process per GPU.
 //
-// Every rank owns a slab [header | raw (d+2, padded) | result (d+1, padded)] allocated with cudaMalloc and opened by all the other
-// ranks through CUDA IPC.  After a rank's evaluation kernels have left its raw sums [vectorSum(d), valueSum,
-// prefactorSum] in its slab, ONE kernel per rank does the whole exchange:
-//   1. barrier: tell every peer "my raw sums are complete", wait until every peer said so;
-//   2. rank r adds up slice r of the vector over all ranks' slabs (peer loads, ranks in a fixed order, so every
-//      element is summed once, by one rank, in one order: the result is bit-identical on all ranks and from run to
-//      run), applies getVector to it (the total prefactorSum is 8 bytes per rank, read by everyone) and stores the
-//      finished slice into EVERY rank's result (peer stores);
-//   3. barrier: "my stores are out", wait for everyone's -- when the kernel ends, the rank's result is complete and
-//      nobody reads its raw sums any more.
-// Per rank that is (N-1)/N of the vector in and out over NVLink and two flag round trips -- no staging copies, no
-// separate finalize launch, nothing on the host between the evaluation and the finished gradient.  The epoch the
+// Every rank owns a slab [header | raw (d+2) | result (d+1) | staging (N rows of 1/N of the vector)] allocated with
+// cudaMalloc and opened by all the other ranks through CUDA IPC.  After a rank's evaluation kernels have left its raw
+// sums [vectorSum(d), valueSum, prefactorSum] in its slab, ONE kernel per rank does the whole exchange, with posted
+// stores only (loads over NVLink wait a round trip each and measured 2-3x slower than the same bytes stored):
+//   1. push slice q of the raw sums into row [rank] of rank q's staging area, for every peer q;
+//   2. barrier: "my pushes are out" to every peer, wait until every peer said so;
+//   3. rank r adds up slice r from its own staging rows (local loads, ranks in a fixed order, so every element is
+//      summed once, by one rank, in one order: the result is bit-identical on all ranks and from run to run),
+//      applies getVector to it and stores the finished slice into EVERY rank's result;
+//   4. barrier: "my stores are out", wait for everyone's -- when the kernel ends, the rank's result is complete and
+//      nobody writes its staging rows before the next exchange.
+// Per rank that is (N-1)/N of the vector out twice over NVLink and two flag round trips -- no separate finalize
+// launch, nothing on the host between the evaluation and the finished gradient.  The epoch the
 // flags count lives in the slab and is advanced by the kernel itself, so the launch takes no per-call argument and
 // can sit in a CUDA graph behind the evaluation kernels.
+#include <cuda.h>  // types and prototypes only: the driver entry points are looked up at run time
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <unistd.h>
 
 #include <cstring>
 #include <string>
@@ -37,6 +40,9 @@ struct PeerHeader {
     unsigned int pad1[32 - PML_MAX_PEERS];
     unsigned int epoch;                  // exchanges completed
     unsigned int arrived;                // CTAs of the running kernel that have finished their stores
+    unsigned int pushed;                 // CTAs of the running kernel that have pushed their share of the raw sums
+    unsigned int pad2[29];
+    double pref[PML_MAX_PEERS];          // pref[q] = rank q's prefactorSum of the running exchange
 };
 static_assert(sizeof(PeerHeader) <= PEER_HEADER_BYTES, "header does not fit");
 
@@ -82,7 +88,6 @@ __device__ __forceinline__ void wait_for(const unsigned int *flag, unsigned int 
             *status = 1;
             break;
         }
-        __nanosleep(100);
     }
 }
 
@@ -93,35 +98,76 @@ __device__ __forceinline__ double *slab_result(char *slab, int64_t d)
 {
     return reinterpret_cast<double *>(slab + PEER_HEADER_BYTES) + slab_stride(d);
 }
+// staging: world rows of ceil(pairs / world) pairs -- row r holds rank r's raw sums of the owner's slice
+__device__ __forceinline__ double2 *slab_staging(char *slab, int64_t d)
+{
+    return reinterpret_cast<double2 *>(reinterpret_cast<double *>(slab + PEER_HEADER_BYTES) + 2 * slab_stride(d));
+}
 
 template <int WORLD>
 __global__ void __launch_bounds__(PEER_THREADS) peer_merge_kernel(const PeerParams p)
 {
     __shared__ int is_last;
-    PeerHeader *mine = reinterpret_cast<PeerHeader *>(p.slab[p.rank]);
+    char *my_slab = p.slab[p.rank];
+    PeerHeader *mine = reinterpret_cast<PeerHeader *>(my_slab);
     const unsigned int epoch = mine->epoch + 1;
     const int64_t d = p.d;
+    // elements [0, d] (slot d is the value) as 16-byte pairs; the last pair may take the prefactor slot d+1 along
+    const int64_t n_pairs = (d + 2) / 2;
+    const int64_t per = (n_pairs + WORLD - 1) / WORLD;
+    const int64_t T = (int64_t)gridDim.x * PEER_THREADS;
+    const int64_t gtid = (int64_t)blockIdx.x * PEER_THREADS + threadIdx.x;
+    const double *raw = slab_raw(my_slab);
+    const double2 *raw2 = reinterpret_cast<const double2 *>(raw);
 
-    // ---- 1. everyone's raw sums are complete ----
+    // ---- 1. push: slice q of this rank's raw sums goes to row [rank] of rank q's staging area ----
+#pragma unroll
+    for (int q = 0; q < WORLD; ++q) {
+        if (q == p.rank) continue;
+        const int64_t lo_q = per * q;
+        const int64_t hi_q = lo_q + per < n_pairs ? lo_q + per : n_pairs;
+        double2 *dst = slab_staging(p.slab[q], d) + (int64_t)p.rank * per - lo_q;
+        int64_t k = lo_q + gtid;
+        for (; k + 3 * T < hi_q; k += 4 * T) {  // four independent copies in flight per thread
+            const double2 a = raw2[k], b = raw2[k + T], c = raw2[k + 2 * T], e = raw2[k + 3 * T];
+            dst[k] = a;
+            dst[k + T] = b;
+            dst[k + 2 * T] = c;
+            dst[k + 3 * T] = e;
+        }
+        for (; k < hi_q; k += T) dst[k] = raw2[k];
+    }
     if (blockIdx.x == 0 && threadIdx.x < WORLD)
+        reinterpret_cast<PeerHeader *>(p.slab[threadIdx.x])->pref[p.rank] = raw[d + 1];
+    __syncthreads();  // the CTA's stores happen-before thread 0's fence, which is cumulative
+    if (threadIdx.x == 0) {
+        __threadfence_system();
+        is_last = atomicAdd(&mine->pushed, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (is_last && threadIdx.x < WORLD) {  // every CTA of this rank has pushed: tell everyone
+        __threadfence_system();
+        if (threadIdx.x == 0) mine->pushed = 0;
         st_release_sys(&reinterpret_cast<PeerHeader *>(p.slab[threadIdx.x])->ready[p.rank], epoch);
+    }
+
+    // ---- 2. wait for everyone's pushes (all CTAs are resident: the grid never exceeds the SM count) ----
     if (threadIdx.x < WORLD) wait_for(&mine->ready[threadIdx.x], epoch, p.status);
     __syncthreads();
 
-    // ---- 2. this rank's slice: sum over ranks, getVector, store to every rank ----
+    // ---- 3. this rank's slice: add the staged rows in rank order, getVector, store to every rank ----
     double P = 0.0;
 #pragma unroll
-    for (int q = 0; q < WORLD; ++q) P += ld_peer(slab_raw(p.slab[q]) + d + 1);
-    // elements [0, d] (slot d is the value) as pairs; a trailing pair may take the prefactor slot d+1 along (unused)
-    const int64_t n_pairs = (d + 2) / 2;
-    const int64_t per = (n_pairs + WORLD - 1) / WORLD;
+    for (int q = 0; q < WORLD; ++q) P += q == p.rank ? raw[d + 1] : ld_peer(&mine->pref[q]);
     const int64_t lo = per * p.rank;
     const int64_t hi = lo + per < n_pairs ? lo + per : n_pairs;
-    for (int64_t k = lo + (int64_t)blockIdx.x * PEER_THREADS + threadIdx.x; k < hi; k += (int64_t)gridDim.x * PEER_THREADS) {
+    const double2 *staged = slab_staging(my_slab, d) - lo;
+    for (int64_t k = lo + gtid; k < hi; k += T) {
         const int64_t i = 2 * k;
         double2 part[WORLD];
 #pragma unroll
-        for (int q = 0; q < WORLD; ++q) part[q] = ld_peer2(slab_raw(p.slab[q]) + i);
+        for (int q = 0; q < WORLD; ++q)
+            part[q] = q == p.rank ? raw2[k] : ld_peer2(reinterpret_cast<const double *>(staged + (int64_t)q * per + k));
         double2 v = make_double2(0.0, 0.0);
 #pragma unroll
         for (int q = 0; q < WORLD; ++q) {
@@ -140,10 +186,12 @@ __global__ void __launch_bounds__(PEER_THREADS) peer_merge_kernel(const PeerPara
         for (int q = 0; q < WORLD; ++q) *reinterpret_cast<double2 *>(slab_result(p.slab[q], d) + i) = v;
     }
 
-    // ---- 3. everyone's stores are out ----
-    __threadfence_system();
+    // ---- 4. everyone's stores are out ----
     __syncthreads();
-    if (threadIdx.x == 0) is_last = atomicAdd(&mine->arrived, 1u) == gridDim.x - 1;
+    if (threadIdx.x == 0) {
+        __threadfence_system();
+        is_last = atomicAdd(&mine->arrived, 1u) == gridDim.x - 1;
+    }
     __syncthreads();
     if (!is_last) return;
     __threadfence_system();
@@ -157,10 +205,119 @@ __global__ void __launch_bounds__(PEER_THREADS) peer_merge_kernel(const PeerPara
     }
 }
 
+
+// ---- the same exchange through an NVSwitch multicast object (NVLS) --------------------------------------------
+// When the ranks' slabs are bound to one multicast object (pml_peer_multicast_*), the switch does the adding and
+// the fan-out: multimem.ld_reduce returns the sum of all ranks' copies of an address, multimem.st writes all
+// copies, multimem.red increments a counter on every rank at once.  Each rank still owns one slice, so every
+// element is reduced once and stored everywhere -- identical bits on all ranks -- but it pulls 1/N of the vector
+// instead of (N-1)/N and pushes each finished element once instead of N times.
+struct McParams {
+    char *uc;  // this rank's slab (ordinary mapping)
+    char *mc;  // the multicast mapping of all ranks' slabs
+    int rank, world;
+    int64_t d;
+    const double *factors, *shifts;
+    int *status;
+};
+
+__device__ __forceinline__ double mc_ld_reduce(const double *p)
+{
+    double v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.f64 %0, [%1];" : "=d"(v) : "l"(p) : "memory");
+    return v;
+}
+
+__device__ __forceinline__ void mc_st(double *p, double v)
+{
+    asm volatile("multimem.st.relaxed.sys.global.f64 [%0], %1;" ::"l"(p), "d"(v) : "memory");
+}
+
+__device__ __forceinline__ void mc_signal(unsigned int *p)
+{
+    asm volatile("multimem.red.release.sys.global.add.u32 [%0], %1;" ::"l"(p), "r"(1u) : "memory");
+}
+
+__global__ void __launch_bounds__(PEER_THREADS) peer_merge_mc_kernel(const McParams p)
+{
+    __shared__ int is_last;
+    PeerHeader *mine = reinterpret_cast<PeerHeader *>(p.uc);
+    PeerHeader *all = reinterpret_cast<PeerHeader *>(p.mc);
+    const unsigned int epoch = mine->epoch + 1;
+    const unsigned int target = epoch * (unsigned int)p.world;  // the counters only ever grow: world per exchange
+    const int64_t d = p.d;
+
+    // ---- 1. everyone's raw sums are complete ----
+    if (blockIdx.x == 0 && threadIdx.x == 0) mc_signal(&all->ready[0]);
+    if (threadIdx.x == 0) wait_for(&mine->ready[0], target, p.status);
+    __syncthreads();
+
+    // ---- 2. this rank's slice: the switch adds, getVector, one store reaches every rank ----
+    const double *raw = slab_raw(p.mc);
+    double *result = slab_result(p.mc, d);
+    const double P = mc_ld_reduce(raw + d + 1);
+    const int64_t per = (d + 1 + p.world - 1) / p.world;  // elements [0, d]; slot d is the value
+    const int64_t lo = per * p.rank;
+    const int64_t hi = lo + per < d + 1 ? lo + per : d + 1;
+    // four independent requests per thread in flight: the switch round trip is what this loop waits for
+    const int64_t T = (int64_t)gridDim.x * PEER_THREADS;
+    for (int64_t base = lo + (int64_t)blockIdx.x * PEER_THREADS + threadIdx.x; base < hi; base += 4 * T) {
+        double v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+            if (base + u * T < hi) v[u] = mc_ld_reduce(raw + base + u * T);
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int64_t i = base + u * T;
+            if (i >= hi) break;
+            double x = v[u];
+            if (i < d) {
+                if (p.shifts) x = __dsub_rn(x, __dmul_rn(p.shifts[i], P));
+                if (p.factors) x = __dmul_rn(x, p.factors[i]);
+            }
+            mc_st(result + i, x);
+        }
+    }
+
+    // ---- 3. everyone's stores are out ----
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence_system();
+        is_last = atomicAdd(&mine->arrived, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (!is_last) return;
+    if (threadIdx.x == 0) {
+        __threadfence_system();
+        mc_signal(&all->stored[0]);
+        wait_for(&mine->stored[0], target, p.status);
+        mine->arrived = 0;
+        mine->epoch = epoch;
+    }
+}
+
 }  // namespace
 
 int launch_peer_merge(cudaStream_t s, int sm_count, const pml_peer *peer, const double *factors, const double *shifts)
 {
+    if (peer->mc_va != nullptr) {
+        McParams m;
+        std::memset(&m, 0, sizeof(m));
+        m.uc = static_cast<char *>(peer->uc_va);
+        m.mc = static_cast<char *>(peer->mc_va);
+        m.rank = peer->rank;
+        m.world = peer->world;
+        m.d = peer->d;
+        m.factors = factors;
+        m.shifts = shifts;
+        m.status = peer->d_status;
+        const int64_t per = (peer->d + 1 + peer->world - 1) / peer->world;
+        int64_t grid = (per + PEER_THREADS - 1) / PEER_THREADS;
+        if (grid > 4 * sm_count) grid = 4 * sm_count;
+        if (grid < 1) grid = 1;
+        peer_merge_mc_kernel<<<(int)grid, PEER_THREADS, 0, s>>>(m);
+        return cudaGetLastError() == cudaSuccess ? 1 : -1;
+    }
     PeerParams p;
     std::memset(&p, 0, sizeof(p));
     for (int q = 0; q < peer->world; ++q) p.slab[q] = static_cast<char *>(peer->peer_slab[q]);
@@ -170,8 +327,8 @@ int launch_peer_merge(cudaStream_t s, int sm_count, const pml_peer *peer, const 
     p.factors = factors;
     p.shifts = shifts;
     p.status = peer->d_status;
-    const int64_t per = ((peer->d + 2) / 2 + peer->world - 1) / peer->world;
-    int64_t grid = (per + PEER_THREADS - 1) / PEER_THREADS;
+    // CTAs wait for the last CTA of every rank: all of them must be resident, one per SM at most
+    int64_t grid = ((peer->d + 2) / 2 + PEER_THREADS - 1) / PEER_THREADS;
     if (grid > sm_count) grid = sm_count;
     if (grid < 1) grid = 1;
     switch (peer->world) {
@@ -188,13 +345,146 @@ int launch_peer_merge(cudaStream_t s, int sm_count, const pml_peer *peer, const 
     return cudaGetLastError() == cudaSuccess ? 1 : -1;
 }
 
-size_t peer_slab_bytes(int64_t d) { return PEER_HEADER_BYTES + sizeof(double) * (size_t)(2 * slab_stride(d)); }
-double *peer_raw(const pml_peer *peer) { return reinterpret_cast<double *>(static_cast<char *>(peer->slab) + PEER_HEADER_BYTES); }
+size_t peer_slab_bytes(int64_t d, int world)
+{
+    const int64_t per = ((d + 2) / 2 + world - 1) / world;
+    return PEER_HEADER_BYTES + sizeof(double) * (size_t)(2 * slab_stride(d) + 2 * per * world);
+}
+double *peer_raw(const pml_peer *peer)
+{
+    char *base = static_cast<char *>(peer->mc_va != nullptr ? peer->uc_va : peer->slab);
+    return reinterpret_cast<double *>(base + PEER_HEADER_BYTES);
+}
 double *peer_result(const pml_peer *peer) { return peer_raw(peer) + slab_stride(peer->d); }
 
 }  // namespace pml
 
 using namespace pml;
+
+// ---- multicast set-up: driver API, looked up at run time (the library links against the runtime only) ----------
+namespace {
+
+struct Driver {
+    decltype(&cuMulticastCreate) MulticastCreate = nullptr;
+    decltype(&cuMulticastAddDevice) MulticastAddDevice = nullptr;
+    decltype(&cuMulticastBindMem) MulticastBindMem = nullptr;
+    decltype(&cuMulticastUnbind) MulticastUnbind = nullptr;
+    decltype(&cuMulticastGetGranularity) MulticastGetGranularity = nullptr;
+    decltype(&cuMemCreate) MemCreate = nullptr;
+    decltype(&cuMemRelease) MemRelease = nullptr;
+    decltype(&cuMemMap) MemMap = nullptr;
+    decltype(&cuMemUnmap) MemUnmap = nullptr;
+    decltype(&cuMemSetAccess) MemSetAccess = nullptr;
+    decltype(&cuMemAddressReserve) MemAddressReserve = nullptr;
+    decltype(&cuMemAddressFree) MemAddressFree = nullptr;
+    decltype(&cuMemExportToShareableHandle) MemExportToShareableHandle = nullptr;
+    decltype(&cuMemImportFromShareableHandle) MemImportFromShareableHandle = nullptr;
+    decltype(&cuDeviceGet) DeviceGet = nullptr;
+    decltype(&cuDeviceGetAttribute) DeviceGetAttribute = nullptr;
+    decltype(&cuGetErrorString) GetErrorString = nullptr;
+    bool ok = false;
+};
+
+template <typename F>
+bool entry(const char *name, F *out)
+{
+    void *fn = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint(name, &fn, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess || !fn) {
+        cudaGetLastError();
+        return false;
+    }
+    *out = reinterpret_cast<F>(fn);
+    return true;
+}
+
+const Driver &driver()
+{
+    static const Driver d = [] {
+        Driver r;
+        r.ok = entry("cuMulticastCreate", &r.MulticastCreate) && entry("cuMulticastAddDevice", &r.MulticastAddDevice) &&
+               entry("cuMulticastBindMem", &r.MulticastBindMem) && entry("cuMulticastUnbind", &r.MulticastUnbind) &&
+               entry("cuMulticastGetGranularity", &r.MulticastGetGranularity) && entry("cuMemCreate", &r.MemCreate) &&
+               entry("cuMemRelease", &r.MemRelease) && entry("cuMemMap", &r.MemMap) && entry("cuMemUnmap", &r.MemUnmap) &&
+               entry("cuMemSetAccess", &r.MemSetAccess) && entry("cuMemAddressReserve", &r.MemAddressReserve) &&
+               entry("cuMemAddressFree", &r.MemAddressFree) &&
+               entry("cuMemExportToShareableHandle", &r.MemExportToShareableHandle) &&
+               entry("cuMemImportFromShareableHandle", &r.MemImportFromShareableHandle) &&
+               entry("cuDeviceGet", &r.DeviceGet) && entry("cuDeviceGetAttribute", &r.DeviceGetAttribute) &&
+               entry("cuGetErrorString", &r.GetErrorString);
+        return r;
+    }();
+    return d;
+}
+
+int drv_fail(const char *what, CUresult e)
+{
+    const char *msg = nullptr;
+    if (driver().GetErrorString) driver().GetErrorString(e, &msg);
+    return fail(PML_ECUDA, std::string(what) + ": " + (msg ? msg : "driver error ") + " (" + std::to_string((int)e) + ")");
+}
+
+#define PML_DRV(call, what)                                   \
+    do {                                                      \
+        CUresult _e = (call);                                 \
+        if (_e != CUDA_SUCCESS) return drv_fail(what, _e);    \
+    } while (0)
+
+CUmulticastObjectProp mc_prop(const pml_peer *peer)
+{
+    CUmulticastObjectProp prop;
+    std::memset(&prop, 0, sizeof(prop));
+    prop.numDevices = (unsigned int)peer->world;
+    prop.size = peer->mc_bytes;
+    prop.handleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
+    return prop;
+}
+
+int mc_prepare(pml_peer *peer)
+{
+    if (!driver().ok) return fail(PML_ECUDA, "this driver has no multicast entry points");
+    PML_CUDA(cudaSetDevice(peer->ctx->device));
+    PML_CUDA(cudaFree(nullptr));  // the primary context is current from here on
+    CUdevice dev;
+    PML_DRV(driver().DeviceGet(&dev, peer->ctx->device), "cuDeviceGet");
+    int supported = 0;
+    PML_DRV(driver().DeviceGetAttribute(&supported, CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED, dev), "cuDeviceGetAttribute");
+    if (!supported) return fail(PML_ECUDA, "the device does not support multicast objects (no NVSwitch fabric?)");
+    if (peer->mc_bytes == 0) {
+        peer->mc_bytes = peer_slab_bytes(peer->d, 1);
+        CUmulticastObjectProp prop = mc_prop(peer);
+        size_t gran = 0;
+        PML_DRV(driver().MulticastGetGranularity(&gran, &prop, CU_MULTICAST_GRANULARITY_RECOMMENDED), "cuMulticastGetGranularity");
+        if (gran == 0) gran = 2u << 20;
+        peer->mc_bytes = (peer->mc_bytes + gran - 1) / gran * gran;
+    }
+    return PML_OK;
+}
+
+void mc_teardown(pml_peer *peer)
+{
+    const Driver &d = driver();
+    if (!d.ok) return;
+    if (peer->mc_va) {
+        d.MemUnmap((CUdeviceptr)peer->mc_va, peer->mc_bytes);
+        d.MemAddressFree((CUdeviceptr)peer->mc_va, peer->mc_bytes);
+        peer->mc_va = nullptr;
+    }
+    if (peer->uc_va) {
+        d.MemUnmap((CUdeviceptr)peer->uc_va, peer->mc_bytes);
+        d.MemAddressFree((CUdeviceptr)peer->uc_va, peer->mc_bytes);
+        peer->uc_va = nullptr;
+    }
+    if (peer->mc_bound && peer->mc_handle) {
+        CUdevice dev;
+        if (d.DeviceGet(&dev, peer->ctx->device) == CUDA_SUCCESS) d.MulticastUnbind(peer->mc_handle, dev, 0, peer->mc_bytes);
+        peer->mc_bound = false;
+    }
+    if (peer->mc_mem) { d.MemRelease(peer->mc_mem); peer->mc_mem = 0; }
+    if (peer->mc_handle) { d.MemRelease(peer->mc_handle); peer->mc_handle = 0; }
+}
+
+}  // namespace
 
 extern "C" {
 
@@ -212,7 +502,7 @@ int pml_peer_create(pml_ctx *ctx, int rank, int world, int32_t d, pml_peer **out
     p->rank = rank;
     p->world = world;
     p->d = d;
-    const size_t bytes = peer_slab_bytes(d);
+    const size_t bytes = peer_slab_bytes(d, world);
     cudaError_t e = cudaMalloc(&p->slab, bytes);
     if (e == cudaSuccess) e = cudaMemset(p->slab, 0, bytes);
     if (e == cudaSuccess) e = cudaHostAlloc(reinterpret_cast<void **>(&p->h_status), sizeof(int), cudaHostAllocMapped);
@@ -263,6 +553,113 @@ int pml_peer_connect(pml_peer *peer, const void *all_handles)
     return PML_OK;
 }
 
+int pml_ctx_pci_bus_id(pml_ctx *ctx, char *out, int len)
+{
+    if (ctx == nullptr || out == nullptr || len < 16) return fail(PML_EINVAL, "bad argument");
+    PML_CUDA(cudaDeviceGetPCIBusId(out, len, ctx->device));
+    return PML_OK;
+}
+
+int pml_peer_multicast_export(pml_peer *peer, int *out_fd)
+{
+    if (peer == nullptr || out_fd == nullptr) return fail(PML_EINVAL, "null argument");
+    *out_fd = -1;
+    if (peer->mc_handle) return fail(PML_ESTATE, "the peer handle already holds a multicast object");
+    PML_TRY(mc_prepare(peer));
+    CUmulticastObjectProp prop = mc_prop(peer);
+    PML_DRV(driver().MulticastCreate(&peer->mc_handle, &prop), "cuMulticastCreate");
+    int fd = -1;
+    CUresult e = driver().MemExportToShareableHandle(&fd, peer->mc_handle, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR, 0);
+    if (e != CUDA_SUCCESS) {
+        driver().MemRelease(peer->mc_handle);
+        peer->mc_handle = 0;
+        return drv_fail("cuMemExportToShareableHandle", e);
+    }
+    *out_fd = fd;
+    return PML_OK;
+}
+
+int pml_peer_multicast_join(pml_peer *peer, int fd)
+{
+    if (peer == nullptr) return fail(PML_EINVAL, "null peer handle");
+    PML_TRY(mc_prepare(peer));
+    if (peer->mc_handle == 0) {
+        if (fd < 0) return fail(PML_EINVAL, "a rank that did not create the multicast object needs its file descriptor");
+        PML_DRV(driver().MemImportFromShareableHandle(&peer->mc_handle, (void *)(uintptr_t)fd,
+                                                      CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR),
+                "cuMemImportFromShareableHandle");
+    }
+    CUdevice dev;
+    PML_DRV(driver().DeviceGet(&dev, peer->ctx->device), "cuDeviceGet");
+    CUresult e = driver().MulticastAddDevice(peer->mc_handle, dev);
+    if (e != CUDA_SUCCESS) {
+        mc_teardown(peer);
+        return drv_fail("cuMulticastAddDevice", e);
+    }
+    return PML_OK;
+}
+
+int pml_peer_multicast_bind(pml_peer *peer)
+{
+    if (peer == nullptr) return fail(PML_EINVAL, "null peer handle");
+    if (peer->mc_handle == 0) return fail(PML_ESTATE, "pml_peer_multicast_join has not been called");
+    if (peer->mc_va) return PML_OK;
+    const Driver &d = driver();
+    PML_CUDA(cudaSetDevice(peer->ctx->device));
+    PML_CUDA(cudaStreamSynchronize(peer->ctx->stream));
+    CUmemAllocationProp ap;
+    std::memset(&ap, 0, sizeof(ap));
+    ap.type = CU_MEM_ALLOCATION_TYPE_PINNED;
+    ap.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+    ap.location.id = peer->ctx->device;
+    ap.requestedHandleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
+    CUmemAccessDesc access;
+    std::memset(&access, 0, sizeof(access));
+    access.location = ap.location;
+    access.flags = CU_MEM_ACCESS_FLAGS_PROT_READWRITE;
+    CUdeviceptr uc = 0, mc = 0;
+    int rc = PML_OK;
+    do {
+        CUresult e;
+        if ((e = d.MemCreate(&peer->mc_mem, peer->mc_bytes, &ap, 0)) != CUDA_SUCCESS) { rc = drv_fail("cuMemCreate", e); break; }
+        // blocks until every rank has added its device
+        if ((e = d.MulticastBindMem(peer->mc_handle, 0, peer->mc_mem, 0, peer->mc_bytes, 0)) != CUDA_SUCCESS) { rc = drv_fail("cuMulticastBindMem", e); break; }
+        peer->mc_bound = true;
+        if ((e = d.MemAddressReserve(&uc, peer->mc_bytes, 0, 0, 0)) != CUDA_SUCCESS) { rc = drv_fail("cuMemAddressReserve", e); break; }
+        if ((e = d.MemMap(uc, peer->mc_bytes, 0, peer->mc_mem, 0)) != CUDA_SUCCESS) { d.MemAddressFree(uc, peer->mc_bytes); rc = drv_fail("cuMemMap", e); break; }
+        peer->uc_va = (void *)uc;
+        if ((e = d.MemSetAccess(uc, peer->mc_bytes, &access, 1)) != CUDA_SUCCESS) { rc = drv_fail("cuMemSetAccess", e); break; }
+        if ((e = d.MemAddressReserve(&mc, peer->mc_bytes, 0, 0, 0)) != CUDA_SUCCESS) { rc = drv_fail("cuMemAddressReserve", e); break; }
+        if ((e = d.MemMap(mc, peer->mc_bytes, 0, peer->mc_handle, 0)) != CUDA_SUCCESS) { d.MemAddressFree(mc, peer->mc_bytes); rc = drv_fail("cuMemMap (multicast)", e); break; }
+        peer->mc_va = (void *)mc;
+        if ((e = d.MemSetAccess(mc, peer->mc_bytes, &access, 1)) != CUDA_SUCCESS) { rc = drv_fail("cuMemSetAccess (multicast)", e); break; }
+    } while (0);
+    if (rc != PML_OK) {
+        const std::string keep = pml_last_error();
+        mc_teardown(peer);
+        return fail(rc, keep);
+    }
+    PML_CUDA(cudaMemset(peer->uc_va, 0, peer->mc_bytes));
+    PML_CUDA(cudaDeviceSynchronize());
+    return PML_OK;
+}
+
+int pml_peer_multicast_release(pml_peer *peer)
+{
+    if (peer == nullptr) return fail(PML_EINVAL, "null peer handle");
+    PML_CUDA(cudaSetDevice(peer->ctx->device));
+    PML_CUDA(cudaStreamSynchronize(peer->ctx->stream));
+    mc_teardown(peer);
+    return PML_OK;
+}
+
+int pml_peer_transport(pml_peer *peer, int *out)
+{
+    if (peer == nullptr || out == nullptr) return fail(PML_EINVAL, "null argument");
+    *out = peer->mc_va != nullptr ? PML_PEER_MULTICAST : PML_PEER_P2P;
+    return PML_OK;
+}
+
 int pml_peer_buffers(pml_peer *peer, double **raw_dev, double **result_dev)
 {
     if (peer == nullptr) return fail(PML_EINVAL, "null peer handle");
@@ -278,6 +675,7 @@ int pml_peer_destroy(pml_peer *peer)
         cudaSetDevice(peer->ctx->device);
         cudaStreamSynchronize(peer->ctx->stream);
     }
+    mc_teardown(peer);
     for (int q = 0; q < PML_MAX_PEERS; ++q)
         if (peer->opened[q] && peer->peer_slab[q]) cudaIpcCloseMemHandle(peer->peer_slab[q]);
     if (peer->slab) cudaFree(peer->slab);

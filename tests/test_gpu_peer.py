@@ -39,7 +39,7 @@ def _problem(loss):
     return n, d, row_ptr, col, val, label, offset, weight, f, s, icpt, w, v
 
 
-def _worker(rank, world, port, loss, out_dir):
+def _worker(rank, world, port, loss, out_dir, multicast):
     import torch
     import torch.distributed as dist
     import photon_ml_b200 as pml
@@ -56,7 +56,7 @@ def _worker(rank, world, port, loss, out_dir):
     ctx = pml.Context(device)
     ds = pml.Dataset.from_csr(ctx, hi - lo, d, rp, c, vv, label[lo:hi], offset[lo:hi], weight[lo:hi])
     ds.set_normalization(f, s, icpt)
-    peer = pml.Peer(ctx, d)
+    peer = pml.Peer(ctx, d, multicast=multicast)
     dev = torch.device("cuda", device)
     with torch.cuda.stream(torch.cuda.ExternalStream(ctx.stream, device=dev)):
         coef = torch.from_numpy(w).to(dev)
@@ -75,7 +75,8 @@ def _worker(rank, world, port, loss, out_dir):
         ctx.synchronize()
         slab = torch.as_tensor(peer.result_array(), device=dev).cpu().numpy().copy()
     np.savez(os.path.join(out_dir, "rank%d.npz" % rank), value=np.array([r[0] for r in results]),
-             grad=np.stack([r[1] for r in results]), hv=np.stack([r[2] for r in results]), slab=slab)
+             grad=np.stack([r[1] for r in results]), hv=np.stack([r[2] for r in results]), slab=slab,
+             transport=peer.transport, why=str(getattr(peer, "multicast_error", None)))
     dist.barrier()
     peer.close()
     ds.close()
@@ -83,16 +84,22 @@ def _worker(rank, world, port, loss, out_dir):
     dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("world", [1, 2, 3])
-def test_peer_merge_matches_the_oracle_on_the_unsplit_data(tmp_path, world):
+@pytest.mark.parametrize("world,multicast", [(1, True), (2, True), (3, True), (2, False)])
+def test_peer_merge_matches_the_oracle_on_the_unsplit_data(tmp_path, world, multicast):
+    """multicast=True: the NVSwitch multicast transport where the box offers it (ranks on distinct GPUs of one
+    NVSwitch fabric), else -- and with multicast=False -- peer-to-peer loads and stores."""
     import torch.multiprocessing as mp
     loss = oracle.LOGISTIC
-    mp.spawn(_worker, args=(world, _free_port(), loss, str(tmp_path)), nprocs=world, join=True)
+    mp.spawn(_worker, args=(world, _free_port(), loss, str(tmp_path), multicast), nprocs=world, join=True)
     n, d, row_ptr, col, val, label, offset, weight, f, s, icpt, w, v = _problem(loss)
     full = oracle.Data(n, d, row_ptr, col, val, label, offset, weight)
     f_ref, g_ref = oracle.value_and_gradient(full, loss, w, f, s, icpt)
     hv_ref = oracle.hessian_vector(full, loss, w, v, f, s, icpt)
     got = [np.load(str(tmp_path / ("rank%d.npz" % r))) for r in range(world)]
+    print("world %d: transport %s (%s)" % (world, got[0]["transport"], got[0]["why"]))
+    assert len({str(g["transport"]) for g in got}) == 1
+    if not multicast:
+        assert str(got[0]["transport"]) == "p2p"
     for r in range(world):
         for rep in range(3):
             assert abs(got[r]["value"][rep] - f_ref) <= TOL * abs(f_ref)
