@@ -48,7 +48,8 @@ extern "C" {
 /* how feature values are stored in HBM */
 #define PML_STORE_F32 0  /* 4 B/value; PML_EINVAL if a value is not exactly representable */
 #define PML_STORE_F64 1  /* 8 B/value, bit-exact for any Double the reference could hold */
-#define PML_STORE_AUTO 2 /* F32 when every value survives the round trip, else F64 */
+#define PML_STORE_AUTO 2 /* ONES when every stored value is 1.0, else F32 when every value survives the round trip, else F64 */
+#define PML_STORE_ONES 3 /* 0 B/value: indicator features, every stored value is exactly 1.0 (PML_EINVAL otherwise) */
 /* OR-ed into `storage`: do not renumber columns by frequency -- for data whose column order already
  * carries locality (the block-diagonal batches of per-entity problems use it internally) */
 #define PML_KEEP_COLUMN_ORDER_FLAG 0x100

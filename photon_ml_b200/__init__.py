@@ -7,4 +7,4 @@ ctypes binding (abi) and a mirror of the reference's objective-function classes 
 """
 from . import abi  # noqa: F401
 from .abi import (Batch, Context, Dataset, IllegalArgumentError, Peer, PhotonError, LOGISTIC, POISSON, SQUARED,  # noqa: F401
-                  SMOOTHED_HINGE, STORE_AUTO, STORE_F32, STORE_F64)
+                  SMOOTHED_HINGE, STORE_AUTO, STORE_F32, STORE_F64, STORE_ONES)

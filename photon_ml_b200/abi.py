@@ -15,7 +15,7 @@ LIB_PATH = os.path.join(HERE, "lib", "libphoton_ml_b200.so")
 OK, EINVAL, ECUDA, ENOMEM, ESTATE = 0, 1, 2, 3, 4
 LOGISTIC, POISSON, SQUARED, SMOOTHED_HINGE = 0, 1, 2, 3
 F32, F64 = 0, 1
-STORE_F32, STORE_F64, STORE_AUTO = 0, 1, 2
+STORE_F32, STORE_F64, STORE_AUTO, STORE_ONES = 0, 1, 2, 3
 
 # every symbol include/photon_ml_b200.h declares (tests check the library exports all of them)
 SYMBOLS = [

@@ -599,7 +599,7 @@ int pml_dataset_create_csr_dev(pml_ctx *ctx, int64_t n, int32_t d, const int64_t
     if (values_dtype != PML_F32 && values_dtype != PML_F64) return fail(PML_EINVAL, "values_dtype must be PML_F32 or PML_F64");
     const int storage_arg = storage;
     storage &= ~PML_KEEP_COLUMN_ORDER_FLAG;
-    if (storage < PML_STORE_F32 || storage > PML_STORE_AUTO) return fail(PML_EINVAL, "unknown storage mode");
+    if (storage < PML_STORE_F32 || storage > PML_STORE_ONES) return fail(PML_EINVAL, "unknown storage mode");
     Guard g(ctx);
     PML_CUDA(cudaSetDevice(ctx->device));
     cudaStream_t s = ctx->stream;
@@ -644,7 +644,14 @@ int pml_dataset_create_csr_dev(pml_ctx *ctx, int64_t n, int32_t d, const int64_t
 
     const int src_bytes = values_dtype == PML_F32 ? 4 : 8;
     int dst_bytes = src_bytes;
-    if (storage == PML_STORE_F64) dst_bytes = 8;
+    bool ones = false;
+    if (storage == PML_STORE_ONES || storage == PML_STORE_AUTO) {
+        PML_TRY(ones_check(s, values_dev, src_bytes, nnz, &ones));
+        if (!ones && storage == PML_STORE_ONES)
+            return fail(PML_EINVAL, "PML_STORE_ONES requested but some stored value is not exactly 1.0");
+    }
+    if (ones) dst_bytes = 0;  // indicator features: the indices say it all
+    else if (storage == PML_STORE_F64) dst_bytes = 8;
     else if (src_bytes == 8) {
         bool exact = true;
         PML_TRY(narrow_check(s, static_cast<const double *>(values_dev), nnz, &exact));
@@ -658,7 +665,7 @@ int pml_dataset_create_csr_dev(pml_ctx *ctx, int64_t n, int32_t d, const int64_t
     // 16 entries of zeroed padding: seg_spmv_kernel's 128-bit loads may read up to 7 entries past nnz
     PML_TRY(dev_alloc(&ds->col, (size_t)nnz + 16, &ds->bytes));
     PML_CUDA(cudaMemsetAsync(ds->col + nnz, 0, sizeof(int32_t) * 16, s));
-    {
+    if (dst_bytes > 0) {
         void *v = nullptr;
         cudaError_t e = cudaMalloc(&v, (size_t)(nnz + 16) * dst_bytes);
         if (e != cudaSuccess) return fail(PML_ENOMEM, std::string("cudaMalloc values: ") + cudaGetErrorString(e));
@@ -668,7 +675,7 @@ int pml_dataset_create_csr_dev(pml_ctx *ctx, int64_t n, int32_t d, const int64_t
     }
     if (nnz > 0) {
         PML_CUDA(cudaMemcpyAsync(ds->col, col_idx_dev, sizeof(int32_t) * (size_t)nnz, cudaMemcpyDeviceToDevice, s));
-        PML_TRY(convert_values(s, values_dev, src_bytes, ds->val, dst_bytes, nnz));
+        if (dst_bytes > 0) PML_TRY(convert_values(s, values_dev, src_bytes, ds->val, dst_bytes, nnz));
     }
     PML_TRY(upload_optional(s, &ds->label, n > 0 ? labels_dev : nullptr, n, true, &ds->bytes));
     if (ds->label == nullptr) PML_TRY(dev_alloc(&ds->label, 1, &ds->bytes));

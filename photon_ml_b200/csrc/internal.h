@@ -130,6 +130,7 @@ constexpr int64_t SUPER_MIN_ROWS_DEFAULT = 12ll << 20; // up to this many rows r
 int build_row_side(cudaStream_t s, int64_t n, int64_t nnz, const uint32_t *row_ptr, int32_t *col, int chunk_entries,
                    RowSide *out);
 int narrow_check(cudaStream_t s, const double *val, int64_t nnz, bool *all_exact);
+int ones_check(cudaStream_t s, const void *val, int value_bytes, int64_t nnz, bool *all_ones);
 int convert_values(cudaStream_t s, const void *src, int src_bytes, void *dst, int dst_bytes, int64_t nnz);
 int check_columns(cudaStream_t s, const int32_t *col, int64_t nnz, int32_t d, int64_t *bad);
 int convert_row_ptr(cudaStream_t s, const int64_t *src, uint32_t *dst, int64_t n_plus_1, int64_t *bad);

@@ -20,6 +20,8 @@
 // lookup per lane and a 32-byte L2 sector (the measured limiter of the first version of these
 // kernels), while shared memory serves 32 lanes in a few cycles.
 #include <cuda_runtime.h>
+
+#include <type_traits>
 #include <stdint.h>
 
 #include "internal.h"
@@ -156,7 +158,7 @@ __global__ void __launch_bounds__(R_THREADS, 5) row_pass_kernel(const RowPassPar
 #pragma unroll 4
                 for (uint32_t k = pb + lane; k < pe; k += 32) {
                     const int32_t c = __ldcs(col + k) & 0x7fffffff;
-                    const double x = widen(__ldcs(val + k));
+                    const double x = load_value(val, k);
                     double w0, w1;
                     gather<TWO>(vec, c, w0, w1);
                     buf[k - pb] = __dmul_rn(x, w0);
@@ -185,8 +187,8 @@ __global__ void __launch_bounds__(R_THREADS, 5) row_pass_kernel(const RowPassPar
                 for (; k + 3 * L < end; k += 4 * L) {
                     const int32_t c0 = __ldcs(col + k) & 0x7fffffff, c1 = __ldcs(col + k + L) & 0x7fffffff;
                     const int32_t c2 = __ldcs(col + k + 2 * L) & 0x7fffffff, c3 = __ldcs(col + k + 3 * L) & 0x7fffffff;
-                    const double x0 = widen(__ldcs(val + k)), x1 = widen(__ldcs(val + k + L));
-                    const double x2 = widen(__ldcs(val + k + 2 * L)), x3 = widen(__ldcs(val + k + 3 * L));
+                    const double x0 = load_value(val, k), x1 = load_value(val, k + L);
+                    const double x2 = load_value(val, k + 2 * L), x3 = load_value(val, k + 3 * L);
                     double w00, w01, w10, w11, w20, w21, w30, w31;
                     gather<TWO>(vec, c0, w00, w01);
                     gather<TWO>(vec, c1, w10, w11);
@@ -197,7 +199,7 @@ __global__ void __launch_bounds__(R_THREADS, 5) row_pass_kernel(const RowPassPar
                 }
                 for (; k < end; k += L) {
                     const int32_t c = __ldcs(col + k) & 0x7fffffff;
-                    const double x = widen(__ldcs(val + k));
+                    const double x = load_value(val, k);
                     double w0, w1;
                     gather<TWO>(vec, c, w0, w1);
                     a = fma(x, w0, a);
@@ -297,6 +299,9 @@ int launch_row_pass(cudaStream_t s, int sm_count, int value_bytes, int lanes_per
     int grid = (int)(want < cap ? want : cap);
     if (grid < 1) grid = 1;
     *grid_out = grid;
+    if (value_bytes == 0)
+        return two ? launch_row_variant<One, true>(s, grid, lanes_per_row, p)
+                   : launch_row_variant<One, false>(s, grid, lanes_per_row, p);
     if (value_bytes == 4)
         return two ? launch_row_variant<float, true>(s, grid, lanes_per_row, p)
                    : launch_row_variant<float, false>(s, grid, lanes_per_row, p);
@@ -372,26 +377,61 @@ __device__ __forceinline__ SegScan<TWO> seg_shfl(const SegScan<TWO> &v, int src)
     return o;
 }
 
-// One table look-up: shared memory for the hot prefix, the read-only global path otherwise.
-// Written as two predicated loads so that a warp mixing hot and cold indices does not diverge.
-template <bool HOT>
-__device__ __forceinline__ double seg_lookup(const double *hot, int n_hot, const double *__restrict__ table, int k)
+// One table look-up.  LOOKUP_GLOBAL: the read-only global path; LOOKUP_MIXED: shared memory for the hot prefix
+// [0, n_hot), global beyond (two predicated loads, so a warp mixing both does not diverge); LOOKUP_SHARED: every
+// index is a shared-memory index (the tiled CSC pass).  The shared table is addressed through its 32-bit
+// shared-window address, computed once per kernel: handed over as a generic pointer, the compiler rebuilt the
+// window base (S2R SR_CgaCtaId, MOV, LEA) and kept a bounds test and a dead global path for every single entry --
+// a dozen instructions per look-up where two do.
+enum { LOOKUP_GLOBAL = 0, LOOKUP_MIXED = 1, LOOKUP_SHARED = 2 };
+
+__device__ __forceinline__ uint32_t shared_window_address(const void *p)
 {
-    if (!HOT) return __ldg(table + k);
-    return (k < n_hot) ? hot[k] : __ldg(table + k);
+    uint32_t a = (uint32_t)__cvta_generic_to_shared(p);
+    asm volatile("" : "+r"(a));  // opaque from here on: keep it in a register instead of rematerialising it
+    return a;
 }
 
-template <bool HOT>
-__device__ __forceinline__ double2 seg_lookup2(const double *hot, int n_hot, const double *__restrict__ table, int k)
+__device__ __forceinline__ double lds_f64(uint32_t addr)
 {
-    if (!HOT || k >= n_hot) return __ldg(reinterpret_cast<const double2 *>(table) + k);
-    return reinterpret_cast<const double2 *>(hot)[k];
+    double v;
+    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(addr));
+    return v;
+}
+
+__device__ __forceinline__ double2 lds_f64x2(uint32_t addr)
+{
+    double2 v;
+    asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "r"(addr));
+    return v;
+}
+
+template <int LOOKUP>
+__device__ __forceinline__ double seg_lookup(uint32_t hot, int n_hot, const double *__restrict__ table, int k)
+{
+    if (LOOKUP == LOOKUP_GLOBAL) return __ldg(table + k);
+    if (LOOKUP == LOOKUP_SHARED) return lds_f64(hot + 8u * (uint32_t)k);
+    return (k < n_hot) ? lds_f64(hot + 8u * (uint32_t)k) : __ldg(table + k);
+}
+
+template <int LOOKUP>
+__device__ __forceinline__ double2 seg_lookup2(uint32_t hot, int n_hot, const double *__restrict__ table, int k)
+{
+    if (LOOKUP == LOOKUP_GLOBAL || (LOOKUP == LOOKUP_MIXED && k >= n_hot))
+        return __ldg(reinterpret_cast<const double2 *>(table) + k);
+    return lds_f64x2(hot + 16u * (uint32_t)k);
 }
 
 template <typename VT, int ITEMS>
 struct SegRegs {
     int32_t idx[ITEMS];
     VT val[ITEMS];
+    __device__ __forceinline__ double value(int i) const { return widen(val[i]); }
+};
+template <int ITEMS>
+struct SegRegs<One, ITEMS> {  // implicit 1.0: only the indices travel
+    int32_t idx[ITEMS];
+    __device__ __forceinline__ double value(int) const { return 1.0; }
 };
 
 template <typename VT, int ITEMS>
@@ -400,7 +440,10 @@ __device__ __forceinline__ void seg_load(SegRegs<VT, ITEMS> &g, const int32_t *_
 {
     if (mine_cnt <= 0) {
 #pragma unroll
-        for (int i = 0; i < ITEMS; ++i) { g.idx[i] = 0; g.val[i] = (VT)0; }
+        for (int i = 0; i < ITEMS; ++i) {
+            g.idx[i] = 0;
+            if constexpr (!std::is_same<VT, One>::value) g.val[i] = (VT)0;
+        }
         return;
     }
     // the arrays are padded by 16 entries past nnz, so a partially filled thread may read ahead
@@ -408,10 +451,10 @@ __device__ __forceinline__ void seg_load(SegRegs<VT, ITEMS> &g, const int32_t *_
     for (int i = 0; i < ITEMS / 4; ++i) {
         const int4 rr = __ldcs(reinterpret_cast<const int4 *>(idx + first) + i);
         g.idx[4 * i] = rr.x; g.idx[4 * i + 1] = rr.y; g.idx[4 * i + 2] = rr.z; g.idx[4 * i + 3] = rr.w;
-        if (sizeof(VT) == 4) {
+        if constexpr (std::is_same<VT, float>::value) {
             const float4 vv = __ldcs(reinterpret_cast<const float4 *>(val + first) + i);
             g.val[4 * i] = vv.x; g.val[4 * i + 1] = vv.y; g.val[4 * i + 2] = vv.z; g.val[4 * i + 3] = vv.w;
-        } else {
+        } else if constexpr (std::is_same<VT, double>::value) {
             const double2 va = __ldcs(reinterpret_cast<const double2 *>(val + first) + 2 * i);
             const double2 vb = __ldcs(reinterpret_cast<const double2 *>(val + first) + 2 * i + 1);
             g.val[4 * i] = va.x; g.val[4 * i + 1] = va.y; g.val[4 * i + 2] = vb.x; g.val[4 * i + 3] = vb.y;
@@ -422,9 +465,9 @@ __device__ __forceinline__ void seg_load(SegRegs<VT, ITEMS> &g, const int32_t *_
 // Reduces one chunk held in `cur`.  FULL = every thread owns ITEMS live entries (all chunks but
 // possibly the last), which keeps the bounds tests out of the persistent loop.
 // A chunk belongs to one warp (32*ITEMS entries): the scan is warp-wide, no barrier, no shared memory.
-template <typename VT, int ITEMS, bool TWO, bool SQUARE, bool HOT, bool FULL>
+template <typename VT, int ITEMS, bool TWO, bool SQUARE, int LOOKUP, bool FULL>
 __device__ __forceinline__ void seg_chunk(const SegParams &p, const SegRegs<VT, ITEMS> &cur, int c, int mine_cnt,
-                                          const double *hot)
+                                          uint32_t hot)
 {
     const int lane = threadIdx.x & 31;
     const double *__restrict__ table = p.table;
@@ -439,14 +482,21 @@ __device__ __forceinline__ void seg_chunk(const SegParams &p, const SegRegs<VT, 
         const int32_t raw = live ? cur.idx[i] : 0;
         mask |= ((unsigned)raw >> 31) << i;
         const int32_t k = raw & 0x7fffffff;
-        double x = live ? widen(cur.val[i]) : 0.0;
+        double x = live ? cur.value(i) : 0.0;
         if (SQUARE) x *= x;
         if (TWO) {
-            const double2 g = seg_lookup2<HOT>(hot, n_hot, table, k);
-            pr[i] = __dmul_rn(g.x, x);
-            pr2[i] = __dmul_rn(g.y, x);
+            const double2 g = seg_lookup2<LOOKUP>(hot, n_hot, table, k);
+            if constexpr (std::is_same<VT, One>::value) {
+                pr[i] = live ? g.x : 0.0;
+                pr2[i] = live ? g.y : 0.0;
+            } else {
+                pr[i] = __dmul_rn(g.x, x);
+                pr2[i] = __dmul_rn(g.y, x);
+            }
         } else {
-            pr[i] = __dmul_rn(seg_lookup<HOT>(hot, n_hot, table, k), x);
+            const double g = seg_lookup<LOOKUP>(hot, n_hot, table, k);
+            if constexpr (std::is_same<VT, One>::value) pr[i] = live ? g : 0.0;
+            else pr[i] = __dmul_rn(g, x);
         }
     }
 
@@ -540,15 +590,34 @@ __device__ __forceinline__ void seg_load_full(SegRegs<VT, ITEMS> &g, const int32
     for (int i = 0; i < ITEMS / 4; ++i) {
         const int4 rr = __ldcs(reinterpret_cast<const int4 *>(idx + first) + i);
         g.idx[4 * i] = rr.x; g.idx[4 * i + 1] = rr.y; g.idx[4 * i + 2] = rr.z; g.idx[4 * i + 3] = rr.w;
-        if (sizeof(VT) == 4) {
+        if constexpr (std::is_same<VT, float>::value) {
             const float4 vv = __ldcs(reinterpret_cast<const float4 *>(val + first) + i);
             g.val[4 * i] = vv.x; g.val[4 * i + 1] = vv.y; g.val[4 * i + 2] = vv.z; g.val[4 * i + 3] = vv.w;
-        } else {
+        } else if constexpr (std::is_same<VT, double>::value) {
             const double2 va = __ldcs(reinterpret_cast<const double2 *>(val + first) + 2 * i);
             const double2 vb = __ldcs(reinterpret_cast<const double2 *>(val + first) + 2 * i + 1);
             g.val[4 * i] = va.x; g.val[4 * i + 1] = va.y; g.val[4 * i + 2] = vb.x; g.val[4 * i + 3] = vb.y;
         }
     }
+}
+
+// Pulls the lines of a chunk two steps ahead into L2 (no registers held): the register prefetch of the next chunk
+// then finds its data a few hundred cycles away instead of a DRAM round trip under load -- the first use of the
+// prefetched registers was the single largest stall of these kernels (ncu source view, long scoreboard).
+constexpr int PF_AHEAD = 4;  // chunks (per warp) between the L2 prefetch and the chunk being reduced
+
+template <typename VT, int ITEMS>
+__device__ __forceinline__ void seg_prefetch_l2(const int32_t *__restrict__ idx, const VT *__restrict__ val, int64_t chunk)
+{
+    constexpr int CHUNK = 32 * ITEMS;
+    constexpr int IDX_LINES = CHUNK * 4 / 128;
+    constexpr int VAL_LINES = std::is_same<VT, One>::value ? 0 : CHUNK * (int)sizeof(VT) / 128;
+    const int lane = threadIdx.x & 31;
+    const char *ptr = nullptr;
+    if (lane < IDX_LINES) ptr = reinterpret_cast<const char *>(idx + chunk * CHUNK) + 128 * lane;
+    else if (lane < IDX_LINES + VAL_LINES)
+        ptr = reinterpret_cast<const char *>(val) + (size_t)chunk * CHUNK * sizeof(VT) + 128 * (lane - IDX_LINES);
+    if (ptr != nullptr) asm volatile("prefetch.global.L2 [%0];" ::"l"(ptr));
 }
 
 // Persistent CTAs; warp w of CTA b takes chunks (b*WARPS + w) + k*(grid*WARPS).  With a table (the CSR stream) one
@@ -567,6 +636,8 @@ __global__ void __launch_bounds__(SW_THREADS, 1024 / SW_THREADS) seg_spmv_warp_k
         for (int i = tid; i < words; i += SW_THREADS) hot[i] = p.table[i];
         __syncthreads();
     }
+    constexpr int LOOKUP = HOT ? LOOKUP_MIXED : LOOKUP_GLOBAL;
+    const uint32_t hot_at = shared_window_address(hot);
     const int n_full = (int)(p.nnz / CHUNK);
     const int stride = gridDim.x * WARPS;
     SegRegs<VT, ITEMS> cur;
@@ -576,14 +647,17 @@ __global__ void __launch_bounds__(SW_THREADS, 1024 / SW_THREADS) seg_spmv_warp_k
         SegRegs<VT, ITEMS> nxt;
         const int cn = c + stride;
         if (cn < n_full) seg_load_full<VT, ITEMS>(nxt, idx, val, (int64_t)cn * CHUNK + lane * ITEMS);
-        seg_chunk<VT, ITEMS, TWO, SQUARE, HOT, true>(p, cur, c, ITEMS, hot);
+        // (not for the cold CSC columns: their gathers of r live in L2 and the extra lines cost them more than
+        // the stream gains -- measured 0.42 -> 0.52 ms)
+        if (HOT && cn + (PF_AHEAD - 1) * stride < n_full) seg_prefetch_l2<VT, ITEMS>(idx, val, cn + (PF_AHEAD - 1) * stride);
+        seg_chunk<VT, ITEMS, TWO, SQUARE, LOOKUP, true>(p, cur, c, ITEMS, hot_at);
         cur = nxt;
     }
     if (n_full < p.n_chunks && (int)(blockIdx.x * WARPS + warp) == n_full % stride) {
         const int64_t base = (int64_t)n_full * CHUNK;
         const int cnt = (int)(p.nnz - base);
         seg_load<VT, ITEMS>(cur, idx, val, base + lane * ITEMS, cnt - lane * ITEMS);
-        seg_chunk<VT, ITEMS, TWO, SQUARE, HOT, false>(p, cur, n_full, cnt - lane * ITEMS, hot);
+        seg_chunk<VT, ITEMS, TWO, SQUARE, LOOKUP, false>(p, cur, n_full, cnt - lane * ITEMS, hot_at);
     }
 }
 
@@ -629,6 +703,7 @@ seg_spmv_tiled_kernel(const SegParams p, const int32_t *__restrict__ tile_first_
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const VT *__restrict__ val = static_cast<const VT *>(p.val);
     const int32_t *__restrict__ idx = p.idx;
+    const uint32_t hot_at = shared_window_address(hot);
     for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
         __syncthreads();  // every warp is done with the previous tile's slice
         const int64_t row0 = (int64_t)t * tile_rows;
@@ -642,7 +717,8 @@ seg_spmv_tiled_kernel(const SegParams p, const int32_t *__restrict__ tile_first_
             SegRegs<VT, ITEMS> nxt;
             const int cn = c + WARPS;
             if (cn < c_end) seg_load_full<VT, ITEMS>(nxt, idx, val, (int64_t)cn * CHUNK + lane * ITEMS);
-            seg_chunk<VT, ITEMS, false, SQUARE, true, true>(p, cur, c, ITEMS, hot);
+            if (cn + (PF_AHEAD - 1) * WARPS < c_end) seg_prefetch_l2<VT, ITEMS>(idx, val, cn + (PF_AHEAD - 1) * WARPS);
+            seg_chunk<VT, ITEMS, false, SQUARE, LOOKUP_SHARED, true>(p, cur, c, ITEMS, hot_at);
             cur = nxt;
         }
     }
@@ -675,7 +751,9 @@ int launch_seg_tiled(cudaStream_t s, int sm_count, int value_bytes, bool square,
             return -1;                                                                                              \
         seg_spmv_tiled_kernel<VT, SQ><<<grid, ST_THREADS, smem, s>>>(p, t.tile_first_chunk, t.n_tiles, t.tile_rows, r, n); \
     } while (0)
-    if (value_bytes == 4) {
+    if (value_bytes == 0) {
+        if (square) PML_TILED(One, true); else PML_TILED(One, false);
+    } else if (value_bytes == 4) {
         if (square) PML_TILED(float, true); else PML_TILED(float, false);
     } else {
         if (square) PML_TILED(double, true); else PML_TILED(double, false);
@@ -738,6 +816,11 @@ int launch_seg_spmv(cudaStream_t s, int sm_count, int value_bytes, bool two, boo
     const size_t smem = (size_t)p.n_hot * (two ? 16 : 8);
 #define PML_SEG_WARP_DISPATCH(T)                                                                       \
     do {                                                                                               \
+        if (value_bytes == 0) {                                                                        \
+            if (two) return launch_seg_warp<One, true, false, T>(s, sm_count, smem, p);                \
+            return square ? launch_seg_warp<One, false, true, T>(s, sm_count, smem, p)                 \
+                          : launch_seg_warp<One, false, false, T>(s, sm_count, smem, p);               \
+        }                                                                                              \
         if (value_bytes == 4) {                                                                        \
             if (two) return launch_seg_warp<float, true, false, T>(s, sm_count, smem, p);              \
             return square ? launch_seg_warp<float, false, true, T>(s, sm_count, smem, p)               \

@@ -50,7 +50,7 @@ __global__ void permute_kernel(int64_t nnz, const uint32_t *__restrict__ perm, c
     for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < nnz; k += (int64_t)gridDim.x * blockDim.x) {
         const uint32_t src = perm[k];
         csc_row[k] = entry_row[src];
-        csc_val[k] = val[src];
+        if (val != nullptr) csc_val[k] = val[src];  // null: implicit ones, nothing stored
     }
 }
 
@@ -148,6 +148,15 @@ __global__ void exact_f32_kernel(const double *__restrict__ val, int64_t nnz, in
         if ((double)(float)v != v && v == v) bad = 1;
     }
     if (__syncthreads_or(bad) && threadIdx.x == 0) *inexact = 1;
+}
+
+template <typename T>
+__global__ void all_ones_kernel(const T *__restrict__ val, int64_t nnz, int *__restrict__ other)
+{
+    int bad = 0;
+    for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < nnz; k += (int64_t)gridDim.x * blockDim.x)
+        if (!(val[k] == (T)1)) bad = 1;  // NaN counts as "not one"
+    if (__syncthreads_or(bad) && threadIdx.x == 0) *other = 1;
 }
 
 template <typename S, typename D>
@@ -249,7 +258,7 @@ __global__ void tile_scatter_kernel(int64_t nnz, const uint32_t *__restrict__ so
         run_flag[i] = start ? 1 : 0;
         run_dest[i] = dest;
         idx[dest] = start ? (row | (int32_t)0x80000000) : row;
-        out_val[dest] = val[src];
+        if (val != nullptr) out_val[dest] = val[src];  // null: implicit ones, nothing stored
     }
 }
 
@@ -274,6 +283,23 @@ int narrow_check(cudaStream_t s, const double *val, int64_t nnz, bool *all_exact
     PML_CUDA(cudaMemcpyAsync(&h, flag.p, sizeof(int), cudaMemcpyDeviceToHost, s));
     PML_CUDA(cudaStreamSynchronize(s));
     *all_exact = (h == 0);
+    return PML_OK;
+}
+
+int ones_check(cudaStream_t s, const void *val, int value_bytes, int64_t nnz, bool *all_ones)
+{
+    DevBuf flag;
+    PML_CUDA(flag.alloc(sizeof(int)));
+    PML_CUDA(cudaMemsetAsync(flag.p, 0, sizeof(int), s));
+    if (nnz > 0) {
+        if (value_bytes == 4) all_ones_kernel<float><<<grid_for(nnz), 256, 0, s>>>((const float *)val, nnz, flag.as<int>());
+        else all_ones_kernel<double><<<grid_for(nnz), 256, 0, s>>>((const double *)val, nnz, flag.as<int>());
+    }
+    PML_CUDA(cudaGetLastError());
+    int h = 0;
+    PML_CUDA(cudaMemcpyAsync(&h, flag.p, sizeof(int), cudaMemcpyDeviceToHost, s));
+    PML_CUDA(cudaStreamSynchronize(s));
+    *all_ones = (h == 0);
     return PML_OK;
 }
 
@@ -461,7 +487,7 @@ int build_transpose(cudaStream_t s, int sm_count, int64_t n, int32_t d, int64_t 
     }
 
     PML_CUDA(cudaMalloc(&out->csc_row, sizeof(int32_t) * (size_t)(nnz + 16)));
-    PML_CUDA(cudaMalloc(&out->csc_val, (size_t)value_bytes * (size_t)(nnz + 16)));
+    if (value_bytes > 0) PML_CUDA(cudaMalloc(&out->csc_val, (size_t)value_bytes * (size_t)(nnz + 16)));
     out->idx_alloc = out->csc_row;
     out->val_alloc = out->csc_val;
     PML_CUDA(cudaMalloc(&out->chunk_col_lo, sizeof(int32_t) * (size_t)(n_chunks + 1)));
@@ -485,9 +511,10 @@ int build_transpose(cudaStream_t s, int sm_count, int64_t n, int32_t d, int64_t 
         PML_CUDA(tmp.alloc(tmp_bytes));
         PML_CUDA(cub::DeviceRadixSort::SortPairs(tmp.p, tmp_bytes, (const int32_t *)col, keys_out.as<int32_t>(),
                                                  perm_in.as<uint32_t>(), perm_out.as<uint32_t>(), nnz, 0, end_bit, s));
-        if (value_bytes == 4)
+        if (value_bytes <= 4)
             permute_kernel<float><<<grid_for(nnz), 256, 0, s>>>(nnz, perm_out.as<uint32_t>(), entry_row.as<int32_t>(),
-                                                               (const float *)val, out->csc_row, (float *)out->csc_val);
+                                                               value_bytes ? (const float *)val : nullptr, out->csc_row,
+                                                               (float *)out->csc_val);
         else
             permute_kernel<double><<<grid_for(nnz), 256, 0, s>>>(nnz, perm_out.as<uint32_t>(), entry_row.as<int32_t>(),
                                                                 (const double *)val, out->csc_row, (double *)out->csc_val);
@@ -497,7 +524,8 @@ int build_transpose(cudaStream_t s, int sm_count, int64_t n, int32_t d, int64_t 
     }
     // tail padding is read by the vector loads of the last (partial) chunk's neighbours: keep it benign
     PML_CUDA(cudaMemsetAsync(out->csc_row + nnz, 0, sizeof(int32_t) * 16, s));
-    PML_CUDA(cudaMemsetAsync((char *)out->csc_val + (size_t)nnz * value_bytes, 0, (size_t)value_bytes * 16, s));
+    if (value_bytes > 0)
+        PML_CUDA(cudaMemsetAsync((char *)out->csc_val + (size_t)nnz * value_bytes, 0, (size_t)value_bytes * 16, s));
     chunk_meta_kernel<<<grid_for((int64_t)n_chunks + 1), 256, 0, s>>>(n_chunks, chunk_entries, m, out->nzcol_ptr,
                                                                      out->chunk_col_lo, head.as<int32_t>());
     PML_CUDA(cudaGetLastError());
@@ -607,16 +635,19 @@ static int build_tiled(cudaStream_t s, int sm_count, int64_t n, int64_t nnz, con
 
     TiledSide &h = out->hot;
     PML_CUDA(cudaMalloc(&out->idx_alloc, sizeof(int32_t) * (size_t)(total + 16)));
-    PML_CUDA(cudaMalloc(&out->val_alloc, (size_t)value_bytes * (size_t)(total + 16)));
+    if (value_bytes > 0) {
+        PML_CUDA(cudaMalloc(&out->val_alloc, (size_t)value_bytes * (size_t)(total + 16)));
+        PML_CUDA(cudaMemsetAsync(out->val_alloc, 0, (size_t)value_bytes * (size_t)(total + 16), s));
+    }
     out->bytes += (int64_t)(sizeof(int32_t) + value_bytes) * (total + 16);
-    PML_CUDA(cudaMemsetAsync(out->val_alloc, 0, (size_t)value_bytes * (size_t)(total + 16), s));
     PML_CUDA(cudaMemsetAsync(out->idx_alloc + hot_len, 0, sizeof(int32_t) * (size_t)(cold_nnz + 16), s));
     fill_pad_kernel<<<grid_for(hot_len), 256, 0, s>>>(hot_len, tile_rows, out->idx_alloc);
     PML_CUDA(run_flag.alloc((size_t)(nnz + 1)));
     PML_CUDA(hot_dest.alloc(sizeof(uint32_t) * (size_t)(nnz + 1)));
-    if (value_bytes == 4)
+    if (value_bytes <= 4)
         tile_scatter_kernel<float><<<grid_for(nnz), 256, 0, s>>>(
-            nnz, keys_sorted.as<uint32_t>(), perm_out.as<uint32_t>(), entry_row.as<int32_t>(), (const float *)val, (int)K,
+            nnz, keys_sorted.as<uint32_t>(), perm_out.as<uint32_t>(), entry_row.as<int32_t>(),
+            value_bytes ? (const float *)val : nullptr, (int)K,
             tile_rows, (int)n_tiles, hs_dev.as<uint32_t>(), po_dev.as<uint32_t>(), (uint32_t)hot_len, out->idx_alloc,
             (float *)out->val_alloc, run_flag.as<unsigned char>(), hot_dest.as<uint32_t>());
     else
@@ -677,7 +708,7 @@ static int build_tiled(cudaStream_t s, int sm_count, int64_t n, int64_t nnz, con
 
     // cold region: CSC over internal columns [K, m), one copy per super block of rows
     out->csc_row = out->idx_alloc + hot_len;
-    out->csc_val = (char *)out->val_alloc + (size_t)hot_len * value_bytes;
+    out->csc_val = value_bytes ? (char *)out->val_alloc + (size_t)hot_len * value_bytes : nullptr;
     out->cold_nnz = cold_nnz;
     out->n_chunks = (int)((cold_nnz + 255) / 256);
     PML_CUDA(cudaMalloc(&out->chunk_col_lo, sizeof(int32_t) * (size_t)(out->n_chunks + 1)));

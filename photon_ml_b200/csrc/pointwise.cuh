@@ -122,4 +122,18 @@ __device__ __forceinline__ void block_sum2(double &a, double &b, double *red)
 __device__ __forceinline__ double widen(float v) { return (double)v; }
 __device__ __forceinline__ double widen(double v) { return v; }
 
+// Feature values as stored: float, double, or nothing at all when every stored value is exactly 1.0 (indicator
+// features: a9a, hashed Criteo-style categories, GLMix id features) -- the kernels then read only the indices.
+struct One {};
+template <typename VT>
+__device__ __forceinline__ double load_value(const VT *__restrict__ val, int64_t k)
+{
+    return widen(__ldcs(val + k));
+}
+template <>
+__device__ __forceinline__ double load_value<One>(const One *__restrict__, int64_t)
+{
+    return 1.0;
+}
+
 }  // namespace pml

@@ -87,7 +87,7 @@ def test_a1a_shaped_logistic_all_row_variants(ctx, variant):
     n, d, row_ptr, col, val, label = _a9a()
     ds, ref = _pair(ctx, n, d, row_ptr, col, val, label)
     info = ds.info()
-    assert info.value_bytes == 4  # all values are exactly 1.0
+    assert info.value_bytes == 0  # all values are exactly 1.0: AUTO stores the indices only
     if os.environ.get("PML_TILE_ROWS"):   # the tiled layout really is in use in the tiled-csc runs
         assert info.tiled_hot_cols >= 16 and info.tiled_tiles == (n + 36) // 37 and info.tiled_tile_rows == 37
     else:
@@ -123,6 +123,40 @@ def test_heart_with_normalization_fp64_values(ctx, loss, kind):
     fh, gh = ds.value_and_gradient(oracle.SMOOTHED_HINGE, w)
     assert abs(fh - fh_ref) <= TOL * abs(fh_ref) and util.rel_err(gh, gh_ref) <= TOL
     ds.close()
+
+
+@pytest.mark.parametrize("variant", [1, 8])
+def test_indicator_values_stored_or_implicit_give_the_same_bits(ctx, variant):
+    """PML_STORE_ONES (what AUTO picks for a9a) against the same data with its 1.0s stored as fp32: multiplying by
+    1.0 is exact, so value, gradient, Hessian-vector product and diagonal must agree to the last bit."""
+    import photon_ml_b200 as pml
+    n, d, row_ptr, col, val, label = _a9a()
+    rng = np.random.default_rng(8)
+    offset, weight = rng.normal(scale=0.2, size=n), rng.uniform(0.5, 2.0, size=n)
+    f, s, icpt = util.normalization_context("STANDARDIZATION", n, d, row_ptr, col, val, d - 1)
+    w, v = rng.normal(scale=0.2, size=d), rng.normal(size=d)
+    got = []
+    for storage in (pml.STORE_ONES, pml.STORE_F32, pml.STORE_F64):
+        ds = pml.Dataset.from_csr(ctx, n, d, row_ptr, col, val, label, offset, weight, storage=storage)
+        assert ds.info().value_bytes == {pml.STORE_ONES: 0, pml.STORE_F32: 4, pml.STORE_F64: 8}[storage]
+        ds.set_margin_variant(variant)
+        ds.set_normalization(f, s, icpt)
+        fv, g = ds.value_and_gradient(oracle.LOGISTIC, w)
+        got.append((fv, g, ds.hessian_vector(oracle.LOGISTIC, w, v), ds.hessian_vector(oracle.LOGISTIC, w, v, tag=5),
+                    ds.hessian_vector(oracle.LOGISTIC, w, v, tag=5), ds.hessian_diagonal(oracle.LOGISTIC, w), ds.scores(w)))
+        ds.close()
+    for other in got[1:]:
+        assert got[0][0] == other[0]
+        for a, b in zip(got[0][1:], other[1:]):
+            assert np.array_equal(a, b)
+    ref = oracle.Data(n, d, row_ptr, col, val, label, offset, weight)
+    f_ref, g_ref = oracle.value_and_gradient(ref, oracle.LOGISTIC, w, f, s, icpt)
+    assert abs(got[0][0] - f_ref) <= TOL * abs(f_ref) and util.rel_err(got[0][1], g_ref) <= TOL
+    # values other than 1.0 are refused in this mode
+    val2 = val.copy()
+    val2[7] = 0.5
+    with pytest.raises(pml.IllegalArgumentError):
+        pml.Dataset.from_csr(ctx, n, d, row_ptr, col, val2, label, storage=pml.STORE_ONES)
 
 
 def test_heart_fp32_storage_is_refused_but_f32_input_is_fine(ctx):

@@ -42,9 +42,11 @@ def main():
     print("generated %d rows, %d entries in %.1f s" % (N, cols.numel(), time.time() - t0), flush=True)
     t0 = time.time()
     ds = pml.Dataset.from_device_pointers(ctx, N, D, row_ptr.data_ptr(), cols.data_ptr(), vals.data_ptr(), pml.abi.F32,
-                                          labels.data_ptr(), storage=pml.STORE_F32)
+                                          labels.data_ptr(),
+                                          storage=pml.STORE_F32 if os.environ.get("STORAGE") == "f32" else pml.STORE_AUTO)
     ctx.synchronize()
     info = ds.info()
+    print("value bytes per entry: %d" % info.value_bytes)
     print("packed in %.2f s; device bytes %.2f GB; tiling: %d hot cols, %d tiles x %d rows; peak torch+lib memory %.1f GB" %
           (time.time() - t0, info.device_bytes / 1e9, info.tiled_hot_cols, info.tiled_tiles, info.tiled_tile_rows,
            (torch.cuda.mem_get_info()[1] - torch.cuda.mem_get_info()[0]) / 1e9), flush=True)
