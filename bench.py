@@ -134,12 +134,15 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
+NCU_FULL_CAPTURES = ("r01_final3_ncu_full.csv", "r01_tiled_ncu_full.csv")   # newest first
+
+
 def ncu_traffic(kernel_substrings):
     """DRAM bytes (read + write) per launch of the named kernels, summed, from the committed `ncu --set full`
     capture of this same workload (profiles/); None when the capture is not there."""
     import csv
-    path = os.path.join(ROOT, "profiles", "r01_tiled_ncu_full.csv")
-    if not os.path.exists(path):
+    path = next((q for q in (os.path.join(ROOT, "profiles", f) for f in NCU_FULL_CAPTURES) if os.path.exists(q)), None)
+    if path is None:
         return None
     rows = list(csv.reader(open(path)))
     hdr, units = rows[0], rows[1]
@@ -397,7 +400,8 @@ def run_ours(args):
             "clocks": clocks,
             "roofline": {"bound": "hbm", "kernel": dominant, "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "frac_of_nominal_8000": achieved / 8000.0, "peak_source": peak_src,
-                         "traffic": traffic, "traffic_source": "profiles/r01_tiled_ncu_full.csv (ncu --set full, dram read+write)",
+                         "traffic": traffic, "traffic_source": "profiles/%s (ncu --set full, dram read+write)" % next(
+                             (f for f in NCU_FULL_CAPTURES if os.path.exists(os.path.join(ROOT, "profiles", f))), "-"),
                          "algorithmic_bytes_per_launch": int(dom_bytes),
                          "avg_launch_ms": dom_ms},
             "kernels": {k: {"ms_per_launch": v[0] / max(1, v[1]), "launches": int(v[1])} for k, v in profile.items()},
