@@ -540,6 +540,19 @@ def random_effect_batch(ctx):
            "ms_per_batch_evaluation_host_buffers": 1e3 * per, "entity_evaluations_per_s_host_buffers": n_ent / per,
            "ms_per_batch_evaluation_device_buffers": 1e3 * per_dev, "entity_evaluations_per_s_device_buffers": n_ent / per_dev,
            "device_ms": {kk: vv[0] for kk, vv in prof.items() if vv[1]}}
+    # every entity's L2-regularised logistic problem solved to TRON's tolerance in lock step, state in device memory
+    # (what RandomEffectCoordinate.updateModel does one entity at a time, RandomEffectCoordinate.scala:108-119)
+    from photon_ml_b200.batched import BatchedTRON, REASONS
+    del t_coef, t_val, t_grad
+    solver = BatchedTRON(batch, pml.LOGISTIC, l2RegWeight=1.0)
+    t0 = time.perf_counter()
+    _, _, info = solver.optimize()
+    wall = time.perf_counter() - t0
+    out["lockstep_tron_logistic_l2_1"] = {
+        "wall_s": wall, "entities_solved_per_s": n_ent / wall, "batched_value_gradient_evals": info["evaluations"],
+        "batched_hessian_vector_evals": info["hessian_vector_evaluations"],
+        "mean_iterations_per_entity": float(info["iterations"].mean()),
+        "reasons": {REASONS[c]: int((info["reasons"] == c).sum()) for c in range(len(REASONS))}}
     batch.close()
     return out
 

@@ -251,6 +251,19 @@ int pml_batch_set_offsets(pml_batch *b, const double *offsets);
  * come back as 0 (a lock-step batched optimizer uses this for entities that have converged).  NULL = all active. */
 int pml_batch_set_active(pml_batch *b, const uint8_t *active /* E, host */);
 
+/* same with the mask already in device memory (a device-resident optimizer updates it without a host round trip);
+ * the bytes are copied.  NULL = all active. */
+int pml_batch_set_active_dev(pml_batch *b, const uint8_t *active_dev /* E, device */);
+/* Vector algebra of a lock-step batched optimizer over the concatenated per-entity vectors -- what Breeze's dot and
+ * axpy do for ONE entity inside TRON.truncatedCG / LBFGS (lib/optimization/TRON.scala:279-339), for all at once:
+ *   segment_dot:   out[e] = sum over entity e's coefficients of x_j * y_j            (fixed order per entity)
+ *   segment_axpby: out_j  = a[e(j)] * x_j + c[e(j)] * y_j   (a / c NULL = 1, y NULL = no second term; out may alias
+ *                  x or y; entities with active_dev[e] == 0 keep out_j, NULL = all)
+ * Device pointers, asynchronous on the context's stream. */
+int pml_batch_segment_dot_dev(pml_batch *b, const double *x_dev, const double *y_dev, double *out_dev /* E */);
+int pml_batch_segment_axpby_dev(pml_batch *b, const double *a_dev /* E */, const double *x_dev, const double *c_dev /* E */,
+                                const double *y_dev, const uint8_t *active_dev /* E */, double *out_dev);
+
 /* ---- the merge step across GPUs over peer memory ------------------------------------------------ */
 /* One process per GPU.  Replaces treeAggregate's merge (ValueAndGradientAggregator.scala:161-176, :243-247;
  * HessianVectorAggregator.scala:136-152) AND getVector (:199-221) by one kernel per rank that adds up the ranks'

@@ -33,6 +33,7 @@ SYMBOLS = [
     "pml_value_and_gradient_allreduce_dev", "pml_hessian_vector_allreduce_dev",
     "pml_peer_multicast_export", "pml_peer_multicast_join", "pml_peer_multicast_bind", "pml_peer_multicast_release",
     "pml_peer_transport", "pml_ctx_pci_bus_id", "pml_peer_merge_dev",
+    "pml_batch_set_active_dev", "pml_batch_segment_dot_dev", "pml_batch_segment_axpby_dev",
 ]
 
 
@@ -131,6 +132,9 @@ def load():
         "pml_peer_transport": [vp, ctypes.POINTER(ctypes.c_int)],
         "pml_ctx_pci_bus_id": [vp, ctypes.c_char_p, ctypes.c_int],
         "pml_peer_merge_dev": [vp, vp, ctypes.c_int],
+        "pml_batch_set_active_dev": [vp, vp],
+        "pml_batch_segment_dot_dev": [vp, vp, vp, vp],
+        "pml_batch_segment_axpby_dev": [vp, vp, vp, vp, vp, vp, vp],
         "pml_value_and_gradient_allreduce_dev": [vp, vp, ctypes.c_int, vp, vp, vp],
         "pml_hessian_vector_allreduce_dev": [vp, vp, ctypes.c_int, vp, u64, vp, vp],
     })
@@ -427,6 +431,18 @@ class Batch:
         if a is not None and a.shape != (self.n_entities,):
             raise IllegalArgumentError("Size mismatch. active size: %d != %d." % (a.size, self.n_entities))
         check(load().pml_batch_set_active(self._h, _ptr(a)))
+
+    def set_active_dev(self, active_dev):
+        """active_dev: device address of E bytes (copied), or None for all active."""
+        check(load().pml_batch_set_active_dev(self._h, active_dev))
+
+    def segment_dot_dev(self, x_dev, y_dev, out_dev):
+        """out[e] = sum_j x_j y_j over entity e's coefficients (device addresses; E doubles out)."""
+        check(load().pml_batch_segment_dot_dev(self._h, x_dev, y_dev, out_dev))
+
+    def segment_axpby_dev(self, a_dev, x_dev, c_dev, y_dev, out_dev, active_dev=None):
+        """out_j = a[e(j)] x_j + c[e(j)] y_j; a / c None = 1, y None = no second term; inactive entities keep out_j."""
+        check(load().pml_batch_segment_axpby_dev(self._h, a_dev, x_dev, c_dev, y_dev, active_dev, out_dev))
 
     def close(self):
         if self._h:

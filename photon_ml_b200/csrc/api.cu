@@ -1186,6 +1186,7 @@ int pml_batch_destroy(pml_batch *b)
     if (b->ent_row_ptr) cudaFree(b->ent_row_ptr);
     if (b->ent_values) cudaFree(b->ent_values);
     if (b->coef_ptr_dev) cudaFree(b->coef_ptr_dev);
+    if (b->ent_of_coef) cudaFree(b->ent_of_coef);
     if (b->active_dev) cudaFree(b->active_dev);
     if (b->ds) pml_dataset_destroy(b->ds);
     delete b;
@@ -1301,6 +1302,49 @@ int pml_batch_set_offsets(pml_batch *b, const double *offsets)
     return pml_dataset_set_offsets(b->ds, offsets);
 }
 
+// device copy of the coefficient offsets (and, on request, the entity of every coefficient), made on first use
+static int batch_index(pml_batch *b, bool need_ent_of)
+{
+    cudaStream_t s = b->ds->ctx->stream;
+    if (b->coef_ptr_dev == nullptr) {
+        PML_CUDA(cudaMalloc(&b->coef_ptr_dev, sizeof(int64_t) * (size_t)(b->n_entities + 1)));
+        PML_CUDA(cudaMemcpyAsync(b->coef_ptr_dev, b->coef_ptr.data(), sizeof(int64_t) * (size_t)(b->n_entities + 1),
+                                 cudaMemcpyHostToDevice, s));
+        PML_CUDA(cudaStreamSynchronize(s));
+    }
+    if (need_ent_of && b->ent_of_coef == nullptr && b->ds->d > 0) {
+        PML_CUDA(cudaMalloc(&b->ent_of_coef, sizeof(int32_t) * (size_t)b->ds->d));
+        PML_TRY(count(b->ds->ctx, launch_entity_of_coef(s, b->n_entities, b->coef_ptr_dev, b->ent_of_coef)));
+    }
+    return PML_OK;
+}
+
+int pml_batch_segment_dot_dev(pml_batch *b, const double *x_dev, const double *y_dev, double *out_dev)
+{
+    if (!b || !b->ds) return fail(PML_EINVAL, "null batch handle");
+    if (b->n_entities > 0 && (!x_dev || !y_dev || !out_dev)) return fail(PML_EINVAL, "null buffer");
+    Guard g(b->ds->ctx);
+    PML_CUDA(cudaSetDevice(b->ds->ctx->device));
+    PML_TRY(batch_index(b, false));
+    return run(b->ds->ctx, PML_K_ENTITY, [&] {
+        return launch_segment_dot(b->ds->ctx->stream, b->n_entities, b->coef_ptr_dev, x_dev, y_dev, out_dev);
+    });
+}
+
+int pml_batch_segment_axpby_dev(pml_batch *b, const double *a_dev, const double *x_dev, const double *c_dev,
+                                const double *y_dev, const uint8_t *active_dev, double *out_dev)
+{
+    if (!b || !b->ds) return fail(PML_EINVAL, "null batch handle");
+    if (b->ds->d > 0 && (!x_dev || !out_dev)) return fail(PML_EINVAL, "null buffer");
+    Guard g(b->ds->ctx);
+    PML_CUDA(cudaSetDevice(b->ds->ctx->device));
+    PML_TRY(batch_index(b, true));
+    return run(b->ds->ctx, PML_K_ENTITY, [&] {
+        return launch_segment_axpby(b->ds->ctx->stream, b->ds->d, b->ent_of_coef, a_dev, x_dev, c_dev, y_dev, active_dev,
+                                    out_dev);
+    });
+}
+
 int pml_batch_set_active(pml_batch *b, const uint8_t *active)
 {
     if (!b || !b->ds) return fail(PML_EINVAL, "null batch handle");
@@ -1317,14 +1361,32 @@ int pml_batch_set_active(pml_batch *b, const uint8_t *active)
         return PML_OK;
     }
     if (b->n_entities == 0) return PML_OK;
-    if (b->coef_ptr_dev == nullptr) {
-        PML_CUDA(cudaMalloc(&b->coef_ptr_dev, sizeof(int64_t) * (size_t)(b->n_entities + 1)));
-        PML_CUDA(cudaMemcpyAsync(b->coef_ptr_dev, b->coef_ptr.data(), sizeof(int64_t) * (size_t)(b->n_entities + 1),
-                                 cudaMemcpyHostToDevice, s));
-    }
+    PML_TRY(batch_index(b, false));
     if (b->active_dev == nullptr) PML_CUDA(cudaMalloc(&b->active_dev, (size_t)b->n_entities));
     PML_CUDA(cudaMemcpyAsync(b->active_dev, active, (size_t)b->n_entities, cudaMemcpyHostToDevice, s));
     PML_CUDA(cudaStreamSynchronize(s));
+    return PML_OK;
+}
+
+int pml_batch_set_active_dev(pml_batch *b, const uint8_t *active_dev)
+{
+    if (!b || !b->ds) return fail(PML_EINVAL, "null batch handle");
+    pml_dataset *ds = b->ds;
+    Guard g(ds->ctx);
+    PML_CUDA(cudaSetDevice(ds->ctx->device));
+    cudaStream_t s = ds->ctx->stream;
+    if (active_dev == nullptr) {
+        if (b->active_dev) {
+            PML_CUDA(cudaStreamSynchronize(s));
+            cudaFree(b->active_dev);
+            b->active_dev = nullptr;
+        }
+        return PML_OK;
+    }
+    if (b->n_entities == 0) return PML_OK;
+    PML_TRY(batch_index(b, false));
+    if (b->active_dev == nullptr) PML_CUDA(cudaMalloc(&b->active_dev, (size_t)b->n_entities));
+    PML_CUDA(cudaMemcpyAsync(b->active_dev, active_dev, (size_t)b->n_entities, cudaMemcpyDeviceToDevice, s));
     return PML_OK;
 }
 

@@ -114,6 +114,11 @@ int launch_globalize_cols(cudaStream_t s, int64_t n_entities, const int64_t *ent
                           const int32_t *ent_dim, const int64_t *row_ptr, int32_t *col, unsigned long long *bad);
 int launch_entity_values(cudaStream_t s, int64_t n_entities, const int64_t *ent_row_ptr, const double *row_loss,
                          double *out);
+int launch_entity_of_coef(cudaStream_t s, int64_t n_entities, const int64_t *coef_ptr, int32_t *ent_of);
+int launch_segment_dot(cudaStream_t s, int64_t n_entities, const int64_t *coef_ptr, const double *x, const double *y,
+                       double *out);
+int launch_segment_axpby(cudaStream_t s, int64_t d, const int32_t *ent_of, const double *a, const double *x,
+                         const double *c, const double *y, const uint8_t *active, double *out);
 int launch_mask_entities(cudaStream_t s, int64_t n_entities, const int64_t *coef_ptr, const uint8_t *active, double *values,
                          double *vec);
 
@@ -223,7 +228,8 @@ struct pml_batch {
     int64_t *ent_row_ptr = nullptr; // device, E+1
     double *ent_values = nullptr;   // device, E
     std::vector<int64_t> coef_ptr;  // host, E+1
-    int64_t *coef_ptr_dev = nullptr; // device, E+1 (allocated by set_active)
+    int64_t *coef_ptr_dev = nullptr; // device, E+1
+    int32_t *ent_of_coef = nullptr;  // device, d_total, lazily: entity of every coefficient (segment_axpby)
     uint8_t *active_dev = nullptr;  // device, E; null = every entity active
 };
 

@@ -1132,6 +1132,98 @@ int launch_entity_values(cudaStream_t s, int64_t n_entities, const int64_t *ent_
     return cudaGetLastError() == cudaSuccess ? 1 : -1;
 }
 
+// ------------------------------------------------------------------------------------------
+// Vector algebra of a lock-step batched optimizer over the concatenated per-entity vectors: per-entity dot
+// products and per-entity scaled sums (what Breeze's dot / axpy do inside TRON.truncatedCG and LBFGS for ONE
+// entity, lib/optimization/TRON.scala:279-339, for all entities at once).  Fixed summation order per entity.
+// ------------------------------------------------------------------------------------------
+__global__ void entity_of_coef_kernel(int64_t n_entities, const int64_t *__restrict__ coef_ptr, int32_t *__restrict__ ent_of)
+{
+    const int lane = threadIdx.x & 31;
+    int64_t e = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (; e < n_entities; e += nw)
+        for (int64_t j = coef_ptr[e] + lane; j < coef_ptr[e + 1]; j += 32) ent_of[j] = (int32_t)e;
+}
+
+int launch_entity_of_coef(cudaStream_t s, int64_t n_entities, const int64_t *coef_ptr, int32_t *ent_of)
+{
+    if (n_entities <= 0) return 0;
+    int64_t grid = (n_entities * 32 + 255) / 256;
+    if (grid > 148 * 16) grid = 148 * 16;
+    entity_of_coef_kernel<<<(int)grid, 256, 0, s>>>(n_entities, coef_ptr, ent_of);
+    return cudaGetLastError() == cudaSuccess ? 1 : -1;
+}
+
+// out[e] = sum over entity e's coefficients of x_j * y_j.  Same shape as entity_values_kernel: a lane per small
+// entity, the whole warp (fixed shuffle tree) for entities of 64 coefficients and more.
+__global__ void segment_dot_kernel(int64_t n_entities, const int64_t *__restrict__ coef_ptr, const double *__restrict__ x,
+                                   const double *__restrict__ y, double *__restrict__ out)
+{
+    const int lane = threadIdx.x & 31;
+    int64_t e0 = (((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5) << 5;
+    const int64_t stride = (((int64_t)gridDim.x * blockDim.x) >> 5) << 5;
+    for (; e0 < n_entities; e0 += stride) {
+        const int64_t e = e0 + lane;
+        int64_t lo = 0, hi = 0;
+        if (e < n_entities) {
+            lo = coef_ptr[e];
+            hi = coef_ptr[e + 1];
+        }
+        const bool big = hi - lo >= 64;
+        if (e < n_entities && !big) {
+            double s = 0.0;
+            for (int64_t j = lo; j < hi; ++j) s = fma(x[j], y[j], s);
+            out[e] = s;
+        }
+        unsigned todo = __ballot_sync(0xffffffffu, big);
+        while (todo) {
+            const int src = __ffs(todo) - 1;
+            todo &= todo - 1;
+            const int64_t blo = __shfl_sync(0xffffffffu, lo, src), bhi = __shfl_sync(0xffffffffu, hi, src);
+            double s = 0.0;
+            for (int64_t j = blo + lane; j < bhi; j += 32) s = fma(x[j], y[j], s);
+            s = warp_sum(s);
+            if (lane == 0) out[e0 + src] = s;
+        }
+    }
+}
+
+int launch_segment_dot(cudaStream_t s, int64_t n_entities, const int64_t *coef_ptr, const double *x, const double *y,
+                       double *out)
+{
+    if (n_entities <= 0) return 0;
+    int64_t grid = (n_entities + 255) / 256;
+    if (grid > 148 * 16) grid = 148 * 16;
+    segment_dot_kernel<<<(int)grid, 256, 0, s>>>(n_entities, coef_ptr, x, y, out);
+    return cudaGetLastError() == cudaSuccess ? 1 : -1;
+}
+
+// out_j = a[e(j)] * x_j + c[e(j)] * y_j   (a or c null = 1; y null = no second term); out may alias x or y.
+// active (may be null): entities with active[e] == 0 keep out_j as it is.
+__global__ void segment_axpby_kernel(int64_t d, const int32_t *__restrict__ ent_of, const double *__restrict__ a,
+                                     const double *x, const double *__restrict__ c, const double *y,
+                                     const uint8_t *__restrict__ active, double *out)
+{
+    for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < d; j += (int64_t)gridDim.x * blockDim.x) {
+        const int32_t e = ent_of[j];
+        if (active != nullptr && !active[e]) continue;
+        double v = a ? __dmul_rn(a[e], x[j]) : x[j];
+        if (y != nullptr) v = __dadd_rn(v, c ? __dmul_rn(c[e], y[j]) : y[j]);
+        out[j] = v;
+    }
+}
+
+int launch_segment_axpby(cudaStream_t s, int64_t d, const int32_t *ent_of, const double *a, const double *x,
+                         const double *c, const double *y, const uint8_t *active, double *out)
+{
+    if (d <= 0) return 0;
+    int64_t grid = (d + 255) / 256;
+    if (grid > 148 * 16) grid = 148 * 16;
+    segment_axpby_kernel<<<(int)grid, 256, 0, s>>>(d, ent_of, a, x, c, y, active, out);
+    return cudaGetLastError() == cudaSuccess ? 1 : -1;
+}
+
 // offsets'_i = base_i + score_{map(i)}: DataSet.addScoresToOffsets (api/data/FixedEffectDataSet.scala:45-54,
 // api/data/LocalDataSet.scala:82-89) without the RDD join -- `row_map` carries the row correspondence
 // between two coordinates' row orders (e.g. entity-grouped rows -> fixed-effect rows); null = identity.
