@@ -183,6 +183,11 @@ int pml_dataset_set_offsets_dev(pml_dataset *ds, const double *offsets_dev);
 int pml_offsets_from_scores_dev(pml_ctx *ctx, int64_t n, const double *base_offsets_dev,
                                 const double *scores_dev, const int64_t *row_map_dev,
                                 double *out_offsets_dev);
+/* Training-loss evaluator on given scores: *out_value_dev = sum_i weights[i] * l(scores[i] + offsets[i], labels[i])
+ * (Evaluator.evaluate over (score + offset, label, weight): lib/evaluation/Evaluator.scala:35-45,
+ * api/evaluation/LogisticLossEvaluator.scala:39-46 and its Poisson / squared / smoothed-hinge siblings), for scores
+ * that are already on the device (the sum of the coordinates' pml_scores_dev).  Asynchronous on the stream. */
+int pml_loss_from_scores_dev(pml_dataset *ds, int loss, const double *scores_dev, double *out_value_dev);
 
 /* number of kernel launches this context has issued (bench.py's gpu_launches) */
 int pml_ctx_launch_count(pml_ctx *ctx, int64_t *out);

@@ -33,7 +33,7 @@ SYMBOLS = [
     "pml_value_and_gradient_allreduce_dev", "pml_hessian_vector_allreduce_dev",
     "pml_peer_multicast_export", "pml_peer_multicast_join", "pml_peer_multicast_bind", "pml_peer_multicast_release",
     "pml_peer_transport", "pml_ctx_pci_bus_id", "pml_peer_merge_dev",
-    "pml_batch_set_active_dev", "pml_batch_segment_dot_dev", "pml_batch_segment_axpby_dev",
+    "pml_batch_set_active_dev", "pml_batch_segment_dot_dev", "pml_batch_segment_axpby_dev", "pml_loss_from_scores_dev",
 ]
 
 
@@ -132,6 +132,7 @@ def load():
         "pml_peer_transport": [vp, ctypes.POINTER(ctypes.c_int)],
         "pml_ctx_pci_bus_id": [vp, ctypes.c_char_p, ctypes.c_int],
         "pml_peer_merge_dev": [vp, vp, ctypes.c_int],
+        "pml_loss_from_scores_dev": [vp, ctypes.c_int, vp, vp],
         "pml_batch_set_active_dev": [vp, vp],
         "pml_batch_segment_dot_dev": [vp, vp, vp, vp],
         "pml_batch_segment_axpby_dev": [vp, vp, vp, vp, vp, vp, vp],
@@ -351,6 +352,10 @@ class Dataset:
 
     def hessian_vector_dev(self, loss, coef_dev, v_dev, out_hv_dev, tag=0):
         check(load().pml_hessian_vector_dev(self._h, loss, coef_dev, int(tag), v_dev, out_hv_dev))
+
+    def loss_from_scores_dev(self, loss, scores_dev, out_value_dev):
+        """sum_i wt_i * l(scores_i + offset_i, y_i) for scores already on the device (the training-loss evaluator)."""
+        check(load().pml_loss_from_scores_dev(self._h, loss, scores_dev, out_value_dev))
 
     def close(self):
         if self._h and not getattr(self, "_borrowed", False):

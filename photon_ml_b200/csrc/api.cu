@@ -1048,6 +1048,33 @@ int pml_scores_dev(pml_dataset *ds, const double *coef_dev, double *out_scores_d
     return run_rows(ds, rp, false);
 }
 
+int pml_loss_from_scores_dev(pml_dataset *ds, int loss, const double *scores_dev, double *out_value_dev)
+{
+    PML_TRY(check_ds(ds));
+    if (!valid_loss(loss)) return fail(PML_EINVAL, "unknown loss");
+    if ((!scores_dev && ds->n > 0) || !out_value_dev) return fail(PML_EINVAL, "null buffer");
+    Guard g(ds->ctx);
+    PML_CUDA(cudaSetDevice(ds->ctx->device));
+    cudaStream_t s = ds->ctx->stream;
+    // the scalar half of `add` on given margins: z_i = score_i + offset_i, sum_i wt_i * l(z_i, y_i)
+    RowPassParams rp;
+    std::memset(&rp, 0, sizeof(rp));
+    rp.n = ds->n;
+    rp.label = ds->label;
+    rp.offset = ds->offset;
+    rp.weight = ds->weight;
+    rp.r = ds->r;
+    rp.partials = ds->partials;
+    rp.mode = MODE_VG;
+    rp.loss = loss;
+    PML_TRY(run(ds->ctx, PML_K_EPILOGUE, [&] { return launch_row_epilogue(s, ds->ctx->sm_count, rp, scores_dev, nullptr, &ds->row_grid); }));
+    PML_TRY(run(ds->ctx, PML_K_FIXUP, [&] {
+        return launch_fixup(s, nullptr, 0, 0, nullptr, ds->raw, nullptr, nullptr, 0, ds->partials, ds->row_grid, true, true);
+    }));
+    PML_CUDA(cudaMemcpyAsync(out_value_dev, ds->raw, sizeof(double), cudaMemcpyDeviceToDevice, s));
+    return PML_OK;
+}
+
 int pml_dataset_set_offsets_dev(pml_dataset *ds, const double *offsets_dev)
 {
     PML_TRY(check_ds(ds));

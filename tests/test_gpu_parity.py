@@ -452,3 +452,32 @@ def test_two_contexts_from_two_threads():
     for t in threads:
         t.join()
     assert not errors, errors
+
+
+@pytest.mark.parametrize("loss", LOSSES + [oracle.SMOOTHED_HINGE])
+def test_training_loss_evaluator_on_device_scores(ctx, loss):
+    """pml_loss_from_scores_dev: sum wt * l(score + offset, y) for scores that are already on the device equals the
+    objective value at the coefficients the scores came from (Evaluator.evaluate, lib/evaluation/Evaluator.scala:35-45)."""
+    import torch
+    rng = np.random.default_rng(60 + loss)
+    n, d = 2500, 300
+    row_ptr, col, val = util.random_csr(rng, n, d, 7, skew=1.1, empty_rows=0.05)
+    label = util.labels_for(rng, loss, n)
+    offset, weight = rng.normal(scale=0.3, size=n), rng.uniform(0.5, 2.0, size=n)
+    ds, ref = _pair(ctx, n, d, row_ptr, col, val, label, offset, weight)
+    w = rng.normal(scale=0.2, size=d)
+    f_ref, _ = oracle.value_and_gradient(ref, loss, w)
+    dev = torch.device("cuda", 0)
+    with torch.cuda.stream(torch.cuda.ExternalStream(ctx.stream, device=dev)):
+        t_w = torch.from_numpy(w).to(dev)
+        t_scores = torch.empty(n, dtype=torch.float64, device=dev)
+        t_value = torch.zeros(1, dtype=torch.float64, device=dev)
+        ds.scores_dev(t_w.data_ptr(), t_scores.data_ptr())
+        ds.loss_from_scores_dev(loss, t_scores.data_ptr(), t_value.data_ptr())
+        ctx.synchronize()
+        assert abs(float(t_value.cpu()) - f_ref) <= TOL * abs(f_ref)
+        # and the evaluation that follows is not disturbed by the evaluator's use of the scratch
+        f, g = ds.value_and_gradient(loss, w)
+        f_ref, g_ref = oracle.value_and_gradient(ref, loss, w)
+        assert abs(f - f_ref) <= TOL * abs(f_ref) and util.rel_err(g, g_ref) <= TOL
+    ds.close()
