@@ -13,6 +13,21 @@ object NativeGLM {                       // 1:1 with include/photon_ml_b200.h
   @native def hessianVector(ds: Long, loss: Int, coef: Array[Double], tag: Long, v: Array[Double], out: Array[Double]): Unit
   @native def hessianDiagonal(ds: Long, loss: Int, coef: Array[Double], out: Array[Double]): Unit
   @native def datasetDestroy(ds: Long): Unit
+  // random-effect coordinates: all entities of a partition in one call (pml_batch_*)
+  @native def batchCreate(ctx: Long, entRowPtr: Array[Long], entDim: Array[Int], rowPtr: Array[Long], colLocal: Array[Int],
+                          value: Array[Double], labels: Array[Double], offsets: Array[Double], weights: Array[Double]): Long
+  @native def batchValueAndGradient(batch: Long, loss: Int, coefs: Array[Double], outValues: Array[Double], outGrads: Array[Double]): Unit
+  @native def batchHessianVector(batch: Long, loss: Int, coefs: Array[Double], tag: Long, vs: Array[Double], outHvs: Array[Double]): Unit
+  @native def batchSetOffsets(batch: Long, offsets: Array[Double]): Unit
+  @native def batchSetActive(batch: Long, active: Array[Byte]): Unit
+  @native def batchDestroy(batch: Long): Unit
+  // several executors, one GPU each: the merge of treeAggregate over NVLink peer memory (pml_peer_*)
+  @native def peerCreate(ctx: Long, rank: Int, world: Int, d: Int): Long
+  @native def peerHandle(peer: Long): Array[Byte]                       // 64 bytes, collected by the driver ...
+  @native def peerConnect(peer: Long, allHandles: Array[Byte]): Unit    // ... and sent back in rank order
+  @native def valueAndGradientAllReduce(ds: Long, peer: Long, loss: Int, coef: Array[Double], outGrad: Array[Double]): Double
+  @native def hessianVectorAllReduce(ds: Long, peer: Long, loss: Int, coef: Array[Double], tag: Long, v: Array[Double], out: Array[Double]): Unit
+  @native def peerDestroy(peer: Long): Unit
 }
 
 /** Drop-in for DistributedGLMLossFunction (api/function/glm/DistributedGLMLossFunction.scala:49-137):
