@@ -4,6 +4,8 @@
   BasicStatisticalSummary  lib/stat/BasicStatisticalSummary.scala:60-117 (MLlib colStats: zeros included,
                            unbiased variance) computed sparsely from the CSR arrays
   normalization_context    lib/normalization/NormalizationContext.scala:124-162 (the factory)
+  IndexMapProjection       api/projector/IndexMapProjectorRDD.scala:166-206 + IndexMapProjector.scala:45-91: per-entity
+                           projection of the shard's feature space onto the features the entity's rows use
 (paths under photon-client / photon-lib src/main/scala/com/linkedin/photon/ml).  Host-side, numpy; they run once
 per data set, before packing.
 """
@@ -98,3 +100,46 @@ def normalization_context(normalization_type, summary, intercept_id):
             factors[intercept_id] = 1.0
         return NormalizationContext(factors, shifts, intercept_id)
     raise ValueError("NormalizationType %s not recognized." % normalization_type)
+
+
+class IndexMapProjection:
+    """Per-entity index-map projectors for a random-effect data set whose rows are grouped by entity: entity e's
+    projected space is the set of original feature indices active in its rows (IndexMapProjectorRDD.
+    buildIndexMapProjector: activeIndices ... zipWithIndex), here numbered in ascending original index so the result
+    is deterministic (the reference numbers them in Set iteration order; the model in the original space is the same).
+
+      ent_dim[e]                        projected dimension of entity e
+      coef_ptr[e] .. coef_ptr[e + 1]    its slice of the concatenated projected coefficient vector (pml_batch layout)
+      col_local[k]                      projected index of stored entry k (what pml_batch_create_csr takes)
+      original_index[j]                 original feature index of concatenated projected coefficient j
+    """
+
+    def __init__(self, ent_row_ptr, row_ptr, col, original_dimension):
+        ent_row_ptr = np.asarray(ent_row_ptr, dtype=np.int64)
+        row_ptr = np.asarray(row_ptr, dtype=np.int64)
+        col = np.asarray(col, dtype=np.int64)
+        n_entities = len(ent_row_ptr) - 1
+        self.original_dimension = int(original_dimension)
+        if col.size and (col.min() < 0 or col.max() >= self.original_dimension):
+            raise ValueError("feature index outside [0, %d)" % self.original_dimension)
+        entries_per_entity = row_ptr[ent_row_ptr[1:]] - row_ptr[ent_row_ptr[:-1]]
+        ent_of_entry = np.repeat(np.arange(n_entities, dtype=np.int64), entries_per_entity)
+        keys, inverse = np.unique(ent_of_entry * self.original_dimension + col, return_inverse=True)
+        ent_of_key = keys // self.original_dimension
+        self.original_index = (keys % self.original_dimension).astype(np.int64)
+        self.ent_dim = np.bincount(ent_of_key, minlength=n_entities).astype(np.int32)
+        self.coef_ptr = np.concatenate([[0], np.cumsum(self.ent_dim)]).astype(np.int64)
+        self.col_local = (inverse - self.coef_ptr[ent_of_entry]).astype(np.int32)
+
+    def project_coefficients(self, coefficients_original, e):
+        """Projector.projectCoefficients for entity e: original space -> its projected space."""
+        a, b = int(self.coef_ptr[e]), int(self.coef_ptr[e + 1])
+        return np.asarray(coefficients_original, dtype=np.float64)[self.original_index[a:b]]
+
+    def to_original_space(self, coefficients_projected_all, e):
+        """IndexMapProjector.projectCoefficients back (projectedToOriginalSpaceMap): entity e's model as a dense vector
+        of the original dimension, from the concatenated projected coefficients of all entities."""
+        a, b = int(self.coef_ptr[e]), int(self.coef_ptr[e + 1])
+        out = np.zeros(self.original_dimension)
+        out[self.original_index[a:b]] = np.asarray(coefficients_projected_all, dtype=np.float64)[a:b]
+        return out

@@ -44,3 +44,35 @@ def test_summary_counts_implicit_zeros():
     s = io.BasicStatisticalSummary(3, 2, row_ptr, col, val)
     assert s.mean[0] == 2.0 and s.min[0] == 0.0 and s.max[0] == 4.0 and abs(s.variance[0] - 4.0) < 1e-15
     assert s.mean[1] == 0.0 and s.max[1] == 0.0 and s.min[1] == 0.0 and s.variance[1] == 0.0
+
+
+def test_index_map_projection_per_entity():
+    from photon_ml_b200.io import IndexMapProjection
+    rng = np.random.default_rng(9)
+    n_ent, d = 40, 500
+    rows = rng.integers(0, 6, size=n_ent)          # some entities have no rows at all
+    ent_row_ptr = np.concatenate([[0], np.cumsum(rows)]).astype(np.int64)
+    n = int(ent_row_ptr[-1])
+    lens = rng.integers(0, 9, size=n)
+    row_ptr = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
+    col = rng.integers(0, d, size=int(row_ptr[-1])).astype(np.int32)
+    proj = IndexMapProjection(ent_row_ptr, row_ptr, col, d)
+    assert proj.coef_ptr[-1] == len(proj.original_index) and proj.col_local.shape == col.shape
+    for e in range(n_ent):
+        a, b = int(row_ptr[ent_row_ptr[e]]), int(row_ptr[ent_row_ptr[e + 1]])
+        active = np.unique(col[a:b])
+        lo, hi = int(proj.coef_ptr[e]), int(proj.coef_ptr[e + 1])
+        assert proj.ent_dim[e] == len(active) == hi - lo
+        assert np.array_equal(proj.original_index[lo:hi], active)                 # one-to-one, ascending
+        assert np.array_equal(proj.original_index[lo + proj.col_local[a:b]], col[a:b])   # every entry maps back
+        assert (proj.col_local[a:b] >= 0).all() and (proj.col_local[a:b] < max(1, hi - lo)).all()
+    w = rng.normal(size=d)
+    e = int(np.argmax(proj.ent_dim))
+    local = proj.project_coefficients(w, e)
+    concat = np.zeros(int(proj.coef_ptr[-1]))
+    concat[int(proj.coef_ptr[e]):int(proj.coef_ptr[e + 1])] = local
+    back = proj.to_original_space(concat, e)
+    active = proj.original_index[int(proj.coef_ptr[e]):int(proj.coef_ptr[e + 1])]
+    assert np.array_equal(back[active], w[active]) and np.count_nonzero(back) <= len(active)
+    with pytest.raises(ValueError):
+        IndexMapProjection(ent_row_ptr, row_ptr, col, int(col.max()))
