@@ -26,9 +26,9 @@ def _free_port():
     return port
 
 
-def _problem(loss):
+def _problem(loss, d=257):
     rng = np.random.default_rng(23)
-    n, d = 3000, 257
+    n = 3000
     row_ptr, col, val = util.random_csr(rng, n, d, 9, skew=1.1, empty_rows=0.03)
     label = util.labels_for(rng, loss, n)
     offset = rng.normal(scale=0.2, size=n)
@@ -39,7 +39,15 @@ def _problem(loss):
     return n, d, row_ptr, col, val, label, offset, weight, f, s, icpt, w, v
 
 
-def _worker(rank, world, port, loss, out_dir, multicast):
+def _shards(row_ptr, world, empty_last):
+    """Row ranges per rank; with empty_last the last rank gets no rows at all (a straggler partition)."""
+    from photon_ml_b200 import parallel
+    if not empty_last or world == 1:
+        return parallel.shard_rows_by_nnz(row_ptr, world)
+    return parallel.shard_rows_by_nnz(row_ptr, world - 1) + [(len(row_ptr) - 1, len(row_ptr) - 1)]
+
+
+def _worker(rank, world, port, loss, out_dir, multicast, d=257, empty_last=False):
     import torch
     import torch.distributed as dist
     import photon_ml_b200 as pml
@@ -50,8 +58,8 @@ def _worker(rank, world, port, loss, out_dir, multicast):
     dist.init_process_group("gloo", rank=rank, world_size=world)
     device = rank % torch.cuda.device_count()
     torch.cuda.set_device(device)
-    n, d, row_ptr, col, val, label, offset, weight, f, s, icpt, w, v = _problem(loss)
-    lo, hi = parallel.shard_rows_by_nnz(row_ptr, world)[rank]
+    n, d, row_ptr, col, val, label, offset, weight, f, s, icpt, w, v = _problem(loss, d)
+    lo, hi = _shards(row_ptr, world, empty_last)[rank]
     rp, c, vv = parallel.slice_csr(row_ptr, col, val, lo, hi)
     ctx = pml.Context(device)
     ds = pml.Dataset.from_csr(ctx, hi - lo, d, rp, c, vv, label[lo:hi], offset[lo:hi], weight[lo:hi])
@@ -111,6 +119,23 @@ def test_peer_merge_matches_the_oracle_on_the_unsplit_data(tmp_path, world, mult
         assert np.array_equal(got[r]["value"], got[0]["value"])
         # ... and repeating the evaluation reproduces them
         assert np.array_equal(got[r]["grad"][0], got[r]["grad"][2])
+
+
+@pytest.mark.parametrize("d", [2, 5])
+def test_peer_merge_tiny_dimension_and_an_empty_shard(tmp_path, d):
+    """d + 2 raw sums split over 3 ranks leaves ranks with one pair or none; the last rank holds no rows."""
+    import torch.multiprocessing as mp
+    loss, world = oracle.POISSON, 3
+    mp.spawn(_worker, args=(world, _free_port(), loss, str(tmp_path), False, d, True), nprocs=world, join=True)
+    n, d, row_ptr, col, val, label, offset, weight, f, s, icpt, w, v = _problem(loss, d)
+    full = oracle.Data(n, d, row_ptr, col, val, label, offset, weight)
+    f_ref, g_ref = oracle.value_and_gradient(full, loss, w, f, s, icpt)
+    hv_ref = oracle.hessian_vector(full, loss, w, v, f, s, icpt)
+    for r in range(world):
+        got = np.load(str(tmp_path / ("rank%d.npz" % r)))
+        assert abs(got["value"][0] - f_ref) <= TOL * abs(f_ref)
+        assert util.rel_err(got["grad"][0], g_ref) <= TOL and util.rel_err(got["hv"][2], hv_ref) <= TOL
+        assert util.rel_err(got["slab"][:d], g_ref) <= TOL
 
 
 def test_peer_rejects_mismatched_dimension():
