@@ -60,7 +60,7 @@ class BatchedTRON:
         self.evaluations += 1
         if self.l2 != 0.0:
             f = f + self._dot(w, w) * (self.l2 / 2)
-            g.add_(w, alpha=self.l2)
+            g.add_(w * self.l2)      # product rounded, then the sum: as the host-side L2 mix-in does
         return f, g
 
     def _hessian_vector(self, w, v):
@@ -68,7 +68,7 @@ class BatchedTRON:
         self.batch.hessian_vector_dev(self.loss, w.data_ptr(), v.data_ptr(), hv.data_ptr(), tag=self._tag)
         self.hessian_vector_evaluations += 1
         if self.l2 != 0.0:
-            hv.add_(v, alpha=self.l2)
+            hv.add_(v * self.l2)
         return hv
 
     # ---- TRON.truncatedCG for the entities in `mask` -------------------------------------------------------------
