@@ -256,6 +256,15 @@ int pml_batch_set_offsets(pml_batch *b, const double *offsets);
  * come back as 0 (a lock-step batched optimizer uses this for entities that have converged).  NULL = all active. */
 int pml_batch_set_active(pml_batch *b, const uint8_t *active /* E, host */);
 
+/* Per-entity NormalizationContext (lib/normalization/NormalizationContext.scala:39-47; the random-effect problems
+ * train in the transformed space of their projected features exactly as the fixed effect does:
+ * ValueAndGradientAggregator.scala:90-122, 199-221, HessianVectorAggregator.scala:60-85 per entity).  factors / shifts
+ * are concatenated like the coefficients (either may be NULL); intercept_local[e] is entity e's intercept index in its
+ * own space, -1 = none (NULL = none anywhere).  The reference's requires hold per entity (shifts need an intercept;
+ * its factor is 1 and its shift 0) -> PML_EINVAL.  With shifts every row of an entity must also hold the entry
+ * (intercept, 1.0) -- the library folds the per-entity shift terms into the intercept coefficient -- else PML_EINVAL.
+ * All NULL removes the context.  The smoothed hinge loss ignores it, as in the reference. */
+int pml_batch_set_normalization(pml_batch *b, const double *factors, const double *shifts, const int32_t *intercept_local);
 /* same with the mask already in device memory (a device-resident optimizer updates it without a host round trip);
  * the bytes are copied.  NULL = all active. */
 int pml_batch_set_active_dev(pml_batch *b, const uint8_t *active_dev /* E, device */);

@@ -34,6 +34,7 @@ SYMBOLS = [
     "pml_peer_multicast_export", "pml_peer_multicast_join", "pml_peer_multicast_bind", "pml_peer_multicast_release",
     "pml_peer_transport", "pml_ctx_pci_bus_id", "pml_peer_merge_dev",
     "pml_batch_set_active_dev", "pml_batch_segment_dot_dev", "pml_batch_segment_axpby_dev", "pml_loss_from_scores_dev",
+    "pml_batch_set_normalization",
 ]
 
 
@@ -134,6 +135,7 @@ def load():
         "pml_peer_merge_dev": [vp, vp, ctypes.c_int],
         "pml_loss_from_scores_dev": [vp, ctypes.c_int, vp, vp],
         "pml_batch_set_active_dev": [vp, vp],
+        "pml_batch_set_normalization": [vp, vp, vp, vp],
         "pml_batch_segment_dot_dev": [vp, vp, vp, vp],
         "pml_batch_segment_axpby_dev": [vp, vp, vp, vp, vp, vp, vp],
         "pml_value_and_gradient_allreduce_dev": [vp, vp, ctypes.c_int, vp, vp, vp],
@@ -436,6 +438,14 @@ class Batch:
         if a is not None and a.shape != (self.n_entities,):
             raise IllegalArgumentError("Size mismatch. active size: %d != %d." % (a.size, self.n_entities))
         check(load().pml_batch_set_active(self._h, _ptr(a)))
+
+    def set_normalization(self, factors=None, shifts=None, intercept_local=None):
+        """Per-entity NormalizationContext: factors / shifts concatenated like the coefficients, intercept_local[e] =
+        entity e's intercept index in its own space (-1 = none).  All None removes it."""
+        f = _np(factors, np.float64, self.d_total, "factors")
+        s = _np(shifts, np.float64, self.d_total, "shifts")
+        ic = _np(intercept_local, np.int32, self.n_entities, "intercept ids")
+        check(load().pml_batch_set_normalization(self._h, _ptr(f), _ptr(s), _ptr(ic)))
 
     def set_active_dev(self, active_dev):
         """active_dev: device address of E bytes (copied), or None for all active."""

@@ -1203,6 +1203,8 @@ int pml_batch_create_csr(pml_ctx *ctx, int64_t n_entities, const int64_t *ent_ro
     return PML_OK;
 }
 
+static void batch_clear_normalization(pml_batch *b);
+
 int pml_batch_destroy(pml_batch *b)
 {
     if (!b) return PML_OK;
@@ -1212,6 +1214,7 @@ int pml_batch_destroy(pml_batch *b)
     }
     if (b->ent_row_ptr) cudaFree(b->ent_row_ptr);
     if (b->ent_values) cudaFree(b->ent_values);
+    batch_clear_normalization(b);
     if (b->coef_ptr_dev) cudaFree(b->coef_ptr_dev);
     if (b->ent_of_coef) cudaFree(b->ent_of_coef);
     if (b->active_dev) cudaFree(b->active_dev);
@@ -1234,6 +1237,123 @@ int pml_batch_coef_ptr(pml_batch *b, int64_t *out)
     return PML_OK;
 }
 
+// ---- per-entity NormalizationContext of a batch ---------------------------------------------------------------
+static bool batch_normalized(const pml_batch *b, int loss)
+{
+    return loss != PML_LOSS_SMOOTHED_HINGE && (b->factors != nullptr || b->shifts != nullptr);
+}
+
+// device copy of the coefficient offsets (and, on request, the entity of every coefficient), made on first use
+static int batch_index(pml_batch *b, bool need_ent_of)
+{
+    cudaStream_t s = b->ds->ctx->stream;
+    if (b->coef_ptr_dev == nullptr) {
+        PML_CUDA(cudaMalloc(&b->coef_ptr_dev, sizeof(int64_t) * (size_t)(b->n_entities + 1)));
+        PML_CUDA(cudaMemcpyAsync(b->coef_ptr_dev, b->coef_ptr.data(), sizeof(int64_t) * (size_t)(b->n_entities + 1),
+                                 cudaMemcpyHostToDevice, s));
+        PML_CUDA(cudaStreamSynchronize(s));
+    }
+    if (need_ent_of && b->ent_of_coef == nullptr && b->ds->d > 0) {
+        PML_CUDA(cudaMalloc(&b->ent_of_coef, sizeof(int32_t) * (size_t)b->ds->d));
+        PML_TRY(count(b->ds->ctx, launch_entity_of_coef(s, b->n_entities, b->coef_ptr_dev, b->ent_of_coef)));
+    }
+    return PML_OK;
+}
+
+// What the block-diagonal data set is evaluated at: x itself, or x .* factors with the per-entity shift term folded
+// into the intercept entry (see the kernels' comment), left in `scratch`.
+static int batch_effective(pml_batch *b, const double *x_dev, double *scratch, const double **out)
+{
+    pml_ctx *ctx = b->ds->ctx;
+    cudaStream_t s = ctx->stream;
+    PML_TRY(run(ctx, PML_K_PREPARE, [&] { return launch_scale(s, b->ds->d, x_dev, b->factors, scratch); }));
+    if (b->shifts) {
+        PML_TRY(run(ctx, PML_K_PREPARE, [&] {
+            return launch_segment_dot(s, b->n_entities, b->coef_ptr_dev, scratch, b->shifts, b->dots);
+        }));
+        PML_TRY(run(ctx, PML_K_PREPARE, [&] { return launch_absorb_shift(s, b->n_entities, b->icpt_pos, b->dots, scratch); }));
+    }
+    *out = scratch;
+    return PML_OK;
+}
+
+static int batch_get_vector(pml_batch *b, const double *V, double *out_dev)
+{
+    pml_ctx *ctx = b->ds->ctx;
+    return run(ctx, PML_K_FINALIZE, [&] {
+        return launch_batch_finalize(ctx->stream, b->ds->d, b->ent_of_coef, V, b->factors, b->shifts, b->icpt_pos, out_dev);
+    });
+}
+
+static void batch_clear_normalization(pml_batch *b)
+{
+    for (double **p : { &b->factors, &b->shifts, &b->ec, &b->ev, &b->dots })
+        if (*p) { cudaFree(*p); *p = nullptr; }
+    if (b->icpt_pos) { cudaFree(b->icpt_pos); b->icpt_pos = nullptr; }
+}
+
+int pml_batch_set_normalization(pml_batch *b, const double *factors, const double *shifts, const int32_t *intercept_local)
+{
+    if (!b || !b->ds) return fail(PML_EINVAL, "null batch handle");
+    pml_dataset *ds = b->ds;
+    const int64_t E = b->n_entities, D = ds->d;
+    // the `require`s of NormalizationContext / ValueAndGradientAggregator.init, entity by entity
+    std::vector<int64_t> pos((size_t)E, -1);
+    for (int64_t e = 0; e < E; ++e) {
+        const int64_t lo = b->coef_ptr[(size_t)e], dim = b->coef_ptr[(size_t)e + 1] - lo;
+        const int32_t ic = intercept_local ? intercept_local[e] : -1;
+        if (ic < -1 || ic >= dim) return fail(PML_EINVAL, "intercept id outside [0, ent_dim) for entity " + std::to_string(e));
+        if (shifts && dim > 0 && ic < 0) return fail(PML_EINVAL, "Shift without intercept is illegal.");
+        if (ic < 0) continue;
+        pos[(size_t)e] = lo + ic;
+        if (factors && factors[lo + ic] != 1.0)
+            return fail(PML_EINVAL, "The intercept should not be transformed. Intercept scaling factor: " + std::to_string(factors[lo + ic]));
+        if (shifts && shifts[lo + ic] != 0.0)
+            return fail(PML_EINVAL, "The intercept should not be transformed. Intercept shift: " + std::to_string(shifts[lo + ic]));
+    }
+    Guard g(ds->ctx);
+    PML_CUDA(cudaSetDevice(ds->ctx->device));
+    cudaStream_t s = ds->ctx->stream;
+    PML_CUDA(cudaStreamSynchronize(s));
+    ds->cache_valid = false;
+    batch_clear_normalization(b);
+    if ((!factors && !shifts) || D == 0 || E == 0) return PML_OK;
+    PML_TRY(batch_index(b, true));
+    const size_t db = sizeof(double) * (size_t)D;
+    if (factors) {
+        PML_CUDA(cudaMalloc(&b->factors, db));
+        PML_CUDA(cudaMemcpyAsync(b->factors, factors, db, cudaMemcpyHostToDevice, s));
+    }
+    if (shifts) {
+        PML_CUDA(cudaMalloc(&b->shifts, db));
+        PML_CUDA(cudaMemcpyAsync(b->shifts, shifts, db, cudaMemcpyHostToDevice, s));
+    }
+    PML_CUDA(cudaMalloc(&b->icpt_pos, sizeof(int64_t) * (size_t)E));
+    PML_CUDA(cudaMemcpyAsync(b->icpt_pos, pos.data(), sizeof(int64_t) * (size_t)E, cudaMemcpyHostToDevice, s));
+    PML_CUDA(cudaMalloc(&b->ec, db));
+    PML_CUDA(cudaMalloc(&b->ev, db));
+    PML_CUDA(cudaMalloc(&b->dots, sizeof(double) * (size_t)E));
+    if (shifts) {
+        // the shift term is folded into the intercept coefficient: every row must hold (intercept, 1.0)
+        unsigned long long *bad_dev = nullptr, bad = 0;
+        PML_CUDA(cudaMalloc(&bad_dev, sizeof(bad)));
+        PML_CUDA(cudaMemsetAsync(bad_dev, 0, sizeof(bad), s));
+        const int rc = count(ds->ctx, launch_check_intercepts(s, ds->value_bytes, E, b->ent_row_ptr, ds->row_ptr, ds->col, ds->val,
+                                                              ds->t.rank, b->icpt_pos, bad_dev));
+        cudaMemcpyAsync(&bad, bad_dev, sizeof(bad), cudaMemcpyDeviceToHost, s);
+        cudaStreamSynchronize(s);
+        cudaFree(bad_dev);
+        if (rc != PML_OK || bad != 0) {
+            batch_clear_normalization(b);
+            if (rc != PML_OK) return rc;
+            return fail(PML_EINVAL, "shifts need the intercept feature with value 1 in every row of its entity: " +
+                                        std::to_string(bad) + " rows lack it");
+        }
+    }
+    PML_CUDA(cudaStreamSynchronize(s));
+    return PML_OK;
+}
+
 int pml_batch_value_and_gradient_dev(pml_batch *b, int loss, const double *coefs_dev, double *out_values_dev,
                                      double *out_grads_dev)
 {
@@ -1245,6 +1365,8 @@ int pml_batch_value_and_gradient_dev(pml_batch *b, int loss, const double *coefs
     PML_CUDA(cudaSetDevice(ds->ctx->device));
     cudaStream_t s = ds->ctx->stream;
     double *raw = ds->raw;
+    const bool normalized = batch_normalized(b, loss);
+    if (normalized) PML_TRY(batch_effective(b, coefs_dev, b->ec, &coefs_dev));
     ds->want_row_loss = true;
     const int rc = vg_raw(ds, loss, coefs_dev, raw, out_grads_dev != nullptr);
     ds->want_row_loss = false;
@@ -1252,8 +1374,10 @@ int pml_batch_value_and_gradient_dev(pml_batch *b, int loss, const double *coefs
     PML_TRY(run(ds->ctx, PML_K_ENTITY, [&] {
         return launch_entity_values(s, b->n_entities, b->ent_row_ptr, ds->row_loss, out_values_dev);
     }));
-    if (out_grads_dev && ds->d > 0)
-        PML_CUDA(cudaMemcpyAsync(out_grads_dev, ds->raw, sizeof(double) * (size_t)ds->d, cudaMemcpyDeviceToDevice, s));
+    if (out_grads_dev && ds->d > 0) {
+        if (normalized) PML_TRY(batch_get_vector(b, ds->raw, out_grads_dev));
+        else PML_CUDA(cudaMemcpyAsync(out_grads_dev, ds->raw, sizeof(double) * (size_t)ds->d, cudaMemcpyDeviceToDevice, s));
+    }
     if (b->active_dev)
         PML_TRY(run(ds->ctx, PML_K_ENTITY, [&] {
             return launch_mask_entities(s, b->n_entities, b->coef_ptr_dev, b->active_dev, out_values_dev, out_grads_dev);
@@ -1272,19 +1396,27 @@ int pml_batch_value_and_gradient(pml_batch *b, int loss, const double *coefs, do
     cudaStream_t s = ds->ctx->stream;
     const size_t db = sizeof(double) * (size_t)ds->d;
     if (ds->d > 0) PML_CUDA(cudaMemcpyAsync(ds->io_a, coefs, db, cudaMemcpyHostToDevice, s));
+    const bool normalized = batch_normalized(b, loss);
+    const double *coefs_dev = ds->io_a;
+    if (normalized) PML_TRY(batch_effective(b, coefs_dev, b->ec, &coefs_dev));
     ds->want_row_loss = true;
-    const int rc = vg_raw(ds, loss, ds->io_a, ds->raw);
+    const int rc = vg_raw(ds, loss, coefs_dev, ds->raw);
     ds->want_row_loss = false;
     PML_TRY(rc);
     PML_TRY(run(ds->ctx, PML_K_ENTITY, [&] {
         return launch_entity_values(s, b->n_entities, b->ent_row_ptr, ds->row_loss, b->ent_values);
     }));
+    double *grads_dev = ds->raw;
+    if (normalized && out_grads && ds->d > 0) {
+        PML_TRY(batch_get_vector(b, ds->raw, ds->io_b));
+        grads_dev = ds->io_b;
+    }
     if (b->active_dev)
         PML_TRY(run(ds->ctx, PML_K_ENTITY, [&] {
             return launch_mask_entities(s, b->n_entities, b->coef_ptr_dev, b->active_dev, b->ent_values,
-                                        out_grads ? ds->raw : nullptr);
+                                        out_grads ? grads_dev : nullptr);
         }));
-    if (out_grads && ds->d > 0) PML_CUDA(cudaMemcpyAsync(out_grads, ds->raw, db, cudaMemcpyDeviceToHost, s));
+    if (out_grads && ds->d > 0) PML_CUDA(cudaMemcpyAsync(out_grads, grads_dev, db, cudaMemcpyDeviceToHost, s));
     if (b->n_entities > 0)
         PML_CUDA(cudaMemcpyAsync(out_values, b->ent_values, sizeof(double) * (size_t)b->n_entities, cudaMemcpyDeviceToHost, s));
     PML_CUDA(cudaStreamSynchronize(s));
@@ -1298,7 +1430,22 @@ int pml_batch_hessian_vector_dev(pml_batch *b, int loss, const double *coefs_dev
     pml_dataset *ds = b->ds;
     // entities are the diagonal blocks of one data set: the product of the block-diagonal Hessian with the
     // concatenated vector is the concatenation of the per-entity products
-    PML_TRY(pml_hessian_vector_dev(ds, loss, coefs_dev, coef_tag, vs_dev, out_hvs_dev));
+    if (batch_normalized(b, loss)) {
+        if (!valid_loss(loss)) return fail(PML_EINVAL, "unknown loss");
+        if (!vs_dev || !out_hvs_dev) return fail(PML_EINVAL, "null buffer");
+        Guard g(ds->ctx);
+        PML_CUDA(cudaSetDevice(ds->ctx->device));
+        const bool cached = coef_tag != 0 && ds->cache_valid && ds->cached_tag == coef_tag && ds->cached_loss == loss;
+        if (!cached) {
+            if (!coefs_dev) return fail(PML_EINVAL, "coefficients are required when no cached pass matches the tag");
+            PML_TRY(batch_effective(b, coefs_dev, b->ec, &coefs_dev));
+        }
+        PML_TRY(batch_effective(b, vs_dev, b->ev, &vs_dev));
+        PML_TRY(hv_raw(ds, loss, coefs_dev, coef_tag, vs_dev, ds->raw));
+        PML_TRY(batch_get_vector(b, ds->raw, out_hvs_dev));
+    } else {
+        PML_TRY(pml_hessian_vector_dev(ds, loss, coefs_dev, coef_tag, vs_dev, out_hvs_dev));
+    }
     if (b->active_dev) {
         Guard g(ds->ctx);
         PML_TRY(run(ds->ctx, PML_K_ENTITY, [&] {
@@ -1312,7 +1459,26 @@ int pml_batch_hessian_vector(pml_batch *b, int loss, const double *coefs, uint64
 {
     if (!b || !b->ds) return fail(PML_EINVAL, "null batch handle");
     pml_dataset *ds = b->ds;
-    PML_TRY(pml_hessian_vector(ds, loss, coefs, coef_tag, vs, out_hvs));
+    if (batch_normalized(b, loss)) {
+        if (!valid_loss(loss)) return fail(PML_EINVAL, "unknown loss");
+        if ((!coefs || !vs || !out_hvs) && ds->d > 0) return fail(PML_EINVAL, "null buffer");
+        const size_t db = sizeof(double) * (size_t)ds->d;
+        {
+            Guard g(ds->ctx);
+            PML_CUDA(cudaSetDevice(ds->ctx->device));
+            PML_CUDA(cudaMemcpyAsync(ds->io_a, coefs, db, cudaMemcpyHostToDevice, ds->ctx->stream));
+            PML_CUDA(cudaMemcpyAsync(ds->io_b, vs, db, cudaMemcpyHostToDevice, ds->ctx->stream));
+        }
+        // the device form does the rest (it takes the lock itself, and applies the active mask); the product lands
+        // in io_a, which the coefficients no longer need by then
+        PML_TRY(pml_batch_hessian_vector_dev(b, loss, ds->io_a, coef_tag, ds->io_b, ds->io_a));
+        Guard g(ds->ctx);
+        PML_CUDA(cudaMemcpyAsync(out_hvs, ds->io_a, db, cudaMemcpyDeviceToHost, ds->ctx->stream));
+        PML_CUDA(cudaStreamSynchronize(ds->ctx->stream));
+        return PML_OK;
+    } else {
+        PML_TRY(pml_hessian_vector(ds, loss, coefs, coef_tag, vs, out_hvs));
+    }
     if (b->active_dev && ds->d > 0) {  // rare on the host path: mask on the host copy
         std::vector<uint8_t> act((size_t)b->n_entities);
         PML_CUDA(cudaMemcpy(act.data(), b->active_dev, act.size(), cudaMemcpyDeviceToHost));
@@ -1327,23 +1493,6 @@ int pml_batch_set_offsets(pml_batch *b, const double *offsets)
 {
     if (!b || !b->ds) return fail(PML_EINVAL, "null batch handle");
     return pml_dataset_set_offsets(b->ds, offsets);
-}
-
-// device copy of the coefficient offsets (and, on request, the entity of every coefficient), made on first use
-static int batch_index(pml_batch *b, bool need_ent_of)
-{
-    cudaStream_t s = b->ds->ctx->stream;
-    if (b->coef_ptr_dev == nullptr) {
-        PML_CUDA(cudaMalloc(&b->coef_ptr_dev, sizeof(int64_t) * (size_t)(b->n_entities + 1)));
-        PML_CUDA(cudaMemcpyAsync(b->coef_ptr_dev, b->coef_ptr.data(), sizeof(int64_t) * (size_t)(b->n_entities + 1),
-                                 cudaMemcpyHostToDevice, s));
-        PML_CUDA(cudaStreamSynchronize(s));
-    }
-    if (need_ent_of && b->ent_of_coef == nullptr && b->ds->d > 0) {
-        PML_CUDA(cudaMalloc(&b->ent_of_coef, sizeof(int32_t) * (size_t)b->ds->d));
-        PML_TRY(count(b->ds->ctx, launch_entity_of_coef(s, b->n_entities, b->coef_ptr_dev, b->ent_of_coef)));
-    }
-    return PML_OK;
 }
 
 int pml_batch_segment_dot_dev(pml_batch *b, const double *x_dev, const double *y_dev, double *out_dev)

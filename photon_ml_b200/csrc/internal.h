@@ -119,6 +119,13 @@ int launch_segment_dot(cudaStream_t s, int64_t n_entities, const int64_t *coef_p
                        double *out);
 int launch_segment_axpby(cudaStream_t s, int64_t d, const int32_t *ent_of, const double *a, const double *x,
                          const double *c, const double *y, const uint8_t *active, double *out);
+int launch_check_intercepts(cudaStream_t s, int value_bytes, int64_t n_entities, const int64_t *ent_row_ptr,
+                            const uint32_t *row_ptr, const int32_t *col, const void *val, const int32_t *rank,
+                            const int64_t *icpt_pos, unsigned long long *bad);
+int launch_scale(cudaStream_t s, int64_t d, const double *x, const double *f, double *out);
+int launch_absorb_shift(cudaStream_t s, int64_t n_entities, const int64_t *icpt_pos, const double *dots, double *vec);
+int launch_batch_finalize(cudaStream_t s, int64_t d, const int32_t *ent_of, const double *V, const double *factors,
+                          const double *shifts, const int64_t *icpt_pos, double *out);
 int launch_mask_entities(cudaStream_t s, int64_t n_entities, const int64_t *coef_ptr, const uint8_t *active, double *values,
                          double *vec);
 
@@ -231,6 +238,11 @@ struct pml_batch {
     int64_t *coef_ptr_dev = nullptr; // device, E+1
     int32_t *ent_of_coef = nullptr;  // device, d_total, lazily: entity of every coefficient (segment_axpby)
     uint8_t *active_dev = nullptr;  // device, E; null = every entity active
+    // per-entity NormalizationContext (pml_batch_set_normalization); all null = none
+    double *factors = nullptr, *shifts = nullptr;  // device, d_total (concatenated)
+    int64_t *icpt_pos = nullptr;    // device, E: concatenated index of entity e's intercept coefficient, -1 = none
+    double *ec = nullptr, *ev = nullptr;  // device, d_total: effective coefficients / multiply vector of the running call
+    double *dots = nullptr;         // device, E
 };
 
 struct pml_span {

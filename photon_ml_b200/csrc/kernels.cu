@@ -1224,6 +1224,114 @@ int launch_segment_axpby(cudaStream_t s, int64_t d, const int32_t *ent_of, const
     return cudaGetLastError() == cudaSuccess ? 1 : -1;
 }
 
+// ------------------------------------------------------------------------------------------
+// Per-entity NormalizationContext of a batch (every entity of a random-effect coordinate trains in the transformed
+// space of ITS projected features: ValueAndGradientAggregator.init / getVector, :90-122 and :199-221, per entity).
+// Shifts need an intercept, and the intercept column is 1 in every row, so the per-entity scalars fold into the
+// intercept: x_i.ec + marginShift_e = x_i.ec' with ec'[icpt_e] = ec[icpt_e] - sum_j ec_j s_j, and the entity's
+// prefactorSum_e = sum_i r_i is vectorSum[icpt_e].  What is left is element-wise.
+// ------------------------------------------------------------------------------------------
+__global__ void scale_kernel(int64_t d, const double *__restrict__ x, const double *__restrict__ f, double *__restrict__ out)
+{
+    for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < d; j += (int64_t)gridDim.x * blockDim.x)
+        out[j] = f ? __dmul_rn(x[j], f[j]) : x[j];
+}
+
+int launch_scale(cudaStream_t s, int64_t d, const double *x, const double *f, double *out)
+{
+    if (d <= 0) return 0;
+    int64_t grid = (d + 255) / 256;
+    if (grid > 148 * 16) grid = 148 * 16;
+    scale_kernel<<<(int)grid, 256, 0, s>>>(d, x, f, out);
+    return cudaGetLastError() == cudaSuccess ? 1 : -1;
+}
+
+// vec[icpt_pos[e]] -= dots[e] for every entity that has an intercept
+__global__ void absorb_shift_kernel(int64_t n_entities, const int64_t *__restrict__ icpt_pos, const double *__restrict__ dots,
+                                    double *__restrict__ vec)
+{
+    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < n_entities; e += (int64_t)gridDim.x * blockDim.x)
+        if (icpt_pos[e] >= 0) vec[icpt_pos[e]] -= dots[e];
+}
+
+int launch_absorb_shift(cudaStream_t s, int64_t n_entities, const int64_t *icpt_pos, const double *dots, double *vec)
+{
+    if (n_entities <= 0) return 0;
+    int64_t grid = (n_entities + 255) / 256;
+    if (grid > 148 * 16) grid = 148 * 16;
+    absorb_shift_kernel<<<(int)grid, 256, 0, s>>>(n_entities, icpt_pos, dots, vec);
+    return cudaGetLastError() == cudaSuccess ? 1 : -1;
+}
+
+// getVector per entity: out_j = (V_j - s_j * P_e) * f_j with P_e = V[icpt_pos[e]]   (out must not alias V)
+__global__ void batch_finalize_kernel(int64_t d, const int32_t *__restrict__ ent_of, const double *__restrict__ V,
+                                      const double *__restrict__ factors, const double *__restrict__ shifts,
+                                      const int64_t *__restrict__ icpt_pos, double *__restrict__ out)
+{
+    for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < d; j += (int64_t)gridDim.x * blockDim.x) {
+        double v = V[j];
+        if (shifts) {
+            const int64_t ip = icpt_pos[ent_of[j]];
+            if (ip >= 0) v = __dsub_rn(v, __dmul_rn(shifts[j], V[ip]));
+        }
+        if (factors) v = __dmul_rn(v, factors[j]);
+        out[j] = v;
+    }
+}
+
+int launch_batch_finalize(cudaStream_t s, int64_t d, const int32_t *ent_of, const double *V, const double *factors,
+                          const double *shifts, const int64_t *icpt_pos, double *out)
+{
+    if (d <= 0) return 0;
+    int64_t grid = (d + 255) / 256;
+    if (grid > 148 * 16) grid = 148 * 16;
+    batch_finalize_kernel<<<(int)grid, 256, 0, s>>>(d, ent_of, V, factors, shifts, icpt_pos, out);
+    return cudaGetLastError() == cudaSuccess ? 1 : -1;
+}
+
+// Counts rows of entities with an intercept that do NOT hold the entry (intercept column, 1.0): folding the shifts
+// into the intercept is only valid when there are none.  One warp per entity, lanes stride its rows.
+template <typename VT>
+__global__ void check_intercepts_kernel(int64_t n_entities, const int64_t *__restrict__ ent_row_ptr,
+                                        const uint32_t *__restrict__ row_ptr, const int32_t *__restrict__ col,
+                                        const VT *__restrict__ val, const int32_t *__restrict__ rank,
+                                        const int64_t *__restrict__ icpt_pos, unsigned long long *__restrict__ bad)
+{
+    const int lane = threadIdx.x & 31;
+    int64_t e = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    unsigned long long wrong = 0;
+    for (; e < n_entities; e += nw) {
+        if (icpt_pos[e] < 0) continue;
+        const int32_t want = rank[icpt_pos[e]];
+        for (int64_t i = ent_row_ptr[e] + lane; i < ent_row_ptr[e + 1]; i += 32) {
+            bool found = false;
+            for (uint32_t k = row_ptr[i]; k < row_ptr[i + 1]; ++k)
+                if ((col[k] & 0x7fffffff) == want && load_value(val, k) == 1.0) found = true;
+            if (!found) ++wrong;
+        }
+    }
+    if (wrong) atomicAdd(bad, wrong);  // a count for the error message: order does not matter
+}
+
+int launch_check_intercepts(cudaStream_t s, int value_bytes, int64_t n_entities, const int64_t *ent_row_ptr,
+                            const uint32_t *row_ptr, const int32_t *col, const void *val, const int32_t *rank,
+                            const int64_t *icpt_pos, unsigned long long *bad)
+{
+    if (n_entities <= 0) return 0;
+    int64_t grid = (n_entities * 32 + 255) / 256;
+    if (grid > 148 * 16) grid = 148 * 16;
+    if (value_bytes == 0)
+        check_intercepts_kernel<One><<<(int)grid, 256, 0, s>>>(n_entities, ent_row_ptr, row_ptr, col, nullptr, rank, icpt_pos, bad);
+    else if (value_bytes == 4)
+        check_intercepts_kernel<float><<<(int)grid, 256, 0, s>>>(n_entities, ent_row_ptr, row_ptr, col, (const float *)val, rank,
+                                                                 icpt_pos, bad);
+    else
+        check_intercepts_kernel<double><<<(int)grid, 256, 0, s>>>(n_entities, ent_row_ptr, row_ptr, col, (const double *)val,
+                                                                  rank, icpt_pos, bad);
+    return cudaGetLastError() == cudaSuccess ? 1 : -1;
+}
+
 // offsets'_i = base_i + score_{map(i)}: DataSet.addScoresToOffsets (api/data/FixedEffectDataSet.scala:45-54,
 // api/data/LocalDataSet.scala:82-89) without the RDD join -- `row_map` carries the row correspondence
 // between two coordinates' row orders (e.g. entity-grouped rows -> fixed-effect rows); null = identity.

@@ -171,3 +171,101 @@ def test_batch_active_mask_and_batch_offsets():
         batch.set_offsets(off[:-1])
     batch.close()
     ctx.close()
+
+
+def _entities_with_intercept(rng, n_entities, max_dim, mean_rows):
+    """Like _entities, but every entity's last local column is an intercept: 1.0 in every one of its rows."""
+    ent_row_ptr, dims, row_ptr, col, val, n = _entities(rng, n_entities, max_dim, mean_rows)
+    new_ptr, new_col, new_val = [0], [], []
+    for e in range(n_entities):
+        for i in range(int(ent_row_ptr[e]), int(ent_row_ptr[e + 1])):
+            a, b = int(row_ptr[i]), int(row_ptr[i + 1])
+            new_col.extend(col[a:b].tolist() + [int(dims[e])])
+            new_val.extend(val[a:b].tolist() + [1.0])
+            new_ptr.append(len(new_col))
+    return (ent_row_ptr, (dims + 1).astype(np.int32), np.asarray(new_ptr, np.int64), np.asarray(new_col, np.int32),
+            np.asarray(new_val, np.float64), n)
+
+
+@pytest.mark.parametrize("kind", ["SCALE_WITH_STANDARD_DEVIATION", "STANDARDIZATION"])
+@pytest.mark.parametrize("loss", [oracle.LOGISTIC, oracle.POISSON])
+def test_batch_per_entity_normalization(kind, loss):
+    """pml_batch_set_normalization: every entity evaluated in the transformed space of its own context, against the
+    oracle run entity by entity with that entity's (factors, shifts, intercept)."""
+    import torch
+    import photon_ml_b200 as pml
+    rng = np.random.default_rng(31 + loss)
+    ent_row_ptr, dims, row_ptr, col, val, n = _entities_with_intercept(rng, 250, 10, 14)
+    label = util.labels_for(rng, loss, n)
+    offset, weight = rng.normal(scale=0.2, size=n), rng.uniform(0.5, 2.0, size=n)
+    ctx = pml.Context(0)
+    batch = pml.Batch(ctx, ent_row_ptr, dims, row_ptr, col, val, label, offset, weight)
+    D = batch.d_total
+    factors, shifts, icpt = np.ones(D), np.zeros(D), (dims - 1).astype(np.int32)
+    contexts = []
+    for e in range(len(dims)):
+        lo, hi = int(ent_row_ptr[e]), int(ent_row_ptr[e + 1])
+        a = int(batch.coef_ptr[e])
+        sl = slice(int(row_ptr[lo]), int(row_ptr[hi]))
+        d_e = int(dims[e])
+        if hi > lo:
+            f, s, _ = util.normalization_context(kind, hi - lo, d_e, row_ptr[lo:hi + 1] - row_ptr[lo], col[sl], val[sl], d_e - 1)
+        else:
+            f, s = None, None
+        f = np.ones(d_e) if f is None else f
+        s = np.zeros(d_e) if s is None else s
+        factors[a:a + d_e], shifts[a:a + d_e] = f, s
+        contexts.append((f, s))
+    use_shifts = kind == "STANDARDIZATION"
+    batch.set_normalization(factors, shifts if use_shifts else None, icpt)
+    coefs = rng.normal(scale=0.2, size=D)
+    vs = rng.normal(size=D)
+    values, grads = batch.value_and_gradient(loss, coefs)
+    hv_cold = batch.hessian_vector(loss, coefs, vs, tag=9)
+    hv_cached = batch.hessian_vector(loss, coefs, vs, tag=9)
+    dev = torch.device("cuda", 0)
+    with torch.cuda.stream(torch.cuda.ExternalStream(ctx.stream, device=dev)):
+        c, v = torch.from_numpy(coefs).to(dev), torch.from_numpy(vs).to(dev)
+        ov = torch.empty(len(dims), dtype=torch.float64, device=dev)
+        og, oh = torch.empty(D, dtype=torch.float64, device=dev), torch.empty(D, dtype=torch.float64, device=dev)
+        batch.value_and_gradient_dev(loss, c.data_ptr(), ov.data_ptr(), og.data_ptr())
+        batch.hessian_vector_dev(loss, c.data_ptr(), v.data_ptr(), oh.data_ptr(), tag=0)
+        ctx.synchronize()
+        assert np.array_equal(ov.cpu().numpy(), values) and np.array_equal(og.cpu().numpy(), grads)
+        assert np.array_equal(oh.cpu().numpy(), hv_cold)
+    for e in range(len(dims)):
+        lo, hi = int(ent_row_ptr[e]), int(ent_row_ptr[e + 1])
+        a, b = int(batch.coef_ptr[e]), int(batch.coef_ptr[e + 1])
+        sl = slice(int(row_ptr[lo]), int(row_ptr[hi]))
+        local = oracle.Data(hi - lo, int(dims[e]), row_ptr[lo:hi + 1] - row_ptr[lo], col[sl], val[sl], label[lo:hi],
+                            offset[lo:hi], weight[lo:hi])
+        f, s = contexts[e]
+        s_arg = s if use_shifts else None
+        f_ref, g_ref = oracle.value_and_gradient(local, loss, coefs[a:b], f, s_arg, int(dims[e]) - 1)
+        hv_ref = oracle.hessian_vector(local, loss, coefs[a:b], vs[a:b], f, s_arg, int(dims[e]) - 1)
+        assert abs(values[e] - f_ref) <= 1e-10 * max(abs(f_ref), 1e-300), (e, values[e], f_ref)
+        assert util.rel_err(grads[a:b], g_ref) <= 1e-10, e
+        assert util.rel_err(hv_cold[a:b], hv_ref) <= 1e-10 and util.rel_err(hv_cached[a:b], hv_ref) <= 1e-10, e
+    # the smoothed hinge ignores the context; removing it restores the plain results
+    hinge_with, _ = batch.value_and_gradient(oracle.SMOOTHED_HINGE, coefs)
+    batch.set_normalization(None, None, None)
+    hinge_without, _ = batch.value_and_gradient(oracle.SMOOTHED_HINGE, coefs)
+    assert np.array_equal(hinge_with, hinge_without)
+    # the requires, entity by entity
+    with pytest.raises(pml.IllegalArgumentError):
+        batch.set_normalization(None, shifts, None)                       # shift without intercept
+    bad = factors.copy()
+    bad[int(batch.coef_ptr[3]) + int(dims[3]) - 1] = 2.0
+    with pytest.raises(pml.IllegalArgumentError):
+        batch.set_normalization(bad, None, icpt)                          # the intercept must not be scaled
+    wrong = icpt.copy()
+    wrong[:] = 0                                                          # column 0 is not a column of ones
+    s2 = shifts.copy()
+    s2[batch.coef_ptr[:-1]] = 0.0
+    f2 = factors.copy()
+    f2[batch.coef_ptr[:-1]] = 1.0
+    if use_shifts:
+        with pytest.raises(pml.IllegalArgumentError):
+            batch.set_normalization(f2, s2, wrong)
+    batch.close()
+    ctx.close()
