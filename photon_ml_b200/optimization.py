@@ -38,6 +38,18 @@ def _copy(x):
     return np.array(x, dtype=np.float64) if isinstance(x, np.ndarray) else x.clone()
 
 
+EPSILON = 1e-12   # MathConst.EPSILON, lib/constants/MathConst.scala:21
+
+
+def compute_variances(objectiveFunction, data, coefficients):
+    """Distributed / SingleNodeOptimizationProblem.computeVariances (api/optimization/DistributedOptimizationProblem.scala:
+    81-95, SingleNodeOptimizationProblem.scala:57-67): 1 / (hessianDiagonal_j + EPSILON) -- the one caller of
+    TwiceDiffFunction.hessianDiagonal; None for an objective that is not twice differentiable."""
+    if not getattr(objectiveFunction, "twice_differentiable", False):
+        return None
+    return 1.0 / (objectiveFunction.hessianDiagonal(data, coefficients) + EPSILON)
+
+
 class OptimizerState:
     def __init__(self, coefficients, loss, gradient, iter):
         self.coefficients, self.loss, self.gradient, self.iter = coefficients, loss, gradient, iter

@@ -114,3 +114,28 @@ def test_tron_with_device_resident_state_matches_host_state(ctx):
     assert abs(f_dev - f_host) <= 1e-9 * abs(f_host)
     assert np.max(np.abs(w_dev.cpu().numpy() - w_host)) <= 1e-6 * max(1.0, np.max(np.abs(w_host)))
     ds.close()
+
+
+def test_compute_variances_matches_the_closed_form(ctx):
+    """computeVariances = 1 / (diag(H) + EPSILON) with the L2 term in the diagonal; for the squared loss the diagonal
+    is sum_i wt_i x_ij^2 + lambda whatever the coefficients (DistributedOptimizationProblemTest.scala:280-373)."""
+    import photon_ml_b200 as pml
+    from photon_ml_b200.function import DistributedGLMLossFunction, DistributedSmoothedHingeLossFunction
+    from photon_ml_b200.optimization import compute_variances
+    rng = np.random.default_rng(17)
+    n, d, lam = 800, 60, 0.7
+    row_ptr, col, val = util.random_csr(rng, n, d, 6)
+    weight = rng.uniform(0.5, 2.0, size=n)
+    label = rng.normal(size=n)
+    ds = pml.Dataset.from_csr(ctx, n, d, row_ptr, col, val, label, None, weight)
+    w = rng.normal(size=d)
+    got = compute_variances(DistributedGLMLossFunction.create(pml.SQUARED, l2RegWeight=lam), ds, w)
+    X = util.csr_to_dense(n, d, row_ptr, col, val)
+    expect = 1.0 / ((weight[:, None] * X * X).sum(axis=0) + lam + 1e-12)
+    assert util.rel_err(got, expect) <= 1e-11
+    ref = oracle.Data(n, d, row_ptr, col, val, (label > 0).astype(np.float64), None, weight)
+    ds.set_labels(ref.label)
+    got = compute_variances(DistributedGLMLossFunction.create(pml.LOGISTIC, l2RegWeight=lam), ds, w)
+    assert util.rel_err(got, 1.0 / (oracle.hessian_diagonal(ref, oracle.LOGISTIC, w) + lam + 1e-12)) <= 1e-11
+    assert compute_variances(DistributedSmoothedHingeLossFunction.create(), ds, w) is None
+    ds.close()
