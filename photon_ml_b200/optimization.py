@@ -38,6 +38,27 @@ def _copy(x):
     return np.array(x, dtype=np.float64) if isinstance(x, np.ndarray) else x.clone()
 
 
+def _where(cond, a, b):
+    """np.where / torch.where with python scalars allowed on either side."""
+    if isinstance(cond, np.ndarray):
+        return np.where(cond, a, b)
+    import torch
+    like = a if torch.is_tensor(a) else (b if torch.is_tensor(b) else None)
+    if not torch.is_tensor(a):
+        a = torch.full_like(like, a) if like is not None else torch.full(cond.shape, a, dtype=torch.float64, device=cond.device)
+    if not torch.is_tensor(b):
+        b = torch.full_like(a, b)
+    return torch.where(cond, a, b)
+
+
+def _sign(x):
+    return np.sign(x) if isinstance(x, np.ndarray) else x.sign()
+
+
+def _abs_sum(x):
+    return float(np.abs(x).sum()) if isinstance(x, np.ndarray) else float(x.abs().sum())
+
+
 EPSILON = 1e-12   # MathConst.EPSILON, lib/constants/MathConst.scala:21
 
 
@@ -390,25 +411,25 @@ class OWLQN(LBFGS):
 
     def _adjusted(self, x, f, g):
         l1 = self.l1RegWeight
-        adj_f = f + l1 * float(np.abs(x).sum())
+        adj_f = f + l1 * _abs_sum(x)
         right, left = g + l1, g - l1
-        pg = np.where(x > 0, right, np.where(x < 0, left, np.where(left > 0, left, np.where(right < 0, right, 0.0))))
+        pg = _where(x > 0, right, _where(x < 0, left, _where(left > 0, left, _where(right < 0, right, 0.0))))
         return adj_f, pg
 
     def _direction(self, adj_g):
         d = super()._direction(adj_g)
-        return np.where(d * adj_g < 0, d, 0.0)     # keep only components that descend along the pseudo-gradient
+        return _where(d * adj_g < 0, d, 0.0)       # keep only components that descend along the pseudo-gradient
 
     def _line_search(self, objectiveFunction, data, x, f, g, adj_f, adj_g, direction):
-        orthant = np.where(x != 0, np.sign(x), -np.sign(adj_g))
+        orthant = _where(x != 0, _sign(x), -_sign(adj_g))
         gd = float(adj_g.dot(direction))
         t = 1.0 / _norm(direction) if self._inner_iter == 0 else 1.0
         for _ in range(30):
             xt = x + t * direction
-            xt = np.where(np.sign(xt) == orthant, xt, 0.0)
+            xt = _where(_sign(xt) == orthant, xt, 0.0)
             ft, gt = objectiveFunction.calculate(data, xt, self.normalizationContext)
             self.evaluations += 1
-            adj_ft = ft + self.l1RegWeight * float(np.abs(xt).sum())
+            adj_ft = ft + self.l1RegWeight * _abs_sum(xt)
             if adj_ft <= adj_f + 1e-4 * float(adj_g.dot(xt - x)):
                 return xt, ft, gt
             t *= 0.5

@@ -93,3 +93,35 @@ def test_heart_training_with_context_equals_training_on_transformed_data(loss, k
     assert abs(fa - fb) <= 1e-9 * abs(fb)
     assert np.max(np.abs(wa - wb)) <= 1e-7 * max(1.0, np.max(np.abs(wb)))
     assert a.currentState.iter == b.currentState.iter
+
+
+@pytest.mark.parametrize("l1", [0.0, 2.0])
+def test_lbfgs_and_owlqn_take_numpy_or_torch_vectors(l1):
+    """The drivers keep their state in whatever vector type the objective speaks (numpy on the host-buffer ABI, torch
+    tensors for device-resident state): same iterates either way."""
+    import torch
+    from photon_ml_b200.function import NoNormalization
+    from photon_ml_b200.optimization import LBFGS, OWLQN
+    rng = np.random.default_rng(0)
+    A, b = rng.normal(size=(40, 15)), rng.normal(size=40)
+
+    class LeastSquares:
+        twice_differentiable = True
+
+        def calculate(self, data, x, ctx, want_gradient=True):
+            if isinstance(x, np.ndarray):
+                r = A @ x - b
+                return float(0.5 * r.dot(r)), A.T @ r
+            r = torch.from_numpy(A) @ x - torch.from_numpy(b)
+            return float(0.5 * r.dot(r)), torch.from_numpy(A).T @ r
+
+    def make():
+        return OWLQN(l1, NoNormalization()) if l1 else LBFGS(NoNormalization())
+    host, dev = make(), make()
+    w_host, f_host = host.optimize(LeastSquares(), np.zeros(15), None)
+    w_dev, f_dev = dev.optimize(LeastSquares(), torch.zeros(15, dtype=torch.float64), None)
+    assert host.currentState.iter == dev.currentState.iter and host.evaluations == dev.evaluations
+    assert abs(f_host - f_dev) <= 1e-12 * abs(f_host)
+    assert np.max(np.abs(w_host - w_dev.numpy())) <= 1e-12
+    if l1:
+        assert int((w_host == 0).sum()) == int((w_dev.numpy() == 0).sum()) > 0

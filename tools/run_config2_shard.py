@@ -89,6 +89,24 @@ def main():
     print("Hv linearity rel err %.2e" % err)
     assert err <= 1e-11
     print("ok")
+    if os.environ.get("OWLQN"):
+        # configs[2]'s optimizer on this shard alone: OWL-QN, L1 (alpha = 1) and elastic net (alpha = 0.5), lambda = 1,
+        # optimizer state in device memory (the Breeze-style driver of photon_ml_b200/optimization.py)
+        from photon_ml_b200.function import DeviceGLMLossFunction, NoNormalization
+        from photon_ml_b200.optimization import OWLQN
+        del h, w, raw, raw2
+        for alpha in (1.0, 0.5):
+            obj = DeviceGLMLossFunction(ctx, pml.LOGISTIC, l2RegWeight=(1.0 - alpha) or None)
+            opt = OWLQN(alpha, NoNormalization(), isTrackingState=False)
+            with obj.stream():
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()
+                w_opt, f_opt = opt.optimize(obj, torch.zeros(D, dtype=torch.float64, device=dev), ds)
+                torch.cuda.synchronize()
+                wall = time.perf_counter() - t0
+            print("OWLQN alpha=%.1f lambda=1: %.2f s, %d iterations, %d evaluations, %s, objective %.6f, %d of %d coefficients non-zero"
+                  % (alpha, wall, opt.currentState.iter, opt.evaluations, opt.convergenceReason, f_opt,
+                     int((w_opt != 0).sum()), D), flush=True)
 
 
 if __name__ == "__main__":
