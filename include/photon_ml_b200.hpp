@@ -407,6 +407,117 @@ class TRON {
     double lossAbsTol_ = 0.0, gradAbsTol_ = 0.0;
 };
 
+// ---- random-effect coordinates: all per-entity problems of a partition as one batch ---------------------------
+// What RandomEffectCoordinate.updateModel hands to SingleNodeGLMLossFunction entity by entity
+// (api/algorithm/RandomEffectCoordinate.scala:108-119); coefficients / gradients / multiply vectors of all entities
+// are concatenated in entity order, coefPtr() gives the offsets.
+class Batch {
+  public:
+    Batch(const Context &ctx, const std::vector<int64_t> &entRowPtr, const std::vector<int32_t> &entDim, const int64_t *row_ptr,
+          const int32_t *col_local, const double *val, const double *labels, const double *offsets = nullptr,
+          const double *weights = nullptr)
+        : entities_((int64_t)entDim.size())
+    {
+        if (entRowPtr.size() != entDim.size() + 1) throw IllegalArgumentException("entRowPtr must hold one more entry than entDim");
+        check(pml_batch_create_csr(ctx.handle(), entities_, entRowPtr.data(), entDim.data(), row_ptr, col_local, val, PML_F64,
+                                   PML_STORE_AUTO, labels, offsets, weights, &h_));
+        coefPtr_.resize((size_t)entities_ + 1);
+        check(pml_batch_coef_ptr(h_, coefPtr_.data()));
+    }
+    ~Batch() { pml_batch_destroy(h_); }
+    Batch(const Batch &) = delete;
+    Batch &operator=(const Batch &) = delete;
+    int64_t entities() const { return entities_; }
+    int64_t totalDimension() const { return coefPtr_.back(); }
+    const std::vector<int64_t> &coefPtr() const { return coefPtr_; }
+    pml_batch *handle() const { return h_; }
+
+    // per-entity objective values; gradients (concatenated) when wanted
+    Vector calculate(int loss, const Vector &coefs, Vector *gradients) const
+    {
+        requireTotal(coefs.size(), "Coefficient");
+        Vector values((size_t)entities_);
+        if (gradients) gradients->resize(coefs.size());
+        check(pml_batch_value_and_gradient(h_, loss, coefs.data(), values.data(), gradients ? gradients->data() : nullptr));
+        return values;
+    }
+    Vector hessianVector(int loss, const Vector &coefs, const Vector &multiply, uint64_t coefTag = 0) const
+    {
+        requireTotal(coefs.size(), "Coefficient");
+        requireTotal(multiply.size(), "Multiply vector");
+        Vector out(coefs.size());
+        check(pml_batch_hessian_vector(h_, loss, coefs.data(), coefTag, multiply.data(), out.data()));
+        return out;
+    }
+    void setOffsets(const double *offsets) { check(pml_batch_set_offsets(h_, offsets)); }   // LocalDataSet.addScoresToOffsets
+    void setActive(const std::vector<uint8_t> *active)
+    {
+        if (active && (int64_t)active->size() != entities_) throw IllegalArgumentException("Size mismatch. active size");
+        check(pml_batch_set_active(h_, active ? active->data() : nullptr));
+    }
+    // one NormalizationContext per entity, concatenated like the coefficients; interceptLocal[e] = -1 for none
+    void setNormalization(const Vector *factors, const Vector *shifts, const std::vector<int32_t> *interceptLocal)
+    {
+        if (factors) requireTotal(factors->size(), "Factors vector");
+        if (shifts) requireTotal(shifts->size(), "Shifts vector");
+        check(pml_batch_set_normalization(h_, factors ? factors->data() : nullptr, shifts ? shifts->data() : nullptr,
+                                          interceptLocal ? interceptLocal->data() : nullptr));
+    }
+
+  private:
+    void requireTotal(size_t got, const char *what) const
+    {
+        if ((int64_t)got != totalDimension())
+            throw IllegalArgumentException(std::string("Size mismatch. ") + what + " size: " + std::to_string(got) + " != " +
+                                           std::to_string(totalDimension()) + ".");
+    }
+    pml_batch *h_ = nullptr;
+    int64_t entities_;
+    std::vector<int64_t> coefPtr_;
+};
+
+// ---- several processes, one GPU each: the merge of treeAggregate over NVLink peer memory -----------------------
+// `exchange` is the caller's only host-side communication: it takes this rank's 64-byte handle and returns the handles
+// of all ranks concatenated in rank order (an MPI_Allgather, a Spark collect + broadcast, ...).
+class Peer {
+  public:
+    template <class Exchange>
+    Peer(const Context &ctx, int rank, int world, int32_t d, Exchange &&exchange)
+    {
+        check(pml_peer_create(ctx.handle(), rank, world, d, &h_));
+        std::vector<char> mine(PML_PEER_HANDLE_BYTES);
+        int rc = pml_peer_handle(h_, mine.data());
+        if (rc == PML_OK) {
+            const std::vector<char> all = exchange(mine);
+            if (all.size() != (size_t)world * PML_PEER_HANDLE_BYTES) rc = -1;
+            else rc = pml_peer_connect(h_, all.data());
+        }
+        if (rc != PML_OK) {
+            pml_peer_destroy(h_);
+            h_ = nullptr;
+            if (rc == -1) throw IllegalArgumentException("exchange must return world * PML_PEER_HANDLE_BYTES bytes");
+            check(rc);
+        }
+    }
+    ~Peer() { pml_peer_destroy(h_); }
+    Peer(const Peer &) = delete;
+    Peer &operator=(const Peer &) = delete;
+    pml_peer *handle() const { return h_; }
+    // DistributedGLMLossFunction.calculate / hessianVector over all ranks' rows; device pointers, asynchronous
+    void calculate(const DataSet &data, int loss, const double *coef_dev, double *out_value_dev, double *out_grad_dev) const
+    {
+        check(pml_value_and_gradient_allreduce_dev(data.handle(), h_, loss, coef_dev, out_value_dev, out_grad_dev));
+    }
+    void hessianVector(const DataSet &data, int loss, const double *coef_dev, uint64_t coefTag, const double *v_dev,
+                       double *out_hv_dev) const
+    {
+        check(pml_hessian_vector_allreduce_dev(data.handle(), h_, loss, coef_dev, coefTag, v_dev, out_hv_dev));
+    }
+
+  private:
+    pml_peer *h_ = nullptr;
+};
+
 }  // namespace photon_ml_b200
 
 #endif  // PHOTON_ML_B200_HPP

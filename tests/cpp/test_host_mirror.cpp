@@ -1,6 +1,8 @@
 // Drives the C++ host-side mirror (include/photon_ml_b200.hpp): reads a LibSVM file, packs it, checks the
 // require() behaviour, and runs TRON on a logistic objective with the L2 mix-in.  Prints a few numbers that
 // tests/test_cpp_host.py compares with the Python driver on the same data.
+#include <algorithm>
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <fstream>
@@ -74,5 +76,44 @@ int main(int argc, char **argv)
     std::printf("checksum %.17g\n", checksum);
     const Vector diag = objective.hessianDiagonal(data, result.first);
     std::printf("diag0 %.17g\n", diag[0]);
+
+    // Batch: the first 64 rows as 8 entities of 8 rows each, every entity in the full d-dimensional space; the sum of
+    // the per-entity values / the concatenated gradients must be what the same rows give as 8 separate data sets
+    {
+        const int64_t E = 8, per = 8;
+        std::vector<int64_t> ent_row_ptr;
+        for (int64_t e = 0; e <= E; ++e) ent_row_ptr.push_back(e * per);
+        std::vector<int32_t> ent_dim((size_t)E, d);
+        Batch batch(ctx, ent_row_ptr, ent_dim, row_ptr.data(), col.data(), val.data(), label.data());
+        Vector coefs((size_t)batch.totalDimension());
+        for (size_t j = 0; j < coefs.size(); ++j) coefs[j] = 0.01 * (double)((j * 7) % 13) - 0.05;
+        Vector grads;
+        const Vector values = batch.calculate(PML_LOSS_LOGISTIC, coefs, &grads);
+        double worst = 0.0;
+        for (int64_t e = 0; e < E; ++e) {
+            const int64_t lo = row_ptr[(size_t)(e * per)];
+            std::vector<int64_t> rp;
+            for (int64_t i = e * per; i <= (e + 1) * per; ++i) rp.push_back(row_ptr[(size_t)i] - lo);
+            DataSet one(ctx, per, d, rp.data(), col.data() + lo, val.data() + lo, label.data() + e * per);
+            const Vector c(coefs.begin() + batch.coefPtr()[(size_t)e], coefs.begin() + batch.coefPtr()[(size_t)e + 1]);
+            const auto ref = plain.calculate(one, c, none);
+            worst = std::max(worst, std::fabs(ref.first - values[(size_t)e]) / std::fabs(ref.first));
+            for (int32_t j = 0; j < d; ++j)
+                worst = std::max(worst, std::fabs(ref.second[(size_t)j] - grads[(size_t)(batch.coefPtr()[(size_t)e] + j)]));
+        }
+        std::printf("batch_worst_diff %.3g\n", worst);
+        bool batch_threw = false;
+        try {
+            batch.calculate(PML_LOSS_LOGISTIC, Vector(3, 0.0), nullptr);
+        } catch (const IllegalArgumentException &) {
+            batch_threw = true;
+        }
+        std::printf("batch_require_throws %d\n", batch_threw ? 1 : 0);
+    }
+    // Peer with a single rank: the merge kernel degenerates to getVector; the handle exchange is the identity
+    {
+        Peer peer(ctx, 0, 1, d, [](const std::vector<char> &mine) { return mine; });
+        std::printf("peer_created %d\n", peer.handle() != nullptr ? 1 : 0);
+    }
     return 0;
 }

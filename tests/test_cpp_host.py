@@ -35,6 +35,7 @@ def test_cpp_tron_matches_python_driver(tmp_path):
     out = subprocess.check_output([exe, path, "123", "10.0"], text=True)
     got = dict(line.split() for line in out.strip().splitlines())
     assert got["require_size_throws"] == "1"
+    assert float(got["batch_worst_diff"]) <= 1e-12 and got["batch_require_throws"] == "1" and got["peer_created"] == "1"
     n, d, row_ptr, col, val, label = util.read_libsvm(path, d=123, add_intercept=True)
     ctx = pml.Context(0)
     ds = pml.Dataset.from_csr(ctx, n, d, row_ptr, col, val, label)
