@@ -60,7 +60,7 @@ class BatchedTRON:
         self.evaluations += 1
         if self.l2 != 0.0:
             f = f + self._dot(w, w) * (self.l2 / 2)
-            g.add_(w * self.l2)      # product rounded, then the sum: as the host-side L2 mix-in does
+            self._axpby(self._l2_per_entity(), w, None, g, g)   # g += l2 * w: product rounded, then the sum
         return f, g
 
     def _hessian_vector(self, w, v):
@@ -68,8 +68,13 @@ class BatchedTRON:
         self.batch.hessian_vector_dev(self.loss, w.data_ptr(), v.data_ptr(), hv.data_ptr(), tag=self._tag)
         self.hessian_vector_evaluations += 1
         if self.l2 != 0.0:
-            hv.add_(v * self.l2)
+            self._axpby(self._l2_per_entity(), v, None, hv, hv)
         return hv
+
+    def _l2_per_entity(self):
+        if getattr(self, "_l2_vec", None) is None:
+            self._l2_vec = self.torch.full((self.E,), self.l2, dtype=self.torch.float64, device=self.device)
+        return self._l2_vec
 
     # ---- TRON.truncatedCG for the entities in `mask` -------------------------------------------------------------
     def _truncated_cg(self, w, g, delta, mask):
@@ -82,7 +87,7 @@ class BatchedTRON:
         iters = torch.zeros(self.E, dtype=torch.int64, device=self.device)
         done = ~mask
         for _ in range(self.MAX_CG_ITERATIONS):
-            done = done | (self._dot(residual, residual).sqrt() <= cg_tol)
+            done = done | (rTr.sqrt() <= cg_tol)     # rTr is residual . residual of the current residual
             if bool(done.all()):
                 break
             run = ~done
