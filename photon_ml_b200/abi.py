@@ -10,7 +10,8 @@ import weakref
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "lib", "libphoton_ml_b200.so")
+# PML_LIB points at another build of the same library (kernel A/B runs: tools/); the default is the in-tree build
+LIB_PATH = os.environ.get("PML_LIB") or os.path.join(HERE, "lib", "libphoton_ml_b200.so")
 
 OK, EINVAL, ECUDA, ENOMEM, ESTATE = 0, 1, 2, 3, 4
 LOGISTIC, POISSON, SQUARED, SMOOTHED_HINGE = 0, 1, 2, 3
