@@ -262,6 +262,73 @@ __global__ void tile_scatter_kernel(int64_t nnz, const uint32_t *__restrict__ so
     }
 }
 
+// Bank-aware order inside the runs of the tiled hot region.  The tiled kernel looks r up in shared memory with 8-byte
+// loads, 8 entries per lane: for item i of the 8, the 16 lanes of a half warp are served in one pass only when their
+// rows fall into 16 different 8-byte bank pairs (row mod 16 all different); random rows collide about three deep, and a
+// dense column read in row order collides eight deep (lane L holds rows 8L..8L+7, so item i of 16 lanes strides by 8).
+// A sum does not care about the order of its terms, so within each run the entries are re-dealt: position p of a chunk
+// belongs to group (half warp, item) = (p / 128, p % 8), and every group greedily takes an entry whose residue it has
+// not seen yet, from the fullest residue class left in the run.  One warp per 256-entry chunk: the lanes copy the
+// chunk to shared memory, lane 0 deals (4096 cheap steps, pack time only), the lanes write the new order back.
+// Run-start flags stay with their POSITIONS.  Deterministic: the result depends on the chunk's content only.
+template <typename VT>
+__global__ void __launch_bounds__(256) bank_order_kernel(int64_t n_chunks, int32_t *__restrict__ idx, VT *__restrict__ val)
+{
+    constexpr int WARPS = 8;
+    __shared__ int32_t s_row[WARPS][256];
+    __shared__ unsigned char s_perm[WARPS][256], s_sorted[WARPS][256];
+    __shared__ double s_val[WARPS][(sizeof(VT) > 1) ? 256 : 1];   // wide enough for float and double values
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int64_t c = (int64_t)blockIdx.x * WARPS + warp; c < n_chunks; c += (int64_t)gridDim.x * WARPS) {
+        int32_t *ci = idx + c * 256;
+        for (int k = lane; k < 256; k += 32) {
+            s_row[warp][k] = ci[k];
+            if (val != nullptr) reinterpret_cast<VT *>(s_val[warp])[k] = val[c * 256 + k];
+        }
+        __syncwarp();
+        if (lane == 0) {
+            unsigned short used[16];
+            for (int g = 0; g < 16; ++g) used[g] = 0;
+            int a = 0;
+            while (a < 256) {
+                int b = a + 1;
+                while (b < 256 && s_row[warp][b] >= 0) ++b;   // [a, b): one run's share of this chunk
+                int cnt[16], off[16];
+                for (int q = 0; q < 16; ++q) cnt[q] = 0;
+                for (int k = a; k < b; ++k) ++cnt[s_row[warp][k] & 15];
+                int acc = a;
+                for (int q = 0; q < 16; ++q) { off[q] = acc; acc += cnt[q]; }
+                {
+                    int fill[16];
+                    for (int q = 0; q < 16; ++q) fill[q] = off[q];
+                    for (int k = a; k < b; ++k) s_sorted[warp][fill[s_row[warp][k] & 15]++] = (unsigned char)k;
+                }
+                for (int pos = a; pos < b; ++pos) {
+                    const int g = (pos >> 7) * 8 + (pos & 7);
+                    int best = -1, best_any = -1;
+                    for (int q = 0; q < 16; ++q) {
+                        if (cnt[q] == 0) continue;
+                        if (best_any < 0 || cnt[q] > cnt[best_any]) best_any = q;
+                        if (!((used[g] >> q) & 1) && (best < 0 || cnt[q] > cnt[best])) best = q;
+                    }
+                    const int q = best >= 0 ? best : best_any;
+                    used[g] |= (unsigned short)(1u << q);
+                    s_perm[warp][pos] = s_sorted[warp][off[q] + (--cnt[q])];
+                }
+                a = b;
+            }
+        }
+        __syncwarp();
+        for (int k = lane; k < 256; k += 32) {
+            const int src = s_perm[warp][k];
+            const int32_t flag = s_row[warp][k] & (int32_t)0x80000000;
+            ci[k] = (s_row[warp][src] & 0x7fffffff) | flag;
+            if (val != nullptr) val[c * 256 + k] = reinterpret_cast<const VT *>(s_val[warp])[src];
+        }
+        __syncwarp();
+    }
+}
+
 inline int grid_for(int64_t n, int block = 256)
 {
     int64_t g = (n + block - 1) / block;
@@ -656,6 +723,14 @@ static int build_tiled(cudaStream_t s, int sm_count, int64_t n, int64_t nnz, con
             tile_rows, (int)n_tiles, hs_dev.as<uint32_t>(), po_dev.as<uint32_t>(), (uint32_t)hot_len, out->idx_alloc,
             (double *)out->val_alloc, run_flag.as<unsigned char>(), hot_dest.as<uint32_t>());
     PML_CUDA(cudaGetLastError());
+    if (std::getenv("PML_NO_BANK_ORDER") == nullptr && hot_len > 0) {
+        const int64_t hc = hot_len / 256;
+        const int grid = (int)(hc / 8 + 1 < 148 * 8 ? hc / 8 + 1 : 148 * 8);
+        if (value_bytes == 0) bank_order_kernel<char><<<grid, 256, 0, s>>>(hc, out->idx_alloc, (char *)nullptr);
+        else if (value_bytes == 4) bank_order_kernel<float><<<grid, 256, 0, s>>>(hc, out->idx_alloc, (float *)out->val_alloc);
+        else bank_order_kernel<double><<<grid, 256, 0, s>>>(hc, out->idx_alloc, (double *)out->val_alloc);
+        PML_CUDA(cudaGetLastError());
+    }
 
     // hot run list: positions (padded coordinates) and partial slots (= keys) of the run starts
     DevBuf n_sel, run_ptr_hot;
