@@ -322,6 +322,32 @@ int pml_hessian_vector_allreduce_dev(pml_dataset *ds, pml_peer *peer, int loss, 
 /* The merge + getVector alone, for callers that filled the raw buffer themselves (pml_*_raw_dev with
  * out_raw_dev = the peer's raw buffer): same as pml_finalize_dev after an all-reduce of the raw sums. */
 int pml_peer_merge_dev(pml_dataset *ds, pml_peer *peer, int loss);
+/* The same two exchanges with HOST vectors in and out -- the shape DistributedObjectiveFunction hands over
+ * (coefficients broadcast to every executor, DistributedObjectiveFunction.scala:57-58; result to the driver, :73;
+ * bodies DistributedGLMLossFunction.scala:93-102, 114-125).  Every rank passes the SAME coefficient vector (d
+ * doubles) and uploads only its own slice [lo, hi) of it (pml_peer_slice) over its own PCIe link; the slices are
+ * exchanged between the GPUs over NVLink, then evaluation, merge and getVector run as in the _dev forms.
+ * gather_output = 0: only out[lo, hi) is written -- ranks that pass one shared host buffer (a memory-mapped file,
+ * a buffer of the driver JVM registered by every rank) assemble the full vector in it with N parallel downloads;
+ * gather_output = 1: the whole vector is downloaded on this rank.  *out_value is set on every rank.  Synchronous.
+ * coef may be NULL for a Hessian-vector product whose tag matches the cached pass. */
+int pml_peer_slice(pml_peer *peer, int64_t *out_lo, int64_t *out_hi);
+int pml_value_and_gradient_allreduce(pml_dataset *ds, pml_peer *peer, int loss, const double *coef, double *out_value,
+                                     double *out_grad, int gather_output);
+int pml_hessian_vector_allreduce(pml_dataset *ds, pml_peer *peer, int loss, const double *coef, uint64_t coef_tag,
+                                 const double *v, double *out_hv, int gather_output);
+/* 1 when an exchange on this handle gave up waiting for another rank (its result was filled with NaN);
+ * pml_ctx_synchronize and every later *_allreduce* call on the handle then return PML_ECUDA. */
+int pml_peer_status(pml_peer *peer, int *out);
+/* The whole exchange of `world` ranks on ONE device, every rank's CTAs inside one cooperative launch (no reference
+ * counterpart: a check of the exchange kernels for boxes with fewer GPUs than ranks -- kernels that wait on one
+ * another must not run as separate launches on one GPU).  raw: world x (d+2) host doubles, rank q's raw sums
+ * [vectorSum(d), valueSum, prefactorSum]; out_result: world x (d+1), what each rank would hold after the merge +
+ * getVector (factors / shifts: d host doubles or NULL).  vec_in / vec_out (both or neither): world x d; rank q
+ * uploads its slice of vec_in[q], the all-gather runs, and vec_out[q] is rank q's assembled copy.  The exchange is
+ * repeated `repeats` times on the same slabs (the flag epochs advance). */
+int pml_peer_emulate(pml_ctx *ctx, int world, int32_t d, int repeats, const double *raw, const double *factors,
+                     const double *shifts, double *out_result, const double *vec_in, double *vec_out);
 
 /* ---- evaluation without any allocation ------------------------------------------------------ */
 /* No counterpart in the reference (the JVM allocates freely); this exists for callers of THIS

@@ -36,6 +36,8 @@ SYMBOLS = [
     "pml_peer_transport", "pml_ctx_pci_bus_id", "pml_peer_merge_dev",
     "pml_batch_set_active_dev", "pml_batch_segment_dot_dev", "pml_batch_segment_axpby_dev", "pml_loss_from_scores_dev",
     "pml_batch_set_normalization",
+    "pml_peer_slice", "pml_value_and_gradient_allreduce", "pml_hessian_vector_allreduce", "pml_peer_status",
+    "pml_peer_emulate",
 ]
 
 
@@ -141,6 +143,11 @@ def load():
         "pml_batch_segment_axpby_dev": [vp, vp, vp, vp, vp, vp, vp],
         "pml_value_and_gradient_allreduce_dev": [vp, vp, ctypes.c_int, vp, vp, vp],
         "pml_hessian_vector_allreduce_dev": [vp, vp, ctypes.c_int, vp, u64, vp, vp],
+        "pml_peer_slice": [vp, ctypes.POINTER(i64), ctypes.POINTER(i64)],
+        "pml_value_and_gradient_allreduce": [vp, vp, ctypes.c_int, vp, ctypes.POINTER(dbl), vp, ctypes.c_int],
+        "pml_hessian_vector_allreduce": [vp, vp, ctypes.c_int, vp, u64, vp, vp, ctypes.c_int],
+        "pml_peer_status": [vp, ctypes.POINTER(ctypes.c_int)],
+        "pml_peer_emulate": [vp, ctypes.c_int, i32, ctypes.c_int, vp, vp, vp, vp, vp, vp],
     })
     for name, argtypes in sigs.items():
         fn = getattr(lib, name)
@@ -179,6 +186,22 @@ def value_noalloc_dev(device, stream, n, d, row_ptr_dev, col_dev, val_dev, value
     Asynchronous on `stream`; at most 16,777,216 rows; calls on one device must not overlap."""
     check(load().pml_value_noalloc_dev(int(device), stream, n, d, row_ptr_dev, col_dev, val_dev, values_dtype, label_dev,
                                        offset_dev, weight_dev, loss, coef_dev, out_value_dev))
+
+
+def peer_emulate(ctx, raw, factors=None, shifts=None, vec_in=None, repeats=1):
+    """pml_peer_emulate: the exchange of len(raw) ranks on one device.  raw: (world, d+2).  Returns the (world, d+1)
+    results, and with vec_in (world, d) also the (world, d) assembled input vectors."""
+    raw = np.ascontiguousarray(raw, dtype=np.float64)
+    world, d = raw.shape[0], raw.shape[1] - 2
+    out = np.empty((world, d + 1))
+    f = None if factors is None else _np(factors, np.float64, d, "factors")
+    s = None if shifts is None else _np(shifts, np.float64, d, "shifts")
+    vin = None if vec_in is None else np.ascontiguousarray(vec_in, dtype=np.float64)
+    vout = None if vec_in is None else np.empty((world, d))
+    check(load().pml_peer_emulate(ctx._h, world, d, repeats, _ptr(raw), None if f is None else _ptr(f),
+                                  None if s is None else _ptr(s), _ptr(out), None if vin is None else _ptr(vin),
+                                  None if vout is None else _ptr(vout)))
+    return out if vec_in is None else (out, vout)
 
 
 def offsets_from_scores_dev(ctx, n, base_offsets_dev, scores_dev, row_map_dev, out_offsets_dev):
@@ -301,6 +324,9 @@ class Dataset:
         f = _np(factors, np.float64, self.d, "Factors vector")
         s = _np(shifts, np.float64, self.d, "Shifts vector")
         check(load().pml_dataset_set_normalization(self._h, _ptr(f), _ptr(s), -1 if intercept is None else int(intercept)))
+        # what is set on the device right now: None, or a token the objective classes (function.py) replace by
+        # the NormalizationContext object they applied
+        self._applied_norm = None if (f is None and s is None) else object()
 
     def set_margin_variant(self, lanes_per_row):
         check(load().pml_dataset_set_margin_variant(self._h, int(lanes_per_row)))
@@ -598,6 +624,32 @@ class Peer:
 
     def hessian_vector(self, ds, loss, coef_dev, v_dev, out_hv_dev=None, tag=0):
         check(load().pml_hessian_vector_allreduce_dev(ds._h, self._h, loss, coef_dev, tag, v_dev, out_hv_dev))
+
+    def slice(self):
+        """[lo, hi): the part of the coefficient vector this rank uploads, and of the result it downloads, in the
+        host-buffer calls below."""
+        lo, hi = ctypes.c_int64(), ctypes.c_int64()
+        check(load().pml_peer_slice(self._h, ctypes.byref(lo), ctypes.byref(hi)))
+        return lo.value, hi.value
+
+    def value_and_gradient_host(self, ds, loss, coef, out_grad, gather_output=False):
+        """pml_value_and_gradient_allreduce: host vectors in and out; returns the objective value.  With
+        gather_output=False only out_grad[lo:hi] (this rank's slice) is written."""
+        value = ctypes.c_double()
+        check(load().pml_value_and_gradient_allreduce(ds._h, self._h, loss, _ptr(_np(coef, np.float64, self.d, "coef")),
+                                                      ctypes.byref(value), _ptr(out_grad), 1 if gather_output else 0))
+        return value.value
+
+    def hessian_vector_host(self, ds, loss, coef, v, out_hv, tag=0, gather_output=False):
+        check(load().pml_hessian_vector_allreduce(ds._h, self._h, loss,
+                                                  None if coef is None else _ptr(_np(coef, np.float64, self.d, "coef")), tag,
+                                                  _ptr(_np(v, np.float64, self.d, "v")), _ptr(out_hv),
+                                                  1 if gather_output else 0))
+
+    def status(self):
+        out = ctypes.c_int()
+        check(load().pml_peer_status(self._h, ctypes.byref(out)))
+        return out.value
 
     def merge(self, ds, loss):
         """Merge + getVector of whatever the ranks left in their raw buffers (raw_ptr)."""

@@ -509,6 +509,13 @@ int pml_ctx_synchronize(pml_ctx *ctx)
     if (!ctx) return fail(PML_EINVAL, "null context");
     PML_CUDA(cudaSetDevice(ctx->device));
     PML_CUDA(cudaStreamSynchronize(ctx->stream));
+    {
+        // An exchange over peer memory that gave up waiting for another rank has poisoned its result with NaN and
+        // raised its status word: the caller that reads results after this synchronize must hear about it.
+        std::lock_guard<std::mutex> lock(ctx->mu);
+        for (const int *st : ctx->peer_status)
+            if (*st != 0) return fail(PML_ECUDA, "a merge over peer memory timed out waiting for another rank");
+    }
     return PML_OK;
 }
 
@@ -1634,6 +1641,84 @@ int pml_hessian_vector_allreduce_dev(pml_dataset *ds, pml_peer *peer, int loss, 
     if (out_hv_dev && ds->d > 0)
         PML_CUDA(cudaMemcpyAsync(out_hv_dev, peer_result(peer), sizeof(double) * (size_t)ds->d, cudaMemcpyDeviceToDevice, s));
     return PML_OK;
+}
+
+
+// ---- host-buffer forms of the two exchanges (the shape the JNI natives bind: DistributedObjectiveFunction.scala:57-58,73)
+// Every rank is handed the same coefficient vector in host memory and uploads only ITS 1/N slice over its own PCIe
+// link; the slices are exchanged over NVLink (peer_gather_kernel), the evaluation and the merge run as in the
+// *_allreduce_dev forms, and every rank downloads its slice of the result (gather_output = 0: out_grad[lo, hi) is
+// written, [lo, hi) from pml_peer_slice -- ranks that share one host buffer assemble the full vector in it) or all of
+// it (gather_output = 1).  The objective value is returned on every rank.
+static int upload_slices(pml_dataset *ds, pml_peer *peer, const double *coef, const double *v, int *n_vec)
+{
+    cudaStream_t s = ds->ctx->stream;
+    const bool whole = peer->world == 1 || peer->mc_va != nullptr;  // no pairwise mappings: every rank uploads everything
+    int64_t lo = 0, hi = ds->d;
+    if (!whole) peer_slice(peer, &lo, &hi);
+    if (coef && hi > lo)
+        PML_CUDA(cudaMemcpyAsync(peer_vec(peer, 0) + lo, coef + lo, sizeof(double) * (size_t)(hi - lo), cudaMemcpyHostToDevice, s));
+    if (v && hi > lo)
+        PML_CUDA(cudaMemcpyAsync(peer_vec(peer, 1) + lo, v + lo, sizeof(double) * (size_t)(hi - lo), cudaMemcpyHostToDevice, s));
+    *n_vec = coef && v ? 2 : (v ? -2 : 1);
+    return PML_OK;
+}
+
+static int download_result(pml_dataset *ds, pml_peer *peer, double *out_value, double *out_vec, int gather_output)
+{
+    cudaStream_t s = ds->ctx->stream;
+    const double *res = peer_result(peer);
+    int64_t lo = 0, hi = ds->d;
+    if (!gather_output) peer_slice(peer, &lo, &hi);
+    if (out_vec && hi > lo)
+        PML_CUDA(cudaMemcpyAsync(out_vec + lo, res + lo, sizeof(double) * (size_t)(hi - lo), cudaMemcpyDeviceToHost, s));
+    if (out_value) PML_CUDA(cudaMemcpyAsync(ds->ctx->h_scalar, res + ds->d, sizeof(double), cudaMemcpyDeviceToHost, s));
+    PML_CUDA(cudaStreamSynchronize(s));
+    if (out_value) *out_value = ds->ctx->h_scalar[0];
+    if (*peer->h_status != 0)
+        return fail(PML_ECUDA, "the exchange over peer memory timed out waiting for another rank");
+    return PML_OK;
+}
+
+int pml_value_and_gradient_allreduce(pml_dataset *ds, pml_peer *peer, int loss, const double *coef, double *out_value,
+                                     double *out_grad, int gather_output)
+{
+    PML_TRY(check_ds(ds));
+    PML_TRY(check_peer(ds, peer));
+    if (!valid_loss(loss)) return fail(PML_EINVAL, "unknown loss");
+    if (!coef) return fail(PML_EINVAL, "null buffer");
+    Guard g(ds->ctx);
+    PML_CUDA(cudaSetDevice(ds->ctx->device));
+    cudaStream_t s = ds->ctx->stream;
+    const bool hinge = loss == PML_LOSS_SMOOTHED_HINGE;
+    int n_vec = 1;
+    PML_TRY(upload_slices(ds, peer, coef, nullptr, &n_vec));
+    PML_TRY(run(ds->ctx, PML_K_PEER, [&] { return launch_peer_gather(s, ds->ctx->sm_count, peer, n_vec); }));
+    PML_TRY(vg_raw(ds, loss, peer_vec(peer, 0), peer_raw(peer), true));
+    PML_TRY(run(ds->ctx, PML_K_PEER, [&] {
+        return launch_peer_merge(s, ds->ctx->sm_count, peer, hinge ? nullptr : ds->factors, hinge ? nullptr : ds->shifts);
+    }));
+    return download_result(ds, peer, out_value, out_grad, gather_output);
+}
+
+int pml_hessian_vector_allreduce(pml_dataset *ds, pml_peer *peer, int loss, const double *coef, uint64_t coef_tag,
+                                 const double *v, double *out_hv, int gather_output)
+{
+    PML_TRY(check_ds(ds));
+    PML_TRY(check_peer(ds, peer));
+    if (!valid_loss(loss)) return fail(PML_EINVAL, "unknown loss");
+    if (!v) return fail(PML_EINVAL, "null buffer");
+    Guard g(ds->ctx);
+    PML_CUDA(cudaSetDevice(ds->ctx->device));
+    cudaStream_t s = ds->ctx->stream;
+    const bool cached = coef_tag != 0 && ds->cache_valid && ds->cached_tag == coef_tag && ds->cached_loss == loss;
+    if (!cached && !coef) return fail(PML_EINVAL, "coefficients are required when no cached pass matches the tag");
+    int n_vec = 2;
+    PML_TRY(upload_slices(ds, peer, cached ? nullptr : coef, v, &n_vec));
+    PML_TRY(run(ds->ctx, PML_K_PEER, [&] { return launch_peer_gather(s, ds->ctx->sm_count, peer, n_vec); }));
+    PML_TRY(hv_raw(ds, loss, peer_vec(peer, 0), coef_tag, peer_vec(peer, 1), peer_raw(peer)));
+    PML_TRY(run(ds->ctx, PML_K_PEER, [&] { return launch_peer_merge(s, ds->ctx->sm_count, peer, ds->factors, ds->shifts); }));
+    return download_result(ds, peer, nullptr, out_hv, gather_output);
 }
 
 }  // extern "C"

@@ -226,6 +226,9 @@ namespace pml {
 int launch_peer_merge(cudaStream_t s, int sm_count, const pml_peer *peer, const double *factors, const double *shifts);
 double *peer_raw(const pml_peer *peer);
 double *peer_result(const pml_peer *peer);
+double *peer_vec(const pml_peer *peer, int which);
+void peer_slice(const pml_peer *peer, int64_t *lo, int64_t *hi);
+int launch_peer_gather(cudaStream_t s, int sm_count, const pml_peer *peer, int n_vec);
 size_t peer_slab_bytes(int64_t d, int world);
 }  // namespace pml
 
@@ -261,6 +264,7 @@ struct pml_ctx {
     // pinned staging for scalars, and for small coefficient / gradient vectors of host-buffer calls
     double *h_scalar = nullptr;
     double *h_stage = nullptr;  // 2 * (SMALL_IO_DIM + 2) doubles
+    std::vector<int *> peer_status;  // mapped host words of this context's peer handles: 1 = an exchange timed out
 };
 
 // a captured value+gradient sequence and what it was captured for

@@ -43,6 +43,11 @@ struct PeerHeader {
     unsigned int pushed;                 // CTAs of the running kernel that have pushed their share of the raw sums
     unsigned int pad2[29];
     double pref[PML_MAX_PEERS];          // pref[q] = rank q's prefactorSum of the running exchange
+    unsigned int gathered[PML_MAX_PEERS];  // gathered[q] = epoch_g: rank q's slice of the input vectors has arrived here
+    unsigned int pad3[32 - PML_MAX_PEERS];
+    unsigned int epoch_g;                // all-gathers completed
+    unsigned int pushed_g;               // CTAs of the running all-gather that have pushed their share
+    unsigned int pad4[30];
 };
 static_assert(sizeof(PeerHeader) <= PEER_HEADER_BYTES, "header does not fit");
 
@@ -80,15 +85,17 @@ __device__ __forceinline__ double2 ld_peer2(const double *p)
     return v;
 }
 
-__device__ __forceinline__ void wait_for(const unsigned int *flag, unsigned int epoch, int *status)
+// false = gave up: the flag never reached `epoch` (a rank that never arrived); the mapped host word tells the caller
+__device__ __forceinline__ bool wait_for(const unsigned int *flag, unsigned int epoch, int *status)
 {
     const long long t0 = clock64();
     while ((int)(ld_acquire_sys(flag) - epoch) < 0) {
         if (clock64() - t0 > PEER_TIMEOUT_CYCLES) {
             *status = 1;
-            break;
+            return false;
         }
     }
+    return true;
 }
 
 // raw and result are both padded to an even number of doubles: everything moves as 16-byte pairs
@@ -104,29 +111,45 @@ __device__ __forceinline__ double2 *slab_staging(char *slab, int64_t d)
     return reinterpret_cast<double2 *>(reinterpret_cast<double *>(slab + PEER_HEADER_BYTES) + 2 * slab_stride(d));
 }
 
-template <int WORLD>
-__global__ void __launch_bounds__(PEER_THREADS) peer_merge_kernel(const PeerParams p)
+// input vectors of the host-buffer entry points (coefficients, multiply vector): two regions of slab_stride(d)
+// doubles behind the staging rows; every rank uploads one slice of each and the all-gather kernel fills in the rest
+__host__ __device__ __forceinline__ int64_t staging_doubles(int64_t d, int world)
 {
-    __shared__ int is_last;
-    char *my_slab = p.slab[p.rank];
+    const int64_t per = ((d + 2) / 2 + world - 1) / world;
+    return 2 * per * world;
+}
+__device__ __forceinline__ double *slab_vec(char *slab, int64_t d, int world, int which)
+{
+    return reinterpret_cast<double *>(slab + PEER_HEADER_BYTES) + 2 * slab_stride(d) + staging_doubles(d, world) +
+           (int64_t)which * slab_stride(d);
+}
+
+// The body of the exchange, for rank `rank` as CTA `bid` of `nblk`: the kernel proper passes its own rank and
+// grid; the single-device emulation (pml_peer_emulate) runs all ranks' CTAs in one cooperative launch.
+template <int WORLD>
+__device__ __forceinline__ void peer_merge_body(const PeerParams &p, const int rank, const int bid, const int nblk)
+{
+    __shared__ int is_last, gave_up;
+    if (threadIdx.x == 0) gave_up = 0;
+    char *my_slab = p.slab[rank];
     PeerHeader *mine = reinterpret_cast<PeerHeader *>(my_slab);
     const unsigned int epoch = mine->epoch + 1;
     const int64_t d = p.d;
     // elements [0, d] (slot d is the value) as 16-byte pairs; the last pair may take the prefactor slot d+1 along
     const int64_t n_pairs = (d + 2) / 2;
     const int64_t per = (n_pairs + WORLD - 1) / WORLD;
-    const int64_t T = (int64_t)gridDim.x * PEER_THREADS;
-    const int64_t gtid = (int64_t)blockIdx.x * PEER_THREADS + threadIdx.x;
+    const int64_t T = (int64_t)nblk * PEER_THREADS;
+    const int64_t gtid = (int64_t)bid * PEER_THREADS + threadIdx.x;
     const double *raw = slab_raw(my_slab);
     const double2 *raw2 = reinterpret_cast<const double2 *>(raw);
 
     // ---- 1. push: slice q of this rank's raw sums goes to row [rank] of rank q's staging area ----
 #pragma unroll
     for (int q = 0; q < WORLD; ++q) {
-        if (q == p.rank) continue;
+        if (q == rank) continue;
         const int64_t lo_q = per * q;
         const int64_t hi_q = lo_q + per < n_pairs ? lo_q + per : n_pairs;
-        double2 *dst = slab_staging(p.slab[q], d) + (int64_t)p.rank * per - lo_q;
+        double2 *dst = slab_staging(p.slab[q], d) + (int64_t)rank * per - lo_q;
         int64_t k = lo_q + gtid;
         for (; k + 3 * T < hi_q; k += 4 * T) {  // four independent copies in flight per thread
             const double2 a = raw2[k], b = raw2[k + T], c = raw2[k + 2 * T], e = raw2[k + 3 * T];
@@ -137,29 +160,31 @@ __global__ void __launch_bounds__(PEER_THREADS) peer_merge_kernel(const PeerPara
         }
         for (; k < hi_q; k += T) dst[k] = raw2[k];
     }
-    if (blockIdx.x == 0 && threadIdx.x < WORLD)
-        reinterpret_cast<PeerHeader *>(p.slab[threadIdx.x])->pref[p.rank] = raw[d + 1];
+    if (bid == 0 && threadIdx.x < WORLD)
+        reinterpret_cast<PeerHeader *>(p.slab[threadIdx.x])->pref[rank] = raw[d + 1];
     __syncthreads();  // the CTA's stores happen-before thread 0's fence, which is cumulative
     if (threadIdx.x == 0) {
         __threadfence_system();
-        is_last = atomicAdd(&mine->pushed, 1u) == gridDim.x - 1;
+        is_last = atomicAdd(&mine->pushed, 1u) == nblk - 1;
     }
     __syncthreads();
     if (is_last && threadIdx.x < WORLD) {  // every CTA of this rank has pushed: tell everyone
         __threadfence_system();
         if (threadIdx.x == 0) mine->pushed = 0;
-        st_release_sys(&reinterpret_cast<PeerHeader *>(p.slab[threadIdx.x])->ready[p.rank], epoch);
+        st_release_sys(&reinterpret_cast<PeerHeader *>(p.slab[threadIdx.x])->ready[rank], epoch);
     }
 
     // ---- 2. wait for everyone's pushes (all CTAs are resident: the grid never exceeds the SM count) ----
-    if (threadIdx.x < WORLD) wait_for(&mine->ready[threadIdx.x], epoch, p.status);
+    if (threadIdx.x < WORLD && !wait_for(&mine->ready[threadIdx.x], epoch, p.status)) gave_up = 1;
     __syncthreads();
+    // a rank that never arrived: the sums below would be partial -- hand out NaN instead of a plausible number
+    const bool poisoned = gave_up != 0;
 
     // ---- 3. this rank's slice: add the staged rows in rank order, getVector, store to every rank ----
     double P = 0.0;
 #pragma unroll
-    for (int q = 0; q < WORLD; ++q) P += q == p.rank ? raw[d + 1] : ld_peer(&mine->pref[q]);
-    const int64_t lo = per * p.rank;
+    for (int q = 0; q < WORLD; ++q) P += q == rank ? raw[d + 1] : ld_peer(&mine->pref[q]);
+    const int64_t lo = per * rank;
     const int64_t hi = lo + per < n_pairs ? lo + per : n_pairs;
     const double2 *staged = slab_staging(my_slab, d) - lo;
     for (int64_t k = lo + gtid; k < hi; k += T) {
@@ -167,7 +192,7 @@ __global__ void __launch_bounds__(PEER_THREADS) peer_merge_kernel(const PeerPara
         double2 part[WORLD];
 #pragma unroll
         for (int q = 0; q < WORLD; ++q)
-            part[q] = q == p.rank ? raw2[k] : ld_peer2(reinterpret_cast<const double *>(staged + (int64_t)q * per + k));
+            part[q] = q == rank ? raw2[k] : ld_peer2(reinterpret_cast<const double *>(staged + (int64_t)q * per + k));
         double2 v = make_double2(0.0, 0.0);
 #pragma unroll
         for (int q = 0; q < WORLD; ++q) {
@@ -182,6 +207,7 @@ __global__ void __launch_bounds__(PEER_THREADS) peer_merge_kernel(const PeerPara
             if (p.shifts) v.y = __dsub_rn(v.y, __dmul_rn(p.shifts[i + 1], P));
             if (p.factors) v.y = __dmul_rn(v.y, p.factors[i + 1]);
         }
+        if (poisoned) v.x = v.y = __longlong_as_double(0x7ff8000000000000ll);
 #pragma unroll
         for (int q = 0; q < WORLD; ++q) *reinterpret_cast<double2 *>(slab_result(p.slab[q], d) + i) = v;
     }
@@ -190,13 +216,13 @@ __global__ void __launch_bounds__(PEER_THREADS) peer_merge_kernel(const PeerPara
     __syncthreads();
     if (threadIdx.x == 0) {
         __threadfence_system();
-        is_last = atomicAdd(&mine->arrived, 1u) == gridDim.x - 1;
+        is_last = atomicAdd(&mine->arrived, 1u) == nblk - 1;
     }
     __syncthreads();
     if (!is_last) return;
     __threadfence_system();
     if (threadIdx.x < WORLD)
-        st_release_sys(&reinterpret_cast<PeerHeader *>(p.slab[threadIdx.x])->stored[p.rank], epoch);
+        st_release_sys(&reinterpret_cast<PeerHeader *>(p.slab[threadIdx.x])->stored[rank], epoch);
     if (threadIdx.x < WORLD) wait_for(&mine->stored[threadIdx.x], epoch, p.status);
     __syncthreads();
     if (threadIdx.x == 0) {
@@ -204,6 +230,100 @@ __global__ void __launch_bounds__(PEER_THREADS) peer_merge_kernel(const PeerPara
         mine->epoch = epoch;
     }
 }
+
+template <int WORLD>
+__global__ void __launch_bounds__(PEER_THREADS) peer_merge_kernel(const PeerParams p)
+{
+    peer_merge_body<WORLD>(p, p.rank, (int)blockIdx.x, (int)gridDim.x);
+}
+
+// All ranks of a WORLD-rank exchange as ONE cooperative launch on one device (every CTA resident, so the flag waits
+// between "ranks" cannot starve): CTAs [r * per_rank, (r + 1) * per_rank) play rank r.  For tests and for checking a
+// build on a box with fewer GPUs than ranks -- waiting kernels of separate launches must not share a GPU.
+template <int WORLD>
+__global__ void __launch_bounds__(PEER_THREADS) peer_merge_emulated_kernel(const PeerParams p, const int per_rank)
+{
+    peer_merge_body<WORLD>(p, (int)blockIdx.x / per_rank, (int)blockIdx.x % per_rank, per_rank);
+}
+
+// ---- all-gather of the input vectors (host-buffer entry points) ------------------------------------------------
+// Every rank has uploaded ITS slice of the coefficients (and of the multiply vector) from host memory over its own
+// PCIe link; this kernel stores that slice into every peer's copy (posted NVLink stores) and waits until every
+// peer's slice has arrived here: Spark's sc.broadcast (DistributedObjectiveFunction.scala:57-58) with the upload
+// spread over all links instead of funnelled through one.
+struct GatherParams {
+    char *slab[PML_MAX_PEERS];
+    int rank, world;
+    int64_t d;
+    int n_vec;    // 1: region 0 only; 2: regions 0 and 1; -2: region 1 only (cached Hessian-vector: v without coefficients)
+    int *status;
+};
+
+__host__ __device__ __forceinline__ void vec_slice(int64_t d, int world, int rank, int64_t *lo, int64_t *hi)
+{
+    const int64_t n_pairs = (d + 1) / 2;
+    const int64_t per = (n_pairs + world - 1) / world;
+    int64_t a = 2 * per * rank, b = 2 * per * (rank + 1);
+    *lo = a < d ? a : d;
+    *hi = b < d ? b : d;
+}
+
+template <int WORLD>
+__device__ __forceinline__ void peer_gather_body(const GatherParams &p, const int rank, const int bid, const int nblk)
+{
+    __shared__ int is_last;
+    char *my_slab = p.slab[rank];
+    PeerHeader *mine = reinterpret_cast<PeerHeader *>(my_slab);
+    const unsigned int epoch = mine->epoch_g + 1;
+    int64_t lo, hi;
+    vec_slice(p.d, WORLD, rank, &lo, &hi);
+    const int64_t T = (int64_t)nblk * PEER_THREADS;
+    const int64_t gtid = (int64_t)bid * PEER_THREADS + threadIdx.x;
+    const int first = p.n_vec == -2 ? 1 : 0, last = p.n_vec == 1 ? 0 : 1;
+    for (int which = first; which <= last; ++which) {
+        const double *src = slab_vec(my_slab, p.d, WORLD, which);
+        // slices start at even elements: 16-byte pairs, a trailing odd element on its own
+        const int64_t pairs = (hi - lo) / 2;
+#pragma unroll
+        for (int q = 0; q < WORLD; ++q) {
+            if (q == rank) continue;
+            double *dst = slab_vec(p.slab[q], p.d, WORLD, which);
+            const double2 *s2 = reinterpret_cast<const double2 *>(src + lo);
+            double2 *d2 = reinterpret_cast<double2 *>(dst + lo);
+            for (int64_t k = gtid; k < pairs; k += T) d2[k] = s2[k];
+            if (gtid == 0 && ((hi - lo) & 1)) dst[hi - 1] = src[hi - 1];
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence_system();
+        is_last = atomicAdd(&mine->pushed_g, 1u) == (unsigned int)(nblk - 1);
+    }
+    __syncthreads();
+    if (is_last && threadIdx.x < WORLD) {
+        __threadfence_system();
+        if (threadIdx.x == 0) mine->pushed_g = 0;
+        st_release_sys(&reinterpret_cast<PeerHeader *>(p.slab[threadIdx.x])->gathered[rank], epoch);
+    }
+    if (!is_last) return;
+    // the last CTA waits for everyone's slices: when the kernel ends, this rank's copies are complete
+    if (threadIdx.x < WORLD) wait_for(&mine->gathered[threadIdx.x], epoch, p.status);
+    __syncthreads();
+    if (threadIdx.x == 0) mine->epoch_g = epoch;
+}
+
+template <int WORLD>
+__global__ void __launch_bounds__(PEER_THREADS) peer_gather_kernel(const GatherParams p)
+{
+    peer_gather_body<WORLD>(p, p.rank, (int)blockIdx.x, (int)gridDim.x);
+}
+
+template <int WORLD>
+__global__ void __launch_bounds__(PEER_THREADS) peer_gather_emulated_kernel(const GatherParams p, const int per_rank)
+{
+    peer_gather_body<WORLD>(p, (int)blockIdx.x / per_rank, (int)blockIdx.x % per_rank, per_rank);
+}
+
 
 
 // ---- the same exchange through an NVSwitch multicast object (NVLS) --------------------------------------------
@@ -347,8 +467,109 @@ int launch_peer_merge(cudaStream_t s, int sm_count, const pml_peer *peer, const 
 
 size_t peer_slab_bytes(int64_t d, int world)
 {
-    const int64_t per = ((d + 2) / 2 + world - 1) / world;
-    return PEER_HEADER_BYTES + sizeof(double) * (size_t)(2 * slab_stride(d) + 2 * per * world);
+    return PEER_HEADER_BYTES + sizeof(double) * (size_t)(2 * slab_stride(d) + staging_doubles(d, world) + 2 * slab_stride(d));
+}
+
+// this rank's copy of input vector `which` (0 = coefficients, 1 = multiply vector) inside its slab
+double *peer_vec(const pml_peer *peer, int which)
+{
+    char *base = static_cast<char *>(peer->mc_va != nullptr ? peer->uc_va : peer->slab);
+    const int world = peer->mc_va != nullptr ? 1 : peer->world;   // the multicast slab is laid out for one staging row
+    return reinterpret_cast<double *>(base + PEER_HEADER_BYTES) + 2 * slab_stride(peer->d) + staging_doubles(peer->d, world) +
+           (int64_t)which * slab_stride(peer->d);
+}
+
+void peer_slice(const pml_peer *peer, int64_t *lo, int64_t *hi) { vec_slice(peer->d, peer->world, peer->rank, lo, hi); }
+
+// n_vec as in GatherParams.  With the multicast transport the slabs are not mapped pairwise: the caller uploads the
+// whole vector instead (returns 0 launches).
+int launch_peer_gather(cudaStream_t s, int sm_count, const pml_peer *peer, int n_vec)
+{
+    if (peer->world == 1 || peer->mc_va != nullptr) return 0;
+    GatherParams g;
+    std::memset(&g, 0, sizeof(g));
+    for (int q = 0; q < peer->world; ++q) g.slab[q] = static_cast<char *>(peer->peer_slab[q]);
+    g.rank = peer->rank;
+    g.world = peer->world;
+    g.d = peer->d;
+    g.n_vec = n_vec;
+    g.status = peer->d_status;
+    int64_t lo, hi;
+    peer_slice(peer, &lo, &hi);
+    int64_t grid = ((hi - lo) / 2 + PEER_THREADS - 1) / PEER_THREADS;
+    if (grid > sm_count / 2) grid = sm_count / 2;
+    if (grid < 1) grid = 1;
+    switch (peer->world) {
+    case 2: peer_gather_kernel<2><<<(int)grid, PEER_THREADS, 0, s>>>(g); break;
+    case 3: peer_gather_kernel<3><<<(int)grid, PEER_THREADS, 0, s>>>(g); break;
+    case 4: peer_gather_kernel<4><<<(int)grid, PEER_THREADS, 0, s>>>(g); break;
+    case 5: peer_gather_kernel<5><<<(int)grid, PEER_THREADS, 0, s>>>(g); break;
+    case 6: peer_gather_kernel<6><<<(int)grid, PEER_THREADS, 0, s>>>(g); break;
+    case 7: peer_gather_kernel<7><<<(int)grid, PEER_THREADS, 0, s>>>(g); break;
+    case 8: peer_gather_kernel<8><<<(int)grid, PEER_THREADS, 0, s>>>(g); break;
+    default: return -1;
+    }
+    return cudaGetLastError() == cudaSuccess ? 1 : -1;
+}
+
+// The whole exchange of WORLD ranks on ONE device, as cooperative launches: all-gather of `n_vec` input vectors
+// (0 = skip), then merge + getVector.  slabs[q] = rank q's slab (peer_slab_bytes(d, world) each, zeroed once).
+template <int WORLD>
+static int emulate_world(cudaStream_t s, int sm_count, char *const *slabs, int64_t d, int n_vec, const double *factors,
+                         const double *shifts, int *status)
+{
+    const int per_rank = sm_count / WORLD < 4 ? (sm_count / WORLD < 1 ? 1 : sm_count / WORLD) : 4;
+    if (n_vec != 0) {
+        GatherParams g;
+        std::memset(&g, 0, sizeof(g));
+        for (int q = 0; q < WORLD; ++q) g.slab[q] = slabs[q];
+        g.world = WORLD;
+        g.d = d;
+        g.n_vec = n_vec;
+        g.status = status;
+        int pr = per_rank;
+        void *args[] = { &g, &pr };
+        if (cudaLaunchCooperativeKernel((const void *)peer_gather_emulated_kernel<WORLD>, dim3(per_rank * WORLD),
+                                        dim3(PEER_THREADS), args, 0, s) != cudaSuccess)
+            return -1;
+    }
+    PeerParams p;
+    std::memset(&p, 0, sizeof(p));
+    for (int q = 0; q < WORLD; ++q) p.slab[q] = slabs[q];
+    p.world = WORLD;
+    p.d = d;
+    p.factors = factors;
+    p.shifts = shifts;
+    p.status = status;
+    int pr = per_rank;
+    void *args[] = { &p, &pr };
+    if (cudaLaunchCooperativeKernel((const void *)peer_merge_emulated_kernel<WORLD>, dim3(per_rank * WORLD),
+                                    dim3(PEER_THREADS), args, 0, s) != cudaSuccess)
+        return -1;
+    return 1;
+}
+
+int launch_peer_emulation(cudaStream_t s, int sm_count, int world, char *const *slabs, int64_t d, int n_vec,
+                          const double *factors, const double *shifts, int *status)
+{
+    switch (world) {
+    case 1: return emulate_world<1>(s, sm_count, slabs, d, n_vec, factors, shifts, status);
+    case 2: return emulate_world<2>(s, sm_count, slabs, d, n_vec, factors, shifts, status);
+    case 3: return emulate_world<3>(s, sm_count, slabs, d, n_vec, factors, shifts, status);
+    case 4: return emulate_world<4>(s, sm_count, slabs, d, n_vec, factors, shifts, status);
+    case 5: return emulate_world<5>(s, sm_count, slabs, d, n_vec, factors, shifts, status);
+    case 6: return emulate_world<6>(s, sm_count, slabs, d, n_vec, factors, shifts, status);
+    case 7: return emulate_world<7>(s, sm_count, slabs, d, n_vec, factors, shifts, status);
+    case 8: return emulate_world<8>(s, sm_count, slabs, d, n_vec, factors, shifts, status);
+    default: return -1;
+    }
+}
+
+size_t peer_offset_raw() { return PEER_HEADER_BYTES; }
+size_t peer_offset_result(int64_t d) { return PEER_HEADER_BYTES + sizeof(double) * (size_t)slab_stride(d); }
+size_t peer_offset_vec(int64_t d, int world, int which)
+{
+    return PEER_HEADER_BYTES + sizeof(double) * (size_t)(2 * slab_stride(d) + staging_doubles(d, world) + which * slab_stride(d));
 }
 double *peer_raw(const pml_peer *peer)
 {
@@ -516,8 +737,109 @@ int pml_peer_create(pml_ctx *ctx, int rank, int world, int32_t d, pml_peer **out
     }
     p->peer_slab[rank] = p->slab;
     p->connected = world == 1;
+    {
+        std::lock_guard<std::mutex> lock(ctx->mu);
+        ctx->peer_status.push_back(p->h_status);   // pml_ctx_synchronize reports a timed-out exchange
+    }
     *out = p;
     return PML_OK;
+}
+
+int pml_peer_status(pml_peer *peer, int *out)
+{
+    if (peer == nullptr || out == nullptr) return fail(PML_EINVAL, "null argument");
+    *out = *peer->h_status;
+    return PML_OK;
+}
+
+int pml_peer_slice(pml_peer *peer, int64_t *out_lo, int64_t *out_hi)
+{
+    if (peer == nullptr || out_lo == nullptr || out_hi == nullptr) return fail(PML_EINVAL, "null argument");
+    peer_slice(peer, out_lo, out_hi);
+    return PML_OK;
+}
+
+int pml_peer_emulate(pml_ctx *ctx, int world, int32_t d, int repeats, const double *raw, const double *factors,
+                     const double *shifts, double *out_result, const double *vec_in, double *vec_out)
+{
+    if (ctx == nullptr || raw == nullptr || out_result == nullptr) return fail(PML_EINVAL, "null argument");
+    if (world < 1 || world > PML_MAX_PEERS) return fail(PML_EINVAL, "world size must be between 1 and " + std::to_string(PML_MAX_PEERS));
+    if (d < 0 || repeats < 1) return fail(PML_EINVAL, "bad dimension or repeat count");
+    if ((vec_in == nullptr) != (vec_out == nullptr)) return fail(PML_EINVAL, "vec_in and vec_out go together");
+    std::lock_guard<std::mutex> lock(ctx->mu);
+    PML_CUDA(cudaSetDevice(ctx->device));
+    int coop = 0;
+    PML_CUDA(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, ctx->device));
+    if (!coop) return fail(PML_ECUDA, "the device does not support cooperative launches");
+    cudaStream_t s = ctx->stream;
+    const size_t bytes = peer_slab_bytes(d, world);
+    char *slabs[PML_MAX_PEERS] = {};
+    double *f_dev = nullptr, *s_dev = nullptr;
+    int *h_status = nullptr, *d_status = nullptr;
+    int rc = PML_OK;
+    auto cleanup = [&] {
+        for (int q = 0; q < world; ++q)
+            if (slabs[q]) cudaFree(slabs[q]);
+        if (f_dev) cudaFree(f_dev);
+        if (s_dev) cudaFree(s_dev);
+        if (h_status) cudaFreeHost(h_status);
+    };
+#define EMU_CUDA(expr)                                                                                     \
+    do {                                                                                                   \
+        cudaError_t _e = (expr);                                                                           \
+        if (_e != cudaSuccess) {                                                                           \
+            cleanup();                                                                                     \
+            return fail(PML_ECUDA, std::string(#expr) + ": " + cudaGetErrorString(_e));                    \
+        }                                                                                                  \
+    } while (0)
+    EMU_CUDA(cudaHostAlloc(reinterpret_cast<void **>(&h_status), sizeof(int), cudaHostAllocMapped));
+    *h_status = 0;
+    EMU_CUDA(cudaHostGetDevicePointer(reinterpret_cast<void **>(&d_status), h_status, 0));
+    for (int q = 0; q < world; ++q) {
+        EMU_CUDA(cudaMalloc(&slabs[q], bytes));
+        EMU_CUDA(cudaMemsetAsync(slabs[q], 0, bytes, s));
+    }
+    if (factors) {
+        EMU_CUDA(cudaMalloc(&f_dev, sizeof(double) * (size_t)(d + 1)));
+        EMU_CUDA(cudaMemcpyAsync(f_dev, factors, sizeof(double) * (size_t)d, cudaMemcpyHostToDevice, s));
+    }
+    if (shifts) {
+        EMU_CUDA(cudaMalloc(&s_dev, sizeof(double) * (size_t)(d + 1)));
+        EMU_CUDA(cudaMemcpyAsync(s_dev, shifts, sizeof(double) * (size_t)d, cudaMemcpyHostToDevice, s));
+    }
+    for (int rep = 0; rep < repeats && rc == PML_OK; ++rep) {
+        for (int q = 0; q < world; ++q) {
+            EMU_CUDA(cudaMemcpyAsync(slabs[q] + peer_offset_raw(), raw + (size_t)q * (size_t)(d + 2),
+                                     sizeof(double) * (size_t)(d + 2), cudaMemcpyHostToDevice, s));
+            if (vec_in) {  // every rank uploads ITS slice only: the rest of its copy must come from the all-gather
+                int64_t lo, hi;
+                vec_slice(d, world, q, &lo, &hi);
+                EMU_CUDA(cudaMemsetAsync(slabs[q] + peer_offset_vec(d, world, 0), 0xff, sizeof(double) * (size_t)d, s));
+                if (hi > lo)
+                    EMU_CUDA(cudaMemcpyAsync(slabs[q] + peer_offset_vec(d, world, 0) + sizeof(double) * (size_t)lo,
+                                             vec_in + (size_t)q * (size_t)d + lo, sizeof(double) * (size_t)(hi - lo),
+                                             cudaMemcpyHostToDevice, s));
+            }
+        }
+        if (launch_peer_emulation(s, ctx->sm_count, world, slabs, d, vec_in ? 1 : 0, f_dev, s_dev, d_status) < 0) {
+            cudaError_t e = cudaGetLastError();
+            cleanup();
+            return fail(PML_ECUDA, std::string("cooperative launch failed: ") + cudaGetErrorString(e));
+        }
+        EMU_CUDA(cudaStreamSynchronize(s));
+        if (*h_status != 0) rc = fail(PML_ECUDA, "the emulated exchange timed out");
+    }
+    for (int q = 0; q < world && rc == PML_OK; ++q) {
+        EMU_CUDA(cudaMemcpyAsync(out_result + (size_t)q * (size_t)(d + 1), slabs[q] + peer_offset_result(d),
+                                 sizeof(double) * (size_t)(d + 1), cudaMemcpyDeviceToHost, s));
+        if (vec_out)
+            EMU_CUDA(cudaMemcpyAsync(vec_out + (size_t)q * (size_t)d, slabs[q] + peer_offset_vec(d, world, 0),
+                                     sizeof(double) * (size_t)d, cudaMemcpyDeviceToHost, s));
+    }
+    EMU_CUDA(cudaStreamSynchronize(s));
+#undef EMU_CUDA
+    cleanup();
+    return rc;
 }
 
 int pml_peer_handle(pml_peer *peer, void *out_handle)
@@ -676,6 +998,12 @@ int pml_peer_destroy(pml_peer *peer)
         cudaStreamSynchronize(peer->ctx->stream);
     }
     mc_teardown(peer);
+    if (peer->ctx && peer->h_status) {
+        std::lock_guard<std::mutex> lock(peer->ctx->mu);
+        auto &v = peer->ctx->peer_status;
+        for (size_t i = 0; i < v.size(); ++i)
+            if (v[i] == peer->h_status) { v.erase(v.begin() + (long)i); break; }
+    }
     for (int q = 0; q < PML_MAX_PEERS; ++q)
         if (peer->opened[q] && peer->peer_slab[q]) cudaIpcCloseMemHandle(peer->peer_slab[q]);
     if (peer->slab) cudaFree(peer->slab);

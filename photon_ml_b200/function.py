@@ -52,6 +52,28 @@ def NoNormalization():
     return NormalizationContext(None, None, None)
 
 
+import itertools
+
+# Hessian-vector cache tags: one process-wide counter, so that two objectives evaluating the same data set can
+# never present the same tag for different coefficients (a data set remembers only the last tag it saw)
+_TAGS = itertools.count(1)
+
+
+def _apply_normalization(data, ctx):
+    """The reference passes the NormalizationContext on every call; the packed data set keeps what was set last.  The
+    record of what is set lives ON THE DATA SET (not in the objective, not keyed by id()): several objectives may
+    take turns on one data set, and a new data set must never inherit another one's record."""
+    empty = ctx.factors is None and ctx.shifts is None
+    applied = getattr(data, "_applied_norm", None)
+    if empty:
+        if applied is not None:
+            data.set_normalization(None, None, None)     # clear whatever an earlier caller left behind
+        return
+    if applied is not ctx:
+        data.set_normalization(ctx.factors, ctx.shifts, ctx.interceptId)
+        data._applied_norm = ctx
+
+
 class _NativeObjective:
     """value / gradient / calculate (+ hessianVector / hessianDiagonal) on a packed Dataset."""
 
@@ -59,15 +81,10 @@ class _NativeObjective:
 
     def __init__(self, loss):
         self.loss = loss
-        self._norm_applied = {}   # dataset id -> NormalizationContext currently set on it
-        self._next_tag = 1
         self._tags = {}
 
-    # the reference passes the context on every call; the packed data set keeps it between calls
     def _apply(self, data, ctx):
-        if self._norm_applied.get(id(data)) is not ctx:
-            data.set_normalization(ctx.factors, ctx.shifts, ctx.interceptId)
-            self._norm_applied[id(data)] = ctx
+        _apply_normalization(data, ctx)
 
     def domainDimension(self, data):
         return data.d
@@ -89,8 +106,7 @@ class _NativeObjective:
         # the coefficient vector's identity is the cache tag (TRON's CG loop keeps passing the same one)
         key = id(coefficients)
         if self._tags.get("key") != key or not np.array_equal(self._tags.get("copy"), coefficients):
-            self._tags = {"key": key, "copy": np.array(coefficients, copy=True), "tag": self._next_tag}
-            self._next_tag += 1
+            self._tags = {"key": key, "copy": np.array(coefficients, copy=True), "tag": next(_TAGS)}
         return data.hessian_vector(self.loss, coefficients, multiplyVector, tag=self._tags["tag"])
 
     def hessianDiagonal(self, data, coefficients):
@@ -181,14 +197,13 @@ class DeviceGLMLossFunction:
         self.ctx, self.loss = ctx, loss
         self.l2RegWeight = None if l2RegWeight is None else float(l2RegWeight)
         self._ext = torch.cuda.ExternalStream(ctx.stream, device=torch.device("cuda", ctx.device))
-        self._tag, self._tag_src = 0, None
+        self._tag, self._tag_src, self._tag_version = 0, None, -1
 
     def stream(self):
         return self._torch.cuda.stream(self._ext)
 
     def _apply(self, data, ctx):
-        if ctx.factors is not None or ctx.shifts is not None:
-            data.set_normalization(ctx.factors, ctx.shifts, ctx.interceptId)
+        _apply_normalization(data, ctx)
 
     def calculate(self, data, coefficients, normalizationContext, want_gradient=True):
         torch = self._torch
@@ -207,9 +222,11 @@ class DeviceGLMLossFunction:
     def hessianVector(self, data, coefficients, multiplyVector, normalizationContext):
         torch = self._torch
         self._apply(data, normalizationContext)
-        if self._tag_src is not coefficients:     # TRON passes the same tensor object for a whole CG loop
-            self._tag_src = coefficients
-            self._tag += 1
+        # TRON passes the same tensor object for a whole CG loop; a tensor updated in place (its version counter
+        # moves) is a new coefficient vector
+        if self._tag_src is not coefficients or self._tag_version != coefficients._version:
+            self._tag_src, self._tag_version = coefficients, coefficients._version
+            self._tag = next(_TAGS)
         hv = torch.empty_like(coefficients)
         data.hessian_vector_dev(self.loss, coefficients.data_ptr(), multiplyVector.data_ptr(), hv.data_ptr(), tag=self._tag)
         if self.l2RegWeight is not None:

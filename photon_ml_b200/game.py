@@ -106,8 +106,9 @@ class CoordinateDescent:
     def _to_global(self, coord, local_scores):
         if coord.row_map is None:
             return local_scores
-        out = self.torch.empty(self.n, dtype=self.torch.float64, device=self.device)
-        out[coord.row_map] = local_scores          # every global row belongs to exactly one local row
+        # rows the coordinate does not cover (dropped by its active-data bounds) score 0, as in the reference
+        out = self.torch.zeros(self.n, dtype=self.torch.float64, device=self.device)
+        out[coord.row_map] = local_scores
         return out
 
     def run(self):
