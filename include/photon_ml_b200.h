@@ -374,7 +374,11 @@ int pml_peer_emulate(pml_ctx *ctx, int world, int32_t d, int repeats, const doub
  *    stream, or otherwise order them.  The array keeps the previous call's contents; the call
  *    clears the counter itself, nothing needs resetting by the caller.
  *  - the first call on each device also looks up the array's device address
- *    (cudaGetSymbolAddress); make that first call before starting any stream capture. */
+ *    (cudaGetSymbolAddress), which may load the library's device code on that GPU -- the one
+ *    moment the CUDA runtime itself may allocate and synchronise.  Make that first call once per
+ *    device at start-up: before starting any stream capture, and OUTSIDE any
+ *    GetPrimitiveArrayCritical region or other section in which allocation is forbidden.
+ *  - the calling thread's current CUDA device is the same after the call as before it. */
 int pml_value_noalloc_dev(int device, void *stream, int64_t n, int32_t d,
                           const int64_t *row_ptr_dev, const int32_t *col_idx_dev,
                           const void *values_dev, int values_dtype, const double *labels_dev,

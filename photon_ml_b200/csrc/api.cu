@@ -697,6 +697,10 @@ int pml_dataset_create_csr_dev(pml_ctx *ctx, int64_t n, int32_t d, const int64_t
     // flags in bit 31
     PML_TRY(build_row_side(s, n, nnz, ds->row_ptr, ds->col, chunk_entries, &ds->rs));
     ds->bytes += ds->rs.bytes;
+    // Inside every row the entries are dealt to the lanes so that the look-ups of the staged coefficient prefix
+    // spread over the shared-memory banks (pack.cu, bank_order_kernel); the order of a row's terms is free.
+    if (std::getenv("PML_NO_BANK_ORDER") == nullptr && std::getenv("PML_NO_BANK_ORDER_CSR") == nullptr)
+        PML_TRY(bank_order(s, nnz / SEG_CHUNK, ds->col, ds->val, dst_bytes, SEG_TABLE_BYTES / 8));
     PML_TRY(dev_alloc(&ds->za, (size_t)n, &ds->bytes));
     PML_TRY(dev_alloc(&ds->carry_row, (size_t)ds->rs.n_chunks + 1, &ds->bytes));
 

@@ -138,9 +138,10 @@ constexpr int TILE_MAX_ROWS = 25000;            // r slice + zero slot <= 200 KB
 constexpr int64_t TILE_MIN_ROWS_DEFAULT = 262144;  // below this r lives happily in L2: no tiling
 constexpr int64_t TILE_PARTIAL_BYTES = 128ll << 20; // cap on the (tile, column) partial matrix
 constexpr int64_t SUPER_ROWS_DEFAULT = 6ll << 20;   // rows per super block of the cold columns: 48 MB of r in the L2
-constexpr int64_t SUPER_MIN_ROWS_DEFAULT = 12ll << 20; // up to this many rows r (96 MB) is left in one piece
+constexpr int64_t SUPER_MIN_ROWS_DEFAULT = 6ll << 20;  // up to this many rows r (48 MB) is left in one piece
 int build_row_side(cudaStream_t s, int64_t n, int64_t nnz, const uint32_t *row_ptr, int32_t *col, int chunk_entries,
                    RowSide *out);
+int bank_order(cudaStream_t s, int64_t n_chunks, int32_t *idx, void *val, int value_bytes, int32_t n_table);
 int narrow_check(cudaStream_t s, const double *val, int64_t nnz, bool *all_exact);
 int ones_check(cudaStream_t s, const void *val, int value_bytes, int64_t nnz, bool *all_ones);
 int convert_values(cudaStream_t s, const void *src, int src_bytes, void *dst, int dst_bytes, int64_t nnz);

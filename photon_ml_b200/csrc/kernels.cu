@@ -705,7 +705,6 @@ seg_spmv_tiled_kernel(const SegParams p, const int32_t *__restrict__ tile_first_
     const VT *__restrict__ val = static_cast<const VT *>(p.val);
     const int32_t *__restrict__ idx = p.idx;
     const uint32_t hot_at = shared_window_address(hot);
-    const bool fast_uniform = p.n_hot != 0;   // (a switch for A/B measurements: PML_NO_UNIFORM_FAST=1)
     for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
         __syncthreads();  // every warp is done with the previous tile's slice
         const int64_t row0 = (int64_t)t * tile_rows;
@@ -720,18 +719,17 @@ seg_spmv_tiled_kernel(const SegParams p, const int32_t *__restrict__ tile_first_
             const int cn = c + WARPS;
             if (cn < c_end) seg_load_full<VT, ITEMS>(nxt, idx, val, (int64_t)cn * CHUNK + lane * ITEMS);
             if (cn + (PF_AHEAD - 1) * WARPS < c_end) seg_prefetch_l2<VT, ITEMS>(idx, val, cn + (PF_AHEAD - 1) * WARPS);
-            if (fast_uniform && p.chunk_lo[c] == p.chunk_lo[c + 1]) {
-                // No run starts in this chunk: all 256 entries continue one (tile, column) run -- the long runs of the
-                // hottest columns, about half of the region on Zipf data.  No flags, no scan, no run look-up: the
-                // products are added up per lane, one warp reduction, and the sum joins the run through carry[c] like
-                // any other chunk head (fixup_kernel).  The entries of such a chunk were dealt to the lanes at pack
-                // time so that the look-ups below are free of bank conflicts (pack.cu, bank_order_kernel).
+            if (cur.idx[0] & 0x40000000) {
+                // Marked at pack time (pack.cu, mark_uniform_kernel): no run starts in this chunk, all 256 entries
+                // continue one (tile, column) run -- the long runs of the hottest columns, about half of the region on
+                // Zipf data.  No flags, no scan, no run look-up: the products are added up per lane, one warp
+                // reduction, and the sum joins the run through carry[c] like any other chunk head (fixup_kernel).
                 double s = 0.0;
 #pragma unroll
                 for (int i = 0; i < ITEMS; ++i) {
                     double x = cur.value(i);
                     if (SQUARE) x *= x;
-                    const double g = lds_f64(hot_at + 8u * (uint32_t)cur.idx[i]);
+                    const double g = lds_f64(hot_at + 8u * (uint32_t)(cur.idx[i] & 0x3fffffff));
                     if constexpr (std::is_same<VT, One>::value) s += g;
                     else s += __dmul_rn(g, x);
                 }
@@ -761,8 +759,7 @@ int launch_seg_tiled(cudaStream_t s, int sm_count, int value_bytes, bool square,
     p.carry = t.carry;
     p.carry2 = nullptr;
     p.n_chunks = t.n_chunks;
-    const bool no_fast = std::getenv("PML_NO_UNIFORM_FAST") != nullptr;  // read per launch: tests flip it
-    p.n_hot = no_fast ? 0 : 0x7fffffff;  // (unused by LOOKUP_SHARED: every index is a shared-memory index)
+    p.n_hot = 0x7fffffff;  // every index is a shared-memory index
     const size_t smem = sizeof(double) * (size_t)(t.tile_rows + 1);
     const int grid = t.n_tiles < sm_count ? t.n_tiles : sm_count;
 #define PML_TILED(VT, SQ)                                                                                           \

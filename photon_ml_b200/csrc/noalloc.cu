@@ -147,6 +147,13 @@ extern "C" int pml_value_noalloc_dev(int device, void *stream, int64_t n, int32_
     if (!out_value_dev) return fail(PML_EINVAL, "null out_value_dev");
     if (n > 0 && (!row_ptr_dev || !labels_dev || !coef_dev)) return fail(PML_EINVAL, "null input array");
     if (device < 0 || device >= NA_MAX_DEVICES) return fail(PML_EINVAL, "device index out of range");
+    // the calling thread gets its current device back on every way out
+    struct DeviceRestore {
+        int prev = -1;
+        ~DeviceRestore() { if (prev >= 0) cudaSetDevice(prev); }
+    } restore;
+    int current = -1;
+    if (cudaGetDevice(&current) == cudaSuccess && current != device) restore.prev = current;
     PML_CUDA(cudaSetDevice(device));
     cudaStream_t s = static_cast<cudaStream_t>(stream);
 

@@ -272,36 +272,47 @@ __global__ void tile_scatter_kernel(int64_t nnz, const uint32_t *__restrict__ so
 // chunk to shared memory, lane 0 deals (4096 cheap steps, pack time only), the lanes write the new order back.
 // Run-start flags stay with their POSITIONS.  Deterministic: the result depends on the chunk's content only.
 template <typename VT>
-__global__ void __launch_bounds__(256) bank_order_kernel(int64_t n_chunks, int32_t *__restrict__ idx, VT *__restrict__ val)
+__global__ void __launch_bounds__(256) bank_order_kernel(int64_t n_chunks, int32_t *__restrict__ idx, VT *__restrict__ val,
+                                                         int32_t n_table)
 {
+    // n_table: indices below it are looked up in shared memory (the tiled region: all of them; the CSR stream: the
+    // staged prefix of the coefficient vector); the others go through the global path and fit anywhere.  Lanes that
+    // read the SAME word share one pass (a broadcast), so an index may join a group that already holds it.
     constexpr int WARPS = 8;
     __shared__ int32_t s_row[WARPS][256];
     __shared__ unsigned char s_perm[WARPS][256], s_sorted[WARPS][256];
+    __shared__ int32_t s_owner[WARPS][16][16];   // [group][bank pair] -> the index that occupies it, -1 = free
     __shared__ double s_val[WARPS][(sizeof(VT) > 1) ? 256 : 1];   // wide enough for float and double values
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     for (int64_t c = (int64_t)blockIdx.x * WARPS + warp; c < n_chunks; c += (int64_t)gridDim.x * WARPS) {
         int32_t *ci = idx + c * 256;
         for (int k = lane; k < 256; k += 32) {
             s_row[warp][k] = ci[k];
+            s_owner[warp][k >> 4][k & 15] = -1;
             if (val != nullptr) reinterpret_cast<VT *>(s_val[warp])[k] = val[c * 256 + k];
         }
         __syncwarp();
         if (lane == 0) {
-            unsigned short used[16];
-            for (int g = 0; g < 16; ++g) used[g] = 0;
             int a = 0;
             while (a < 256) {
                 int b = a + 1;
                 while (b < 256 && s_row[warp][b] >= 0) ++b;   // [a, b): one run's share of this chunk
-                int cnt[16], off[16];
-                for (int q = 0; q < 16; ++q) cnt[q] = 0;
-                for (int k = a; k < b; ++k) ++cnt[s_row[warp][k] & 15];
+                // classes 0..15: bank pair of a table index; class 16: global path, no constraint
+                int cnt[17], off[17];
+                for (int q = 0; q < 17; ++q) cnt[q] = 0;
+                for (int k = a; k < b; ++k) {
+                    const int32_t v = s_row[warp][k] & 0x3fffffff;
+                    ++cnt[v < n_table ? (v & 15) : 16];
+                }
                 int acc = a;
-                for (int q = 0; q < 16; ++q) { off[q] = acc; acc += cnt[q]; }
+                for (int q = 0; q < 17; ++q) { off[q] = acc; acc += cnt[q]; }
                 {
-                    int fill[16];
-                    for (int q = 0; q < 16; ++q) fill[q] = off[q];
-                    for (int k = a; k < b; ++k) s_sorted[warp][fill[s_row[warp][k] & 15]++] = (unsigned char)k;
+                    int fill[17];
+                    for (int q = 0; q < 17; ++q) fill[q] = off[q];
+                    for (int k = a; k < b; ++k) {
+                        const int32_t v = s_row[warp][k] & 0x3fffffff;
+                        s_sorted[warp][fill[v < n_table ? (v & 15) : 16]++] = (unsigned char)k;
+                    }
                 }
                 for (int pos = a; pos < b; ++pos) {
                     const int g = (pos >> 7) * 8 + (pos & 7);
@@ -309,11 +320,15 @@ __global__ void __launch_bounds__(256) bank_order_kernel(int64_t n_chunks, int32
                     for (int q = 0; q < 16; ++q) {
                         if (cnt[q] == 0) continue;
                         if (best_any < 0 || cnt[q] > cnt[best_any]) best_any = q;
-                        if (!((used[g] >> q) & 1) && (best < 0 || cnt[q] > cnt[best])) best = q;
+                        const int32_t own = s_owner[warp][g][q];
+                        const int32_t top = s_row[warp][s_sorted[warp][off[q] + cnt[q] - 1]] & 0x3fffffff;
+                        if ((own < 0 || own == top) && (best < 0 || cnt[q] > cnt[best])) best = q;
                     }
-                    const int q = best >= 0 ? best : best_any;
-                    used[g] |= (unsigned short)(1u << q);
-                    s_perm[warp][pos] = s_sorted[warp][off[q] + (--cnt[q])];
+                    int q = best;
+                    if (q < 0) q = cnt[16] > 0 ? 16 : best_any;   // nothing fits: an unconstrained entry, else a conflict
+                    const int src = s_sorted[warp][off[q] + (--cnt[q])];
+                    if (q < 16 && s_owner[warp][g][q] < 0) s_owner[warp][g][q] = s_row[warp][src] & 0x3fffffff;
+                    s_perm[warp][pos] = (unsigned char)src;
                 }
                 a = b;
             }
@@ -326,6 +341,24 @@ __global__ void __launch_bounds__(256) bank_order_kernel(int64_t n_chunks, int32
             if (val != nullptr) val[c * 256 + k] = reinterpret_cast<const VT *>(s_val[warp])[src];
         }
         __syncwarp();
+    }
+}
+
+// Chunks of the tiled hot region in which no run starts (all 256 entries continue one (tile, column) run) are marked
+// in the data itself: bit 30 of the first index of every lane (positions 8L).  The kernel then knows from the
+// registers it already holds that the chunk needs no scan -- a look-up of chunk_lo[c], chunk_lo[c + 1] in front of the
+// chunk was measured to cost more (an exposed load per chunk) than the scan it saved.
+__global__ void __launch_bounds__(256) mark_uniform_kernel(int64_t n_chunks, int32_t *__restrict__ idx)
+{
+    const int lane = threadIdx.x & 31;
+    int64_t c = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (; c < n_chunks; c += nw) {
+        int4 *ci = reinterpret_cast<int4 *>(idx + c * 256) + 2 * lane;
+        const int4 a = ci[0], b = ci[1];
+        const bool start = (a.x | a.y | a.z | a.w | b.x | b.y | b.z | b.w) < 0;
+        if (__any_sync(0xffffffffu, start)) continue;
+        idx[c * 256 + 8 * lane] = a.x | 0x40000000;
     }
 }
 
@@ -409,6 +442,18 @@ int check_columns(cudaStream_t s, const int32_t *col, int64_t nnz, int32_t d, in
     PML_CUDA(cudaMemcpyAsync(&h, cnt.p, sizeof(h), cudaMemcpyDeviceToHost, s));
     PML_CUDA(cudaStreamSynchronize(s));
     *bad = (int64_t)h;
+    return PML_OK;
+}
+
+// Bank-aware order of `n_chunks` full chunks of an entry stream (see bank_order_kernel)
+int bank_order(cudaStream_t s, int64_t n_chunks, int32_t *idx, void *val, int value_bytes, int32_t n_table)
+{
+    if (n_chunks <= 0) return PML_OK;
+    const int grid = (int)(n_chunks / 8 + 1 < 148 * 8 ? n_chunks / 8 + 1 : 148 * 8);
+    if (value_bytes == 0) bank_order_kernel<char><<<grid, 256, 0, s>>>(n_chunks, idx, (char *)nullptr, n_table);
+    else if (value_bytes == 4) bank_order_kernel<float><<<grid, 256, 0, s>>>(n_chunks, idx, (float *)val, n_table);
+    else bank_order_kernel<double><<<grid, 256, 0, s>>>(n_chunks, idx, (double *)val, n_table);
+    PML_CUDA(cudaGetLastError());
     return PML_OK;
 }
 
@@ -726,9 +771,10 @@ static int build_tiled(cudaStream_t s, int sm_count, int64_t n, int64_t nnz, con
     if (std::getenv("PML_NO_BANK_ORDER") == nullptr && hot_len > 0) {
         const int64_t hc = hot_len / 256;
         const int grid = (int)(hc / 8 + 1 < 148 * 8 ? hc / 8 + 1 : 148 * 8);
-        if (value_bytes == 0) bank_order_kernel<char><<<grid, 256, 0, s>>>(hc, out->idx_alloc, (char *)nullptr);
-        else if (value_bytes == 4) bank_order_kernel<float><<<grid, 256, 0, s>>>(hc, out->idx_alloc, (float *)out->val_alloc);
-        else bank_order_kernel<double><<<grid, 256, 0, s>>>(hc, out->idx_alloc, (double *)out->val_alloc);
+        PML_TRY(bank_order(s, hc, out->idx_alloc, out->val_alloc, value_bytes, 0x3fffffff));
+    }
+    if (std::getenv("PML_NO_UNIFORM_FAST") == nullptr && hot_len > 0) {
+        mark_uniform_kernel<<<grid_for(hot_len / 8), 256, 0, s>>>(hot_len / 256, out->idx_alloc);
         PML_CUDA(cudaGetLastError());
     }
 

@@ -210,7 +210,8 @@ def test_host_buffer_allreduce_entry_points(tmp_path, world):
         got = np.load(str(tmp_path / ("host%d.npz" % r)))
         assert got["status"] == 0
         assert np.all(np.abs(got["values"] - f_ref) <= TOL * abs(f_ref))
-        assert np.array_equal(got["grad"], shared_g) and np.array_equal(got["hv"], shared_h)   # same bits everywhere
+        assert np.array_equal(got["grad"], shared_g)           # same path, same bits on every rank
+        assert util.rel_err(got["hv"], shared_h) <= 1e-13      # margin pass recomputed vs cached curvature
         covered[got["slice"][0]:got["slice"][1]] += 1
     assert np.all(covered == 1)   # the ranks' slices tile [0, d)
 
