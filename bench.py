@@ -322,12 +322,21 @@ def run_ours(args):
         ctx.set_profiling(False)
 
         # ---- end to end through the host-buffer C ABI: pinned host coefficients in, gradient out
-        h_coef = torch.empty(d, dtype=torch.float64).pin_memory()
-        h_coef.copy_(coef.cpu())
-        h_grad = torch.empty(d, dtype=torch.float64).pin_memory()
-        h_raw = torch.empty(d + 2, dtype=torch.float64).pin_memory()
-        h_coef_np, h_grad_np = h_coef.numpy(), h_grad.numpy()
         host_peer = peer is not None and hasattr(peer, "value_and_gradient_host")
+        shared = None
+        if host_peer:
+            # One host buffer for all ranks (the driver's coefficient / gradient arrays, as a file in /dev/shm mapped
+            # and page-locked by every rank): rank 0 owns the vectors, every rank moves its slice, and a flag word per
+            # rank tells the driver when the last slice has landed.
+            shared = SharedHostVectors(torch, dist, rank, world, d, coef.cpu().numpy())
+            h_coef_np, h_grad_np = shared.coef, shared.grad
+        else:
+            h_coef = torch.empty(d, dtype=torch.float64).pin_memory()
+            h_coef.copy_(coef.cpu())
+            h_grad = torch.empty(d, dtype=torch.float64).pin_memory()
+            h_raw = torch.empty(d + 2, dtype=torch.float64).pin_memory()
+            h_coef_np, h_grad_np = h_coef.numpy(), h_grad.numpy()
+        e2e_iter = [0]
 
         def e2e_step():
             if world == 1:
@@ -335,7 +344,10 @@ def run_ours(args):
             if host_peer:
                 # every rank moves 1/N of the coefficients up and 1/N of the gradient down over its own PCIe link;
                 # the slices travel between the GPUs over NVLink inside the call
-                return peer.value_and_gradient_host(ds, LOSS_POISSON, h_coef_np, h_grad_np)
+                value = peer.value_and_gradient_host(ds, LOSS_POISSON, h_coef_np, h_grad_np)
+                e2e_iter[0] += 1
+                shared.arrive_and_wait(e2e_iter[0])
+                return value
             # the driver (rank 0) owns the host buffers: one upload, an NVLink broadcast of the coefficients
             # (what sc.broadcast does in the reference, DistributedObjectiveFunction.scala:57-58), the
             # evaluation with its all-reduce, and one download of gradient + value on rank 0
@@ -381,6 +393,9 @@ def run_ours(args):
             b.record(ext)
             barrier()
             hv_ms[name] = a.elapsed_time(b) / max(3, args.steps // 2)
+        e2e_grad = np.array(h_grad_np, copy=True)
+        if shared is not None:
+            shared.close()
         hv_result = out_grad.clone()
         step()                      # leaves the value+gradient result in out_value / out_grad for the parity block
         barrier()
@@ -394,7 +409,7 @@ def run_ours(args):
     parity = None
     if not args.no_parity:
         parity = parity_block(torch, dist, pml, ctx, ext, world, rank, device, ds, coef, v, out_value, out_grad, hv_result,
-                              host_rows, e2e_value)
+                              host_rows, e2e_value, e2e_grad)
 
     if rank == 0:
         peak, peak_src = peaks()
@@ -444,7 +459,7 @@ def run_ours(args):
                 "generate_s": round(t_gen, 2), "pack_s": round(t_pack, 2),
             },
             "e2e": {"value": e2e_steps / e2e_s, "unit": "evals/s",
-                    "h2d_bytes_per_step": d * 8, "d2h_bytes_per_step": d * 8 + 8,
+                    "h2d_bytes_per_step": d * 8, "d2h_bytes_per_step": d * 8 + 8 * world,
                     "ms_per_step": 1e3 * e2e_s / e2e_steps,
                     "api": "pml_value_and_gradient (host buffers, pinned)" if world == 1 else
                            ("pml_value_and_gradient_allreduce (host buffers): every rank uploads 1/N of the coefficients and "
@@ -489,6 +504,43 @@ def run_ours(args):
         raise SystemExit("parity block failed: %s" % json.dumps(parity))
 
 
+class SharedHostVectors:
+    """Coefficients and gradient of the end-to-end step in ONE host buffer shared by the rank processes (a file in
+    /dev/shm, page-locked by every rank with cudaHostRegister), plus a flag word per rank: rank r bumps flags[r] once
+    its slice of the gradient has landed, and everybody waits for all flags -- the driver then holds the full vector."""
+
+    def __init__(self, torch, dist, rank, world, d, coef):
+        self.rank, self.world, self.torch = rank, world, torch
+        self.path = "/dev/shm/pml_bench_%s_%s.bin" % (os.environ.get("MASTER_PORT", "0"), os.getppid() if world > 1 else os.getpid())
+        words = 2 * d + 64
+        if rank == 0:
+            np.zeros(words).tofile(self.path)
+        dist.barrier()
+        self.map = np.memmap(self.path, dtype=np.float64, mode="r+", shape=(words,))
+        self.coef, self.grad = self.map[:d], self.map[d:2 * d]
+        self.flags = self.map[2 * d:2 * d + world]
+        if rank == 0:
+            self.coef[:] = coef
+        self.registered = torch.cuda.cudart().cudaHostRegister(self.map.ctypes.data, self.map.nbytes, 0)
+        dist.barrier()
+
+    def arrive_and_wait(self, it):
+        self.flags[self.rank] = it
+        while float(self.flags.min()) < it:
+            pass
+
+    def close(self):
+        try:
+            self.torch.cuda.cudart().cudaHostUnregister(self.map.ctypes.data)
+        except Exception:  # noqa: BLE001
+            pass
+        if self.rank == 0:
+            try:
+                os.unlink(self.path)
+            except OSError:
+                pass
+
+
 def hessian_vector_report(info, d, hv_ms, peak):
     """Hessian-vector evaluations/s with their own algorithmic bytes (no offsets / weights here)."""
     n, nnz = info.n, info.nnz
@@ -507,7 +559,7 @@ PARITY_SAMPLE_ROWS = 500_000   # natural tiling geometry (tiling starts at 262 1
 
 
 def parity_block(torch, dist, pml, ctx, ext, world, rank, device, ds, coef, v, out_value, out_grad, hv_result, host_rows,
-                 e2e_value):
+                 e2e_value, e2e_grad):
     """What this run's numbers are worth: the evaluated result against an independent evaluation of the same rows.
     N = 1: the GPU value / gradient over all 10 M rows against the oracle (the reference's row loop, partitioned) on
     the same rows, and value / gradient / Hessian-vector on the first 500 k rows -- packed on their own, so in the
@@ -531,7 +583,8 @@ def parity_block(torch, dist, pml, ctx, ext, world, rank, device, ds, coef, v, o
         f_ref, g_ref = oracle.value_and_gradient(full, oracle.POISSON, coef_h, parts=cores)
         out["full_rows_vs_oracle"] = {"rows": N_ROWS, "oracle": "partitioned x%d" % cores, "value": value, "oracle_value": f_ref,
                                       "value_rel": abs(value - f_ref) / abs(f_ref), "gradient_rel_inf": rel_inf(grad, g_ref),
-                                      "e2e_value_rel": abs(e2e_value - f_ref) / abs(f_ref)}
+                                      "e2e_value_rel": abs(e2e_value - f_ref) / abs(f_ref),
+                                      "e2e_gradient_rel_inf": rel_inf(e2e_grad, g_ref)}
         ns = PARITY_SAMPLE_ROWS
         end = int(row_ptr[ns])
         sample = oracle.Data(ns, N_FEATS, row_ptr[:ns + 1], cols[:end], vals[:end], labels[:ns])
@@ -553,7 +606,7 @@ def parity_block(torch, dist, pml, ctx, ext, world, rank, device, ds, coef, v, o
                                    "hessian_vector_rel_inf": max(rel_inf(hv_g, hv_s), rel_inf(hv_g2, hv_s)),
                                    "hessian_vector_cached_rel_inf": rel_inf(hv_g3, hv_s)}
         worst = max(out["full_rows_vs_oracle"]["value_rel"], out["full_rows_vs_oracle"]["gradient_rel_inf"],
-                    out["full_rows_vs_oracle"]["e2e_value_rel"],
+                    out["full_rows_vs_oracle"]["e2e_value_rel"], out["full_rows_vs_oracle"]["e2e_gradient_rel_inf"],
                     *[x for k, x in out["sample_vs_oracle"].items() if k.endswith("_rel") or k.endswith("_rel_inf")])
         out["worst"] = worst
         out["ok"] = bool(worst <= tol)
@@ -581,7 +634,9 @@ def parity_block(torch, dist, pml, ctx, ext, world, rank, device, ds, coef, v, o
     out["merged_vs_single_gpu"] = {"rows": N_ROWS, "value": value, "single_gpu_value": f_one,
                                    "value_rel": abs(value - f_one) / abs(f_one), "gradient_rel_inf": rel_inf(grad, g_one),
                                    "hessian_vector_rel_inf": rel_inf(hv, h_one),
-                                   "e2e_value_rel": abs(e2e_value - f_one) / abs(f_one)}
+                                   "e2e_value_rel": abs(e2e_value - f_one) / abs(f_one),
+                                   # the gradient the driver (rank 0) finds in its host buffer after the end-to-end step
+                                   "e2e_gradient_rel_inf": rel_inf(e2e_grad, g_one)}
     out["result_crc32_per_rank"] = [int(x) for x in crcs.tolist()]
     out["ranks_bit_identical"] = len(set(out["result_crc32_per_rank"])) == 1
     worst = max(x for k, x in out["merged_vs_single_gpu"].items() if k.endswith("_rel") or k.endswith("_rel_inf"))

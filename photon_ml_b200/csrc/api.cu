@@ -582,7 +582,7 @@ int pml_dataset_destroy(pml_dataset *ds)
     }
     for (pml_graph *g : { &ds->vg_graph, &ds->hv_cold_graph, &ds->hv_cached_graph })
         if (g->exec) cudaGraphExecDestroy(g->exec);
-    void *ptrs[] = { ds->row_ptr, ds->col, ds->val, ds->label, ds->offset, ds->weight, ds->t.idx_alloc, ds->t.val_alloc, ds->t.hot.run_id, ds->t.hot.chunk_lo, ds->t.hot.tile_first_chunk, ds->t.hot.fix,
+    void *ptrs[] = { ds->row_ptr, ds->col, ds->val, ds->label, ds->offset, ds->weight, ds->t.idx_alloc, ds->t.val_alloc, ds->t.hot.idx16, ds->t.hot.uniform, ds->t.hot.run_id, ds->t.hot.chunk_lo, ds->t.hot.tile_first_chunk, ds->t.hot.fix,
                      ds->t.hot.partial, ds->t.hot.carry, ds->t.cold_slot, ds->t.cold_partial,
                      ds->t.nzcol_ptr, ds->t.nzcol_id, ds->t.rank, ds->t.chunk_col_lo, ds->t.fix, ds->rs.nzrow_id, ds->rs.chunk_lo,
                      ds->rs.fix, ds->za, ds->zb, ds->carry_row, ds->carry_row2, ds->row_loss, ds->factors, ds->shifts, ds->r,
@@ -697,10 +697,10 @@ int pml_dataset_create_csr_dev(pml_ctx *ctx, int64_t n, int32_t d, const int64_t
     // flags in bit 31
     PML_TRY(build_row_side(s, n, nnz, ds->row_ptr, ds->col, chunk_entries, &ds->rs));
     ds->bytes += ds->rs.bytes;
-    // Inside every row the entries are dealt to the lanes so that the look-ups of the staged coefficient prefix
-    // spread over the shared-memory banks (pack.cu, bank_order_kernel); the order of a row's terms is free.
-    if (std::getenv("PML_NO_BANK_ORDER") == nullptr && std::getenv("PML_NO_BANK_ORDER_CSR") == nullptr)
-        PML_TRY(bank_order(s, nnz / SEG_CHUNK, ds->col, ds->val, dst_bytes, SEG_TABLE_BYTES / 8));
+    // (The rows of the CSR stream keep their ascending column order: re-dealing a row's entries over the lanes for
+    // the shared-memory banks, as pack.cu does inside the runs of the tiled CSC region, was measured to slow the pass
+    // from 1.03 to 1.12 ms -- in sorted order the lanes that hold row heads read the same few hottest coefficients at
+    // the same item, which is a broadcast, not a conflict.)
     PML_TRY(dev_alloc(&ds->za, (size_t)n, &ds->bytes));
     PML_TRY(dev_alloc(&ds->carry_row, (size_t)ds->rs.n_chunks + 1, &ds->bytes));
 

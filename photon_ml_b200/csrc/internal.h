@@ -150,8 +150,9 @@ int convert_row_ptr(cudaStream_t s, const int64_t *src, uint32_t *dst, int64_t n
 
 // Hot columns of the CSC copy, tiled by row blocks so that a CTA gathers r from a slice staged in shared memory.
 struct TiledSide {
-    int32_t *idx = nullptr;        // view into Packed::idx_alloc: row index LOCAL to the tile (tile_rows = the zero slot
-    void *val = nullptr;           //   used by padding), bit 31 on the first entry of each (tile, column) run
+    uint16_t *idx16 = nullptr;     // owned: row index LOCAL to the tile (tile_rows = the zero slot used by padding),
+    void *val = nullptr;           //   bit 15 on the first entry of each (tile, column) run; val: view into val_alloc
+    unsigned char *uniform = nullptr;  // owned, n_chunks: 1 = no run starts in the chunk (it lies inside one run)
     int64_t len = 0;               // entries incl. padding; every tile starts at a multiple of 256
     int32_t *run_id = nullptr;     // run ordinal -> slot tile * n_hot_cols + column in `partial`
     int32_t *chunk_lo = nullptr;   // n_chunks + 1
@@ -166,8 +167,8 @@ struct TiledSide {
 };
 
 struct Packed {
-    int32_t *idx_alloc = nullptr;  // one allocation holds [hot tiled region | cold region]
-    void *val_alloc = nullptr;
+    int32_t *idx_alloc = nullptr;  // row indices of the cold region (all columns when nothing is tiled)
+    void *val_alloc = nullptr;     // one allocation holds the values of [hot tiled region | cold region]
     TiledSide hot;
     // cold region (all columns when nothing is tiled): plain CSC ordered by (internal column, row)
     int64_t cold_nnz = 0;

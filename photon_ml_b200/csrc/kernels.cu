@@ -692,9 +692,52 @@ static int launch_seg_warp(cudaStream_t s, int sm_count, size_t smem, const SegP
 // ------------------------------------------------------------------------------------------
 constexpr int ST_THREADS = 1024;
 
+// The tiled region stores its row indices -- local to the tile, below 2^15 -- as 16-bit words with the run-start
+// flag in bit 15: 6 bytes per entry instead of 8 with fp32 values (the pass is close to the HBM bound once its
+// look-ups are free of bank conflicts).  Unpacked into the 32-bit form (flag in bit 31) the reduction expects.
+template <typename VT, int ITEMS>
+__device__ __forceinline__ void seg_load_full16(SegRegs<VT, ITEMS> &g, const uint16_t *__restrict__ idx,
+                                                const VT *__restrict__ val, int64_t first)
+{
+    static_assert(ITEMS == 8, "one 16-byte load carries a lane's 8 indices");
+    const uint4 rr = __ldcs(reinterpret_cast<const uint4 *>(idx + first));
+    const uint32_t w[4] = { rr.x, rr.y, rr.z, rr.w };
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        g.idx[2 * i] = (int32_t)((w[i] & 0x7fffu) | ((w[i] << 16) & 0x80000000u));
+        g.idx[2 * i + 1] = (int32_t)(((w[i] >> 16) & 0x7fffu) | (w[i] & 0x80000000u));
+    }
+#pragma unroll
+    for (int i = 0; i < ITEMS / 4; ++i) {
+        if constexpr (std::is_same<VT, float>::value) {
+            const float4 vv = __ldcs(reinterpret_cast<const float4 *>(val + first) + i);
+            g.val[4 * i] = vv.x; g.val[4 * i + 1] = vv.y; g.val[4 * i + 2] = vv.z; g.val[4 * i + 3] = vv.w;
+        } else if constexpr (std::is_same<VT, double>::value) {
+            const double2 va = __ldcs(reinterpret_cast<const double2 *>(val + first) + 2 * i);
+            const double2 vb = __ldcs(reinterpret_cast<const double2 *>(val + first) + 2 * i + 1);
+            g.val[4 * i] = va.x; g.val[4 * i + 1] = va.y; g.val[4 * i + 2] = vb.x; g.val[4 * i + 3] = vb.y;
+        }
+    }
+}
+
+template <typename VT, int ITEMS>
+__device__ __forceinline__ void seg_prefetch_l2_16(const uint16_t *__restrict__ idx, const VT *__restrict__ val, int64_t chunk)
+{
+    constexpr int CHUNK = 32 * ITEMS;
+    constexpr int IDX_LINES = CHUNK * 2 / 128;
+    constexpr int VAL_LINES = std::is_same<VT, One>::value ? 0 : CHUNK * (int)sizeof(VT) / 128;
+    const int lane = threadIdx.x & 31;
+    const char *ptr = nullptr;
+    if (lane < IDX_LINES) ptr = reinterpret_cast<const char *>(idx + chunk * CHUNK) + 128 * lane;
+    else if (lane < IDX_LINES + VAL_LINES)
+        ptr = reinterpret_cast<const char *>(val) + (size_t)chunk * CHUNK * sizeof(VT) + 128 * (lane - IDX_LINES);
+    if (ptr != nullptr) asm volatile("prefetch.global.L2 [%0];" ::"l"(ptr));
+}
+
 template <typename VT, bool SQUARE>
 __global__ void __launch_bounds__(ST_THREADS, 1)
-seg_spmv_tiled_kernel(const SegParams p, const int32_t *__restrict__ tile_first_chunk, int n_tiles, int tile_rows,
+seg_spmv_tiled_kernel(const SegParams p, const uint16_t *__restrict__ idx, const unsigned char *__restrict__ uniform,
+                      const int32_t *__restrict__ tile_first_chunk, int n_tiles, int tile_rows,
                       const double *__restrict__ r, int64_t n)
 {
     constexpr int ITEMS = 8;
@@ -703,7 +746,6 @@ seg_spmv_tiled_kernel(const SegParams p, const int32_t *__restrict__ tile_first_
     extern __shared__ __align__(16) double hot[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const VT *__restrict__ val = static_cast<const VT *>(p.val);
-    const int32_t *__restrict__ idx = p.idx;
     const uint32_t hot_at = shared_window_address(hot);
     for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
         __syncthreads();  // every warp is done with the previous tile's slice
@@ -713,14 +755,22 @@ seg_spmv_tiled_kernel(const SegParams p, const int32_t *__restrict__ tile_first_
         const int c_end = tile_first_chunk[t + 1];
         int c = tile_first_chunk[t] + warp;
         SegRegs<VT, ITEMS> cur;
-        if (c < c_end) seg_load_full<VT, ITEMS>(cur, idx, val, (int64_t)c * CHUNK + lane * ITEMS);
+        unsigned char uni = 0;
+        if (c < c_end) {
+            seg_load_full16<VT, ITEMS>(cur, idx, val, (int64_t)c * CHUNK + lane * ITEMS);
+            uni = uniform[c];
+        }
         for (; c < c_end; c += WARPS) {
             SegRegs<VT, ITEMS> nxt;
+            unsigned char uni_nxt = 0;
             const int cn = c + WARPS;
-            if (cn < c_end) seg_load_full<VT, ITEMS>(nxt, idx, val, (int64_t)cn * CHUNK + lane * ITEMS);
-            if (cn + (PF_AHEAD - 1) * WARPS < c_end) seg_prefetch_l2<VT, ITEMS>(idx, val, cn + (PF_AHEAD - 1) * WARPS);
-            if (cur.idx[0] & 0x40000000) {
-                // Marked at pack time (pack.cu, mark_uniform_kernel): no run starts in this chunk, all 256 entries
+            if (cn < c_end) {
+                seg_load_full16<VT, ITEMS>(nxt, idx, val, (int64_t)cn * CHUNK + lane * ITEMS);
+                uni_nxt = uniform[cn];
+            }
+            if (cn + (PF_AHEAD - 1) * WARPS < c_end) seg_prefetch_l2_16<VT, ITEMS>(idx, val, cn + (PF_AHEAD - 1) * WARPS);
+            if (uni) {
+                // Marked at pack time (pack.cu, narrow_tiled_kernel): no run starts in this chunk, all 256 entries
                 // continue one (tile, column) run -- the long runs of the hottest columns, about half of the region on
                 // Zipf data.  No flags, no scan, no run look-up: the products are added up per lane, one warp
                 // reduction, and the sum joins the run through carry[c] like any other chunk head (fixup_kernel).
@@ -729,7 +779,7 @@ seg_spmv_tiled_kernel(const SegParams p, const int32_t *__restrict__ tile_first_
                 for (int i = 0; i < ITEMS; ++i) {
                     double x = cur.value(i);
                     if (SQUARE) x *= x;
-                    const double g = lds_f64(hot_at + 8u * (uint32_t)(cur.idx[i] & 0x3fffffff));
+                    const double g = lds_f64(hot_at + 8u * (uint32_t)cur.idx[i]);
                     if constexpr (std::is_same<VT, One>::value) s += g;
                     else s += __dmul_rn(g, x);
                 }
@@ -739,6 +789,7 @@ seg_spmv_tiled_kernel(const SegParams p, const int32_t *__restrict__ tile_first_
                 seg_chunk<VT, ITEMS, false, SQUARE, LOOKUP_SHARED, true>(p, cur, c, ITEMS, hot_at);
             }
             cur = nxt;
+            uni = uni_nxt;
         }
     }
 }
@@ -749,7 +800,7 @@ int launch_seg_tiled(cudaStream_t s, int sm_count, int value_bytes, bool square,
     if (t.n_chunks <= 0) return 0;
     SegParams p;
     p.nnz = t.len;
-    p.idx = t.idx;
+    p.idx = nullptr;  // the tiled region's indices are the 16-bit array handed over separately
     p.val = t.val;
     p.run_id = t.run_id;
     p.chunk_lo = t.chunk_lo;
@@ -768,7 +819,8 @@ int launch_seg_tiled(cudaStream_t s, int sm_count, int value_bytes, bool square,
                                                      cudaFuncAttributeMaxDynamicSharedMemorySize,                   \
                                                      (int)(sizeof(double) * 28002)) != cudaSuccess)   \
             return -1;                                                                                              \
-        seg_spmv_tiled_kernel<VT, SQ><<<grid, ST_THREADS, smem, s>>>(p, t.tile_first_chunk, t.n_tiles, t.tile_rows, r, n); \
+        seg_spmv_tiled_kernel<VT, SQ><<<grid, ST_THREADS, smem, s>>>(p, t.idx16, t.uniform, t.tile_first_chunk, t.n_tiles, \
+                                                                     t.tile_rows, r, n);                            \
     } while (0)
     if (value_bytes == 0) {
         if (square) PML_TILED(One, true); else PML_TILED(One, false);

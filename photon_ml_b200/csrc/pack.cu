@@ -344,21 +344,31 @@ __global__ void __launch_bounds__(256) bank_order_kernel(int64_t n_chunks, int32
     }
 }
 
-// Chunks of the tiled hot region in which no run starts (all 256 entries continue one (tile, column) run) are marked
-// in the data itself: bit 30 of the first index of every lane (positions 8L).  The kernel then knows from the
-// registers it already holds that the chunk needs no scan -- a look-up of chunk_lo[c], chunk_lo[c + 1] in front of the
-// chunk was measured to cost more (an exposed load per chunk) than the scan it saved.
-__global__ void __launch_bounds__(256) mark_uniform_kernel(int64_t n_chunks, int32_t *__restrict__ idx)
+// Final form of the tiled hot region: the 32-bit work copy (flag in bit 31) narrowed to 16-bit words (flag in bit
+// 15; local rows are below 2^15), and one byte per chunk that says whether any run starts in it -- chunks without a
+// start lie inside one (tile, column) run and take the kernel's no-scan path.  One warp per chunk.
+__global__ void __launch_bounds__(256) narrow_tiled_kernel(int64_t n_chunks, const int32_t *__restrict__ idx,
+                                                           uint16_t *__restrict__ idx16, unsigned char *__restrict__ uniform,
+                                                           int mark_uniform)
 {
     const int lane = threadIdx.x & 31;
     int64_t c = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int64_t nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
     for (; c < n_chunks; c += nw) {
-        int4 *ci = reinterpret_cast<int4 *>(idx + c * 256) + 2 * lane;
+        const int4 *ci = reinterpret_cast<const int4 *>(idx + c * 256) + 2 * lane;
         const int4 a = ci[0], b = ci[1];
+        const int32_t v[8] = { a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w };
+        uint32_t w[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const uint32_t lo = ((uint32_t)v[2 * i] & 0x7fffu) | (v[2 * i] < 0 ? 0x8000u : 0u);
+            const uint32_t hi = ((uint32_t)v[2 * i + 1] & 0x7fffu) | (v[2 * i + 1] < 0 ? 0x8000u : 0u);
+            w[i] = lo | (hi << 16);
+        }
+        reinterpret_cast<uint4 *>(idx16 + c * 256)[lane] = make_uint4(w[0], w[1], w[2], w[3]);
         const bool start = (a.x | a.y | a.z | a.w | b.x | b.y | b.z | b.w) < 0;
-        if (__any_sync(0xffffffffu, start)) continue;
-        idx[c * 256 + 8 * lane] = a.x | 0x40000000;
+        const bool any = __any_sync(0xffffffffu, start);
+        if (lane == 0) uniform[c] = (mark_uniform && !any) ? 1 : 0;
     }
 }
 
@@ -746,37 +756,44 @@ static int build_tiled(cudaStream_t s, int sm_count, int64_t n, int64_t nnz, con
     PML_CUDA(cudaMemcpyAsync(po_dev.p, po.data(), sizeof(uint32_t) * (size_t)(n_tiles + 1), cudaMemcpyHostToDevice, s));
 
     TiledSide &h = out->hot;
-    PML_CUDA(cudaMalloc(&out->idx_alloc, sizeof(int32_t) * (size_t)(total + 16)));
+    // 32-bit work copy of [hot | cold]: scattered, ordered and marked here, then the hot part is narrowed to 16 bits
+    // and the cold part moves to an allocation of its own
+    DevBuf work;
+    PML_CUDA(work.alloc(sizeof(int32_t) * (size_t)(total + 16)));
+    int32_t *work_idx = work.as<int32_t>();
     if (value_bytes > 0) {
         PML_CUDA(cudaMalloc(&out->val_alloc, (size_t)value_bytes * (size_t)(total + 16)));
         PML_CUDA(cudaMemsetAsync(out->val_alloc, 0, (size_t)value_bytes * (size_t)(total + 16), s));
     }
-    out->bytes += (int64_t)(sizeof(int32_t) + value_bytes) * (total + 16);
-    PML_CUDA(cudaMemsetAsync(out->idx_alloc + hot_len, 0, sizeof(int32_t) * (size_t)(cold_nnz + 16), s));
-    fill_pad_kernel<<<grid_for(hot_len), 256, 0, s>>>(hot_len, tile_rows, out->idx_alloc);
+    PML_CUDA(cudaMemsetAsync(work_idx + hot_len, 0, sizeof(int32_t) * (size_t)(cold_nnz + 16), s));
+    fill_pad_kernel<<<grid_for(hot_len), 256, 0, s>>>(hot_len, tile_rows, work_idx);
     PML_CUDA(run_flag.alloc((size_t)(nnz + 1)));
     PML_CUDA(hot_dest.alloc(sizeof(uint32_t) * (size_t)(nnz + 1)));
     if (value_bytes <= 4)
         tile_scatter_kernel<float><<<grid_for(nnz), 256, 0, s>>>(
             nnz, keys_sorted.as<uint32_t>(), perm_out.as<uint32_t>(), entry_row.as<int32_t>(),
             value_bytes ? (const float *)val : nullptr, (int)K,
-            tile_rows, (int)n_tiles, hs_dev.as<uint32_t>(), po_dev.as<uint32_t>(), (uint32_t)hot_len, out->idx_alloc,
+            tile_rows, (int)n_tiles, hs_dev.as<uint32_t>(), po_dev.as<uint32_t>(), (uint32_t)hot_len, work_idx,
             (float *)out->val_alloc, run_flag.as<unsigned char>(), hot_dest.as<uint32_t>());
     else
         tile_scatter_kernel<double><<<grid_for(nnz), 256, 0, s>>>(
             nnz, keys_sorted.as<uint32_t>(), perm_out.as<uint32_t>(), entry_row.as<int32_t>(), (const double *)val, (int)K,
-            tile_rows, (int)n_tiles, hs_dev.as<uint32_t>(), po_dev.as<uint32_t>(), (uint32_t)hot_len, out->idx_alloc,
+            tile_rows, (int)n_tiles, hs_dev.as<uint32_t>(), po_dev.as<uint32_t>(), (uint32_t)hot_len, work_idx,
             (double *)out->val_alloc, run_flag.as<unsigned char>(), hot_dest.as<uint32_t>());
     PML_CUDA(cudaGetLastError());
-    if (std::getenv("PML_NO_BANK_ORDER") == nullptr && hot_len > 0) {
-        const int64_t hc = hot_len / 256;
-        const int grid = (int)(hc / 8 + 1 < 148 * 8 ? hc / 8 + 1 : 148 * 8);
-        PML_TRY(bank_order(s, hc, out->idx_alloc, out->val_alloc, value_bytes, 0x3fffffff));
-    }
-    if (std::getenv("PML_NO_UNIFORM_FAST") == nullptr && hot_len > 0) {
-        mark_uniform_kernel<<<grid_for(hot_len / 8), 256, 0, s>>>(hot_len / 256, out->idx_alloc);
-        PML_CUDA(cudaGetLastError());
-    }
+    if (std::getenv("PML_NO_BANK_ORDER") == nullptr && hot_len > 0)
+        PML_TRY(bank_order(s, hot_len / 256, work_idx, out->val_alloc, value_bytes, 0x3fffffff));
+    PML_CUDA(cudaMalloc(&h.idx16, sizeof(uint16_t) * (size_t)(hot_len + 16)));
+    PML_CUDA(cudaMalloc(&h.uniform, (size_t)(hot_len / 256 + 1)));
+    PML_CUDA(cudaMemsetAsync(h.idx16 + hot_len, 0, sizeof(uint16_t) * 16, s));
+    narrow_tiled_kernel<<<grid_for(hot_len / 8), 256, 0, s>>>(hot_len / 256, work_idx, h.idx16, h.uniform,
+                                                              std::getenv("PML_NO_UNIFORM_FAST") == nullptr ? 1 : 0);
+    PML_CUDA(cudaGetLastError());
+    PML_CUDA(cudaMalloc(&out->idx_alloc, sizeof(int32_t) * (size_t)(cold_nnz + 16)));
+    PML_CUDA(cudaMemcpyAsync(out->idx_alloc, work_idx + hot_len, sizeof(int32_t) * (size_t)(cold_nnz + 16),
+                             cudaMemcpyDeviceToDevice, s));
+    out->bytes += (int64_t)value_bytes * (total + 16) + (int64_t)sizeof(uint16_t) * (hot_len + 16) + hot_len / 256 + 1 +
+                  (int64_t)sizeof(int32_t) * (cold_nnz + 16);
 
     // hot run list: positions (padded coordinates) and partial slots (= keys) of the run starts
     DevBuf n_sel, run_ptr_hot;
@@ -801,7 +818,6 @@ static int build_tiled(cudaStream_t s, int sm_count, int64_t n, int64_t nnz, con
     PML_CUDA(cudaMemcpyAsync(run_ptr_hot.as<uint32_t>() + runs_hot, &hot_len32, sizeof(uint32_t), cudaMemcpyHostToDevice, s));
     out->bytes += (int64_t)sizeof(int32_t) * (n_hot + 2);
 
-    h.idx = out->idx_alloc;
     h.val = out->val_alloc;
     h.len = hot_len;
     h.n_runs = runs_hot;
@@ -828,7 +844,7 @@ static int build_tiled(cudaStream_t s, int sm_count, int64_t n, int64_t nnz, con
     }
 
     // cold region: CSC over internal columns [K, m), one copy per super block of rows
-    out->csc_row = out->idx_alloc + hot_len;
+    out->csc_row = out->idx_alloc;
     out->csc_val = value_bytes ? (char *)out->val_alloc + (size_t)hot_len * value_bytes : nullptr;
     out->cold_nnz = cold_nnz;
     out->n_chunks = (int)((cold_nnz + 255) / 256);
