@@ -32,7 +32,10 @@ int fail(int code, const std::string &msg);
 
 // ---- geometry of the entry-chunked kernels: a chunk is SEG_CHUNK consecutive entries, owned by one warp ----
 constexpr int SEG_CHUNK = 256;               // 32 lanes x 8 entries
-constexpr int SEG_TABLE_BYTES = 96 * 1024;   // hot prefix of the coefficient vector staged per CTA (CSR stream)
+#ifndef PML_SEG_TABLE_KB
+#define PML_SEG_TABLE_KB 96
+#endif
+constexpr int SEG_TABLE_BYTES = PML_SEG_TABLE_KB * 1024;   // hot prefix of the coefficient vector staged per CTA (CSR stream)
 
 // ---- geometry of the lanes-per-row / segment-per-warp row kernel ----
 constexpr int R_THREADS = 256;
