@@ -715,22 +715,40 @@ def convergence(ctx, ds, d):
     return out
 
 
-def random_effect_batch(ctx):
-    """configs[4]-shaped per-entity batch at 1/10 scale: 1 M entities, power-law rows per entity (mean ~4),
-    10 entries per row in a 32-dimensional per-entity space; every entity's value+gradient in one call."""
-    import photon_ml_b200 as pml
-    rng = np.random.default_rng(5)
-    n_ent, k, d_e = 1_000_000, 10, 32
-    rows = np.minimum(rng.zipf(1.8, size=n_ent), 2000).astype(np.int64)
+def make_entity_problems(rng, n_ent, k=10, d_e=32, rows=None):
+    """configs[4]-shaped per-entity problems: power-law rows per entity (Zipf(1.8), mean ~4, capped at 2000), k entries
+    per row in a d_e-dimensional per-entity space (after index-map projection), indicator values, ~10 % positives."""
+    if rows is None:
+        rows = np.minimum(rng.zipf(1.8, size=n_ent), 2000).astype(np.int64)
     ent_row_ptr = np.concatenate([[0], np.cumsum(rows)]).astype(np.int64)
     n = int(ent_row_ptr[-1])
     col = np.sort(rng.integers(0, d_e, size=(n, k), dtype=np.int32), axis=1).ravel()
     row_ptr = np.arange(n + 1, dtype=np.int64) * k
     val = np.ones(n * k, dtype=np.float32)
     label = (rng.random(n) < 0.1).astype(np.float64)
+    return ent_row_ptr, np.full(n_ent, d_e, np.int32), row_ptr, col, val, label
+
+
+def batch_bytes(n_ent, n, nnz, d_total, value_bytes):
+    """ALGORITHMIC bytes of one batched value+gradient evaluation: the two entry streams, labels, the per-row
+    multiplier and the per-row loss (each written once and read once), row / column / entity pointers, coefficients in,
+    gradients and values out."""
+    return 2 * nnz * (value_bytes + 4) + n * (8 + 16 + 16) + (n + 1) * 4 + d_total * 4 + d_total * 16 + n_ent * (8 + 8 + 8)
+
+
+def random_effect_batch(ctx, n_ent=1_000_000, seed=5, solver_runs=("skip", "stream-all")):
+    """configs[4]-shaped per-entity batch (default: 1/10 scale, 1 M entities): every entity's value+gradient in one
+    call, with its roofline, and every entity's L2-regularised problem solved in lock step."""
+    import photon_ml_b200 as pml
+    import torch
+    rng = np.random.default_rng(seed)
+    k, d_e = 10, 32
+    ent_row_ptr, ent_dim, row_ptr, col, val, label = make_entity_problems(rng, n_ent, k, d_e)
+    n = int(ent_row_ptr[-1])
     t0 = time.perf_counter()
-    batch = pml.Batch(ctx, ent_row_ptr, np.full(n_ent, d_e, np.int32), row_ptr, col, val, label)
+    batch = pml.Batch(ctx, ent_row_ptr, ent_dim, row_ptr, col, val, label)
     t_pack = time.perf_counter() - t0
+    del col, val
     coefs = rng.normal(scale=0.2, size=batch.d_total)
     for _ in range(3):
         batch.value_and_gradient(pml.LOGISTIC, coefs)
@@ -739,44 +757,357 @@ def random_effect_batch(ctx):
     for _ in range(reps):
         batch.value_and_gradient(pml.LOGISTIC, coefs)
     per = (time.perf_counter() - t0) / reps
-    ctx.read_profile()
-    ctx.set_profiling(True)
-    batch.value_and_gradient(pml.LOGISTIC, coefs)
-    prof = ctx.read_profile()
-    ctx.set_profiling(False)
-    import torch
     dev = torch.device("cuda", ctx.device)
     t_coef = torch.tensor(coefs, device=dev)
     t_val = torch.empty(n_ent, dtype=torch.float64, device=dev)
     t_grad = torch.empty(batch.d_total, dtype=torch.float64, device=dev)
     torch.cuda.synchronize()
+    ext = torch.cuda.ExternalStream(ctx.stream, device=dev)
     for _ in range(3):
         batch.value_and_gradient_dev(pml.LOGISTIC, t_coef.data_ptr(), t_val.data_ptr(), t_grad.data_ptr())
     ctx.synchronize()
-    t0 = time.perf_counter()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record(ext)
     for _ in range(reps):
         batch.value_and_gradient_dev(pml.LOGISTIC, t_coef.data_ptr(), t_val.data_ptr(), t_grad.data_ptr())
+    b.record(ext)
     ctx.synchronize()
-    per_dev = (time.perf_counter() - t0) / reps
+    per_dev = a.elapsed_time(b) / reps * 1e-3
+    ctx.read_profile()
+    ctx.set_profiling(True)
+    batch.value_and_gradient_dev(pml.LOGISTIC, t_coef.data_ptr(), t_val.data_ptr(), t_grad.data_ptr())
+    ctx.synchronize()
+    prof = ctx.read_profile()
+    ctx.set_profiling(False)
+    info = batch.dataset.info()
+    peak, _ = peaks()
+    nbytes = batch_bytes(n_ent, n, n * k, batch.d_total, info.value_bytes)
     out = {"entities": n_ent, "rows": n, "entries": n * k, "coefficients": int(batch.d_total), "pack_s": round(t_pack, 2),
            "ms_per_batch_evaluation_host_buffers": 1e3 * per, "entity_evaluations_per_s_host_buffers": n_ent / per,
            "ms_per_batch_evaluation_device_buffers": 1e3 * per_dev, "entity_evaluations_per_s_device_buffers": n_ent / per_dev,
-           "device_ms": {kk: vv[0] for kk, vv in prof.items() if vv[1]}}
+           "device_ms": {kk: vv[0] for kk, vv in prof.items() if vv[1]},
+           "roofline": {"bound": "hbm", "kernel": "pml_batch_value_and_gradient_dev (all kernels of one batched evaluation)",
+                        "algorithmic_bytes": int(nbytes), "value_bytes_per_entry": int(info.value_bytes),
+                        "achieved": nbytes / per_dev / 1e9, "peak": peak, "unit": "GB/s", "frac": nbytes / per_dev / 1e9 / peak}}
     # every entity's L2-regularised logistic problem solved to TRON's tolerance in lock step, state in device memory
-    # (what RandomEffectCoordinate.updateModel does one entity at a time, RandomEffectCoordinate.scala:108-119)
+    # (what RandomEffectCoordinate.updateModel does one entity at a time, RandomEffectCoordinate.scala:108-119);
+    # "skip": converged entities are masked out and their rows are no longer streamed; "stream-all": as in round 1
     from photon_ml_b200.batched import BatchedTRON, REASONS
     del t_coef, t_val, t_grad
-    solver = BatchedTRON(batch, pml.LOGISTIC, l2RegWeight=1.0)
-    t0 = time.perf_counter()
-    _, _, info = solver.optimize()
-    wall = time.perf_counter() - t0
-    out["lockstep_tron_logistic_l2_1"] = {
-        "wall_s": wall, "entities_solved_per_s": n_ent / wall, "batched_value_gradient_evals": info["evaluations"],
-        "batched_hessian_vector_evals": info["hessian_vector_evaluations"],
-        "mean_iterations_per_entity": float(info["iterations"].mean()),
-        "reasons": {REASONS[c]: int((info["reasons"] == c).sum()) for c in range(len(REASONS))}}
+    for mode in solver_runs:
+        solver = BatchedTRON(batch, pml.LOGISTIC, l2RegWeight=1.0, skip_converged=(mode == "skip"))
+        ctx.synchronize()
+        t0 = time.perf_counter()
+        _, _, sinfo = solver.optimize()
+        wall = time.perf_counter() - t0
+        out["lockstep_tron_logistic_l2_1" + ("" if mode == "skip" else "_streaming_converged_entities")] = {
+            "wall_s": wall, "entities_solved_per_s": n_ent / wall, "batched_value_gradient_evals": sinfo["evaluations"],
+            "batched_hessian_vector_evals": sinfo["hessian_vector_evaluations"],
+            "mean_iterations_per_entity": float(sinfo["iterations"].mean()),
+            "reasons": {REASONS[c]: int((sinfo["reasons"] == c).sum()) for c in range(len(REASONS))}}
     batch.close()
     return out
+
+
+def run_config4(args):
+    """configs[4], the random-effect half: 10 M per-member problems sharded over the GPUs by entity with the
+    reference's partitioner rule (bin packing of the heaviest entities, hash for the rest) and NO collective on the
+    data path; every rank solves its entities in lock step.  value = entities solved per second, whole job."""
+    import torch
+    import torch.distributed as dist
+    import photon_ml_b200 as pml
+    from photon_ml_b200 import parallel
+    from photon_ml_b200.batched import BatchedTRON, REASONS
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=device)
+    n_total = int(os.environ.get("PML_BENCH_ENTITIES", "10000000"))
+    rows_all = np.minimum(np.random.default_rng(5).zipf(1.8, size=n_total), 2000).astype(np.int64)   # same on every rank
+    assignment = parallel.shard_entities(rows_all, world, capacity=10000)
+    mine = np.flatnonzero(assignment == rank)
+    ctx = pml.Context(local_rank)
+    rng = np.random.default_rng(500 + rank)
+    ent_row_ptr, ent_dim, row_ptr, col, val, label = make_entity_problems(rng, len(mine), rows=rows_all[mine])
+    n = int(ent_row_ptr[-1])
+    t0 = time.perf_counter()
+    batch = pml.Batch(ctx, ent_row_ptr, ent_dim, row_ptr, col, val, label)
+    t_pack = time.perf_counter() - t0
+    del col, val
+    ext = torch.cuda.ExternalStream(ctx.stream, device=device)
+    t_coef = torch.randn(batch.d_total, dtype=torch.float64, device=device) * 0.2
+    t_val = torch.empty(len(mine), dtype=torch.float64, device=device)
+    t_grad = torch.empty(batch.d_total, dtype=torch.float64, device=device)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    with torch.cuda.stream(ext):
+        for _ in range(args.warmup):
+            batch.value_and_gradient_dev(pml.LOGISTIC, t_coef.data_ptr(), t_val.data_ptr(), t_grad.data_ptr())
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        a.record(ext)
+        for _ in range(args.steps):
+            batch.value_and_gradient_dev(pml.LOGISTIC, t_coef.data_ptr(), t_val.data_ptr(), t_grad.data_ptr())
+        b.record(ext)
+        barrier()
+        eval_ms = a.elapsed_time(b) / args.steps
+    del t_coef, t_val, t_grad
+    solver = BatchedTRON(batch, pml.LOGISTIC, l2RegWeight=1.0)
+    barrier()
+    t0 = time.perf_counter()
+    _, _, sinfo = solver.optimize()
+    ctx.synchronize()
+    wall = time.perf_counter() - t0
+    stats = torch.tensor([eval_ms, wall, float(n), float(len(mine)), float(sinfo["iterations"].sum())], dtype=torch.float64,
+                         device=device)
+    mx = stats.clone()
+    if world > 1:
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        dist.all_reduce(stats, op=dist.ReduceOp.SUM)
+    info = batch.dataset.info()
+    if rank == 0:
+        peak, peak_src = peaks()
+        eval_ms, wall = float(mx[0]), float(mx[1])
+        rows_total, ents_total = int(stats[2]), int(stats[3])
+        nbytes = batch_bytes(len(mine), n, n * 10, batch.d_total, info.value_bytes)
+        emit({
+            "metric": "per-entity problems solved/s (lock-step TRON, L2 logistic)", "value": ents_total / wall,
+            "unit": "entities/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": eval_ms,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "configs[4] random-effect coordinate: %d per-member problems (%d rows, 10 entries per row, "
+                                   "32-dim projected spaces), entities sharded over ranks, no collective" % (ents_total, rows_total),
+                       "entities_rank0": int(len(mine)), "rows_rank0": n, "rows_max_over_ranks": int(mx[2]),
+                       "partitioner": "bin packing of the 10000 heaviest entities + id mod N (RandomEffectDataSetPartitioner.scala:113-146)",
+                       "pack_s_rank0": round(t_pack, 2)},
+            "solve": {"wall_s_max_over_ranks": wall, "mean_iterations_per_entity": float(stats[4]) / ents_total,
+                      "batched_value_gradient_evals_rank0": sinfo["evaluations"],
+                      "batched_hessian_vector_evals_rank0": sinfo["hessian_vector_evaluations"],
+                      "reasons_rank0": {REASONS[c]: int((sinfo["reasons"] == c).sum()) for c in range(len(REASONS))}},
+            "batched_evaluation": {"ms_max_over_ranks": eval_ms, "entity_evaluations_per_s": ents_total / (eval_ms * 1e-3)},
+            "roofline": {"bound": "hbm", "kernel": "pml_batch_value_and_gradient_dev (rank 0's shard)",
+                         "algorithmic_bytes": int(nbytes), "achieved": nbytes / (eval_ms * 1e-3) / 1e9, "peak": peak,
+                         "unit": "GB/s", "frac": nbytes / (eval_ms * 1e-3) / 1e9 / peak, "peak_source": peak_src, "traffic": None},
+            "gpu_launches": int(ctx.launch_count),
+        })
+    batch.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+C2_FEATS = 10_000_000
+C2_ROWS_PER_GPU = 25_000_000
+C2_NNZ_PER_ROW = 39
+C2_GEN_CHUNK = 500_000
+# Above this many coefficients an 8-rank exchange goes through NCCL's in-switch all-reduce (+ finalize_dev) instead of
+# the peer-memory merge kernel: measured (profiles/r01_merge_latency.txt) 322 vs 275 us at d = 8 M on 8 GPUs, while the
+# peer kernel wins at every size on 2 and 4 GPUs and below ~4 M coefficients on 8.
+PEER_MERGE_MAX_D_AT_8 = 4_000_000
+
+
+def run_config2(args):
+    """configs[2]: Criteo-shaped sparse logistic regression, 200 M rows x 10 M hashed features on 8 GPUs -- 25 M rows
+    per GPU whatever N is (weak scaling): 39 entries per row (13 from a small dense range + 26 hashed Zipf(1.05)
+    categoricals), values 1.0 (stored as indices only), CTR ~3 %.  A step = one value+gradient evaluation of all
+    ranks' rows with one exchange of d+2 doubles; also the OWL-QN solve the configuration names (alpha = 1 and 0.5)."""
+    import torch
+    import torch.distributed as dist
+    import photon_ml_b200 as pml
+    from photon_ml_b200.function import DeviceGLMLossFunction, NoNormalization
+    from photon_ml_b200.optimization import OWLQN
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=device)
+    n_local = int(os.environ.get("PML_BENCH_ROWS_PER_GPU", C2_ROWS_PER_GPU))
+    D = C2_FEATS
+    ctx = pml.Context(local_rank)
+    ext = torch.cuda.ExternalStream(ctx.stream, device=device)
+    p = np.arange(1, D - 64 + 1, dtype=np.float64) ** -1.05
+    cdf = torch.from_numpy(np.cumsum(p / p.sum())).to(device)      # built on the host: the same bits on every rank
+    g = torch.Generator(device=device)
+    g.manual_seed(3_000 + rank)
+    t0 = time.time()
+    cols, labels = [], []
+    for _ in range(n_local // C2_GEN_CHUNK):
+        dense = torch.randint(0, 64, (C2_GEN_CHUNK, 13), generator=g, device=device)
+        hashed = 64 + torch.searchsorted(cdf, torch.rand((C2_GEN_CHUNK, 26), generator=g, device=device,
+                                                         dtype=torch.float64)).clamp_(max=D - 65)
+        cc, _ = torch.sort(torch.cat([dense, hashed], 1), dim=1)
+        cols.append(cc.to(torch.int32).reshape(-1))
+        labels.append((torch.rand(C2_GEN_CHUNK, generator=g, device=device) < 0.03).to(torch.float64))
+    cols, labels = torch.cat(cols), torch.cat(labels)
+    n_local = labels.numel()
+    vals = torch.ones(cols.numel(), dtype=torch.float32, device=device)
+    row_ptr = torch.arange(n_local + 1, dtype=torch.int64, device=device) * C2_NNZ_PER_ROW
+    torch.cuda.synchronize()
+    t_gen = time.time() - t0
+    t0 = time.time()
+    ds = pml.Dataset.from_device_pointers(ctx, n_local, D, row_ptr.data_ptr(), cols.data_ptr(), vals.data_ptr(), pml.abi.F32,
+                                          labels.data_ptr(), storage=pml.STORE_AUTO)
+    ctx.synchronize()
+    t_pack = time.time() - t0
+    del cols, vals, row_ptr, labels, cdf
+    torch.cuda.empty_cache()
+    info = ds.info()
+    coef = torch.randn(D, generator=g, device=device, dtype=torch.float64) * 0.05
+    if world > 1:
+        dist.broadcast(coef, 0)
+    raw = torch.empty(D + 2, dtype=torch.float64, device=device)
+    out_value = torch.empty(1, dtype=torch.float64, device=device)
+    out_grad = torch.empty(D, dtype=torch.float64, device=device)
+    peer, collective = None, "none"
+    if world > 1:
+        want_peer = os.environ.get("PML_BENCH_COLLECTIVE", "auto")
+        use_peer = want_peer == "peer" or (want_peer == "auto" and not (world >= 8 and D > PEER_MERGE_MAX_D_AT_8))
+        collective = "nccl all-reduce of d+2 doubles, then finalize_dev (chosen by size: d = %d on %d ranks)" % (D, world)
+        if use_peer:
+            peer = pml.Peer(ctx, D)
+            collective = "peer_merge_kernel: sums over NVLink peer memory in rank order, fused with getVector"
+            result = torch.as_tensor(peer.result_array(), device=device)
+            out_grad, out_value = result[:D], result[D:D + 1]
+
+    def step(w=coef):
+        if peer is not None:
+            peer.value_and_gradient(ds, pml.LOGISTIC, w.data_ptr())
+            return
+        ds.value_and_gradient_raw_dev(pml.LOGISTIC, w.data_ptr(), raw.data_ptr())
+        if world > 1:
+            dist.all_reduce(raw)
+        ds.finalize_dev(pml.LOGISTIC, raw.data_ptr(), out_value.data_ptr(), out_grad.data_ptr())
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    class ShardedObjective(DeviceGLMLossFunction):
+        """calculate() over all ranks' rows: every rank runs the same optimizer on the same (bit-identical) results."""
+
+        def calculate(self, data, coefficients, normalizationContext, want_gradient=True):
+            step(coefficients)
+            f = float(out_value)
+            return f, (out_grad.clone() if want_gradient else None)
+
+    with torch.cuda.stream(ext):
+        for _ in range(args.warmup):
+            step()
+        barrier()
+        sampler = ClockSampler(local_rank)
+        if rank == 0:
+            sampler.start()
+        launches0 = ctx.launch_count
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        a.record(ext)
+        for _ in range(args.steps):
+            step()
+        b.record(ext)
+        barrier()
+        ms = a.elapsed_time(b)
+        launches = ctx.launch_count - launches0
+        clocks = sampler.stop() if rank == 0 else None
+        ctx.read_profile()
+        ctx.set_profiling(True)
+        for _ in range(3):
+            step()
+        barrier()
+        profile = ctx.read_profile()
+        ctx.set_profiling(False)
+        # end to end: host coefficients in, host gradient out (every rank its slice when the peer exchange is in use)
+        h_coef = torch.empty(D, dtype=torch.float64).pin_memory()
+        h_coef.copy_(coef.cpu())
+        h_grad = torch.empty(D, dtype=torch.float64).pin_memory()
+        h_coef_np, h_grad_np = h_coef.numpy(), h_grad.numpy()
+
+        def e2e_step():
+            if world == 1:
+                return ds.value_and_gradient(pml.LOGISTIC, h_coef_np, out=h_grad_np)[0]
+            if peer is not None:
+                return peer.value_and_gradient_host(ds, pml.LOGISTIC, h_coef_np, h_grad_np)
+            coef.copy_(h_coef, non_blocking=True)          # every rank holds the vector on its host (Spark broadcast)
+            step()
+            h_grad.copy_(out_grad, non_blocking=True)
+            ext.synchronize()
+            return float(out_value)
+
+        for _ in range(3):
+            e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            e2e_value = e2e_step()
+        barrier()
+        e2e_s = time.perf_counter() - t0
+        # the configuration's optimizer: OWL-QN, L1 (alpha = 1) and elastic net (alpha = 0.5; the reference mixes the L2
+        # part in only for RegularizationType.L2, so ELASTIC_NET gets the L1 part alone: DistributedGLMLossFunction.scala:160-169)
+        owlqn = {}
+        if not args.no_convergence:
+            for alpha in (1.0, 0.5):
+                opt = OWLQN(alpha * 1.0, NoNormalization(), maxNumIterations=int(os.environ.get("PML_BENCH_OWLQN_ITERS", "30")))
+                obj = ShardedObjective(ctx, pml.LOGISTIC)
+                barrier()
+                t0 = time.perf_counter()
+                w, f = opt.optimize(obj, torch.zeros(D, dtype=torch.float64, device=device), ds)
+                barrier()
+                owlqn["alpha_%g" % alpha] = {"wall_s": time.perf_counter() - t0, "iterations": opt.currentState.iter,
+                                             "evaluations": opt.evaluations, "reason": opt.convergenceReason, "objective": f,
+                                             "nonzero_coefficients": int((w != 0).sum())}
+    times = torch.tensor([ms, e2e_s], dtype=torch.float64, device=device)
+    if world > 1:
+        dist.all_reduce(times, op=dist.ReduceOp.MAX)
+    ms, e2e_s = float(times[0]), float(times[1])
+    if rank == 0:
+        peak, peak_src = peaks()
+        per = lambda k: profile[k][0] / max(1, profile[k][1])   # noqa: E731
+        ms_per_step = ms / args.steps
+        V = info.value_bytes
+        n, nnz = info.n, info.nnz
+        step_bytes = 2 * nnz * (V + 4) + 28 * n + 28 * D       # per GPU: two entry streams, label + r written and read, w, g
+        row_bytes = nnz * (V + 4) + (n + 1) * 4 + n * 16 + D * 8
+        col_bytes = nnz * (V + 4) + n * 8 + D * 12
+        row_ms = per("row_pass") + per("row_epilogue")
+        col_ms = per("col_pass") + per("col_pass_tiled")
+        dom_bytes, dom_ms, dom = ((col_bytes, col_ms, "CSC pass X^T r (tiled hot columns + cold columns in super blocks)")
+                                  if col_ms >= row_ms else (row_bytes, row_ms, "CSR pass X w (seg_spmv_warp_kernel + row epilogue)"))
+        emit({
+            "metric": "value+gradient evals/s", "value": 1e3 / ms_per_step, "unit": "evals/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "configs[2]: Criteo-shaped logistic, %d rows per GPU x %d hashed features, %d entries per row, "
+                                   "indicator values stored as indices only" % (n, D, C2_NNZ_PER_ROW),
+                       "rows_total": int(n) * world, "rows_per_gpu": int(n), "nnz_per_gpu": int(nnz), "d": D,
+                       "value_bytes_per_entry": int(V), "collective": collective,
+                       "l2_flush": "inputs larger than L2 (%.1f GB streamed per step per GPU)" % (step_bytes / 1e9),
+                       "csc_tiling": {"hot_cols": int(info.tiled_hot_cols), "tiles": int(info.tiled_tiles),
+                                      "tile_rows": int(info.tiled_tile_rows)},
+                       "device_GB": info.device_bytes / 1e9, "generate_s": round(t_gen, 1), "pack_s": round(t_pack, 2)},
+            "rows_per_s": int(n) * world / (ms_per_step * 1e-3),
+            "e2e": {"value": args.steps / e2e_s, "unit": "evals/s", "h2d_bytes_per_step": D * 8,
+                    "d2h_bytes_per_step": D * 8 + 8 * world, "ms_per_step": 1e3 * e2e_s / args.steps, "objective": e2e_value},
+            "gpu_launches": int(launches), "clocks": clocks,
+            "roofline": {"bound": "hbm", "kernel": dom, "achieved": dom_bytes / (dom_ms * 1e-3) / 1e9, "peak": peak,
+                         "unit": "GB/s", "frac": dom_bytes / (dom_ms * 1e-3) / 1e9 / peak, "peak_source": peak_src,
+                         "traffic": None, "algorithmic_bytes_per_launch": int(dom_bytes), "avg_launch_ms": dom_ms},
+            "step": {"algorithmic_bytes_per_gpu": int(step_bytes), "GBps_per_gpu": step_bytes / (ms_per_step * 1e-3) / 1e9,
+                     "frac": step_bytes / (ms_per_step * 1e-3) / 1e9 / peak},
+            "kernels": {k: {"ms_per_launch": v[0] / max(1, v[1]), "launches": int(v[1])} for k, v in profile.items()},
+            "owlqn_logistic_lambda_1": owlqn,
+        })
+    ds.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
 
 
 def full_rows_on_host():
@@ -870,11 +1201,18 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-convergence", action="store_true")
     ap.add_argument("--no-parity", action="store_true")
+    ap.add_argument("--config", type=int, default=1, choices=[1, 2, 4],
+                    help="BASELINE.json configs index: 1 = the headline workload (default); 2 = Criteo-shaped logistic, "
+                         "25 M rows per GPU (weak scaling); 4 = the random-effect coordinate, entities sharded over GPUs")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = 3
     if args.impl == "reference":
         run_reference(args)
+    elif args.config == 4:
+        run_config4(args)
+    elif args.config == 2:
+        run_config2(args)
     else:
         run_ours(args)
 

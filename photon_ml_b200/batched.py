@@ -16,6 +16,8 @@ that.  torch is used for the per-entity scalar bookkeeping (E-sized element-wise
 """
 import numpy as np
 
+from .function import _TAGS
+
 MAX_ITERATIONS, OBJECTIVE_NOT_IMPROVING, FUNCTION_VALUES_CONVERGED, GRADIENT_CONVERGED = 0, 1, 2, 3
 REASONS = ["MaxIterations", "ObjectiveNotImproving", "FunctionValuesConverged", "GradientConverged"]
 
@@ -23,7 +25,8 @@ REASONS = ["MaxIterations", "ObjectiveNotImproving", "FunctionValuesConverged", 
 class BatchedTRON:
     MAX_CG_ITERATIONS = 20      # TRON.scala:97-98
 
-    def __init__(self, batch, loss, l2RegWeight=0.0, tolerance=1.0e-5, maxNumIterations=15, maxNumImprovementFailures=5):
+    def __init__(self, batch, loss, l2RegWeight=0.0, tolerance=1.0e-5, maxNumIterations=15, maxNumImprovementFailures=5,
+                 skip_converged=True):
         import torch
         self.torch = torch
         self.batch, self.loss, self.l2 = batch, loss, float(l2RegWeight)
@@ -37,6 +40,7 @@ class BatchedTRON:
         self.evaluations = 0
         self.hessian_vector_evaluations = 0
         self._tag = 0
+        self.skip_converged, self._masked, self._mask8 = bool(skip_converged), False, None
 
     # ---- the library's batched kernels -------------------------------------------------------------------------
     def _new(self, n, dtype=None):
@@ -53,8 +57,24 @@ class BatchedTRON:
                                      None if y is None else y.data_ptr(), out.data_ptr(),
                                      None if active is None else active.data_ptr())
 
-    def _objective(self, w):
+    def _only(self, mask):
+        """Entities outside `mask` (a bool tensor; None = everybody) drop out of the next evaluations: their results
+        come back as 0 and -- the point -- their rows are no longer streamed (pml_batch_set_active_dev).  In the
+        reference a converged entity's solve has simply ended (RandomEffectCoordinate.scala:112-119)."""
+        if not self.skip_converged:
+            return
+        if mask is None:
+            if self._masked:
+                self.batch.set_active_dev(None)
+                self._masked = False
+            return
+        self._mask8 = mask.to(self.torch.uint8)      # kept alive until the next mask replaces it
+        self.batch.set_active_dev(self._mask8.data_ptr())
+        self._masked = True
+
+    def _objective(self, w, only=None):
         """(value[E], gradient[D]) with the L2 term of L2RegularizationDiff (lib/function/L2Regularization.scala:69-125)."""
+        self._only(only)
         f, g = self._new(self.E), self._new(self.D)
         self.batch.value_and_gradient_dev(self.loss, w.data_ptr(), f.data_ptr(), g.data_ptr())
         self.evaluations += 1
@@ -92,6 +112,7 @@ class BatchedTRON:
                 break
             run = ~done
             iters += run
+            self._only(run)                          # within one coefficient tag the set only ever shrinks
             Hd = self._hessian_vector(w, direction)
             alpha = rTr / self._dot(direction, Hd)
             run8 = run.to(torch.uint8)
@@ -126,7 +147,7 @@ class BatchedTRON:
         with torch.cuda.stream(self.stream):
             w = torch.zeros(self.D, dtype=torch.float64, device=self.device) if initial is None else \
                 torch.as_tensor(initial, dtype=torch.float64, device=self.device).clone()
-            self._tag += 1
+            self._tag = next(_TAGS)
             f0, g0 = self._objective(torch.zeros_like(w))           # tolerances from the state at zero (Optimizer.scala:68-71)
             loss_tol = f0 * self.tol
             grad_tol = self._dot(g0, g0).sqrt() * self.tol
@@ -147,13 +168,13 @@ class BatchedTRON:
                 failures = torch.zeros(self.E, dtype=torch.int64, device=self.device)
                 attempting = active.clone()
                 while bool(attempting.any()):
-                    self._tag += 1                                   # new coefficient vector for the curvature cache
+                    self._tag = next(_TAGS)                                   # new coefficient vector for the curvature cache
                     cg_iters, step, residual = self._truncated_cg(w, g, delta, attempting)
                     cg_total += cg_iters
                     w_try = w + step
                     gs = self._dot(g, step)
                     predicted = -0.5 * (gs - self._dot(step, residual))
-                    f_try, g_try = self._objective(w_try)
+                    f_try, g_try = self._objective(w_try, only=attempting)
                     actual = f - f_try
                     step_norm = self._dot(step, step).sqrt()
                     delta = torch.where(attempting & first, torch.minimum(delta, step_norm), delta)
@@ -188,6 +209,7 @@ class BatchedTRON:
                 newly = active & (r >= 0)
                 reason = torch.where(newly, r, reason)
                 done = done | newly
+            self._only(None)
             self.batch.ctx.synchronize()
             info = {"iterations": it.cpu().numpy(), "reasons": reason.cpu().numpy(), "cg_iterations": cg_total.cpu().numpy(),
                     "evaluations": self.evaluations, "hessian_vector_evaluations": self.hessian_vector_evaluations}

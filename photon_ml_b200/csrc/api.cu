@@ -140,6 +140,7 @@ int run_col_and_fixup(pml_dataset *ds, bool square, double *out, bool with_scala
     cp.table = ds->r;
     cp.carry = ds->carry_head;
     cp.n_chunks = ds->t.n_chunks;
+    cp.active = ds->col_chunk_active;
     // cold columns cut into super blocks of rows: per-(super block, column) sums (slots without a run stay zero from
     // pack time), then one reduction over the blocks
     const bool super = ds->t.n_super > 1;
@@ -176,6 +177,7 @@ int run_rows(pml_dataset *ds, RowPassParams &rp, bool two)
     // scores) are fastest on the entry-chunked kernel (1.06 ms vs 1.29 ms at 50 entries/row); the paired
     // (ec, ev) pass of a cold Hessian-vector product is fastest with lanes-per-row (1.59 vs 2.35 ms).
     const int variant = ds->variant_forced ? ds->lanes_per_row : (two ? ds->lanes_per_row : 1);
+    rp.block_active = rp.mode == MODE_SCORE ? nullptr : ds->row_block_active;
     if (variant != 1) {
         return run(ctx, PML_K_ROW, [&] {
             return launch_row_pass(s, ctx->sm_count, ds->value_bytes, variant, two, rp, &ds->row_grid);
@@ -202,6 +204,8 @@ int run_rows(pml_dataset *ds, RowPassParams &rp, bool two)
     sp.carry = ds->carry_row;
     sp.carry2 = two ? ds->carry_row2 : nullptr;
     sp.n_chunks = ds->rs.n_chunks;
+    // (scores are wanted for every row, masked entities included)
+    sp.active = rp.mode == MODE_SCORE ? nullptr : ds->row_chunk_active;
     PML_TRY(run(ctx, PML_K_ROW, [&] {
         return launch_seg_spmv(s, ctx->sm_count, ds->value_bytes, two, false, sp, ds->t.m);
     }));
@@ -585,7 +589,7 @@ int pml_dataset_destroy(pml_dataset *ds)
     void *ptrs[] = { ds->row_ptr, ds->col, ds->val, ds->label, ds->offset, ds->weight, ds->t.idx_alloc, ds->t.val_alloc, ds->t.hot.idx16, ds->t.hot.uniform, ds->t.hot.run_id, ds->t.hot.chunk_lo, ds->t.hot.tile_first_chunk, ds->t.hot.fix,
                      ds->t.hot.partial, ds->t.hot.carry, ds->t.cold_slot, ds->t.cold_partial,
                      ds->t.nzcol_ptr, ds->t.nzcol_id, ds->t.rank, ds->t.chunk_col_lo, ds->t.fix, ds->rs.nzrow_id, ds->rs.chunk_lo,
-                     ds->rs.fix, ds->za, ds->zb, ds->carry_row, ds->carry_row2, ds->row_loss, ds->factors, ds->shifts, ds->r,
+                     ds->rs.fix, ds->za, ds->zb, ds->carry_row, ds->carry_row2, ds->row_loss, ds->row_chunk_active, ds->col_chunk_active, ds->row_block_active, ds->factors, ds->shifts, ds->r,
                      ds->dcache, ds->partials, ds->carry_head, ds->raw, ds->vec, ds->shift_partials, ds->io_a, ds->io_b,
                      ds->io_n };
     for (void *p : ptrs)
@@ -1532,6 +1536,38 @@ int pml_batch_segment_axpby_dev(pml_batch *b, const double *a_dev, const double 
     });
 }
 
+// After the mask changed: which chunks of the CSR / CSC streams and which 32-row blocks still hold an active entity
+// (the evaluation kernels skip the others).  PML_NO_SKIP_INACTIVE=1 keeps streaming everything (A/B measurements).
+static int batch_refresh_flags(pml_batch *b)
+{
+    pml_dataset *ds = b->ds;
+    cudaStream_t s = ds->ctx->stream;
+    static const bool off = std::getenv("PML_NO_SKIP_INACTIVE") != nullptr;
+    const bool had = ds->row_chunk_active != nullptr;
+    if (b->active_dev == nullptr || off || ds->n == 0 || ds->nnz == 0 || ds->t.hot.n_chunks > 0 || ds->t.n_super > 1) {
+        if (had) {
+            PML_CUDA(cudaStreamSynchronize(s));
+            cudaFree(ds->row_chunk_active);
+            cudaFree(ds->col_chunk_active);
+            cudaFree(ds->row_block_active);
+            ds->row_chunk_active = ds->col_chunk_active = ds->row_block_active = nullptr;
+            ++ds->version;  // the captured sequences hold the old pointers
+        }
+        return PML_OK;
+    }
+    PML_TRY(batch_index(b, true));
+    if (!had) {
+        PML_CUDA(cudaMalloc(&ds->row_chunk_active, (size_t)ds->rs.n_chunks + 1));
+        PML_CUDA(cudaMalloc(&ds->col_chunk_active, (size_t)ds->t.n_chunks + 1));
+        PML_CUDA(cudaMalloc(&ds->row_block_active, (size_t)((ds->n + 31) / 32) + 1));
+        ++ds->version;
+    }
+    return count(ds->ctx, launch_active_flags(s, b->n_entities, b->active_dev, b->ent_row_ptr, ds->n, ds->nnz, ds->row_ptr,
+                                              ds->rs.n_chunks, ds->row_chunk_active, ds->row_block_active, ds->t.m,
+                                              ds->t.nzcol_ptr, ds->t.nzcol_id, b->ent_of_coef, ds->t.cold_nnz, ds->t.n_chunks,
+                                              ds->col_chunk_active));
+}
+
 int pml_batch_set_active(pml_batch *b, const uint8_t *active)
 {
     if (!b || !b->ds) return fail(PML_EINVAL, "null batch handle");
@@ -1545,12 +1581,13 @@ int pml_batch_set_active(pml_batch *b, const uint8_t *active)
             cudaFree(b->active_dev);
             b->active_dev = nullptr;
         }
-        return PML_OK;
+        return batch_refresh_flags(b);
     }
     if (b->n_entities == 0) return PML_OK;
     PML_TRY(batch_index(b, false));
     if (b->active_dev == nullptr) PML_CUDA(cudaMalloc(&b->active_dev, (size_t)b->n_entities));
     PML_CUDA(cudaMemcpyAsync(b->active_dev, active, (size_t)b->n_entities, cudaMemcpyHostToDevice, s));
+    PML_TRY(batch_refresh_flags(b));
     PML_CUDA(cudaStreamSynchronize(s));
     return PML_OK;
 }
@@ -1568,13 +1605,13 @@ int pml_batch_set_active_dev(pml_batch *b, const uint8_t *active_dev)
             cudaFree(b->active_dev);
             b->active_dev = nullptr;
         }
-        return PML_OK;
+        return batch_refresh_flags(b);
     }
     if (b->n_entities == 0) return PML_OK;
     PML_TRY(batch_index(b, false));
     if (b->active_dev == nullptr) PML_CUDA(cudaMalloc(&b->active_dev, (size_t)b->n_entities));
     PML_CUDA(cudaMemcpyAsync(b->active_dev, active_dev, (size_t)b->n_entities, cudaMemcpyDeviceToDevice, s));
-    return PML_OK;
+    return batch_refresh_flags(b);
 }
 
 // ---- the merge step across GPUs over peer memory (peer.cu) ------------------------------------

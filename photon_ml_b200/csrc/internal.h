@@ -67,6 +67,7 @@ struct RowPassParams {
     double *dcache;           // n: wt*l''(z) written (HV_COLD) or read (HV_CACHED)
     double *partials;         // 2 * gridDim.x: per-CTA (F, P)
     double *row_loss;         // n or null: wt_i * l_i per row (batched per-entity values)
+    const unsigned char *block_active;  // (n+31)/32 or null: 0 = every row of the 32-row block belongs to a masked entity
     int mode;
     int loss;
 };
@@ -82,6 +83,7 @@ struct SegParams {
     double *carry, *carry2;   // n_chunks: sum of the part of a chunk that precedes its first run start
     int n_chunks;
     int n_hot;                // leading table entries staged in shared memory (set by the launcher)
+    const unsigned char *active;  // n_chunks or null: 0 = every entry of the chunk belongs to a masked entity (skipped)
 };
 
 struct FixEntry {
@@ -129,6 +131,10 @@ int launch_scale(cudaStream_t s, int64_t d, const double *x, const double *f, do
 int launch_absorb_shift(cudaStream_t s, int64_t n_entities, const int64_t *icpt_pos, const double *dots, double *vec);
 int launch_batch_finalize(cudaStream_t s, int64_t d, const int32_t *ent_of, const double *V, const double *factors,
                           const double *shifts, const int64_t *icpt_pos, double *out);
+int launch_active_flags(cudaStream_t s, int64_t n_entities, const unsigned char *active, const int64_t *ent_row_ptr,
+                        int64_t n, int64_t nnz, const uint32_t *row_ptr, int n_row_chunks, unsigned char *row_chunk_active,
+                        unsigned char *row_block_active, int64_t m, const uint32_t *nzcol_ptr, const int32_t *nzcol_id,
+                        const int32_t *ent_of_coef, int64_t col_nnz, int n_col_chunks, unsigned char *col_chunk_active);
 int launch_mask_entities(cudaStream_t s, int64_t n_entities, const int64_t *coef_ptr, const uint8_t *active, double *values,
                          double *vec);
 
@@ -324,6 +330,8 @@ struct pml_dataset {
     double *io_n = nullptr;        // n, lazily: scores output staging
     double *row_loss = nullptr;    // n, lazily: per-row wt*l for per-entity objective values (pml_batch)
     bool want_row_loss = false;
+    // batches with a mask (pml_batch_set_active): which chunks / row blocks still hold rows of an active entity
+    unsigned char *row_chunk_active = nullptr, *col_chunk_active = nullptr, *row_block_active = nullptr;
     uint64_t cached_tag = 0;
     int cached_loss = -1;
     bool cache_valid = false;

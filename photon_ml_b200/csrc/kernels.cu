@@ -142,6 +142,7 @@ __global__ void __launch_bounds__(R_THREADS, 5) row_pass_kernel(const RowPassPar
     double accF = 0.0, accP = 0.0;
     const int64_t n_blk = (p.n + 31) >> 5;
     for (int64_t blk = (int64_t)blockIdx.x * R_WARPS + warp; blk < n_blk; blk += (int64_t)gridDim.x * R_WARPS) {
+        if (p.block_active != nullptr && !p.block_active[blk]) continue;  // all 32 rows belong to masked entities
         const int64_t row0 = blk << 5;
         const int64_t my_row = row0 + lane;
         const int64_t clamp_lo = my_row < p.n ? my_row : p.n;
@@ -641,20 +642,29 @@ __global__ void __launch_bounds__(SW_THREADS, 1024 / SW_THREADS) seg_spmv_warp_k
     const uint32_t hot_at = shared_window_address(hot);
     const int n_full = (int)(p.nnz / CHUNK);
     const int stride = gridDim.x * WARPS;
+    // Batches with masked entities (pml_batch_set_active): a chunk whose entries all belong to masked entities is
+    // neither loaded nor reduced -- converged entities stop costing bandwidth.  Whatever such a chunk would have
+    // written (run sums, its carry) feeds masked entities only, whose results the caller overwrites.
+    const unsigned char *__restrict__ active = p.active;
     SegRegs<VT, ITEMS> cur;
     int c = blockIdx.x * WARPS + warp;
-    if (c < n_full) seg_load_full<VT, ITEMS>(cur, idx, val, (int64_t)c * CHUNK + lane * ITEMS);
+    bool live = c < n_full && (active == nullptr || active[c] != 0);
+    if (live) seg_load_full<VT, ITEMS>(cur, idx, val, (int64_t)c * CHUNK + lane * ITEMS);
     for (; c < n_full; c += stride) {
         SegRegs<VT, ITEMS> nxt;
         const int cn = c + stride;
-        if (cn < n_full) seg_load_full<VT, ITEMS>(nxt, idx, val, (int64_t)cn * CHUNK + lane * ITEMS);
+        const bool live_nxt = cn < n_full && (active == nullptr || active[cn] != 0);
+        if (live_nxt) seg_load_full<VT, ITEMS>(nxt, idx, val, (int64_t)cn * CHUNK + lane * ITEMS);
         // (not for the cold CSC columns: their gathers of r live in L2 and the extra lines cost them more than
         // the stream gains -- measured 0.42 -> 0.52 ms)
-        if (HOT && cn + (PF_AHEAD - 1) * stride < n_full) seg_prefetch_l2<VT, ITEMS>(idx, val, cn + (PF_AHEAD - 1) * stride);
-        seg_chunk<VT, ITEMS, TWO, SQUARE, LOOKUP, true>(p, cur, c, ITEMS, hot_at);
+        if (HOT && active == nullptr && cn + (PF_AHEAD - 1) * stride < n_full)
+            seg_prefetch_l2<VT, ITEMS>(idx, val, cn + (PF_AHEAD - 1) * stride);
+        if (live) seg_chunk<VT, ITEMS, TWO, SQUARE, LOOKUP, true>(p, cur, c, ITEMS, hot_at);
         cur = nxt;
+        live = live_nxt;
     }
-    if (n_full < p.n_chunks && (int)(blockIdx.x * WARPS + warp) == n_full % stride) {
+    if (n_full < p.n_chunks && (int)(blockIdx.x * WARPS + warp) == n_full % stride &&
+        (active == nullptr || active[n_full] != 0)) {
         const int64_t base = (int64_t)n_full * CHUNK;
         const int cnt = (int)(p.nnz - base);
         seg_load<VT, ITEMS>(cur, idx, val, base + lane * ITEMS, cnt - lane * ITEMS);
@@ -811,6 +821,7 @@ int launch_seg_tiled(cudaStream_t s, int sm_count, int value_bytes, bool square,
     p.carry2 = nullptr;
     p.n_chunks = t.n_chunks;
     p.n_hot = 0x7fffffff;  // every index is a shared-memory index
+    p.active = nullptr;
     const size_t smem = sizeof(double) * (size_t)(t.tile_rows + 1);
     const int grid = t.n_tiles < sm_count ? t.n_tiles : sm_count;
 #define PML_TILED(VT, SQ)                                                                                           \
@@ -929,6 +940,7 @@ __global__ void __launch_bounds__(E_THREADS) row_epilogue_kernel(const RowPassPa
     const double fs = (p.mode == MODE_HV_CACHED) ? shift0 : shift1;
     double accF = 0.0, accP = 0.0;
     for (int64_t i = (int64_t)blockIdx.x * E_THREADS + threadIdx.x; i < p.n; i += (int64_t)gridDim.x * E_THREADS) {
+        if (p.block_active != nullptr && !p.block_active[i >> 5]) continue;
         const double o = p.offset ? __ldcs(p.offset + i) : 0.0;
         const double wt = p.weight ? __ldcs(p.weight + i) : 1.0;
         const double dot = __ldcs(za + i);
@@ -1089,6 +1101,109 @@ int launch_finalize(cudaStream_t s, int d, const double *raw, const double *fact
     if (grid > 2048) grid = 2048;
     finalize_kernel<<<grid, 256, 0, s>>>(d, raw, factors, shifts, out_value, out_vec);
     return cudaGetLastError() == cudaSuccess ? 1 : -1;
+}
+
+// ------------------------------------------------------------------------------------------
+// Which chunks of the two entry streams, and which 32-row blocks, still hold rows of an ACTIVE entity of a batch
+// (pml_batch_set_active).  An entity's rows are contiguous, and so are its columns in the block-diagonal data set, so
+// a chunk touches a contiguous range of entities: found by binary search, one thread per chunk / block.  In the
+// reference a converged entity's solve simply ends (RandomEffectCoordinate.scala:112-119 ->
+// SingleNodeOptimizationProblem.scala:85-103); here its rows stop being streamed.
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ int64_t last_not_above_u32(const uint32_t *__restrict__ a, int64_t n, uint32_t key)
+{
+    int64_t lo = 0, hi = n;  // largest i in [0, n] with a[i] <= key (a[0] = 0)
+    while (lo < hi) {
+        const int64_t mid = (lo + hi + 1) >> 1;
+        if (a[mid] <= key) lo = mid;
+        else hi = mid - 1;
+    }
+    return lo;
+}
+
+__device__ __forceinline__ int64_t last_not_above_i64(const int64_t *__restrict__ a, int64_t n, int64_t key)
+{
+    int64_t lo = 0, hi = n;
+    while (lo < hi) {
+        const int64_t mid = (lo + hi + 1) >> 1;
+        if (a[mid] <= key) lo = mid;
+        else hi = mid - 1;
+    }
+    return lo;
+}
+
+__device__ __forceinline__ unsigned char any_active(const unsigned char *__restrict__ active, int64_t e0, int64_t e1)
+{
+    for (int64_t e = e0; e <= e1; ++e)
+        if (active[e]) return 1;
+    return 0;
+}
+
+__global__ void __launch_bounds__(256)
+row_flags_kernel(int64_t n_entities, const unsigned char *__restrict__ active, const int64_t *__restrict__ ent_row_ptr,
+                 int64_t n, int64_t nnz, const uint32_t *__restrict__ row_ptr, int n_chunks,
+                 unsigned char *__restrict__ chunk_active, unsigned char *__restrict__ block_active)
+{
+    const int64_t n_blocks = (n + 31) >> 5;
+    for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < n_chunks + n_blocks;
+         q += (int64_t)gridDim.x * blockDim.x) {
+        int64_t r0, r1;
+        if (q < n_chunks) {
+            const int64_t k0 = q * SEG_CHUNK, k1 = (k0 + SEG_CHUNK < nnz ? k0 + SEG_CHUNK : nnz) - 1;
+            r0 = last_not_above_u32(row_ptr, n, (uint32_t)k0);
+            r1 = last_not_above_u32(row_ptr, n, (uint32_t)k1);
+        } else {
+            r0 = (q - n_chunks) << 5;
+            r1 = r0 + 31 < n ? r0 + 31 : n - 1;
+        }
+        if (r0 >= n) r0 = n - 1;
+        if (r1 >= n) r1 = n - 1;
+        const int64_t e0 = last_not_above_i64(ent_row_ptr, n_entities, r0);
+        const int64_t e1 = last_not_above_i64(ent_row_ptr, n_entities, r1);
+        const unsigned char a = any_active(active, e0 < n_entities ? e0 : n_entities - 1, e1 < n_entities ? e1 : n_entities - 1);
+        if (q < n_chunks) chunk_active[q] = a;
+        else block_active[q - n_chunks] = a;
+    }
+}
+
+__global__ void __launch_bounds__(256)
+col_flags_kernel(const unsigned char *__restrict__ active, int64_t m, const uint32_t *__restrict__ nzcol_ptr,
+                 const int32_t *__restrict__ nzcol_id, const int32_t *__restrict__ ent_of_coef, int64_t nnz, int n_chunks,
+                 unsigned char *__restrict__ chunk_active)
+{
+    for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < n_chunks; q += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t k0 = q * SEG_CHUNK, k1 = (k0 + SEG_CHUNK < nnz ? k0 + SEG_CHUNK : nnz) - 1;
+        int64_t j0 = last_not_above_u32(nzcol_ptr, m, (uint32_t)k0);
+        int64_t j1 = last_not_above_u32(nzcol_ptr, m, (uint32_t)k1);
+        if (j0 >= m) j0 = m - 1;
+        if (j1 >= m) j1 = m - 1;
+        // the batch keeps the caller's column order, so internal ids are monotone in the entity
+        chunk_active[q] = any_active(active, ent_of_coef[nzcol_id[j0]], ent_of_coef[nzcol_id[j1]]);
+    }
+}
+
+int launch_active_flags(cudaStream_t s, int64_t n_entities, const unsigned char *active, const int64_t *ent_row_ptr,
+                        int64_t n, int64_t nnz, const uint32_t *row_ptr, int n_row_chunks, unsigned char *row_chunk_active,
+                        unsigned char *row_block_active, int64_t m, const uint32_t *nzcol_ptr, const int32_t *nzcol_id,
+                        const int32_t *ent_of_coef, int64_t col_nnz, int n_col_chunks, unsigned char *col_chunk_active)
+{
+    if (n_entities <= 0 || n <= 0) return 0;
+    int launched = 0;
+    {
+        int64_t grid = (n_row_chunks + ((n + 31) >> 5) + 255) / 256;
+        if (grid > 148 * 16) grid = 148 * 16;
+        row_flags_kernel<<<(int)grid, 256, 0, s>>>(n_entities, active, ent_row_ptr, n, nnz, row_ptr, n_row_chunks,
+                                                   row_chunk_active, row_block_active);
+        ++launched;
+    }
+    if (n_col_chunks > 0 && m > 0) {
+        int64_t grid = (n_col_chunks + 255) / 256;
+        if (grid > 148 * 16) grid = 148 * 16;
+        col_flags_kernel<<<(int)grid, 256, 0, s>>>(active, m, nzcol_ptr, nzcol_id, ent_of_coef, col_nnz, n_col_chunks,
+                                                   col_chunk_active);
+        ++launched;
+    }
+    return cudaGetLastError() == cudaSuccess ? launched : -1;
 }
 
 // Entities taken out of a batched evaluation (pml_batch_set_active): their value and their slice of the

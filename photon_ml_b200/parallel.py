@@ -29,15 +29,19 @@ def shard_rows_by_nnz(row_ptr, world):
     return [(cuts[r], cuts[r + 1]) for r in range(world)]
 
 
-def shard_entities(rows_per_entity, world):
+def shard_entities(rows_per_entity, world, capacity=None):
     """Greedy bin packing: entities by descending row count, each to the least loaded rank.
     Returns assignment[e] = rank.  Ties resolve to the lowest rank / lowest entity id, so every
-    rank computes the same map without communication."""
+    rank computes the same map without communication.  `capacity` is the reference's partitionerCapacity
+    (RandomEffectDataSetPartitioner.scala:117, default 10000 there): only that many of the heaviest entities go
+    through the heap, the others fall back to the hash partitioner (:74-84; entity id mod world here)."""
     rows_per_entity = np.asarray(rows_per_entity, dtype=np.int64)
     order = np.argsort(-rows_per_entity, kind="stable")
     heap = [(0, r) for r in range(world)]
     heapq.heapify(heap)
-    assignment = np.empty(len(rows_per_entity), dtype=np.int32)
+    assignment = (np.arange(len(rows_per_entity)) % world).astype(np.int32)
+    if capacity is not None:
+        order = order[:capacity]
     for e in order:
         load, r = heapq.heappop(heap)
         assignment[e] = r

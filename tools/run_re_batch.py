@@ -1,6 +1,12 @@
-import sys, json, time
-sys.path.insert(0, "/root/repo")
-import bench, photon_ml_b200 as pml
+"""The per-entity batch of bench.py on its own: one batched evaluation with its roofline, and the lock-step solve
+with and without skipping the rows of converged entities."""
+import json
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import bench  # noqa: E402
+import photon_ml_b200 as pml  # noqa: E402
+
 ctx = pml.Context(0)
-out = bench.random_effect_batch(ctx)
-print(json.dumps(out, indent=1))
+print(json.dumps(bench.random_effect_batch(ctx), indent=1))
