@@ -794,6 +794,8 @@ def random_effect_batch(ctx, n_ent=1_000_000, seed=5, solver_runs=("skip", "stre
     # "skip": converged entities are masked out and their rows are no longer streamed; "stream-all": as in round 1
     from photon_ml_b200.batched import BatchedTRON, REASONS
     del t_coef, t_val, t_grad
+    # (one untimed solve first: the first Hessian-vector products allocate the curvature cache and capture the graphs)
+    BatchedTRON(batch, pml.LOGISTIC, l2RegWeight=1.0, maxNumIterations=2).optimize()
     for mode in solver_runs:
         solver = BatchedTRON(batch, pml.LOGISTIC, l2RegWeight=1.0, skip_converged=(mode == "skip"))
         ctx.synchronize()
@@ -859,6 +861,7 @@ def run_config4(args):
         barrier()
         eval_ms = a.elapsed_time(b) / args.steps
     del t_coef, t_val, t_grad
+    BatchedTRON(batch, pml.LOGISTIC, l2RegWeight=1.0, maxNumIterations=2).optimize()   # untimed: lazy buffers, graph captures
     solver = BatchedTRON(batch, pml.LOGISTIC, l2RegWeight=1.0)
     barrier()
     t0 = time.perf_counter()

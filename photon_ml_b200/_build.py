@@ -8,7 +8,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB_DIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIB_DIR, "libphoton_ml_b200.so")
-SOURCES = ["api.cu", "kernels.cu", "pack.cu"]
+STAMP = os.path.join(LIB_DIR, "build.sha256")
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-O2", "--expt-relaxed-constexpr"]
 
@@ -20,26 +20,34 @@ def _nvcc():
     return "nvcc"
 
 
-def _stale(target, deps):
-    if not os.path.exists(target):
-        return True
-    t = os.path.getmtime(target)
-    return any(os.path.getmtime(d) > t for d in deps)
+def _digest(paths, flags):
+    """Content hash of what a build depends on: the sources, the headers and the compiler flags (modification times
+    say nothing after a checkout or a copy: a binary that merely LOOKS newer must not be reused)."""
+    import hashlib
+    h = hashlib.sha256(" ".join(flags).encode())
+    for path in sorted(paths):
+        h.update(os.path.basename(path).encode())
+        with open(path, "rb") as f:
+            h.update(f.read())
+    return h.hexdigest()
 
 
 def build_library(force=False, verbose=False):
     os.makedirs(LIB_DIR, exist_ok=True)
     headers = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".h", ".cuh"))]
     headers.append(os.path.join(os.path.dirname(HERE), "include", "photon_ml_b200.h"))
-    objs = []
-    procs = []
-    for src in [f for f in os.listdir(CSRC) if f.endswith(".cu")]:
-        path = os.path.join(CSRC, src)
-        obj = os.path.join(LIB_DIR, src[:-3] + ".o")
+    sources = [os.path.join(CSRC, f) for f in sorted(os.listdir(CSRC)) if f.endswith(".cu")]
+    want = _digest(sources + headers, NVCC_FLAGS)
+    have = open(STAMP).read().strip() if os.path.exists(STAMP) else ""
+    if not force and not verbose and os.path.exists(LIB) and have == want:
+        return LIB
+    # every object is rebuilt whenever anything changed: five files, compiled in parallel in well under a minute
+    objs, procs = [], []
+    for path in sources:
+        obj = os.path.join(LIB_DIR, os.path.basename(path)[:-3] + ".o")
         objs.append(obj)
-        if force or _stale(obj, [path] + headers):
-            cmd = [_nvcc()] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", path, "-o", obj]
-            procs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
+        cmd = [_nvcc()] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", path, "-o", obj]
+        procs.append((os.path.basename(path), subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
     failed = False
     for src, p in procs:
         out, _ = p.communicate()
@@ -48,8 +56,9 @@ def build_library(force=False, verbose=False):
         failed |= p.returncode != 0
     if failed:
         raise RuntimeError("nvcc failed")
-    if force or procs or _stale(LIB, objs):
-        subprocess.check_call([_nvcc(), "-shared", "-o", LIB] + objs + ["-gencode", "arch=compute_100a,code=sm_100a"])
+    subprocess.check_call([_nvcc(), "-shared", "-o", LIB] + objs + ["-gencode", "arch=compute_100a,code=sm_100a"])
+    with open(STAMP, "w") as f:
+        f.write(want + "\n")
     return LIB
 
 
