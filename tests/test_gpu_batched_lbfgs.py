@@ -1,0 +1,66 @@
+"""The lock-step batched L-BFGS / OWL-QN (photon_ml_b200/batched_lbfgs.py) against one run of the single-problem
+driver (optimization.LBFGS / OWLQN) per entity on the CPU oracle objective -- the optimizer GAME's coordinates
+default to (api/optimization/OptimizerFactory.scala:46-62), run entity by entity by RandomEffectCoordinate.updateModel
+(api/algorithm/RandomEffectCoordinate.scala:108-119).  `-m gpu`."""
+import numpy as np
+import pytest
+
+import oracle
+from tests import util
+from tests.objectives import OracleGLMObjective
+from tests.test_gpu_batch import _entities
+
+pytestmark = pytest.mark.gpu
+
+
+def _check(loss, l2, l1, n_ent=120):
+    import photon_ml_b200 as pml
+    from photon_ml_b200.batched import reason_names
+    from photon_ml_b200.batched_lbfgs import BatchedLBFGS
+    from photon_ml_b200.function import NoNormalization
+    from photon_ml_b200.optimization import LBFGS, OWLQN
+    rng = np.random.default_rng(70 + loss + int(10 * l1))
+    ent_row_ptr, dims, row_ptr, col, val, n = _entities(rng, n_ent, 12, 25)
+    label = util.labels_for(rng, loss, n)
+    offset = rng.normal(scale=0.2, size=n)
+    weight = rng.uniform(0.5, 2.0, size=n)
+    ctx = pml.Context(0)
+    batch = pml.Batch(ctx, ent_row_ptr, dims, row_ptr, col, val, label, offset, weight)
+    solver = BatchedLBFGS(batch, loss, l2RegWeight=l2, l1RegWeight=l1)
+    w, f, info = solver.optimize()
+    w, f = w.cpu().numpy(), f.cpu().numpy()
+    reasons = reason_names(info["reasons"])
+    mismatched = 0
+    total_single = 0
+    for e in range(len(dims)):
+        lo, hi = int(ent_row_ptr[e]), int(ent_row_ptr[e + 1])
+        a, b = int(batch.coef_ptr[e]), int(batch.coef_ptr[e + 1])
+        sl = slice(int(row_ptr[lo]), int(row_ptr[hi]))
+        local = oracle.Data(hi - lo, int(dims[e]), row_ptr[lo:hi + 1] - row_ptr[lo], col[sl], val[sl], label[lo:hi],
+                            offset[lo:hi], weight[lo:hi])
+        opt = OWLQN(l1, NoNormalization()) if l1 > 0 else LBFGS(NoNormalization())
+        w_ref, f_ref = opt.optimize(OracleGLMObjective(loss, l2RegWeight=l2), np.zeros(int(dims[e])), local)
+        total_single += opt.evaluations
+        assert np.max(np.abs(w[a:b] - w_ref), initial=0.0) <= 1e-6 * max(1.0, np.max(np.abs(w_ref), initial=0.0)), e
+        assert abs(f[e] - f_ref) <= 1e-9 * max(abs(f_ref), 1e-300), e
+        if (info["iterations"][e], reasons[e], info["entity_evaluations"][e]) != \
+                (opt.currentState.iter, opt.convergenceReason, opt.evaluations):
+            mismatched += 1
+    # same operations in the same order; the summation order inside the dot products differs in the last bits, which
+    # can flip a line-search or convergence test that sits exactly on its threshold for an odd entity
+    assert mismatched <= max(2, n_ent // 40), mismatched
+    # one batched call serves every entity that is still searching: far fewer calls than per-entity evaluations
+    assert info["evaluations"] < total_single / 8
+    batch.close()
+    ctx.close()
+
+
+@pytest.mark.parametrize("loss,l2", [(oracle.LOGISTIC, 1.0), (oracle.POISSON, 5.0), (oracle.SQUARED, 0.5),
+                                     (oracle.SMOOTHED_HINGE, 1.0)])
+def test_every_entity_follows_its_own_lbfgs_run(loss, l2):
+    _check(loss, l2, 0.0)
+
+
+@pytest.mark.parametrize("loss,l1", [(oracle.LOGISTIC, 0.5), (oracle.SQUARED, 0.3)])
+def test_every_entity_follows_its_own_owlqn_run(loss, l1):
+    _check(loss, 0.0, l1)
