@@ -146,7 +146,7 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
-NCU_FULL_CAPTURES = ("r01_final3_ncu_full.csv", "r01_tiled_ncu_full.csv")   # newest first
+NCU_FULL_CAPTURES = ("r02_ncu_full.csv", "r01_final3_ncu_full.csv", "r01_tiled_ncu_full.csv")   # newest first
 
 
 def ncu_traffic(kernel_substrings):
