@@ -226,8 +226,12 @@ int vg_raw_launches(pml_dataset *ds, int loss, const double *coef_dev, double *o
     const bool norm = !hinge && (ds->factors || ds->shifts);
     RowPassParams rp;
     std::memset(&rp, 0, sizeof(rp));
-    {
-        // always runs: besides ec = c .* f it moves the coefficients to the columns' internal ids
+    if (!norm && ds->keep_column_order && ds->t.m == ds->d) {
+        // a batch of per-entity problems without empty columns: internal ids ARE the caller's ids and there is
+        // nothing to scale, so the kernels read the caller's vector directly (one pass over d-sized arrays less)
+        rp.vec = coef_dev;
+    } else {
+        // besides ec = c .* f this moves the coefficients to the columns' internal ids
         int np = 0;
         PML_TRY(run(ctx, PML_K_PREPARE, [&] {
             return launch_prepare_vectors(s, ds->d, coef_dev, nullptr, norm ? ds->factors : nullptr,
@@ -343,17 +347,21 @@ int hv_raw_launches(pml_dataset *ds, int loss, const double *coef_dev, const dou
     rp.r = ds->r;
     rp.partials = ds->partials;
     rp.loss = loss;
-    int np = 0;
-    PML_TRY(run(ctx, PML_K_PREPARE, [&] {
-        return cached ? launch_prepare_vectors(s, ds->d, v_dev, nullptr, ds->factors, ds->shifts, ds->t.rank, ds->vec,
-                                               ds->shift_partials, &np)
-                      : launch_prepare_vectors(s, ds->d, coef_dev, v_dev, ds->factors, ds->shifts, ds->t.rank, ds->vec,
-                                               ds->shift_partials, &np);
-    }));
-    rp.vec = ds->vec;
-    if (ds->shifts) {
-        rp.shift_partials = ds->shift_partials;
-        rp.n_shift_partials = np;
+    if (cached && !ds->factors && !ds->shifts && ds->keep_column_order && ds->t.m == ds->d) {
+        rp.vec = v_dev;   // as in vg_raw_launches: identity renumbering, nothing to scale
+    } else {
+        int np = 0;
+        PML_TRY(run(ctx, PML_K_PREPARE, [&] {
+            return cached ? launch_prepare_vectors(s, ds->d, v_dev, nullptr, ds->factors, ds->shifts, ds->t.rank, ds->vec,
+                                                   ds->shift_partials, &np)
+                          : launch_prepare_vectors(s, ds->d, coef_dev, v_dev, ds->factors, ds->shifts, ds->t.rank, ds->vec,
+                                                   ds->shift_partials, &np);
+        }));
+        rp.vec = ds->vec;
+        if (ds->shifts) {
+            rp.shift_partials = ds->shift_partials;
+            rp.n_shift_partials = np;
+        }
     }
     rp.dcache = (cached || keep) ? ds->dcache : nullptr;
     rp.mode = cached ? MODE_HV_CACHED : MODE_HV_COLD;
@@ -696,6 +704,7 @@ int pml_dataset_create_csr_dev(pml_ctx *ctx, int64_t n, int32_t d, const int64_t
     const int chunk_entries = SEG_CHUNK;
     PML_TRY(build_transpose(s, ctx->sm_count, n, d, nnz, ds->row_ptr, ds->col, ds->val, dst_bytes, chunk_entries,
                             (storage_arg & PML_KEEP_COLUMN_ORDER_FLAG) == 0, &ds->t));
+    ds->keep_column_order = (storage_arg & PML_KEEP_COLUMN_ORDER_FLAG) != 0;
     ds->bytes += ds->t.bytes;
     // after the transpose (which sorts by the column ids): from here on the CSR column array carries the row-start
     // flags in bit 31
