@@ -491,9 +491,10 @@ def run_ours(args):
         }
         if world == 1 and not args.no_cpu_baseline:
             out["cpu_baseline"] = cpu_baseline(host_rows, steps=20, warmup=5)
+        if world == 1 and not args.no_convergence:
+            out["convergence"] = convergence(ctx, ds, d, host_rows)
         host_rows = None
         if world == 1 and not args.no_convergence:
-            out["convergence"] = convergence(ctx, ds, d)
             out["random_effect_batch"] = random_effect_batch(ctx)
         emit(out)
     ds.close()
@@ -645,7 +646,7 @@ def parity_block(torch, dist, pml, ctx, ext, world, rank, device, ds, coef, v, o
     return out
 
 
-def convergence(ctx, ds, d):
+def convergence(ctx, ds, d, host_rows=None):
     """Metric (3): optimizer wall time to convergence, driven through the host-buffer C ABI.
     TRON on this run's configs[1] data (Hessian-vector path) and LBFGS on configs[0] (a1a-shaped: the
     first 1605 rows of the reference's a9a fixture), the latter also on the CPU oracle under the same
@@ -659,25 +660,53 @@ def convergence(ctx, ds, d):
     import torch
     from photon_ml_b200.function import DeviceGLMLossFunction
     out = {}
-    # (a) optimizer state in device memory (torch tensors), only scalars come back
-    dev_obj = DeviceGLMLossFunction(ctx, LOSS_POISSON, l2RegWeight=1.0)
-    tron = TRON(NoNormalization())
-    with dev_obj.stream():
-        torch.cuda.synchronize()
+    dev = torch.device("cuda", ctx.device)
+
+    def tron_device(lam, max_iter):
+        obj = DeviceGLMLossFunction(ctx, LOSS_POISSON, l2RegWeight=lam)
+        tron = TRON(NoNormalization(), maxNumIterations=max_iter)
+        with obj.stream():
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            _, f = tron.optimize(obj, torch.zeros(d, dtype=torch.float64, device=dev), ds)
+            torch.cuda.synchronize()
+            wall = time.perf_counter() - t0
+        return {"wall_s": wall, "iterations": tron.currentState.iter, "reason": tron.convergenceReason,
+                "value_gradient_evals": tron.evaluations, "hessian_vector_evals": tron.hessian_vector_evaluations,
+                "cg_iterations": int(sum(tron.cg_iterations)), "objective": f}
+
+    def tron_host(objective, data, dim, max_iter):
+        tron = TRON(NoNormalization(), maxNumIterations=max_iter)
         t0 = time.perf_counter()
-        _, f = tron.optimize(dev_obj, torch.zeros(d, dtype=torch.float64, device=torch.device("cuda", ctx.device)), ds)
-        torch.cuda.synchronize()
-        wall = time.perf_counter() - t0
-    out["tron_configs1_poisson_l2_1_device_state"] = {
-        "wall_s": wall, "iterations": tron.currentState.iter, "reason": tron.convergenceReason,
-        "value_gradient_evals": tron.evaluations, "hessian_vector_evals": tron.hessian_vector_evaluations, "objective": f}
-    # (b) the drop-in shape: host vectors through the host-buffer ABI every evaluation (numpy optimizer state)
-    t0 = time.perf_counter()
-    tron = TRON(NoNormalization())
-    _, f = tron.optimize(DistributedGLMLossFunction.create(LOSS_POISSON, l2RegWeight=1.0), np.zeros(d), ds)
-    out["tron_configs1_poisson_l2_1"] = {
-        "wall_s": time.perf_counter() - t0, "iterations": tron.currentState.iter, "reason": tron.convergenceReason,
-        "value_gradient_evals": tron.evaluations, "hessian_vector_evals": tron.hessian_vector_evaluations, "objective": f}
+        _, f = tron.optimize(objective, np.zeros(dim), data)
+        return {"wall_s": time.perf_counter() - t0, "iterations": tron.currentState.iter, "reason": tron.convergenceReason,
+                "value_gradient_evals": tron.evaluations, "hessian_vector_evals": tron.hessian_vector_evaluations,
+                "cg_iterations": int(sum(tron.cg_iterations)), "objective": f}
+
+    # (a) the reference's defaults (TRON.scala:97-98: 15 iterations): on this problem that is the iteration cap
+    out["tron_configs1_poisson_l2_1_device_state"] = tron_device(1.0, 15)
+    # (b) the same problem run TO CONVERGENCE (cap lifted to 100; FunctionValuesConverged, Optimizer.scala:136-150)
+    out["tron_configs1_poisson_l2_1_device_state_to_convergence"] = tron_device(1.0, 100)
+    # (c) a better conditioned setting, where the optimizer state in device memory and the drop-in shape (host vectors
+    #     through the host-buffer ABI every evaluation, numpy optimizer state) can be compared count by count
+    out["tron_configs1_poisson_l2_1000_device_state"] = tron_device(1000.0, 100)
+    out["tron_configs1_poisson_l2_1000"] = tron_host(DistributedGLMLossFunction.create(LOSS_POISSON, l2RegWeight=1000.0), ds, d, 100)
+    # (d) the same driver on the CUDA objective and on the CPU oracle objective, first 500 k rows of the workload:
+    #     iteration / evaluation / CG counts must agree (north star: identical iteration counts)
+    if host_rows is not None:
+        rp, cc, vv, yy = host_rows
+        ns = PARITY_SAMPLE_ROWS
+        end = int(rp[ns])
+        sample_ds = pml.Dataset.from_csr(ctx, ns, N_FEATS, rp[:ns + 1], cc[:end], vv[:end], yy[:ns])
+        sample_ref = oracle.Data(ns, N_FEATS, rp[:ns + 1], cc[:end], vv[:end], yy[:ns])
+        lam = 50.0
+        on_gpu = tron_host(DistributedGLMLossFunction.create(LOSS_POISSON, l2RegWeight=lam), sample_ds, N_FEATS, 100)
+        on_cpu = tron_host(OracleGLMObjective(oracle.POISSON, l2RegWeight=lam), sample_ref, N_FEATS, 100)
+        sample_ds.close()
+        keys = ("iterations", "reason", "value_gradient_evals", "hessian_vector_evals", "cg_iterations")
+        out["tron_first_500k_rows_poisson_l2_50_gpu_vs_cpu_oracle"] = {
+            "gpu": on_gpu, "cpu_oracle": on_cpu, "same_counts": all(on_gpu[k] == on_cpu[k] for k in keys),
+            "objective_rel_diff": abs(on_gpu["objective"] - on_cpu["objective"]) / abs(on_cpu["objective"])}
     n1, d1, row_ptr, col, val, label = util.read_libsvm(os.path.join(util.GOLDEN, "a9a_1605.libsvm"), d=123,
                                                         add_intercept=True)
     small = pml.Dataset.from_csr(ctx, n1, d1, row_ptr, col, val, label)
