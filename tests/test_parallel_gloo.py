@@ -124,3 +124,23 @@ def test_shard_entities_is_deterministic_and_greedy():
     assert np.array_equal(a, parallel.shard_entities(rows, 3))
     loads = [rows[a == r].sum() for r in range(3)]
     assert sum(loads) == rows.sum() and max(loads) - min(loads) <= 3
+
+
+def test_shard_entities_capacity_follows_the_reference_partitioner():
+    """RandomEffectDataSetPartitioner.fromGameDataSet (api/data/RandomEffectDataSetPartitioner.scala:113-146): only the
+    `partitionerCapacity` heaviest entities go through the min-heap; getPartition (:74-84) hashes the others."""
+    import numpy as np
+    from photon_ml_b200 import parallel
+    rng = np.random.default_rng(0)
+    rows = np.minimum(rng.zipf(1.8, size=5000), 2000)
+    full = parallel.shard_entities(rows, 4)
+    capped = parallel.shard_entities(rows, 4, capacity=100)
+    heavy = np.argsort(-rows, kind="stable")[:100]
+    light = np.setdiff1d(np.arange(5000), heavy)
+    assert np.array_equal(capped[light], light % 4)                   # hash fallback
+    # the heap part is the same greedy rule as without a cap, applied to the same (heaviest-first) prefix
+    assert np.array_equal(capped[heavy], parallel.shard_entities(rows[heavy], 4)[np.arange(100)])
+    loads = [rows[full == r].sum() for r in range(4)]
+    assert max(loads) - min(loads) <= rows.max()
+    loads = [rows[capped == r].sum() for r in range(4)]
+    assert max(loads) <= 1.2 * min(loads)
