@@ -998,13 +998,17 @@ def run_config2(args):
     raw = torch.empty(D + 2, dtype=torch.float64, device=device)
     out_value = torch.empty(1, dtype=torch.float64, device=device)
     out_grad = torch.empty(D, dtype=torch.float64, device=device)
-    peer, collective = None, "none"
+    peer, host_peer, collective = None, None, "none"
     if world > 1:
         want_peer = os.environ.get("PML_BENCH_COLLECTIVE", "auto")
         use_peer = want_peer == "peer" or (want_peer == "auto" and not (world >= 8 and D > PEER_MERGE_MAX_D_AT_8))
         collective = "nccl all-reduce of d+2 doubles, then finalize_dev (chosen by size: d = %d on %d ranks)" % (D, world)
+        # the peer handle exists either way: the end-to-end step below goes through the host-buffer exchange
+        # (pml_value_and_gradient_allreduce), whose slice-wise PCIe traffic matters far more at d = 10 M than the
+        # 50 us between the two merges
+        host_peer = pml.Peer(ctx, D)
         if use_peer:
-            peer = pml.Peer(ctx, D)
+            peer = host_peer
             collective = "peer_merge_kernel: sums over NVLink peer memory in rank order, fused with getVector"
             result = torch.as_tensor(peer.result_array(), device=device)
             out_grad, out_value = result[:D], result[D:D + 1]
@@ -1061,17 +1065,18 @@ def run_config2(args):
         h_coef.copy_(coef.cpu())
         h_grad = torch.empty(D, dtype=torch.float64).pin_memory()
         h_coef_np, h_grad_np = h_coef.numpy(), h_grad.numpy()
+        shared, e2e_iter = None, [0]
+        if world > 1:      # one host buffer for all ranks, as in the configs[1] run: the driver ends up with the full gradient
+            shared = SharedHostVectors(torch, dist, rank, world, D, coef.cpu().numpy())
+            h_coef_np, h_grad_np = shared.coef, shared.grad
 
         def e2e_step():
             if world == 1:
                 return ds.value_and_gradient(pml.LOGISTIC, h_coef_np, out=h_grad_np)[0]
-            if peer is not None:
-                return peer.value_and_gradient_host(ds, pml.LOGISTIC, h_coef_np, h_grad_np)
-            coef.copy_(h_coef, non_blocking=True)          # every rank holds the vector on its host (Spark broadcast)
-            step()
-            h_grad.copy_(out_grad, non_blocking=True)
-            ext.synchronize()
-            return float(out_value)
+            value = host_peer.value_and_gradient_host(ds, pml.LOGISTIC, h_coef_np, h_grad_np)
+            e2e_iter[0] += 1
+            shared.arrive_and_wait(e2e_iter[0])
+            return value
 
         for _ in range(3):
             e2e_step()
@@ -1081,6 +1086,8 @@ def run_config2(args):
             e2e_value = e2e_step()
         barrier()
         e2e_s = time.perf_counter() - t0
+        if shared is not None:
+            shared.close()
         # the configuration's optimizer: OWL-QN, L1 (alpha = 1) and elastic net (alpha = 0.5; the reference mixes the L2
         # part in only for RegularizationType.L2, so ELASTIC_NET gets the L1 part alone: DistributedGLMLossFunction.scala:160-169)
         owlqn = {}
@@ -1126,7 +1133,10 @@ def run_config2(args):
                        "device_GB": info.device_bytes / 1e9, "generate_s": round(t_gen, 1), "pack_s": round(t_pack, 2)},
             "rows_per_s": int(n) * world / (ms_per_step * 1e-3),
             "e2e": {"value": args.steps / e2e_s, "unit": "evals/s", "h2d_bytes_per_step": D * 8,
-                    "d2h_bytes_per_step": D * 8 + 8 * world, "ms_per_step": 1e3 * e2e_s / args.steps, "objective": e2e_value},
+                    "d2h_bytes_per_step": D * 8 + 8 * world, "ms_per_step": 1e3 * e2e_s / args.steps, "objective": e2e_value,
+                    "api": "pml_value_and_gradient (host buffers, pinned)" if world == 1 else
+                           "pml_value_and_gradient_allreduce: every rank uploads 1/N of the coefficients and downloads 1/N of "
+                           "the gradient over its own PCIe link (one host copy of the vector per rank: Spark's broadcast)"},
             "gpu_launches": int(launches), "clocks": clocks,
             "roofline": {"bound": "hbm", "kernel": dom, "achieved": dom_bytes / (dom_ms * 1e-3) / 1e9, "peak": peak,
                          "unit": "GB/s", "frac": dom_bytes / (dom_ms * 1e-3) / 1e9 / peak, "peak_source": peak_src,
