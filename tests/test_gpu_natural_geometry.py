@@ -3,7 +3,7 @@
 tests/test_gpu_parity.py forces 37-row tiles and 101-row super blocks onto small inputs; that exercises every
 code path of the tiled layout except the ones that only large inputs reach: (tile, column) runs longer than a
 256-entry chunk (the no-scan path of seg_spmv_tiled_kernel and the bank-aware order of pack.cu), the 96 KB
-coefficient table of the CSR pass, tiles of ~20 000 rows, and super blocks above 12 M rows.  Here the inputs are
+coefficient table of the CSR pass, tiles of thousands of rows, and the default super blocks (above 6 M rows).  Here the inputs are
 bench-shaped (Zipf(1.1) columns, ~50 entries per row, values in {1,2,3,4}/4) and no packing knob is set.
 
 Reference semantics: ValueAndGradientAggregator.scala:132-153,199-221; HessianVectorAggregator.scala:96-121;
@@ -139,8 +139,8 @@ def test_bench_shaped_rows_with_normalization_and_indicator_values(ctx, natural)
 
 
 def test_more_than_twelve_million_rows_super_blocks_vs_oracle(ctx):
-    """Above 12 M rows the cold columns are cut into super blocks of <= 6 M rows by default (pack.cu); the oracle
-    streams the same 12.7 M rows (partitioned over the host cores)."""
+    """Above 6 M rows the cold columns are cut into super blocks of <= 6 M rows by default (pack.cu): three of them
+    here; the oracle streams the same 12.7 M rows (partitioned over the host cores)."""
     import photon_ml_b200 as pml
     n, d = 12_700_000, 300_000
     row_ptr, col, val = zipf_rows(21, n, d, 6, sort_rows=False)
