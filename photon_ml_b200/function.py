@@ -232,3 +232,39 @@ class DeviceGLMLossFunction:
         if self.l2RegWeight is not None:
             hv += multiplyVector * self.l2RegWeight
         return hv
+
+
+class ShardedDeviceGLMLossFunction(DeviceGLMLossFunction):
+    """DistributedGLMLossFunction over rows sharded across GPUs, one process per GPU: `data` is THIS rank's shard and
+    every evaluation ends in the exchange over peer memory (abi.Peer: pml_value_and_gradient_allreduce_dev /
+    pml_hessian_vector_allreduce_dev), which leaves bit-identical results on all ranks -- so every rank can run the
+    same optimizer on the same numbers (SPMD) and all ranks hold the same model, as Spark's driver + broadcast do
+    (DistributedObjectiveFunction.scala:57-58,73).  The normalization context must be the same on every rank."""
+
+    def __init__(self, ctx, loss, peer, l2RegWeight=None):
+        super().__init__(ctx, loss, l2RegWeight)
+        self.peer = peer
+        result = self._torch.as_tensor(peer.result_array(), device=self._torch.device("cuda", ctx.device))
+        self._vector, self._value = result[:peer.d], result[peer.d:peer.d + 1]   # the library's result buffer
+
+    def calculate(self, data, coefficients, normalizationContext, want_gradient=True):
+        self._apply(data, normalizationContext)
+        self.peer.value_and_gradient(data, self.loss, coefficients.data_ptr())
+        f = float(self._value)
+        grad = self._vector.clone() if want_gradient else None
+        if self.l2RegWeight is not None:
+            f += self.l2RegWeight * float(coefficients.dot(coefficients)) / 2
+            if want_gradient:
+                grad += coefficients * self.l2RegWeight
+        return f, grad
+
+    def hessianVector(self, data, coefficients, multiplyVector, normalizationContext):
+        self._apply(data, normalizationContext)
+        if self._tag_src is not coefficients or self._tag_version != coefficients._version:
+            self._tag_src, self._tag_version = coefficients, coefficients._version
+            self._tag = next(_TAGS)
+        self.peer.hessian_vector(data, self.loss, coefficients.data_ptr(), multiplyVector.data_ptr(), tag=self._tag)
+        hv = self._vector.clone()
+        if self.l2RegWeight is not None:
+            hv += multiplyVector * self.l2RegWeight
+        return hv

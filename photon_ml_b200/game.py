@@ -17,7 +17,7 @@ import time
 
 from . import abi
 from .batched import BatchedTRON
-from .function import DeviceGLMLossFunction, NoNormalization
+from .function import DeviceGLMLossFunction, NoNormalization, ShardedDeviceGLMLossFunction
 from .optimization import TRON
 
 
@@ -25,7 +25,8 @@ class FixedEffect:
     """FixedEffectCoordinate (api/algorithm/FixedEffectCoordinate.scala).  `row_map[i]` = global row of local row i
     (None = the coordinate's rows are in global order); `base_offset` = the data's own offsets, local order."""
 
-    def __init__(self, dataset, loss, l2RegWeight=0.0, base_offset=None, row_map=None, tolerance=1e-5, maxNumIterations=15):
+    def __init__(self, dataset, loss, l2RegWeight=0.0, base_offset=None, row_map=None, tolerance=1e-5, maxNumIterations=15,
+                 peer=None):
         import torch
         self.torch = torch
         self.ds, self.loss, self.l2 = dataset, loss, l2RegWeight
@@ -33,7 +34,10 @@ class FixedEffect:
         self.device = torch.device("cuda", self.ctx.device)
         self.base_offset, self.row_map = base_offset, row_map
         self.tolerance, self.max_iter = tolerance, maxNumIterations
-        self.objective = DeviceGLMLossFunction(self.ctx, loss, l2RegWeight=l2RegWeight or None)
+        # peer: the rows are one rank's shard (one process per GPU); every evaluation is merged over peer memory and
+        # every rank trains the same model on the same numbers
+        self.objective = (DeviceGLMLossFunction(self.ctx, loss, l2RegWeight=l2RegWeight or None) if peer is None else
+                          ShardedDeviceGLMLossFunction(self.ctx, loss, peer, l2RegWeight=l2RegWeight or None))
         self.model = torch.zeros(dataset.d, dtype=torch.float64, device=self.device)
         self.n = dataset.n
 
@@ -59,7 +63,8 @@ class RandomEffect:
     """RandomEffectCoordinate (api/algorithm/RandomEffectCoordinate.scala): `batch` holds the rows grouped by entity,
     `row_map[i]` = global row of the batch's row i."""
 
-    def __init__(self, batch, row_map, loss, l2RegWeight=0.0, base_offset=None, tolerance=1e-5, maxNumIterations=15):
+    def __init__(self, batch, row_map, loss, l2RegWeight=0.0, base_offset=None, tolerance=1e-5, maxNumIterations=15,
+                 optimizer="TRON"):
         import torch
         self.torch = torch
         self.batch, self.loss, self.l2 = batch, loss, l2RegWeight
@@ -69,14 +74,20 @@ class RandomEffect:
         self.tolerance, self.max_iter = tolerance, maxNumIterations
         self.model = torch.zeros(batch.d_total, dtype=torch.float64, device=self.device)
         self.n = batch.dataset.n
+        self.optimizer = optimizer     # "TRON" or "LBFGS" (OptimizerFactory.scala:46-62; GAME's tests default to LBFGS)
 
     def train(self):
-        solver = BatchedTRON(self.batch, self.loss, l2RegWeight=self.l2, tolerance=self.tolerance,
-                             maxNumIterations=self.max_iter)
+        if self.optimizer == "LBFGS":
+            from .batched_lbfgs import BatchedLBFGS
+            solver = BatchedLBFGS(self.batch, self.loss, l2RegWeight=self.l2, tolerance=self.tolerance,
+                                  maxNumIterations=self.max_iter)
+        else:
+            solver = BatchedTRON(self.batch, self.loss, l2RegWeight=self.l2, tolerance=self.tolerance,
+                                 maxNumIterations=self.max_iter)
         self.model, values, info = solver.optimize(self.model)
         return float(values.sum()), {"mean_iterations": float(info["iterations"].mean()),
                                      "evaluations": info["evaluations"],
-                                     "hessian_vector_evaluations": info["hessian_vector_evaluations"]}
+                                     "hessian_vector_evaluations": info.get("hessian_vector_evaluations", 0)}
 
     def score_local(self):
         out = self.torch.empty(self.n, dtype=self.torch.float64, device=self.device)
