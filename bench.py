@@ -857,7 +857,8 @@ def run_config4(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=device)
     n_total = int(os.environ.get("PML_BENCH_ENTITIES", "10000000"))
-    rows_all = np.minimum(np.random.default_rng(5).zipf(1.8, size=n_total), 2000).astype(np.int64)   # same on every rank
+    # rows per member: Pareto tail with mean ~3.3, capped ("power-law, mean 4"); the same on every rank
+    rows_all = np.minimum(np.floor(np.random.default_rng(5).random(n_total) ** (-1.0 / 1.35)), 5000).astype(np.int64)
     assignment = parallel.shard_entities(rows_all, world, capacity=10000)
     mine = np.flatnonzero(assignment == rank)
     ctx = pml.Context(local_rank)
