@@ -331,3 +331,52 @@ def test_peer_rejects_mismatched_dimension():
     peer.close()
     ds.close()
     ctx.close()
+
+
+def _fe_worker(rank, world, port, out_dir):
+    """A fixed-effect coordinate trained SPMD: every rank holds a row shard and runs the same TRON on merged numbers."""
+    import torch
+    import torch.distributed as dist
+    import photon_ml_b200 as pml
+    from photon_ml_b200 import parallel
+    from photon_ml_b200.game import FixedEffect
+
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    device = rank % torch.cuda.device_count()
+    torch.cuda.set_device(device)
+    n, d, row_ptr, col, val, label, offset, weight, f, s, icpt, w, v = _problem(oracle.LOGISTIC)
+    lo, hi = _shards(row_ptr, world, False)[rank]
+    rp, c, vv = parallel.slice_csr(row_ptr, col, val, lo, hi)
+    ctx = pml.Context(device)
+    ds = pml.Dataset.from_csr(ctx, hi - lo, d, rp, c, vv, label[lo:hi], offset[lo:hi], weight[lo:hi])
+    peer = pml.Peer(ctx, d, multicast=False) if world > 1 else None
+    fe = FixedEffect(ds, pml.LOGISTIC, l2RegWeight=0.7, peer=peer)
+    with fe.objective.stream():
+        value, info = fe.train()
+        model = fe.model.cpu().numpy()
+    np.savez(os.path.join(out_dir, "fe%d_of_%d.npz" % (rank, world)), model=model, value=value,
+             iterations=info["iterations"], hv=info["hessian_vector_evaluations"])
+    dist.barrier()
+    if peer is not None:
+        peer.close()
+    ds.close()
+    ctx.close()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_sharded_fixed_effect_trains_the_same_model_as_one_gpu(tmp_path, world):
+    import torch.multiprocessing as mp
+    _need_gpus(world)
+    mp.spawn(_fe_worker, args=(1, _free_port(), str(tmp_path)), nprocs=1, join=True)
+    mp.spawn(_fe_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    one = np.load(str(tmp_path / "fe0_of_1.npz"))
+    for r in range(world):
+        got = np.load(str(tmp_path / ("fe%d_of_%d.npz" % (r, world))))
+        assert got["iterations"] == one["iterations"] and got["hv"] == one["hv"]
+        assert util.rel_err(got["model"], one["model"]) <= 1e-9
+        assert abs(got["value"] - one["value"]) <= 1e-11 * abs(one["value"])
+        # every rank trained on the same merged numbers: the same model to the last bit
+        assert np.array_equal(got["model"], np.load(str(tmp_path / ("fe0_of_%d.npz" % world)))["model"])
