@@ -356,8 +356,13 @@ def _fe_worker(rank, world, port, out_dir):
     with fe.objective.stream():
         value, info = fe.train()
         model = fe.model.cpu().numpy()
+        # another coordinate's scores arrive as new offsets (Coordinate.updateModel): re-train from the current model
+        fe.set_offsets(torch.from_numpy(offset[lo:hi] * -1.5 + 0.3).to(torch.device("cuda", device)))
+        value2, info2 = fe.train()
+        model2 = fe.model.cpu().numpy()
     np.savez(os.path.join(out_dir, "fe%d_of_%d.npz" % (rank, world)), model=model, value=value,
-             iterations=info["iterations"], hv=info["hessian_vector_evaluations"])
+             iterations=info["iterations"], hv=info["hessian_vector_evaluations"], model2=model2, value2=value2,
+             iterations2=info2["iterations"])
     dist.barrier()
     if peer is not None:
         peer.close()
@@ -378,5 +383,7 @@ def test_sharded_fixed_effect_trains_the_same_model_as_one_gpu(tmp_path, world):
         assert got["iterations"] == one["iterations"] and got["hv"] == one["hv"]
         assert util.rel_err(got["model"], one["model"]) <= 1e-9
         assert abs(got["value"] - one["value"]) <= 1e-11 * abs(one["value"])
+        assert got["iterations2"] == one["iterations2"] and util.rel_err(got["model2"], one["model2"]) <= 1e-9
+        assert abs(got["value2"] - one["value2"]) <= 1e-11 * abs(one["value2"])
         # every rank trained on the same merged numbers: the same model to the last bit
         assert np.array_equal(got["model"], np.load(str(tmp_path / ("fe0_of_%d.npz" % world)))["model"])
