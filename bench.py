@@ -928,9 +928,15 @@ def run_config4(args):
         torch.cuda.empty_cache()
         peer = pml.Peer(ctx, D_FE) if world > 1 else None
         passes = 2
+
+        def all_sum(x):
+            t = torch.tensor([x], dtype=torch.float64, device=device)
+            dist.all_reduce(t)
+            return float(t)
+
         descent = CoordinateDescent({"fixed": FixedEffect(fe_ds, pml.LOGISTIC, l2RegWeight=1.0, peer=peer),
                                      "per-member": RandomEffect(batch, None, pml.LOGISTIC, l2RegWeight=1.0)}, n,
-                                    descent_iterations=passes)
+                                    descent_iterations=passes, all_reduce_sum=all_sum if world > 1 else None)
         barrier()
         t0 = time.perf_counter()
         _, history = descent.run()

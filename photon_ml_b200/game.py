@@ -105,8 +105,12 @@ class CoordinateDescent:
     """CoordinateDescent.run (lib/algorithm/CoordinateDescent.scala:138-260) without validation: `coordinates` is an
     ordered {name: FixedEffect | RandomEffect} (the update sequence), `n` the number of global rows."""
 
-    def __init__(self, coordinates, n, descent_iterations=1):
+    def __init__(self, coordinates, n, descent_iterations=1, all_reduce_sum=None):
+        """all_reduce_sum(float) -> float: with one process per GPU, sums a rank-local scalar over the ranks (the logged
+        objective then counts every rank's random-effect terms; a fixed effect trained through the peer exchange is
+        global already).  None = single process."""
         import torch
+        self.all_reduce_sum = all_reduce_sum
         self.torch = torch
         self.coordinates, self.n, self.passes = dict(coordinates), int(n), descent_iterations
         first = next(iter(self.coordinates.values()))
@@ -145,7 +149,12 @@ class CoordinateDescent:
                     self.ctx.synchronize()
                     # the coordinate's objective = training loss of the full model + its own regularization term;
                     # add the other coordinates' terms for the value CoordinateDescent logs
-                    total = objective + sum(c.regularization_term() for o, c in self.coordinates.items() if o != name)
+                    def everywhere(x, c):     # a rank-local term of a coordinate whose rows / entities are sharded
+                        local = self.all_reduce_sum is not None and getattr(c, "objective", None).__class__.__name__ != \
+                            "ShardedDeviceGLMLossFunction"
+                        return self.all_reduce_sum(x) if local else x
+                    total = everywhere(objective, coord) + sum(everywhere(c.regularization_term(), c)
+                                                               for o, c in self.coordinates.items() if o != name)
                     self.history.append({"pass": p, "coordinate": name, "objective": total,
                                          "seconds": time.perf_counter() - t0, **info})
         return {name: c.model for name, c in self.coordinates.items()}, self.history
