@@ -513,6 +513,36 @@ class Peer {
     {
         check(pml_hessian_vector_allreduce_dev(data.handle(), h_, loss, coef_dev, coefTag, v_dev, out_hv_dev));
     }
+    // The same with HOST vectors, the shape DistributedObjectiveFunction hands over (DistributedObjectiveFunction.scala:
+    // 57-58, 73): every rank passes the same coefficients and uploads only its slice; gatherOutput = false writes only
+    // out[slice()] (ranks sharing one host buffer assemble the vector in it), true downloads all of it.  Synchronous.
+    std::pair<int64_t, int64_t> slice() const
+    {
+        int64_t lo = 0, hi = 0;
+        check(pml_peer_slice(h_, &lo, &hi));
+        return { lo, hi };
+    }
+    double calculate(const DataSet &data, int loss, const std::vector<double> &coef, std::vector<double> &outGrad,
+                     bool gatherOutput = true) const
+    {
+        double value = 0.0;
+        outGrad.resize(coef.size());
+        check(pml_value_and_gradient_allreduce(data.handle(), h_, loss, coef.data(), &value, outGrad.data(), gatherOutput ? 1 : 0));
+        return value;
+    }
+    void hessianVector(const DataSet &data, int loss, const std::vector<double> &coef, uint64_t coefTag,
+                       const std::vector<double> &v, std::vector<double> &outHv, bool gatherOutput = true) const
+    {
+        outHv.resize(v.size());
+        check(pml_hessian_vector_allreduce(data.handle(), h_, loss, coef.empty() ? nullptr : coef.data(), coefTag, v.data(),
+                                           outHv.data(), gatherOutput ? 1 : 0));
+    }
+    bool timedOut() const
+    {
+        int st = 0;
+        check(pml_peer_status(h_, &st));
+        return st != 0;
+    }
 
   private:
     pml_peer *h_ = nullptr;

@@ -114,6 +114,16 @@ int main(int argc, char **argv)
     {
         Peer peer(ctx, 0, 1, d, [](const std::vector<char> &mine) { return mine; });
         std::printf("peer_created %d\n", peer.handle() != nullptr ? 1 : 0);
+        // host vectors through the one-rank exchange = the plain host-buffer call on the same data
+        Vector w(d, 0.05), g_peer, g_plain(d, 0.0);
+        const double f_peer = peer.calculate(data, PML_LOSS_LOGISTIC, w, g_peer);
+        double f_plain = 0.0;
+        check(pml_value_and_gradient(data.handle(), PML_LOSS_LOGISTIC, w.data(), &f_plain, g_plain.data()));
+        double worst = std::fabs(f_peer - f_plain);
+        for (int j = 0; j < d; ++j) worst = std::fmax(worst, std::fabs(g_peer[j] - g_plain[j]));
+        const auto sl = peer.slice();
+        std::printf("peer_host_diff %.3e\n", worst);
+        std::printf("peer_slice_ok %d\n", (sl.first == 0 && sl.second == d && !peer.timedOut()) ? 1 : 0);
     }
     return 0;
 }

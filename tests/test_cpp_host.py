@@ -36,6 +36,7 @@ def test_cpp_tron_matches_python_driver(tmp_path):
     got = dict(line.split() for line in out.strip().splitlines())
     assert got["require_size_throws"] == "1"
     assert float(got["batch_worst_diff"]) <= 1e-12 and got["batch_require_throws"] == "1" and got["peer_created"] == "1"
+    assert float(got["peer_host_diff"]) == 0.0 and got["peer_slice_ok"] == "1"
     n, d, row_ptr, col, val, label = util.read_libsvm(path, d=123, add_intercept=True)
     ctx = pml.Context(0)
     ds = pml.Dataset.from_csr(ctx, n, d, row_ptr, col, val, label)
