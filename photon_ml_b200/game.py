@@ -105,12 +105,17 @@ class CoordinateDescent:
     """CoordinateDescent.run (lib/algorithm/CoordinateDescent.scala:138-260) without validation: `coordinates` is an
     ordered {name: FixedEffect | RandomEffect} (the update sequence), `n` the number of global rows."""
 
-    def __init__(self, coordinates, n, descent_iterations=1, all_reduce_sum=None):
+    def __init__(self, coordinates, n, descent_iterations=1, all_reduce_sum=None, exchange_scores=None):
         """all_reduce_sum(float) -> float: with one process per GPU, sums a rank-local scalar over the ranks (the logged
         objective then counts every rank's random-effect terms; a fixed effect trained through the peer exchange is
         global already).  None = single process."""
         import torch
         self.all_reduce_sum = all_reduce_sum
+        # exchange_scores(tensor[n]): in-place sum over the ranks of a global score vector of which every rank has
+        # filled in the rows it owns (zeros elsewhere) -- the one place where per-row data crosses ranks when the
+        # coordinates' rows are partitioned differently (the reference joins score RDDs by row id:
+        # CoordinateDescent.scala:189,218).  None = every coordinate's rows live in this process.
+        self.exchange_scores = exchange_scores
         self.torch = torch
         self.coordinates, self.n, self.passes = dict(coordinates), int(n), descent_iterations
         first = next(iter(self.coordinates.values()))
@@ -146,6 +151,8 @@ class CoordinateDescent:
                     coord.set_offsets(offsets)
                     objective, info = coord.train()
                     scores[name] = self._to_global(coord, coord.score_local())
+                    if self.exchange_scores is not None:
+                        self.exchange_scores(scores[name])
                     self.ctx.synchronize()
                     # the coordinate's objective = training loss of the full model + its own regularization term;
                     # add the other coordinates' terms for the value CoordinateDescent logs
