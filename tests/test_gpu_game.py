@@ -98,3 +98,120 @@ def test_glmix_shaped_coordinate_descent_matches_the_host_passes():
         b.close()
     fe_ds.close()
     ctx.close()
+
+
+def _sharded_problem():
+    """Fixed effect + per-user + per-item effects on 2400 rows, global row order = user-major."""
+    rng = np.random.default_rng(77)
+    n, n_users, n_items, d_fe = 2400, 60, 25, 40
+    user_of_row = np.sort(rng.integers(0, n_users, size=n))            # rows grouped by user already
+    item_of_row = rng.integers(0, n_items, size=n)
+    fe_ptr, fe_col, fe_val = util.random_csr(rng, n, d_fe, 6, skew=1.1)
+    u_ptr, u_col, u_val = util.random_csr(rng, n, 5, 3)               # per-user features, global (user-major) order
+    i_ptr, i_col, i_val = util.random_csr(rng, n, 4, 2)               # per-item features, global order
+    label = util.labels_for(rng, oracle.LOGISTIC, n)
+    return n, n_users, n_items, d_fe, user_of_row, item_of_row, (fe_ptr, fe_col, fe_val), (u_ptr, u_col, u_val), \
+        (i_ptr, i_col, i_val), label
+
+
+def _take_rows(csr, rows):
+    """CSR restricted to `rows` (in that order)."""
+    ptr, col, val = csr
+    lens = (ptr[1:] - ptr[:-1])[rows]
+    new_ptr = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
+    idx = np.concatenate([np.arange(ptr[r], ptr[r + 1]) for r in rows]) if len(rows) else np.zeros(0, dtype=np.int64)
+    return new_ptr, col[idx.astype(np.int64)], val[idx.astype(np.int64)]
+
+
+def _cd_worker(rank, world, port, out_dir):
+    import os
+    import torch
+    import torch.distributed as dist
+    import photon_ml_b200 as pml
+    from photon_ml_b200 import parallel
+    from photon_ml_b200.game import CoordinateDescent, FixedEffect, RandomEffect
+
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    device = rank % torch.cuda.device_count()
+    torch.cuda.set_device(device)
+    dev = torch.device("cuda", device)
+    n, n_users, n_items, d_fe, user_of_row, item_of_row, fe, ufeat, ifeat, label = _sharded_problem()
+    ctx = pml.Context(device)
+    # users -> ranks, a rank owns its users' rows (fixed effect + per-user effect); items -> ranks separately
+    my_users = np.flatnonzero(parallel.shard_entities(np.bincount(user_of_row, minlength=n_users), world) == rank)
+    my_rows = np.flatnonzero(np.isin(user_of_row, my_users)).astype(np.int64)
+    my_items = np.flatnonzero(parallel.shard_entities(np.bincount(item_of_row, minlength=n_items), world) == rank)
+    item_rows = np.flatnonzero(np.isin(item_of_row, my_items)).astype(np.int64)
+    item_rows = item_rows[np.argsort(item_of_row[item_rows], kind="stable")]          # grouped by item
+    fp, fc, fv = _take_rows(fe, my_rows)
+    fe_ds = pml.Dataset.from_csr(ctx, len(my_rows), d_fe, fp, fc, fv, label[my_rows])
+    up, uc, uv = _take_rows(ufeat, my_rows)
+    u_ptr = np.concatenate([[0], np.cumsum(np.bincount(user_of_row[my_rows], minlength=n_users)[my_users])]).astype(np.int64)
+    user_batch = pml.Batch(ctx, u_ptr, np.full(len(my_users), 5, np.int32), up, uc, uv, label[my_rows])
+    ip, ic, iv = _take_rows(ifeat, item_rows)
+    i_ptr = np.concatenate([[0], np.cumsum(np.bincount(item_of_row[item_rows], minlength=n_items)[my_items])]).astype(np.int64)
+    item_batch = pml.Batch(ctx, i_ptr, np.full(len(my_items), 4, np.int32), ip, ic, iv, label[item_rows])
+    peer = pml.Peer(ctx, d_fe, multicast=False) if world > 1 else None
+
+    def all_sum(x):
+        t = torch.tensor([x], dtype=torch.float64)
+        dist.all_reduce(t)
+        return float(t)
+
+    def exchange(t):
+        h = t.cpu()
+        dist.all_reduce(h)
+        t.copy_(h)
+
+    rows_t, items_t = torch.from_numpy(my_rows).to(dev), torch.from_numpy(item_rows).to(dev)
+    coords = {"fixed": FixedEffect(fe_ds, pml.LOGISTIC, l2RegWeight=0.8, row_map=rows_t, peer=peer),
+              "per-user": RandomEffect(user_batch, rows_t, pml.LOGISTIC, l2RegWeight=0.8),
+              "per-item": RandomEffect(item_batch, items_t, pml.LOGISTIC, l2RegWeight=0.8)}
+    cd = CoordinateDescent(coords, n, descent_iterations=2, all_reduce_sum=all_sum if world > 1 else None,
+                           exchange_scores=exchange if world > 1 else None)
+    models, history = cd.run()
+    # per-user models keyed by user id, so that runs with different shardings can be compared
+    user_models = {int(u): models["per-user"][5 * k:5 * k + 5].cpu().numpy() for k, u in enumerate(my_users)}
+    np.savez(os.path.join(out_dir, "cd%d_of_%d.npz" % (rank, world)), fixed=models["fixed"].cpu().numpy(),
+             objective=np.array([h["objective"] for h in history]), users=np.array(sorted(user_models)),
+             user_models=np.stack([user_models[u] for u in sorted(user_models)]) if user_models else np.zeros((0, 5)))
+    dist.barrier()
+    if peer is not None:
+        peer.close()
+    ctx.close()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_sharded_coordinate_descent_matches_one_gpu(tmp_path, world):
+    """One process per GPU: users and items bin-packed over the ranks, the fixed effect merged through the peer
+    exchange, score vectors summed over the ranks after every update -- the same objective history and models as the
+    whole problem on one GPU."""
+    import socket
+    import torch
+    import torch.multiprocessing as mp
+    if torch.cuda.device_count() < world:
+        pytest.skip("%d ranks need %d GPUs (one process per GPU)" % (world, world))
+
+    def port():
+        s = socket.socket()
+        s.bind(("127.0.0.1", 0))
+        p = s.getsockname()[1]
+        s.close()
+        return p
+
+    mp.spawn(_cd_worker, args=(1, port(), str(tmp_path)), nprocs=1, join=True)
+    mp.spawn(_cd_worker, args=(world, port(), str(tmp_path)), nprocs=world, join=True)
+    one = np.load(str(tmp_path / "cd0_of_1.npz"))
+    seen = {}
+    for r in range(world):
+        got = np.load(str(tmp_path / ("cd%d_of_%d.npz" % (r, world))))
+        assert np.max(np.abs(got["objective"] - one["objective"]) / np.abs(one["objective"])) <= 1e-9
+        assert util.rel_err(got["fixed"], one["fixed"]) <= 1e-7
+        for u, m in zip(got["users"], got["user_models"]):
+            seen[int(u)] = m
+    assert sorted(seen) == list(one["users"])
+    for u, m in zip(one["users"], one["user_models"]):
+        assert np.max(np.abs(seen[int(u)] - m)) <= 1e-6 * max(1.0, np.max(np.abs(m)))
