@@ -6,7 +6,8 @@ import sys
 
 d = sys.argv[1] if len(sys.argv) > 1 else "gpurun_out"
 for tag, title in (("bench", "configs[1] value+gradient evals/s (strong scaling)"), ("c2", "configs[2] evals/s (weak scaling, 25 M rows per GPU)"),
-                   ("c4", "configs[4] per-entity problems solved/s (strong scaling)")):
+                   ("c3", "configs[3] GLMix coordinate descent, rows x passes per second (strong scaling)"),
+                   ("c4", "configs[4] per-member problems solved/s (strong scaling) and the full coordinate descent")):
     print(title)
     base = None
     for n in (1, 2, 4, 8):
@@ -23,4 +24,10 @@ for tag, title in (("bench", "configs[1] value+gradient evals/s (strong scaling)
             extra = " e2e %.1f (%.3f ms)" % (j["e2e"]["value"], j["e2e"]["ms_per_step"])
         if tag == "c2":
             extra += " rows/s %.3g" % j["rows_per_s"]
+        if tag == "c3":
+            extra += " wall %.3f s for %d passes over %d rows" % (j["wall_s"], j["steps"], j["config"]["rows_total"])
+        if tag == "c4" and j.get("coordinate_descent"):
+            cd = j["coordinate_descent"]
+            extra += "; fixed (%.3g entries) + per-member coordinate descent: %d passes over %d rows in %.3f s" % (
+                cd["fixed_effect_entries_total"], cd["passes"], cd["rows_total"], cd["wall_s"])
         print("  N=%d: %.1f %s, %.4f ms/step, efficiency %.3f%s" % (n, v, j["unit"], j["ms_per_step"], v / ideal, extra))
