@@ -1417,8 +1417,9 @@ def run_reference(args):
         "n_gpus": args.gpus, "steps": steps, "warmup": warmup, "ms_per_step": ms_per_step,
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": "configs[1]: Poisson regression, 10M rows x 1M feats, 66 Zipf(1.1) draws/row "
-                               "(%.1f stored nnz/row), fp64 values as the reference holds them; each step = one evaluation "
-                               "of ALL rows on the host cores" % (checksum[1] / checksum[0]),
+                               "(%.1f stored nnz/row), fp32 values, fp64 accumulation" % (checksum[1] / checksum[0]),
+                   "reference_arm": "the same rows (values widened to the Doubles the reference holds); each step = one "
+                                    "evaluation of ALL rows on the host cores, %d partitions / threads" % base["cores"],
                    "rows_total": N_ROWS, "d": N_FEATS, "rows_generated_on": where,
                    "data_checksum": dict(zip(("rows", "nnz", "sum_col", "sum_val", "sum_label"), checksum))},
         "cpu_baseline": base,
