@@ -606,7 +606,10 @@ __device__ __forceinline__ void seg_load_full(SegRegs<VT, ITEMS> &g, const int32
 // Pulls the lines of a chunk two steps ahead into L2 (no registers held): the register prefetch of the next chunk
 // then finds its data a few hundred cycles away instead of a DRAM round trip under load -- the first use of the
 // prefetched registers was the single largest stall of these kernels (ncu source view, long scoreboard).
-constexpr int PF_AHEAD = 4;  // chunks (per warp) between the L2 prefetch and the chunk being reduced
+#ifndef PML_PF_AHEAD
+#define PML_PF_AHEAD 4
+#endif
+constexpr int PF_AHEAD = PML_PF_AHEAD;  // chunks (per warp) between the L2 prefetch and the chunk being reduced
 
 template <typename VT, int ITEMS>
 __device__ __forceinline__ void seg_prefetch_l2(const int32_t *__restrict__ idx, const VT *__restrict__ val, int64_t chunk)
