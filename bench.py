@@ -744,18 +744,32 @@ def convergence(ctx, ds, d, host_rows=None):
     return out
 
 
-def make_entity_problems(rng, n_ent, k=10, d_e=32, rows=None):
-    """configs[4]-shaped per-entity problems: power-law rows per entity (Zipf(1.8), mean ~4, capped at 2000), k entries
-    per row in a d_e-dimensional per-entity space (after index-map projection), indicator values, ~10 % positives."""
-    if rows is None:
-        rows = np.minimum(rng.zipf(1.8, size=n_ent), 2000).astype(np.int64)
+def make_entity_problems(rng, n_ent, k=10, d_orig=200, rows=None, device=None):
+    """configs[4]-shaped per-entity problems: power-law rows per entity, k indicator features per row drawn
+    from a d_orig-dimensional member-side shard, ~10 % positives -- and then what GAME does before training a random
+    effect: every entity is projected onto the features ITS rows use (IndexMapProjectorRDD.scala:166-206; the same
+    numbering as photon_ml_b200.io.IndexMapProjection, done with torch.unique on the GPU here because of the size), so
+    per-entity dimensions come out at 10 ... ~40 and no projected column is empty."""
+    import torch
+    if rows is None:   # Pareto tail, mean ~3.3, capped (SURVEY 8d: "power-law, mean 4")
+        rows = np.minimum(np.floor(rng.random(n_ent) ** (-1.0 / 1.35)), 5000).astype(np.int64)
     ent_row_ptr = np.concatenate([[0], np.cumsum(rows)]).astype(np.int64)
     n = int(ent_row_ptr[-1])
-    col = np.sort(rng.integers(0, d_e, size=(n, k), dtype=np.int32), axis=1).ravel()
+    dev = device if device is not None else torch.device("cpu")
+    gen = torch.Generator(device=dev)
+    gen.manual_seed(int(rng.integers(1 << 31)))
+    col = torch.sort(torch.randint(0, d_orig, (n, k), generator=gen, device=dev, dtype=torch.int64), dim=1)[0].reshape(-1)
+    ent_of_entry = torch.repeat_interleave(torch.arange(n_ent, device=dev), torch.from_numpy(rows).to(dev) * k)
+    uniq, inverse = torch.unique(ent_of_entry * d_orig + col, return_inverse=True)
+    del col
+    ent_dim = torch.bincount(uniq // d_orig, minlength=n_ent)
+    coef_ptr = torch.cat([torch.zeros(1, dtype=torch.int64, device=dev), torch.cumsum(ent_dim, 0)])
+    col_local = (inverse - coef_ptr[ent_of_entry]).to(torch.int32).cpu().numpy()
+    del uniq, inverse, ent_of_entry
     row_ptr = np.arange(n + 1, dtype=np.int64) * k
     val = np.ones(n * k, dtype=np.float32)
     label = (rng.random(n) < 0.1).astype(np.float64)
-    return ent_row_ptr, np.full(n_ent, d_e, np.int32), row_ptr, col, val, label
+    return ent_row_ptr, ent_dim.to(torch.int32).cpu().numpy(), row_ptr, col_local, val, label
 
 
 def batch_bytes(n_ent, n, nnz, d_total, value_bytes):
@@ -771,8 +785,8 @@ def random_effect_batch(ctx, n_ent=1_000_000, seed=5, solver_runs=("skip", "stre
     import photon_ml_b200 as pml
     import torch
     rng = np.random.default_rng(seed)
-    k, d_e = 10, 32
-    ent_row_ptr, ent_dim, row_ptr, col, val, label = make_entity_problems(rng, n_ent, k, d_e)
+    k = 10
+    ent_row_ptr, ent_dim, row_ptr, col, val, label = make_entity_problems(rng, n_ent, k, device=torch.device("cuda", ctx.device))
     n = int(ent_row_ptr[-1])
     t0 = time.perf_counter()
     batch = pml.Batch(ctx, ent_row_ptr, ent_dim, row_ptr, col, val, label)
@@ -863,7 +877,7 @@ def run_config4(args):
     mine = np.flatnonzero(assignment == rank)
     ctx = pml.Context(local_rank)
     rng = np.random.default_rng(500 + rank)
-    ent_row_ptr, ent_dim, row_ptr, col, val, label = make_entity_problems(rng, len(mine), rows=rows_all[mine])
+    ent_row_ptr, ent_dim, row_ptr, col, val, label = make_entity_problems(rng, len(mine), rows=rows_all[mine], device=device)
     n = int(ent_row_ptr[-1])
     t0 = time.perf_counter()
     batch = pml.Batch(ctx, ent_row_ptr, ent_dim, row_ptr, col, val, label)
@@ -965,8 +979,9 @@ def run_config4(args):
             "metric": "per-entity problems solved/s (lock-step TRON, L2 logistic)", "value": ents_total / wall,
             "unit": "entities/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": eval_ms,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": "configs[4] random-effect coordinate: %d per-member problems (%d rows, 10 entries per row, "
-                                   "32-dim projected spaces), entities sharded over ranks, no collective" % (ents_total, rows_total),
+            "config": {"workload": "configs[4] random-effect coordinate: %d per-member problems (%d rows, 10 entries per row from a "
+                                   "200-dim member-side shard, index-map projected per member), entities sharded over ranks, "
+                                   "no collective" % (ents_total, rows_total),
                        "entities_rank0": int(len(mine)), "rows_rank0": n, "rows_max_over_ranks": int(mx[2]),
                        "partitioner": "bin packing of the 10000 heaviest entities + id mod N (RandomEffectDataSetPartitioner.scala:113-146)",
                        "pack_s_rank0": round(t_pack, 2)},
