@@ -253,7 +253,11 @@ int pml_batch_hessian_vector_dev(pml_batch *b, int loss, const double *coefs_dev
 /* residual offsets of all rows in concatenated order (LocalDataSet.addScoresToOffsets, api/data/LocalDataSet.scala:82-89) */
 int pml_batch_set_offsets(pml_batch *b, const double *offsets);
 /* active[e] == 0 takes entity e out of the following evaluations: its value, gradient and Hessian-vector entries
- * come back as 0 (a lock-step batched optimizer uses this for entities that have converged).  NULL = all active. */
+ * come back as 0 (a lock-step batched optimizer uses this for entities that have converged: in the reference such an
+ * entity's solve has simply ended, RandomEffectCoordinate.scala:112-119), and the parts of the data that hold only
+ * masked entities' rows are no longer streamed.  Scores (pml_scores* on pml_batch_dataset) are still computed for every
+ * row.  With coefficient tags, entities may only LEAVE the active set between Hessian-vector calls that share a tag
+ * (the cached curvature of rows skipped by the first call is not there).  NULL = all active. */
 int pml_batch_set_active(pml_batch *b, const uint8_t *active /* E, host */);
 
 /* Per-entity NormalizationContext (lib/normalization/NormalizationContext.scala:39-47; the random-effect problems
