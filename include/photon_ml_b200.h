@@ -340,6 +340,10 @@ int pml_value_and_gradient_allreduce(pml_dataset *ds, pml_peer *peer, int loss, 
                                      double *out_grad, int gather_output);
 int pml_hessian_vector_allreduce(pml_dataset *ds, pml_peer *peer, int loss, const double *coef, uint64_t coef_tag,
                                  const double *v, double *out_hv, int gather_output);
+/* DistributedGLMLossFunction.hessianDiagonal (DistributedGLMLossFunction.scala:134-137, HessianDiagonalAggregator.scala:
+ * 89-125) over all ranks' rows; like the reference it ignores the normalization context. */
+int pml_hessian_diagonal_allreduce(pml_dataset *ds, pml_peer *peer, int loss, const double *coef, double *out_diag,
+                                   int gather_output);
 /* 1 when an exchange on this handle gave up waiting for another rank (its result was filled with NaN);
  * pml_ctx_synchronize and every later *_allreduce* call on the handle then return PML_ECUDA. */
 int pml_peer_status(pml_peer *peer, int *out);

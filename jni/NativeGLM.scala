@@ -68,6 +68,8 @@ object NativeGLM {                       // 1:1 with jni/photon_ml_jni.c, which 
                                         gatherOutput: Boolean): Double
   @native def hessianVectorAllReduce(ds: Long, peer: Long, loss: Int, coef: Array[Double], tag: Long, v: Array[Double],
                                      out: Array[Double], gatherOutput: Boolean): Unit
+  @native def hessianDiagonalAllReduce(ds: Long, peer: Long, loss: Int, coef: Array[Double], out: Array[Double],
+                                       gatherOutput: Boolean): Unit
   @native def peerDestroy(peer: Long): Unit
 
   def lossId(f: PointwiseLossFunction): Int = f match {
@@ -232,8 +234,6 @@ protected[ml] class NativeDistributedGLMLossFunction private[glm] (loss: Int, sc
     Assemble(coefficients.value.length, parts)._2
   }
 
-  // HessianDiagonalAggregator has no exchange kernel of its own (called once per solve, computeVariances): every
-  // executor returns its rows' diagonal and the driver adds them up, as treeAggregate's merge did
   override protected[ml] def hessianDiagonal(
       input: RDD[LabeledPoint],
       coefficients: Broadcast[Vector[Double]]): Vector[Double] = {
@@ -241,13 +241,15 @@ protected[ml] class NativeDistributedGLMLossFunction private[glm] (loss: Int, sc
     val parent = input.dependencies.headOption.map(_.rdd.id)
     val lossId = loss
     val dev: Int => Int = deviceOf
-    input.mapPartitionsWithIndex { (part, points) =>
+    val parts = input.mapPartitionsWithIndex { (part, points) =>
       val ds = NativeExecutor.dataset(id, parent, points, lossId, dev(part))
       val w = coefficients.value.toArray
       val out = new Array[Double](w.length)
-      NativeGLM.hessianDiagonal(ds, lossId, w, out)
-      Iterator.single(DenseVector(out))
-    }.treeReduce(_ + _, treeAggregateDepth)
+      NativeGLM.hessianDiagonalAllReduce(ds, NativeExecutor.peerHandleValue, lossId, w, out, gatherOutput = false)
+      val (lo, hi) = NativeExecutor.slice
+      Iterator.single(Slice(lo, java.util.Arrays.copyOfRange(out, lo, hi), 0.0))
+    }.collect()
+    Assemble(coefficients.value.length, parts)._2
   }
 }
 

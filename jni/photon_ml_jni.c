@@ -350,6 +350,18 @@ NATIVE(void, hessianVectorAllReduce)(JNIEnv *env, jclass cls, jlong ds, jlong pe
     if (rc) throw_for(env, rc);
 }
 
+NATIVE(void, hessianDiagonalAllReduce)(JNIEnv *env, jclass cls, jlong ds, jlong peer, jint loss, jdoubleArray coef,
+                                       jdoubleArray out, jboolean gatherOutput)
+{
+    (void)cls;
+    double *w = pin(env, coef), *h = pin(env, out);
+    int rc = (w && h) ? pml_hessian_diagonal_allreduce(DS(ds), PEER(peer), (int)loss, w, h, gatherOutput ? 1 : 0) : PML_EINVAL;
+    unpin_out(env, out, h);
+    unpin_in(env, coef, w);
+    if (!(w && h)) { throw_msg(env, "java/lang/IllegalArgumentException", "null vector"); return; }
+    if (rc) throw_for(env, rc);
+}
+
 NATIVE(void, peerDestroy)(JNIEnv *env, jclass cls, jlong peer)
 {
     (void)cls;

@@ -37,7 +37,7 @@ SYMBOLS = [
     "pml_batch_set_active_dev", "pml_batch_segment_dot_dev", "pml_batch_segment_axpby_dev", "pml_loss_from_scores_dev",
     "pml_batch_set_normalization",
     "pml_peer_slice", "pml_value_and_gradient_allreduce", "pml_hessian_vector_allreduce", "pml_peer_status",
-    "pml_peer_emulate",
+    "pml_peer_emulate", "pml_hessian_diagonal_allreduce",
 ]
 
 
@@ -147,6 +147,7 @@ def load():
         "pml_value_and_gradient_allreduce": [vp, vp, ctypes.c_int, vp, ctypes.POINTER(dbl), vp, ctypes.c_int],
         "pml_hessian_vector_allreduce": [vp, vp, ctypes.c_int, vp, u64, vp, vp, ctypes.c_int],
         "pml_peer_status": [vp, ctypes.POINTER(ctypes.c_int)],
+        "pml_hessian_diagonal_allreduce": [vp, vp, ctypes.c_int, vp, vp, ctypes.c_int],
         "pml_peer_emulate": [vp, ctypes.c_int, i32, ctypes.c_int, vp, vp, vp, vp, vp, vp],
     })
     for name, argtypes in sigs.items():
@@ -645,6 +646,10 @@ class Peer:
                                                   None if coef is None else _ptr(_np(coef, np.float64, self.d, "coef")), tag,
                                                   _ptr(_np(v, np.float64, self.d, "v")), _ptr(out_hv),
                                                   1 if gather_output else 0))
+
+    def hessian_diagonal_host(self, ds, loss, coef, out_diag, gather_output=False):
+        check(load().pml_hessian_diagonal_allreduce(ds._h, self._h, loss, _ptr(_np(coef, np.float64, self.d, "coef")),
+                                                    _ptr(out_diag), 1 if gather_output else 0))
 
     def status(self):
         out = ctypes.c_int()

@@ -1751,6 +1751,26 @@ int pml_value_and_gradient_allreduce(pml_dataset *ds, pml_peer *peer, int loss, 
     return download_result(ds, peer, out_value, out_grad, gather_output);
 }
 
+// HessianDiagonalAggregator over all ranks' rows (DistributedGLMLossFunction.hessianDiagonal, :134-137): every rank's
+// diagonal sums, merged like the other two (no normalization: the reference's diagonal ignores it).  Host vectors.
+int pml_hessian_diagonal_allreduce(pml_dataset *ds, pml_peer *peer, int loss, const double *coef, double *out_diag,
+                                   int gather_output)
+{
+    PML_TRY(check_ds(ds));
+    PML_TRY(check_peer(ds, peer));
+    if (!valid_loss(loss)) return fail(PML_EINVAL, "unknown loss");
+    if (!coef) return fail(PML_EINVAL, "null buffer");
+    Guard g(ds->ctx);
+    PML_CUDA(cudaSetDevice(ds->ctx->device));
+    cudaStream_t s = ds->ctx->stream;
+    int n_vec = 1;
+    PML_TRY(upload_slices(ds, peer, coef, nullptr, &n_vec));
+    PML_TRY(run(ds->ctx, PML_K_PEER, [&] { return launch_peer_gather(s, ds->ctx->sm_count, peer, n_vec); }));
+    PML_TRY(diag_dev(ds, loss, peer_vec(peer, 0), peer_raw(peer)));
+    PML_TRY(run(ds->ctx, PML_K_PEER, [&] { return launch_peer_merge(s, ds->ctx->sm_count, peer, nullptr, nullptr); }));
+    return download_result(ds, peer, nullptr, out_diag, gather_output);
+}
+
 int pml_hessian_vector_allreduce(pml_dataset *ds, pml_peer *peer, int loss, const double *coef, uint64_t coef_tag,
                                  const double *v, double *out_hv, int gather_output)
 {

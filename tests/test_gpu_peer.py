@@ -180,9 +180,11 @@ def _host_worker(rank, world, port, loss, out_dir):
         peer.hessian_vector_host(ds, loss, None, v, shared_h, tag=9)      # cached pass: no coefficients needed
     values.append(peer.value_and_gradient_host(ds, loss, w, full_g, gather_output=True))
     peer.hessian_vector_host(ds, loss, w, v, full_h, gather_output=True)
+    full_d = np.zeros(d)
+    peer.hessian_diagonal_host(ds, loss, w, full_d, gather_output=True)
     shared_g.flush()
     shared_h.flush()
-    np.savez(os.path.join(out_dir, "host%d.npz" % rank), values=np.array(values), grad=full_g, hv=full_h,
+    np.savez(os.path.join(out_dir, "host%d.npz" % rank), values=np.array(values), grad=full_g, hv=full_h, diag=full_d,
              slice=np.array(peer.slice()), status=peer.status())
     dist.barrier()
     peer.close()
@@ -203,12 +205,14 @@ def test_host_buffer_allreduce_entry_points(tmp_path, world):
     full = oracle.Data(n, d, row_ptr, col, val, label, offset, weight)
     f_ref, g_ref = oracle.value_and_gradient(full, loss, w, f, s, icpt)
     hv_ref = oracle.hessian_vector(full, loss, w, v, f, s, icpt)
+    diag_ref = oracle.hessian_diagonal(full, loss, w)     # (no normalization in the diagonal, as in the reference)
     shared_g, shared_h = np.fromfile(str(tmp_path / "grad.bin")), np.fromfile(str(tmp_path / "hv.bin"))
     assert util.rel_err(shared_g, g_ref) <= TOL and util.rel_err(shared_h, hv_ref) <= TOL
     covered = np.zeros(d, dtype=int)
     for r in range(world):
         got = np.load(str(tmp_path / ("host%d.npz" % r)))
         assert got["status"] == 0
+        assert util.rel_err(got["diag"], diag_ref) <= TOL
         assert np.all(np.abs(got["values"] - f_ref) <= TOL * abs(f_ref))
         assert np.array_equal(got["grad"], shared_g)           # same path, same bits on every rank
         assert util.rel_err(got["hv"], shared_h) <= 1e-13      # margin pass recomputed vs cached curvature
