@@ -691,6 +691,18 @@ def convergence(ctx, ds, d, host_rows=None):
     #     through the host-buffer ABI every evaluation, numpy optimizer state) can be compared count by count
     out["tron_configs1_poisson_l2_1000_device_state"] = tron_device(1000.0, 100)
     out["tron_configs1_poisson_l2_1000"] = tron_host(DistributedGLMLossFunction.create(LOSS_POISSON, l2RegWeight=1000.0), ds, d, 100)
+    # (c') the metric's other optimizer on the same data: L-BFGS (Breeze-style driver, state in device memory)
+    for lam in (1.0, 1000.0):
+        obj = DeviceGLMLossFunction(ctx, LOSS_POISSON, l2RegWeight=lam)
+        lb = LBFGS(NoNormalization(), maxNumIterations=100)
+        with obj.stream():
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            _, f = lb.optimize(obj, torch.zeros(d, dtype=torch.float64, device=dev), ds)
+            torch.cuda.synchronize()
+            out["lbfgs_configs1_poisson_l2_%g_device_state" % lam] = {
+                "wall_s": time.perf_counter() - t0, "iterations": lb.currentState.iter, "reason": lb.convergenceReason,
+                "value_gradient_evals": lb.evaluations, "objective": f}
     # (d) the same driver on the CUDA objective and on the CPU oracle objective, first 500 k rows of the workload:
     #     iteration / evaluation / CG counts must agree (north star: identical iteration counts)
     if host_rows is not None:
