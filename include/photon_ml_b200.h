@@ -279,6 +279,15 @@ int pml_batch_set_active_dev(pml_batch *b, const uint8_t *active_dev /* E, devic
  *                  x or y; entities with active_dev[e] == 0 keep out_j, NULL = all)
  * Device pointers, asynchronous on the context's stream. */
 int pml_batch_segment_dot_dev(pml_batch *b, const double *x_dev, const double *y_dev, double *out_dev /* E */);
+/* One iteration of TRON.truncatedCG (lib/optimization/TRON.scala:300-336) for every entity with run[e] != 0, given
+ * hd = (unregularised) Hessian times `direction` from pml_batch_hessian_vector_dev: alpha = rTr / (d . Hd); step += alpha d;
+ * outside the trust region delta[e]: back to the boundary, residual updated, out_over[e] = 1 (the entity's loop ends);
+ * inside: residual -= alpha Hd, beta = r'.r' / rTr, direction = beta direction + residual, rtr[e] = r'.r', out_over[e] = 0.
+ * l2 adds the L2 mix-in's term (Hd += l2 * direction).  All vectors are the entities' vectors concatenated (pml_batch
+ * layout), rtr / delta / run / out_over have one slot per entity; everything in device memory, asynchronous. */
+int pml_batch_cg_step_dev(pml_batch *b, const uint8_t *run_dev, double l2, double *direction_dev, const double *hd_dev,
+                          double *step_dev, double *residual_dev, double *rtr_dev, const double *delta_dev,
+                          uint8_t *out_over_dev);
 int pml_batch_segment_axpby_dev(pml_batch *b, const double *a_dev /* E */, const double *x_dev, const double *c_dev /* E */,
                                 const double *y_dev, const uint8_t *active_dev /* E */, double *out_dev);
 

@@ -26,7 +26,7 @@ class BatchedTRON:
     MAX_CG_ITERATIONS = 20      # TRON.scala:97-98
 
     def __init__(self, batch, loss, l2RegWeight=0.0, tolerance=1.0e-5, maxNumIterations=15, maxNumImprovementFailures=5,
-                 skip_converged=True):
+                 skip_converged=True, fused_cg=True):
         import torch
         self.torch = torch
         self.batch, self.loss, self.l2 = batch, loss, float(l2RegWeight)
@@ -41,6 +41,7 @@ class BatchedTRON:
         self.hessian_vector_evaluations = 0
         self._tag = 0
         self.skip_converged, self._masked, self._mask8 = bool(skip_converged), False, None
+        self.fused_cg = bool(fused_cg)
 
     # ---- the library's batched kernels -------------------------------------------------------------------------
     def _new(self, n, dtype=None):
@@ -83,11 +84,11 @@ class BatchedTRON:
             self._axpby(self._l2_per_entity(), w, None, g, g)   # g += l2 * w: product rounded, then the sum
         return f, g
 
-    def _hessian_vector(self, w, v):
+    def _hessian_vector(self, w, v, regularize=True):
         hv = self._new(self.D)
         self.batch.hessian_vector_dev(self.loss, w.data_ptr(), v.data_ptr(), hv.data_ptr(), tag=self._tag)
         self.hessian_vector_evaluations += 1
-        if self.l2 != 0.0:
+        if self.l2 != 0.0 and regularize:
             self._axpby(self._l2_per_entity(), v, None, hv, hv)
         return hv
 
@@ -97,7 +98,37 @@ class BatchedTRON:
         return self._l2_vec
 
     # ---- TRON.truncatedCG for the entities in `mask` -------------------------------------------------------------
+    def _truncated_cg_fused(self, w, g, delta, mask):
+        """The same loop with the per-entity vector algebra of an iteration done by ONE kernel (pml_batch_cg_step_dev:
+        alpha, step, trust-region boundary, residual, beta, direction -- rounding for rounding what the unfused loop
+        below does with three dots and up to five axpy launches, each a pass over all entities' coefficients)."""
+        torch = self.torch
+        step = torch.zeros(self.D, dtype=torch.float64, device=self.device)
+        residual = -g
+        direction = residual.clone()
+        cg_tol = 0.1 * self._dot(g, g).sqrt()
+        rTr = self._dot(residual, residual)
+        delta = delta.contiguous()
+        iters = torch.zeros(self.E, dtype=torch.int64, device=self.device)
+        over8 = torch.zeros(self.E, dtype=torch.uint8, device=self.device)
+        done = ~mask
+        for _ in range(self.MAX_CG_ITERATIONS):
+            done = done | (rTr.sqrt() <= cg_tol)
+            if bool(done.all()):
+                break
+            run = ~done
+            iters += run
+            self._only(run)
+            Hd = self._hessian_vector(w, direction, regularize=False)
+            run8 = run.to(torch.uint8)
+            self.batch.cg_step_dev(run8.data_ptr(), self.l2, direction.data_ptr(), Hd.data_ptr(), step.data_ptr(),
+                                   residual.data_ptr(), rTr.data_ptr(), delta.data_ptr(), over8.data_ptr())
+            done = done | over8.to(torch.bool)
+        return iters, step, residual
+
     def _truncated_cg(self, w, g, delta, mask):
+        if self.fused_cg:
+            return self._truncated_cg_fused(w, g, delta, mask)
         torch = self.torch
         step = torch.zeros(self.D, dtype=torch.float64, device=self.device)
         residual = -g

@@ -1531,6 +1531,23 @@ int pml_batch_segment_dot_dev(pml_batch *b, const double *x_dev, const double *y
     });
 }
 
+int pml_batch_cg_step_dev(pml_batch *b, const uint8_t *run_dev, double l2, double *direction_dev, const double *hd_dev,
+                          double *step_dev, double *residual_dev, double *rtr_dev, const double *delta_dev,
+                          uint8_t *out_over_dev)
+{
+    if (!b || !b->ds) return fail(PML_EINVAL, "null batch handle");
+    if (b->n_entities > 0 && (!run_dev || !direction_dev || !hd_dev || !step_dev || !residual_dev || !rtr_dev || !delta_dev ||
+                              !out_over_dev))
+        return fail(PML_EINVAL, "null buffer");
+    Guard g(b->ds->ctx);
+    PML_CUDA(cudaSetDevice(b->ds->ctx->device));
+    PML_TRY(batch_index(b, false));
+    return run(b->ds->ctx, PML_K_ENTITY, [&] {
+        return launch_batch_cg_step(b->ds->ctx->stream, b->n_entities, b->coef_ptr_dev, run_dev, l2, direction_dev, hd_dev,
+                                    step_dev, residual_dev, rtr_dev, delta_dev, out_over_dev);
+    });
+}
+
 int pml_batch_segment_axpby_dev(pml_batch *b, const double *a_dev, const double *x_dev, const double *c_dev,
                                 const double *y_dev, const uint8_t *active_dev, double *out_dev)
 {

@@ -124,6 +124,9 @@ int launch_segment_dot(cudaStream_t s, int64_t n_entities, const int64_t *coef_p
                        double *out);
 int launch_segment_axpby(cudaStream_t s, int64_t d, const int32_t *ent_of, const double *a, const double *x,
                          const double *c, const double *y, const uint8_t *active, double *out);
+int launch_batch_cg_step(cudaStream_t s, int64_t n_entities, const int64_t *coef_ptr, const uint8_t *run, double l2,
+                         double *direction, const double *hd, double *step, double *residual, double *rtr,
+                         const double *delta, uint8_t *over);
 int launch_check_intercepts(cudaStream_t s, int value_bytes, int64_t n_entities, const int64_t *ent_row_ptr,
                             const uint32_t *row_ptr, const int32_t *col, const void *val, const int32_t *rank,
                             const int64_t *icpt_pos, unsigned long long *bad);

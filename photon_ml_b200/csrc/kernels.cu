@@ -1425,6 +1425,96 @@ int launch_segment_axpby(cudaStream_t s, int64_t d, const int32_t *ent_of, const
 }
 
 // ------------------------------------------------------------------------------------------
+// One iteration of TRON.truncatedCG (lib/optimization/TRON.scala:300-336) for every entity that is still in its CG
+// loop, after the batched Hessian-vector product Hd = H direction has been computed: the whole per-entity vector
+// algebra of the iteration -- alpha, the step, the trust-region boundary case, the residual, beta, the new direction
+// -- in ONE pass over the concatenated vectors instead of three dots and three to five axpy launches, each of which
+// streams every entity's coefficients.  A lane owns an entity (per-entity vectors are a few dozen coefficients; the
+// slices of a warp's 32 entities stay in L1 between the passes).  The arithmetic is the lock-step driver's, rounding
+// for rounding: dots are sequential fused multiply-adds in index order (segment_dot_kernel), every update is one
+// rounded product plus one rounded sum (segment_axpby_kernel), scalar expressions are evaluated without contraction.
+// The L2 term of L2RegularizationTwiceDiff (Hd += l2 * direction, lib/function/L2Regularization.scala:151-157,176)
+// is applied on the fly.
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+batch_cg_step_kernel(int64_t n_entities, const int64_t *__restrict__ coef_ptr, const uint8_t *__restrict__ run, double l2,
+                     double *__restrict__ direction, const double *__restrict__ hd, double *__restrict__ step,
+                     double *__restrict__ residual, double *__restrict__ rtr, const double *__restrict__ delta,
+                     uint8_t *__restrict__ over)
+{
+    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < n_entities; e += (int64_t)gridDim.x * blockDim.x) {
+        if (!run[e]) {
+            over[e] = 0;
+            continue;
+        }
+        const int64_t lo = coef_ptr[e], hi = coef_ptr[e + 1];
+        const bool reg = l2 != 0.0;
+        // alpha = rTr / (direction . Hd)
+        double dhd = 0.0;
+        for (int64_t j = lo; j < hi; ++j) {
+            const double h = reg ? __dadd_rn(__dmul_rn(l2, direction[j]), hd[j]) : hd[j];
+            dhd = fma(direction[j], h, dhd);
+        }
+        const double r0 = rtr[e];
+        const double alpha = r0 / dhd;
+        // step += alpha * direction; is it still inside the trust region?
+        double sts = 0.0;
+        for (int64_t j = lo; j < hi; ++j) {
+            const double sj = __dadd_rn(__dmul_rn(alpha, direction[j]), step[j]);
+            step[j] = sj;
+            sts = fma(sj, sj, sts);
+        }
+        const double dl = delta[e];
+        if (sqrt(sts) > dl) {
+            // back to the boundary along `direction`, then stop (TRON.scala:311-327)
+            double std_ = 0.0, sts2 = 0.0, dtd = 0.0;
+            const double na = -alpha;
+            for (int64_t j = lo; j < hi; ++j) {
+                const double sj = __dadd_rn(__dmul_rn(na, direction[j]), step[j]);
+                step[j] = sj;
+                std_ = fma(sj, direction[j], std_);
+                sts2 = fma(sj, sj, sts2);
+                dtd = fma(direction[j], direction[j], dtd);
+            }
+            const double dsq = __dmul_rn(dl, dl);
+            const double rad = sqrt(__dadd_rn(__dmul_rn(std_, std_), __dmul_rn(dtd, __dsub_rn(dsq, sts2))));
+            const double alpha_b = std_ >= 0.0 ? __dsub_rn(dsq, sts2) / __dadd_rn(std_, rad) : __dsub_rn(rad, std_) / dtd;
+            const double nab = -alpha_b;
+            for (int64_t j = lo; j < hi; ++j) {
+                const double h = reg ? __dadd_rn(__dmul_rn(l2, direction[j]), hd[j]) : hd[j];
+                step[j] = __dadd_rn(__dmul_rn(alpha_b, direction[j]), step[j]);
+                residual[j] = __dadd_rn(__dmul_rn(nab, h), residual[j]);
+            }
+            over[e] = 1;
+        } else {
+            const double na = -alpha;
+            double rnew = 0.0;
+            for (int64_t j = lo; j < hi; ++j) {
+                const double h = reg ? __dadd_rn(__dmul_rn(l2, direction[j]), hd[j]) : hd[j];
+                const double rj = __dadd_rn(__dmul_rn(na, h), residual[j]);
+                residual[j] = rj;
+                rnew = fma(rj, rj, rnew);
+            }
+            const double beta = rnew / r0;
+            for (int64_t j = lo; j < hi; ++j) direction[j] = __dadd_rn(__dmul_rn(beta, direction[j]), residual[j]);
+            rtr[e] = rnew;
+            over[e] = 0;
+        }
+    }
+}
+
+int launch_batch_cg_step(cudaStream_t s, int64_t n_entities, const int64_t *coef_ptr, const uint8_t *run, double l2,
+                         double *direction, const double *hd, double *step, double *residual, double *rtr,
+                         const double *delta, uint8_t *over)
+{
+    if (n_entities <= 0) return 0;
+    int64_t grid = (n_entities + 255) / 256;
+    if (grid > 148 * 16) grid = 148 * 16;
+    batch_cg_step_kernel<<<(int)grid, 256, 0, s>>>(n_entities, coef_ptr, run, l2, direction, hd, step, residual, rtr, delta, over);
+    return cudaGetLastError() == cudaSuccess ? 1 : -1;
+}
+
+// ------------------------------------------------------------------------------------------
 // Per-entity NormalizationContext of a batch (every entity of a random-effect coordinate trains in the transformed
 // space of ITS projected features: ValueAndGradientAggregator.init / getVector, :90-122 and :199-221, per entity).
 // Shifts need an intercept, and the intercept column is 1 in every row, so the per-entity scalars fold into the

@@ -86,3 +86,26 @@ def test_segment_dot_and_axpby():
     assert np.array_equal(res2, a[ent] * x + y)
     batch.close()
     ctx.close()
+
+
+def test_fused_cg_step_is_the_unfused_loop_rounding_for_rounding():
+    """pml_batch_cg_step_dev does an iteration's per-entity vector algebra in one kernel; for entities below 64
+    coefficients (lane-per-entity dots in index order in both forms) the iterates are bit-identical."""
+    import photon_ml_b200 as pml
+    from photon_ml_b200.batched import BatchedTRON
+    rng = np.random.default_rng(91)
+    ent_row_ptr, dims, row_ptr, col, val, n = _entities(rng, 400, 20, 30)
+    label = util.labels_for(rng, oracle.LOGISTIC, n)
+    ctx = pml.Context(0)
+    batch = pml.Batch(ctx, ent_row_ptr, dims, row_ptr, col, val, label, rng.normal(scale=0.2, size=n))
+    out = {}
+    for fused in (True, False):
+        for l2 in (0.0, 0.7):
+            w, f, info = BatchedTRON(batch, oracle.LOGISTIC, l2RegWeight=l2, fused_cg=fused).optimize()
+            out[(fused, l2)] = (w.cpu().numpy(), f.cpu().numpy(), info["iterations"], info["cg_iterations"], info["reasons"])
+    for l2 in (0.0, 0.7):
+        a, b = out[(True, l2)], out[(False, l2)]
+        assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
+        assert np.array_equal(a[2], b[2]) and np.array_equal(a[3], b[3]) and np.array_equal(a[4], b[4])
+    batch.close()
+    ctx.close()
