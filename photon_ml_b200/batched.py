@@ -26,7 +26,7 @@ class BatchedTRON:
     MAX_CG_ITERATIONS = 20      # TRON.scala:97-98
 
     def __init__(self, batch, loss, l2RegWeight=0.0, tolerance=1.0e-5, maxNumIterations=15, maxNumImprovementFailures=5,
-                 skip_converged=True, fused_cg=True):
+                 skip_converged=True, fused_cg=False):
         import torch
         self.torch = torch
         self.batch, self.loss, self.l2 = batch, loss, float(l2RegWeight)
@@ -41,6 +41,9 @@ class BatchedTRON:
         self.hessian_vector_evaluations = 0
         self._tag = 0
         self.skip_converged, self._masked, self._mask8 = bool(skip_converged), False, None
+        # fused_cg: one kernel per CG iteration for the per-entity vector algebra (pml_batch_cg_step_dev).  Off by
+        # default: measured SLOWER than the unfused loop (10^6 entities: 0.061 vs 0.047 s per solve) -- a lane walking
+        # its own entity's slices makes every load its own wavefront, while the unfused dots / axpys stream coalesced.
         self.fused_cg = bool(fused_cg)
 
     # ---- the library's batched kernels -------------------------------------------------------------------------
