@@ -791,7 +791,7 @@ def batch_bytes(n_ent, n, nnz, d_total, value_bytes):
     return 2 * nnz * (value_bytes + 4) + n * (8 + 16 + 16) + (n + 1) * 4 + d_total * 4 + d_total * 16 + n_ent * (8 + 8 + 8)
 
 
-def random_effect_batch(ctx, n_ent=1_000_000, seed=5, solver_runs=("skip", "stream-all", "fused-cg")):
+def random_effect_batch(ctx, n_ent=1_000_000, seed=5, solver_runs=("skip", "stream-all", "unfused-cg")):
     """configs[4]-shaped per-entity batch (default: 1/10 scale, 1 M entities): every entity's value+gradient in one
     call, with its roofline, and every entity's L2-regularised problem solved in lock step."""
     import photon_ml_b200 as pml
@@ -853,13 +853,13 @@ def random_effect_batch(ctx, n_ent=1_000_000, seed=5, solver_runs=("skip", "stre
     BatchedTRON(batch, pml.LOGISTIC, l2RegWeight=1.0, maxNumIterations=2).optimize()
     for mode in solver_runs:
         solver = BatchedTRON(batch, pml.LOGISTIC, l2RegWeight=1.0, skip_converged=(mode != "stream-all"),
-                             fused_cg=(mode == "fused-cg"))
+                             fused_cg=(mode != "unfused-cg"))
         ctx.synchronize()
         t0 = time.perf_counter()
         _, _, sinfo = solver.optimize()
         wall = time.perf_counter() - t0
         out["lockstep_tron_logistic_l2_1" + {"skip": "", "stream-all": "_streaming_converged_entities",
-                                             "fused-cg": "_cg_step_in_one_kernel"}[mode]] = {
+                                             "unfused-cg": "_cg_step_as_dots_and_axpys"}[mode]] = {
             "wall_s": wall, "entities_solved_per_s": n_ent / wall, "batched_value_gradient_evals": sinfo["evaluations"],
             "batched_hessian_vector_evals": sinfo["hessian_vector_evaluations"],
             "mean_iterations_per_entity": float(sinfo["iterations"].mean()),

@@ -26,7 +26,7 @@ class BatchedTRON:
     MAX_CG_ITERATIONS = 20      # TRON.scala:97-98
 
     def __init__(self, batch, loss, l2RegWeight=0.0, tolerance=1.0e-5, maxNumIterations=15, maxNumImprovementFailures=5,
-                 skip_converged=True, fused_cg=False):
+                 skip_converged=True, fused_cg=True):
         import torch
         self.torch = torch
         self.batch, self.loss, self.l2 = batch, loss, float(l2RegWeight)
@@ -41,14 +41,29 @@ class BatchedTRON:
         self.hessian_vector_evaluations = 0
         self._tag = 0
         self.skip_converged, self._masked, self._mask8 = bool(skip_converged), False, None
-        # fused_cg: one kernel per CG iteration for the per-entity vector algebra (pml_batch_cg_step_dev).  Off by
-        # default: measured SLOWER than the unfused loop (10^6 entities: 0.061 vs 0.047 s per solve) -- a lane walking
-        # its own entity's slices makes every load its own wavefront, while the unfused dots / axpys stream coalesced.
+        # fused_cg: one kernel per CG iteration for the per-entity vector algebra (pml_batch_cg_step_dev) instead of
+        # three dots and up to five axpy launches; same rounding, so the iterates are bit-identical either way.
+        # 10^6 entities: 0.038 s per solve against 0.044 s unfused (profiles/r02_re_solve_profile.json).
         self.fused_cg = bool(fused_cg)
 
     # ---- the library's batched kernels -------------------------------------------------------------------------
     def _new(self, n, dtype=None):
         return self.torch.empty(n, dtype=dtype or self.torch.float64, device=self.device)
+
+    def _download_counts(self, *tensors):
+        """Per-entity counters to numpy (int32) in ONE copy through a pinned buffer kept on the batch: three pageable
+        int64 copies of 10^6 entities cost several milliseconds, a fifth of a whole lock-step solve."""
+        torch = self.torch
+        stacked = torch.stack([t.to(torch.int32) for t in tensors])
+        host = getattr(self.batch, "_counts_host", None)
+        if host is None or host.numel() < stacked.numel():
+            host = torch.empty(stacked.numel(), dtype=torch.int32, pin_memory=True)
+            self.batch._counts_host = host
+        view = host[:stacked.numel()].view(stacked.shape)
+        # (a blocking copy: a non-blocking one ties the pinned block to the context's stream inside torch's host
+        # allocator, which then records an event on that stream when the block is freed -- after Context.close())
+        view.copy_(stacked)
+        return [view[i].numpy().copy() for i in range(len(tensors))]
 
     def _dot(self, x, y):
         out = self._new(self.E)
@@ -244,8 +259,8 @@ class BatchedTRON:
                 reason = torch.where(newly, r, reason)
                 done = done | newly
             self._only(None)
-            self.batch.ctx.synchronize()
-            info = {"iterations": it.cpu().numpy(), "reasons": reason.cpu().numpy(), "cg_iterations": cg_total.cpu().numpy(),
+            its, reasons, cgs = self._download_counts(it, reason, cg_total)
+            info = {"iterations": its, "reasons": reasons, "cg_iterations": cgs,
                     "evaluations": self.evaluations, "hessian_vector_evaluations": self.hessian_vector_evaluations}
         return w, f, info
 

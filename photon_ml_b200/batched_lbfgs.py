@@ -305,8 +305,7 @@ class BatchedLBFGS(BatchedTRON):
                 reason = t.where(newly, r, reason)
                 done = done | newly
             self._only(None)
-            self.batch.ctx.synchronize()
-            info = {"iterations": it.cpu().numpy(), "reasons": reason.cpu().numpy(),
-                    "entity_evaluations": self.entity_evaluations.cpu().numpy(), "evaluations": self.evaluations}
+            its, reasons, evals = self._download_counts(it, reason, self.entity_evaluations)
+            info = {"iterations": its, "reasons": reasons, "entity_evaluations": evals, "evaluations": self.evaluations}
             self._S = self._Y = self._rho = None
         return x, cur_f, info

@@ -1436,69 +1436,214 @@ int launch_segment_axpby(cudaStream_t s, int64_t d, const int32_t *ent_of, const
 // The L2 term of L2RegularizationTwiceDiff (Hd += l2 * direction, lib/function/L2Regularization.scala:151-157,176)
 // is applied on the fly.
 // ------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256)
-batch_cg_step_kernel(int64_t n_entities, const int64_t *__restrict__ coef_ptr, const uint8_t *__restrict__ run, double l2,
-                     double *__restrict__ direction, const double *__restrict__ hd, double *__restrict__ step,
-                     double *__restrict__ residual, double *__restrict__ rtr, const double *__restrict__ delta,
-                     uint8_t *__restrict__ over)
+// The per-entity work of one CG iteration on the slices [lo, hi) of the four vectors (pointers may be global or
+// shared memory).  Returns 1 when the step left the trust region.
+__device__ __forceinline__ int cg_step_entity(int64_t lo, int64_t hi, double l2, double *direction, const double *hd,
+                                              double *step, double *residual, double *rtr_e, double dl)
 {
-    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < n_entities; e += (int64_t)gridDim.x * blockDim.x) {
-        if (!run[e]) {
-            over[e] = 0;
-            continue;
+    const bool reg = l2 != 0.0;
+    // alpha = rTr / (direction . Hd)
+    double dhd = 0.0;
+    for (int64_t j = lo; j < hi; ++j) {
+        const double h = reg ? __dadd_rn(__dmul_rn(l2, direction[j]), hd[j]) : hd[j];
+        dhd = fma(direction[j], h, dhd);
+    }
+    const double r0 = *rtr_e;
+    const double alpha = r0 / dhd;
+    // step += alpha * direction; is it still inside the trust region?
+    double sts = 0.0;
+    for (int64_t j = lo; j < hi; ++j) {
+        const double sj = __dadd_rn(__dmul_rn(alpha, direction[j]), step[j]);
+        step[j] = sj;
+        sts = fma(sj, sj, sts);
+    }
+    if (sqrt(sts) > dl) {
+        // back to the boundary along `direction`, then stop (TRON.scala:311-327)
+        double std_ = 0.0, sts2 = 0.0, dtd = 0.0;
+        const double na = -alpha;
+        for (int64_t j = lo; j < hi; ++j) {
+            const double sj = __dadd_rn(__dmul_rn(na, direction[j]), step[j]);
+            step[j] = sj;
+            std_ = fma(sj, direction[j], std_);
+            sts2 = fma(sj, sj, sts2);
+            dtd = fma(direction[j], direction[j], dtd);
         }
-        const int64_t lo = coef_ptr[e], hi = coef_ptr[e + 1];
-        const bool reg = l2 != 0.0;
-        // alpha = rTr / (direction . Hd)
-        double dhd = 0.0;
+        const double dsq = __dmul_rn(dl, dl);
+        const double rad = sqrt(__dadd_rn(__dmul_rn(std_, std_), __dmul_rn(dtd, __dsub_rn(dsq, sts2))));
+        const double alpha_b = std_ >= 0.0 ? __dsub_rn(dsq, sts2) / __dadd_rn(std_, rad) : __dsub_rn(rad, std_) / dtd;
+        const double nab = -alpha_b;
         for (int64_t j = lo; j < hi; ++j) {
             const double h = reg ? __dadd_rn(__dmul_rn(l2, direction[j]), hd[j]) : hd[j];
-            dhd = fma(direction[j], h, dhd);
+            step[j] = __dadd_rn(__dmul_rn(alpha_b, direction[j]), step[j]);
+            residual[j] = __dadd_rn(__dmul_rn(nab, h), residual[j]);
         }
-        const double r0 = rtr[e];
-        const double alpha = r0 / dhd;
-        // step += alpha * direction; is it still inside the trust region?
-        double sts = 0.0;
-        for (int64_t j = lo; j < hi; ++j) {
-            const double sj = __dadd_rn(__dmul_rn(alpha, direction[j]), step[j]);
+        return 1;
+    }
+    const double na = -alpha;
+    double rnew = 0.0;
+    for (int64_t j = lo; j < hi; ++j) {
+        const double h = reg ? __dadd_rn(__dmul_rn(l2, direction[j]), hd[j]) : hd[j];
+        const double rj = __dadd_rn(__dmul_rn(na, h), residual[j]);
+        residual[j] = rj;
+        rnew = fma(rj, rj, rnew);
+    }
+    const double beta = rnew / r0;
+    for (int64_t j = lo; j < hi; ++j) direction[j] = __dadd_rn(__dmul_rn(beta, direction[j]), residual[j]);
+    *rtr_e = rnew;
+    return 0;
+}
+
+// The same for an entity of 64 coefficients and more, by the whole warp: lanes stride the slice (coalesced without any
+// staging), dots are per-lane fused multiply-adds closed by the fixed shuffle tree -- segment_dot_kernel's order for
+// such entities.  Every lane returns the same flag.
+__device__ __forceinline__ int cg_step_entity_warp(int lane, int64_t lo, int64_t hi, double l2, double *direction,
+                                                   const double *hd, double *step, double *residual, double *rtr_e, double dl)
+{
+    const bool reg = l2 != 0.0;
+    double dhd = 0.0;
+    for (int64_t j = lo + lane; j < hi; j += 32) {
+        const double h = reg ? __dadd_rn(__dmul_rn(l2, direction[j]), hd[j]) : hd[j];
+        dhd = fma(direction[j], h, dhd);
+    }
+    dhd = warp_sum(dhd);
+    const double r0 = *rtr_e;
+    const double alpha = r0 / dhd;
+    double sts = 0.0;
+    for (int64_t j = lo + lane; j < hi; j += 32) {
+        const double sj = __dadd_rn(__dmul_rn(alpha, direction[j]), step[j]);
+        step[j] = sj;
+        sts = fma(sj, sj, sts);
+    }
+    sts = warp_sum(sts);
+    if (sqrt(sts) > dl) {
+        double std_ = 0.0, sts2 = 0.0, dtd = 0.0;
+        const double na = -alpha;
+        for (int64_t j = lo + lane; j < hi; j += 32) {
+            const double sj = __dadd_rn(__dmul_rn(na, direction[j]), step[j]);
             step[j] = sj;
-            sts = fma(sj, sj, sts);
+            std_ = fma(sj, direction[j], std_);
+            sts2 = fma(sj, sj, sts2);
+            dtd = fma(direction[j], direction[j], dtd);
         }
-        const double dl = delta[e];
-        if (sqrt(sts) > dl) {
-            // back to the boundary along `direction`, then stop (TRON.scala:311-327)
-            double std_ = 0.0, sts2 = 0.0, dtd = 0.0;
-            const double na = -alpha;
-            for (int64_t j = lo; j < hi; ++j) {
-                const double sj = __dadd_rn(__dmul_rn(na, direction[j]), step[j]);
-                step[j] = sj;
-                std_ = fma(sj, direction[j], std_);
-                sts2 = fma(sj, sj, sts2);
-                dtd = fma(direction[j], direction[j], dtd);
+        std_ = warp_sum(std_);
+        sts2 = warp_sum(sts2);
+        dtd = warp_sum(dtd);
+        const double dsq = __dmul_rn(dl, dl);
+        const double rad = sqrt(__dadd_rn(__dmul_rn(std_, std_), __dmul_rn(dtd, __dsub_rn(dsq, sts2))));
+        const double alpha_b = std_ >= 0.0 ? __dsub_rn(dsq, sts2) / __dadd_rn(std_, rad) : __dsub_rn(rad, std_) / dtd;
+        const double nab = -alpha_b;
+        for (int64_t j = lo + lane; j < hi; j += 32) {
+            const double h = reg ? __dadd_rn(__dmul_rn(l2, direction[j]), hd[j]) : hd[j];
+            step[j] = __dadd_rn(__dmul_rn(alpha_b, direction[j]), step[j]);
+            residual[j] = __dadd_rn(__dmul_rn(nab, h), residual[j]);
+        }
+        return 1;
+    }
+    const double na = -alpha;
+    double rnew = 0.0;
+    for (int64_t j = lo + lane; j < hi; j += 32) {
+        const double h = reg ? __dadd_rn(__dmul_rn(l2, direction[j]), hd[j]) : hd[j];
+        const double rj = __dadd_rn(__dmul_rn(na, h), residual[j]);
+        residual[j] = rj;
+        rnew = fma(rj, rj, rnew);
+    }
+    rnew = warp_sum(rnew);
+    const double beta = rnew / r0;
+    for (int64_t j = lo + lane; j < hi; j += 32) direction[j] = __dadd_rn(__dmul_rn(beta, direction[j]), residual[j]);
+    *rtr_e = rnew;
+    return 0;
+}
+
+// A warp walks 32 consecutive entities.  Their slices are contiguous in the concatenated vectors, so the warp copies
+// as many whole entities as fit its staging area to shared memory with coalesced loads, every lane then works on ITS
+// entity there, and the three vectors that change go back coalesced; left to walk global memory on its own a lane
+// makes every load a wavefront of its own (measured: slower than the unfused loop).  Entities of 64 coefficients and
+// more are then done by the whole warp straight from global memory.
+constexpr int CG_WARPS = 7;
+constexpr int CG_CAP = 1024;  // doubles per vector and warp: 4 vectors x 8 KB x 7 warps = 224 KB, one CTA per SM.  32 entities
+                              // of a few dozen coefficients fit in one go; more than that and the group takes two passes
+constexpr int CG_BIG = 64;    // segment_dot_kernel's threshold
+
+__global__ void __launch_bounds__(32 * CG_WARPS)
+batch_cg_step_kernel(int64_t n_entities, const int64_t *__restrict__ coef_ptr, const uint8_t *__restrict__ run, double l2,
+                     double *direction, const double *hd, double *step, double *residual, double *__restrict__ rtr,
+                     const double *__restrict__ delta, uint8_t *__restrict__ over)
+{
+    extern __shared__ __align__(16) double cg_smem[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    double *s_dir = cg_smem + (size_t)warp * 4 * CG_CAP, *s_hd = s_dir + CG_CAP, *s_step = s_hd + CG_CAP, *s_res = s_step + CG_CAP;
+    const int64_t n_groups = (n_entities + 31) >> 5;
+    for (int64_t grp = (int64_t)blockIdx.x * CG_WARPS + warp; grp < n_groups; grp += (int64_t)gridDim.x * CG_WARPS) {
+        const int64_t e0 = grp << 5;
+        const int64_t e_end = e0 + 32 < n_entities ? e0 + 32 : n_entities;
+        {
+            const int64_t e = e0 + lane;
+            const bool mine = e < e_end && run[e] != 0;
+            if (e < e_end && !mine) over[e] = 0;
+            if (!__any_sync(0xffffffffu, mine)) continue;
+        }
+        int64_t es = e0;
+        while (es < e_end) {                                   // warp-uniform
+            const int64_t e = es + lane;
+            const bool valid = e < e_end;
+            const int64_t p0 = coef_ptr[es];
+            const int64_t lo = valid ? coef_ptr[e] : p0, hi = valid ? coef_ptr[e + 1] : p0;
+            // how many whole entities from `es` on fit the staging area (a prefix of the lanes)
+            const unsigned fits = __ballot_sync(0xffffffffu, valid && hi - p0 <= CG_CAP);
+            int take = __ffs(~fits) - 1;                       // leading ones; fits == all ones gives -1 + 0 ...
+            if (fits == 0xffffffffu) take = 32;
+            const bool mine = valid && run[e] != 0;
+            const bool big = hi - lo >= CG_BIG;
+            double r = 0.0, dl = 0.0;
+            if (mine) {
+                r = rtr[e];
+                dl = delta[e];
             }
-            const double dsq = __dmul_rn(dl, dl);
-            const double rad = sqrt(__dadd_rn(__dmul_rn(std_, std_), __dmul_rn(dtd, __dsub_rn(dsq, sts2))));
-            const double alpha_b = std_ >= 0.0 ? __dsub_rn(dsq, sts2) / __dadd_rn(std_, rad) : __dsub_rn(rad, std_) / dtd;
-            const double nab = -alpha_b;
-            for (int64_t j = lo; j < hi; ++j) {
-                const double h = reg ? __dadd_rn(__dmul_rn(l2, direction[j]), hd[j]) : hd[j];
-                step[j] = __dadd_rn(__dmul_rn(alpha_b, direction[j]), step[j]);
-                residual[j] = __dadd_rn(__dmul_rn(nab, h), residual[j]);
+            int took = take;
+            if (take > 0) {
+                const unsigned small = __ballot_sync(0xffffffffu, lane < take && mine && !big);
+                if (small != 0) {
+                    const int64_t p1 = __shfl_sync(0xffffffffu, hi, take - 1);
+                    const int len = (int)(p1 - p0);
+                    for (int k = lane; k < len; k += 32) {
+                        s_dir[k] = direction[p0 + k];
+                        s_hd[k] = hd[p0 + k];
+                        s_step[k] = step[p0 + k];
+                        s_res[k] = residual[p0 + k];
+                    }
+                    __syncwarp();
+                    if (lane < take && mine && !big) {
+                        over[e] = (uint8_t)cg_step_entity(lo - p0, hi - p0, l2, s_dir, s_hd, s_step, s_res, &r, dl);
+                        rtr[e] = r;
+                    }
+                    __syncwarp();
+                    // entities of the range that are masked or left to the warp get their own (unchanged) values back:
+                    // harmless, and it keeps the stores coalesced
+                    for (int k = lane; k < len; k += 32) {
+                        direction[p0 + k] = s_dir[k];
+                        step[p0 + k] = s_step[k];
+                        residual[p0 + k] = s_res[k];
+                    }
+                    __syncwarp();
+                }
+            } else {
+                took = 1;                                      // entity `es` alone is larger than the staging area
             }
-            over[e] = 1;
-        } else {
-            const double na = -alpha;
-            double rnew = 0.0;
-            for (int64_t j = lo; j < hi; ++j) {
-                const double h = reg ? __dadd_rn(__dmul_rn(l2, direction[j]), hd[j]) : hd[j];
-                const double rj = __dadd_rn(__dmul_rn(na, h), residual[j]);
-                residual[j] = rj;
-                rnew = fma(rj, rj, rnew);
+            unsigned todo = __ballot_sync(0xffffffffu, lane < took && mine && big);
+            while (todo) {
+                const int src = __ffs(todo) - 1;
+                todo &= todo - 1;
+                const int64_t blo = __shfl_sync(0xffffffffu, lo, src), bhi = __shfl_sync(0xffffffffu, hi, src);
+                double br = __shfl_sync(0xffffffffu, r, src);
+                const double bdl = __shfl_sync(0xffffffffu, dl, src);
+                const int flag = cg_step_entity_warp(lane, blo, bhi, l2, direction, hd, step, residual, &br, bdl);
+                if (lane == 0) {
+                    over[es + src] = (uint8_t)flag;
+                    rtr[es + src] = br;
+                }
+                __syncwarp();
             }
-            const double beta = rnew / r0;
-            for (int64_t j = lo; j < hi; ++j) direction[j] = __dadd_rn(__dmul_rn(beta, direction[j]), residual[j]);
-            rtr[e] = rnew;
-            over[e] = 0;
+            es += took;
         }
     }
 }
@@ -1508,9 +1653,13 @@ int launch_batch_cg_step(cudaStream_t s, int64_t n_entities, const int64_t *coef
                          const double *delta, uint8_t *over)
 {
     if (n_entities <= 0) return 0;
-    int64_t grid = (n_entities + 255) / 256;
-    if (grid > 148 * 16) grid = 148 * 16;
-    batch_cg_step_kernel<<<(int)grid, 256, 0, s>>>(n_entities, coef_ptr, run, l2, direction, hd, step, residual, rtr, delta, over);
+    const size_t smem = sizeof(double) * 4 * CG_CAP * CG_WARPS;
+    if (cudaFuncSetAttribute(batch_cg_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
+        return -1;   // (per device; a few hundred nanoseconds)
+    int64_t grid = ((n_entities + 31) / 32 + CG_WARPS - 1) / CG_WARPS;
+    if (grid > 148) grid = 148;
+    batch_cg_step_kernel<<<(int)grid, 32 * CG_WARPS, smem, s>>>(n_entities, coef_ptr, run, l2, direction, hd, step, residual, rtr,
+                                                                 delta, over);
     return cudaGetLastError() == cudaSuccess ? 1 : -1;
 }
 

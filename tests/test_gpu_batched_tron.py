@@ -88,13 +88,16 @@ def test_segment_dot_and_axpby():
     ctx.close()
 
 
-def test_fused_cg_step_is_the_unfused_loop_rounding_for_rounding():
-    """pml_batch_cg_step_dev does an iteration's per-entity vector algebra in one kernel; for entities below 64
-    coefficients (lane-per-entity dots in index order in both forms) the iterates are bit-identical."""
+@pytest.mark.parametrize("max_dim,n_ent", [(20, 400), (150, 300), (1500, 70)])
+def test_fused_cg_step_is_the_unfused_loop_rounding_for_rounding(max_dim, n_ent):
+    """pml_batch_cg_step_dev does an iteration's per-entity vector algebra in one kernel, with the unfused loop's
+    rounding: a lane per entity below 64 coefficients (dots in index order), the whole warp with the fixed shuffle
+    tree from 64 on.  max_dim 150: 32 consecutive entities do not fit the staging area in one go; 1500: single
+    entities larger than the staging area."""
     import photon_ml_b200 as pml
     from photon_ml_b200.batched import BatchedTRON
     rng = np.random.default_rng(91)
-    ent_row_ptr, dims, row_ptr, col, val, n = _entities(rng, 400, 20, 30)
+    ent_row_ptr, dims, row_ptr, col, val, n = _entities(rng, n_ent, max_dim, 30)
     label = util.labels_for(rng, oracle.LOGISTIC, n)
     ctx = pml.Context(0)
     batch = pml.Batch(ctx, ent_row_ptr, dims, row_ptr, col, val, label, rng.normal(scale=0.2, size=n))
