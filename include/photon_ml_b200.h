@@ -288,6 +288,21 @@ int pml_batch_segment_dot_dev(pml_batch *b, const double *x_dev, const double *y
 int pml_batch_cg_step_dev(pml_batch *b, const uint8_t *run_dev, double l2, double *direction_dev, const double *hd_dev,
                           double *step_dev, double *residual_dev, double *rtr_dev, const double *delta_dev,
                           uint8_t *out_over_dev);
+/* The L-BFGS direction for every entity with go[e] != 0 (NULL = all) in one kernel: Breeze's two-loop recursion, which
+ * lib/optimization/LBFGS.scala:59-107 runs for ONE problem through breeze.optimize.LBFGS (numCorrections pairs,
+ * LBFGS.scala:44, 69-76) --  q = -grad; newest pair to oldest: a_i = rho_i (s_i . q), q -= a_i y_i; q *= s.y / y.y of the
+ * newest pair; oldest to newest: q += (a_i - rho_i (y_i . q)) s_i.  S / Y hold the correction pairs as m concatenated
+ * vectors each (slot-major, m x D doubles), rho their 1 / (y . s) as m x E; every entity keeps its own ring: head[e] is
+ * the slot of its newest pair, len[e] <= m how many it holds (0: the direction is -grad).  Entities that are not worked
+ * on keep out[] as it is.  1 <= m <= 16.  pml_batch_lbfgs_push_dev appends (s, y, rho_new) for every entity with
+ * mask[e] != 0: head advances (a dropped history, len = 0, starts again at slot 0), len grows up to m.
+ * Everything in device memory, asynchronous on the context's stream. */
+int pml_batch_lbfgs_direction_dev(pml_batch *b, const uint8_t *go_dev /* E or NULL */, int m, const double *S_dev,
+                                  const double *Y_dev, const double *rho_dev, const int32_t *head_dev /* E */,
+                                  const int32_t *len_dev /* E */, const double *grad_dev, double *out_dev);
+int pml_batch_lbfgs_push_dev(pml_batch *b, const uint8_t *mask_dev /* E */, int m, const double *rho_new_dev /* E */,
+                             const double *s_dev, const double *y_dev, double *S_dev, double *Y_dev, double *rho_dev,
+                             int32_t *head_dev, int32_t *len_dev);
 int pml_batch_segment_axpby_dev(pml_batch *b, const double *a_dev /* E */, const double *x_dev, const double *c_dev /* E */,
                                 const double *y_dev, const uint8_t *active_dev /* E */, double *out_dev);
 

@@ -37,7 +37,7 @@ SYMBOLS = [
     "pml_batch_set_active_dev", "pml_batch_segment_dot_dev", "pml_batch_segment_axpby_dev", "pml_loss_from_scores_dev",
     "pml_batch_set_normalization",
     "pml_peer_slice", "pml_value_and_gradient_allreduce", "pml_hessian_vector_allreduce", "pml_peer_status",
-    "pml_peer_emulate", "pml_hessian_diagonal_allreduce", "pml_batch_cg_step_dev",
+    "pml_peer_emulate", "pml_hessian_diagonal_allreduce", "pml_batch_cg_step_dev", "pml_batch_lbfgs_direction_dev", "pml_batch_lbfgs_push_dev",
 ]
 
 
@@ -142,6 +142,8 @@ def load():
         "pml_batch_segment_dot_dev": [vp, vp, vp, vp],
         "pml_batch_segment_axpby_dev": [vp, vp, vp, vp, vp, vp, vp],
         "pml_batch_cg_step_dev": [vp, vp, dbl, vp, vp, vp, vp, vp, vp, vp],
+        "pml_batch_lbfgs_direction_dev": [vp, vp, ctypes.c_int, vp, vp, vp, vp, vp, vp, vp],
+        "pml_batch_lbfgs_push_dev": [vp, vp, ctypes.c_int, vp, vp, vp, vp, vp, vp, vp, vp],
         "pml_value_and_gradient_allreduce_dev": [vp, vp, ctypes.c_int, vp, vp, vp],
         "pml_hessian_vector_allreduce_dev": [vp, vp, ctypes.c_int, vp, u64, vp, vp],
         "pml_peer_slice": [vp, ctypes.POINTER(i64), ctypes.POINTER(i64)],
@@ -483,6 +485,14 @@ class Batch:
     def segment_dot_dev(self, x_dev, y_dev, out_dev):
         """out[e] = sum_j x_j y_j over entity e's coefficients (device addresses; E doubles out)."""
         check(load().pml_batch_segment_dot_dev(self._h, x_dev, y_dev, out_dev))
+
+    def lbfgs_direction_dev(self, go_dev, m, S_dev, Y_dev, rho_dev, head_dev, len_dev, grad_dev, out_dev):
+        check(load().pml_batch_lbfgs_direction_dev(self._h, go_dev, int(m), S_dev, Y_dev, rho_dev, head_dev, len_dev, grad_dev,
+                                                   out_dev))
+
+    def lbfgs_push_dev(self, mask_dev, m, rho_new_dev, s_dev, y_dev, S_dev, Y_dev, rho_dev, head_dev, len_dev):
+        check(load().pml_batch_lbfgs_push_dev(self._h, mask_dev, int(m), rho_new_dev, s_dev, y_dev, S_dev, Y_dev, rho_dev,
+                                              head_dev, len_dev))
 
     def cg_step_dev(self, run_dev, l2, direction_dev, hd_dev, step_dev, residual_dev, rtr_dev, delta_dev, out_over_dev):
         check(load().pml_batch_cg_step_dev(self._h, run_dev, float(l2), direction_dev, hd_dev, step_dev, residual_dev, rtr_dev,

@@ -8,8 +8,10 @@ slot per entity, every branch a mask, every vector operation a batched kernel ov
 single-problem run on entity e would.  The strong-Wolfe line search is a per-entity state machine (bracketing, then
 zoom): entities sit in different phases at different step lengths, and each round evaluates all trial points with ONE
 batched value+gradient call; entities whose search has ended are masked out and their rows are no longer streamed.
-The correction pairs are kept as 2 x m concatenated vectors ordered oldest to newest per entity; an entity that skips
-an update (curvature test) or drops its history keeps its own list, invalid slots carrying rho = 0.
+The correction pairs are kept as 2 x m concatenated vectors; every entity has its own ring in them (an entity that
+skips an update -- curvature test -- or drops its history keeps its own list), and the two-loop recursion is one kernel
+(pml_batch_lbfgs_direction_dev).  fused_direction=False is the same algebra as 2m dots and 2m + 1 axpys over lists
+ordered oldest to newest, invalid slots carrying rho = 0; both give the same bits.
 
 Like optimization.LBFGS this is NOT Breeze-verified (Breeze 0.11.2 is not in the reference tree): counts are
 comparable with optimization.LBFGS / OWLQN on the same objective, entity by entity (tests/test_gpu_batched_lbfgs.py).
@@ -28,10 +30,14 @@ class BatchedLBFGS(BatchedTRON):
     C1, C2, LS_MAX_ITER, LS_MAX_ZOOM = 1e-4, 0.9, 10, 10     # optimization._strong_wolfe
 
     def __init__(self, batch, loss, l2RegWeight=0.0, l1RegWeight=0.0, numCorrections=10, tolerance=1.0e-7,
-                 maxNumIterations=100, skip_converged=True):
+                 maxNumIterations=100, skip_converged=True, fused_direction=True):
         super().__init__(batch, loss, l2RegWeight=l2RegWeight, tolerance=tolerance, maxNumIterations=maxNumIterations,
                          skip_converged=skip_converged)
         self.m, self.l1 = int(numCorrections), float(l1RegWeight)
+        # fused_direction: the two-loop recursion is ONE kernel (pml_batch_lbfgs_direction_dev) over per-entity rings of
+        # correction pairs instead of 2m dots and 2m + 1 axpys, and a push writes one slot instead of shifting 2(m - 1)
+        # vectors; same rounding, so the iterates are bit-identical either way (the ABI takes up to 16 pairs).
+        self.fused_direction = bool(fused_direction) and self.m <= 16
         self.entity_evaluations = None
 
     # ---- small helpers ------------------------------------------------------------------------------------------
@@ -73,8 +79,16 @@ class BatchedLBFGS(BatchedTRON):
         return adj_f, pg
 
     # ---- L-BFGS two-loop recursion over per-entity histories (optimization.LBFGS._direction) ----------------------
-    def _direction(self, adj_g):
+    def _direction(self, adj_g, go):
         t = self.torch
+        if self.fused_direction:
+            q = self._zeros(self.D)
+            self.batch.lbfgs_direction_dev(go.to(t.uint8).data_ptr(), self.m, self._S.data_ptr(), self._Y.data_ptr(),
+                                           self._rho.data_ptr(), self._head.data_ptr(), self._len.data_ptr(),
+                                           adj_g.data_ptr(), q.data_ptr())
+            if self.l1 != 0.0:
+                q = t.where(q * adj_g < 0, q, t.zeros_like(q))
+            return q
         q = -adj_g
         alphas = [None] * self.m
         for i in range(self.m - 1, -1, -1):              # newest (slot m-1) to oldest; rho = 0 where the slot is empty
@@ -96,6 +110,12 @@ class BatchedLBFGS(BatchedTRON):
         """Append (s, y) to the history of the entities in mask: their slots shift down by one, the newest goes last."""
         t = self.torch
         m8 = mask.to(t.uint8)
+        if self.fused_direction:
+            rho_new = 1.0 / self._dot(y, s)
+            self.batch.lbfgs_push_dev(m8.data_ptr(), self.m, rho_new.data_ptr(), s.data_ptr(), y.data_ptr(),
+                                      self._S.data_ptr(), self._Y.data_ptr(), self._rho.data_ptr(), self._head.data_ptr(),
+                                      self._len.data_ptr())
+            return
         for i in range(self.m - 1):
             self._axpby(None, self._S[i + 1], None, None, self._S[i], m8)
             self._axpby(None, self._Y[i + 1], None, None, self._Y[i], m8)
@@ -107,6 +127,9 @@ class BatchedLBFGS(BatchedTRON):
 
     def _drop_history(self, mask):
         t = self.torch
+        if self.fused_direction:
+            self._len.masked_fill_(mask, 0)
+            return
         for i in range(self.m):
             self._rho[i] = t.where(mask, t.zeros_like(self._rho[i]), self._rho[i])
         self._len = t.where(mask, t.zeros_like(self._len), self._len)
@@ -246,10 +269,15 @@ class BatchedLBFGS(BatchedTRON):
             grad_tol = self._dot(g0, g0).sqrt() * self.tol
             cur_f, cur_g = self._evaluate(x, everybody)                 # currentState: (loss, gradient) as the Optimizer sees them
             f, g = self._evaluate(x, everybody)                         # the L-BFGS inner state
-            self._S = [self._zeros(D) for _ in range(self.m)]
-            self._Y = [self._zeros(D) for _ in range(self.m)]
-            self._rho = [self._zeros(E) for _ in range(self.m)]
-            self._len = t.zeros(E, dtype=t.int64, device=self.device)
+            if self.fused_direction:
+                self._S, self._Y, self._rho = self._zeros(self.m * D), self._zeros(self.m * D), self._zeros(self.m * E)
+                self._head = t.zeros(E, dtype=t.int32, device=self.device)
+                self._len = t.zeros(E, dtype=t.int32, device=self.device)
+            else:
+                self._S = [self._zeros(D) for _ in range(self.m)]
+                self._Y = [self._zeros(D) for _ in range(self.m)]
+                self._rho = [self._zeros(E) for _ in range(self.m)]
+                self._len = t.zeros(E, dtype=t.int64, device=self.device)
             inner_iter = t.zeros(E, dtype=t.int64, device=self.device)
             inner_converged = t.zeros(E, dtype=t.bool, device=self.device)
             it = t.zeros(E, dtype=t.int64, device=self.device)
@@ -263,7 +291,7 @@ class BatchedLBFGS(BatchedTRON):
                 inner_converged = inner_converged | (active & stationary)
                 go = active & ~inner_converged                          # the others hand back the same state
                 if bool(go.any()):
-                    direction = self._direction(adj_g)
+                    direction = self._direction(adj_g, go)
                     gd = self._dot(adj_g, direction)
                     not_descent = go & (gd >= 0)
                     if bool(not_descent.any()):

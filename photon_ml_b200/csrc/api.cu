@@ -1548,6 +1548,40 @@ int pml_batch_cg_step_dev(pml_batch *b, const uint8_t *run_dev, double l2, doubl
     });
 }
 
+int pml_batch_lbfgs_direction_dev(pml_batch *b, const uint8_t *go_dev, int m, const double *S_dev, const double *Y_dev,
+                                  const double *rho_dev, const int32_t *head_dev, const int32_t *len_dev,
+                                  const double *grad_dev, double *out_dev)
+{
+    if (!b || !b->ds) return fail(PML_EINVAL, "null batch handle");
+    if (m < 1 || m > 16) return fail(PML_EINVAL, "1 to 16 correction pairs");
+    if (b->n_entities > 0 && (!S_dev || !Y_dev || !rho_dev || !head_dev || !len_dev || !grad_dev || !out_dev))
+        return fail(PML_EINVAL, "null buffer");
+    Guard g(b->ds->ctx);
+    PML_CUDA(cudaSetDevice(b->ds->ctx->device));
+    PML_TRY(batch_index(b, false));
+    return run(b->ds->ctx, PML_K_ENTITY, [&] {
+        return launch_batch_lbfgs_direction(b->ds->ctx->stream, b->n_entities, b->ds->d, b->coef_ptr_dev, go_dev, m, S_dev, Y_dev,
+                                            rho_dev, head_dev, len_dev, grad_dev, out_dev);
+    });
+}
+
+int pml_batch_lbfgs_push_dev(pml_batch *b, const uint8_t *mask_dev, int m, const double *rho_new_dev, const double *s_dev,
+                             const double *y_dev, double *S_dev, double *Y_dev, double *rho_dev, int32_t *head_dev,
+                             int32_t *len_dev)
+{
+    if (!b || !b->ds) return fail(PML_EINVAL, "null batch handle");
+    if (m < 1 || m > 16) return fail(PML_EINVAL, "1 to 16 correction pairs");
+    if (b->n_entities > 0 && (!mask_dev || !rho_new_dev || !s_dev || !y_dev || !S_dev || !Y_dev || !rho_dev || !head_dev || !len_dev))
+        return fail(PML_EINVAL, "null buffer");
+    Guard g(b->ds->ctx);
+    PML_CUDA(cudaSetDevice(b->ds->ctx->device));
+    PML_TRY(batch_index(b, true));
+    return run(b->ds->ctx, PML_K_ENTITY, [&] {
+        return launch_batch_lbfgs_push(b->ds->ctx->stream, b->n_entities, b->ds->d, b->ent_of_coef, mask_dev, m, rho_new_dev,
+                                       s_dev, y_dev, S_dev, Y_dev, rho_dev, head_dev, len_dev);
+    });
+}
+
 int pml_batch_segment_axpby_dev(pml_batch *b, const double *a_dev, const double *x_dev, const double *c_dev,
                                 const double *y_dev, const uint8_t *active_dev, double *out_dev)
 {

@@ -127,6 +127,12 @@ int launch_segment_axpby(cudaStream_t s, int64_t d, const int32_t *ent_of, const
 int launch_batch_cg_step(cudaStream_t s, int64_t n_entities, const int64_t *coef_ptr, const uint8_t *run, double l2,
                          double *direction, const double *hd, double *step, double *residual, double *rtr,
                          const double *delta, uint8_t *over);
+int launch_batch_lbfgs_direction(cudaStream_t s, int64_t n_entities, int64_t d_total, const int64_t *coef_ptr, const uint8_t *go,
+                                 int m, const double *S, const double *Y, const double *rho, const int32_t *head,
+                                 const int32_t *len, const double *grad, double *out);
+int launch_batch_lbfgs_push(cudaStream_t st, int64_t n_entities, int64_t d, const int32_t *ent_of, const uint8_t *mask, int m,
+                            const double *rho_new, const double *s, const double *y, double *S, double *Y, double *rho,
+                            int32_t *head, int32_t *len);
 int launch_check_intercepts(cudaStream_t s, int value_bytes, int64_t n_entities, const int64_t *ent_row_ptr,
                             const uint32_t *row_ptr, const int32_t *col, const void *val, const int32_t *rank,
                             const int64_t *icpt_pos, unsigned long long *bad);

@@ -1664,6 +1664,258 @@ int launch_batch_cg_step(cudaStream_t s, int64_t n_entities, const int64_t *coef
 }
 
 // ------------------------------------------------------------------------------------------
+// L-BFGS two-loop recursion for every entity of a batch in ONE kernel (Breeze's LBFGS direction as the lock-step driver
+// states it, batched_lbfgs.BatchedLBFGS._direction; lib/optimization/LBFGS.scala:59-107 hands the problem to Breeze):
+//   q = -g;  newest pair to oldest: a_i = rho_i (s_i . q), q -= a_i y_i;  q *= (s.y / y.y) of the newest pair;
+//   oldest to newest: b = rho_i (y_i . q), q += (a_i - b) s_i.
+// The unfused loop is 2m dots and 2m + 1 axpys, each a launch and a pass over every entity's coefficients.  The
+// correction pairs live in 2 x m concatenated vectors (slot-major); every entity has its own ring position: head[e] is
+// the slot of its newest pair, len[e] how many it holds.  Same rounding as the unfused loop: dots are sequential fused
+// multiply-adds in index order below 64 coefficients and lane-strided with the fixed shuffle tree from 64 on
+// (segment_dot_kernel), every update is one rounded product plus one rounded sum (segment_axpby_kernel).
+// ------------------------------------------------------------------------------------------
+constexpr int LB_WARPS = 8;
+constexpr int LB_CAP = 1024;     // doubles per staged vector and warp: 3 x 8 KB + 2 KB of ring positions, 8 warps = 208 KB
+constexpr int LB_MAX_M = 16;
+
+struct LbfgsParams {
+    int64_t n_entities, d_total;
+    const int64_t *coef_ptr;
+    const uint8_t *go;
+    int m;
+    const double *S, *Y, *rho;   // m x d_total, m x d_total, m x n_entities
+    const int32_t *head, *len;
+    const double *grad;
+    double *out;
+};
+
+__device__ __forceinline__ int lb_slot(int head, int t, int m)
+{
+    const int s = head - t;
+    return s < 0 ? s + m : s;
+}
+
+// an entity of 64 coefficients and more, by the whole warp straight from global memory; q lives in `out`
+__device__ __forceinline__ void lbfgs_direction_warp(const LbfgsParams &p, int lane, int64_t e, int64_t lo, int64_t hi)
+{
+    double *q = p.out;
+    for (int64_t j = lo + lane; j < hi; j += 32) q[j] = -p.grad[j];
+    const int n = p.len[e], head = p.head[e];
+    double alpha[LB_MAX_M];
+    double scale = 1.0;
+#pragma unroll 1
+    for (int t = 0; t < n; ++t) {
+        const int slot = lb_slot(head, t, p.m);
+        const double *s = p.S + (int64_t)slot * p.d_total, *y = p.Y + (int64_t)slot * p.d_total;
+        double sq = 0.0;
+        for (int64_t j = lo + lane; j < hi; j += 32) sq = fma(s[j], q[j], sq);
+        sq = warp_sum(sq);
+        const double a = __dmul_rn(p.rho[(int64_t)slot * p.n_entities + e], sq);
+        alpha[t] = a;
+        const double na = -a;
+        if (t == 0) {
+            double sy = 0.0, yy = 0.0;
+            for (int64_t j = lo + lane; j < hi; j += 32) {
+                sy = fma(s[j], y[j], sy);
+                yy = fma(y[j], y[j], yy);
+            }
+            scale = warp_sum(sy) / warp_sum(yy);
+        }
+        for (int64_t j = lo + lane; j < hi; j += 32) q[j] = __dadd_rn(q[j], __dmul_rn(na, y[j]));
+    }
+    for (int64_t j = lo + lane; j < hi; j += 32) q[j] = __dmul_rn(scale, q[j]);
+#pragma unroll 1
+    for (int t = n - 1; t >= 0; --t) {
+        const int slot = lb_slot(head, t, p.m);
+        const double *s = p.S + (int64_t)slot * p.d_total, *y = p.Y + (int64_t)slot * p.d_total;
+        double yq = 0.0;
+        for (int64_t j = lo + lane; j < hi; j += 32) yq = fma(y[j], q[j], yq);
+        yq = warp_sum(yq);
+        const double c = __dsub_rn(alpha[t], __dmul_rn(p.rho[(int64_t)slot * p.n_entities + e], yq));
+        for (int64_t j = lo + lane; j < hi; j += 32) q[j] = __dadd_rn(q[j], __dmul_rn(c, s[j]));
+    }
+}
+
+// Stage pair t (0 = newest) of the entities of a staged range: element k of the range belongs to an entity whose ring
+// position is in pos[k]; elements of entities that hold fewer than t + 1 pairs (or are not worked on) are left alone.
+__device__ __forceinline__ void lb_stage(const LbfgsParams &p, int lane, int t, int64_t p0, int n, const uint16_t *pos,
+                                         double *sA, double *sB)
+{
+    for (int k = lane; k < n; k += 32) {
+        const unsigned w = pos[k];
+        if (t < (int)((w >> 8) & 0x7fu)) {
+            const int64_t at = (int64_t)lb_slot((int)(w & 0xffu), t, p.m) * p.d_total + p0 + k;
+            sA[k] = p.S[at];
+            sB[k] = p.Y[at];
+        }
+    }
+}
+
+// A warp walks 32 consecutive entities as batch_cg_step_kernel does: the gradient slices of as many whole entities as
+// fit go to shared memory (q), then pair by pair the s and y slices are staged with coalesced loads and every lane
+// works on ITS entity there; q goes back coalesced.  Entities of 64 coefficients and more: the whole warp, from global.
+__global__ void __launch_bounds__(32 * LB_WARPS) batch_lbfgs_direction_kernel(const LbfgsParams p)
+{
+    extern __shared__ __align__(16) double lb_smem[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    double *sQ = lb_smem + (size_t)warp * 3 * LB_CAP, *sA = sQ + LB_CAP, *sB = sA + LB_CAP;
+    uint16_t *sPos = reinterpret_cast<uint16_t *>(lb_smem + (size_t)LB_WARPS * 3 * LB_CAP) + (size_t)warp * LB_CAP;
+    const int64_t n_groups = (p.n_entities + 31) >> 5;
+    for (int64_t grp = (int64_t)blockIdx.x * LB_WARPS + warp; grp < n_groups; grp += (int64_t)gridDim.x * LB_WARPS) {
+        const int64_t e0 = grp << 5;
+        const int64_t e_end = e0 + 32 < p.n_entities ? e0 + 32 : p.n_entities;
+        {
+            const int64_t e = e0 + lane;
+            if (!__any_sync(0xffffffffu, e < e_end && (p.go == nullptr || p.go[e] != 0))) continue;
+        }
+        int64_t es = e0;
+        while (es < e_end) {                                   // warp-uniform
+            const int64_t e = es + lane;
+            const bool valid = e < e_end;
+            const int64_t p0 = p.coef_ptr[es];
+            const int64_t lo = valid ? p.coef_ptr[e] : p0, hi = valid ? p.coef_ptr[e + 1] : p0;
+            const unsigned fits = __ballot_sync(0xffffffffu, valid && hi - p0 <= LB_CAP);
+            int take = fits == 0xffffffffu ? 32 : __ffs(~fits) - 1;   // whole entities from `es` on that fit the staging area
+            const bool mine = valid && (p.go == nullptr || p.go[e] != 0);
+            const bool big = hi - lo >= CG_BIG;
+            int took = take;
+            if (take > 0) {
+                const bool small = lane < take && mine && !big;
+                if (__any_sync(0xffffffffu, small)) {
+                    const int n = (int)(__shfl_sync(0xffffffffu, hi, take - 1) - p0);
+                    const int my_len = small ? p.len[e] : 0, my_head = small ? p.head[e] : 0;
+                    const int a0 = (int)(lo - p0), a1 = (int)(hi - p0);
+                    for (int k = lane; k < n; k += 32) {
+                        sPos[k] = 0;
+                        sQ[k] = -p.grad[p0 + k];
+                    }
+                    __syncwarp();
+                    if (small) {
+                        const uint16_t w = (uint16_t)(0x8000u | ((unsigned)my_len << 8) | (unsigned)my_head);
+                        for (int j = a0; j < a1; ++j) sPos[j] = w;
+                    }
+                    __syncwarp();
+                    const int L = __reduce_max_sync(0xffffffffu, my_len);
+                    double alpha[LB_MAX_M];
+                    double scale = 1.0;
+#pragma unroll 1
+                    for (int t = 0; t < L; ++t) {
+                        lb_stage(p, lane, t, p0, n, sPos, sA, sB);
+                        __syncwarp();
+                        if (t < my_len) {
+                            double sq = 0.0;
+                            for (int j = a0; j < a1; ++j) sq = fma(sA[j], sQ[j], sq);
+                            const double a = __dmul_rn(p.rho[(int64_t)lb_slot(my_head, t, p.m) * p.n_entities + e], sq);
+                            alpha[t] = a;
+                            const double na = -a;
+                            if (t == 0) {
+                                double sy = 0.0, yy = 0.0;
+                                for (int j = a0; j < a1; ++j) {
+                                    sy = fma(sA[j], sB[j], sy);
+                                    yy = fma(sB[j], sB[j], yy);
+                                }
+                                scale = sy / yy;
+                            }
+                            for (int j = a0; j < a1; ++j) sQ[j] = __dadd_rn(sQ[j], __dmul_rn(na, sB[j]));
+                        }
+                        __syncwarp();
+                    }
+                    if (small)
+                        for (int j = a0; j < a1; ++j) sQ[j] = __dmul_rn(scale, sQ[j]);
+#pragma unroll 1
+                    for (int t = L - 1; t >= 0; --t) {
+                        if (t != L - 1) {                      // pair L-1 is still there from the first loop
+                            lb_stage(p, lane, t, p0, n, sPos, sA, sB);
+                            __syncwarp();
+                        }
+                        if (t < my_len) {
+                            double yq = 0.0;
+                            for (int j = a0; j < a1; ++j) yq = fma(sB[j], sQ[j], yq);
+                            const double c = __dsub_rn(alpha[t], __dmul_rn(p.rho[(int64_t)lb_slot(my_head, t, p.m) * p.n_entities + e], yq));
+                            for (int j = a0; j < a1; ++j) sQ[j] = __dadd_rn(sQ[j], __dmul_rn(c, sA[j]));
+                        }
+                        __syncwarp();
+                    }
+                    for (int k = lane; k < n; k += 32)
+                        if (sPos[k] & 0x8000u) p.out[p0 + k] = sQ[k];
+                    __syncwarp();
+                }
+            } else {
+                took = 1;                                      // entity `es` alone is larger than the staging area
+            }
+            unsigned todo = __ballot_sync(0xffffffffu, lane < took && mine && big);
+            while (todo) {
+                const int src = __ffs(todo) - 1;
+                todo &= todo - 1;
+                lbfgs_direction_warp(p, lane, es + src, __shfl_sync(0xffffffffu, lo, src), __shfl_sync(0xffffffffu, hi, src));
+            }
+            es += took;
+        }
+    }
+}
+
+int launch_batch_lbfgs_direction(cudaStream_t s, int64_t n_entities, int64_t d_total, const int64_t *coef_ptr, const uint8_t *go,
+                                 int m, const double *S, const double *Y, const double *rho, const int32_t *head,
+                                 const int32_t *len, const double *grad, double *out)
+{
+    if (n_entities <= 0) return 0;
+    if (m < 1 || m > LB_MAX_M) return -1;
+    const size_t smem = sizeof(double) * 3 * LB_CAP * LB_WARPS + sizeof(uint16_t) * LB_CAP * LB_WARPS;
+    if (cudaFuncSetAttribute(batch_lbfgs_direction_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
+        return -1;
+    LbfgsParams p{n_entities, d_total, coef_ptr, go, m, S, Y, rho, head, len, grad, out};
+    int64_t grid = ((n_entities + 31) / 32 + LB_WARPS - 1) / LB_WARPS;
+    if (grid > 148) grid = 148;
+    batch_lbfgs_direction_kernel<<<(int)grid, 32 * LB_WARPS, smem, s>>>(p);
+    return cudaGetLastError() == cudaSuccess ? 1 : -1;
+}
+
+// Append (s, y) to the ring of every entity with mask[e] != 0: the entity pass moves head / len and stores rho, the
+// coefficient pass then copies the two vectors into the entity's new slot.
+__global__ void lbfgs_push_entity_kernel(int64_t n_entities, const uint8_t *__restrict__ mask, int m, const double *__restrict__ rho_new,
+                                         double *__restrict__ rho, int32_t *__restrict__ head, int32_t *__restrict__ len)
+{
+    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < n_entities; e += (int64_t)gridDim.x * blockDim.x) {
+        if (!mask[e]) continue;
+        const int n = len[e];
+        const int h = n == 0 ? 0 : (head[e] + 1 == m ? 0 : head[e] + 1);
+        head[e] = h;
+        len[e] = n < m ? n + 1 : m;
+        rho[(int64_t)h * n_entities + e] = rho_new[e];
+    }
+}
+
+__global__ void lbfgs_push_coef_kernel(int64_t d, const int32_t *__restrict__ ent_of, const uint8_t *__restrict__ mask,
+                                       const int32_t *__restrict__ head, const double *__restrict__ s, const double *__restrict__ y,
+                                       double *__restrict__ S, double *__restrict__ Y)
+{
+    for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < d; j += (int64_t)gridDim.x * blockDim.x) {
+        const int32_t e = ent_of[j];
+        if (!mask[e]) continue;
+        const int64_t at = (int64_t)head[e] * d + j;
+        S[at] = s[j];
+        Y[at] = y[j];
+    }
+}
+
+int launch_batch_lbfgs_push(cudaStream_t st, int64_t n_entities, int64_t d, const int32_t *ent_of, const uint8_t *mask, int m,
+                            const double *rho_new, const double *s, const double *y, double *S, double *Y, double *rho,
+                            int32_t *head, int32_t *len)
+{
+    if (n_entities <= 0) return 0;
+    if (m < 1 || m > LB_MAX_M) return -1;
+    int64_t grid = (n_entities + 255) / 256;
+    if (grid > 148 * 16) grid = 148 * 16;
+    lbfgs_push_entity_kernel<<<(int)grid, 256, 0, st>>>(n_entities, mask, m, rho_new, rho, head, len);
+    if (d > 0) {
+        grid = (d + 255) / 256;
+        if (grid > 148 * 16) grid = 148 * 16;
+        lbfgs_push_coef_kernel<<<(int)grid, 256, 0, st>>>(d, ent_of, mask, head, s, y, S, Y);
+    }
+    return cudaGetLastError() == cudaSuccess ? 2 : -1;
+}
+
+// ------------------------------------------------------------------------------------------
 // Per-entity NormalizationContext of a batch (every entity of a random-effect coordinate trains in the transformed
 // space of ITS projected features: ValueAndGradientAggregator.init / getVector, :90-122 and :199-221, per entity).
 // Shifts need an intercept, and the intercept column is 1 in every row, so the per-entity scalars fold into the

@@ -70,3 +70,52 @@ def test_every_entity_follows_its_own_owlqn_run(loss, l1):
     # (a little L2 next to the L1 term keeps every tiny per-entity problem well conditioned: without it an entity whose
     # rows barely determine a coefficient ends 1e-4 apart in that coefficient at an objective difference of 1e-9)
     _check(loss, 0.1, l1)
+
+
+@pytest.mark.parametrize("max_dim,n_ent", [(20, 300), (150, 200), (1500, 40)])
+@pytest.mark.parametrize("l1,m", [(0.0, 10), (0.3, 10), (0.0, 3)])
+def test_fused_direction_is_the_unfused_recursion_rounding_for_rounding(max_dim, n_ent, l1, m):
+    """pml_batch_lbfgs_direction_dev / pml_batch_lbfgs_push_dev (one kernel for the two-loop recursion over per-entity
+    rings of correction pairs) against the same algebra as 2m dots and 2m + 1 axpys over shifted lists: bit-identical
+    iterates.  max_dim 150: 32 consecutive entities do not fit the staging area in one go, and entities on both sides
+    of the 64-coefficient switch to whole-warp dots; 1500: entities larger than the staging area.  m = 3: rings wrap
+    early and the oldest pairs are overwritten."""
+    import photon_ml_b200 as pml
+    from photon_ml_b200.batched_lbfgs import BatchedLBFGS
+    rng = np.random.default_rng(17)
+    ent_row_ptr, dims, row_ptr, col, val, n = _entities(rng, n_ent, max_dim, 30)
+    label = util.labels_for(rng, oracle.LOGISTIC, n)
+    ctx = pml.Context(0)
+    batch = pml.Batch(ctx, ent_row_ptr, dims, row_ptr, col, val, label, rng.normal(scale=0.2, size=n))
+    out = []
+    for fused in (True, False):
+        solver = BatchedLBFGS(batch, oracle.LOGISTIC, l2RegWeight=0.1, l1RegWeight=l1, numCorrections=m,
+                              maxNumIterations=40, fused_direction=fused)
+        assert solver.fused_direction == fused
+        w, f, info = solver.optimize()
+        out.append((w.cpu().numpy(), f.cpu().numpy(), info["iterations"], info["entity_evaluations"], info["reasons"],
+                    info["evaluations"]))
+    a, b = out
+    assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
+    assert np.array_equal(a[2], b[2]) and np.array_equal(a[3], b[3]) and np.array_equal(a[4], b[4]) and a[5] == b[5]
+    assert a[2].max() > m            # the rings did wrap
+    batch.close()
+    ctx.close()
+
+
+def test_more_than_16_correction_pairs_take_the_unfused_recursion():
+    import photon_ml_b200 as pml
+    from photon_ml_b200.batched_lbfgs import BatchedLBFGS
+    rng = np.random.default_rng(18)
+    ent_row_ptr, dims, row_ptr, col, val, n = _entities(rng, 30, 12, 20)
+    ctx = pml.Context(0)
+    batch = pml.Batch(ctx, ent_row_ptr, dims, row_ptr, col, val, util.labels_for(rng, oracle.LOGISTIC, n))
+    solver = BatchedLBFGS(batch, oracle.LOGISTIC, l2RegWeight=0.1, numCorrections=20)
+    assert not solver.fused_direction
+    w, f, info = solver.optimize()
+    assert np.all(np.isfinite(w.cpu().numpy()))
+    with pytest.raises(pml.IllegalArgumentError):
+        batch.lbfgs_direction_dev(None, 17, w.data_ptr(), w.data_ptr(), w.data_ptr(), w.data_ptr(), w.data_ptr(),
+                                  w.data_ptr(), w.data_ptr())
+    batch.close()
+    ctx.close()

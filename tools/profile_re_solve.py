@@ -1,5 +1,5 @@
 """Where the lock-step per-entity TRON solve spends its time: device time by kernel and the host wall time around it,
-for the unfused CG loop and for the one-kernel CG step (BatchedTRON(fused_cg=True)).  Not a bench value: torch's
+for the unfused CG loop, for the one-kernel CG step (BatchedTRON(fused_cg=True)) and for lock-step L-BFGS.  Not a bench value: torch's
 profiler is attached."""
 import json
 import os
@@ -21,15 +21,19 @@ parts = bench.make_entity_problems(rng, n_ent, 10, device=torch.device("cuda", c
 batch = pml.Batch(ctx, *parts)
 BatchedTRON(batch, pml.LOGISTIC, l2RegWeight=1.0, maxNumIterations=2).optimize()
 out = {}
-for fused in (False, True):
-    BatchedTRON(batch, pml.LOGISTIC, l2RegWeight=1.0, fused_cg=fused).optimize()
+from photon_ml_b200.batched_lbfgs import BatchedLBFGS  # noqa: E402
+forms = {"unfused": lambda: BatchedTRON(batch, pml.LOGISTIC, l2RegWeight=1.0, fused_cg=False),
+         "fused": lambda: BatchedTRON(batch, pml.LOGISTIC, l2RegWeight=1.0, fused_cg=True),
+         "lbfgs": lambda: BatchedLBFGS(batch, pml.LOGISTIC, l2RegWeight=1.0)}
+for name, make in forms.items():
+    make().optimize()
     torch.cuda.synchronize()
     t0 = time.perf_counter()
-    BatchedTRON(batch, pml.LOGISTIC, l2RegWeight=1.0, fused_cg=fused).optimize()
+    info = make().optimize()[2]
     torch.cuda.synchronize()
     wall = time.perf_counter() - t0
     with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA]) as prof:
-        BatchedTRON(batch, pml.LOGISTIC, l2RegWeight=1.0, fused_cg=fused).optimize()
+        make().optimize()
         torch.cuda.synchronize()
     rows = []
     total = 0.0
@@ -41,7 +45,8 @@ for fused in (False, True):
             total += dev_us
             launches += e.count
     rows.sort(reverse=True)
-    out["fused" if fused else "unfused"] = {
-        "wall_s_unprofiled": wall, "device_ms_total": total / 1e3, "kernel_launches": launches,
+    out[name] = {
+        "wall_s_unprofiled": wall, "batched_evaluations": info["evaluations"],
+        "mean_iterations_per_entity": float(info["iterations"].mean()), "device_ms_total": total / 1e3, "kernel_launches": launches,
         "top": [{"ms": r[0] / 1e3, "n": r[1], "kernel": r[2]} for r in rows[:14]]}
 print(json.dumps(out, indent=1))
