@@ -106,12 +106,13 @@ class BatchedLBFGS(BatchedTRON):
             q = t.where(q * adj_g < 0, q, t.zeros_like(q))
         return q
 
-    def _push_pair(self, s, y, mask):
-        """Append (s, y) to the history of the entities in mask: their slots shift down by one, the newest goes last."""
+    def _push_pair(self, s, y, mask, sy):
+        """Append (s, y) to the history of the entities in mask (sy = s . y per entity, which the caller has): their
+        slots shift down by one, the newest goes last -- or, with rings, the head moves on by one."""
         t = self.torch
         m8 = mask.to(t.uint8)
         if self.fused_direction:
-            rho_new = 1.0 / self._dot(y, s)
+            rho_new = 1.0 / sy
             self.batch.lbfgs_push_dev(m8.data_ptr(), self.m, rho_new.data_ptr(), s.data_ptr(), y.data_ptr(),
                                       self._S.data_ptr(), self._Y.data_ptr(), self._rho.data_ptr(), self._head.data_ptr(),
                                       self._len.data_ptr())
@@ -122,7 +123,7 @@ class BatchedLBFGS(BatchedTRON):
             self._rho[i] = t.where(mask, self._rho[i + 1], self._rho[i])
         self._axpby(None, s, None, None, self._S[self.m - 1], m8)
         self._axpby(None, y, None, None, self._Y[self.m - 1], m8)
-        self._rho[self.m - 1] = t.where(mask, 1.0 / self._dot(y, s), self._rho[self.m - 1])
+        self._rho[self.m - 1] = t.where(mask, 1.0 / sy, self._rho[self.m - 1])
         self._len = t.where(mask, t.clamp(self._len + 1, max=self.m), self._len)
 
     def _drop_history(self, mask):
@@ -153,6 +154,7 @@ class BatchedLBFGS(BatchedTRON):
         i_zm = t_.zeros(E, dtype=t_.int64, device=self.device)
         ok = t_.zeros(E, dtype=t_.bool, device=self.device)
         res_t, res_f, res_g = self._zeros(E), self._zeros(E), self._zeros(self.D)
+        xt = x.clone()        # trial points; an entity's slice is rewritten while it is searching and ignored afterwards
 
         def finish(who, tt, ff, gg, valid):
             nonlocal ok, res_t, res_f, phase
@@ -178,7 +180,6 @@ class BatchedLBFGS(BatchedTRON):
             tz = t_.where(inside, tz, mid)
             step = t_.where(zooming, tz, step)
             # phi(step) for everybody still searching: one batched evaluation
-            xt = x.clone()
             self._axpby(None, x, step, direction, xt, running.to(t_.uint8))
             f_t, g_t = self._evaluate(xt, running)
             d_t = self._dot(g_t, direction)
@@ -283,11 +284,17 @@ class BatchedLBFGS(BatchedTRON):
             it = t.zeros(E, dtype=t.int64, device=self.device)
             done = t.zeros(E, dtype=t.bool, device=self.device)
             reason = t.full((E,), -1, dtype=t.int64, device=self.device)
+            # Per-entity sums depend only on the entity's own numbers, so what an iteration has computed for the state
+            # it leaves is what the next one would compute again: the adjusted state and its squared gradient norm are
+            # carried over, and |cur_g|^2 follows cur_g entity by entity.
+            adj_f, adj_g = self._adjusted(x, f, g)
+            adj_gg = self._dot(adj_g, adj_g)
+            cur_gg = self._dot(cur_g, cur_g)
+            first_pass = True
             while not bool(done.all()):
                 active = ~done
                 prev_f, prev_it = cur_f.clone(), it.clone()
-                adj_f, adj_g = self._adjusted(x, f, g)
-                stationary = self._dot(adj_g, adj_g).sqrt() <= t.clamp(self.tol * adj_f.abs(), min=1e-8)
+                stationary = adj_gg.sqrt() <= t.clamp(self.tol * adj_f.abs(), min=1e-8)
                 inner_converged = inner_converged | (active & stationary)
                 go = active & ~inner_converged                          # the others hand back the same state
                 if bool(go.any()):
@@ -298,7 +305,8 @@ class BatchedLBFGS(BatchedTRON):
                         self._drop_history(not_descent)
                         self._masked_copy(-adj_g, direction, not_descent)
                         gd = self._dot(adj_g, direction)
-                    init = t.where(inner_iter == 0, 1.0 / self._dot(direction, direction).sqrt(), t.ones_like(gd))
+                    # (inner_iter is 0 only in the first pass: an entity either moves or stops for good)
+                    init = 1.0 / self._dot(direction, direction).sqrt() if first_pass else t.ones_like(gd)
                     if self.l1 == 0.0:
                         ok, step, fn, gn = self._strong_wolfe(x, f, direction, gd, init, go)
                         xn = x.clone()
@@ -311,19 +319,22 @@ class BatchedLBFGS(BatchedTRON):
                     sy = self._dot(s, y)
                     keep = moved & (sy > 1e-10 * self._dot(s, s).sqrt() * self._dot(y, y).sqrt())
                     if bool(keep.any()):
-                        self._push_pair(s, y, keep)
-                    self._masked_copy(xn, x, moved)
+                        self._push_pair(s, y, keep, sy)
+                    x = xn                                              # xn is x wherever the entity has not moved
                     self._masked_copy(gn, g, moved)
                     f = t.where(moved, fn, f)
                     inner_iter = inner_iter + moved.to(t.int64)
-                    adj_fn, adj_gn = self._adjusted(x, f, g)
-                    stop = self._dot(adj_gn, adj_gn).sqrt() <= t.clamp(self.tol * adj_fn.abs(), min=1e-8)
+                    adj_f, adj_g = self._adjusted(x, f, g)
+                    adj_gg = self._dot(adj_g, adj_g)
+                    stop = adj_gg.sqrt() <= t.clamp(self.tol * adj_f.abs(), min=1e-8)
                     inner_converged = inner_converged | (moved & (stop | (inner_iter >= self.max_iter)))
-                    cur_f = t.where(moved, adj_fn, cur_f)
-                    self._masked_copy(adj_gn, cur_g, moved)
+                    cur_f = t.where(moved, adj_f, cur_f)
+                    self._masked_copy(adj_g, cur_g, moved)
+                    cur_gg = t.where(moved, adj_gg, cur_gg)
                     it = it + moved.to(t.int64)
+                    first_pass = False
                 # Optimizer.getConvergenceReason (:136-150), in its order
-                gnorm = self._dot(cur_g, cur_g).sqrt()
+                gnorm = cur_gg.sqrt()
                 r = t.full((E,), -1, dtype=t.int64, device=self.device)
                 r = t.where(gnorm <= grad_tol, t.full_like(r, GRADIENT_CONVERGED), r)
                 r = t.where((cur_f - prev_f).abs() <= loss_tol, t.full_like(r, FUNCTION_VALUES_CONVERGED), r)
