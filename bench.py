@@ -791,7 +791,7 @@ def batch_bytes(n_ent, n, nnz, d_total, value_bytes):
     return 2 * nnz * (value_bytes + 4) + n * (8 + 16 + 16) + (n + 1) * 4 + d_total * 4 + d_total * 16 + n_ent * (8 + 8 + 8)
 
 
-def random_effect_batch(ctx, n_ent=1_000_000, seed=5, solver_runs=("skip", "stream-all", "unfused-cg")):
+def random_effect_batch(ctx, n_ent=1_000_000, seed=5, solver_runs=("skip", "stream-all", "unfused-cg", "lbfgs")):
     """configs[4]-shaped per-entity batch (default: 1/10 scale, 1 M entities): every entity's value+gradient in one
     call, with its roofline, and every entity's L2-regularised problem solved in lock step."""
     import photon_ml_b200 as pml
@@ -852,6 +852,8 @@ def random_effect_batch(ctx, n_ent=1_000_000, seed=5, solver_runs=("skip", "stre
     # (one untimed solve first: the first Hessian-vector products allocate the curvature cache and capture the graphs)
     BatchedTRON(batch, pml.LOGISTIC, l2RegWeight=1.0, maxNumIterations=2).optimize()
     for mode in solver_runs:
+        if mode == "lbfgs":
+            continue
         solver = BatchedTRON(batch, pml.LOGISTIC, l2RegWeight=1.0, skip_converged=(mode != "stream-all"),
                              fused_cg=(mode != "unfused-cg"))
         ctx.synchronize()
@@ -863,6 +865,20 @@ def random_effect_batch(ctx, n_ent=1_000_000, seed=5, solver_runs=("skip", "stre
             "wall_s": wall, "entities_solved_per_s": n_ent / wall, "batched_value_gradient_evals": sinfo["evaluations"],
             "batched_hessian_vector_evals": sinfo["hessian_vector_evaluations"],
             "mean_iterations_per_entity": float(sinfo["iterations"].mean()),
+            "reasons": {REASONS[c]: int((sinfo["reasons"] == c).sum()) for c in range(len(REASONS))}}
+    # the same problems under the optimizer GAME's coordinates default to (OptimizerFactory.scala:46-62): lock-step L-BFGS
+    if "lbfgs" in solver_runs:
+        from photon_ml_b200.batched_lbfgs import BatchedLBFGS
+        BatchedLBFGS(batch, pml.LOGISTIC, l2RegWeight=1.0, maxNumIterations=2).optimize()
+        solver = BatchedLBFGS(batch, pml.LOGISTIC, l2RegWeight=1.0)
+        ctx.synchronize()
+        t0 = time.perf_counter()
+        _, _, sinfo = solver.optimize()
+        wall = time.perf_counter() - t0
+        out["lockstep_lbfgs_logistic_l2_1"] = {
+            "wall_s": wall, "entities_solved_per_s": n_ent / wall, "batched_value_gradient_evals": sinfo["evaluations"],
+            "mean_iterations_per_entity": float(sinfo["iterations"].mean()),
+            "mean_evaluations_per_entity": float(sinfo["entity_evaluations"].mean()),
             "reasons": {REASONS[c]: int((sinfo["reasons"] == c).sum()) for c in range(len(REASONS))}}
     batch.close()
     return out

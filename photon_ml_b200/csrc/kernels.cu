@@ -1559,9 +1559,16 @@ __device__ __forceinline__ int cg_step_entity_warp(int lane, int64_t lo, int64_t
 // entity there, and the three vectors that change go back coalesced; left to walk global memory on its own a lane
 // makes every load a wavefront of its own (measured: slower than the unfused loop).  Entities of 64 coefficients and
 // more are then done by the whole warp straight from global memory.
-constexpr int CG_WARPS = 7;
-constexpr int CG_CAP = 1024;  // doubles per vector and warp: 4 vectors x 8 KB x 7 warps = 224 KB, one CTA per SM.  32 entities
-                              // of a few dozen coefficients fit in one go; more than that and the group takes two passes
+#ifndef PML_CG_WARPS
+#define PML_CG_WARPS 28
+#endif
+#ifndef PML_CG_CAP
+#define PML_CG_CAP 256
+#endif
+constexpr int CG_WARPS = PML_CG_WARPS;
+constexpr int CG_CAP = PML_CG_CAP;  // doubles per vector and warp: 4 vectors x 2 KB x 28 warps = 224 KB, one CTA per SM.
+// (The kernel is latency-bound -- a warp loads, waits, works, stores -- so what counts is warps in flight, not how many
+// entities a warp takes at once: 7 warps x 1024 doubles ran 0.36 ms per launch on 10^6 entities, 18 x 384 0.20 ms, 28 x 256 0.17 ms.)
 constexpr int CG_BIG = 64;    // segment_dot_kernel's threshold
 
 __global__ void __launch_bounds__(32 * CG_WARPS)
@@ -1674,8 +1681,16 @@ int launch_batch_cg_step(cudaStream_t s, int64_t n_entities, const int64_t *coef
 // multiply-adds in index order below 64 coefficients and lane-strided with the fixed shuffle tree from 64 on
 // (segment_dot_kernel), every update is one rounded product plus one rounded sum (segment_axpby_kernel).
 // ------------------------------------------------------------------------------------------
-constexpr int LB_WARPS = 8;
-constexpr int LB_CAP = 1024;     // doubles per staged vector and warp: 3 x 8 KB + 2 KB of ring positions, 8 warps = 208 KB
+#ifndef PML_LB_WARPS
+#define PML_LB_WARPS 32
+#endif
+#ifndef PML_LB_CAP
+#define PML_LB_CAP 256
+#endif
+constexpr int LB_WARPS = PML_LB_WARPS;
+constexpr int LB_CAP = PML_LB_CAP;   // doubles per staged vector and warp: 3 x 2 KB + 0.5 KB of ring positions, 32 warps = 208 KB
+// (latency-bound like batch_cg_step_kernel, once per pair and loop: 8 warps x 1024 doubles took 1.47 ms per launch on
+// 10^6 entities, 32 x 256 0.73 ms; a warp then takes the 32 entities of its group in passes of about a dozen)
 constexpr int LB_MAX_M = 16;
 
 struct LbfgsParams {

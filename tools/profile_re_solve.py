@@ -25,7 +25,10 @@ from photon_ml_b200.batched_lbfgs import BatchedLBFGS  # noqa: E402
 forms = {"unfused": lambda: BatchedTRON(batch, pml.LOGISTIC, l2RegWeight=1.0, fused_cg=False),
          "fused": lambda: BatchedTRON(batch, pml.LOGISTIC, l2RegWeight=1.0, fused_cg=True),
          "lbfgs": lambda: BatchedLBFGS(batch, pml.LOGISTIC, l2RegWeight=1.0)}
+only = os.environ.get("PML_FORMS")
 for name, make in forms.items():
+    if only and name not in only.split(","):
+        continue
     make().optimize()
     torch.cuda.synchronize()
     t0 = time.perf_counter()
