@@ -71,7 +71,8 @@ typedef struct pml_dataset_info {
     int32_t tiled_hot_cols; /* columns of the CSC copy tiled by row blocks (0 = plain layout) */
     int32_t tiled_tiles;    /* row tiles of that layout */
     int32_t tiled_tile_rows;
-    int32_t reserved;
+    int32_t sliced_ell_padding_permille; /* the rows' sliced-ELL copy that single-vector margin passes run on: padding
+                                          * entries per 1000 stored entries; -1 = not built (batches; rows too uneven) */
 } pml_dataset_info;
 
 /* message of the calling thread's last failing call ("" if none) */

@@ -61,7 +61,7 @@ class DatasetInfo(ctypes.Structure):
                 ("nonempty_cols", ctypes.c_int64), ("device_bytes", ctypes.c_int64),
                 ("vg_algorithmic_bytes", ctypes.c_int64), ("hv_algorithmic_bytes", ctypes.c_int64),
                 ("tiled_hot_cols", ctypes.c_int32), ("tiled_tiles", ctypes.c_int32), ("tiled_tile_rows", ctypes.c_int32),
-                ("reserved", ctypes.c_int32)]
+                ("sliced_ell_padding_permille", ctypes.c_int32)]
 
 
 _lib = None

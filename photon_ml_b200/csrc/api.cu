@@ -183,6 +183,13 @@ int run_rows(pml_dataset *ds, RowPassParams &rp, bool two)
             return launch_row_pass(s, ctx->sm_count, ds->value_bytes, variant, two, rp, &ds->row_grid);
         });
     }
+    if (!two && ds->sell.idx != nullptr && !ds->variant_forced) {
+        // one lane per row over the sliced-ELL copy: every row's dot is written, nothing to fix up
+        PML_TRY(run(ctx, PML_K_ROW, [&] {
+            return launch_sell_rows(s, ctx->sm_count, ds->value_bytes, ds->sell, ds->n, rp.vec, ds->t.m, ds->za);
+        }));
+        return run(ctx, PML_K_EPILOGUE, [&] { return launch_row_epilogue(s, ctx->sm_count, rp, ds->za, ds->zb, &ds->row_grid); });
+    }
     if (two && ds->zb == nullptr) {
         PML_TRY(dev_alloc(&ds->zb, (size_t)ds->n, &ds->bytes));
         PML_TRY(dev_alloc(&ds->carry_row2, (size_t)ds->rs.n_chunks + 1, &ds->bytes));
@@ -599,7 +606,7 @@ int pml_dataset_destroy(pml_dataset *ds)
                      ds->t.nzcol_ptr, ds->t.nzcol_id, ds->t.rank, ds->t.chunk_col_lo, ds->t.fix, ds->rs.nzrow_id, ds->rs.chunk_lo,
                      ds->rs.fix, ds->za, ds->zb, ds->carry_row, ds->carry_row2, ds->row_loss, ds->row_chunk_active, ds->col_chunk_active, ds->row_block_active, ds->factors, ds->shifts, ds->r,
                      ds->dcache, ds->partials, ds->carry_head, ds->raw, ds->vec, ds->shift_partials, ds->io_a, ds->io_b,
-                     ds->io_n };
+                     ds->io_n, ds->sell.idx, ds->sell.val, ds->sell.base, ds->sell.perm };
     for (void *p : ptrs)
         if (p) cudaFree(p);
     delete ds;
@@ -714,6 +721,17 @@ int pml_dataset_create_csr_dev(pml_ctx *ctx, int64_t n, int32_t d, const int64_t
     // the shared-memory banks, as pack.cu does inside the runs of the tiled CSC region, was measured to slow the pass
     // from 1.03 to 1.12 ms -- in sorted order the lanes that hold row heads read the same few hottest coefficients at
     // the same item, which is a broadcast, not a conflict.)
+    // The rows once more as sliced ELL for the one-lane-per-row margin pass (not for batches of per-entity problems:
+    // their masks work on chunks of the entry stream; not when rows are so uneven that padding would cost more than
+    // 15 % of the entries, PML_SELL_MAX_OVERHEAD; PML_NO_SELL keeps every pass on the entry-chunked stream).
+    if (!ds->keep_column_order && std::getenv("PML_NO_SELL") == nullptr) {
+        const char *lim = std::getenv("PML_SELL_MAX_OVERHEAD"), *sig = std::getenv("PML_SELL_SIGMA_SHIFT");
+        PML_TRY(build_sell(s, n, nnz, ds->row_ptr, ds->col, ds->val, dst_bytes, lim ? std::atof(lim) : 0.15,
+                           sig ? std::atoi(sig) : 13,
+                           std::getenv("PML_NO_SELL_BANK_ORDER") ? 0 : (int32_t)std::min<int64_t>(ds->t.m, SEG_TABLE_BYTES / 8 - 1),
+                           &ds->sell));
+        ds->bytes += ds->sell.bytes;
+    }
     PML_TRY(dev_alloc(&ds->za, (size_t)n, &ds->bytes));
     PML_TRY(dev_alloc(&ds->carry_row, (size_t)ds->rs.n_chunks + 1, &ds->bytes));
 
@@ -790,7 +808,8 @@ int pml_dataset_get_info(const pml_dataset *ds, pml_dataset_info *out)
     out->tiled_hot_cols = ds->t.hot.n_hot_cols;
     out->tiled_tiles = ds->t.hot.n_tiles;
     out->tiled_tile_rows = ds->t.hot.tile_rows;
-    out->reserved = 0;
+    out->sliced_ell_padding_permille =
+        ds->sell.idx && ds->nnz > 0 ? (int32_t)((ds->sell.len - ds->nnz) * 1000 / ds->nnz) : -1;
     const int64_t V = ds->value_bytes, n = ds->n, d = ds->d, nnz = ds->nnz;
     // CSR stream + CSC stream + (y, o, wt) + r written and read + pointers + (read w, write g)
     out->vg_algorithmic_bytes = 2 * nnz * (V + 4) + n * 24 + n * 16 + (n + 1) * 4 + ((int64_t)d + 1) * 4 + (int64_t)d * 16;

@@ -212,6 +212,19 @@ struct Packed {
 };
 
 // chunk metadata of the CSR stream (the column array itself carries the row-start flags)
+// Sliced-ELL copy of the CSR rows (pack.cu build_sell; kernels.cu sell_rows_kernel)
+struct SellSide {
+    int32_t *idx = nullptr;   // column id + 1, 0 = padding; [slice][quad of positions][row of the slice][4]
+    void *val = nullptr;
+    int64_t *base = nullptr;  // n_slices + 1: first entry of every slice (multiples of 128)
+    int32_t *perm = nullptr;  // n: the row at every position (rows are sorted by length inside windows)
+    int64_t n_slices = 0, len = 0, bytes = 0;
+};
+int build_sell(cudaStream_t s, int64_t n, int64_t nnz, const uint32_t *row_ptr, const int32_t *col, const void *val,
+               int value_bytes, double max_overhead, int sigma_shift, int32_t n_hot, SellSide *out);
+int launch_sell_rows(cudaStream_t s, int sm_count, int value_bytes, const SellSide &sell, int64_t n, const double *vec,
+                     int64_t table_len, double *out);
+
 struct RowSide {
     int32_t *nzrow_id = nullptr;  // non-empty row ordinal -> row id; null when no row is empty
     int32_t *chunk_lo = nullptr;
@@ -322,6 +335,7 @@ struct pml_dataset {
     // CSC + chunk metadata
     pml::Packed t;
     pml::RowSide rs;
+    pml::SellSide sell;        // rows once more, sliced-ELL, when padding is cheap: the single-vector margin pass runs on it
     double *za = nullptr, *zb = nullptr;   // n each: sparse dots of row-pass variant 1 (zb lazily, Hessian-vector)
     double *carry_row = nullptr, *carry_row2 = nullptr;  // rs.n_chunks each
     // normalization

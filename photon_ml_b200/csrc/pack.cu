@@ -10,6 +10,7 @@
 #include <cuda_runtime.h>
 
 #include <cstdlib>
+#include <type_traits>
 #include <vector>
 
 #include "internal.h"
@@ -949,6 +950,218 @@ int build_row_side(cudaStream_t s, int64_t n, int64_t nnz, const uint32_t *row_p
     PML_CUDA(cudaGetLastError());
     PML_TRY(build_fix_list(s, n_chunks, out->chunk_lo, head.as<int32_t>(), out->nzrow_id, runs, &out->fix, &out->n_fix,
                            &out->n_fix_long, &out->bytes));
+    return PML_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// Sliced-ELL copy of the CSR rows for the one-lane-per-row margin pass (sell_rows_kernel): 32 consecutive rows make a
+// slice, padded to the longest of them (rounded up to 4 entries); inside a slice the entries are stored
+// [quad of positions][row][4], so a warp's 128-bit loads are coalesced while lane l walks row l.  Rows keep their
+// ascending internal column order, which puts the same few hottest coefficients at the same position of most rows: the
+// warp's table look-ups at one position are then broadcasts or neighbours, not bank conflicts.  Stored ids are
+// column + 1; 0 is padding and selects the zero slot of the table.  Not built when padding would cost more than
+// `max_overhead` of the entries (rows of very uneven length): the entry-chunked stream then serves the pass.
+// ------------------------------------------------------------------------------------------
+__global__ void sell_keys_kernel(int64_t n, int sigma_shift, const uint32_t *__restrict__ row_ptr, uint64_t *__restrict__ keys,
+                                 int32_t *__restrict__ rows)
+{
+    for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += (int64_t)gridDim.x * blockDim.x) {
+        const uint32_t len = row_ptr[r + 1] - row_ptr[r];
+        keys[r] = ((uint64_t)(r >> sigma_shift) << 20) | (len < 0xfffffu ? len : 0xfffffu);
+        rows[r] = (int32_t)r;
+    }
+}
+
+__global__ void sell_width_kernel(int64_t n, int64_t n_slices, const uint32_t *__restrict__ row_ptr, const int32_t *__restrict__ perm,
+                                  int64_t *__restrict__ entries)
+{
+    for (int64_t sl = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; sl <= n_slices; sl += (int64_t)gridDim.x * blockDim.x) {
+        if (sl == n_slices) {
+            entries[sl] = 0;
+            continue;
+        }
+        const int64_t r0 = sl << 5, r1 = r0 + 32 < n ? r0 + 32 : n;
+        uint32_t w = 0;
+        for (int64_t i = r0; i < r1; ++i) {
+            const int64_t r = perm[i];
+            const uint32_t len = row_ptr[r + 1] - row_ptr[r];
+            w = len > w ? len : w;
+        }
+        entries[sl] = 32ll * ((w + 3u) & ~3u);
+    }
+}
+
+struct NoValue {};   // indicator features: only the indices are stored
+
+// n_hot > 0: the entries of a row are dealt to its positions so that the table look-ups of a warp instruction --
+// the same position of 32 rows -- fall into different shared-memory banks: stored id k <= n_hot lives in table slot k,
+// 8 bytes wide, i.e. bank pair k mod 16, and a 64-bit shared load is served half a warp at a time.  The row in lane l
+// puts at position p an entry of class (l + p) mod 16 if it has one left, else an entry beyond the table (no
+// shared-memory access at all); what is left over afterwards fills the holes (those may conflict).  A row's sum is
+// taken in the stored order, which is fixed at pack time.
+template <typename VT>
+__global__ void sell_fill_kernel(int64_t n, int64_t n_slices, const uint32_t *__restrict__ row_ptr, const int32_t *__restrict__ col,
+                                 const VT *__restrict__ val, const int32_t *__restrict__ perm, const int64_t *__restrict__ base,
+                                 int32_t n_hot, int32_t *__restrict__ idx, VT *__restrict__ out_val)
+{
+    const int lane = threadIdx.x & 31;
+    const int64_t warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (int64_t sl = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; sl < n_slices; sl += warps) {
+        const int64_t b = base[sl];
+        const int quads = (int)((base[sl + 1] - b) >> 7);
+        const int64_t at_row = (sl << 5) + lane;
+        const int64_t row = at_row < n ? perm[at_row] : -1;
+        const int64_t start = row >= 0 ? row_ptr[row] : 0;
+        const int len = row >= 0 ? (int)(row_ptr[row + 1] - row_ptr[row]) : 0;
+        if (n_hot <= 0) {
+            for (int q = 0; q < quads; ++q) {
+                const int64_t at = b + ((int64_t)q * 32 + lane) * 4;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const int pos = 4 * q + j;
+                    const bool in = pos < len;
+                    idx[at + j] = in ? (col[start + pos] & 0x7fffffff) + 1 : 0;
+                    if constexpr (!std::is_same<VT, NoValue>::value) out_val[at + j] = in ? val[start + pos] : (VT)0;
+                }
+            }
+            continue;
+        }
+        auto klass = [&](int i) {
+            const int32_t k = (col[start + i] & 0x7fffffff) + 1;
+            return k <= n_hot ? (k & 15) : 16;
+        };
+        int cur[17];      // first entry of every class that has not been placed yet (len: none left)
+        for (int c = 0; c < 17; ++c) cur[c] = len;
+        for (int i = len - 1; i >= 0; --i) cur[klass(i)] = i;
+        auto advance = [&](int c) {
+            int i = cur[c] + 1;
+            while (i < len && klass(i) != c) ++i;
+            cur[c] = i;
+        };
+        auto put = [&](int pos, int i) {
+            const int64_t at = b + ((int64_t)(pos >> 2) * 32 + lane) * 4 + (pos & 3);
+            idx[at] = i < len ? (col[start + i] & 0x7fffffff) + 1 : 0;
+            if constexpr (!std::is_same<VT, NoValue>::value) out_val[at] = i < len ? val[start + i] : (VT)0;
+        };
+        const int width = 4 * quads;
+        int holes = 0;
+        for (int pos = 0; pos < width; ++pos) {
+            int c = (lane + pos) & 15;
+            if (cur[c] >= len) c = 16;
+            const int i = cur[c];
+            put(pos, i);
+            if (i < len) advance(c);
+            else ++holes;
+        }
+        if (holes > 0) {
+            int c = 0;
+            for (int pos = 0; pos < width; ++pos) {
+                const int64_t at = b + ((int64_t)(pos >> 2) * 32 + lane) * 4 + (pos & 3);
+                if (idx[at] != 0) continue;
+                while (c < 17 && cur[c] >= len) ++c;
+                if (c == 17) break;
+                put(pos, cur[c]);
+                advance(c);
+            }
+        }
+    }
+}
+
+int build_sell(cudaStream_t s, int64_t n, int64_t nnz, const uint32_t *row_ptr, const int32_t *col, const void *val,
+               int value_bytes, double max_overhead, int sigma_shift, int32_t n_hot, SellSide *out)
+{
+    *out = SellSide();
+    if (n <= 0 || nnz <= 0 || n > 0x7fffffffll) return PML_OK;
+    const int64_t n_slices = (n + 31) >> 5;
+    // rows sorted by length inside windows of 2^sigma_shift rows (stable: rows of one length keep their order), so that
+    // the 32 rows of a slice are about equally long and the sums still land in a small window of the output
+    int32_t *perm = nullptr;
+    {
+        DevBuf keys, keys_out, rows, t;
+        PML_CUDA(keys.alloc(sizeof(uint64_t) * (size_t)n));
+        PML_CUDA(keys_out.alloc(sizeof(uint64_t) * (size_t)n));
+        PML_CUDA(rows.alloc(sizeof(int32_t) * (size_t)n));
+        PML_CUDA(cudaMalloc(&perm, sizeof(int32_t) * (size_t)n));
+        sell_keys_kernel<<<grid_for(n), 256, 0, s>>>(n, sigma_shift, row_ptr, keys.as<uint64_t>(), rows.as<int32_t>());
+        size_t tb = 0;
+        cudaError_t e = cub::DeviceRadixSort::SortPairs(nullptr, tb, keys.as<uint64_t>(), keys_out.as<uint64_t>(), rows.as<int32_t>(),
+                                                        perm, n, 0, 64, s);
+        if (e == cudaSuccess) e = t.alloc(tb);
+        if (e == cudaSuccess)
+            e = cub::DeviceRadixSort::SortPairs(t.p, tb, keys.as<uint64_t>(), keys_out.as<uint64_t>(), rows.as<int32_t>(), perm, n,
+                                                0, 64, s);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+        if (e != cudaSuccess) {
+            cudaFree(perm);
+            PML_CUDA(e);
+        }
+    }
+    DevBuf entries;
+    int64_t *base = nullptr;
+    auto drop = [&] {
+        cudaFree(base);
+        cudaFree(perm);
+    };
+    if (entries.alloc(sizeof(int64_t) * (size_t)(n_slices + 1)) != cudaSuccess ||
+        cudaMalloc(&base, sizeof(int64_t) * (size_t)(n_slices + 1)) != cudaSuccess) {
+        drop();
+        return fail(PML_ENOMEM, "sliced-ELL slice table");
+    }
+    sell_width_kernel<<<grid_for(n_slices + 1), 256, 0, s>>>(n, n_slices, row_ptr, perm, entries.as<int64_t>());
+    {
+        DevBuf t;
+        size_t tb = 0;
+        cudaError_t e = cub::DeviceScan::ExclusiveSum(nullptr, tb, entries.as<int64_t>(), base, n_slices + 1, s);
+        if (e == cudaSuccess) e = t.alloc(tb);
+        if (e == cudaSuccess) e = cub::DeviceScan::ExclusiveSum(t.p, tb, entries.as<int64_t>(), base, n_slices + 1, s);
+        int64_t len = 0;
+        if (e == cudaSuccess) e = cudaMemcpyAsync(&len, base + n_slices, sizeof(int64_t), cudaMemcpyDeviceToHost, s);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+        if (e != cudaSuccess) {
+            drop();
+            PML_CUDA(e);
+        }
+        out->len = len;
+    }
+    if ((double)out->len > (1.0 + max_overhead) * (double)nnz) {   // too much padding: leave the pass to the entry-chunked stream
+        drop();
+        out->len = 0;
+        return PML_OK;
+    }
+    int32_t *idx = nullptr;
+    void *v = nullptr;
+    cudaError_t e = cudaMalloc(&idx, sizeof(int32_t) * (size_t)(out->len + 4));
+    if (e == cudaSuccess && value_bytes > 0) e = cudaMalloc(&v, (size_t)value_bytes * (size_t)(out->len + 4));
+    if (e != cudaSuccess) {                                          // no room for a second copy of the rows: not an error
+        cudaGetLastError();
+        cudaFree(idx);
+        drop();
+        out->len = 0;
+        return PML_OK;
+    }
+    const int grid = (int)(n_slices < 148 * 64 ? (n_slices + 7) / 8 : 148 * 8);
+    if (value_bytes == 0)
+        sell_fill_kernel<NoValue><<<grid, 256, 0, s>>>(n, n_slices, row_ptr, col, nullptr, perm, base, n_hot, idx, nullptr);
+    else if (value_bytes == 4)
+        sell_fill_kernel<float><<<grid, 256, 0, s>>>(n, n_slices, row_ptr, col, static_cast<const float *>(val), perm, base,
+                                                     n_hot, idx, static_cast<float *>(v));
+    else
+        sell_fill_kernel<double><<<grid, 256, 0, s>>>(n, n_slices, row_ptr, col, static_cast<const double *>(val), perm, base,
+                                                      n_hot, idx, static_cast<double *>(v));
+    e = cudaGetLastError();
+    if (e != cudaSuccess) {
+        cudaFree(idx);
+        cudaFree(v);
+        drop();
+        PML_CUDA(e);
+    }
+    out->idx = idx;
+    out->val = v;
+    out->base = base;
+    out->perm = perm;
+    out->n_slices = n_slices;
+    out->bytes = (int64_t)sizeof(int64_t) * (n_slices + 1) + (int64_t)(sizeof(int32_t) + value_bytes) * (out->len + 4) +
+                 (int64_t)sizeof(int32_t) * n;
     return PML_OK;
 }
 
