@@ -146,27 +146,31 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
-NCU_FULL_CAPTURES = ("r02_ncu_full.csv", "r01_final3_ncu_full.csv", "r01_tiled_ncu_full.csv")   # newest first
+NCU_FULL_CAPTURES = ("r02_sell_ncu_full.csv", "r02_ncu_full.csv", "r01_final3_ncu_full.csv", "r01_tiled_ncu_full.csv")   # newest first
 
 
 def ncu_traffic(kernel_substrings):
     """DRAM bytes (read + write) per launch of the named kernels, summed, from the committed `ncu --set full`
-    capture of this same workload (profiles/); None when the capture is not there."""
+    captures of this same workload (profiles/, the newest capture that holds the kernel); (None, []) when one of them
+    is in no capture."""
     import csv
-    path = next((q for q in (os.path.join(ROOT, "profiles", f) for f in NCU_FULL_CAPTURES) if os.path.exists(q)), None)
-    if path is None:
-        return None
-    rows = list(csv.reader(open(path)))
-    hdr, units = rows[0], rows[1]
-    ki, ri, wi = hdr.index("Kernel Name"), hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
     scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
-    total, found = 0.0, set()
-    for r in rows[2:]:
-        for sub in kernel_substrings:
-            if sub in r[ki] and sub not in found:
-                total += float(r[ri]) * scale[units[ri]] + float(r[wi]) * scale[units[wi]]
-                found.add(sub)
-    return total if len(found) == len(kernel_substrings) else None
+    total, found, used = 0.0, set(), []
+    for name in NCU_FULL_CAPTURES:
+        path = os.path.join(ROOT, "profiles", name)
+        if not os.path.exists(path):
+            continue
+        rows = list(csv.reader(open(path)))
+        hdr, units = rows[0], rows[1]
+        ki, ri, wi = hdr.index("Kernel Name"), hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
+        for r in rows[2:]:
+            for sub in kernel_substrings:
+                if sub in r[ki] and sub not in found:
+                    total += float(r[ri]) * scale[units[ri]] + float(r[wi]) * scale[units[wi]]
+                    found.add(sub)
+                    if name not in used:
+                        used.append(name)
+    return (total, used) if len(found) == len(kernel_substrings) else (None, [])
 
 
 def kernel_bytes(info, has_offset, has_weight):
@@ -418,14 +422,19 @@ def run_ours(args):
         # the CSR pass = the entry-chunked product + its row epilogue; the CSC pass = tiled hot columns + cold columns
         row_ms = per("row_pass") + per("row_epilogue")
         col_ms = per("col_pass") + per("col_pass_tiled")
+        sliced_ell = info.sliced_ell_padding_permille >= 0
+        row_kernels = ("CSR pass X w: sell_rows_kernel (one lane per row, sliced ELL) + row_epilogue_kernel" if sliced_ell else
+                       "CSR pass X w: seg_spmv_warp_kernel + row_epilogue_kernel" if info.margin_variant == 1 else
+                       "row_pass_kernel<%d lanes/row> (CSR pass, X w + pointwise)" % info.margin_variant)
         dominant = ("CSC pass X^T r: seg_spmv_tiled_kernel (hot columns) + seg_spmv_warp_kernel (cold columns)" if col_ms >= row_ms
-                    else ("CSR pass X w: seg_spmv_warp_kernel + row_epilogue_kernel" if info.margin_variant == 1 else
-                          "row_pass_kernel<%d lanes/row> (CSR pass, X w + pointwise)" % info.margin_variant))
+                    else row_kernels)
         dom_bytes, dom_ms = (col_bytes, col_ms) if col_ms >= row_ms else (row_bytes, row_ms)
-        traffic = None
+        traffic, traffic_files = None, []
+        row_traffic = None
         if world == 1:
-            traffic = (ncu_traffic(["seg_spmv_tiled_kernel", "0, 0, 0, 256>"]) if col_ms >= row_ms
-                       else ncu_traffic(["0, 0, 1, 1024>", "row_epilogue_kernel"]))
+            row_traffic, row_files = ncu_traffic(["sell_rows_kernel" if sliced_ell else "0, 0, 1, 1024>", "row_epilogue_kernel"])
+            traffic, traffic_files = (ncu_traffic(["seg_spmv_tiled_kernel", "0, 0, 0, 256>"]) if col_ms >= row_ms
+                                      else (row_traffic, row_files))
         achieved = dom_bytes / (dom_ms * 1e-3) / 1e9
         ms_per_step = ms / args.steps
         step_bytes = info.vg_algorithmic_bytes - 2 * info.n * 8  # no offsets / weights in this workload
@@ -471,13 +480,14 @@ def run_ours(args):
             "clocks": clocks,
             "roofline": {"bound": "hbm", "kernel": dominant, "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "frac_of_nominal_8000": achieved / 8000.0, "peak_source": peak_src,
-                         "traffic": traffic, "traffic_source": "profiles/%s (ncu --set full, dram read+write)" % next(
-                             (f for f in NCU_FULL_CAPTURES if os.path.exists(os.path.join(ROOT, "profiles", f))), "-"),
+                         "traffic": traffic, "traffic_source": "profiles/%s (ncu --set full, dram read+write)" % (
+                             " + ".join(traffic_files) or "-"),
                          "algorithmic_bytes_per_launch": int(dom_bytes),
                          "avg_launch_ms": dom_ms},
             "kernels": {k: {"ms_per_launch": v[0] / max(1, v[1]), "launches": int(v[1])} for k, v in profile.items()},
-            "row_pass": {"algorithmic_bytes": int(row_bytes), "ms": row_ms, "GBps": row_bytes / (row_ms * 1e-3) / 1e9,
-                         "frac": row_bytes / (row_ms * 1e-3) / 1e9 / peak},
+            "row_pass": {"kernel": row_kernels, "algorithmic_bytes": int(row_bytes), "ms": row_ms,
+                         "GBps": row_bytes / (row_ms * 1e-3) / 1e9, "frac": row_bytes / (row_ms * 1e-3) / 1e9 / peak,
+                         "traffic": row_traffic, "sliced_ell_padding_permille": int(info.sliced_ell_padding_permille)},
             "col_pass": {"algorithmic_bytes": int(col_bytes), "ms": col_ms, "GBps": col_bytes / (col_ms * 1e-3) / 1e9,
                          "frac": col_bytes / (col_ms * 1e-3) / 1e9 / peak},
             "step": {"algorithmic_bytes_two_pass": int(step_bytes), "GBps": step_bytes / (ms_per_step * 1e-3) / 1e9,

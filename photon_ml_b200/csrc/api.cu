@@ -173,27 +173,29 @@ int run_rows(pml_dataset *ds, RowPassParams &rp, bool two)
 {
     pml_ctx *ctx = ds->ctx;
     cudaStream_t s = ctx->stream;
-    // Default split (measured, profiles/): single-vector passes (value+gradient, cached Hessian-vector, diagonal,
+    // With a sliced-ELL copy of the rows every pass runs one lane per row on it (sell_rows_kernel).  Without (batches,
+    // rows too uneven; measured, profiles/): single-vector passes (value+gradient, cached Hessian-vector, diagonal,
     // scores) are fastest on the entry-chunked kernel (1.06 ms vs 1.29 ms at 50 entries/row); the paired
     // (ec, ev) pass of a cold Hessian-vector product is fastest with lanes-per-row (1.59 vs 2.35 ms).
     const int variant = ds->variant_forced ? ds->lanes_per_row : (two ? ds->lanes_per_row : 1);
     rp.block_active = rp.mode == MODE_SCORE ? nullptr : ds->row_block_active;
+    const bool sell_pairs = std::getenv("PML_NO_SELL_PAIRS") == nullptr;
+    if (ds->sell.idx != nullptr && !ds->variant_forced && (!two || sell_pairs)) {
+        // one lane per row over the sliced-ELL copy: every row's dot is written, nothing to fix up
+        if (two && ds->zb == nullptr) PML_TRY(dev_alloc(&ds->zb, (size_t)ds->n, &ds->bytes));
+        PML_TRY(run(ctx, PML_K_ROW, [&] {
+            return launch_sell_rows(s, ctx->sm_count, ds->value_bytes, ds->sell, ds->n, rp.vec, ds->t.m, ds->za,
+                                    two ? ds->zb : nullptr);
+        }));
+        return run(ctx, PML_K_EPILOGUE, [&] { return launch_row_epilogue(s, ctx->sm_count, rp, ds->za, ds->zb, &ds->row_grid); });
+    }
     if (variant != 1) {
         return run(ctx, PML_K_ROW, [&] {
             return launch_row_pass(s, ctx->sm_count, ds->value_bytes, variant, two, rp, &ds->row_grid);
         });
     }
-    if (!two && ds->sell.idx != nullptr && !ds->variant_forced) {
-        // one lane per row over the sliced-ELL copy: every row's dot is written, nothing to fix up
-        PML_TRY(run(ctx, PML_K_ROW, [&] {
-            return launch_sell_rows(s, ctx->sm_count, ds->value_bytes, ds->sell, ds->n, rp.vec, ds->t.m, ds->za);
-        }));
-        return run(ctx, PML_K_EPILOGUE, [&] { return launch_row_epilogue(s, ctx->sm_count, rp, ds->za, ds->zb, &ds->row_grid); });
-    }
-    if (two && ds->zb == nullptr) {
-        PML_TRY(dev_alloc(&ds->zb, (size_t)ds->n, &ds->bytes));
-        PML_TRY(dev_alloc(&ds->carry_row2, (size_t)ds->rs.n_chunks + 1, &ds->bytes));
-    }
+    if (two && ds->zb == nullptr) PML_TRY(dev_alloc(&ds->zb, (size_t)ds->n, &ds->bytes));
+    if (two && ds->carry_row2 == nullptr) PML_TRY(dev_alloc(&ds->carry_row2, (size_t)ds->rs.n_chunks + 1, &ds->bytes));
     if (ds->rs.n_runs < ds->n) {  // empty rows have no run: their dot product is 0
         PML_CUDA(cudaMemsetAsync(ds->za, 0, sizeof(double) * (size_t)ds->n, s));
         if (two) PML_CUDA(cudaMemsetAsync(ds->zb, 0, sizeof(double) * (size_t)ds->n, s));
@@ -389,10 +391,11 @@ int hv_raw(pml_dataset *ds, int loss, const double *coef_dev, uint64_t tag, cons
         if (coef_dev == nullptr) return fail(PML_EINVAL, "coefficients are required when no cached pass matches the tag");
         // allocate outside the captured sequence
         if (keep && ds->dcache == nullptr) PML_TRY(dev_alloc(&ds->dcache, (size_t)ds->n, &ds->bytes));
-        if (ds->lanes_per_row == 1 && ds->zb == nullptr) {  // the paired pass on the entry-chunked kernel (run_rows)
+        // (the paired pass over the sliced-ELL copy or on the entry-chunked kernel, run_rows)
+        if ((ds->sell.idx != nullptr || ds->lanes_per_row == 1) && ds->zb == nullptr)
             PML_TRY(dev_alloc(&ds->zb, (size_t)ds->n, &ds->bytes));
+        if (ds->lanes_per_row == 1 && ds->carry_row2 == nullptr)
             PML_TRY(dev_alloc(&ds->carry_row2, (size_t)ds->rs.n_chunks + 1, &ds->bytes));
-        }
     }
     pml_graph_key key;
     key.version = ds->version;

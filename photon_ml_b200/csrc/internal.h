@@ -223,7 +223,7 @@ struct SellSide {
 int build_sell(cudaStream_t s, int64_t n, int64_t nnz, const uint32_t *row_ptr, const int32_t *col, const void *val,
                int value_bytes, double max_overhead, int sigma_shift, int32_t n_hot, SellSide *out);
 int launch_sell_rows(cudaStream_t s, int sm_count, int value_bytes, const SellSide &sell, int64_t n, const double *vec,
-                     int64_t table_len, double *out);
+                     int64_t table_len, double *out, double *out2);
 
 struct RowSide {
     int32_t *nzrow_id = nullptr;  // non-empty row ordinal -> row id; null when no row is empty

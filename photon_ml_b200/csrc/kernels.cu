@@ -936,111 +936,111 @@ int launch_seg_spmv(cudaStream_t s, int sm_count, int value_bytes, bool two, boo
 // LabeledPoint.computeMargin, lib/data/LabeledPoint.scala:62) with ONE LANE PER ROW over the sliced-ELL copy of the
 // rows (pack.cu build_sell).  Against the entry-chunked kernel: no run flags, no segmented scan, no carries and no
 // fix-up -- a lane keeps its row's sum in a register -- and the 32 look-ups of one instruction are the same position
-// of 32 rows: in ascending (hottest-first) column order mostly the same or neighbouring coefficients, which the
-// shared-memory table serves as a broadcast or without bank conflicts.  Coefficients beyond the table come from L2, one
-// line per lane, as before.  hot[0] is the zero slot padding points at; hot[1 + k] = c_k.
+// of 32 rows, which the packer has dealt over the shared-memory banks.  Coefficients beyond the table come from L2, one
+// line per lane, as before.  hot[0] is the zero slot padding points at; hot[1 + k] = c_k.  TWO: the table and the
+// vector hold (c_k, v_k) pairs and both dots are formed (the paired pass of a cold Hessian-vector product,
+// HessianVectorAggregator.scala:96-121).
+// (Tried: looking the next quad's coefficients up one iteration ahead -- slower, 0.91 against 0.84 ms.)
 // ------------------------------------------------------------------------------------------
 constexpr int SELL_THREADS = 1024;
-#ifndef PML_SELL_PIPE
-#define PML_SELL_PIPE 0
-#endif
 
-__device__ __forceinline__ double sell_lookup(uint32_t hot_at, int n_hot, const double *__restrict__ vm1, int32_t k)
-{
-    return (uint32_t)k <= (uint32_t)n_hot ? lds_f64(hot_at + 8u * (uint32_t)k) : __ldg(vm1 + k);
-}
-
-template <typename VT>
+template <typename VT, bool TWO>
 __global__ void __launch_bounds__(SELL_THREADS, 1)
 sell_rows_kernel(int64_t n, int64_t n_slices, const int32_t *__restrict__ idx, const VT *__restrict__ val,
                  const int64_t *__restrict__ base, const int32_t *__restrict__ perm, const double *__restrict__ vec, int n_hot,
-                 double *__restrict__ out)
+                 double *__restrict__ out, double *__restrict__ out2)
 {
     extern __shared__ __align__(16) double hot[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (tid == 0) hot[0] = 0.0;
-    for (int i = tid; i < n_hot; i += SELL_THREADS) hot[i + 1] = vec[i];
+    constexpr int W = TWO ? 2 : 1;
+    if (tid < W) hot[tid] = 0.0;
+    for (int i = tid; i < W * n_hot; i += SELL_THREADS) hot[i + W] = vec[i];
     __syncthreads();
     const uint32_t hot_at = shared_window_address(hot);
-    const double *__restrict__ vm1 = vec - 1;   // stored ids are column + 1
+    const double *__restrict__ vm1 = vec - W;   // stored ids are column + 1
     const int64_t stride = (int64_t)gridDim.x * (SELL_THREADS / 32);
     for (int64_t sl = (int64_t)blockIdx.x * (SELL_THREADS / 32) + warp; sl < n_slices; sl += stride) {
         const int64_t b = __ldg(base + sl);
         const int quads = (int)((__ldg(base + sl + 1) - b) >> 7);
-        double acc = 0.0;
-#if PML_SELL_PIPE
-        // software pipeline: the entries two quads ahead are in flight and the coefficients of the NEXT quad are being
-        // looked up while this quad is multiplied (a coefficient from L2 takes several hundred cycles)
-        SegRegs<VT, 4> cur, nxt;
-        double g[4];
-        if (quads > 0) seg_load_full<VT, 4>(cur, idx, val, b + lane * 4);
-        if (quads > 1) seg_load_full<VT, 4>(nxt, idx, val, b + (32 + lane) * 4);
-        if (quads > 0) {
-#pragma unroll
-            for (int j = 0; j < 4; ++j) g[j] = sell_lookup(hot_at, n_hot, vm1, cur.idx[j]);
-        }
-        for (int q = 0; q < quads; ++q) {
-            SegRegs<VT, 4> nn;
-            double gn[4];
-            if (q + 2 < quads) seg_load_full<VT, 4>(nn, idx, val, b + ((int64_t)(q + 2) * 32 + lane) * 4);
-            if (q + 1 < quads) {
-#pragma unroll
-                for (int j = 0; j < 4; ++j) gn[j] = sell_lookup(hot_at, n_hot, vm1, nxt.idx[j]);
-            }
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                if constexpr (std::is_same<VT, One>::value) acc += g[j];
-                else acc = fma(g[j], cur.value(j), acc);
-            }
-            cur = nxt;
-            nxt = nn;
-#pragma unroll
-            for (int j = 0; j < 4; ++j) g[j] = gn[j];
-        }
-#else
+        double acc = 0.0, acc2 = 0.0;
         SegRegs<VT, 4> cur;
         if (quads > 0) seg_load_full<VT, 4>(cur, idx, val, b + lane * 4);
         for (int q = 0; q < quads; ++q) {
             SegRegs<VT, 4> nxt;
             if (q + 1 < quads) seg_load_full<VT, 4>(nxt, idx, val, b + ((int64_t)(q + 1) * 32 + lane) * 4);
-            double g[4];
+            if constexpr (TWO) {
+                double2 g[4];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) g[j] = sell_lookup(hot_at, n_hot, vm1, cur.idx[j]);
+                for (int j = 0; j < 4; ++j) {
+                    const int32_t k = cur.idx[j];
+                    g[j] = (uint32_t)k <= (uint32_t)n_hot ? lds_f64x2(hot_at + 16u * (uint32_t)k)
+                                                           : __ldg(reinterpret_cast<const double2 *>(vm1) + k);
+                }
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                if constexpr (std::is_same<VT, One>::value) acc += g[j];
-                else acc = fma(g[j], cur.value(j), acc);
+                for (int j = 0; j < 4; ++j) {
+                    if constexpr (std::is_same<VT, One>::value) {
+                        acc += g[j].x;
+                        acc2 += g[j].y;
+                    } else {
+                        acc = fma(g[j].x, cur.value(j), acc);
+                        acc2 = fma(g[j].y, cur.value(j), acc2);
+                    }
+                }
+            } else {
+                double g[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const int32_t k = cur.idx[j];
+                    g[j] = (uint32_t)k <= (uint32_t)n_hot ? lds_f64(hot_at + 8u * (uint32_t)k) : __ldg(vm1 + k);
+                }
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    if constexpr (std::is_same<VT, One>::value) acc += g[j];
+                    else acc = fma(g[j], cur.value(j), acc);
+                }
             }
             cur = nxt;
         }
-#endif
         const int64_t at = (sl << 5) + lane;
-        if (at < n) out[__ldg(perm + at)] = acc;
+        if (at < n) {
+            const int32_t row = __ldg(perm + at);
+            out[row] = acc;
+            if (TWO) out2[row] = acc2;
+        }
     }
 }
 
+template <typename VT, bool TWO>
+static int launch_sell(cudaStream_t s, int grid, size_t smem, const SellSide &sell, int64_t n, const double *vec, int n_hot,
+                       double *out, double *out2)
+{
+    if (smem > 48 * 1024 && cudaFuncSetAttribute(sell_rows_kernel<VT, TWO>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                 SEG_TABLE_BYTES) != cudaSuccess)
+        return -1;
+    sell_rows_kernel<VT, TWO><<<grid, SELL_THREADS, smem, s>>>(n, sell.n_slices, sell.idx, static_cast<const VT *>(sell.val),
+                                                               sell.base, sell.perm, vec, n_hot, out, out2);
+    return cudaGetLastError() == cudaSuccess ? 1 : -1;
+}
+
+// out2 != nullptr: vec holds (c, v) pairs and both dots are wanted
 int launch_sell_rows(cudaStream_t s, int sm_count, int value_bytes, const SellSide &sell, int64_t n, const double *vec,
-                     int64_t table_len, double *out)
+                     int64_t table_len, double *out, double *out2)
 {
     if (sell.n_slices <= 0) return 0;
-    const int64_t cap = SEG_TABLE_BYTES / 8 - 1;
+    const bool two = out2 != nullptr;
+    const int64_t cap = SEG_TABLE_BYTES / (two ? 16 : 8) - 1;
     const int n_hot = (int)(table_len < cap ? table_len : cap);
-    const size_t smem = 8 * (size_t)(n_hot + 1);
+    const size_t smem = (two ? 16 : 8) * (size_t)(n_hot + 1);
     const int64_t want = (sell.n_slices + SELL_THREADS / 32 - 1) / (SELL_THREADS / 32);
     const int grid = (int)(want < sm_count ? want : sm_count);
-#define PML_SELL_LAUNCH(VT)                                                                                             \
-    do {                                                                                                                \
-        if (smem > 48 * 1024 && cudaFuncSetAttribute(sell_rows_kernel<VT>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
-                                                     SEG_TABLE_BYTES) != cudaSuccess)                                   \
-            return -1;                                                                                                  \
-        sell_rows_kernel<VT><<<grid, SELL_THREADS, smem, s>>>(n, sell.n_slices, sell.idx, static_cast<const VT *>(sell.val), \
-                                                              sell.base, sell.perm, vec, n_hot, out);                   \
-    } while (0)
-    if (value_bytes == 0) PML_SELL_LAUNCH(One);
-    else if (value_bytes == 4) PML_SELL_LAUNCH(float);
-    else PML_SELL_LAUNCH(double);
-#undef PML_SELL_LAUNCH
-    return cudaGetLastError() == cudaSuccess ? 1 : -1;
+    if (value_bytes == 0)
+        return two ? launch_sell<One, true>(s, grid, smem, sell, n, vec, n_hot, out, out2)
+                   : launch_sell<One, false>(s, grid, smem, sell, n, vec, n_hot, out, out2);
+    if (value_bytes == 4)
+        return two ? launch_sell<float, true>(s, grid, smem, sell, n, vec, n_hot, out, out2)
+                   : launch_sell<float, false>(s, grid, smem, sell, n, vec, n_hot, out, out2);
+    return two ? launch_sell<double, true>(s, grid, smem, sell, n, vec, n_hot, out, out2)
+               : launch_sell<double, false>(s, grid, smem, sell, n, vec, n_hot, out, out2);
 }
 
 // ------------------------------------------------------------------------------------------

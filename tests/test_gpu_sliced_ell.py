@@ -4,7 +4,7 @@ the CPU oracle and against the entry-chunked pass it replaces for single-vector 
 Covered: all three value storages (indices only / fp32 / fp64), coefficients inside and beyond the shared-memory table,
 empty rows, a row count that is no multiple of 32, rows of very uneven length (the copy is then not built by default and
 built on request), the bank-aware entry order on and off, normalization, and every single-vector pass that runs on it
-(value+gradient, cached Hessian-vector, Hessian diagonal, scores).
+(value+gradient, cold and cached Hessian-vector, Hessian diagonal, scores).
 
 Reference semantics: the margin x_i . c of ValueAndGradientAggregator.add (lib/function/glm/ValueAndGradientAggregator.scala:
 132-153, via LabeledPoint.computeMargin, lib/data/LabeledPoint.scala:62), restated by oracle/glm_oracle.c.
@@ -65,7 +65,8 @@ def _check_all(pml, ds, ref, loss, rng, d, norm=None):
         f, g = ds.value_and_gradient(loss, w)
         assert abs(f - f_ref) <= TOL * abs(f_ref)
         assert util.rel_err(g, g_ref) <= TOL
-        ds.hessian_vector(loss, w, v, tag=9)                       # fills the curvature cache
+        # cold: the paired (c, v) pass, also one lane per row; with a tag it fills the curvature cache
+        assert util.rel_err(ds.hessian_vector(loss, w, v, tag=9), hv_ref) <= TOL
         hv = ds.hessian_vector(loss, w, v, tag=9)                  # cached: X v is a single-vector pass
         assert util.rel_err(hv, hv_ref) <= TOL
         diag = ds.hessian_diagonal(loss, w)
