@@ -695,8 +695,11 @@ def convergence(ctx, ds, d, host_rows=None):
 
     # (a) the reference's defaults (TRON.scala:97-98: 15 iterations): on this problem that is the iteration cap
     out["tron_configs1_poisson_l2_1_device_state"] = tron_device(1.0, 15)
-    # (b) the same problem run TO CONVERGENCE (cap lifted to 100; FunctionValuesConverged, Optimizer.scala:136-150)
-    out["tron_configs1_poisson_l2_1_device_state_to_convergence"] = tron_device(1.0, 100)
+    # (b) the same problem run TO CONVERGENCE (cap lifted to 300; FunctionValuesConverged, Optimizer.scala:136-150).  The
+    #     per-iteration decrease hovers around the stopping threshold (1e-5 of the value at zero) for dozens of
+    #     iterations on this ill-conditioned problem, so where exactly the run stops moves with the last bits of the
+    #     evaluations: 79 iterations with the entry-chunked margin pass, more with the one-lane-per-row pass.
+    out["tron_configs1_poisson_l2_1_device_state_to_convergence"] = tron_device(1.0, 300)
     # (c) a better conditioned setting, where the optimizer state in device memory and the drop-in shape (host vectors
     #     through the host-buffer ABI every evaluation, numpy optimizer state) can be compared count by count
     out["tron_configs1_poisson_l2_1000_device_state"] = tron_device(1000.0, 100)

@@ -730,7 +730,7 @@ int pml_dataset_create_csr_dev(pml_ctx *ctx, int64_t n, int32_t d, const int64_t
     if (!ds->keep_column_order && std::getenv("PML_NO_SELL") == nullptr) {
         const char *lim = std::getenv("PML_SELL_MAX_OVERHEAD"), *sig = std::getenv("PML_SELL_SIGMA_SHIFT");
         PML_TRY(build_sell(s, n, nnz, ds->row_ptr, ds->col, ds->val, dst_bytes, lim ? std::atof(lim) : 0.15,
-                           sig ? std::atoi(sig) : 13,
+                           sig ? std::atoi(sig) : 16,
                            std::getenv("PML_NO_SELL_BANK_ORDER") ? 0 : (int32_t)std::min<int64_t>(ds->t.m, SEG_TABLE_BYTES / 8 - 1),
                            &ds->sell));
         ds->bytes += ds->sell.bytes;

@@ -133,7 +133,7 @@ def test_rows_of_uneven_length(ctx, monkeypatch):
         seen.append(ds.info().sliced_ell_padding_permille)
         _check_all(pml, ds, ref, oracle.POISSON, rng, d)
         ds.close()
-    assert 0 <= seen[0] <= 150          # sorted by length inside windows of 8192 rows
+    assert 0 <= seen[0] <= 150          # sorted by length inside windows of 65 536 rows
     assert seen[1] == -1                # unsorted: too much padding, the entry-chunked stream serves the pass
     assert seen[2] > 150                # built on request all the same
     assert seen[3] == -1
